@@ -1,0 +1,101 @@
+"""ctypes binding of librmem_b200.so (the C ABI in include/rmem_b200.h).
+
+There is no fallback: if the shared library is missing or an entry point is absent, importing the
+ops raises.  ``build()`` compiles the library in-tree with nvcc for sm_100a (no GPU needed).
+"""
+import ctypes
+import os
+import subprocess
+import sys
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(_HERE, "librmem_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "rmem_b200.h")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-shared", "-Xcompiler", "-fPIC",
+]
+
+
+def sources():
+    return sorted(os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith(".cu"))
+
+
+def _stale():
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)] + [HEADER_PATH]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False):
+    """nvcc -> rmem_ocu_b200/librmem_b200.so (cross-compiles without a GPU)."""
+    if not force and not _stale():
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB_PATH] + sources()
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+        print(" ".join(cmd), file=sys.stderr)
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr, file=sys.stderr)
+    return LIB_PATH
+
+
+_lib = None
+
+_c_void_p = ctypes.c_void_p
+_c_int = ctypes.c_int
+_c_float = ctypes.c_float
+
+# name -> argtypes; every function returns int (status) unless listed in _RESTYPES
+_SIGNATURES = {
+    "rmem_abi_version": [],
+    "rmem_last_error": [],
+    "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
+    "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
+}
+_RESTYPES = {"rmem_last_error": ctypes.c_char_p}
+
+
+def declared_symbols():
+    """Entry points declared in include/rmem_b200.h (parsed, so tests can check the export list)."""
+    import re
+    with open(HEADER_PATH) as f:
+        text = f.read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rmem_[a-z0-9_]+)\s*\(", text)))
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "librmem_b200.so is not built (%s). Run `python -c 'import __graft_entry__ as g; "
+            "g.build()'`. There is no CPU or PyTorch fallback for the RMem hot path." % LIB_PATH)
+    handle = ctypes.CDLL(LIB_PATH)
+    for name, argtypes in _SIGNATURES.items():
+        fn = getattr(handle, name)  # AttributeError if the symbol is missing: fail loudly
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPES.get(name, _c_int)
+    _lib = handle
+    return _lib
+
+
+class RmemError(RuntimeError):
+    pass
+
+
+def check(status, what):
+    if status != 0:
+        msg = lib().rmem_last_error()
+        raise RmemError("%s failed (%d): %s" % (what, status, msg.decode() if msg else "?"))

@@ -1,0 +1,457 @@
+// Long-term (global) gated attention of the current frame's tokens against the restricted memory
+// bank -- DeAOT shape: 1 head, d_qk = 128, d_v = 1024 (V | ID_V), bf16 in, fp32 accumulate.
+//
+// Replaces the explicit softmax(QK^T)V path of GatedPropagation.forward
+// (reference aot_plus/networks/layers/attention.py:174-193) together with the attention-weight
+// recording of GatedPropagationModule.forward (layers/transformer.py:1185-1192) and the temporal
+// positional embedding on the bank keys (transformer.py:1140-1172).
+//
+// Decomposition (split-KV by memory frame):
+//   rmem_lt_attn_partial : grid (q_tile, dv_split, chunk).  One CTA owns 128 queries x 256 value
+//       channels x one key chunk (a memory frame, or a part of one).  TMA streams 64-key K/V tiles
+//       through a 3-stage ring, one elected thread issues tcgen05.mma (S = QK^T into a double
+//       buffered TMEM tile, O += P V into a 256-column TMEM accumulator), four softmax warps own
+//       one query row per thread (tcgen05.ld 32x32b), write bf16 P into a 128B-swizzled smem tile
+//       and rescale O lazily.  Output: un-normalised O, running max m (log2 units) and sum l.
+//   rmem_lt_attn_combine : merges the chunk partials, adds the per-frame TPE bias
+//       (q'.e_row -- a rank-1 term, so K is never rewritten), emits the per-frame attention mass
+//       W[q,t] (= record_attn_weight), applies the gate U and writes bf16.
+#include "sm100_ptx.cuh"
+#include "rmem_internal.h"
+
+namespace rmem {
+using namespace sm100;
+
+constexpr int kBlockM = 128;      // queries per CTA
+constexpr int kBlockN = 64;       // keys per pipeline tile
+constexpr int kDK = 128;          // d_att
+constexpr int kDV = 1024;         // expand_d_vu (V | ID_V)
+constexpr int kDVTile = 256;      // value channels per CTA (TMEM accumulator columns)
+constexpr int kDVSplits = kDV / kDVTile;
+constexpr int kStages = 3;
+constexpr int kThreads = 192;     // warp0 TMA, warp1 MMA, warps2-5 softmax/epilogue
+
+constexpr uint32_t kQBytes = kBlockM * kDK * 2;            // 32 KB  [2][128][64]
+constexpr uint32_t kKBytes = kBlockN * kDK * 2;            // 16 KB  [2][64][64]
+constexpr uint32_t kVBytes = kBlockN * kDVTile * 2;        // 32 KB  [4][64][64]
+constexpr uint32_t kStageBytes = kKBytes + kVBytes;        // 48 KB
+constexpr uint32_t kPBytes = kBlockM * kBlockN * 2;        // 16 KB  [128][64]
+constexpr uint32_t kSmemData = kQBytes + kStages * kStageBytes + 2 * kPBytes;
+constexpr uint32_t kSmemTotal = kSmemData + 1024 /*align slack*/ + 256 /*barriers*/;
+
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemS0 = 0;      // S buffers: 2 x 64 columns
+constexpr uint32_t kTmemO = 128;     // O: 256 columns
+
+constexpr float kRescaleThreshold = 8.0f;  // log2 units
+
+struct LtParams {
+  int L;                 // tokens per frame
+  int n_chunks;          // total key chunks = T * chunks_per_frame
+  int chunks_per_frame;
+  const int32_t* order;  // [T] logical bank position -> physical slot (device)
+  float* part_o;         // [n_chunks][L][1024]
+  float* part_m;         // [n_chunks][L]
+  float* part_l;         // [n_chunks][L]
+  float scale_log2;      // log2(e) / sqrt(d_att)
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
+                       const __grid_constant__ CUtensorMap tm_k,
+                       const __grid_constant__ CUtensorMap tm_v, const LtParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+  uint8_t* sQ = smem;
+  uint8_t* sKV = sQ + kQBytes;
+  uint8_t* sP = sKV + kStages * kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
+  uint64_t* q_full = bars + 0;
+  uint64_t* kv_full = bars + 1;            // [3]
+  uint64_t* kv_empty = bars + 4;           // [3]
+  uint64_t* s_full = bars + 7;             // [2]
+  uint64_t* p_full = bars + 9;             // [2]
+  uint64_t* pv_done = bars + 11;           // [2]
+  uint64_t* o_full = bars + 13;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q_tile = blockIdx.x;
+  const int dv_split = blockIdx.y;
+  const int chunk = blockIdx.z;
+
+  // key range of this chunk
+  const int frame_pos = chunk / p.chunks_per_frame;
+  const int sub = chunk - frame_pos * p.chunks_per_frame;
+  const int per = (p.L + p.chunks_per_frame - 1) / p.chunks_per_frame;
+  const int per_aligned = ((per + kBlockN - 1) / kBlockN) * kBlockN;
+  const int key_begin = sub * per_aligned;
+  int key_len = p.L - key_begin;
+  if (key_len > per_aligned) key_len = per_aligned;
+  if (key_len < 0) key_len = 0;
+  const int n_tiles = (key_len + kBlockN - 1) / kBlockN;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_v);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(kv_full + i, 1);
+      mbar_init(kv_empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(s_full + i, 1);
+      mbar_init(p_full + i, 128);
+      mbar_init(pv_done + i, 1);
+    }
+    mbar_init(o_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0 && n_tiles > 0) {   // never leave a bulk copy in flight when there is no consumer
+      const int slot = p.order[frame_pos];
+      mbar_expect_tx(q_full, kQBytes);
+      tma_load_3d(sQ, &tm_q, q_full, 0, q_tile * kBlockM, 0);
+      for (int j = 0; j < n_tiles; ++j) {
+        const int st = j % kStages;
+        if (j >= kStages) mbar_wait(kv_empty + st, ((j / kStages) - 1) & 1);
+        uint8_t* dK = sKV + st * kStageBytes;
+        uint8_t* dV = dK + kKBytes;
+        mbar_expect_tx(kv_full + st, kStageBytes);
+        tma_load_4d(dK, &tm_k, kv_full + st, 0, key_begin + j * kBlockN, 0, slot);
+        tma_load_4d(dV, &tm_v, kv_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0 && n_tiles > 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(kBlockM, kBlockN, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockM, kDVTile, 0, 1);
+      const uint32_t q_addr = smem_u32(sQ);
+      auto issue_qk = [&](int j) {
+        const int st = j % kStages;
+        mbar_wait(kv_full + st, (j / kStages) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(sKV + st * kStageBytes);
+        const uint32_t d = tmem_base + kTmemS0 + (j & 1) * kBlockN;
+#pragma unroll
+        for (int ks = 0; ks < kDK / 16; ++ks) {
+          const uint32_t blk = ks >> 2, within = ks & 3;
+          const uint64_t a = make_desc_sw128(q_addr + blk * (kBlockM * 128) + within * 32, 16, 1024);
+          const uint64_t b = make_desc_sw128(k_addr + blk * (kBlockN * 128) + within * 32, 16, 1024);
+          mma_bf16_ss(d, a, b, idesc_qk, ks > 0);
+        }
+        tc_commit(s_full + (j & 1));
+      };
+      mbar_wait(q_full, 0);
+      issue_qk(0);
+      for (int j = 0; j < n_tiles; ++j) {
+        if (j + 1 < n_tiles) issue_qk(j + 1);
+        mbar_wait(p_full + (j & 1), (j >> 1) & 1);
+        tc_fence_after();
+        const int st = j % kStages;
+        const uint32_t v_addr = smem_u32(sKV + st * kStageBytes + kKBytes);
+        const uint32_t p_addr = smem_u32(sP + (j & 1) * kPBytes);
+        const uint32_t d = tmem_base + kTmemO;
+#pragma unroll
+        for (int ks = 0; ks < kBlockN / 16; ++ks) {
+          const uint64_t a = make_desc_sw128(p_addr + ks * 32, 16, 1024);
+          const uint64_t b = make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024);
+          mma_bf16_ss(d, a, b, idesc_pv, (j > 0) || (ks > 0));
+        }
+        tc_commit(kv_empty + st);
+        tc_commit(pv_done + (j & 1));
+      }
+      tc_commit(o_full);
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + epilogue
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+    const int row = quarter * 32 + lane;          // query row inside the tile
+    const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+    const int q_global = q_tile * kBlockM + row;
+    float m_used = -INFINITY;
+    float l_sum = 0.f;
+    const float c = p.scale_log2;
+
+    for (int j = 0; j < n_tiles; ++j) {
+      mbar_wait(s_full + (j & 1), (j >> 1) & 1);
+      tc_fence_after();
+      uint32_t sr[2][32];
+      const uint32_t s_addr = tmem_base + lane_addr + kTmemS0 + (j & 1) * kBlockN;
+      tmem_ld32(s_addr, sr[0]);
+      tmem_ld32(s_addr + 32, sr[1]);
+      tmem_ld_wait();
+      const int valid = key_len - j * kBlockN;    // keys valid in this tile (>= 1)
+      float mx = -INFINITY;
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(sr[h][i]) * c;
+          if (h * 32 + i >= valid) s = -INFINITY;
+          sr[h][i] = __float_as_uint(s);
+          mx = fmaxf(mx, s);
+        }
+      // lazy rescale: keep the reference max unless it grew by more than the threshold
+      const bool grow = mx > m_used + kRescaleThreshold;
+      float scale = 1.f;
+      float m_new = m_used;
+      if (grow) {
+        m_new = mx;
+        scale = fast_exp2(m_used - m_new);            // 0 when m_used == -inf
+      }
+      if (j > 0 && __any_sync(0xffffffffu, grow)) {
+        mbar_wait(pv_done + ((j - 1) & 1), ((j - 1) >> 1) & 1);
+        tc_fence_after();
+        const uint32_t o_addr = tmem_base + lane_addr + kTmemO;
+#pragma unroll 1
+        for (int cb = 0; cb < kDVTile / 32; ++cb) {
+          uint32_t orow[32];
+          tmem_ld32(o_addr + cb * 32, orow);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) orow[i] = __float_as_uint(__uint_as_float(orow[i]) * scale);
+          tmem_st32(o_addr + cb * 32, orow);
+        }
+        tmem_st_wait();
+      }
+      l_sum *= scale;
+      m_used = m_new;
+      // P buffer (j&1) was last read by PV(j-2)
+      if (j >= 2) mbar_wait(pv_done + (j & 1), ((j - 2) >> 1) & 1);
+      uint8_t* pbuf = sP + (j & 1) * kPBytes;
+      float acc = 0.f;
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {              // 8 chunks of 8 keys (16 bytes of bf16)
+        uint32_t packed[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i0 = ch * 8 + e * 2;
+          const float p0 = fast_exp2(__uint_as_float(sr[i0 >> 5][i0 & 31]) - m_used);
+          const float p1 = fast_exp2(__uint_as_float(sr[(i0 + 1) >> 5][(i0 + 1) & 31]) - m_used);
+          const __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
+          // accumulate what the tensor core will actually see (bf16-rounded) so O / l is consistent
+          acc += __bfloat162float(b2.x) + __bfloat162float(b2.y);
+          packed[e] = *reinterpret_cast<const uint32_t*>(&b2);
+        }
+        *reinterpret_cast<uint4*>(pbuf + sw128_offset(row, ch)) =
+            make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      }
+      l_sum += acc;
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(p_full + (j & 1));
+    }
+
+    // epilogue: O (fp32, un-normalised) -> part_o ; m, l -> part_m / part_l
+    if (n_tiles > 0) {
+      mbar_wait(o_full, 0);
+      tc_fence_after();
+    }
+    const bool row_ok = q_global < p.L;
+    float* orow_g = p.part_o + (static_cast<size_t>(chunk) * p.L + (row_ok ? q_global : 0)) * kDV +
+                    dv_split * kDVTile;
+    const uint32_t o_addr = tmem_base + lane_addr + kTmemO;
+#pragma unroll 1
+    for (int cb = 0; cb < kDVTile / 32; ++cb) {
+      uint32_t orow[32];
+      if (n_tiles > 0) {
+        tmem_ld32(o_addr + cb * 32, orow);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) orow[i] = 0u;
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+          *reinterpret_cast<uint4*>(orow_g + cb * 32 + i) =
+              make_uint4(orow[i], orow[i + 1], orow[i + 2], orow[i + 3]);
+      }
+    }
+    if (row_ok && dv_split == 0) {
+      p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;
+      p.part_l[static_cast<size_t>(chunk) * p.L + q_global] = l_sum;
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// combine: out[q,:] = gate[q,:] * sum_c w_c O_c[q,:] / sum_c w_c l_c,  w_c = 2^(m_c + bias[q,row(t_c)] - M)
+//          W[q,t]   = sum_{c in frame t} w_c l_c / sum_c w_c l_c
+struct CombineParams {
+  int L, T, chunks_per_frame;
+  const float* part_o;
+  const float* part_m;
+  const float* part_l;
+  const float* tpe_bias;      // [L][4] (log2 units) or nullptr
+  int tpe_rows[RMEM_MAX_BANK];  // TPE table row per logical bank position
+  const __nv_bfloat16* gate;  // [L][1024] or nullptr
+  __nv_bfloat16* out;         // [L][1024]
+  float* attn_mass;           // [L][T] or nullptr
+};
+
+__global__ void __launch_bounds__(256)
+lt_attn_combine_kernel(const CombineParams p) {
+  const int q = blockIdx.x;
+  const int n_chunks = p.T * p.chunks_per_frame;
+  __shared__ float w_sh[RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME];
+  __shared__ float inv_sh;
+  if (threadIdx.x == 0) {
+    float mm[RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME];
+    float M = -INFINITY;
+    for (int c = 0; c < n_chunks; ++c) {
+      const int t = c / p.chunks_per_frame;
+      float m = p.part_m[static_cast<size_t>(c) * p.L + q];
+      const float l = p.part_l[static_cast<size_t>(c) * p.L + q];
+      if (p.tpe_bias) m += p.tpe_bias[q * 4 + p.tpe_rows[t]];
+      if (!(l > 0.f)) m = -INFINITY;               // empty chunk
+      mm[c] = m;
+      M = fmaxf(M, m);
+    }
+    float denom = 0.f;
+    for (int c = 0; c < n_chunks; ++c) {
+      const float w = (mm[c] == -INFINITY) ? 0.f : exp2f(mm[c] - M);
+      w_sh[c] = w;
+      denom += w * p.part_l[static_cast<size_t>(c) * p.L + q];
+    }
+    const float inv = 1.f / denom;
+    inv_sh = inv;
+    if (p.attn_mass) {
+      for (int t = 0; t < p.T; ++t) {
+        float s = 0.f;
+        for (int k = 0; k < p.chunks_per_frame; ++k) {
+          const int c = t * p.chunks_per_frame + k;
+          s += w_sh[c] * p.part_l[static_cast<size_t>(c) * p.L + q];
+        }
+        p.attn_mass[static_cast<size_t>(q) * p.T + t] = s * inv;
+      }
+    }
+  }
+  __syncthreads();
+  const float inv = inv_sh;
+  const int col = threadIdx.x * 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c = 0; c < n_chunks; ++c) {
+    const float w = w_sh[c];
+    if (w == 0.f) continue;
+    const float4 o = *reinterpret_cast<const float4*>(
+        p.part_o + (static_cast<size_t>(c) * p.L + q) * kDV + col);
+    acc.x += w * o.x; acc.y += w * o.y; acc.z += w * o.z; acc.w += w * o.w;
+  }
+  acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+  if (p.gate) {
+    const uint2 g = *reinterpret_cast<const uint2*>(p.gate + static_cast<size_t>(q) * kDV + col);
+    const __nv_bfloat162 g01 = *reinterpret_cast<const __nv_bfloat162*>(&g.x);
+    const __nv_bfloat162 g23 = *reinterpret_cast<const __nv_bfloat162*>(&g.y);
+    acc.x *= __bfloat162float(g01.x); acc.y *= __bfloat162float(g01.y);
+    acc.z *= __bfloat162float(g23.x); acc.w *= __bfloat162float(g23.y);
+  }
+  const __nv_bfloat162 o01 = __floats2bfloat162_rn(acc.x, acc.y);
+  const __nv_bfloat162 o23 = __floats2bfloat162_rn(acc.z, acc.w);
+  uint2 packed;
+  packed.x = *reinterpret_cast<const uint32_t*>(&o01);
+  packed.y = *reinterpret_cast<const uint32_t*>(&o23);
+  *reinterpret_cast<uint2*>(p.out + static_cast<size_t>(q) * kDV + col) = packed;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int encode_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes /*rank-1*/, const uint32_t* box) {
+  auto fn = get_tensor_map_encoder();
+  if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
+  uint32_t elem_strides[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims,
+                  strides_bytes, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled failed");
+  return RMEM_OK;
+}
+
+int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
+                           const int32_t* order_dev, int T, int L, int n_slots,
+                           int chunks_per_frame, float* part_o, float* part_m, float* part_l,
+                           cudaStream_t stream) {
+  if (T < 1 || T > RMEM_MAX_BANK || chunks_per_frame < 1 ||
+      chunks_per_frame > RMEM_MAX_CHUNKS_PER_FRAME || L < 1 || n_slots < T)
+    return set_error(RMEM_ERR_ARG, "lt_attn: bad T / L / chunks_per_frame / n_slots");
+  CUtensorMap tm_q, tm_k, tm_v;
+  {
+    const uint64_t dims[3] = {64, static_cast<uint64_t>(L), 2};
+    const uint64_t strides[2] = {kDK * 2, 128};
+    const uint32_t box[3] = {64, kBlockM, 2};
+    if (int e = encode_map(&tm_q, q, 3, dims, strides, box)) return e;
+  }
+  {
+    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), 2, static_cast<uint64_t>(n_slots)};
+    const uint64_t strides[3] = {kDK * 2, 128, static_cast<uint64_t>(L) * kDK * 2};
+    const uint32_t box[4] = {64, kBlockN, 2, 1};
+    if (int e = encode_map(&tm_k, kbank, 4, dims, strides, box)) return e;
+  }
+  {
+    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), kDV / 64, static_cast<uint64_t>(n_slots)};
+    const uint64_t strides[3] = {kDV * 2, 128, static_cast<uint64_t>(L) * kDV * 2};
+    const uint32_t box[4] = {64, kBlockN, kDVTile / 64, 1};
+    if (int e = encode_map(&tm_v, vbank, 4, dims, strides, box)) return e;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(lt_attn_partial_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
+    if (e != cudaSuccess) return set_cuda_error(e, "lt_attn: cudaFuncSetAttribute");
+    attr_set = true;
+  }
+  LtParams p;
+  p.L = L;
+  p.n_chunks = T * chunks_per_frame;
+  p.chunks_per_frame = chunks_per_frame;
+  p.order = order_dev;
+  p.part_o = part_o;
+  p.part_m = part_m;
+  p.part_l = part_l;
+  p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
+  dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, p.n_chunks);
+  lt_attn_partial_kernel<<<grid, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, p);
+  return check_launch("lt_attn_partial_kernel");
+}
+
+int lt_attn_combine_launch(const float* part_o, const float* part_m, const float* part_l,
+                           const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
+                           int chunks_per_frame, const void* gate, void* out, float* attn_mass,
+                           cudaStream_t stream) {
+  if (T < 1 || T > RMEM_MAX_BANK || chunks_per_frame < 1 ||
+      chunks_per_frame > RMEM_MAX_CHUNKS_PER_FRAME)
+    return set_error(RMEM_ERR_ARG, "lt_combine: bad T / chunks_per_frame");
+  CombineParams p;
+  p.L = L; p.T = T; p.chunks_per_frame = chunks_per_frame;
+  p.part_o = part_o; p.part_m = part_m; p.part_l = part_l;
+  p.tpe_bias = tpe_bias;
+  for (int t = 0; t < RMEM_MAX_BANK; ++t) p.tpe_rows[t] = (tpe_rows_host && t < T) ? tpe_rows_host[t] : 0;
+  p.gate = static_cast<const __nv_bfloat16*>(gate);
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.attn_mass = attn_mass;
+  lt_attn_combine_kernel<<<L, 256, 0, stream>>>(p);
+  return check_launch("lt_attn_combine_kernel");
+}
+
+}  // namespace rmem
