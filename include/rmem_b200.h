@@ -71,6 +71,133 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
                                int chunks_per_frame, const void* gate, void* out,
                                float* attn_mass, void* stream);
 
+
+/* ---------------------------------------------------------------------------------------------
+ * Linear layer with fused epilogue: C[M,N] = A[M,K] * W[N,K]^T + bias, then per column segment an
+ * activation and a destination (so one launch produces e.g. K | silu(V) | silu(U) into three
+ * buffers, or adds the projection straight into the fp32 residual streams).
+ * Replaces nn.Linear + silu / split / cat / residual adds in GatedPropagationModule.forward
+ * (layers/transformer.py:1104-1123, 1212-1232), GatedPropagation (attention.py:152-172, 209) and
+ * fuse_key_value_id (transformer.py:1238-1244).
+ *   a   bf16 [M][lda]   w  bf16 [N][ldw]   bias f32 [N] or NULL
+ */
+#define RMEM_GEMM_MAX_SEGMENTS 4
+#define RMEM_ACT_NONE 0
+#define RMEM_ACT_SILU 1
+#define RMEM_OUT_BF16 0       /* dst bf16, store          */
+#define RMEM_OUT_F32 1        /* dst f32, store           */
+#define RMEM_OUT_F32_ACCUM 2  /* dst f32, dst += value    */
+typedef struct rmem_gemm_segment {
+  int32_t col_begin;  /* first output column of the segment, multiple of 32 */
+  int32_t col_end;    /* one past the last output column                    */
+  int32_t act;        /* RMEM_ACT_*                                         */
+  int32_t mode;       /* RMEM_OUT_*                                         */
+  void* dst;          /* destination matrix                                  */
+  int32_t ld;         /* destination leading dimension (elements)           */
+  int32_t dst_col0;   /* destination column of col_begin                    */
+} rmem_gemm_segment;
+int rmem_linear(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N,
+                int K, const rmem_gemm_segment* segments_host, int n_segments, void* stream);
+
+/* LayerNorm over the last dim (C = 256) of up to two [L][C] streams in one launch, bf16 output
+ * written at a column offset of a wider buffer (so norm2 | id_norm2 land concatenated).
+ * Replaces nn.LayerNorm calls norm1 / id_norm1 / norm2 / id_norm2 (transformer.py:1104, 1120,
+ * 1223-1225) and DeAOT.get_id_emb's id_norm (models/deaot.py:65-69).
+ *   x{0,1}  f32 (in_bf16 = 0) or bf16 (in_bf16 = 1) [L][C];  gamma/beta f32 [C];  x1 may be NULL
+ */
+int rmem_layernorm(const void* x0, const float* gamma0, const float* beta0, void* out0, int ld0,
+                   int col0, const void* x1, const float* gamma1, const float* beta1, void* out1,
+                   int ld1, int col1, int L, int C, int in_bf16, void* stream);
+
+/* 5x5 depth-wise convolution over the (h, w) token grid, channels-last bf16, zero padding 2.
+ * Replaces DWConv2d.forward (layers/basic.py:38-57) behind the gate of GatedPropagation /
+ * LocalGatedPropagation (attention.py:208, 357).
+ *   x bf16 [h*w][ldx] (channels at col xcol0..xcol0+C)   wt f32 [25][C] (tap-major repack of
+ *   conv.weight [C,1,5,5])   y bf16 [h*w][ldy] at column ycol0
+ */
+int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                 int h, int w, int C, void* stream);
+
+/* GroupNorm over an [L][C] token matrix viewed as [1, C, L] (GroupNorm1D, layers/basic.py:6-12):
+ * statistics per group over (C/groups channels x L tokens).  Replaces DualBranchGPM's
+ * decoder_norms[-1] (transformer.py:806-808).  x = cat(x_a[L][Ca], x_b[L][C-Ca]) f32, out bf16.
+ *   workspace: 16 * groups bytes, 8-byte aligned (fp64 sum / sum of squares; zeroed by the call)
+ */
+int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const float* gamma,
+                          const float* beta, void* out, int L, int C, int groups, void* workspace,
+                          void* stream);
+
+/* Per-query temporal-PE score bias and the time-shifted query (transformer.py:1142-1172):
+ *   q_time = bf16(q + cur_pos_emb);  tpe_bias[q][r] = log2e/sqrt(C) * ((q + cur_pos_emb) . mem_pos_emb[r])
+ *   q bf16 [L][C] (C = 128);  cur_pos_emb f32 [C];  mem_pos_emb f32 [4][C]
+ */
+int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_pos_emb,
+                     void* q_time, float* tpe_bias, int L, int C, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Short-term local attention, DeAOT: 15x15 window (max_dis 7, dilation 1), 1 head, d_att 128,
+ * value width 1024.  Replaces LocalGatedPropagation.forward (layers/attention.py:289-361):
+ * F.unfold correlation (:331-335), relative-position bias (:314, 342), border mask (:305-312,
+ * 344), softmax over the 225 taps (:346), local2global scatter + dense matmul (:350-353, 363-402)
+ * and the gate (:355).
+ *
+ * Stage 1 (scores): probs[q][t] = softmax_t( q.k[nbr(q,t)]/sqrt(128) + rel_bias[q][t] ) over the
+ *   in-image taps (out-of-image taps get probability 0, as exp(-1e8) does in fp32).
+ *   q, k bf16 [h*w][128];  rel_bias f32 [h*w][ld_rel] (= q W_rel^T + b_rel, from rmem_linear);
+ *   probs f32 [h*w][225]  (this is local_attn[0,0,:,q] of the reference, transposed)
+ * Stage 2 (aggregate): out[q][c] = gate[q][c] * sum_t probs[q][t] * v[nbr(q,t)][c]
+ *   v bf16 [h*w][1024];  gate bf16 [h*w][1024] or NULL;  out bf16 [h*w][1024]
+ */
+int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, int ld_rel,
+                           float* probs, int h, int w, void* stream);
+int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gate, void* out,
+                              int h, int w, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Restricted long-term bank.  State lives on the device so the frame loop never synchronises:
+ *   order     i32 [RMEM_MAX_BANK]  logical position (oldest first) -> slot; order[T..] = free slots
+ *   frame_id  i32 [RMEM_MAX_BANK]  per SLOT: frame_step stored there
+ *   ema       f32 [RMEM_MAX_BANK]  per SLOT: moving-mean relevance (stored_attn_weight_dict)
+ *   ema_valid i32 [RMEM_MAX_BANK]  per SLOT: 1 once the slot has a stored relevance
+ *   times     i32 [RMEM_MAX_BANK]  per SLOT: UCB visit count (stored_frame_times)
+ * laid out consecutively in one int32/f32 block of RMEM_BANK_STATE_WORDS words.
+ */
+#define RMEM_BANK_STATE_WORDS (5 * RMEM_MAX_BANK + 8)
+/* words [5*RMEM_MAX_BANK ..): 0 = last drop index (logical, -1 none), 1 = dropped frame id,
+ * 2 = decision margin (f32 bits), 3 = number of evictions so far, 4 = argmin of the last scoring
+ * pass (set even when nothing had to be dropped) */
+
+/* Reset the state for a new sequence: order = identity, slot 0 holds the reference frame
+ * (init_memory, transformer.py:438-443 / 993-998 + aot_engine.py:321-323). */
+int rmem_bank_init(void* bank_state, int frame_step, void* stream);
+
+/* Append: copy the candidate rows into the free slot order[T] of every bank tensor and stamp
+ * frame_id. Replaces update_long_term_memory (transformer.py:306-322, 859-878) -- torch.cat
+ * re-allocation becomes one strided copy.  n_tensors <= 8.
+ *   src_host / dst_host: HOST arrays of device pointers; row_bytes_host: bytes per slot.
+ */
+int rmem_bank_append(void* bank_state, int T, int frame_step, const void* const* src_host,
+                     void* const* dst_host, const int64_t* row_bytes_host, int n_tensors,
+                     void* stream);
+
+/* Relevance + freshness scoring and eviction, in place (restrict_long_memories,
+ * transformer.py:324-436 AOT / 880-991 DeAOT, use_atten_weight=True):
+ *   s_t = sum_q W[q,t] fg[q]; r = s / sum s; EMA 0.2/0.8 with the stored value of the same frame;
+ *   times += 1 for all T_old+1 frames; n_t = times (n_0 = T_old); bonus = 1.5 sqrt(log(sum n)/(n+8));
+ *   drop = 1 + argmin_{t>=1}(r_t + bonus_t); if T_old + 1 > capacity: remove position `drop`
+ *   from `order` (later positions shift down, the slot becomes free) and clear its statistics.
+ * attn_mass f32 [L][T_old] (layer-0 record_attn_weight), fg f32 [L] or NULL.
+ * The AOT variant returns before any statistics while the bank is filling (transformer.py:332-334):
+ * its caller simply does not call this function until T_old + 1 > capacity.
+ */
+int rmem_bank_score_evict(void* bank_state, const float* attn_mass, const float* fg, int L,
+                          int T_old, int capacity, void* stream);
+
+/* fg[q] = 1 - softmax_c(bilinear_align_corners(pred_id_logits -> (h,w)))[0]
+ * (aot_engine.py:355-362).  logits f32 [C][Hs][Ws] -> fg f32 [h*w]. */
+int rmem_foreground_prob(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

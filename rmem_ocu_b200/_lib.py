@@ -61,7 +61,34 @@ _SIGNATURES = {
     "rmem_last_error": [],
     "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
+    "rmem_linear": [_c_void_p, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_int,
+                    _c_void_p, _c_int, _c_void_p],
+    "rmem_layernorm": [_c_void_p] * 4 + [_c_int] * 2 + [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p],
+    "rmem_dwconv5": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int,
+                     _c_int, _c_void_p],
+    "rmem_groupnorm_tokens": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p] * 2,
+    "rmem_tpe_prepare": [_c_void_p] * 5 + [_c_int] * 2 + [_c_void_p],
+    "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_int, _c_int, _c_void_p],
+    "rmem_local_attn_aggregate": [_c_void_p] * 4 + [_c_int, _c_int, _c_void_p],
+    "rmem_bank_init": [_c_void_p, _c_int, _c_void_p],
+    "rmem_bank_append": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p],
+    "rmem_bank_score_evict": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
+    "rmem_foreground_prob": [_c_void_p] + [_c_int] * 3 + [_c_void_p, _c_int, _c_int, _c_void_p],
 }
+
+
+class GemmSegment(ctypes.Structure):
+    """rmem_gemm_segment (include/rmem_b200.h)."""
+    _fields_ = [("col_begin", ctypes.c_int32), ("col_end", ctypes.c_int32), ("act", ctypes.c_int32),
+                ("mode", ctypes.c_int32), ("dst", ctypes.c_void_p), ("ld", ctypes.c_int32),
+                ("dst_col0", ctypes.c_int32)]
+
+
+MAX_BANK = 16
+MAX_CHUNKS_PER_FRAME = 4
+BANK_STATE_WORDS = 5 * MAX_BANK + 8
+ACT_NONE, ACT_SILU = 0, 1
+OUT_BF16, OUT_F32, OUT_F32_ACCUM = 0, 1, 2
 _RESTYPES = {"rmem_last_error": ctypes.c_char_p}
 
 

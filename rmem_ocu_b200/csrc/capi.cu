@@ -63,4 +63,55 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
                                 static_cast<cudaStream_t>(stream));
 }
 
+#define ST(s) static_cast<cudaStream_t>(s)
+
+int rmem_linear(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N,
+                int K, const rmem_gemm_segment* segments_host, int n_segments, void* stream) {
+  return gemm_launch(a, lda, w, ldw, bias, M, N, K, segments_host, n_segments, ST(stream));
+}
+int rmem_layernorm(const void* x0, const float* gamma0, const float* beta0, void* out0, int ld0,
+                   int col0, const void* x1, const float* gamma1, const float* beta1, void* out1,
+                   int ld1, int col1, int L, int C, int in_bf16, void* stream) {
+  return layernorm_launch(x0, gamma0, beta0, out0, ld0, col0, x1, gamma1, beta1, out1, ld1, col1, L, C,
+                          in_bf16, ST(stream));
+}
+int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                 int h, int w, int C, void* stream) {
+  return dwconv5_launch(x, ldx, xcol0, wt, y, ldy, ycol0, h, w, C, ST(stream));
+}
+int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const float* gamma,
+                          const float* beta, void* out, int L, int C, int groups, void* workspace,
+                          void* stream) {
+  return groupnorm_tokens_launch(x_a, Ca, x_b, gamma, beta, out, L, C, groups, workspace, ST(stream));
+}
+int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_pos_emb,
+                     void* q_time, float* tpe_bias, int L, int C, void* stream) {
+  return tpe_prepare_launch(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias, L, C, ST(stream));
+}
+int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, int ld_rel,
+                           float* probs, int h, int w, void* stream) {
+  return local_scores_launch(q, k, rel_bias, ld_rel, probs, h, w, ST(stream));
+}
+int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gate, void* out,
+                              int h, int w, void* stream) {
+  return local_aggregate_launch(probs, v, gate, out, h, w, ST(stream));
+}
+int rmem_bank_init(void* bank_state, int frame_step, void* stream) {
+  return bank_init_launch(bank_state, frame_step, ST(stream));
+}
+int rmem_bank_append(void* bank_state, int T, int frame_step, const void* const* src_host,
+                     void* const* dst_host, const int64_t* row_bytes_host, int n_tensors,
+                     void* stream) {
+  return bank_append_launch(bank_state, T, frame_step, src_host, dst_host, row_bytes_host, n_tensors,
+                            ST(stream));
+}
+int rmem_bank_score_evict(void* bank_state, const float* attn_mass, const float* fg, int L,
+                          int T_old, int capacity, void* stream) {
+  return bank_score_evict_launch(bank_state, attn_mass, fg, L, T_old, capacity, ST(stream));
+}
+int rmem_foreground_prob(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
+                         void* stream) {
+  return foreground_prob_launch(logits, C, Hs, Ws, fg, h, w, ST(stream));
+}
+
 }  // extern "C"

@@ -1,0 +1,287 @@
+// Normalisation / element-wise kernels of the propagation block (HBM/L2-bound, vectorised,
+// coalesced): LayerNorm (dual stream, bf16 out at a column offset), 5x5 depth-wise conv over the
+// token grid, token GroupNorm, TPE query preparation, foreground probability for the eviction rule.
+#include <cuda_bf16.h>
+#include "rmem_internal.h"
+
+namespace rmem {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm, C = 256: one warp per row, 8 channels per lane. Two streams per launch (blockIdx.y).
+struct LnStream {
+  const void* x;
+  const float* gamma;
+  const float* beta;
+  __nv_bfloat16* out;
+  int ld, col0;
+};
+struct LnParams {
+  LnStream s[2];
+  int L, in_bf16;
+};
+
+__global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
+  const LnStream st = p.s[blockIdx.y];
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= p.L) return;
+  float v[8];
+  if (p.in_bf16) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(st.x) +
+                                                      static_cast<size_t>(row) * 256 + lane * 8);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __bfloat162float(h[i].x);
+      v[2 * i + 1] = __bfloat162float(h[i].y);
+    }
+  } else {
+    const float4* px = reinterpret_cast<const float4*>(static_cast<const float*>(st.x) +
+                                                       static_cast<size_t>(row) * 256 + lane * 8);
+    const float4 a = px[0], b = px[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { const float d = v[i] - mean; q += d * d; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + 1e-5f);
+  const float4 g0 = *reinterpret_cast<const float4*>(st.gamma + lane * 8);
+  const float4 g1 = *reinterpret_cast<const float4*>(st.gamma + lane * 8 + 4);
+  const float4 b0 = *reinterpret_cast<const float4*>(st.beta + lane * 8);
+  const float4 b1 = *reinterpret_cast<const float4*>(st.beta + lane * 8 + 4);
+  const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+  const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+  uint4 pk;
+  __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    o[i] = __floats2bfloat162_rn((v[2 * i] - mean) * rstd * g[2 * i] + b[2 * i],
+                                 (v[2 * i + 1] - mean) * rstd * g[2 * i + 1] + b[2 * i + 1]);
+  *reinterpret_cast<uint4*>(st.out + static_cast<size_t>(row) * st.ld + st.col0 + lane * 8) = pk;
+}
+
+int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
+                     const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
+                     int L, int C, int in_bf16, cudaStream_t stream) {
+  if (C != 256 || L < 1 || (ld0 % 8) || (c0 % 8) || (x1 && ((ld1 % 8) || (c1 % 8))))
+    return set_error(RMEM_ERR_ARG, "layernorm: C must be 256 and ld/col offsets multiples of 8");
+  LnParams p;
+  p.L = L; p.in_bf16 = in_bf16;
+  p.s[0] = {x0, g0, b0, static_cast<__nv_bfloat16*>(o0), ld0, c0};
+  p.s[1] = {x1, g1, b1, static_cast<__nv_bfloat16*>(o1), ld1, c1};
+  dim3 grid((L + 7) / 8, x1 ? 2 : 1);
+  layernorm256_kernel<<<grid, 256, 0, stream>>>(p);
+  return check_launch("layernorm256_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// 5x5 depth-wise conv, channels-last. Thread = (pixel, 8 channels); weights tap-major [25][C].
+__global__ void __launch_bounds__(128)
+dwconv5_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int xcol0, const float* __restrict__ wt,
+               __nv_bfloat16* __restrict__ y, int ldy, int ycol0, int h, int w, int C) {
+  const int cg = C / 8;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= h * w * cg) return;
+  const int c = (idx % cg) * 8;
+  const int pix = idx / cg;
+  const int py = pix / w, px = pix - py * w;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int dy = 0; dy < 5; ++dy) {
+    const int yy = py + dy - 2;
+    if (yy < 0 || yy >= h) continue;
+#pragma unroll
+    for (int dx = 0; dx < 5; ++dx) {
+      const int xx = px + dx - 2;
+      if (xx < 0 || xx >= w) continue;
+      const uint4 raw = *reinterpret_cast<const uint4*>(
+          x + static_cast<size_t>(yy * w + xx) * ldx + xcol0 + c);
+      const __nv_bfloat162* hv = reinterpret_cast<const __nv_bfloat162*>(&raw);
+      const float4 w0 = *reinterpret_cast<const float4*>(wt + (dy * 5 + dx) * C + c);
+      const float4 w1 = *reinterpret_cast<const float4*>(wt + (dy * 5 + dx) * C + c + 4);
+      acc[0] += __bfloat162float(hv[0].x) * w0.x; acc[1] += __bfloat162float(hv[0].y) * w0.y;
+      acc[2] += __bfloat162float(hv[1].x) * w0.z; acc[3] += __bfloat162float(hv[1].y) * w0.w;
+      acc[4] += __bfloat162float(hv[2].x) * w1.x; acc[5] += __bfloat162float(hv[2].y) * w1.y;
+      acc[6] += __bfloat162float(hv[3].x) * w1.z; acc[7] += __bfloat162float(hv[3].y) * w1.w;
+    }
+  }
+  uint4 pk;
+  __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) o[i] = __floats2bfloat162_rn(acc[2 * i], acc[2 * i + 1]);
+  *reinterpret_cast<uint4*>(y + static_cast<size_t>(pix) * ldy + ycol0 + c) = pk;
+}
+
+int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                   int h, int w, int C, cudaStream_t stream) {
+  if ((C % 8) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1)
+    return set_error(RMEM_ERR_ARG, "dwconv5: C / ld / col offsets must be multiples of 8");
+  const int n = h * w * (C / 8);
+  dwconv5_kernel<<<(n + 127) / 128, 128, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(x), ldx, xcol0, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0,
+      h, w, C);
+  return check_launch("dwconv5_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// Token GroupNorm (GroupNorm1D): pass 1 accumulates per-group sum / sum-of-squares in fp64 atomics,
+// pass 2 normalises. x = cat(x_a [L][Ca], x_b [L][C-Ca]).
+__global__ void __launch_bounds__(256)
+gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int L, int C,
+                int groups, double* __restrict__ ws) {
+  // block handles 8 rows; thread t covers channels t, t+256, ... (C <= 1024)
+  const int cpg = C / groups;
+  __shared__ float sh_s[8][8], sh_q[8][8];   // [group][warp]
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int r = 0; r < 8; ++r) {
+    const int row = blockIdx.x * 8 + r;
+    if (row >= L) break;
+    int k = 0;
+    for (int c = threadIdx.x; c < C; c += 256, ++k) {
+      const float v = c < Ca ? xa[static_cast<size_t>(row) * Ca + c]
+                             : xb[static_cast<size_t>(row) * (C - Ca) + (c - Ca)];
+      s[k] += v; q[k] += v * v;
+    }
+  }
+  // channel c = threadIdx.x + 256*k belongs to group c / cpg; reduce per (k) then add to its group.
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < 64) { sh_s[threadIdx.x >> 3][threadIdx.x & 7] = 0.f; sh_q[threadIdx.x >> 3][threadIdx.x & 7] = 0.f; }
+  __syncthreads();
+  int k = 0;
+  for (int c0 = 0; c0 < C; c0 += 256, ++k) {
+    // all lanes of a warp share the group when cpg is a multiple of 32
+    const int g = (c0 + warp * 32) / cpg;
+    const float ws_ = warp_sum(s[k]), wq_ = warp_sum(q[k]);
+    if (lane == 0) { atomicAdd(&sh_s[g][warp], ws_); atomicAdd(&sh_q[g][warp], wq_); }
+  }
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    double ts = 0.0, tq = 0.0;
+    for (int wv = 0; wv < 8; ++wv) { ts += sh_s[threadIdx.x][wv]; tq += sh_q[threadIdx.x][wv]; }
+    atomicAdd(ws + 2 * threadIdx.x, ts);
+    atomicAdd(ws + 2 * threadIdx.x + 1, tq);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb,
+                const float* __restrict__ gamma, const float* __restrict__ beta,
+                __nv_bfloat16* __restrict__ out, int L, int C, int groups, const double* __restrict__ ws) {
+  const int cpg = C / groups;
+  const double cnt = static_cast<double>(cpg) * L;
+  const size_t total = static_cast<size_t>(L) * C;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(i / C), c = static_cast<int>(i - static_cast<size_t>(row) * C);
+    const int g = c / cpg;
+    const double mean = ws[2 * g] / cnt;
+    const double var = ws[2 * g + 1] / cnt - mean * mean;
+    const float rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
+    const float v = c < Ca ? xa[static_cast<size_t>(row) * Ca + c]
+                           : xb[static_cast<size_t>(row) * (C - Ca) + (c - Ca)];
+    out[i] = __float2bfloat16((v - static_cast<float>(mean)) * rstd * gamma[c] + beta[c]);
+  }
+}
+
+int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
+                            const float* beta, void* out, int L, int C, int groups, void* workspace,
+                            cudaStream_t stream) {
+  if (groups < 1 || groups > 8 || C > 1024 || (C % groups) || ((C / groups) % 32) || Ca > C ||
+      (Ca < C && !xb))
+    return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
+  cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 2 * groups, stream);
+  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_tokens: memset");
+  gn_stats_kernel<<<(L + 7) / 8, 256, 0, stream>>>(xa, Ca, xb, L, C, groups,
+                                                    static_cast<double*>(workspace));
+  if (int r = check_launch("gn_stats_kernel")) return r;
+  gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta, static_cast<__nv_bfloat16*>(out), L,
+                                           C, groups, static_cast<const double*>(workspace));
+  return check_launch("gn_apply_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// TPE preparation: q_time = bf16(q + cur), bias[q][r] = log2e/sqrt(C) * ((q + cur) . mem[r]).  C = 128.
+__global__ void __launch_bounds__(256)
+tpe_prepare_kernel(const __nv_bfloat16* __restrict__ q, const float* __restrict__ cur,
+                   const float* __restrict__ mem, __nv_bfloat16* __restrict__ q_time,
+                   float* __restrict__ bias, int L, float scale) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= L) return;
+  const uint2 raw = *reinterpret_cast<const uint2*>(q + static_cast<size_t>(row) * 128 + lane * 4);
+  const __nv_bfloat162* hv = reinterpret_cast<const __nv_bfloat162*>(&raw);
+  const float4 c4 = *reinterpret_cast<const float4*>(cur + lane * 4);
+  float v[4] = {__bfloat162float(hv[0].x) + c4.x, __bfloat162float(hv[0].y) + c4.y,
+                __bfloat162float(hv[1].x) + c4.z, __bfloat162float(hv[1].y) + c4.w};
+  uint2 pk;
+  __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
+  o[0] = __floats2bfloat162_rn(v[0], v[1]);
+  o[1] = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(q_time + static_cast<size_t>(row) * 128 + lane * 4) = pk;
+  // the bias uses the same bf16-rounded q' the tensor cores will see, so both score terms agree
+  const float r0 = __bfloat162float(o[0].x), r1 = __bfloat162float(o[0].y);
+  const float r2 = __bfloat162float(o[1].x), r3 = __bfloat162float(o[1].y);
+#pragma unroll
+  for (int r = 0; r < RMEM_TPE_ROWS; ++r) {
+    const float4 m4 = *reinterpret_cast<const float4*>(mem + r * 128 + lane * 4);
+    const float d = warp_sum(r0 * m4.x + r1 * m4.y + r2 * m4.z + r3 * m4.w);
+    if (lane == 0) bias[row * RMEM_TPE_ROWS + r] = d * scale;
+  }
+}
+
+int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* q_time, float* bias,
+                       int L, int C, cudaStream_t stream) {
+  if (C != 128) return set_error(RMEM_ERR_ARG, "tpe_prepare: C must be 128");
+  tpe_prepare_kernel<<<(L + 7) / 8, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(q), cur, mem, static_cast<__nv_bfloat16*>(q_time), bias, L,
+      1.4426950408889634f / sqrtf(128.f));
+  return check_launch("tpe_prepare_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// fg[q] = 1 - softmax_c(bilinear(align_corners=True) logits)[0]  (aot_engine.py:355-362)
+__global__ void __launch_bounds__(128)
+foreground_prob_kernel(const float* __restrict__ logits, int C, int Hs, int Ws, float* __restrict__ fg,
+                       int h, int w) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= h * w) return;
+  const int y = i / w, x = i - y * w;
+  const float sy = h > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(h - 1) : 0.f;
+  const float sx = w > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(w - 1) : 0.f;
+  const float fy = sy * y, fx = sx * x;
+  const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
+  const int y1 = min(y0 + 1, Hs - 1), x1 = min(x0 + 1, Ws - 1);
+  const float ly = fy - y0, lx = fx - x0;
+  float mx = -INFINITY, v0 = 0.f;
+  float vals[16];
+  for (int c = 0; c < C; ++c) {
+    const float* pl = logits + static_cast<size_t>(c) * Hs * Ws;
+    const float v = (1.f - ly) * ((1.f - lx) * pl[y0 * Ws + x0] + lx * pl[y0 * Ws + x1]) +
+                    ly * ((1.f - lx) * pl[y1 * Ws + x0] + lx * pl[y1 * Ws + x1]);
+    vals[c] = v;
+    mx = fmaxf(mx, v);
+    if (c == 0) v0 = v;
+  }
+  float den = 0.f;
+  for (int c = 0; c < C; ++c) den += expf(vals[c] - mx);
+  fg[i] = 1.f - expf(v0 - mx) / den;
+}
+
+int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
+                           cudaStream_t stream) {
+  if (C < 1 || C > 16) return set_error(RMEM_ERR_ARG, "foreground_prob: C must be in [1,16]");
+  foreground_prob_kernel<<<(h * w + 127) / 128, 128, 0, stream>>>(logits, C, Hs, Ws, fg, h, w);
+  return check_launch("foreground_prob_kernel");
+}
+
+}  // namespace rmem

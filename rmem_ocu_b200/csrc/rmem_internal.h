@@ -28,4 +28,28 @@ int lt_attn_combine_launch(const float* part_o, const float* part_m, const float
                            int chunks_per_frame, const void* gate, void* out, float* attn_mass,
                            cudaStream_t stream);
 
+int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
+                const rmem_gemm_segment* segs, int n_seg, cudaStream_t stream);
+int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
+                     const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
+                     int L, int C, int in_bf16, cudaStream_t stream);
+int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                   int h, int w, int C, cudaStream_t stream);
+int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
+                            const float* beta, void* out, int L, int C, int groups, void* workspace,
+                            cudaStream_t stream);
+int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* q_time, float* bias,
+                       int L, int C, cudaStream_t stream);
+int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
+                           cudaStream_t stream);
+int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, int h,
+                        int w, cudaStream_t stream);
+int local_aggregate_launch(const float* probs, const void* v, const void* gate, void* out, int h, int w,
+                           cudaStream_t stream);
+int bank_init_launch(void* state, int frame_step, cudaStream_t stream);
+int bank_append_launch(void* state, int T, int frame_step, const void* const* src, void* const* dst,
+                       const int64_t* row_bytes, int n_tensors, cudaStream_t stream);
+int bank_score_evict_launch(void* state, const float* attn_mass, const float* fg, int L, int T_old,
+                            int capacity, cudaStream_t stream);
+
 }  // namespace rmem

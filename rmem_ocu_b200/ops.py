@@ -1,0 +1,125 @@
+"""Thin Python wrappers over the C ABI: torch tensors in, raw device pointers out.
+
+PyTorch is used for device memory and streams only; every function here launches hand-written
+sm_100a kernels from librmem_b200.so on the current CUDA stream.  No fallbacks.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import (ACT_NONE, ACT_SILU, OUT_BF16, OUT_F32, OUT_F32_ACCUM, GemmSegment)  # noqa: F401
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.RmemError("rmem ops need CUDA tensors (there is no CPU path)")
+
+
+# ---------------------------------------------------------------------------------------------
+def linear(a, w, bias, segments, M=None):
+    """C = a @ w.T + bias with a segmented epilogue.
+
+    a: bf16 [M, K] (row stride may exceed K); w: bf16 [N, K]; bias: f32 [N] or None;
+    segments: list of (col_begin, col_end, act, mode, dst_tensor, dst_col0)."""
+    _chk_cuda(a, w)
+    M = a.shape[0] if M is None else M
+    K = a.shape[1]
+    N = w.shape[0]
+    segs = (GemmSegment * len(segments))()
+    for i, (c0, c1, act, mode, dst, dcol) in enumerate(segments):
+        segs[i] = GemmSegment(c0, c1, act, mode, dst.data_ptr(), dst.stride(0), dcol)
+    _lib.check(_lib.lib().rmem_linear(_p(a), a.stride(0), _p(w), w.stride(0), _p(bias), M, N, K,
+                                      ctypes.cast(segs, ctypes.c_void_p), len(segments), _stream()),
+               "rmem_linear")
+
+
+def layernorm(x0, g0, b0, out0, col0=0, x1=None, g1=None, b1=None, out1=None, col1=0):
+    """LayerNorm(256) of one or two [L,256] streams (f32 or bf16 in), bf16 out at a column offset."""
+    _chk_cuda(x0, out0)
+    L, C = x0.shape
+    in_bf16 = 1 if x0.dtype == torch.bfloat16 else 0
+    _lib.check(_lib.lib().rmem_layernorm(_p(x0), _p(g0), _p(b0), _p(out0), out0.stride(0), col0,
+                                         _p(x1), _p(g1), _p(b1), _p(out1),
+                                         out1.stride(0) if out1 is not None else 0, col1, L, C, in_bf16,
+                                         _stream()), "rmem_layernorm")
+
+
+def dwconv5(x, xcol0, wt, y, ycol0, h, w, C):
+    _lib.check(_lib.lib().rmem_dwconv5(_p(x), x.stride(0), xcol0, _p(wt), _p(y), y.stride(0), ycol0, h, w, C,
+                                       _stream()), "rmem_dwconv5")
+
+
+def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
+    L, Ca = xa.shape
+    C = Ca + (xb.shape[1] if xb is not None else 0)
+    _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), L, C,
+                                                groups, _p(workspace), _stream()), "rmem_groupnorm_tokens")
+
+
+def tpe_prepare(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias):
+    L, C = q.shape
+    _lib.check(_lib.lib().rmem_tpe_prepare(_p(q), _p(cur_pos_emb), _p(mem_pos_emb), _p(q_time), _p(tpe_bias),
+                                           L, C, _stream()), "rmem_tpe_prepare")
+
+
+# ---------------------------------------------------------------------------------------------
+def lt_attn_partial(q, kbank, vbank, order, T, cpf, part_o, part_m, part_l):
+    L = q.shape[0]
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_partial(_p(q), _p(kbank), _p(vbank), _p(order), T, L,
+                                                     kbank.shape[0], cpf, _p(part_o), _p(part_m), _p(part_l),
+                                                     _stream()), "rmem_lt_attn_deaot_partial")
+
+
+def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate, out, attn_mass):
+    rows = (ctypes.c_int32 * max(T, 1))(*(tpe_rows if tpe_rows is not None else [0] * T))
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_combine(_p(part_o), _p(part_m), _p(part_l), _p(tpe_bias),
+                                                     ctypes.cast(rows, ctypes.c_void_p), T, L, cpf, _p(gate),
+                                                     _p(out), _p(attn_mass), _stream()),
+               "rmem_lt_attn_deaot_combine")
+
+
+def local_attn_scores(q, k, rel_bias, probs, h, w):
+    _lib.check(_lib.lib().rmem_local_attn_scores(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs), h, w,
+                                                 _stream()), "rmem_local_attn_scores")
+
+
+def local_attn_aggregate(probs, v, gate, out, h, w):
+    _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(probs), _p(v), _p(gate), _p(out), h, w, _stream()),
+               "rmem_local_attn_aggregate")
+
+
+# ---------------------------------------------------------------------------------------------
+def bank_init(state, frame_step):
+    _lib.check(_lib.lib().rmem_bank_init(_p(state), frame_step, _stream()), "rmem_bank_init")
+
+
+def bank_append(state, T, frame_step, srcs, dsts):
+    """Copy each src tensor (one slot's worth) into slot order[T] of the matching bank tensor."""
+    n = len(srcs)
+    sp = (ctypes.c_void_p * n)(*[s.data_ptr() for s in srcs])
+    dp = (ctypes.c_void_p * n)(*[d.data_ptr() for d in dsts])
+    rb = (ctypes.c_int64 * n)(*[s.numel() * s.element_size() for s in srcs])
+    _lib.check(_lib.lib().rmem_bank_append(_p(state), T, frame_step, ctypes.cast(sp, ctypes.c_void_p),
+                                           ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(rb, ctypes.c_void_p),
+                                           n, _stream()), "rmem_bank_append")
+
+
+def bank_score_evict(state, attn_mass, fg, L, T_old, capacity):
+    _lib.check(_lib.lib().rmem_bank_score_evict(_p(state), _p(attn_mass), _p(fg), L, T_old, capacity,
+                                                _stream()), "rmem_bank_score_evict")
+
+
+def foreground_prob(logits, fg, h, w):
+    C, Hs, Ws = logits.shape[-3:]
+    _lib.check(_lib.lib().rmem_foreground_prob(_p(logits), C, Hs, Ws, _p(fg), h, w, _stream()),
+               "rmem_foreground_prob")

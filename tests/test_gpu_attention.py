@@ -1,0 +1,133 @@
+"""Parity of the attention kernels and the bank kernels against the oracle (oracle/restate.py)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)).item()
+
+
+def _lt_run(q, kb, vb, order, T, cpf, bias=None, rows=None, gate=None):
+    from rmem_ocu_b200 import ops
+    L = q.shape[0]
+    nch = T * cpf
+    po = torch.empty(nch, L, 1024, device="cuda")
+    pm = torch.empty(nch, L, device="cuda")
+    pl = torch.empty(nch, L, device="cuda")
+    out = torch.empty(L, 1024, device="cuda", dtype=torch.bfloat16)
+    mass = torch.empty(L, T, device="cuda")
+    ops.lt_attn_partial(q, kb, vb, order, T, cpf, po, pm, pl)
+    ops.lt_attn_combine(po, pm, pl, bias, rows, T, L, cpf, gate, out, mass)
+    torch.cuda.synchronize()
+    return out, mass
+
+
+@pytest.mark.parametrize("L,T,cpf,qscale", [(1705, 5, 1, 1.0), (1620, 3, 2, 3.0), (333, 9, 1, 6.0),
+                                            (1705, 1, 3, 1.0), (64, 2, 1, 1.0), (3600, 2, 1, 2.0)])
+def test_long_term_attention_vs_oracle(lib_built, L, T, cpf, qscale):
+    """GatedPropagation explicit path + TPE + record_attn_weight + gate (oracle: restate.gated_propagation
+    semantics, evaluated here in fp32 on the bf16-rounded inputs). Tolerance: bf16 kernel vs fp32,
+    relative Frobenius error <= 2e-2 on the output, <= 5e-3 absolute on the per-frame masses."""
+    torch.manual_seed(L + T)
+    n_slots = T + 1
+    q = _bf(torch.randn(L, 128, device="cuda") * qscale)
+    kb = _bf(torch.randn(n_slots, L, 128, device="cuda"))
+    vb = _bf(torch.randn(n_slots, L, 1024, device="cuda"))
+    gate = _bf(torch.randn(L, 1024, device="cuda"))
+    perm = torch.randperm(n_slots)[:T]
+    order = perm.to(device="cuda", dtype=torch.int32)
+    rows = [min(t, 3) for t in range(T)]
+    bias_nat = torch.randn(L, 4, device="cuda") * 0.5
+    out, mass = _lt_run(q, kb, vb, order, T, cpf, (bias_nat * math.log2(math.e)).contiguous(), rows, gate)
+    s = torch.cat([q.float() @ kb[perm[t]].float().t() / math.sqrt(128.0) + bias_nat[:, rows[t]][:, None]
+                   for t in range(T)], 1)
+    a = torch.softmax(s, -1)
+    o_ref = (a @ torch.cat([vb[perm[t]].float() for t in range(T)], 0)) * gate.float()
+    m_ref = a.view(L, T, L).sum(-1)
+    assert torch.isfinite(out.float()).all()
+    assert _rel(out, o_ref) < 2e-2
+    assert (mass - m_ref).abs().max().item() < 5e-3
+    assert (mass.sum(1) - 1).abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("h,w", [(31, 55), (30, 54), (9, 20), (45, 80)])
+def test_local_attention_vs_oracle(lib_built, h, w):
+    """LocalGatedPropagation (15x15 window) against the oracle's direct windowed restatement."""
+    from oracle import restate as R
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(h * w)
+    L = h * w
+    q = _bf(torch.randn(L, 128) * 1.5)
+    k = _bf(torch.randn(L, 128))
+    v = _bf(torch.randn(L, 1024))
+    u = _bf(torch.randn(L, 1024))
+    rel_w = torch.randn(225, 128, 1, 1) * 0.1
+    rel_b = torch.randn(225) * 0.1
+    sd = {"p.relative_emb_k.weight": _bf(rel_w).float(), "p.relative_emb_k.bias": rel_b,
+          "p.dw_conv.conv.weight": torch.zeros(1024, 1, 5, 5), "p.projection.weight": torch.zeros(8, 1024),
+          "p.projection.bias": torch.zeros(8)}
+    to2d = lambda t: t.float().view(h, w, 1, -1).permute(2, 3, 0, 1).contiguous()
+    _, attn_ref, agg_ref = R.local_gated_propagation(to2d(q), to2d(k), to2d(v), u.float().view(L, 1, 1024),
+                                                     (h, w), sd, "p")
+    gated_ref = agg_ref.view(L, 1024) * u.float()
+    probs_ref = attn_ref[0, 0].t()                                  # [L, 225]
+
+    qd, kd, vd, ud = q.cuda(), k.cuda(), v.cuda(), u.cuda()
+    rel = torch.zeros(L, 256, device="cuda")
+    ops.linear(qd, _bf(rel_w.view(225, 128)).cuda(), rel_b.cuda(), [(0, 225, ops.ACT_NONE, ops.OUT_F32, rel, 0)])
+    probs = torch.empty(L, 225, device="cuda")
+    out = torch.empty(L, 1024, device="cuda", dtype=torch.bfloat16)
+    ops.local_attn_scores(qd, kd, rel, probs, h, w)
+    ops.local_attn_aggregate(probs, vd, ud, out, h, w)
+    torch.cuda.synchronize()
+    assert (probs.cpu() - probs_ref).abs().max().item() < 2e-3
+    assert (probs.sum(1) - 1).abs().max().item() < 1e-4
+    assert _rel(out.cpu(), gated_ref) < 2e-2
+
+
+def test_bank_score_evict_bit_exact_vs_oracle(lib_built):
+    """Slot choices of the device rule == oracle rule (restate.eviction_scores) over long random
+    histories, for the DeAOT call pattern (statistics on every append) and the AOT one (only when full)."""
+    from oracle import restate as R
+    from rmem_ocu_b200 import ops, _lib
+    for variant, seed in [("deaot", 0), ("aot", 1), ("deaot", 2)]:
+        g = torch.Generator().manual_seed(seed)
+        L, cap = 420, 5
+        state = torch.zeros(_lib.BANK_STATE_WORDS, device="cuda", dtype=torch.int32)
+        ops.bank_init(state, 0)
+        idx = [0]
+        ev = R.EvictionState()
+        T = 1
+        for step in range(1, 120):
+            # concentrated, non-uniform masses so the relevance term matters
+            W = torch.rand(L, T, generator=g) ** 3 + 1e-3
+            W = W / W.sum(1, keepdim=True)
+            fg = torch.rand(L, generator=g)
+            idx.append(step * 3)
+            src = torch.zeros(L, 8, device="cuda")
+            dst = torch.zeros(_lib.MAX_BANK, L, 8, device="cuda")
+            ops.bank_append(state, T, step * 3, [src], [dst])
+            T_new = T + 1
+            if variant == "aot" and T_new <= cap:
+                T = T_new
+                continue
+            drop, detail = R.eviction_scores(W, fg, idx, ev)
+            ops.bank_score_evict(state, W.cuda().contiguous(), fg.cuda(), L, T, cap)
+            st = state.cpu()
+            assert int(st[5 * _lib.MAX_BANK + 4]) == drop, (variant, step, detail["margin"])
+            if T_new > cap:
+                idx.remove(idx[drop])
+                T = cap
+            else:
+                T = T_new
+            order = st[:T].tolist()
+            frame_ids = [int(st[_lib.MAX_BANK + s]) for s in order]
+            assert frame_ids == idx, (variant, step)

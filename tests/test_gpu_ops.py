@@ -1,0 +1,135 @@
+"""Parity of the element-wise / GEMM / bank kernels against plain PyTorch fp32 and the oracle."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize("M,K,N", [(1705, 256, 1152), (1620, 2048, 512), (100, 512, 2176), (3600, 1024, 512)])
+def test_linear_segments(lib_built, M, K, N):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(0)
+    dev = "cuda"
+    a = _bf(torch.randn(M, K, device=dev))
+    w = _bf(torch.randn(N, K, device=dev) / math.sqrt(K))
+    bias = torch.randn(N, device=dev)
+    ref = a.float() @ w.float().t() + bias
+    n0 = 128 if N > 256 else 64
+    n1 = (N - n0) // 2 // 32 * 32 + n0
+    o0 = torch.zeros(M, n0 + 64, device=dev, dtype=torch.bfloat16)          # ld > width, col offset 32
+    o1 = torch.zeros(M, n1 - n0, device=dev, dtype=torch.float32)
+    o2 = torch.randn(M, N - n1, device=dev, dtype=torch.float32)
+    o2_init = o2.clone()
+    ops.linear(a, w, bias, [(0, n0, ops.ACT_NONE, ops.OUT_BF16, o0, 32),
+                            (n0, n1, ops.ACT_SILU, ops.OUT_F32, o1, 0),
+                            (n1, N, ops.ACT_NONE, ops.OUT_F32_ACCUM, o2, 0)])
+    torch.cuda.synchronize()
+    assert _rel(o0[:, 32:32 + n0], ref[:, :n0]) < 6e-3
+    assert (o0[:, :32] == 0).all() and (o0[:, 32 + n0:] == 0).all()
+    assert _rel(o1, F.silu(ref[:, n0:n1])) < 2e-3
+    assert _rel(o2 - o2_init, ref[:, n1:]) < 2e-3
+
+
+def test_linear_ragged_columns(lib_built):
+    """N not a multiple of 32 (the 225 relative-position taps)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(1)
+    a = _bf(torch.randn(333, 128, device="cuda"))
+    w = _bf(torch.randn(225, 128, device="cuda") * 0.1)
+    bias = torch.randn(225, device="cuda")
+    out = torch.full((333, 256), 7.0, device="cuda")
+    ops.linear(a, w, bias, [(0, 225, ops.ACT_NONE, ops.OUT_F32, out, 0)])
+    torch.cuda.synchronize()
+    ref = a.float() @ w.float().t() + bias
+    assert _rel(out[:, :225], ref) < 2e-3
+    assert (out[:, 225:] == 7.0).all()
+
+
+@pytest.mark.parametrize("in_bf16", [False, True])
+def test_layernorm_dual(lib_built, in_bf16):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(2)
+    L = 1705
+    x0 = torch.randn(L, 256, device="cuda") * 3 + 1
+    x1 = torch.randn(L, 256, device="cuda")
+    if in_bf16:
+        x0, x1 = _bf(x0), _bf(x1)
+    g0, b0, g1, b1 = (torch.randn(256, device="cuda") for _ in range(4))
+    out = torch.zeros(L, 512, device="cuda", dtype=torch.bfloat16)
+    ops.layernorm(x0, g0, b0, out, 0, x1, g1, b1, out, 256)
+    torch.cuda.synchronize()
+    r0 = F.layer_norm(x0.float(), (256,), g0, b0, 1e-5)
+    r1 = F.layer_norm(x1.float(), (256,), g1, b1, 1e-5)
+    assert _rel(out[:, :256], r0) < 4e-3 and _rel(out[:, 256:], r1) < 4e-3
+
+
+@pytest.mark.parametrize("h,w", [(31, 55), (30, 54), (5, 3)])
+def test_dwconv5(lib_built, h, w):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(3)
+    C = 1024
+    x = _bf(torch.randn(h * w, C, device="cuda"))
+    wt = torch.randn(C, 1, 5, 5, device="cuda") * 0.2
+    y = torch.zeros(h * w, 2 * C, device="cuda", dtype=torch.bfloat16)
+    ops.dwconv5(x, 0, wt.view(C, 25).t().contiguous(), y, C, h, w, C)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().view(1, h, w, C).permute(0, 3, 1, 2), wt, None, 1, 2, 1, C)
+    ref = ref.permute(0, 2, 3, 1).reshape(h * w, C)
+    assert _rel(y[:, C:], ref) < 4e-3 and (y[:, :C] == 0).all()
+
+
+def test_groupnorm_tokens(lib_built):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(4)
+    L = 1705
+    xa = torch.randn(L, 256, device="cuda") * 2 + 0.5
+    xb = torch.randn(L, 256, device="cuda") * 0.3 - 1
+    g, b = torch.randn(512, device="cuda"), torch.randn(512, device="cuda")
+    out = torch.empty(L, 512, device="cuda", dtype=torch.bfloat16)
+    ws = torch.empty(4, device="cuda", dtype=torch.float64)
+    ops.groupnorm_tokens(xa, xb, g, b, out, 2, ws)
+    torch.cuda.synchronize()
+    x = torch.cat([xa, xb], 1)
+    ref = F.group_norm(x.t().unsqueeze(0), 2, g, b, 1e-5)[0].t()
+    assert _rel(out, ref) < 4e-3
+
+
+def test_tpe_prepare(lib_built):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(5)
+    L = 1705
+    q = _bf(torch.randn(L, 128, device="cuda"))
+    cur = torch.randn(128, device="cuda") * 0.05
+    mem = torch.randn(4, 128, device="cuda") * 0.05
+    qt = torch.empty_like(q)
+    bias = torch.empty(L, 4, device="cuda")
+    ops.tpe_prepare(q, cur, mem, qt, bias)
+    torch.cuda.synchronize()
+    qref = q.float() + cur
+    assert _rel(qt, qref) < 4e-3
+    bref = (qt.float() @ mem.t()) * (math.log2(math.e) / math.sqrt(128))
+    assert (bias - bref).abs().max().item() < 1e-4
+
+
+def test_foreground_prob(lib_built):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(6)
+    logits = torch.randn(1, 11, 121, 217, device="cuda") * 3
+    h, w = 31, 55
+    fg = torch.empty(h * w, device="cuda")
+    ops.foreground_prob(logits[0], fg, h, w)
+    torch.cuda.synchronize()
+    pl = F.interpolate(logits, size=(h, w), mode="bilinear", align_corners=True)
+    ref = (1 - torch.softmax(pl, 1)[:, 0]).flatten()
+    assert (fg - ref).abs().max().item() < 1e-5
