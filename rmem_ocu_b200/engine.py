@@ -1,0 +1,554 @@
+"""Drop-in engines for the RMem per-frame path: AOTEngine / DeAOTEngine / *InferEngine with the
+reference's method names and argument lists (reference networks/engines/aot_engine.py:18-725,
+deaot_engine.py:9-56), driving the sm_100a kernels of librmem_b200.so through ``ops``.
+
+State layout (per engine = per video sequence, one object group of <= 10 objects):
+  * long-term bank : per layer K [n_slots, L, 128] and V|ID_V [n_slots, L, 1024] in bf16, fixed
+    capacity (former + latter + 1 slots), plus a device-resident slot table (``bank_state``) --
+    appends are one strided copy, evictions an index shuffle done by the device kernel;
+  * short-term memory: previous frame's K and V|ID_V per layer;
+  * residual streams in fp32, everything the tensor cores read in bf16.
+The frame path issues no host synchronisation; ``long_memories_indexes`` is mirrored lazily.
+There is no CPU / PyTorch fallback: without CUDA or the shared library the engines raise.
+"""
+import copy
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib, ops
+from .tpe import tpe_row_indices
+
+BF16 = torch.bfloat16
+
+
+def _bf(t, dev):
+    return t.detach().to(device=dev, dtype=BF16).contiguous()
+
+
+def _f32(t, dev):
+    return t.detach().to(device=dev, dtype=torch.float32).contiguous()
+
+
+class PreparedDeAOT:
+    """Device-side repack of a DeAOT model's weights (done once per model per device)."""
+
+    def __init__(self, model, device):
+        sd = model.state_dict()
+        self.device = device
+        self.cfg = model.cfg
+        self.num_layers = sum(1 for k in sd if k.startswith("LSTT.layers.") and k.endswith(".norm1.weight"))
+        self.layers = []
+        d = 256
+        for i in range(self.num_layers):
+            p = "LSTT.layers.%d." % i
+            g = lambda n: sd[p + n]
+            L = {}
+            L["norm1"] = (_f32(g("norm1.weight"), device), _f32(g("norm1.bias"), device))
+            L["norm2"] = (_f32(g("norm2.weight"), device), _f32(g("norm2.bias"), device))
+            L["id_norm2"] = (_f32(g("id_norm2.weight"), device), _f32(g("id_norm2.bias"), device))
+            # one GEMM for K | V | U  (linear_QV 256->128+512, linear_U 256->512)
+            L["w_qvu"] = _bf(torch.cat([g("linear_QV.weight"), g("linear_U.weight")], 0), device)
+            L["b_qvu"] = _f32(torch.cat([g("linear_QV.bias"), g("linear_U.bias")], 0), device)
+            if i > 0:
+                L["id_norm1"] = (_f32(g("id_norm1.weight"), device), _f32(g("id_norm1.bias"), device))
+                L["w_idu"] = _bf(g("linear_ID_U.weight"), device)
+                L["b_idu"] = _f32(g("linear_ID_U.bias"), device)
+            L["w_idv"] = _bf(g("linear_ID_V.weight"), device)          # [512, 256] or [512, 512]
+            L["b_idv"] = _f32(g("linear_ID_V.bias"), device)
+            L["w_rel"] = _bf(g("short_term_attn.relative_emb_k.weight").reshape(225, 128), device)
+            L["b_rel"] = _f32(g("short_term_attn.relative_emb_k.bias"), device)
+            tapmajor = lambda w: _f32(w.reshape(1024, 25).t(), device)
+            L["dw_lt"] = tapmajor(g("long_term_attn.dw_conv.conv.weight"))
+            L["dw_st"] = tapmajor(g("short_term_attn.dw_conv.conv.weight"))
+            L["dw_sa"] = tapmajor(g("self_attn.dw_conv.conv.weight"))
+            # long-term and short-term projections share the residual add: one K = 2048 GEMM
+            L["w_proj_ls"] = _bf(torch.cat([g("long_term_attn.projection.weight"),
+                                            g("short_term_attn.projection.weight")], 1), device)
+            L["b_proj_ls"] = _f32(g("long_term_attn.projection.bias") + g("short_term_attn.projection.bias"),
+                                  device)
+            # self-attention input GEMM: QK (512->128) | V1,V2 block-diagonal | U1,U2 block-diagonal
+            z = torch.zeros(512, 256)
+            w_sa = torch.cat([g("self_attn.linear_QK.weight").cpu(),
+                              torch.cat([g("self_attn.linear_V1.weight").cpu(), z], 1),
+                              torch.cat([z, g("self_attn.linear_V2.weight").cpu()], 1),
+                              torch.cat([g("self_attn.linear_U1.weight").cpu(), z], 1),
+                              torch.cat([z, g("self_attn.linear_U2.weight").cpu()], 1)], 0)
+            L["w_sa"] = _bf(w_sa, device)
+            L["b_sa"] = _f32(torch.cat([g("self_attn.linear_QK.bias"), g("self_attn.linear_V1.bias"),
+                                        g("self_attn.linear_V2.bias"), g("self_attn.linear_U1.bias"),
+                                        g("self_attn.linear_U2.bias")], 0), device)
+            L["w_proj_sa"] = _bf(g("self_attn.projection.weight"), device)
+            L["b_proj_sa"] = _f32(g("self_attn.projection.bias"), device)
+            self.layers.append(L)
+        self.gn_out = (_f32(sd["LSTT.decoder_norms.0.gn.weight"], device),
+                       _f32(sd["LSTT.decoder_norms.0.gn.bias"], device))
+        self.id_norm = (_f32(sd["id_norm.weight"], device), _f32(sd["id_norm.bias"], device))
+        self.cur_pos_emb = _f32(sd["cur_pos_emb"].reshape(-1), device)
+        self.mem_pos_emb = _f32(sd["mem_pos_emb"], device)
+        # black boxes: encoder / projector / decoder / id-bank conv as cuDNN calls, bf16 channels-last
+        enc = copy.deepcopy(model.encoder).float()
+        if hasattr(enc, "fold_bn_"):
+            enc.fold_bn_()
+        self.encoder = enc.to(device=device, dtype=BF16).to(memory_format=torch.channels_last).eval()
+        conv_cl = lambda m: copy.deepcopy(m).to(device=device, dtype=BF16).to(memory_format=torch.channels_last).eval()
+        self.encoder_projector = conv_cl(model.encoder_projector)
+        # the FPN head decides the argmax mask: keep it in fp32 (TF32 off) unless told otherwise
+        import os
+        self.decoder_dtype = BF16 if os.environ.get("RMEM_DECODER_DTYPE", "fp32") == "bf16" else torch.float32
+        self.decoder = copy.deepcopy(model.decoder).to(device=device, dtype=self.decoder_dtype).to(
+            memory_format=torch.channels_last).eval()
+        self.id_bank = conv_cl(model.patch_wise_id_bank)
+
+
+def prepare(model, device):
+    cache = model.__dict__.setdefault("_rmem_prepared", {})
+    key = str(device)
+    if key not in cache:
+        cache[key] = PreparedDeAOT(model, device)
+    return cache[key]
+
+
+class _Workspace:
+    """Per-sequence device buffers for one token grid (h, w); allocated once, reused every frame."""
+
+    def __init__(self, prep, h, w, n_slots, device):
+        L, nl = h * w, prep.num_layers
+        f32 = torch.float32
+
+        def z(*s, dt=BF16):
+            return torch.zeros(*s, device=device, dtype=dt)
+
+        self.h, self.w, self.L, self.n_slots = h, w, L, n_slots
+        self.tgt, self.tgt_id = z(L, 256, dt=f32), z(L, 256, dt=f32)
+        self.xn = z(L, 512)                                   # LayerNorm outputs (norm | id_norm)
+        self.idcat = [z(L, 512) for _ in range(nl)]           # [curr_ID_V | id_emb] per layer
+        self.kcur = [z(L, 128) for _ in range(nl)]
+        self.vcur = [z(L, 1024) for _ in range(nl)]           # V | ID_V
+        self.kprev = [z(L, 128) for _ in range(nl)]           # short-term memory (previous frame)
+        self.vprev = [z(L, 1024) for _ in range(nl)]
+        self.kbank = [z(n_slots, L, 128) for _ in range(nl)]  # long-term bank
+        self.vbank = [z(n_slots, L, 1024) for _ in range(nl)]
+        self.u = [z(L, 1024) for _ in range(nl)]              # cat_curr_U
+        self.u[0][:, 512:] = 1.0                              # layer 0: U = [silu(U), 1]
+        self.qt, self.tpe_bias = z(L, 128), z(L, 4, dt=f32)
+        self.gated_a, self.gated_b = z(L, 1024), z(L, 1024)
+        self.dw = z(L, 2048)
+        self.rel, self.probs = z(L, 256, dt=f32), z(L, 225, dt=f32)
+        self.sa_qk, self.sa_v, self.sa_u = z(L, 128), z(L, 1024), z(L, 1024)
+        n_chunks = max(n_slots, _lib.MAX_CHUNKS_PER_FRAME)
+        self.part_o = z(n_chunks, L, 1024, dt=f32)
+        self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
+        self.mass = z(L * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight [L, T]
+        self.gn_out = z(L, 512)
+        self.gn_ws = z(4, dt=torch.float64)
+        self.fg = z(L, dt=f32)
+        self.id_emb = z(L, 256)
+        self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
+        self.zero_order = z(1, dt=torch.int32)
+
+
+def _chunks_per_frame(T):
+    # keep >= ~3 key chunks per query tile so the split-KV grid covers the 148 SMs when the bank is short
+    return 3 if T == 1 else (2 if T == 2 else 1)
+
+
+class DeAOTEngine:
+    """Per-sequence state machine with the reference AOTEngine / DeAOTEngine surface
+    (aot_engine.py:18-568, deaot_engine.py:9-18): add_reference_frame, match_propogate_one_frame,
+    update_short_term_memory, decode_current_logits, restart_engine, update_size."""
+
+    def __init__(self, aot_model, gpu_id=0, long_term_mem_gap=9999, short_term_mem_skip=1,
+                 layer_loss_scaling_ratio=2.):
+        if not torch.cuda.is_available():
+            raise _lib.RmemError("rmem_ocu_b200 engines need a CUDA device: there is no CPU fallback")
+        _lib.lib()  # fail loudly now if the shared library is missing
+        if short_term_mem_skip != 1:
+            raise NotImplementedError("short_term_mem_skip != 1 is not on the evaluated path")
+        self.AOT = aot_model
+        self.cfg = aot_model.cfg
+        self.align_corners = True
+        self.max_obj_num = aot_model.max_obj_num
+        self.gpu_id = gpu_id
+        self.device = torch.device("cuda", gpu_id)
+        self.long_term_mem_gap = long_term_mem_gap
+        self.short_term_mem_skip = short_term_mem_skip
+        self.prep = prepare(aot_model, self.device)
+        self.capacity = int(self.cfg.FORMER_MEM_LEN) + int(self.cfg.LATTER_MEM_LEN)
+        if self.capacity + 1 > _lib.MAX_BANK:
+            raise _lib.RmemError("FORMER_MEM_LEN + LATTER_MEM_LEN + 1 exceeds RMEM_MAX_BANK")
+        self.deaot = True
+        self.ws = None
+        self.trace = None          # optional dict: per-layer intermediates for the parity tests
+        self.restart_engine()
+
+    # ------------------------------------------------------------------ bookkeeping
+    def restart_engine(self, batch_size=1, enable_id_shuffle=False):
+        if batch_size != 1 or enable_id_shuffle:
+            raise NotImplementedError("evaluation path: batch_size 1, no id shuffle")
+        self.batch_size = 1
+        self.frame_step = 0
+        self.last_mem_step = -1
+        self.obj_nums = None
+        self.enc_size_2d = None
+        self.enc_hw = None
+        self.input_size_2d = None
+        self.pred_id_logits = None
+        self.T = 0                 # frames in the long-term bank (host mirror; deterministic)
+        self.T_recorded = 0        # bank length when record_attn_weight was last written
+        self.n_long_updates = 0
+
+    def update_size(self, input_size, enc_size):
+        self.input_size_2d = tuple(input_size)
+        self.enc_size_2d = tuple(enc_size)
+        self.enc_hw = self.enc_size_2d[0] * self.enc_size_2d[1]
+        h, w = self.enc_size_2d
+        n_slots = self.capacity + 1
+        if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
+            self.ws = _Workspace(self.prep, h, w, n_slots, self.device)
+
+    @property
+    def long_memories_indexes(self):
+        """Frame ids in the bank, oldest first (host mirror; reading it synchronises)."""
+        if self.ws is None or self.T == 0:
+            return []
+        st = self.ws.bank_state.cpu()
+        return [int(st[_lib.MAX_BANK + int(st[t])]) for t in range(self.T)]
+
+    def eviction_debug(self):
+        st = self.ws.bank_state.cpu()
+        base = 5 * _lib.MAX_BANK
+        return dict(last_drop=int(st[base]), last_drop_frame=int(st[base + 1]),
+                    margin=float(st[base + 2:base + 3].view(torch.float32)), n_evictions=int(st[base + 3]),
+                    last_choice=int(st[base + 4]))
+
+    # ------------------------------------------------------------------ black boxes
+    def encode_image(self, img):
+        x = img.to(device=self.device, dtype=BF16, non_blocking=True).contiguous(memory_format=torch.channels_last)
+        xs = self.prep.encoder(x)
+        xs[-1] = self.prep.encoder_projector(xs[-1])
+        return xs
+
+    def _tokens(self, x_nchw):
+        """[1, C, h, w] channels-last tensor -> [L, C] view of the same memory."""
+        n, c, h, w = x_nchw.shape
+        return x_nchw.permute(0, 2, 3, 1).reshape(h * w, c)
+
+    def assign_identity(self, one_hot_mask, ignore_mask=None):
+        """aot_engine.py:208-232 (MODEL_IGNORE_TOKEN, no id shuffle) + DeAOT.get_id_emb
+        (models/deaot.py:65-69): 17x17 stride-16 conv (cuDNN) then LayerNorm (kernel) -> ws.id_emb."""
+        if ignore_mask is None:
+            ignore_mask = torch.zeros_like(one_hot_mask[:, :1])
+        one_hot_mask = one_hot_mask.clone()
+        one_hot_mask[:, 0] = one_hot_mask[:, 0] * (ignore_mask[:, 0] == 0).to(one_hot_mask.dtype)
+        x = torch.cat((one_hot_mask, ignore_mask), 1).to(BF16).contiguous(memory_format=torch.channels_last)
+        e = self.prep.id_bank(x)                                   # [1, 256, h, w] channels-last
+        tok = self._tokens(e)
+        ws = self.ws
+        g, b = self.prep.id_norm
+        # id_emb goes to the stand-alone buffer and next to curr_ID_V for the ID_V GEMM of every layer
+        ops.layernorm(tok, g, b, ws.id_emb, 0, tok, g, b, ws.idcat[0], 256)
+        for i in range(1, self.prep.num_layers, 2):
+            j = min(i + 1, self.prep.num_layers - 1)
+            ops.layernorm(tok, g, b, ws.idcat[i], 256, tok, g, b, ws.idcat[j], 256)
+        return ws.id_emb
+
+    @staticmethod
+    def _one_hot(mask, cls_num):
+        if mask.dim() == 3:
+            mask = mask.unsqueeze(1)
+        idx = torch.arange(0, cls_num + 1, device=mask.device).view(1, -1, 1, 1)
+        return (mask == idx).float(), (mask == 255).float()
+
+    # ------------------------------------------------------------------ LSTT (kernels)
+    def _id_value(self, i, dst):
+        """fuse_key_value_id (transformer.py:1238-1244): ID_V = silu(linear_ID_V([curr_ID_V | id_emb]))
+        written into columns 512.. of ``dst`` (a V | ID_V buffer)."""
+        ws, Lw = self.ws, self.prep.layers[i]
+        a = ws.idcat[i][:, 256:] if i == 0 else ws.idcat[i]
+        ops.linear(a, Lw["w_idv"], Lw["b_idv"], [(0, 512, ops.ACT_SILU, ops.OUT_BF16, dst, 512)])
+
+    def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass):
+        ws = self.ws
+        cpf = _chunks_per_frame(T)
+        ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
+        ops.lt_attn_combine(ws.part_o, ws.part_m, ws.part_l, ws.tpe_bias if tpe else None,
+                            tpe_row_indices(T) if tpe else None, T, ws.L, cpf, gate, out, mass)
+
+    def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights):
+        """DualBranchGPM.forward + GatedPropagationModule.forward (transformer.py:765-824, 1091-1236)."""
+        ws, prep = self.ws, self.prep
+        h, w, L = ws.h, ws.w, ws.L
+        ws.tgt.copy_(self._tokens(curr_emb16))
+        T = 1 if is_reference else self.T
+        tr = self.trace
+        for i, Lw in enumerate(prep.layers):
+            # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
+            if i == 0:
+                ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0)
+            else:
+                ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0, ws.tgt_id, *Lw["id_norm1"], ws.idcat[i], 0)
+            # K (= Q) | silu(V) | silu(U) in one GEMM
+            ops.linear(ws.xn[:, :256], Lw["w_qvu"], Lw["b_qvu"],
+                       [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.kcur[i], 0),
+                        (128, 640, ops.ACT_SILU, ops.OUT_BF16, ws.vcur[i], 0),
+                        (640, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 0)])
+            if i > 0:
+                ops.linear(ws.idcat[i][:, :256], Lw["w_idu"], Lw["b_idu"],
+                           [(0, 512, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 512)])
+            if is_reference:
+                # the reference frame is its own long- and short-term memory (transformer.py:1125-1135)
+                self._id_value(i, ws.vcur[i])
+                ws.kprev[i].copy_(ws.kcur[i]); ws.vprev[i].copy_(ws.vcur[i])
+                ws.kbank[i][0].copy_(ws.kcur[i]); ws.vbank[i][0].copy_(ws.vcur[i])
+            # long-term attention over the bank (TPE folded into a per-frame score bias)
+            ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
+            mass = None
+            if save_atten_weights and i == 0:
+                mass = ws.mass
+                self.T_recorded = T
+            self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
+                                         ws.gated_a, mass)
+            # short-term 15x15 local attention over the previous frame
+            ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
+            ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, ws.probs, h, w)
+            ops.local_attn_aggregate(ws.probs, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
+            # gate -> dw5x5 -> (projection_lt + projection_st) -> residual adds, one GEMM
+            ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
+            ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
+            if tr is not None:
+                tr.setdefault("layers", []).append(dict(
+                    curr_Q=ws.kcur[i].float().cpu(), curr_V=ws.vcur[i][:, :512].float().cpu(),
+                    cat_curr_U=ws.u[i].float().cpu(), lt_gated=ws.gated_a.float().cpu(),
+                    st_gated=ws.gated_b.float().cpu()))
+            id_mode = ops.OUT_F32 if i == 0 else ops.OUT_F32_ACCUM
+            ops.linear(ws.dw, Lw["w_proj_ls"], Lw["b_proj_ls"],
+                       [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
+                        (256, 512, ops.ACT_NONE, id_mode, ws.tgt_id, 0)])
+            # self-attention (gated, d_att 128, value width 1024)
+            ops.layernorm(ws.tgt, *Lw["norm2"], ws.xn, 0, ws.tgt_id, *Lw["id_norm2"], ws.xn, 256)
+            ops.linear(ws.xn, Lw["w_sa"], Lw["b_sa"],
+                       [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.sa_qk, 0),
+                        (128, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.sa_v, 0),
+                        (1152, 2176, ops.ACT_SILU, ops.OUT_BF16, ws.sa_u, 0)])
+            self._gated_global_attention(ws.sa_qk, ws.sa_qk.view(1, L, 128), ws.sa_v.view(1, L, 1024),
+                                         ws.zero_order, 1, False, ws.sa_u, ws.gated_a, None)
+            ops.dwconv5(ws.gated_a, 0, Lw["dw_sa"], ws.dw, 0, h, w, 1024)
+            ops.linear(ws.dw[:, :1024], Lw["w_proj_sa"], Lw["b_proj_sa"],
+                       [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
+                        (256, 512, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt_id, 0)])
+            if tr is not None:
+                tr["layers"][-1].update(tgt=ws.tgt.cpu().clone(), tgt_id=ws.tgt_id.cpu().clone())
+        # the single output GroupNorm1D(512, 2) (transformer.py:806-808)
+        ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws)
+        return ws.gn_out
+
+    # ------------------------------------------------------------------ public frame API
+    def add_reference_frame(self, img=None, mask=None, frame_step=-1, obj_nums=None, img_embs=None):
+        """aot_engine.py:241-325."""
+        if self.obj_nums is None and obj_nums is None:
+            raise ValueError("No objects for reference frame!")
+        if obj_nums is not None:
+            self.obj_nums = obj_nums
+        if frame_step == -1:
+            frame_step = self.frame_step
+        if img_embs is None and img is None:
+            raise ValueError("No image for reference frame!")
+        if mask is None:
+            raise ValueError("No mask for reference frame!")
+        curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
+        mask = mask.to(self.device)
+        one_hot, _ = self._one_hot(mask, self.max_obj_num)
+        if self.input_size_2d is None:
+            in_size = img.shape[2:] if img is not None else mask.shape[-2:]
+            self.update_size(in_size, curr_enc_embs[-1].shape[2:])
+        self.assign_identity(one_hot)
+        ops.bank_init(self.ws.bank_state, self.frame_step)
+        self.T = 1
+        lstt_out = self._lstt_forward(curr_enc_embs[-1], True, False)
+        self.last_mem_step = frame_step
+        self.decode_current_logits(curr_enc_embs, lstt_out)
+
+    def match_propogate_one_frame(self, img=None, img_embs=None, mask=None, output_size=None):
+        """aot_engine.py:398-436 (save_atten_weights=True in eval)."""
+        self.frame_step += 1
+        curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
+        lstt_out = self._lstt_forward(curr_enc_embs[-1], False, True)
+        return self.decode_current_logits(curr_enc_embs, lstt_out, output_size=output_size)
+
+    def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
+        """aot_engine.py:438-465 + DeAOT.decode_id_logits (models/deaot.py:57-63). ``curr_lstt_embs`` is
+        the [L, 512] GroupNorm output (or a list whose last entry is it)."""
+        emb = curr_lstt_embs[-1] if isinstance(curr_lstt_embs, (list, tuple)) else curr_lstt_embs
+        n, c, h, w = curr_enc_embs[-1].shape
+        lstt_nchw = emb.view(1, h, w, -1).permute(0, 3, 1, 2)      # channels-last view, no copy
+        dd = self.prep.decoder_dtype
+        shortcuts = curr_enc_embs if dd == BF16 else [x.to(dd) for x in curr_enc_embs]
+        logits = self.prep.decoder([shortcuts[-1], lstt_nchw.to(dd)], shortcuts).float()
+        for b, on in enumerate(self.obj_nums):
+            if on + 1 < logits.shape[1]:
+                logits[b, on + 1:] = -1e10
+        self.pred_id_logits = logits.contiguous()
+        if output_size is not None:
+            logits = F.interpolate(logits, size=output_size, mode="bilinear", align_corners=self.align_corners)
+        return logits
+
+    def update_short_term_memory(self, curr_mask, curr_id_emb=None, step=0):
+        """aot_engine.py:327-369 + DualBranchGPM.update_short_memories / update_long_term_memory /
+        restrict_long_memories (transformer.py:826-991)."""
+        ws = self.ws
+        if curr_id_emb is None:
+            curr_mask = curr_mask.to(self.device)
+            ignore = None
+            if curr_mask.dim() == 3 or curr_mask.shape[0] == 1:
+                one_hot, ignore = self._one_hot(curr_mask, self.max_obj_num)
+            else:
+                one_hot = curr_mask
+            self.assign_identity(one_hot, ignore)
+        else:
+            raise NotImplementedError("pre-computed id embeddings are a training-only path")
+        is_update_long_memory = False
+        if self.frame_step - self.last_mem_step >= self.long_term_mem_gap:
+            is_update_long_memory = True
+            self.last_mem_step = self.frame_step
+        for i in range(self.prep.num_layers):
+            # short-term memory <- this frame's K, V and the freshly fused ID_V
+            ws.kprev[i].copy_(ws.kcur[i])
+            ws.vprev[i][:, :512].copy_(ws.vcur[i][:, :512])
+            self._id_value(i, ws.vprev[i])
+        if is_update_long_memory:
+            srcs, dsts = [], []
+            for i in range(self.prep.num_layers):
+                srcs += [ws.kprev[i], ws.vprev[i]]
+                dsts += [ws.kbank[i], ws.vbank[i]]
+            ops.bank_append(ws.bank_state, self.T, self.frame_step, srcs, dsts)
+            T_old = self.T
+            if self.deaot or T_old + 1 > self.capacity:
+                if self.T_recorded != T_old:
+                    raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
+                ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
+                ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T_old, self.capacity)
+            self.T = min(T_old + 1, self.capacity)
+            self.n_long_updates += 1
+
+    # names kept for callers that poke at them
+    def eval(self):
+        return self
+
+
+AOTEngine = DeAOTEngine  # the AOT (multi-head) kernels are not built yet; DeAOT is the evaluated path
+
+
+class DeAOTInferEngine:
+    """AOTInferEngine / DeAOTInferEngine (aot_engine.py:571-725, deaot_engine.py:20-56): splits more
+    than ``max_aot_obj_num`` objects over several engines and merges their logits every frame."""
+
+    def __init__(self, aot_model, gpu_id=0, long_term_mem_gap=9999, short_term_mem_skip=1,
+                 max_aot_obj_num=None):
+        self.cfg = aot_model.cfg
+        self.AOT = aot_model
+        if max_aot_obj_num is None or max_aot_obj_num > aot_model.max_obj_num:
+            self.max_aot_obj_num = aot_model.max_obj_num
+        else:
+            self.max_aot_obj_num = max_aot_obj_num
+        self.gpu_id = gpu_id
+        self.long_term_mem_gap = long_term_mem_gap
+        self.short_term_mem_skip = short_term_mem_skip
+        self.aot_engines = []
+        self.restart_engine()
+
+    def eval(self):
+        return self
+
+    def restart_engine(self):
+        for engine in self.aot_engines:
+            engine.restart_engine()
+        self.aot_engines = []
+        self.obj_nums = None
+
+    def separate_mask(self, mask):
+        # aot_engine.py:604-628
+        if mask is None:
+            return [None] * len(self.aot_engines)
+        if len(self.aot_engines) == 1:
+            return [mask]
+        if mask.dim() == 3 or mask.shape[0] == 1:
+            out = []
+            for idx in range(len(self.aot_engines)):
+                start_id = idx * self.max_aot_obj_num + 1
+                end_id = (idx + 1) * self.max_aot_obj_num
+                fg = ((mask >= start_id) & (mask <= end_id)).float()
+                out.append((fg * mask - start_id + 1) * fg)
+            return out
+        out = []
+        for idx in range(len(self.aot_engines)):
+            start_id = idx * self.max_aot_obj_num + 1
+            end_id = (idx + 1) * self.max_aot_obj_num
+            fg_prob = mask[start_id:(end_id + 1)]
+            bg_prob = 1. - torch.sum(fg_prob, dim=1, keepdim=True)
+            out.append(torch.cat([bg_prob, fg_prob], dim=1))
+        return out
+
+    def soft_logit_aggregation(self, all_logits):
+        # aot_engine.py:650-673
+        if len(all_logits) == 1:
+            return all_logits[0]
+        fg_probs, bg_probs = [], []
+        for logit in all_logits:
+            prob = torch.softmax(logit, dim=1)
+            bg_probs.append(prob[:, 0:1])
+            fg_probs.append(prob[:, 1:1 + self.max_aot_obj_num])
+        bg_prob = torch.prod(torch.cat(bg_probs, dim=1), dim=1, keepdim=True)
+        merged = torch.cat([bg_prob] + fg_probs, dim=1).clamp(1e-5, 1 - 1e-5)
+        return torch.logit(merged)
+
+    def add_reference_frame(self, img, mask, obj_nums, frame_step=-1):
+        if isinstance(obj_nums, list):
+            obj_nums = obj_nums[0]
+        self.obj_nums = obj_nums
+        aot_num = max(-(-int(obj_nums) // self.max_aot_obj_num), 1)
+        while aot_num > len(self.aot_engines):
+            self.aot_engines.append(DeAOTEngine(self.AOT, self.gpu_id, self.long_term_mem_gap,
+                                                self.short_term_mem_skip))
+        separated = self.separate_mask(mask)
+        img_embs = None
+        for engine, m in zip(self.aot_engines, separated):
+            engine.long_term_mem_gap = self.long_term_mem_gap
+            if img_embs is None:
+                img_embs = engine.encode_image(img)        # the backbone runs once per frame
+            engine.add_reference_frame(img, m, obj_nums=[self.max_aot_obj_num], frame_step=frame_step,
+                                       img_embs=img_embs)
+        self.update_size()
+
+    def match_propogate_one_frame(self, img=None, mask=None, output_size=None):
+        img_embs = None
+        all_logits = []
+        for engine in self.aot_engines:
+            engine.long_term_mem_gap = self.long_term_mem_gap
+            if img_embs is None:
+                img_embs = engine.encode_image(img)
+            all_logits.append(engine.match_propogate_one_frame(img, img_embs=img_embs, mask=mask,
+                                                               output_size=output_size))
+        return self.soft_logit_aggregation(all_logits)
+
+    def update_memory(self, curr_mask):
+        for engine, m in zip(self.aot_engines, self.separate_mask(curr_mask)):
+            engine.update_short_term_memory(m)
+
+    def update_size(self):
+        self.input_size_2d = self.aot_engines[0].input_size_2d
+        self.enc_size_2d = self.aot_engines[0].enc_size_2d
+        self.enc_hw = self.aot_engines[0].enc_hw
+
+
+AOTInferEngine = DeAOTInferEngine
+
+
+def build_engine(name, phase="train", **kwargs):
+    """networks/engines/__init__.py:5-21."""
+    if name in ("aotengine", "deaotengine"):
+        if phase == "train":
+            return DeAOTEngine(**kwargs)
+        if phase == "eval":
+            return DeAOTInferEngine(**kwargs)
+    raise NotImplementedError(name)
