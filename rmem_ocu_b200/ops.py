@@ -11,6 +11,16 @@ from . import _lib
 from ._lib import (ACT_NONE, ACT_SILU, OUT_BF16, OUT_F32, OUT_F32_ACCUM, GemmSegment)  # noqa: F401
 
 
+# number of librmem_b200 kernels launched through this module (bench.py reports it as gpu_launches)
+LAUNCHES = 0
+_KERNELS_PER_CALL = {"rmem_groupnorm_tokens": 2}
+
+
+def _count(name):
+    global LAUNCHES
+    LAUNCHES += _KERNELS_PER_CALL.get(name, 1)
+
+
 def _p(t):
     return None if t is None else t.data_ptr()
 
@@ -41,6 +51,7 @@ def linear(a, w, bias, segments, M=None):
     _lib.check(_lib.lib().rmem_linear(_p(a), a.stride(0), _p(w), w.stride(0), _p(bias), M, N, K,
                                       ctypes.cast(segs, ctypes.c_void_p), len(segments), _stream()),
                "rmem_linear")
+    _count("rmem_linear")
 
 
 def layernorm(x0, g0, b0, out0, col0=0, x1=None, g1=None, b1=None, out1=None, col1=0):
@@ -52,11 +63,13 @@ def layernorm(x0, g0, b0, out0, col0=0, x1=None, g1=None, b1=None, out1=None, co
                                          _p(x1), _p(g1), _p(b1), _p(out1),
                                          out1.stride(0) if out1 is not None else 0, col1, L, C, in_bf16,
                                          _stream()), "rmem_layernorm")
+    _count("rmem_layernorm")
 
 
 def dwconv5(x, xcol0, wt, y, ycol0, h, w, C):
     _lib.check(_lib.lib().rmem_dwconv5(_p(x), x.stride(0), xcol0, _p(wt), _p(y), y.stride(0), ycol0, h, w, C,
                                        _stream()), "rmem_dwconv5")
+    _count("rmem_dwconv5")
 
 
 def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
@@ -64,12 +77,14 @@ def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
     C = Ca + (xb.shape[1] if xb is not None else 0)
     _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), L, C,
                                                 groups, _p(workspace), _stream()), "rmem_groupnorm_tokens")
+    _count("rmem_groupnorm_tokens")
 
 
 def tpe_prepare(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias):
     L, C = q.shape
     _lib.check(_lib.lib().rmem_tpe_prepare(_p(q), _p(cur_pos_emb), _p(mem_pos_emb), _p(q_time), _p(tpe_bias),
                                            L, C, _stream()), "rmem_tpe_prepare")
+    _count("rmem_tpe_prepare")
 
 
 # ---------------------------------------------------------------------------------------------
@@ -78,6 +93,7 @@ def lt_attn_partial(q, kbank, vbank, order, T, cpf, part_o, part_m, part_l):
     _lib.check(_lib.lib().rmem_lt_attn_deaot_partial(_p(q), _p(kbank), _p(vbank), _p(order), T, L,
                                                      kbank.shape[0], cpf, _p(part_o), _p(part_m), _p(part_l),
                                                      _stream()), "rmem_lt_attn_deaot_partial")
+    _count("rmem_lt_attn_deaot_partial")
 
 
 def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate, out, attn_mass):
@@ -86,21 +102,25 @@ def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate,
                                                      ctypes.cast(rows, ctypes.c_void_p), T, L, cpf, _p(gate),
                                                      _p(out), _p(attn_mass), _stream()),
                "rmem_lt_attn_deaot_combine")
+    _count("rmem_lt_attn_deaot_combine")
 
 
 def local_attn_scores(q, k, rel_bias, probs, h, w):
     _lib.check(_lib.lib().rmem_local_attn_scores(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs), h, w,
                                                  _stream()), "rmem_local_attn_scores")
+    _count("rmem_local_attn_scores")
 
 
 def local_attn_aggregate(probs, v, gate, out, h, w):
     _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(probs), _p(v), _p(gate), _p(out), h, w, _stream()),
                "rmem_local_attn_aggregate")
+    _count("rmem_local_attn_aggregate")
 
 
 # ---------------------------------------------------------------------------------------------
 def bank_init(state, frame_step):
     _lib.check(_lib.lib().rmem_bank_init(_p(state), frame_step, _stream()), "rmem_bank_init")
+    _count("rmem_bank_init")
 
 
 def bank_append(state, T, frame_step, srcs, dsts):
@@ -112,14 +132,17 @@ def bank_append(state, T, frame_step, srcs, dsts):
     _lib.check(_lib.lib().rmem_bank_append(_p(state), T, frame_step, ctypes.cast(sp, ctypes.c_void_p),
                                            ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(rb, ctypes.c_void_p),
                                            n, _stream()), "rmem_bank_append")
+    _count("rmem_bank_append")
 
 
 def bank_score_evict(state, attn_mass, fg, L, T_old, capacity):
     _lib.check(_lib.lib().rmem_bank_score_evict(_p(state), _p(attn_mass), _p(fg), L, T_old, capacity,
                                                 _stream()), "rmem_bank_score_evict")
+    _count("rmem_bank_score_evict")
 
 
 def foreground_prob(logits, fg, h, w):
     C, Hs, Ws = logits.shape[-3:]
     _lib.check(_lib.lib().rmem_foreground_prob(_p(logits), C, Hs, Ws, _p(fg), h, w, _stream()),
                "rmem_foreground_prob")
+    _count("rmem_foreground_prob")
