@@ -144,6 +144,8 @@ def run_b200(args, rank, world):
             eng.add_reference_frame(imgs[0].to(dev), lab.to(dev), obj_nums=[N_OBJ], frame_step=0)
             for f in range(1, 1 + args.warmup):
                 frame_step(eng, imgs[f].to(dev) if dev_imgs is None else dev_imgs[f], (H, W))
+                if f == 1:
+                    eng.precapture((H, W))      # CUDA graphs for every bank length, recorded during warm-up
             barrier()
             launches0 = ops.LAUNCHES
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -153,8 +155,7 @@ def run_b200(args, rank, world):
                     if mode == "device":
                         label = frame_step(eng, dev_imgs[f], (H, W))
                     else:
-                        img = imgs[f].to(dev, non_blocking=True)            # H2D from pinned memory
-                        label = frame_step(eng, img, (H, W))
+                        label = frame_step(eng, imgs[f], (H, W))            # pinned host image: H2D inside
                         host_out.copy_(label[0, 0].to(torch.uint8), non_blocking=True)   # D2H of the result
                         torch.cuda.current_stream().synchronize()
                 e1.record()

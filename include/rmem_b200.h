@@ -165,14 +165,18 @@ int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gat
 #define RMEM_BANK_STATE_WORDS (5 * RMEM_MAX_BANK + 8)
 /* words [5*RMEM_MAX_BANK ..): 0 = last drop index (logical, -1 none), 1 = dropped frame id,
  * 2 = decision margin (f32 bits), 3 = number of evictions so far, 4 = argmin of the last scoring
- * pass (set even when nothing had to be dropped) */
+ * pass (set even when nothing had to be dropped), 5 = device-side frame_step */
 
 /* Reset the state for a new sequence: order = identity, slot 0 holds the reference frame
  * (init_memory, transformer.py:438-443 / 993-998 + aot_engine.py:321-323). */
 int rmem_bank_init(void* bank_state, int frame_step, void* stream);
 
+/* frame_step += 1 on the device (AOTEngine.match_propogate_one_frame, aot_engine.py:399); keeps the
+ * frame counter in the state block so a captured CUDA graph needs no per-frame host scalar. */
+int rmem_bank_tick(void* bank_state, void* stream);
+
 /* Append: copy the candidate rows into the free slot order[T] of every bank tensor and stamp
- * frame_id. Replaces update_long_term_memory (transformer.py:306-322, 859-878) -- torch.cat
+ * frame_id (frame_step < 0: use the device-side counter). Replaces update_long_term_memory (transformer.py:306-322, 859-878) -- torch.cat
  * re-allocation becomes one strided copy.  n_tensors <= 8.
  *   src_host / dst_host: HOST arrays of device pointers; row_bytes_host: bytes per slot.
  */
@@ -192,6 +196,19 @@ int rmem_bank_append(void* bank_state, int T, int frame_step, const void* const*
  */
 int rmem_bank_score_evict(void* bank_state, const float* attn_mass, const float* fg, int L,
                           int T_old, int capacity, void* stream);
+
+/* Identity embedding of a label map in one gather kernel: one_hot_mask + ignore channel
+ * (utils/image.py:69-74, aot_engine.py:208-225) + the 17x17 stride-16 pad-8 patch_wise_id_bank conv
+ * (models/aot.py:64-83, 111-114) + optionally DeAOT's id_norm LayerNorm (models/deaot.py:65-69).
+ *   label  f32 [H][W]: 0..n_cls-2 object ids, 255 = ignore (class n_cls-1), anything else = no class
+ *   prefix f32 [n_cls][17][18][256]: row-prefix sums of conv.weight: prefix[k][ky][j][c] =
+ *          sum_{kx<j} weight[c][k][ky][kx];   bias f32 [256];  gamma/beta f32 [256] or NULL
+ *   dst_host: HOST array of n_dst (<= 4) bf16 destinations [h*w][ld_host[i]], written at col0_host[i]
+ */
+int rmem_id_embed(const float* label, int H, int W, const float* prefix, const float* bias,
+                  const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                  const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w,
+                  void* stream);
 
 /* fg[q] = 1 - softmax_c(bilinear_align_corners(pred_id_logits -> (h,w)))[0]
  * (aot_engine.py:355-362).  logits f32 [C][Hs][Ws] -> fg f32 [h*w]. */

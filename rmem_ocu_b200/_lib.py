@@ -71,6 +71,8 @@ _SIGNATURES = {
     "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_local_attn_aggregate": [_c_void_p] * 4 + [_c_int, _c_int, _c_void_p],
     "rmem_bank_init": [_c_void_p, _c_int, _c_void_p],
+    "rmem_bank_tick": [_c_void_p, _c_void_p],
+    "rmem_id_embed": [_c_void_p, _c_int, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "rmem_bank_append": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p],
     "rmem_bank_score_evict": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "rmem_foreground_prob": [_c_void_p] + [_c_int] * 3 + [_c_void_p, _c_int, _c_int, _c_void_p],

@@ -23,7 +23,8 @@ struct BankState {
   float last_margin;       // second-smallest minus smallest objective among candidates
   int32_t n_evictions;
   int32_t last_choice;     // argmin of the last scoring pass even when nothing had to be dropped
-  int32_t pad[3];
+  int32_t cur_frame;       // device-side frame_step (so a captured CUDA graph stamps the right frame id)
+  int32_t pad[2];
 };
 static_assert(sizeof(BankState) == RMEM_BANK_STATE_WORDS * 4, "bank state layout");
 
@@ -38,8 +39,15 @@ __global__ void bank_init_kernel(BankState* st, int frame_step) {
   }
   if (i == 0) {
     st->last_drop = -1; st->last_drop_frame = -1; st->last_margin = 0.f; st->n_evictions = 0;
-    st->last_choice = -1; st->pad[0] = st->pad[1] = st->pad[2] = 0;
+    st->last_choice = -1; st->cur_frame = frame_step; st->pad[0] = st->pad[1] = 0;
   }
+}
+
+__global__ void bank_tick_kernel(BankState* st) { st->cur_frame += 1; }
+
+int bank_tick_launch(void* state, cudaStream_t stream) {
+  bank_tick_kernel<<<1, 1, 0, stream>>>(static_cast<BankState*>(state));
+  return check_launch("bank_tick_kernel");
 }
 
 int bank_init_launch(void* state, int frame_step, cudaStream_t stream) {
@@ -65,7 +73,8 @@ bank_append_kernel(BankState* st, int T, int frame_step, const AppendParams p) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     d[i] = s[i];
-  if (blockIdx.x == 0 && t == 0 && threadIdx.x == 0) st->frame_id[slot] = frame_step;
+  if (blockIdx.x == 0 && t == 0 && threadIdx.x == 0)
+    st->frame_id[slot] = frame_step >= 0 ? frame_step : st->cur_frame;
 }
 
 int bank_append_launch(void* state, int T, int frame_step, const void* const* src, void* const* dst,

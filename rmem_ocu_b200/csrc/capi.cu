@@ -96,6 +96,14 @@ int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gat
                               int h, int w, void* stream) {
   return local_aggregate_launch(probs, v, gate, out, h, w, ST(stream));
 }
+int rmem_bank_tick(void* bank_state, void* stream) { return bank_tick_launch(bank_state, ST(stream)); }
+int rmem_id_embed(const float* label, int H, int W, const float* prefix, const float* bias,
+                  const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                  const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w,
+                  void* stream) {
+  return id_embed_launch(label, H, W, prefix, bias, gamma, beta, n_cls, dst_host, ld_host, col0_host, n_dst,
+                         h, w, ST(stream));
+}
 int rmem_bank_init(void* bank_state, int frame_step, void* stream) {
   return bank_init_launch(bank_state, frame_step, ST(stream));
 }

@@ -46,6 +46,10 @@ int local_scores_launch(const void* q, const void* k, const float* rel, int ld_r
                         int w, cudaStream_t stream);
 int local_aggregate_launch(const float* probs, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream);
+int bank_tick_launch(void* state, cudaStream_t stream);
+int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
+                    const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
+                    const int* col0, int n_dst, int h, int w, cudaStream_t stream);
 int bank_init_launch(void* state, int frame_step, cudaStream_t stream);
 int bank_append_launch(void* state, int T, int frame_step, const void* const* src, void* const* dst,
                        const int64_t* row_bytes, int n_tensors, cudaStream_t stream);

@@ -86,19 +86,84 @@ class PreparedDeAOT:
         self.id_norm = (_f32(sd["id_norm.weight"], device), _f32(sd["id_norm.bias"], device))
         self.cur_pos_emb = _f32(sd["cur_pos_emb"].reshape(-1), device)
         self.mem_pos_emb = _f32(sd["mem_pos_emb"], device)
-        # black boxes: encoder / projector / decoder / id-bank conv as cuDNN calls, bf16 channels-last
-        enc = copy.deepcopy(model.encoder).float()
-        if hasattr(enc, "fold_bn_"):
-            enc.fold_bn_()
-        self.encoder = enc.to(device=device, dtype=BF16).to(memory_format=torch.channels_last).eval()
-        conv_cl = lambda m: copy.deepcopy(m).to(device=device, dtype=BF16).to(memory_format=torch.channels_last).eval()
-        self.encoder_projector = conv_cl(model.encoder_projector)
-        # the FPN head decides the argmax mask: keep it in fp32 (TF32 off) unless told otherwise
+        # ID bank as a lookup table: row-prefix sums of the 17x17 kernel per class (csrc/id_embed.cu)
+        wid = sd["patch_wise_id_bank.weight"].detach().float().cpu()            # [256, n_cls, 17, 17]
+        self.n_id_cls = wid.shape[1]
+        pref = torch.zeros(self.n_id_cls, 17, 18, 256)
+        pref[:, :, 1:, :] = torch.cumsum(wid.permute(1, 2, 3, 0).double(), dim=2).float()
+        self.id_prefix = pref.contiguous().to(device)
+        self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
+        # black boxes (library calls): encoder / projector in bf16 channels-last with the frozen BN folded
+        # into the convs, FPN head in fp32 (it decides the argmax mask)
         import os
+        self.encoder = InferenceResNet(model.encoder, model.encoder_projector, device)
         self.decoder_dtype = BF16 if os.environ.get("RMEM_DECODER_DTYPE", "fp32") == "bf16" else torch.float32
         self.decoder = copy.deepcopy(model.decoder).to(device=device, dtype=self.decoder_dtype).to(
             memory_format=torch.channels_last).eval()
-        self.id_bank = conv_cl(model.patch_wise_id_bank)
+
+
+class InferenceResNet:
+    """ResNet-50 trunk (stride 16) + encoder_projector for inference: frozen-BN affine folded into the
+    conv weights (exact algebra), bf16 channels-last, conv + bias + ReLU (+ residual) issued as single
+    fused cuDNN calls where the installed PyTorch exposes them.  A black box of this tier (cuDNN)."""
+
+    def __init__(self, enc, projector, device):
+        enc = copy.deepcopy(enc).float()
+        enc.fold_bn_()
+        cv = lambda c: (c.weight.detach().to(device=device, dtype=BF16).contiguous(memory_format=torch.channels_last),
+                        c.bias.detach().to(device=device, dtype=BF16), c.stride, c.padding)
+        w1 = enc.conv1.weight.detach()
+        # 3 input channels starve the tensor-core conv kernels: pad to 8 (zeros) -> same result
+        w1p = torch.zeros(w1.shape[0], 8, *w1.shape[2:])
+        w1p[:, :3] = w1
+        self.conv1 = (w1p.to(device=device, dtype=BF16).contiguous(memory_format=torch.channels_last),
+                      enc.conv1.bias.detach().to(device=device, dtype=BF16), enc.conv1.stride, enc.conv1.padding)
+        self.blocks = []
+        for li in (1, 2, 3):
+            stage = []
+            for blk in getattr(enc, "layer%d" % li):
+                down = cv(blk.downsample[0]) if blk.downsample is not None else None
+                stage.append((cv(blk.conv1), cv(blk.conv2), cv(blk.conv3), down))
+            self.blocks.append(stage)
+        self.proj = cv(projector)
+        self.fused = hasattr(torch, "cudnn_convolution_relu") and os_env_flag("RMEM_FUSED_CONV", True)
+
+    @staticmethod
+    def _conv(x, c, relu):
+        w, b, stride, pad = c
+        if relu:
+            return torch.cudnn_convolution_relu(x, w, b, stride, pad, (1, 1), 1)
+        return F.conv2d(x, w, b, stride, pad)
+
+    def __call__(self, img):
+        n, c, h, w = img.shape
+        x = torch.zeros(n, 8, h, w, device=img.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
+        x[:, :3] = img
+        if self.fused:
+            x = self._conv(x, self.conv1, True)
+        else:
+            x = F.relu(F.conv2d(x, self.conv1[0], self.conv1[1], self.conv1[2], self.conv1[3]))
+        x = F.max_pool2d(x, 3, 2, 1)
+        xs = []
+        for stage in self.blocks:
+            for (c1, c2, c3, down) in stage:
+                idt = x if down is None else F.conv2d(x, down[0], down[1], down[2], down[3])
+                if self.fused:
+                    y = self._conv(self._conv(x, c1, True), c2, True)
+                    x = torch.cudnn_convolution_add_relu(y, c3[0], idt, 1.0, c3[1], c3[2], c3[3], (1, 1), 1)
+                else:
+                    y = F.relu(F.conv2d(x, c1[0], c1[1], c1[2], c1[3]))
+                    y = F.relu(F.conv2d(y, c2[0], c2[1], c2[2], c2[3]))
+                    x = F.relu(F.conv2d(y, c3[0], c3[1], c3[2], c3[3]) + idt)
+            xs.append(x)
+        xs.append(F.conv2d(x, self.proj[0], self.proj[1]))
+        return xs
+
+
+def os_env_flag(name, default):
+    import os
+    v = os.environ.get(name)
+    return default if v is None else v not in ("0", "false", "False")
 
 
 def prepare(model, device):
@@ -146,6 +211,7 @@ class _Workspace:
         self.id_emb = z(L, 256)
         self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
         self.zero_order = z(1, dt=torch.int32)
+        self.pred_logits = None                               # [1, 11, H/4, W/4] f32, allocated on first decode
 
 
 def _chunks_per_frame(T):
@@ -180,6 +246,9 @@ class DeAOTEngine:
         self.deaot = True
         self.ws = None
         self.trace = None          # optional dict: per-layer intermediates for the parity tests
+        self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
+        self._graphs = {}
+        self._graph_pool = None
         self.restart_engine()
 
     # ------------------------------------------------------------------ bookkeeping
@@ -193,7 +262,7 @@ class DeAOTEngine:
         self.enc_size_2d = None
         self.enc_hw = None
         self.input_size_2d = None
-        self.pred_id_logits = None
+        self.pred_id_logits = None if getattr(self, "ws", None) is None else self.ws.pred_logits
         self.T = 0                 # frames in the long-term bank (host mirror; deterministic)
         self.T_recorded = 0        # bank length when record_attn_weight was last written
         self.n_long_updates = 0
@@ -206,6 +275,7 @@ class DeAOTEngine:
         n_slots = self.capacity + 1
         if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
             self.ws = _Workspace(self.prep, h, w, n_slots, self.device)
+            self._graphs, self._graph_pool = {}, None             # graphs bake the workspace pointers
 
     @property
     def long_memories_indexes(self):
@@ -224,41 +294,29 @@ class DeAOTEngine:
 
     # ------------------------------------------------------------------ black boxes
     def encode_image(self, img):
-        x = img.to(device=self.device, dtype=BF16, non_blocking=True).contiguous(memory_format=torch.channels_last)
-        xs = self.prep.encoder(x)
-        xs[-1] = self.prep.encoder_projector(xs[-1])
-        return xs
+        """ResNet-50 trunk + encoder_projector (cuDNN, bf16 channels-last) -> [x4, x8, x16, emb16]."""
+        return self.prep.encoder(img.to(device=self.device, non_blocking=True))
 
     def _tokens(self, x_nchw):
         """[1, C, h, w] channels-last tensor -> [L, C] view of the same memory."""
         n, c, h, w = x_nchw.shape
         return x_nchw.permute(0, 2, 3, 1).reshape(h * w, c)
 
-    def assign_identity(self, one_hot_mask, ignore_mask=None):
-        """aot_engine.py:208-232 (MODEL_IGNORE_TOKEN, no id shuffle) + DeAOT.get_id_emb
-        (models/deaot.py:65-69): 17x17 stride-16 conv (cuDNN) then LayerNorm (kernel) -> ws.id_emb."""
-        if ignore_mask is None:
-            ignore_mask = torch.zeros_like(one_hot_mask[:, :1])
-        one_hot_mask = one_hot_mask.clone()
-        one_hot_mask[:, 0] = one_hot_mask[:, 0] * (ignore_mask[:, 0] == 0).to(one_hot_mask.dtype)
-        x = torch.cat((one_hot_mask, ignore_mask), 1).to(BF16).contiguous(memory_format=torch.channels_last)
-        e = self.prep.id_bank(x)                                   # [1, 256, h, w] channels-last
-        tok = self._tokens(e)
-        ws = self.ws
-        g, b = self.prep.id_norm
-        # id_emb goes to the stand-alone buffer and next to curr_ID_V for the ID_V GEMM of every layer
-        ops.layernorm(tok, g, b, ws.id_emb, 0, tok, g, b, ws.idcat[0], 256)
-        for i in range(1, self.prep.num_layers, 2):
-            j = min(i + 1, self.prep.num_layers - 1)
-            ops.layernorm(tok, g, b, ws.idcat[i], 256, tok, g, b, ws.idcat[j], 256)
-        return ws.id_emb
+    def _id_embed(self, label_hw):
+        """assign_identity + get_id_emb (aot_engine.py:208-232, models/deaot.py:65-69) from a hard label
+        map [H, W] (0..10 object ids, 255 = ignore): one gather kernel writes id_emb next to curr_ID_V
+        for every layer's ID_V GEMM."""
+        ws, prep = self.ws, self.prep
+        g, b = prep.id_norm
+        dsts = [(ws.id_emb, 0)] + [(ws.idcat[i], 256) for i in range(prep.num_layers)]
+        ops.id_embed(label_hw, prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)
 
     @staticmethod
-    def _one_hot(mask, cls_num):
-        if mask.dim() == 3:
-            mask = mask.unsqueeze(1)
-        idx = torch.arange(0, cls_num + 1, device=mask.device).view(1, -1, 1, 1)
-        return (mask == idx).float(), (mask == 255).float()
+    def _label_map(mask):
+        """Accepts [H,W], [1,H,W] or [1,1,H,W] label maps; soft / one-hot masks are a training-only form."""
+        if mask.dim() == 4 and mask.shape[1] != 1:
+            raise NotImplementedError("one-hot / probability masks are not on the evaluated path")
+        return mask.reshape(mask.shape[-2], mask.shape[-1])
 
     # ------------------------------------------------------------------ LSTT (kernels)
     def _id_value(self, i, dst):
@@ -275,12 +333,11 @@ class DeAOTEngine:
         ops.lt_attn_combine(ws.part_o, ws.part_m, ws.part_l, ws.tpe_bias if tpe else None,
                             tpe_row_indices(T) if tpe else None, T, ws.L, cpf, gate, out, mass)
 
-    def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights):
+    def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):
         """DualBranchGPM.forward + GatedPropagationModule.forward (transformer.py:765-824, 1091-1236)."""
         ws, prep = self.ws, self.prep
         h, w, L = ws.h, ws.w, ws.L
         ws.tgt.copy_(self._tokens(curr_emb16))
-        T = 1 if is_reference else self.T
         tr = self.trace
         for i, Lw in enumerate(prep.layers):
             # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
@@ -306,7 +363,6 @@ class DeAOTEngine:
             mass = None
             if save_atten_weights and i == 0:
                 mass = ws.mass
-                self.T_recorded = T
             self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
                                          ws.gated_a, mass)
             # short-term 15x15 local attention over the previous frame
@@ -343,9 +399,110 @@ class DeAOTEngine:
         ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws)
         return ws.gn_out
 
+    # ------------------------------------------------------------------ device work (graph-capturable)
+    def _read_body(self, img, img_embs, T, output_size):
+        """Everything match_propogate_one_frame puts on the stream; a pure function of (T, output_size)."""
+        ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device
+        embs = self.encode_image(img) if img_embs is None else img_embs
+        lstt_out = self._lstt_forward(embs[-1], False, True, T)
+        return self._decode(embs, lstt_out, output_size)
+
+    def _write_body(self, label_hw, T, update_long, do_evict):
+        """Everything update_short_term_memory puts on the stream (transformer.py:826-991)."""
+        ws = self.ws
+        self._id_embed(label_hw)
+        for i in range(self.prep.num_layers):
+            # short-term memory <- this frame's K, V and the freshly fused ID_V
+            ws.kprev[i].copy_(ws.kcur[i])
+            ws.vprev[i][:, :512].copy_(ws.vcur[i][:, :512])
+            self._id_value(i, ws.vprev[i])
+        if update_long:
+            srcs, dsts = [], []
+            for i in range(self.prep.num_layers):
+                srcs += [ws.kprev[i], ws.vprev[i]]
+                dsts += [ws.kbank[i], ws.vbank[i]]
+            ops.bank_append(ws.bank_state, T, -1, srcs, dsts)           # frame id from the device counter
+            if do_evict:
+                ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
+                ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T, self.capacity)
+
+    def _decode(self, embs, lstt_out, output_size):
+        """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
+        n, c, h, w = embs[-1].shape
+        dd = self.prep.decoder_dtype
+        lstt_nchw = lstt_out.view(1, h, w, -1).permute(0, 3, 1, 2)        # channels-last view, no copy
+        shortcuts = embs if dd == BF16 else [x.to(dd) for x in embs]
+        logits = self.prep.decoder([shortcuts[-1], lstt_nchw.to(dd)], shortcuts).float()
+        for b, on in enumerate(self.obj_nums):
+            if on + 1 < logits.shape[1]:
+                logits[b, on + 1:] = -1e10
+        ws = self.ws
+        if ws.pred_logits is None or ws.pred_logits.shape != logits.shape:
+            ws.pred_logits = torch.empty_like(logits, memory_format=torch.contiguous_format)
+        ws.pred_logits.copy_(logits)                                      # persistent buffer (read by the write path)
+        self.pred_id_logits = ws.pred_logits
+        if output_size is not None:
+            logits = F.interpolate(logits, size=output_size, mode="bilinear", align_corners=self.align_corners)
+        return logits
+
+    # ------------------------------------------------------------------ CUDA graphs
+    def _run(self, key, body, inputs):
+        """Run ``body(*static_inputs)`` eagerly, or through a CUDA graph captured once per key."""
+        if not self.use_cuda_graphs or self.frame_step < 2 or self.trace is not None:
+            return body(*inputs)                                  # frame 1 is eager: cuDNN picks its algorithms
+        ent = self._graphs.get(key)
+        if ent is None:
+            static_in = [torch.empty(t.shape, dtype=t.dtype, device=self.device) for t in inputs]
+            launches0 = ops.LAUNCHES
+            g = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g, pool=self._graph_pool):
+                out = body(*static_in)
+            ent = (g, static_in, out, ops.LAUNCHES - launches0)
+            ops.LAUNCHES = launches0
+            self._graphs[key] = ent
+            if self._graph_pool is None:
+                self._graph_pool = g.pool()
+        g, static_in, out, n_kernels = ent
+        for s, t in zip(static_in, inputs):
+            s.copy_(t, non_blocking=True)
+        g.replay()
+        ops.LAUNCHES += n_kernels
+        return out
+
+    def precapture(self, output_size=None):
+        """Capture the read / write graphs of every bank length now (capturing records, it does not
+        execute, so the sequence state is untouched). Call after the first propagated frame."""
+        if not self.use_cuda_graphs or self.frame_step < 1:
+            return 0
+        H, W = self.input_size_2d
+        img = torch.zeros(1, 3, H, W, device=self.device)
+        label = torch.zeros(H, W, device=self.device)
+        saved = dict(self._graphs)
+        for T in range(1, self.capacity + 1):
+            for key, body, inputs in self._variants(T, output_size, img, label):
+                if key not in self._graphs:
+                    static_in = [torch.empty_like(t) for t in inputs]
+                    launches0 = ops.LAUNCHES
+                    g = torch.cuda.CUDAGraph()
+                    torch.cuda.synchronize()
+                    with torch.cuda.graph(g, pool=self._graph_pool):
+                        out = body(*static_in)
+                    self._graphs[key] = (g, static_in, out, ops.LAUNCHES - launches0)
+                    ops.LAUNCHES = launches0
+                    if self._graph_pool is None:
+                        self._graph_pool = g.pool()
+        return len(self._graphs) - len(saved)
+
+    def _variants(self, T, output_size, img, label):
+        yield (("read", T, output_size), lambda x, T=T: self._read_body(x, None, T, output_size), [img])
+        yield (("write", T, False, False), lambda m, T=T: self._write_body(m, T, False, False), [label])
+        ev = self.deaot or T + 1 > self.capacity
+        yield (("write", T, True, ev), lambda m, T=T, ev=ev: self._write_body(m, T, True, ev), [label])
+
     # ------------------------------------------------------------------ public frame API
     def add_reference_frame(self, img=None, mask=None, frame_step=-1, obj_nums=None, img_embs=None):
-        """aot_engine.py:241-325."""
+        """aot_engine.py:241-325 (always eager: once per sequence)."""
         if self.obj_nums is None and obj_nums is None:
             raise ValueError("No objects for reference frame!")
         if obj_nums is not None:
@@ -357,81 +514,52 @@ class DeAOTEngine:
         if mask is None:
             raise ValueError("No mask for reference frame!")
         curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
-        mask = mask.to(self.device)
-        one_hot, _ = self._one_hot(mask, self.max_obj_num)
+        label = self._label_map(mask.to(self.device)).float()
         if self.input_size_2d is None:
             in_size = img.shape[2:] if img is not None else mask.shape[-2:]
             self.update_size(in_size, curr_enc_embs[-1].shape[2:])
-        self.assign_identity(one_hot)
+        self._id_embed(label)
         ops.bank_init(self.ws.bank_state, self.frame_step)
         self.T = 1
-        lstt_out = self._lstt_forward(curr_enc_embs[-1], True, False)
+        lstt_out = self._lstt_forward(curr_enc_embs[-1], True, False, 1)
         self.last_mem_step = frame_step
-        self.decode_current_logits(curr_enc_embs, lstt_out)
+        self._decode(curr_enc_embs, lstt_out, None)
 
     def match_propogate_one_frame(self, img=None, img_embs=None, mask=None, output_size=None):
-        """aot_engine.py:398-436 (save_atten_weights=True in eval)."""
+        """aot_engine.py:398-436 (save_atten_weights=True in eval). With CUDA graphs the returned logits
+        live in a buffer that the next call overwrites -- consume them (softmax / argmax) first, as the
+        reference's evaluator does."""
         self.frame_step += 1
-        curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
-        lstt_out = self._lstt_forward(curr_enc_embs[-1], False, True)
-        return self.decode_current_logits(curr_enc_embs, lstt_out, output_size=output_size)
+        T = self.T
+        self.T_recorded = T
+        osz = tuple(output_size) if output_size is not None else None
+        if img_embs is not None:
+            return self._read_body(None, img_embs, T, osz)
+        return self._run(("read", T, osz), lambda x: self._read_body(x, None, T, osz), [img])
 
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
-        """aot_engine.py:438-465 + DeAOT.decode_id_logits (models/deaot.py:57-63). ``curr_lstt_embs`` is
-        the [L, 512] GroupNorm output (or a list whose last entry is it)."""
         emb = curr_lstt_embs[-1] if isinstance(curr_lstt_embs, (list, tuple)) else curr_lstt_embs
-        n, c, h, w = curr_enc_embs[-1].shape
-        lstt_nchw = emb.view(1, h, w, -1).permute(0, 3, 1, 2)      # channels-last view, no copy
-        dd = self.prep.decoder_dtype
-        shortcuts = curr_enc_embs if dd == BF16 else [x.to(dd) for x in curr_enc_embs]
-        logits = self.prep.decoder([shortcuts[-1], lstt_nchw.to(dd)], shortcuts).float()
-        for b, on in enumerate(self.obj_nums):
-            if on + 1 < logits.shape[1]:
-                logits[b, on + 1:] = -1e10
-        self.pred_id_logits = logits.contiguous()
-        if output_size is not None:
-            logits = F.interpolate(logits, size=output_size, mode="bilinear", align_corners=self.align_corners)
-        return logits
+        return self._decode(curr_enc_embs, emb, output_size)
 
     def update_short_term_memory(self, curr_mask, curr_id_emb=None, step=0):
-        """aot_engine.py:327-369 + DualBranchGPM.update_short_memories / update_long_term_memory /
-        restrict_long_memories (transformer.py:826-991)."""
-        ws = self.ws
-        if curr_id_emb is None:
-            curr_mask = curr_mask.to(self.device)
-            ignore = None
-            if curr_mask.dim() == 3 or curr_mask.shape[0] == 1:
-                one_hot, ignore = self._one_hot(curr_mask, self.max_obj_num)
-            else:
-                one_hot = curr_mask
-            self.assign_identity(one_hot, ignore)
-        else:
+        """aot_engine.py:327-369."""
+        if curr_id_emb is not None:
             raise NotImplementedError("pre-computed id embeddings are a training-only path")
-        is_update_long_memory = False
+        label = self._label_map(curr_mask.to(self.device)).float()
+        update_long = False
         if self.frame_step - self.last_mem_step >= self.long_term_mem_gap:
-            is_update_long_memory = True
+            update_long = True
             self.last_mem_step = self.frame_step
-        for i in range(self.prep.num_layers):
-            # short-term memory <- this frame's K, V and the freshly fused ID_V
-            ws.kprev[i].copy_(ws.kcur[i])
-            ws.vprev[i][:, :512].copy_(ws.vcur[i][:, :512])
-            self._id_value(i, ws.vprev[i])
-        if is_update_long_memory:
-            srcs, dsts = [], []
-            for i in range(self.prep.num_layers):
-                srcs += [ws.kprev[i], ws.vprev[i]]
-                dsts += [ws.kbank[i], ws.vbank[i]]
-            ops.bank_append(ws.bank_state, self.T, self.frame_step, srcs, dsts)
-            T_old = self.T
-            if self.deaot or T_old + 1 > self.capacity:
-                if self.T_recorded != T_old:
-                    raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
-                ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
-                ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T_old, self.capacity)
-            self.T = min(T_old + 1, self.capacity)
+        T = self.T
+        do_evict = update_long and (self.deaot or T + 1 > self.capacity)
+        if do_evict and self.T_recorded != T:
+            raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
+        self._run(("write", T, update_long, do_evict),
+                  lambda m: self._write_body(m, T, update_long, do_evict), [label])
+        if update_long:
+            self.T = min(T + 1, self.capacity)
             self.n_long_updates += 1
 
-    # names kept for callers that poke at them
     def eval(self):
         return self
 
@@ -521,6 +649,10 @@ class DeAOTInferEngine:
         self.update_size()
 
     def match_propogate_one_frame(self, img=None, mask=None, output_size=None):
+        if len(self.aot_engines) == 1:                      # <= 10 objects: whole frame in one CUDA graph
+            eng = self.aot_engines[0]
+            eng.long_term_mem_gap = self.long_term_mem_gap
+            return eng.match_propogate_one_frame(img, mask=mask, output_size=output_size)
         img_embs = None
         all_logits = []
         for engine in self.aot_engines:
@@ -534,6 +666,9 @@ class DeAOTInferEngine:
     def update_memory(self, curr_mask):
         for engine, m in zip(self.aot_engines, self.separate_mask(curr_mask)):
             engine.update_short_term_memory(m)
+
+    def precapture(self, output_size=None):
+        return sum(e.precapture(output_size) or 0 for e in self.aot_engines[:1])
 
     def update_size(self):
         self.input_size_2d = self.aot_engines[0].input_size_2d

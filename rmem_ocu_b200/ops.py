@@ -123,6 +123,24 @@ def bank_init(state, frame_step):
     _count("rmem_bank_init")
 
 
+def bank_tick(state):
+    _lib.check(_lib.lib().rmem_bank_tick(_p(state), _stream()), "rmem_bank_tick")
+    _count("rmem_bank_tick")
+
+
+def id_embed(label, prefix, bias, gamma, beta, n_cls, dsts, h, w):
+    """label: f32 [H, W]; dsts: list of (bf16 tensor [h*w, ld], col0)."""
+    H, W = label.shape[-2:]
+    n = len(dsts)
+    dp = (ctypes.c_void_p * n)(*[d.data_ptr() for d, _ in dsts])
+    ld = (ctypes.c_int32 * n)(*[d.stride(0) for d, _ in dsts])
+    c0 = (ctypes.c_int32 * n)(*[c for _, c in dsts])
+    _lib.check(_lib.lib().rmem_id_embed(_p(label), H, W, _p(prefix), _p(bias), _p(gamma), _p(beta), n_cls,
+                                        ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(ld, ctypes.c_void_p),
+                                        ctypes.cast(c0, ctypes.c_void_p), n, h, w, _stream()), "rmem_id_embed")
+    _count("rmem_id_embed")
+
+
 def bank_append(state, T, frame_step, srcs, dsts):
     """Copy each src tensor (one slot's worth) into slot order[T] of the matching bank tensor."""
     n = len(srcs)

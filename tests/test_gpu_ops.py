@@ -133,3 +133,34 @@ def test_foreground_prob(lib_built):
     pl = F.interpolate(logits, size=(h, w), mode="bilinear", align_corners=True)
     ref = (1 - torch.softmax(pl, 1)[:, 0]).flatten()
     assert (fg - ref).abs().max().item() < 1e-5
+
+
+@pytest.mark.parametrize("H,W", [(480, 864), (481, 865), (240, 432)])
+def test_id_embed_vs_oracle(lib_built, H, W):
+    """one-hot + ignore channel + 17x17 s16 conv + id_norm (oracle: restate.Engine.assign_identity)."""
+    from oracle import restate as R
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(7)
+    wt = torch.randn(256, 12, 17, 17) * 0.05
+    bias = torch.randn(256) * 0.1
+    g, b = torch.randn(256), torch.randn(256)
+    lab = torch.zeros(1, 1, H, W)
+    lab[:, :, 40:200, 100:300] = 3
+    lab[:, :, 150:260, 250:500] = 10
+    lab[:, :, 5:30, 0:40] = 255                       # ignore region
+    lab[:, :, 300:310, 600:650] = 77                  # label outside 0..10 / 255 -> no class at all
+    lab[:, :, ::37, ::29] = 1                         # isolated pixels (runs of length 1)
+    one_hot, ignore = R.one_hot_mask(lab, 10)
+    one_hot[:, 0] = one_hot[:, 0] * (ignore == 0).float().squeeze()
+    sd = {"patch_wise_id_bank.weight": wt, "patch_wise_id_bank.bias": bias, "id_norm.weight": g, "id_norm.bias": b}
+    ref = R.get_id_emb(torch.cat((one_hot, ignore), 1), sd, True)          # [1, 256, h, w]
+    h, w = ref.shape[-2:]
+    ref = ref.permute(0, 2, 3, 1).reshape(h * w, 256)
+    pref = torch.zeros(12, 17, 18, 256)
+    pref[:, :, 1:, :] = torch.cumsum(wt.permute(1, 2, 3, 0).double(), dim=2).float()
+    out = torch.zeros(h * w, 512, device="cuda", dtype=torch.bfloat16)
+    out2 = torch.zeros(h * w, 256, device="cuda", dtype=torch.bfloat16)
+    ops.id_embed(lab[0, 0].cuda(), pref.cuda(), bias.cuda(), g.cuda(), b.cuda(), 12, [(out, 256), (out2, 0)], h, w)
+    torch.cuda.synchronize()
+    assert _rel(out[:, 256:].cpu(), ref) < 5e-3
+    assert torch.equal(out[:, 256:], out2) and (out[:, :256] == 0).all()
