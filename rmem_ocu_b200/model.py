@@ -259,6 +259,81 @@ class DeAOTModel(nn.Module):
             p.requires_grad_(False)
 
 
+class _MHAParams(nn.Module):
+    """Parameters of MultiheadAttention (networks/layers/attention.py:8-26)."""
+
+    def __init__(self, d_model, use_linear):
+        super().__init__()
+        if use_linear:
+            self.linear_Q = nn.Linear(d_model, d_model)
+            self.linear_K = nn.Linear(d_model, d_model)
+            self.linear_V = nn.Linear(d_model, d_model)
+        self.projection = nn.Linear(d_model, d_model)
+
+
+class _GNActDWConvParams(nn.Module):
+    """GNActDWConv2d (networks/layers/basic.py:15-35): GroupNorm(32) -> GELU -> 5x5 depth-wise."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.gn = nn.GroupNorm(32, dim)
+        self.conv = nn.Conv2d(dim, dim, 5, padding=2, groups=dim, bias=False)
+
+
+class AOTLayerParams(nn.Module):
+    """SimplifiedTransformerBlock (networks/layers/transformer.py:466-551), MODEL_LINEAR_Q = False."""
+
+    def __init__(self, d_model, dim_feedforward=1024):
+        super().__init__()
+        self.norm1 = nn.LayerNorm(d_model)
+        self.self_attn = _MHAParams(d_model, True)
+        self.norm2 = nn.LayerNorm(d_model)
+        self.linear_Q = nn.Linear(d_model, d_model)
+        self.linear_V = nn.Linear(d_model, d_model)
+        self.linear_QMem = nn.Linear(d_model, d_model)
+        self.linear_VMem = nn.Linear(d_model, d_model)
+        self.norm4 = nn.LayerNorm(d_model)
+        self.linear_KMem = nn.Linear(d_model, d_model)        # present in checkpoints, unused in forward
+        self.long_term_attn = _MHAParams(d_model, False)
+        self.short_term_attn = _MHAParams(d_model, False)
+        self.norm3 = nn.LayerNorm(d_model)
+        self.linear1 = nn.Linear(d_model, dim_feedforward)
+        self.activation = _GNActDWConvParams(dim_feedforward)
+        self.linear2 = nn.Linear(dim_feedforward, d_model)
+
+
+class LSTTParams(nn.Module):
+    """LongShortTermTransformer (transformer.py:133-197): 3 blocks + 3 output LayerNorms."""
+
+    def __init__(self, num_layers, d_model):
+        super().__init__()
+        self.layers = nn.ModuleList([AOTLayerParams(d_model) for _ in range(num_layers)])
+        self.decoder_norms = nn.ModuleList([nn.LayerNorm(d_model) for _ in range(num_layers)])
+
+
+class AOTModel(nn.Module):
+    """Parameter-compatible with reference networks/models/aot.py:AOT (R50-AOT-L)."""
+
+    def __init__(self, cfg: RMemConfig = None):
+        super().__init__()
+        self.cfg = cfg or RMemConfig(model_vos="aot")
+        c = self.cfg
+        self.max_obj_num = c.max_obj_num
+        self.encoder = ResNet50S16()
+        self.encoder_projector = nn.Conv2d(c.encoder_dims[-1], c.embed_dim, 1)
+        self.LSTT = LSTTParams(c.lstt_num, c.embed_dim)
+        self.decoder = FPNHead(c.embed_dim * (c.lstt_num + 1), c.max_obj_num + 1, intermediate=True,
+                               hidden=c.embed_dim, shortcut_dims=c.encoder_dims)
+        id_dim = c.max_obj_num + (2 if c.ignore_token else 1)
+        self.patch_wise_id_bank = nn.Conv2d(id_dim, c.embed_dim, 17, 16, 8)
+        self.cur_pos_emb = nn.Parameter(torch.zeros(1, c.embed_dim))
+        self.mem_pos_emb = nn.Parameter(torch.zeros(c.tpe_rows, c.embed_dim))
+        self.use_temporal_pe = True
+        self.eval()
+        for p in self.parameters():
+            p.requires_grad_(False)
+
+
 def deterministic_init_(state_dict, seed=0, attn_sharpness=2.5):
     """Fill every tensor of a state_dict in place with values that depend only on (seed, key name,
     shape): numpy's legacy RandomState is stable across platforms, so the build container (reference
