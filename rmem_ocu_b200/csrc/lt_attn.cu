@@ -8,11 +8,14 @@
 //
 // Decomposition (split-KV by memory frame):
 //   rmem_lt_attn_partial : grid (q_tile, dv_split, chunk).  One CTA owns 128 queries x 256 value
-//       channels x one key chunk (a memory frame, or a part of one).  TMA streams 64-key K/V tiles
-//       through a 3-stage ring, one elected thread issues tcgen05.mma (S = QK^T into a double
-//       buffered TMEM tile, O += P V into a 256-column TMEM accumulator), four softmax warps own
-//       one query row per thread (tcgen05.ld 32x32b), write bf16 P into a 128B-swizzled smem tile
-//       and rescale O lazily.  Output: un-normalised O, running max m (log2 units) and sum l.
+//       channels x one key chunk (a memory frame, or a part of one).  TMA streams 128-key K and V
+//       tiles through two 2-stage rings; one elected thread issues tcgen05.mma: S = Q K^T into a
+//       double-buffered 128-column TMEM tile, O += P V into a 256-column TMEM accumulator with P
+//       read straight from TMEM (the bf16 probabilities overwrite the S tile in place, so P never
+//       touches shared memory).  Eight softmax warps -- two per TMEM lane quarter, each thread
+//       owning half of one query row -- read S with tcgen05.ld, exchange the row max through
+//       shared memory, exponentiate with packed f32x2 FMAs + MUFU.EX2, rescale O lazily and
+//       write P with tcgen05.st.  Output: un-normalised O, running max m (log2 units) and sum l.
 //   rmem_lt_attn_combine : merges the chunk partials, adds the per-frame TPE bias
 //       (q'.e_row -- a rank-1 term, so K is never rewritten), emits the per-frame attention mass
 //       W[q,t] (= record_attn_weight), applies the gate U and writes bf16.
@@ -23,25 +26,26 @@ namespace rmem {
 using namespace sm100;
 
 constexpr int kBlockM = 128;      // queries per CTA
-constexpr int kBlockN = 64;       // keys per pipeline tile
+constexpr int kBlockN = 128;      // keys per pipeline tile
 constexpr int kDK = 128;          // d_att
 constexpr int kDV = 1024;         // expand_d_vu (V | ID_V)
 constexpr int kDVTile = 256;      // value channels per CTA (TMEM accumulator columns)
 constexpr int kDVSplits = kDV / kDVTile;
-constexpr int kStages = 3;
-constexpr int kThreads = 192;     // warp0 TMA, warp1 MMA, warps2-5 softmax/epilogue
+constexpr int kKStages = 2, kVStages = 2;
+constexpr int kSoftmaxWarps = 8;
+constexpr int kThreads = 64 + 32 * kSoftmaxWarps;   // warp0 TMA, warp1 MMA, warps2-9 softmax/epilogue
 
 constexpr uint32_t kQBytes = kBlockM * kDK * 2;            // 32 KB  [2][128][64]
-constexpr uint32_t kKBytes = kBlockN * kDK * 2;            // 16 KB  [2][64][64]
-constexpr uint32_t kVBytes = kBlockN * kDVTile * 2;        // 32 KB  [4][64][64]
-constexpr uint32_t kStageBytes = kKBytes + kVBytes;        // 48 KB
-constexpr uint32_t kPBytes = kBlockM * kBlockN * 2;        // 16 KB  [128][64]
-constexpr uint32_t kSmemData = kQBytes + kStages * kStageBytes + 2 * kPBytes;
-constexpr uint32_t kSmemTotal = kSmemData + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr uint32_t kKBytes = kBlockN * kDK * 2;            // 32 KB  [2][128][64]
+constexpr uint32_t kVBytes = kBlockN * kDVTile * 2;        // 64 KB  [4][128][64]
+constexpr uint32_t kXchBytes = 2 * 2 * kBlockM * 4;        // row-max exchange, one buffer per S buffer
+constexpr uint32_t kSmemData = kQBytes + kKStages * kKBytes + kVStages * kVBytes;
+constexpr uint32_t kSmemTotal = kSmemData + kXchBytes + 256 /*barriers*/;
+static_assert(kSmemTotal <= 232448, "exceeds the 227 KB shared memory of an sm_100 CTA");
 
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kTmemS0 = 0;      // S buffers: 2 x 64 columns
-constexpr uint32_t kTmemO = 128;     // O: 256 columns
+constexpr uint32_t kTmemS0 = 0;      // S / P buffers: 2 x 128 columns (P = 64 columns, aliased on S)
+constexpr uint32_t kTmemO = 256;     // O: 256 columns
 
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
@@ -60,22 +64,24 @@ __global__ void __launch_bounds__(kThreads, 1)
 lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
                        const __grid_constant__ CUtensorMap tm_k,
                        const __grid_constant__ CUtensorMap tm_v, const LtParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw_addr = smem_u32(smem_raw);
-  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-
+  // 128B-swizzled TMA / UMMA tiles need a 1024-byte aligned base; the dynamic shared window of a kernel
+  // without static shared memory starts 1024-aligned, the declared alignment makes that a requirement.
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;
-  uint8_t* sKV = sQ + kQBytes;
-  uint8_t* sP = sKV + kStages * kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
+  uint8_t* sK = sQ + kQBytes;
+  uint8_t* sV = sK + kKStages * kKBytes;
+  float* xch = reinterpret_cast<float*>(sV + kVStages * kVBytes);   // [2][2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xch + 2 * 2 * kBlockM);
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;            // [3]
-  uint64_t* kv_empty = bars + 4;           // [3]
-  uint64_t* s_full = bars + 7;             // [2]
-  uint64_t* p_full = bars + 9;             // [2]
-  uint64_t* pv_done = bars + 11;           // [2]
-  uint64_t* o_full = bars + 13;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* k_full = bars + 1;             // [2]
+  uint64_t* k_empty = bars + 3;            // [2]
+  uint64_t* v_full = bars + 5;             // [2]
+  uint64_t* v_empty = bars + 7;            // [2]
+  uint64_t* s_full = bars + 9;             // [2]
+  uint64_t* p_full = bars + 11;            // [2]
+  uint64_t* pv_done = bars + 13;           // [2]
+  uint64_t* o_full = bars + 15;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -95,17 +101,18 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   const int n_tiles = (key_len + kBlockN - 1) / kBlockN;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) asm volatile("trap;");
     tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
     mbar_init(q_full, 1);
-    for (int i = 0; i < kStages; ++i) {
-      mbar_init(kv_full + i, 1);
-      mbar_init(kv_empty + i, 1);
-    }
     for (int i = 0; i < 2; ++i) {
+      mbar_init(k_full + i, 1);
+      mbar_init(k_empty + i, 1);
+      mbar_init(v_full + i, 1);
+      mbar_init(v_empty + i, 1);
       mbar_init(s_full + i, 1);
-      mbar_init(p_full + i, 128);
+      mbar_init(p_full + i, 32 * kSoftmaxWarps);
       mbar_init(pv_done + i, 1);
     }
     mbar_init(o_full, 1);
@@ -124,13 +131,14 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       mbar_expect_tx(q_full, kQBytes);
       tma_load_3d(sQ, &tm_q, q_full, 0, q_tile * kBlockM, 0);
       for (int j = 0; j < n_tiles; ++j) {
-        const int st = j % kStages;
-        if (j >= kStages) mbar_wait(kv_empty + st, ((j / kStages) - 1) & 1);
-        uint8_t* dK = sKV + st * kStageBytes;
-        uint8_t* dV = dK + kKBytes;
-        mbar_expect_tx(kv_full + st, kStageBytes);
-        tma_load_4d(dK, &tm_k, kv_full + st, 0, key_begin + j * kBlockN, 0, slot);
-        tma_load_4d(dV, &tm_v, kv_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot);
+        const int st = j & 1;
+        const uint32_t ph = ((j >> 1) - 1) & 1;
+        if (j >= 2) mbar_wait(k_empty + st, ph);
+        mbar_expect_tx(k_full + st, kKBytes);
+        tma_load_4d(sK + st * kKBytes, &tm_k, k_full + st, 0, key_begin + j * kBlockN, 0, slot);
+        if (j >= 2) mbar_wait(v_empty + st, ph);
+        mbar_expect_tx(v_full + st, kVBytes);
+        tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot);
       }
     }
   } else if (warp == 1) {
@@ -140,10 +148,10 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockM, kDVTile, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
       auto issue_qk = [&](int j) {
-        const int st = j % kStages;
-        mbar_wait(kv_full + st, (j / kStages) & 1);
+        const int st = j & 1;
+        mbar_wait(k_full + st, (j >> 1) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(sKV + st * kStageBytes);
+        const uint32_t k_addr = smem_u32(sK + st * kKBytes);
         const uint32_t d = tmem_base + kTmemS0 + (j & 1) * kBlockN;
 #pragma unroll
         for (int ks = 0; ks < kDK / 16; ++ks) {
@@ -152,25 +160,28 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
           const uint64_t b = make_desc_sw128(k_addr + blk * (kBlockN * 128) + within * 32, 16, 1024);
           mma_bf16_ss(d, a, b, idesc_qk, ks > 0);
         }
+        tc_commit(k_empty + st);
         tc_commit(s_full + (j & 1));
       };
       mbar_wait(q_full, 0);
       issue_qk(0);
       for (int j = 0; j < n_tiles; ++j) {
+        // S(j+1) goes into the buffer P(j-1) lived in: PV(j-1) was issued before it, and tcgen05.mma
+        // instructions of one thread execute in issue order.
         if (j + 1 < n_tiles) issue_qk(j + 1);
         mbar_wait(p_full + (j & 1), (j >> 1) & 1);
+        const int st = j & 1;
+        mbar_wait(v_full + st, (j >> 1) & 1);
         tc_fence_after();
-        const int st = j % kStages;
-        const uint32_t v_addr = smem_u32(sKV + st * kStageBytes + kKBytes);
-        const uint32_t p_addr = smem_u32(sP + (j & 1) * kPBytes);
+        const uint32_t v_addr = smem_u32(sV + st * kVBytes);
+        const uint32_t p_tmem = tmem_base + kTmemS0 + (j & 1) * kBlockN;   // bf16 P: 64 columns
         const uint32_t d = tmem_base + kTmemO;
 #pragma unroll
         for (int ks = 0; ks < kBlockN / 16; ++ks) {
-          const uint64_t a = make_desc_sw128(p_addr + ks * 32, 16, 1024);
           const uint64_t b = make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024);
-          mma_bf16_ss(d, a, b, idesc_pv, (j > 0) || (ks > 0));
+          mma_bf16_ts(d, p_tmem + ks * 8, b, idesc_pv, (j > 0) || (ks > 0));
         }
-        tc_commit(kv_empty + st);
+        tc_commit(v_empty + st);
         tc_commit(pv_done + (j & 1));
       }
       tc_commit(o_full);
@@ -178,32 +189,42 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   } else {
     // ------------------------------------------------------------------ softmax + epilogue
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+    const int hf = (warp - 2) >> 2;               // which half of the row's columns this thread owns
     const int row = quarter * 32 + lane;          // query row inside the tile
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t pair_bar = 1 + quarter;        // named barrier shared by the two warps of a quarter
     const int q_global = q_tile * kBlockM + row;
     float m_used = -INFINITY;
     float l_sum = 0.f;
     const float c = p.scale_log2;
 
     for (int j = 0; j < n_tiles; ++j) {
-      mbar_wait(s_full + (j & 1), (j >> 1) & 1);
+      const int b = j & 1;
+      mbar_wait(s_full + b, (j >> 1) & 1);
       tc_fence_after();
-      uint32_t sr[2][32];
-      const uint32_t s_addr = tmem_base + lane_addr + kTmemS0 + (j & 1) * kBlockN;
-      tmem_ld32(s_addr, sr[0]);
-      tmem_ld32(s_addr + 32, sr[1]);
-      tmem_ld_wait();
-      const int valid = key_len - j * kBlockN;    // keys valid in this tile (>= 1)
+      uint32_t sr[64];
+      {
+        uint32_t(&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
+        uint32_t(&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[32]);
+        const uint32_t s_addr = tmem_base + lane_addr + kTmemS0 + b * kBlockN + hf * 64;
+        tmem_ld32(s_addr, lo);
+        tmem_ld32(s_addr + 32, hi);
+        tmem_ld_wait();
+      }
+      const int valid = key_len - j * kBlockN - hf * 64;   // valid columns in this half (may be <= 0)
+      if (valid < 64) {                                       // warp-uniform: only the chunk's last tile
+#pragma unroll
+        for (int i = 0; i < 64; ++i)
+          if (i >= valid) sr[i] = 0xff800000u;                // -inf
+      }
       float mx = -INFINITY;
 #pragma unroll
-      for (int h = 0; h < 2; ++h)
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(sr[h][i]) * c;
-          if (h * 32 + i >= valid) s = -INFINITY;
-          sr[h][i] = __float_as_uint(s);
-          mx = fmaxf(mx, s);
-        }
+      for (int i = 0; i < 64; i += 2)
+        mx = fmaxf(mx, fmaxf(__uint_as_float(sr[i]), __uint_as_float(sr[i + 1])));
+      // row max across the two halves (the partner thread lives in warp +-4)
+      xch[(b * 2 + hf) * kBlockM + row] = mx;
+      named_bar_sync(pair_bar, 64);
+      mx = fmaxf(mx, xch[(b * 2 + (hf ^ 1)) * kBlockM + row]) * c;
       // lazy rescale: keep the reference max unless it grew by more than the threshold
       const bool grow = mx > m_used + kRescaleThreshold;
       float scale = 1.f;
@@ -212,12 +233,12 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         m_new = mx;
         scale = fast_exp2(m_used - m_new);            // 0 when m_used == -inf
       }
-      if (j > 0 && __any_sync(0xffffffffu, grow)) {
+      if (j > 0 && __any_sync(0xffffffffu, grow)) {    // same decision in both warps of the pair
         mbar_wait(pv_done + ((j - 1) & 1), ((j - 1) >> 1) & 1);
         tc_fence_after();
-        const uint32_t o_addr = tmem_base + lane_addr + kTmemO;
+        const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
 #pragma unroll 1
-        for (int cb = 0; cb < kDVTile / 32; ++cb) {
+        for (int cb = 0; cb < kDVTile / 64; ++cb) {
           uint32_t orow[32];
           tmem_ld32(o_addr + cb * 32, orow);
           tmem_ld_wait();
@@ -225,34 +246,27 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
           for (int i = 0; i < 32; ++i) orow[i] = __float_as_uint(__uint_as_float(orow[i]) * scale);
           tmem_st32(o_addr + cb * 32, orow);
         }
-        tmem_st_wait();
       }
       l_sum *= scale;
       m_used = m_new;
-      // P buffer (j&1) was last read by PV(j-2)
-      if (j >= 2) mbar_wait(pv_done + (j & 1), ((j - 2) >> 1) & 1);
-      uint8_t* pbuf = sP + (j & 1) * kPBytes;
-      float acc = 0.f;
+      const float neg_m = -m_used;
+      float acc0 = 0.f, acc1 = 0.f;
+      uint32_t packed[32];
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {              // 8 chunks of 8 keys (16 bytes of bf16)
-        uint32_t packed[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int i0 = ch * 8 + e * 2;
-          const float p0 = fast_exp2(__uint_as_float(sr[i0 >> 5][i0 & 31]) - m_used);
-          const float p1 = fast_exp2(__uint_as_float(sr[(i0 + 1) >> 5][(i0 + 1) & 31]) - m_used);
-          const __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
-          // accumulate what the tensor core will actually see (bf16-rounded) so O / l is consistent
-          acc += __bfloat162float(b2.x) + __bfloat162float(b2.y);
-          packed[e] = *reinterpret_cast<const uint32_t*>(&b2);
-        }
-        *reinterpret_cast<uint4*>(pbuf + sw128_offset(row, ch)) =
-            make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      for (int i = 0; i < 64; i += 2) {
+        float x0, x1;
+        fma_f32x2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, c, neg_m, neg_m);
+        const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+        add_f32x2(acc0, acc1, acc0, acc1, p0, p1);
+        packed[i >> 1] = pack_bf16x2(p0, p1);
       }
-      l_sum += acc;
-      fence_proxy_async_smem();
+      l_sum += acc0 + acc1;
+      // P (bf16, 64 columns) overwrites the first half of this S buffer; both partner threads have
+      // their S values in registers (they passed tcgen05.wait::ld before the pair barrier).
+      tmem_st32(tmem_base + lane_addr + kTmemS0 + b * kBlockN + hf * 32, packed);
+      tmem_st_wait();
       tc_fence_before();
-      mbar_arrive(p_full + (j & 1));
+      mbar_arrive(p_full + b);
     }
 
     // epilogue: O (fp32, un-normalised) -> part_o ; m, l -> part_m / part_l
@@ -260,12 +274,18 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       mbar_wait(o_full, 0);
       tc_fence_after();
     }
+    // l of the two halves: exchanged through the buffer the last tile did NOT use (its last readers
+    // passed the last tile's pair barrier)
+    const int xb = (n_tiles & 1);                 // last tile used buffer (n_tiles - 1) & 1
+    xch[(xb * 2 + hf) * kBlockM + row] = l_sum;
+    named_bar_sync(pair_bar, 64);
+    const float l_tot = l_sum + xch[(xb * 2 + (hf ^ 1)) * kBlockM + row];
     const bool row_ok = q_global < p.L;
     float* orow_g = p.part_o + (static_cast<size_t>(chunk) * p.L + (row_ok ? q_global : 0)) * kDV +
-                    dv_split * kDVTile;
-    const uint32_t o_addr = tmem_base + lane_addr + kTmemO;
+                    dv_split * kDVTile + hf * (kDVTile / 2);
+    const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
 #pragma unroll 1
-    for (int cb = 0; cb < kDVTile / 32; ++cb) {
+    for (int cb = 0; cb < kDVTile / 64; ++cb) {
       uint32_t orow[32];
       if (n_tiles > 0) {
         tmem_ld32(o_addr + cb * 32, orow);
@@ -281,9 +301,9 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
               make_uint4(orow[i], orow[i + 1], orow[i + 2], orow[i + 3]);
       }
     }
-    if (row_ok && dv_split == 0) {
+    if (row_ok && dv_split == 0 && hf == 0) {
       p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;
-      p.part_l[static_cast<size_t>(chunk) * p.L + q_global] = l_sum;
+      p.part_l[static_cast<size_t>(chunk) * p.L + q_global] = l_tot;
     }
     tc_fence_before();
   }
@@ -310,55 +330,69 @@ struct CombineParams {
   float* attn_mass;           // [L][T] or nullptr
 };
 
+constexpr int kMaxChunks = RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME;   // 64
+
 __global__ void __launch_bounds__(256)
 lt_attn_combine_kernel(const CombineParams p) {
   const int q = blockIdx.x;
   const int n_chunks = p.T * p.chunks_per_frame;
-  __shared__ float w_sh[RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME];
-  __shared__ float inv_sh;
-  if (threadIdx.x == 0) {
-    float mm[RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME];
+  __shared__ float w_sh[kMaxChunks];      // w_c / denom
+  __shared__ float wl_sh[kMaxChunks];     // w_c l_c / denom
+  if (threadIdx.x < 32) {
+    // lane c (and c + 32) owns one chunk; max / sum through warp shuffles
+    const int lane = threadIdx.x;
+    float mm[2], ll[2];
     float M = -INFINITY;
-    for (int c = 0; c < n_chunks; ++c) {
-      const int t = c / p.chunks_per_frame;
-      float m = p.part_m[static_cast<size_t>(c) * p.L + q];
-      const float l = p.part_l[static_cast<size_t>(c) * p.L + q];
-      if (p.tpe_bias) m += p.tpe_bias[q * 4 + p.tpe_rows[t]];
-      if (!(l > 0.f)) m = -INFINITY;               // empty chunk
-      mm[c] = m;
-      M = fmaxf(M, m);
-    }
-    float denom = 0.f;
-    for (int c = 0; c < n_chunks; ++c) {
-      const float w = (mm[c] == -INFINITY) ? 0.f : exp2f(mm[c] - M);
-      w_sh[c] = w;
-      denom += w * p.part_l[static_cast<size_t>(c) * p.L + q];
-    }
-    const float inv = 1.f / denom;
-    inv_sh = inv;
-    if (p.attn_mass) {
-      for (int t = 0; t < p.T; ++t) {
-        float s = 0.f;
-        for (int k = 0; k < p.chunks_per_frame; ++k) {
-          const int c = t * p.chunks_per_frame + k;
-          s += w_sh[c] * p.part_l[static_cast<size_t>(c) * p.L + q];
-        }
-        p.attn_mass[static_cast<size_t>(q) * p.T + t] = s * inv;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int cidx = lane + 32 * k;
+      mm[k] = -INFINITY;
+      ll[k] = 0.f;
+      if (cidx < n_chunks) {
+        const int t = cidx / p.chunks_per_frame;
+        float m = p.part_m[static_cast<size_t>(cidx) * p.L + q];
+        const float l = p.part_l[static_cast<size_t>(cidx) * p.L + q];
+        if (p.tpe_bias) m += p.tpe_bias[q * 4 + p.tpe_rows[t]];
+        if (l > 0.f) { mm[k] = m; ll[k] = l; }    // empty chunk: stays -inf / 0
       }
+      M = fmaxf(M, mm[k]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    float w[2], denom = 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      w[k] = (mm[k] == -INFINITY) ? 0.f : exp2f(mm[k] - M);
+      denom += w[k] * ll[k];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) denom += __shfl_xor_sync(0xffffffffu, denom, o);
+    const float inv = 1.f / denom;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int cidx = lane + 32 * k;
+      if (cidx < n_chunks) {
+        w_sh[cidx] = w[k] * inv;
+        wl_sh[cidx] = w[k] * ll[k] * inv;
+      }
+    }
+    __syncwarp();
+    if (p.attn_mass && lane < p.T) {
+      float sacc = 0.f;
+      for (int k = 0; k < p.chunks_per_frame; ++k) sacc += wl_sh[lane * p.chunks_per_frame + k];
+      p.attn_mass[static_cast<size_t>(q) * p.T + lane] = sacc;
     }
   }
   __syncthreads();
-  const float inv = inv_sh;
   const int col = threadIdx.x * 4;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int c = 0; c < n_chunks; ++c) {
-    const float w = w_sh[c];
+  for (int cidx = 0; cidx < n_chunks; ++cidx) {
+    const float w = w_sh[cidx];
     if (w == 0.f) continue;
     const float4 o = *reinterpret_cast<const float4*>(
-        p.part_o + (static_cast<size_t>(c) * p.L + q) * kDV + col);
+        p.part_o + (static_cast<size_t>(cidx) * p.L + q) * kDV + col);
     acc.x += w * o.x; acc.y += w * o.y; acc.z += w * o.z; acc.w += w * o.w;
   }
-  acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
   if (p.gate) {
     const uint2 g = *reinterpret_cast<const uint2*>(p.gate + static_cast<size_t>(q) * kDV + col);
     const __nv_bfloat162 g01 = *reinterpret_cast<const __nv_bfloat162*>(&g.x);

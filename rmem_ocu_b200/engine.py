@@ -212,7 +212,7 @@ class _Workspace:
         self.dw = z(L, 2048)
         self.rel, self.probs = z(L, 256, dt=f32), z(L, 225, dt=f32)
         self.sa_qk, self.sa_v, self.sa_u = z(L, 128), z(L, 1024), z(L, 1024)
-        n_chunks = max(n_slots, _lib.MAX_CHUNKS_PER_FRAME)
+        n_chunks = max(T * _chunks_per_frame(T, L) for T in range(1, n_slots + 1))
         self.part_o = z(n_chunks, L, 1024, dt=f32)
         self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
         self.mass = z(L * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight [L, T]
@@ -225,9 +225,18 @@ class _Workspace:
         self.pred_logits = None                               # [1, 11, H/4, W/4] f32, allocated on first decode
 
 
-def _chunks_per_frame(T):
-    # keep >= ~3 key chunks per query tile so the split-KV grid covers the 148 SMs when the bank is short
-    return 3 if T == 1 else (2 if T == 2 else 1)
+def _chunks_per_frame(T, L, n_sms=148):
+    """Split-KV granularity of the long-term attention grid (q tiles x 4 value splits x T x cpf CTAs, one
+    CTA per SM): the cpf in 1..4 that minimises waves x key tiles per chunk."""
+    q_tiles = -(-L // 128)
+    best, best_cost = 1, None
+    for cpf in range(1, _lib.MAX_CHUNKS_PER_FRAME + 1):
+        ctas = q_tiles * 4 * T * cpf
+        tiles = -(-(-(-L // cpf)) // 128)
+        cost = -(-ctas // n_sms) * (tiles + 1.5)          # + fixed prologue / epilogue per CTA
+        if best_cost is None or cost < best_cost:
+            best, best_cost = cpf, cost
+    return best
 
 
 class DeAOTEngine:
@@ -339,7 +348,7 @@ class DeAOTEngine:
 
     def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass):
         ws = self.ws
-        cpf = _chunks_per_frame(T)
+        cpf = _chunks_per_frame(T, ws.L)
         ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
         ops.lt_attn_combine(ws.part_o, ws.part_m, ws.part_l, ws.tpe_bias if tpe else None,
                             tpe_row_indices(T) if tpe else None, T, ws.L, cpf, gate, out, mass)
