@@ -210,6 +210,20 @@ int rmem_id_embed(const float* label, int H, int W, const float* prefix, const f
                   const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w,
                   void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Decoding head (FPNSegmentationHead, decoders/fpn.py:36-68): the convolutions stay cuDNN calls; the
+ * GroupNorm(8) + ReLU of every ConvGN (layers/basic.py:60-70, fpn.py:44-63) and the bilinear
+ * (align_corners=True) upsampling + shortcut add (fpn.py:49-60) run here on the channels-last
+ * [H*W][C] view.
+ *   rmem_groupnorm_nhwc: x, y f32 [P][C] (C = 64 / 128 / 256, C/groups a power of two in [4,32]);
+ *       gamma/beta f32 [C]; relu != 0 applies max(.,0); workspace 16*groups bytes (zeroed by the call).
+ *   rmem_upsample_add_nhwc: out[ho*wo][C] = a[ho*wo][C] (or 0 when NULL) + bilinear(x[hi*wi][C]).
+ */
+int rmem_groupnorm_nhwc(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
+                        int groups, int relu, void* workspace, void* stream);
+int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, float* out, int ho, int wo, int C,
+                           void* stream);
+
 /* fg[q] = 1 - softmax_c(bilinear_align_corners(pred_id_logits -> (h,w)))[0]
  * (aot_engine.py:355-362).  logits f32 [C][Hs][Ws] -> fg f32 [h*w]. */
 int rmem_foreground_prob(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,

@@ -96,6 +96,14 @@ int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gat
                               int h, int w, void* stream) {
   return local_aggregate_launch(probs, v, gate, out, h, w, ST(stream));
 }
+int rmem_groupnorm_nhwc(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
+                        int groups, int relu, void* workspace, void* stream) {
+  return groupnorm_nhwc_launch(x, gamma, beta, y, P, C, groups, relu, workspace, ST(stream));
+}
+int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, float* out, int ho, int wo, int C,
+                           void* stream) {
+  return upsample_add_nhwc_launch(x, hi, wi, a, out, ho, wo, C, ST(stream));
+}
 int rmem_bank_tick(void* bank_state, void* stream) { return bank_tick_launch(bank_state, ST(stream)); }
 int rmem_id_embed(const float* label, int H, int W, const float* prefix, const float* bias,
                   const float* gamma, const float* beta, int n_cls, void* const* dst_host,

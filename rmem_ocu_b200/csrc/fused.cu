@@ -85,49 +85,69 @@ int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0,
 }
 
 // ------------------------------------------------------------------------------------------------
-// 5x5 depth-wise conv, channels-last. Thread = (pixel, 8 channels); weights tap-major [25][C].
+// 5x5 depth-wise conv, channels-last.  Thread = (channel pair, pixel row, strip of 16 pixels): the 25
+// weights of its two channels and a sliding 5x5 window live in registers, so every output costs five
+// new 4-byte loads (coalesced: consecutive lanes = consecutive channel pairs) and 25 packed f32x2 FMAs.
+// Weights tap-major [25][C].
+constexpr int kDwStrip = 16;
+
+__device__ __forceinline__ void fma2(float2& d, const float2 a, const float2 b) {
+  asm("{\n\t.reg .b64 ra, rb, rc;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%0, %1};\n\t"
+      "fma.rn.f32x2 rc, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rc;\n\t}\n"
+      : "+f"(d.x), "+f"(d.y)
+      : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+}
+
 __global__ void __launch_bounds__(128)
 dwconv5_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int xcol0, const float* __restrict__ wt,
                __nv_bfloat16* __restrict__ y, int ldy, int ycol0, int h, int w, int C) {
-  const int cg = C / 8;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= h * w * cg) return;
-  const int c = (idx % cg) * 8;
-  const int pix = idx / cg;
-  const int py = pix / w, px = pix - py * w;
-  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int c = (blockIdx.z * 128 + threadIdx.x) * 2;
+  if (c >= C) return;
+  const int py = blockIdx.y;
+  const int x0 = blockIdx.x * kDwStrip;
+  float2 wgt[25];
+#pragma unroll
+  for (int t = 0; t < 25; ++t) wgt[t] = *reinterpret_cast<const float2*>(wt + t * C + c);
+  const __nv_bfloat16* xc = x + xcol0 + c;
+  auto ld = [&](int yy, int xx) -> float2 {
+    if (yy < 0 || yy >= h || xx < 0 || xx >= w) return make_float2(0.f, 0.f);
+    const uint32_t raw = *reinterpret_cast<const uint32_t*>(xc + static_cast<size_t>(yy * w + xx) * ldx);
+    return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
+  };
+  float2 win[5][5];        // win[dy][k]: input at (py + dy - 2, xx + k - 2)
 #pragma unroll
   for (int dy = 0; dy < 5; ++dy) {
-    const int yy = py + dy - 2;
-    if (yy < 0 || yy >= h) continue;
+    win[dy][0] = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int dx = 0; dx < 5; ++dx) {
-      const int xx = px + dx - 2;
-      if (xx < 0 || xx >= w) continue;
-      const uint4 raw = *reinterpret_cast<const uint4*>(
-          x + static_cast<size_t>(yy * w + xx) * ldx + xcol0 + c);
-      const __nv_bfloat162* hv = reinterpret_cast<const __nv_bfloat162*>(&raw);
-      const float4 w0 = *reinterpret_cast<const float4*>(wt + (dy * 5 + dx) * C + c);
-      const float4 w1 = *reinterpret_cast<const float4*>(wt + (dy * 5 + dx) * C + c + 4);
-      acc[0] += __bfloat162float(hv[0].x) * w0.x; acc[1] += __bfloat162float(hv[0].y) * w0.y;
-      acc[2] += __bfloat162float(hv[1].x) * w0.z; acc[3] += __bfloat162float(hv[1].y) * w0.w;
-      acc[4] += __bfloat162float(hv[2].x) * w1.x; acc[5] += __bfloat162float(hv[2].y) * w1.y;
-      acc[6] += __bfloat162float(hv[3].x) * w1.z; acc[7] += __bfloat162float(hv[3].y) * w1.w;
+    for (int k = 1; k < 5; ++k) win[dy][k] = ld(py + dy - 2, x0 + k - 3);
+  }
+#pragma unroll
+  for (int i = 0; i < kDwStrip; ++i) {
+    const int xx = x0 + i;
+    if (xx < w) {
+      float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int dy = 0; dy < 5; ++dy) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) win[dy][k] = win[dy][k + 1];
+        win[dy][4] = ld(py + dy - 2, xx + 2);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) fma2(acc, win[dy][k], wgt[dy * 5 + k]);
+      }
+      const __nv_bfloat162 o = __floats2bfloat162_rn(acc.x, acc.y);
+      *reinterpret_cast<__nv_bfloat162*>(y + static_cast<size_t>(py * w + xx) * ldy + ycol0 + c) = o;
     }
   }
-  uint4 pk;
-  __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) o[i] = __floats2bfloat162_rn(acc[2 * i], acc[2 * i + 1]);
-  *reinterpret_cast<uint4*>(y + static_cast<size_t>(pix) * ldy + ycol0 + c) = pk;
 }
 
 int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
                    int h, int w, int C, cudaStream_t stream) {
   if ((C % 8) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1)
     return set_error(RMEM_ERR_ARG, "dwconv5: C / ld / col offsets must be multiples of 8");
-  const int n = h * w * (C / 8);
-  dwconv5_kernel<<<(n + 127) / 128, 128, 0, stream>>>(
+  dim3 grid((w + kDwStrip - 1) / kDwStrip, h, (C + 255) / 256);
+  dwconv5_kernel<<<grid, 128, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(x), ldx, xcol0, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0,
       h, w, C);
   return check_launch("dwconv5_kernel");

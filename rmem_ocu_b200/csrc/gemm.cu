@@ -88,72 +88,76 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       tc_commit(acc_full);
     }
   } else {
+    // ---------------------------------------------------------------- epilogue (4 warps, 32 rows each)
+    // Phase 1: the thread that owns TMEM lane r (= output row) reads 32 accumulator columns, adds the
+    // bias and applies the activation in registers, and parks them in a per-warp shared-memory tile.
+    // Phase 2: the warp re-reads the tile transposed -- half a warp per row, two adjacent columns per
+    // lane -- so every global access (store, or load + add + store for the accumulate mode) is a
+    // contiguous 64 B / 128 B run instead of 32 scattered rows.
     const int quarter = warp & 3;
-    const int row = m0 + quarter * 32 + lane;
+    const int row_l = quarter * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+    float* tile = reinterpret_cast<float*>(smem) + quarter * (32 * 33);      // [32 rows][33] (stage 0 is idle)
+    float* bias_s = reinterpret_cast<float*>(smem + kGStageBytes);           // [128]        (stage 1 is idle)
     mbar_wait(acc_full, 0);
     tc_fence_after();
+    // every MMA has completed, so every TMA load has landed and the stage buffers are free
+    if (p.bias) {
+      const int cg = n0 + row_l;
+      bias_s[row_l] = cg < p.N ? __ldg(p.bias + cg) : 0.f;
+    } else {
+      bias_s[row_l] = 0.f;
+    }
+    named_bar_sync(1, 128);
+    const int c2 = 2 * (lane & 15);        // column pair of this lane in phase 2
+    const int rpar = lane >> 4;            // row parity of this half-warp
 #pragma unroll 1
     for (int cb = 0; cb < kGN / 32; ++cb) {
       const int c0 = n0 + cb * 32;
       if (c0 >= p.N) break;                       // warp-uniform
-      uint32_t r[32];
-      tmem_ld32(tmem_base + lane_addr + cb * 32, r);
-      tmem_ld_wait();
       // segment lookup (warp-uniform: segments start on multiples of 32 columns)
       int si = -1;
-      for (int s = 0; s < p.n_seg; ++s)
-        if (c0 >= p.seg[s].col_begin && c0 < p.seg[s].col_end) si = s;
-      if (si < 0 || row >= p.M) continue;
+      for (int sgi = 0; sgi < p.n_seg; ++sgi)
+        if (c0 >= p.seg[sgi].col_begin && c0 < p.seg[sgi].col_end) si = sgi;
+      if (si < 0) continue;
       const rmem_gemm_segment sg = p.seg[si];
       int ncol = sg.col_end - c0;
       if (ncol > 32) ncol = 32;
-      float v[32];
+      uint32_t r[32];
+      tmem_ld32(tmem_base + lane_addr + cb * 32, r);
+      tmem_ld_wait();
+      __syncwarp();                               // phase 2 of the previous block has finished with `tile`
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        float x = __uint_as_float(r[i]);
-        if (p.bias && i < ncol) x += __ldg(p.bias + c0 + i);
-        if (sg.act == RMEM_ACT_SILU) x = silu_f(x);
-        v[i] = x;
+        float x = __uint_as_float(r[i]) + bias_s[cb * 32 + i];
+        if (sg.act == RMEM_ACT_SILU) x = __fdividef(x, 1.f + __expf(-x));
+        tile[lane * 33 + i] = x;
       }
-      const size_t off = static_cast<size_t>(row) * sg.ld + sg.dst_col0 + (c0 - sg.col_begin);
-      if (sg.mode == RMEM_OUT_BF16) {
-        __nv_bfloat16* d = static_cast<__nv_bfloat16*>(sg.dst) + off;
-        if (ncol == 32) {
+      __syncwarp();
+      const bool ok0 = c2 < ncol, ok1 = c2 + 1 < ncol;
+      const size_t col_off = static_cast<size_t>(sg.dst_col0 + (c0 - sg.col_begin) + c2);
 #pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            uint4 pk;
-            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[i], v[i + 1]);
-            __nv_bfloat162 t1 = __floats2bfloat162_rn(v[i + 2], v[i + 3]);
-            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[i + 4], v[i + 5]);
-            __nv_bfloat162 t3 = __floats2bfloat162_rn(v[i + 6], v[i + 7]);
-            pk.x = *reinterpret_cast<uint32_t*>(&t0); pk.y = *reinterpret_cast<uint32_t*>(&t1);
-            pk.z = *reinterpret_cast<uint32_t*>(&t2); pk.w = *reinterpret_cast<uint32_t*>(&t3);
-            *reinterpret_cast<uint4*>(d + i) = pk;
-          }
+      for (int it = 0; it < 16; ++it) {
+        const int rl = 2 * it + rpar;
+        const int row = m0 + quarter * 32 + rl;
+        const float v0 = tile[rl * 33 + c2], v1 = tile[rl * 33 + c2 + 1];
+        if (row >= p.M || !ok0) continue;
+        const size_t off = static_cast<size_t>(row) * sg.ld + col_off;
+        if (sg.mode == RMEM_OUT_BF16) {
+          __nv_bfloat16* d = static_cast<__nv_bfloat16*>(sg.dst) + off;
+          if (ok1) *reinterpret_cast<uint32_t*>(d) = pack_bf16x2(v0, v1);
+          else d[0] = __float2bfloat16(v0);
         } else {
-          for (int i = 0; i < ncol; ++i) d[i] = __float2bfloat16(v[i]);
-        }
-      } else {
-        float* d = static_cast<float*>(sg.dst) + off;
-        if (sg.mode == RMEM_OUT_F32_ACCUM) {
-          if (ncol == 32) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 o = *reinterpret_cast<float4*>(d + i);
-              o.x += v[i]; o.y += v[i + 1]; o.z += v[i + 2]; o.w += v[i + 3];
-              *reinterpret_cast<float4*>(d + i) = o;
+          float* d = static_cast<float*>(sg.dst) + off;
+          if (ok1) {
+            float2 o = make_float2(v0, v1);
+            if (sg.mode == RMEM_OUT_F32_ACCUM) {
+              const float2 old = *reinterpret_cast<const float2*>(d);
+              o.x += old.x; o.y += old.y;
             }
+            *reinterpret_cast<float2*>(d) = o;
           } else {
-            for (int i = 0; i < ncol; ++i) d[i] += v[i];
-          }
-        } else {
-          if (ncol == 32) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4)
-              *reinterpret_cast<float4*>(d + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-          } else {
-            for (int i = 0; i < ncol; ++i) d[i] = v[i];
+            d[0] = (sg.mode == RMEM_OUT_F32_ACCUM) ? d[0] + v0 : v0;
           }
         }
       }
@@ -193,6 +197,9 @@ int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bia
     if (segs[s].col_begin % 32 || segs[s].col_end <= segs[s].col_begin || segs[s].col_end > N ||
         !segs[s].dst)
       return set_error(RMEM_ERR_ARG, "gemm: segment must start on a multiple of 32 columns");
+    if ((segs[s].ld % 2) || (segs[s].dst_col0 % 2) ||
+        (reinterpret_cast<uintptr_t>(segs[s].dst) % (segs[s].mode == RMEM_OUT_BF16 ? 4 : 8)))
+      return set_error(RMEM_ERR_ARG, "gemm: destination ld / column offset must be even and the base 8-byte aligned");
   }
   CUtensorMap tm_a, tm_w;
   if (int e = encode_2d(&tm_a, a, K, M, static_cast<uint64_t>(lda) * 2, kGM)) return e;

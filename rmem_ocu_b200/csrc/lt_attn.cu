@@ -48,6 +48,7 @@ constexpr uint32_t kTmemS0 = 0;      // S / P buffers: 2 x 128 columns (P = 64 c
 constexpr uint32_t kTmemO = 256;     // O: 256 columns
 
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
+constexpr int kPolyEvery = 4;              // every 4th pair of exponentials runs on the FMA pipes (25 %)
 
 struct LtParams {
   int L;                 // tokens per frame
@@ -63,7 +64,8 @@ struct LtParams {
 __global__ void __launch_bounds__(kThreads, 1)
 lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
                        const __grid_constant__ CUtensorMap tm_k,
-                       const __grid_constant__ CUtensorMap tm_v, const LtParams p) {
+                       const __grid_constant__ CUtensorMap tm_v,
+                       const __grid_constant__ CUtensorMap tm_o, const LtParams p) {
   // 128B-swizzled TMA / UMMA tiles need a 1024-byte aligned base; the dynamic shared window of a kernel
   // without static shared memory starts 1024-aligned, the declared alignment makes that a requirement.
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -105,6 +107,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_o);
     mbar_init(q_full, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(k_full + i, 1);
@@ -256,7 +259,13 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       for (int i = 0; i < 64; i += 2) {
         float x0, x1;
         fma_f32x2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, c, neg_m, neg_m);
-        const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+        float p0, p1;
+        if ((i >> 1) % kPolyEvery == kPolyEvery - 1) {
+          exp2_poly_x2(p0, p1, x0, x1);             // FMA / ALU pipes
+        } else {
+          p0 = fast_exp2(x0);                       // MUFU.EX2
+          p1 = fast_exp2(x1);
+        }
         add_f32x2(acc0, acc1, acc0, acc1, p0, p1);
         packed[i >> 1] = pack_bf16x2(p0, p1);
       }
@@ -281,8 +290,10 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     named_bar_sync(pair_bar, 64);
     const float l_tot = l_sum + xch[(xb * 2 + (hf ^ 1)) * kBlockM + row];
     const bool row_ok = q_global < p.L;
-    float* orow_g = p.part_o + (static_cast<size_t>(chunk) * p.L + (row_ok ? q_global : 0)) * kDV +
-                    dv_split * kDVTile + hf * (kDVTile / 2);
+    // O tile -> shared memory (the K / V rings are idle now: o_full means every MMA has completed) as
+    // eight [128 rows][32 fp32] blocks in the 128B-swizzled layout, then one thread issues TMA stores:
+    // full-line writes, rows beyond L clipped by the tensor map.
+    uint8_t* stage = sK;
     const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
 #pragma unroll 1
     for (int cb = 0; cb < kDVTile / 64; ++cb) {
@@ -294,12 +305,20 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
 #pragma unroll
         for (int i = 0; i < 32; ++i) orow[i] = 0u;
       }
-      if (row_ok) {
+      uint8_t* blk = stage + (hf * 4 + cb) * (kBlockM * 128);
 #pragma unroll
-        for (int i = 0; i < 32; i += 4)
-          *reinterpret_cast<uint4*>(orow_g + cb * 32 + i) =
-              make_uint4(orow[i], orow[i + 1], orow[i + 2], orow[i + 3]);
-      }
+      for (int ch = 0; ch < 8; ++ch)
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row, ch)) =
+            make_uint4(orow[4 * ch], orow[4 * ch + 1], orow[4 * ch + 2], orow[4 * ch + 3]);
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(5, 32 * kSoftmaxWarps);
+    if (warp == 2 && lane == 0) {
+#pragma unroll 1
+      for (int cbk = 0; cbk < kDVTile / 32; ++cbk)
+        tma_store_3d(&tm_o, stage + cbk * (kBlockM * 128), dv_split * kDVTile + cbk * 32, q_tile * kBlockM, chunk);
+      tma_store_commit();
+      tma_store_wait_all();
     }
     if (row_ok && dv_split == 0 && hf == 0) {
       p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;
@@ -448,6 +467,19 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
     const uint32_t box[4] = {64, kBlockN, kDVTile / 64, 1};
     if (int e = encode_map(&tm_v, vbank, 4, dims, strides, box)) return e;
   }
+  CUtensorMap tm_o;
+  {
+    auto fn = get_tensor_map_encoder();
+    if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
+    const uint64_t dims[3] = {kDV, static_cast<uint64_t>(L), static_cast<uint64_t>(T * chunks_per_frame)};
+    const uint64_t strides[2] = {kDV * 4, static_cast<uint64_t>(L) * kDV * 4};
+    const uint32_t box[3] = {32, kBlockM, 1};
+    const uint32_t es[3] = {1, 1, 1};
+    CUresult r = fn(&tm_o, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, part_o, dims, strides, box, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (partial O) failed");
+  }
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(lt_attn_partial_kernel,
@@ -465,7 +497,7 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
   p.part_l = part_l;
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
   dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, p.n_chunks);
-  lt_attn_partial_kernel<<<grid, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, p);
+  lt_attn_partial_kernel<<<grid, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, tm_o, p);
   return check_launch("lt_attn_partial_kernel");
 }
 

@@ -46,6 +46,10 @@ int local_scores_launch(const void* q, const void* k, const float* rel, int ld_r
                         int w, cudaStream_t stream);
 int local_aggregate_launch(const float* probs, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream);
+int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
+                          int groups, int relu, void* workspace, cudaStream_t stream);
+int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, float* out, int ho, int wo,
+                             int C, cudaStream_t stream);
 int bank_tick_launch(void* state, cudaStream_t stream);
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
                     const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,

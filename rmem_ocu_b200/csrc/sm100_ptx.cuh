@@ -89,6 +89,30 @@ __device__ __forceinline__ void add_f32x2(float& d0, float& d1, float a0, float 
       : "=f"(d0), "=f"(d1)
       : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
+// 2^x for two values on the FMA / ALU pipes instead of the MUFU: floor split by a round-down magic add,
+// degree-3 minimax polynomial for 2^f on [0,1) (relative error 8.6e-5, far inside bf16 rounding), exponent
+// patched in with integer adds.  x is clamped to >= -126 (2^-126 instead of 0 for masked scores).
+// Used for a fraction of the softmax exponentials so the XU pipe is not the bottleneck.
+__device__ __forceinline__ void exp2_poly_x2(float& y0, float& y1, float x0, float x1) {
+  x0 = fmaxf(x0, -126.f);
+  x1 = fmaxf(x1, -126.f);
+  float t0, t1;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\t"
+      "add.rm.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}\n"
+      : "=f"(t0), "=f"(t1)
+      : "f"(x0), "f"(x1), "f"(12582912.f));
+  float n0, n1, f0, f1, p0, p1;
+  add_f32x2(n0, n1, t0, t1, -12582912.f, -12582912.f);          // floor(x), exact
+  fma_f32x2(f0, f1, n0, n1, -1.f, -1.f, x0, x1);                // x - floor(x) in [0, 1)
+  fma_f32x2(p0, p1, f0, f1, 0.0770670f, 0.0770670f, 0.2276450f, 0.2276450f);
+  fma_f32x2(p0, p1, p0, p1, f0, f1, 0.6951168f, 0.6951168f);
+  fma_f32x2(p0, p1, p0, p1, f0, f1, 1.f, 1.f);
+  y0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  y1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
+
 // bf16x2 pack: low half = lo, high half = hi (round to nearest even)
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   uint32_t r;
@@ -134,6 +158,20 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uin
       "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+
+// TMA store (shared -> global), bulk-group completion.  Out-of-bounds parts of the box are not written.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(m)),
+      "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// waits until the bulk stores of this thread have completed (shared memory read AND global writes done)
+__device__ __forceinline__ void tma_store_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ----------------------------------------------------------------------------- TMEM

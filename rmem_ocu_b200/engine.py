@@ -100,9 +100,59 @@ class PreparedDeAOT:
         # agreement measures the hot-path kernels, not the black-box backbone's bf16 rounding
         enc_dtype = torch.float32 if os.environ.get("RMEM_ENCODER_DTYPE", "bf16") == "fp32" else BF16
         self.encoder = InferenceResNet(model.encoder, model.encoder_projector, device, enc_dtype)
-        self.decoder_dtype = BF16 if os.environ.get("RMEM_DECODER_DTYPE", "fp32") == "bf16" else torch.float32
-        self.decoder = copy.deepcopy(model.decoder).to(device=device, dtype=self.decoder_dtype).to(
-            memory_format=torch.channels_last).eval()
+        self.decoder = InferenceFPN(sd, device, intermediate=False)
+
+
+class InferenceFPN:
+    """FPNSegmentationHead (reference decoders/fpn.py:36-68) for inference, channels-last fp32 (it decides
+    the argmax mask): the convolutions are cuDNN calls (a black box of this tier, TF32 as PyTorch's default),
+    GroupNorm(8)+ReLU and the bilinear upsample + shortcut add run in csrc/decoder.cu."""
+
+    def __init__(self, sd, device, intermediate, prefix="decoder."):
+        self.intermediate = intermediate
+        cl = lambda w: w.detach().to(device=device, dtype=torch.float32).contiguous(memory_format=torch.channels_last)
+        f = lambda t: _f32(t, device)
+        self.w = {}
+        for name in ("conv_in", "conv_16x", "conv_8x", "conv_4x"):
+            self.w[name] = (cl(sd[prefix + name + ".conv.weight"]), f(sd[prefix + name + ".conv.bias"]),
+                            f(sd[prefix + name + ".gn.weight"]), f(sd[prefix + name + ".gn.bias"]))
+        for name in ("adapter_16x", "adapter_8x", "adapter_4x", "conv_out"):
+            self.w[name] = (cl(sd[prefix + name + ".weight"]), f(sd[prefix + name + ".bias"]))
+        self.gn_ws = torch.zeros(16, device=device, dtype=torch.float64)
+
+    @staticmethod
+    def _tok(x):
+        """channels-last [1, C, H, W] -> [H*W, C] view of the same memory."""
+        n, c, h, w = x.shape
+        return x.permute(0, 2, 3, 1).reshape(h * w, c)
+
+    def _conv_gn_relu(self, x, name):
+        w, b, g, be = self.w[name]
+        y = F.conv2d(x, w, b, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
+        t = self._tok(y)
+        ops.groupnorm_nhwc(t, g, be, t, 8, True, self.gn_ws)          # in place
+        return y
+
+    def _up_add(self, x, shortcut, name):
+        w, b = self.w[name]
+        a = F.conv2d(shortcut, w, b).contiguous(memory_format=torch.channels_last)
+        hi, wi = x.shape[-2:]
+        ho, wo = a.shape[-2:]
+        ta = self._tok(a)
+        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo)   # a += bilinear(x), in place
+        return a
+
+    def __call__(self, inputs, shortcuts):
+        x = torch.cat(inputs, dim=1) if self.intermediate else inputs[-1]
+        x = x.float().contiguous(memory_format=torch.channels_last)
+        sc = [s.float().contiguous(memory_format=torch.channels_last) for s in shortcuts]
+        x = self._conv_gn_relu(x, "conv_in")
+        w, b = self.w["adapter_16x"]
+        x = self._conv_gn_relu(F.conv2d(sc[-2], w, b) + x, "conv_16x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x"), "conv_8x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-4], "adapter_4x"), "conv_4x")
+        w, b = self.w["conv_out"]
+        return F.conv2d(x, w, b)
 
 
 class InferenceResNet:
@@ -449,10 +499,8 @@ class DeAOTEngine:
     def _decode(self, embs, lstt_out, output_size):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
         n, c, h, w = embs[-1].shape
-        dd = self.prep.decoder_dtype
         lstt_nchw = lstt_out.view(1, h, w, -1).permute(0, 3, 1, 2)        # channels-last view, no copy
-        shortcuts = [x.to(dd) for x in embs]                              # no-op when the dtypes agree
-        logits = self.prep.decoder([shortcuts[-1], lstt_nchw.to(dd)], shortcuts).float()
+        logits = self.prep.decoder([embs[-1], lstt_nchw], embs)
         for b, on in enumerate(self.obj_nums):
             if on + 1 < logits.shape[1]:
                 logits[b, on + 1:] = -1e10

@@ -13,7 +13,7 @@ from ._lib import (ACT_NONE, ACT_SILU, OUT_BF16, OUT_F32, OUT_F32_ACCUM, GemmSeg
 
 # number of librmem_b200 kernels launched through this module (bench.py reports it as gpu_launches)
 LAUNCHES = 0
-_KERNELS_PER_CALL = {"rmem_groupnorm_tokens": 2}
+_KERNELS_PER_CALL = {"rmem_groupnorm_tokens": 2, "rmem_groupnorm_nhwc": 2}
 
 
 def _count(name):
@@ -78,6 +78,22 @@ def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
     _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), L, C,
                                                 groups, _p(workspace), _stream()), "rmem_groupnorm_tokens")
     _count("rmem_groupnorm_tokens")
+
+
+def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace):
+    """GroupNorm(+ReLU) of a channels-last [1, C, H, W] f32 tensor viewed as [H*W, C]."""
+    P, C = x.shape
+    _lib.check(_lib.lib().rmem_groupnorm_nhwc(_p(x), _p(gamma), _p(beta), _p(y), P, C, groups, 1 if relu else 0,
+                                              _p(workspace), _stream()), "rmem_groupnorm_nhwc")
+    _count("rmem_groupnorm_nhwc")
+
+
+def upsample_add_nhwc(x, hi, wi, a, out, ho, wo):
+    """out = a + bilinear_align_corners(x); x f32 [hi*wi, C], a / out f32 [ho*wo, C]."""
+    C = x.shape[1]
+    _lib.check(_lib.lib().rmem_upsample_add_nhwc(_p(x), hi, wi, _p(a), _p(out), ho, wo, C, _stream()),
+               "rmem_upsample_add_nhwc")
+    _count("rmem_upsample_add_nhwc")
 
 
 def tpe_prepare(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias):

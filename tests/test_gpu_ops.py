@@ -164,3 +164,53 @@ def test_id_embed_vs_oracle(lib_built, H, W):
     torch.cuda.synchronize()
     assert _rel(out[:, 256:].cpu(), ref) < 5e-3
     assert torch.equal(out[:, 256:], out2) and (out[:, :256] == 0).all()
+
+
+@pytest.mark.parametrize("C,H,W", [(256, 30, 54), (128, 60, 108), (128, 120, 216), (64, 7, 5)])
+def test_groupnorm_nhwc(lib_built, C, H, W):
+    """GroupNorm(8) + ReLU of the decoder's ConvGN blocks (basic.py:60-70, fpn.py:44-63) vs F.group_norm."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(8)
+    x = (torch.randn(1, C, H, W, device="cuda") * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    g, b = torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
+    ref = F.relu(F.group_norm(x, 8, g, b, 1e-5))
+    t = x.permute(0, 2, 3, 1).reshape(H * W, C)
+    ws = torch.empty(16, device="cuda", dtype=torch.float64)
+    ops.groupnorm_nhwc(t, g, b, t, 8, True, ws)
+    torch.cuda.synchronize()
+    assert (x - ref).abs().max().item() < 2e-4
+
+
+@pytest.mark.parametrize("C,hi,wi,ho,wo", [(256, 30, 54, 60, 108), (128, 60, 108, 120, 216), (128, 31, 55, 61, 109)])
+def test_upsample_add_nhwc(lib_built, C, hi, wi, ho, wo):
+    """adapter(shortcut) + bilinear(align_corners=True) upsample of the FPN head (fpn.py:49-60)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(9)
+    x = torch.randn(1, C, hi, wi, device="cuda").contiguous(memory_format=torch.channels_last)
+    a = torch.randn(1, C, ho, wo, device="cuda").contiguous(memory_format=torch.channels_last)
+    ref = a + F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
+    ta = a.permute(0, 2, 3, 1).reshape(ho * wo, C)
+    ops.upsample_add_nhwc(x.permute(0, 2, 3, 1).reshape(hi * wi, C), hi, wi, ta, ta, ho, wo)
+    torch.cuda.synchronize()
+    assert (a - ref).abs().max().item() < 1e-4
+
+
+def test_decoder_head_vs_oracle(lib_built):
+    """InferenceFPN (cuDNN convs + csrc/decoder.cu) against the oracle's restatement of fpn.py:36-68."""
+    from oracle import restate as R
+    from rmem_ocu_b200.engine import InferenceFPN
+    from tests import _synth
+    _, sd = _synth.models(2)
+    torch.manual_seed(10)
+    h, w = 15, 27
+    embs = [torch.randn(1, 256, 4 * h, 4 * w), torch.randn(1, 512, 2 * h, 2 * w), torch.randn(1, 1024, h, w),
+            torch.randn(1, 256, h, w)]
+    lstt = torch.randn(1, 512, h, w)
+    with torch.no_grad():
+        ref = R.fpn_decoder([embs[-1], lstt], embs, sd, intermediate=False)
+    fpn = InferenceFPN(sd, torch.device("cuda"), intermediate=False)
+    cl = lambda t: t.cuda().contiguous(memory_format=torch.channels_last)
+    with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        out = fpn([cl(embs[-1]), cl(lstt)], [cl(e) for e in embs])
+    torch.cuda.synchronize()
+    assert _rel(out.cpu(), ref) < 1e-4
