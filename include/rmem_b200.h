@@ -73,6 +73,52 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
 
 
 /* ---------------------------------------------------------------------------------------------
+ * Multi-head attention, AOT (8 heads x 32, d_model 256): MultiheadAttention.forward
+ * (layers/attention.py:28-81, explicit path :45-64) in its three roles inside
+ * SimplifiedTransformerBlock.forward (layers/transformer.py:553-692): long-term attention over the
+ * restricted bank (:632-635), short-term attention over the previous frame (:657-662, T = 1) and
+ * self-attention (:565-571, T = 1).  Same split-KV scheme as the DeAOT kernel.
+ *
+ *   q        bf16 [L][ldq]  (256 channels used)  queries (for the bank: cur_pos_emb already added)
+ *   k, v     bf16 [n_slots][L][ld]  slot s starts at element s * slot_stride (ignored if n_slots == 1)
+ *   order    i32  [T]       logical bank position -> slot
+ *   part_o   f32  [T*cpf][L][256];  part_m, part_l  f32 [T*cpf][8][L]
+ */
+int rmem_mha_partial(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride,
+                     const void* v, int ldv, int64_t v_slot_stride, const int32_t* order, int T, int L,
+                     int n_slots, int chunks_per_frame, float* part_o, float* part_m, float* part_l,
+                     void* stream);
+
+/* Merge of the chunk partials per head + temporal positional embedding (transformer.py:594-629, as a
+ * per-(head, frame) score bias) + attention-weight recording averaged over heads (:636-643).
+ *   tpe_bias  f32 [L][8][4] (log2 units) or NULL;  out bf16 [L][ld_out] at column out_col0;
+ *   attn_mass f32 [L][T] or NULL
+ */
+int rmem_mha_combine(const float* part_o, const float* part_m, const float* part_l,
+                     const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
+                     int chunks_per_frame, void* out, int ld_out, int out_col0, float* attn_mass,
+                     void* stream);
+
+/* q_time = bf16(q + cur_pos_emb) [L][256];  tpe_bias[q][head][r] = log2e/sqrt(32) * (q_time_head . mem_pos_emb[r]_head)
+ * (transformer.py:594-629);  cur_pos_emb f32 [256], mem_pos_emb f32 [4][256]. */
+int rmem_tpe_prepare_mha(const void* q, int ldq, const float* cur_pos_emb, const float* mem_pos_emb,
+                         void* q_time, float* tpe_bias, int L, void* stream);
+
+/* LayerNorm(256) of xa (+ xb), f32 or bf16 inputs, with up to three outputs: bf16 `out`, bf16
+ * `out_plus` = LN(.) + post_add (q = k = norm1(x) + self_pos, transformer.py:563-564) and f32 `out_f32`
+ * (decoder_norms, :248-259).  The two-input form is norm4(local_K + curr_K) of :657-660.  Unused
+ * outputs / xb / post_add are NULL. */
+int rmem_layernorm_ex(const void* xa, int lda, const void* xb, int ldb, int in_bf16, const float* gamma,
+                      const float* beta, void* out, int ld_out, int col_out, const float* post_add,
+                      int ld_add, void* out_plus, int ld_plus, int col_plus, float* out_f32, int ld_f32,
+                      int col_f32, int L, int C, void* stream);
+
+/* GroupNorm(groups, C = 32 * groups) + exact GELU over a token matrix x f32 [L][C] -> bf16 [L][C]
+ * (GNActDWConv2d front half, layers/basic.py:15-35).  workspace: 16 * groups bytes (zeroed by the call). */
+int rmem_groupnorm_gelu_tokens(const float* x, const float* gamma, const float* beta, void* out, int L,
+                               int C, int groups, void* workspace, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Linear layer with fused epilogue: C[M,N] = A[M,K] * W[N,K]^T + bias, then per column segment an
  * activation and a destination (so one launch produces e.g. K | silu(V) | silu(U) into three
  * buffers, or adds the projection straight into the fp32 residual streams).

@@ -41,7 +41,7 @@ CLIPS = {
     "clip_deaot_gap": ("r50_deaotl", 128, 192, 16, 2, 2, 3, 0, 1002),
     "clip_deaot_mid": ("r50_deaotl", 240, 432, 9, 3, 2, 1, 0, 1003),
     "clip_deaot_480p": ("r50_deaotl", 480, 864, 8, 5, 4, 1, 0, 1000),
-    "clip_aot_small": ("r50_aotl", 128, 192, 14, 1, 3, 1, 0, 1004),
+    "clip_aot_small": ("r50_aotl", 128, 192, 14, 1, 3, 1, 0, 1012),
     "clip_aot_repeat": ("r50_aotl", 128, 192, 16, 2, 2, 1, 4, 1005),
     "clip_aot_480p": ("r50_aotl", 480, 864, 10, 1, 3, 1, 0, 1000),
 }
@@ -84,7 +84,33 @@ def gen_clip(name):
     out = dict(meta=np.array([H, W, n, n_obj, latter, gap, repeat, cseed], np.int64),
                model=np.array(mname), masks=np.stack(masks), indexes=idx_arr,
                logits_ref_frame=logits[0], logits_first=logits[1], logits_last=logits[n - 1])
+    out["margins"] = oracle_margins(name, idx_log)
     return out
+
+
+def oracle_margins(name, ref_idx_log):
+    """Decision margin (runner-up score minus the evicted frame's score) of every eviction of the clip, from the
+    oracle restatement run on the same inputs (the reference does not expose it); inf where nothing was scored.
+    Doubles as a cross-check: the oracle's bank indexes must equal the reference's after every frame.  The GPU
+    tests use it to assert that a fixture has no near-tie a bf16 kernel could not resolve."""
+    from oracle import restate as R
+    mname, H, W, n, n_obj, latter, gap, repeat, cseed = CLIPS[name]
+    kind = "deaot" if "deaot" in mname else "aot"
+    _, sd = _synth.models(latter, vos=kind)
+    imgs, lab = _synth.clip(H, W, n, n_obj, cseed, repeat)
+    eng = R.Engine(sd, kind == "deaot", 1, latter, long_term_mem_gap=gap)
+    margins = np.full(n - 1, np.inf, np.float32)
+    with torch.no_grad():
+        eng.add_reference_frame(imgs[0], lab, obj_nums=[10], frame_step=0)
+        for f in range(1, n):
+            lg = eng.match_propogate_one_frame(imgs[f], output_size=(H, W))
+            label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
+            n_log = len(eng.evict_log)
+            eng.update_short_term_memory(F.interpolate(label, size=(H, W), mode="nearest"))
+            if len(eng.evict_log) > n_log and eng.evict_log[-1]["dropped"]:
+                margins[f - 1] = eng.evict_log[-1]["margin"]
+            assert list(eng.long_memories_indexes) == list(ref_idx_log[f - 1]), (name, f)
+    return margins
 
 
 # ------------------------------------------------------------------------------------------------

@@ -61,6 +61,14 @@ _SIGNATURES = {
     "rmem_last_error": [],
     "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
+    "rmem_mha_partial": [_c_void_p, _c_int, _c_void_p, _c_int, ctypes.c_int64, _c_void_p, _c_int, ctypes.c_int64,
+                         _c_void_p] + [_c_int] * 4 + [_c_void_p] * 4,
+    "rmem_mha_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
+    "rmem_tpe_prepare_mha": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int, _c_void_p],
+    "rmem_layernorm_ex": [_c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_void_p, _c_void_p,
+                          _c_void_p, _c_int, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int,
+                          _c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p],
+    "rmem_groupnorm_gelu_tokens": [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p] * 2,
     "rmem_linear": [_c_void_p, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_int,
                     _c_void_p, _c_int, _c_void_p],
     "rmem_layernorm": [_c_void_p] * 4 + [_c_int] * 2 + [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p],

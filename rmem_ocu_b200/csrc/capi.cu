@@ -65,6 +65,36 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
 
 #define ST(s) static_cast<cudaStream_t>(s)
 
+int rmem_mha_partial(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride,
+                     const void* v, int ldv, int64_t v_slot_stride, const int32_t* order, int T, int L,
+                     int n_slots, int chunks_per_frame, float* part_o, float* part_m, float* part_l,
+                     void* stream) {
+  return mha_partial_launch(q, ldq, k, ldk, k_slot_stride, v, ldv, v_slot_stride, order, T, L, n_slots,
+                            chunks_per_frame, part_o, part_m, part_l, ST(stream));
+}
+int rmem_mha_combine(const float* part_o, const float* part_m, const float* part_l,
+                     const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
+                     int chunks_per_frame, void* out, int ld_out, int out_col0, float* attn_mass,
+                     void* stream) {
+  return mha_combine_launch(part_o, part_m, part_l, tpe_bias, tpe_rows_host, T, L, chunks_per_frame, out,
+                            ld_out, out_col0, attn_mass, ST(stream));
+}
+int rmem_tpe_prepare_mha(const void* q, int ldq, const float* cur_pos_emb, const float* mem_pos_emb,
+                         void* q_time, float* tpe_bias, int L, void* stream) {
+  return tpe_prepare_mha_launch(q, ldq, cur_pos_emb, mem_pos_emb, q_time, tpe_bias, L, ST(stream));
+}
+int rmem_layernorm_ex(const void* xa, int lda, const void* xb, int ldb, int in_bf16, const float* gamma,
+                      const float* beta, void* out, int ld_out, int col_out, const float* post_add,
+                      int ld_add, void* out_plus, int ld_plus, int col_plus, float* out_f32, int ld_f32,
+                      int col_f32, int L, int C, void* stream) {
+  return layernorm_ex_launch(xa, lda, xb, ldb, in_bf16, gamma, beta, out, ld_out, col_out, post_add, ld_add,
+                             out_plus, ld_plus, col_plus, out_f32, ld_f32, col_f32, L, C, ST(stream));
+}
+int rmem_groupnorm_gelu_tokens(const float* x, const float* gamma, const float* beta, void* out, int L,
+                               int C, int groups, void* workspace, void* stream) {
+  return groupnorm_gelu_tokens_launch(x, gamma, beta, out, L, C, groups, workspace, ST(stream));
+}
+
 int rmem_linear(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N,
                 int K, const rmem_gemm_segment* segments_host, int n_segments, void* stream) {
   return gemm_launch(a, lda, w, ldw, bias, M, N, K, segments_host, n_segments, ST(stream));

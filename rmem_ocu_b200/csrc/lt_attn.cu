@@ -48,7 +48,7 @@ constexpr uint32_t kTmemS0 = 0;      // S / P buffers: 2 x 128 columns (P = 64 c
 constexpr uint32_t kTmemO = 256;     // O: 256 columns
 
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
-constexpr int kPolyEvery = 4;              // every 4th pair of exponentials runs on the FMA pipes (25 %)
+constexpr int kPolyEvery = 3;              // every 3rd pair of exponentials runs on the FMA pipes (~1/3)
 
 struct LtParams {
   int L;                 // tokens per frame
@@ -318,7 +318,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       for (int cbk = 0; cbk < kDVTile / 32; ++cbk)
         tma_store_3d(&tm_o, stage + cbk * (kBlockM * 128), dv_split * kDVTile + cbk * 32, q_tile * kBlockM, chunk);
       tma_store_commit();
-      tma_store_wait_all();
+      tma_store_wait_read();
     }
     if (row_ok && dv_split == 0 && hf == 0) {
       p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;

@@ -28,6 +28,22 @@ int lt_attn_combine_launch(const float* part_o, const float* part_m, const float
                            int chunks_per_frame, const void* gate, void* out, float* attn_mass,
                            cudaStream_t stream);
 
+int mha_partial_launch(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride, const void* v,
+                       int ldv, int64_t v_slot_stride, const int32_t* order_dev, int T, int L, int n_slots,
+                       int chunks_per_frame, float* part_o, float* part_m, float* part_l,
+                       cudaStream_t stream);
+int mha_combine_launch(const float* part_o, const float* part_m, const float* part_l, const float* tpe_bias,
+                       const int32_t* tpe_rows_host, int T, int L, int chunks_per_frame, void* out, int ld_out,
+                       int out_col0, float* attn_mass, cudaStream_t stream);
+int tpe_prepare_mha_launch(const void* q, int ldq, const float* cur, const float* mem, void* q_time, float* bias,
+                           int L, cudaStream_t stream);
+int layernorm_ex_launch(const void* xa, int lda, const void* xb, int ldb, int in_bf16, const float* gamma,
+                        const float* beta, void* out, int ld_o, int col_o, const float* post_add, int ld_add,
+                        void* out_plus, int ld_p, int col_p, float* out_f32, int ld_f, int col_f, int L, int C,
+                        cudaStream_t stream);
+int groupnorm_gelu_tokens_launch(const float* x, const float* gamma, const float* beta, void* out, int L, int C,
+                                 int groups, void* workspace, cudaStream_t stream);
+
 int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
                 const rmem_gemm_segment* segs, int n_seg, cudaStream_t stream);
 int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,

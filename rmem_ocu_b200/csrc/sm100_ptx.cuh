@@ -50,11 +50,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded spin: a broken pipeline traps (-> launch error the host reports) instead of hanging the GPU.
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// Time-bounded wait: a broken pipeline traps after ~2 s (-> launch error the host reports) instead of
+// hanging the GPU.  try_wait itself may suspend for a system-dependent time, so the bound is on the
+// wall clock, not on the number of polls.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
+  uint64_t t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) { asm volatile("trap;"); }
+    if ((++spins & 0xfffu) == 0) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 2000000000ull) { asm volatile("trap;"); }
+    }
   }
 }
 
@@ -169,9 +182,10 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* s
       : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-// waits until the bulk stores of this thread have completed (shared memory read AND global writes done)
-__device__ __forceinline__ void tma_store_wait_all() {
-  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+// waits until the bulk stores of this thread have finished reading shared memory (the global writes are
+// completed by the hardware before the grid ends; what must not happen is the CTA freeing its smem early)
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
 // ----------------------------------------------------------------------------- TMEM

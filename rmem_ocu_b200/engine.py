@@ -33,6 +33,8 @@ def _f32(t, dev):
 class PreparedDeAOT:
     """Device-side repack of a DeAOT model's weights (done once per model per device)."""
 
+    deaot = True
+
     def __init__(self, model, device):
         sd = model.state_dict()
         self.device = device
@@ -143,7 +145,7 @@ class InferenceFPN:
         return a
 
     def __call__(self, inputs, shortcuts):
-        x = torch.cat(inputs, dim=1) if self.intermediate else inputs[-1]
+        x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
         x = x.float().contiguous(memory_format=torch.channels_last)
         sc = [s.float().contiguous(memory_format=torch.channels_last) for s in shortcuts]
         x = self._conv_gn_relu(x, "conv_in")
@@ -231,8 +233,18 @@ def prepare(model, device):
     import os
     key = (str(device), os.environ.get("RMEM_ENCODER_DTYPE", "bf16"), os.environ.get("RMEM_DECODER_DTYPE", "fp32"))
     if key not in cache:
-        cache[key] = PreparedDeAOT(model, device)
+        if is_deaot_model(model):
+            cache[key] = PreparedDeAOT(model, device)
+        else:
+            from .engine_aot import PreparedAOT
+            enc_dtype = torch.float32 if key[1] == "fp32" else BF16
+            cache[key] = PreparedAOT(model, device, InferenceResNet, InferenceFPN, enc_dtype)
     return cache[key]
+
+
+def is_deaot_model(model):
+    """DeAOT (gated propagation, two branches) or AOT (multi-head attention), told apart by the parameters."""
+    return any(k.endswith("linear_QV.weight") for k in model.state_dict().keys())
 
 
 class _Workspace:
@@ -313,13 +325,29 @@ class DeAOTEngine:
         self.capacity = int(self.cfg.FORMER_MEM_LEN) + int(self.cfg.LATTER_MEM_LEN)
         if self.capacity + 1 > _lib.MAX_BANK:
             raise _lib.RmemError("FORMER_MEM_LEN + LATTER_MEM_LEN + 1 exceeds RMEM_MAX_BANK")
-        self.deaot = True
+        self.deaot = self.prep.deaot
+        if self.deaot != self._family_deaot:
+            raise _lib.RmemError("%s was given a%s model" % (type(self).__name__, "n AOT" if self._family_deaot
+                                                             else " DeAOT"))
         self.ws = None
         self.trace = None          # optional dict: per-layer intermediates for the parity tests
         self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
         self._graphs = {}
         self._graph_pool = None
         self.restart_engine()
+
+    _family_deaot = True
+
+    def _new_workspace(self, h, w, n_slots):
+        return _Workspace(self.prep, h, w, n_slots, self.device)
+
+    @staticmethod
+    def _tpe_rows(T):
+        return tpe_row_indices(T)
+
+    def _decoder_inputs(self, embs, lstt_out):
+        n, c, h, w = embs[-1].shape
+        return [embs[-1], lstt_out.view(1, h, w, -1).permute(0, 3, 1, 2)]   # channels-last view, no copy
 
     # ------------------------------------------------------------------ bookkeeping
     def restart_engine(self, batch_size=1, enable_id_shuffle=False):
@@ -344,7 +372,7 @@ class DeAOTEngine:
         h, w = self.enc_size_2d
         n_slots = self.capacity + 1
         if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
-            self.ws = _Workspace(self.prep, h, w, n_slots, self.device)
+            self.ws = self._new_workspace(h, w, n_slots)
             self._graphs, self._graph_pool = {}, None             # graphs bake the workspace pointers
 
     @property
@@ -498,9 +526,7 @@ class DeAOTEngine:
 
     def _decode(self, embs, lstt_out, output_size):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
-        n, c, h, w = embs[-1].shape
-        lstt_nchw = lstt_out.view(1, h, w, -1).permute(0, 3, 1, 2)        # channels-last view, no copy
-        logits = self.prep.decoder([embs[-1], lstt_nchw], embs)
+        logits = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs)
         for b, on in enumerate(self.obj_nums):
             if on + 1 < logits.shape[1]:
                 logits[b, on + 1:] = -1e10
@@ -632,7 +658,17 @@ class DeAOTEngine:
         return self
 
 
-AOTEngine = DeAOTEngine  # the AOT (multi-head) kernels are not built yet; DeAOT is the evaluated path
+from .engine_aot import AOTBodies, WorkspaceAOT, mha_chunks_per_frame  # noqa: E402
+
+
+class AOTEngine(AOTBodies, DeAOTEngine):
+    """AOTEngine (aot_engine.py:18-568) on the multi-head kernels: the state machine of DeAOTEngine with the
+    AOT block (engine_aot.AOTBodies).  Eviction statistics only run once the bank is full (transformer.py:332-334)."""
+
+    _family_deaot = False
+
+    def _new_workspace(self, h, w, n_slots):
+        return WorkspaceAOT(self.prep, h, w, n_slots, self.device, mha_chunks_per_frame)
 
 
 class DeAOTInferEngine:
@@ -651,6 +687,7 @@ class DeAOTInferEngine:
         self.long_term_mem_gap = long_term_mem_gap
         self.short_term_mem_skip = short_term_mem_skip
         self.aot_engines = []
+        self._engine_cls = DeAOTEngine if is_deaot_model(aot_model) else AOTEngine
         self.restart_engine()
 
     def eval(self):
@@ -704,8 +741,8 @@ class DeAOTInferEngine:
         self.obj_nums = obj_nums
         aot_num = max(-(-int(obj_nums) // self.max_aot_obj_num), 1)
         while aot_num > len(self.aot_engines):
-            self.aot_engines.append(DeAOTEngine(self.AOT, self.gpu_id, self.long_term_mem_gap,
-                                                self.short_term_mem_skip))
+            self.aot_engines.append(self._engine_cls(self.AOT, self.gpu_id, self.long_term_mem_gap,
+                                                     self.short_term_mem_skip))
         separated = self.separate_mask(mask)
         img_embs = None
         for engine, m in zip(self.aot_engines, separated):
@@ -751,7 +788,8 @@ def build_engine(name, phase="train", **kwargs):
     """networks/engines/__init__.py:5-21."""
     if name in ("aotengine", "deaotengine"):
         if phase == "train":
-            return DeAOTEngine(**kwargs)
+            cls = DeAOTEngine if is_deaot_model(kwargs["aot_model"]) else AOTEngine
+            return cls(**kwargs)
         if phase == "eval":
             return DeAOTInferEngine(**kwargs)
     raise NotImplementedError(name)

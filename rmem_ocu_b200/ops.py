@@ -13,7 +13,7 @@ from ._lib import (ACT_NONE, ACT_SILU, OUT_BF16, OUT_F32, OUT_F32_ACCUM, GemmSeg
 
 # number of librmem_b200 kernels launched through this module (bench.py reports it as gpu_launches)
 LAUNCHES = 0
-_KERNELS_PER_CALL = {"rmem_groupnorm_tokens": 2, "rmem_groupnorm_nhwc": 2}
+_KERNELS_PER_CALL = {"rmem_groupnorm_tokens": 2, "rmem_groupnorm_nhwc": 2, "rmem_groupnorm_gelu_tokens": 2}
 
 
 def _count(name):
@@ -180,3 +180,52 @@ def foreground_prob(logits, fg, h, w):
     _lib.check(_lib.lib().rmem_foreground_prob(_p(logits), C, Hs, Ws, _p(fg), h, w, _stream()),
                "rmem_foreground_prob")
     _count("rmem_foreground_prob")
+
+
+# --------------------------------------------------------------------------------------------- AOT (8 heads x 32)
+def mha_partial(q, k, v, order, T, cpf, part_o, part_m, part_l):
+    """q bf16 [L, >=256] (row stride = q.stride(0)); k, v bf16 [n_slots, L, >=256] or [L, >=256] (one slot)."""
+    L = q.shape[0]
+    if k.dim() == 2:
+        n_slots, ldk, ks, ldv, vs = 1, k.stride(0), 0, v.stride(0), 0
+    else:
+        n_slots, ldk, ks, ldv, vs = k.shape[0], k.stride(1), k.stride(0), v.stride(1), v.stride(0)
+    _lib.check(_lib.lib().rmem_mha_partial(_p(q), q.stride(0), _p(k), ldk, ks, _p(v), ldv, vs, _p(order), T, L,
+                                           n_slots, cpf, _p(part_o), _p(part_m), _p(part_l), _stream()),
+               "rmem_mha_partial")
+    _count("rmem_mha_partial")
+
+
+def mha_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, out, out_col0, attn_mass):
+    rows = (ctypes.c_int32 * max(T, 1))(*(tpe_rows if tpe_rows is not None else [0] * T))
+    _lib.check(_lib.lib().rmem_mha_combine(_p(part_o), _p(part_m), _p(part_l), _p(tpe_bias),
+                                           ctypes.cast(rows, ctypes.c_void_p), T, L, cpf, _p(out), out.stride(0),
+                                           out_col0, _p(attn_mass), _stream()), "rmem_mha_combine")
+    _count("rmem_mha_combine")
+
+
+def tpe_prepare_mha(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias):
+    _lib.check(_lib.lib().rmem_tpe_prepare_mha(_p(q), q.stride(0), _p(cur_pos_emb), _p(mem_pos_emb), _p(q_time),
+                                               _p(tpe_bias), q.shape[0], _stream()), "rmem_tpe_prepare_mha")
+    _count("rmem_tpe_prepare_mha")
+
+
+def layernorm_ex(xa, gamma, beta, xb=None, out=None, col_out=0, post_add=None, out_plus=None, col_plus=0,
+                 out_f32=None, col_f32=0):
+    """LN(xa [+ xb]) -> out (bf16) / out_plus = LN + post_add (bf16) / out_f32; all [L, 256] column windows."""
+    _chk_cuda(xa)
+    L = xa.shape[0]
+    in_bf16 = 1 if xa.dtype == torch.bfloat16 else 0
+    st = lambda t: t.stride(0) if t is not None else 0
+    _lib.check(_lib.lib().rmem_layernorm_ex(_p(xa), xa.stride(0), _p(xb), st(xb), in_bf16, _p(gamma), _p(beta),
+                                            _p(out), st(out), col_out, _p(post_add), st(post_add),
+                                            _p(out_plus), st(out_plus), col_plus, _p(out_f32), st(out_f32),
+                                            col_f32, L, 256, _stream()), "rmem_layernorm_ex")
+    _count("rmem_layernorm_ex")
+
+
+def groupnorm_gelu_tokens(x, gamma, beta, out, groups, workspace):
+    L, C = x.shape
+    _lib.check(_lib.lib().rmem_groupnorm_gelu_tokens(_p(x), _p(gamma), _p(beta), _p(out), L, C, groups,
+                                                     _p(workspace), _stream()), "rmem_groupnorm_gelu_tokens")
+    _count("rmem_groupnorm_gelu_tokens")

@@ -131,3 +131,67 @@ def test_bank_score_evict_bit_exact_vs_oracle(lib_built):
             order = st[:T].tolist()
             frame_ids = [int(st[_lib.MAX_BANK + s]) for s in order]
             assert frame_ids == idx, (variant, step)
+
+
+def _mha_run(q, k, v, order, T, cpf, bias=None, rows=None):
+    from rmem_ocu_b200 import ops
+    L = q.shape[0]
+    nch = T * cpf
+    po = torch.empty(nch, L, 256, device="cuda")
+    pm = torch.empty(nch, 8, L, device="cuda")
+    pl = torch.empty(nch, 8, L, device="cuda")
+    out = torch.zeros(L, 512, device="cuda", dtype=torch.bfloat16)
+    mass = torch.empty(L, T, device="cuda")
+    ops.mha_partial(q, k, v, order, T, cpf, po, pm, pl)
+    ops.mha_combine(po, pm, pl, bias, rows, T, L, cpf, out, 256, mass)
+    torch.cuda.synchronize()
+    return out, mass
+
+
+@pytest.mark.parametrize("L,T,cpf,qscale", [(1705, 5, 1, 1.0), (1620, 3, 2, 3.0), (333, 9, 1, 6.0),
+                                            (1620, 1, 3, 1.0), (64, 2, 1, 1.0), (3600, 2, 1, 2.0)])
+def test_multihead_attention_vs_oracle(lib_built, L, T, cpf, qscale):
+    """MultiheadAttention explicit path (8 heads x 32, attention.py:45-64) + per-head TPE bias + head-averaged
+    record_attn_weight, evaluated in fp32 on the bf16-rounded inputs.  Tolerance: relative Frobenius error
+    <= 2e-2 on the output, <= 5e-3 absolute on the per-frame masses."""
+    torch.manual_seed(L + T + 7)
+    n_slots = T + 1
+    qbuf = _bf(torch.randn(L, 512, device="cuda") * qscale)         # queries live in columns 256.. (ld 512)
+    q = qbuf[:, 256:]
+    kb = _bf(torch.randn(n_slots, L, 256, device="cuda"))
+    vb = _bf(torch.randn(n_slots, L, 256, device="cuda"))
+    perm = torch.randperm(n_slots)[:T]
+    order = perm.to(device="cuda", dtype=torch.int32)
+    rows = [min(t, 3) for t in range(T)]
+    bias_nat = torch.randn(L, 8, 4, device="cuda") * 0.5
+    out, mass = _mha_run(q, kb, vb, order, T, cpf, (bias_nat * math.log2(math.e)).contiguous(), rows)
+    qh = q.float().view(L, 8, 32).permute(1, 0, 2)                                  # [8, L, 32]
+    s = torch.cat([qh @ kb[perm[t]].float().view(L, 8, 32).permute(1, 2, 0) / math.sqrt(32.0)
+                   + bias_nat[:, :, rows[t]].t()[:, :, None] for t in range(T)], 2)  # [8, L, T*L]
+    a = torch.softmax(s, -1)
+    vcat = torch.cat([vb[perm[t]].float() for t in range(T)], 0).view(T * L, 8, 32).permute(1, 0, 2)
+    o_ref = (a @ vcat).permute(1, 0, 2).reshape(L, 256)
+    m_ref = a.mean(0).view(L, T, L).sum(-1)
+    assert torch.isfinite(out.float()).all()
+    assert (out[:, :256] == 0).all()                                # column window respected
+    assert _rel(out[:, 256:], o_ref) < 2e-2
+    assert (mass - m_ref).abs().max().item() < 5e-3
+    assert (mass.sum(1) - 1).abs().max().item() < 1e-4
+
+
+def test_multihead_attention_single_slot_strided(lib_built):
+    """Self / short-term attention form: K and V are column windows of wider [L, ld] buffers, T = 1, no TPE."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(5)
+    L = 1620
+    buf = _bf(torch.randn(L, 768, device="cuda"))
+    q, k, v = buf[:, :256], buf[:, 256:512], buf[:, 512:]
+    order = torch.zeros(1, device="cuda", dtype=torch.int32)
+    po = torch.empty(3, L, 256, device="cuda"); pm = torch.empty(3, 8, L, device="cuda"); pl = torch.empty(3, 8, L, device="cuda")
+    out = torch.empty(L, 256, device="cuda", dtype=torch.bfloat16)
+    ops.mha_partial(q, k, v, order, 1, 3, po, pm, pl)
+    ops.mha_combine(po, pm, pl, None, None, 1, L, 3, out, 0, None)
+    torch.cuda.synchronize()
+    h = lambda t: t.float().view(L, 8, 32).permute(1, 0, 2)
+    ref = (torch.softmax(h(q) @ h(k).transpose(1, 2) / math.sqrt(32.0), -1) @ h(v)).permute(1, 0, 2).reshape(L, 256)
+    assert _rel(out, ref) < 2e-2

@@ -139,6 +139,18 @@ def _run_product(g, monkeypatch, encoder_dtype):
     return masks, idx_log, logits, n
 
 
+MIN_MARGIN = 1e-3
+
+
+def _well_conditioned(g, name):
+    """Every eviction of the fixture is decided by more than MIN_MARGIN (score units; the recorded attention
+    masses of the bf16 kernels are within 5e-3 absolute per query and far closer after the sum over queries).
+    A reference decision inside that band is a numerical tie no reduced-precision kernel can be held to --
+    oracle/make_golden.py picks clip seeds without one."""
+    m = np.asarray(g["margins"])
+    assert np.all(m > MIN_MARGIN), (name, float(m.min()))
+
+
 DEAOT_CLIPS = ["clip_deaot_small", "clip_deaot_repeat", "clip_deaot_gap", "clip_deaot_mid", "clip_deaot_480p"]
 
 
@@ -149,6 +161,7 @@ def test_deaot_engine_clip_vs_reference(lib_built, monkeypatch, name):
     hot-path kernels: bank indexes bit-exact after every frame, >= 99.9 % argmax mask agreement per
     frame, stride-4 logits within 5e-2 relative Frobenius error (bf16 kernels vs fp32 reference)."""
     g = _load(name)
+    _well_conditioned(g, name)
     masks, idx_log, logits, n = _run_product(g, monkeypatch, "fp32")
     for f, idx in enumerate(idx_log):
         want = [int(v) for v in g["indexes"][f] if v >= 0]
@@ -171,3 +184,110 @@ def test_deaot_engine_clip_bf16_backbone(lib_built, monkeypatch):
     agree = [float((m == gm).mean()) for m, gm in zip(masks, g["masks"])]
     print("bf16-backbone mask agreement", [round(a, 5) for a in agree])
     assert min(agree) >= 0.97, agree
+
+
+# ------------------------------------------------------------------------------------------------ AOT
+def test_aot_attention_operators_vs_reference(lib_built):
+    """MultiheadAttention as long_term_attn (explicit path + recorded masses) and as self_attn (linear_Q/K/V +
+    SDPA) against the reference module outputs.  Tolerance: relative Frobenius error <= 2e-2 on outputs,
+    <= 5e-3 absolute on the head-averaged per-frame attention masses."""
+    from rmem_ocu_b200 import ops
+    g = _load("ops_aot")
+    _, sd = _synth.models(3, vos="aot")
+    p = "LSTT.layers.0."
+    dev = "cuda"
+    W = lambda n: _bf(sd[p + n + ".weight"]).to(dev)
+    B = lambda n: sd[p + n + ".bias"].to(dev)
+    for tag in _synth.OPS_AOT_CASES:
+        i = _synth.ops_aot_inputs(tag)
+        L, T = i["L"], i["T"]
+        q = _bf(i["Q"][:, 0]).to(dev)
+        perm = torch.randperm(T + 1)[:T]
+        kb = torch.zeros(T + 1, L, 256, device=dev, dtype=torch.bfloat16)
+        vb = torch.zeros(T + 1, L, 256, device=dev, dtype=torch.bfloat16)
+        for t in range(T):
+            kb[perm[t]] = _bf(i["K"][t * L:(t + 1) * L, 0]).to(dev)
+            vb[perm[t]] = _bf(i["V"][t * L:(t + 1) * L, 0]).to(dev)
+        cpf = 2 if T == 1 else 1
+        po = torch.empty(T * cpf, L, 256, device=dev)
+        pm, pl = torch.empty(T * cpf, 8, L, device=dev), torch.empty(T * cpf, 8, L, device=dev)
+        att = torch.empty(L, 256, device=dev, dtype=torch.bfloat16)
+        mass = torch.empty(L, T, device=dev)
+        ops.mha_partial(q, kb, vb, perm.to(device=dev, dtype=torch.int32), T, cpf, po, pm, pl)
+        ops.mha_combine(po, pm, pl, None, None, T, L, cpf, att, 0, mass)
+        out = torch.empty(L, 256, device=dev)
+        ops.linear(att, W("long_term_attn.projection"), B("long_term_attn.projection"),
+                   [(0, 256, ops.ACT_NONE, ops.OUT_F32, out, 0)])
+        torch.cuda.synchronize()
+        assert _rel(out[::RS], g["lt_%s_out" % tag][:, 0]) < 2e-2, tag
+        assert (mass.cpu() - torch.from_numpy(g["lt_%s_mass" % tag])).abs().max().item() < 5e-3, tag
+
+        # self-attention form: q = k = linear_Q/K(Q), v = linear_V(K[:L]); one slot, strided operands
+        qkv = torch.empty(L, 768, device=dev, dtype=torch.bfloat16)
+        k1 = _bf(i["K"][:L, 0]).to(dev)
+        ops.linear(q, W("self_attn.linear_Q"), B("self_attn.linear_Q"), [(0, 256, 0, ops.OUT_BF16, qkv, 0)])
+        ops.linear(q, W("self_attn.linear_K"), B("self_attn.linear_K"), [(0, 256, 0, ops.OUT_BF16, qkv, 256)])
+        ops.linear(k1, W("self_attn.linear_V"), B("self_attn.linear_V"), [(0, 256, 0, ops.OUT_BF16, qkv, 512)])
+        zero = torch.zeros(1, device=dev, dtype=torch.int32)
+        ops.mha_partial(qkv[:, :256], qkv[:, 256:512], qkv[:, 512:], zero, 1, 1, po, pm, pl)
+        ops.mha_combine(po, pm, pl, None, None, 1, L, 1, att, 0, None)
+        ops.linear(att, W("self_attn.projection"), B("self_attn.projection"),
+                   [(0, 256, ops.ACT_NONE, ops.OUT_F32, out, 0)])
+        torch.cuda.synchronize()
+        assert _rel(out[::RS], g["sa_%s_out" % tag][:, 0]) < 2e-2, tag
+
+
+AOT_CLIPS = ["clip_aot_small", "clip_aot_repeat", "clip_aot_480p"]
+
+
+@pytest.mark.parametrize("name", AOT_CLIPS)
+def test_aot_engine_clip_vs_reference(lib_built, monkeypatch, name):
+    """AOT drop-in engine (multi-head kernels) against the reference's own run of the same clip, fp32 cuDNN
+    backbone: bank indexes bit-exact after every frame, >= 99.9 % argmax mask agreement per frame, stride-4
+    logits within 5e-2 relative Frobenius error."""
+    g = _load(name)
+    _well_conditioned(g, name)
+    masks, idx_log, logits, n = _run_product(g, monkeypatch, "fp32")
+    for f, idx in enumerate(idx_log):
+        want = [int(v) for v in g["indexes"][f] if v >= 0]
+        assert idx == want, (name, f + 1, idx, want)
+    agree = [float((m == gm).mean()) for m, gm in zip(masks, g["masks"])]
+    rel = [_rel(logits[0], g["logits_ref_frame"]), _rel(logits[1], g["logits_first"]),
+           _rel(logits[n - 1], g["logits_last"])]
+    print(name, "mask agreement", [round(a, 5) for a in agree], "rel logit err", [round(r, 4) for r in rel])
+    assert min(agree) >= 0.999, (name, agree)
+    assert max(rel) < 5e-2, (name, rel)
+
+
+def test_aot_block_vs_reference_all_bank_lengths(lib_built):
+    """One SimplifiedTransformerBlock forward per bank length T = 1..12 against the reference block's outputs
+    (pins the temporal-PE row selection incl. the T > 4 nearest resample, the head-averaged recorded masses,
+    the short-term K / V candidates).  Tolerance: 2e-2 relative Frobenius on features, 5e-3 absolute on W."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import AOTEngine
+    g = _load("layer_aot")
+    m, _ = _synth.models(11, vos="aot")
+    eng = AOTEngine(m, 0)
+    h, w = _synth.LAYER_HW
+    L = h * w
+    eng.update_size((h * 16, w * 16), (h, w))
+    eng.prep.cur_pos_emb.mul_(20.0)
+    eng.prep.mem_pos_emb.mul_(20.0)
+    ws = eng.ws
+    bf = lambda t: t.to(device="cuda", dtype=torch.bfloat16)
+    for T in range(1, 13):
+        i = _synth.layer_inputs("aot", T)
+        ops.bank_init(ws.bank_state, 0)
+        ws.tgt.copy_(i["tgt"][:, 0].cuda())
+        ws.pos.copy_(i["pos"][:, 0].cuda())
+        ws.kbank[1][:T].copy_(bf(i["gK"][:, :, 0]))
+        ws.vbank[1][:T].copy_(bf(i["gV"][:, :, 0]))
+        ws.kprev[1].copy_(bf(i["lK"][:, 0]))
+        ws.vprev[1].copy_(bf(i["lV"][:, 0]))
+        eng._block_forward(1, False, True, T)
+        torch.cuda.synchronize()
+        W = ws.mass[:L * T].view(L, T).cpu()
+        assert _rel(ws.tgt, g["T%d_out" % T][:, 0]) < 2e-2, T
+        assert (W - torch.from_numpy(g["T%d_W" % T])).abs().max().item() < 5e-3, T
+        assert _rel(ws.knew[1], g["T%d_new_local_K" % T][:, 0]) < 2e-2, T
+        assert _rel(ws.mem[1][:, 512:], g["T%d_new_local_V" % T][:, 0]) < 2e-2, T
