@@ -38,6 +38,8 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="only the isolated kernel rooflines")
+    ap.add_argument("--profile-steps", type=int, default=0,
+                    help="bracket the first N timed steps with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     return ap.parse_args()
 
 
@@ -152,6 +154,12 @@ def run_b200(args, rank, world):
             with ClockSampler(local_rank) as clk:
                 e0.record()
                 for f in range(1 + args.warmup, n_frames):
+                    if mode == "device" and args.profile_steps:
+                        if f == 1 + args.warmup:
+                            torch.cuda.profiler.start()
+                        elif f == 1 + args.warmup + args.profile_steps:
+                            torch.cuda.synchronize()
+                            torch.cuda.profiler.stop()
                     if mode == "device":
                         label = frame_step(eng, dev_imgs[f], (H, W))
                     else:

@@ -11,33 +11,32 @@
 namespace rmem {
 
 // ------------------------------------------------------------------------------------------------
-// stats: thread t of a 256-thread CTA owns channel (t % C) [+ pixel phase t / C when C < 256]; a CTA
-// covers kGnRows pixel rows; partial sums are reduced over the channels of a group with shuffles and
-// added to the fp64 workspace with one atomic per (warp, group).
-constexpr int kGnRows = 64;
-
+// stats: a thread owns four consecutive channels (one float4, always inside one group since cpg % 4 == 0) of
+// every (1024 / C)-th pixel of the CTA's pixel range; partial sums are reduced over the lanes of a group with
+// shuffles, over the CTA in shared memory, and added to the fp64 workspace with one atomic pair per
+// (CTA, group).  The range per CTA is sized so the grid is ~4 CTAs per SM whatever the resolution.
 __global__ void __launch_bounds__(256)
-gn_nhwc_stats_kernel(const float* __restrict__ x, int P, int C, int cpg, double* __restrict__ ws) {
-  const int ppb = 256 / C;                       // pixels processed per step by this CTA (C = 64, 128, 256)
-  const int c = threadIdx.x % C;
-  const int ph = threadIdx.x / C;
-  const int p0 = blockIdx.x * kGnRows;
+gn_nhwc_stats_kernel(const float* __restrict__ x, int P, int C, int cpg, int rows_per_cta,
+                     double* __restrict__ ws) {
+  const int tpp = C >> 2;                        // threads per pixel (C = 64, 128, 256 -> 16, 32, 64)
+  const int ppb = 256 / tpp;                     // pixels per step
+  const int c = (threadIdx.x % tpp) * 4;
+  const int ph = threadIdx.x / tpp;
+  const int p0 = blockIdx.x * rows_per_cta;
+  const int p1 = min(p0 + rows_per_cta, P);
   float s = 0.f, q = 0.f;
-  for (int i = ph; i < kGnRows; i += ppb) {
-    const int pix = p0 + i;
-    if (pix < P) {
-      const float v = x[static_cast<size_t>(pix) * C + c];
-      s += v;
-      q += v * v;
-    }
+#pragma unroll 4
+  for (int pix = p0 + ph; pix < p1; pix += ppb) {
+    const float4 v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    s += (v.x + v.y) + (v.z + v.w);
+    q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
   }
-  // reduce over the lanes that share a group (cpg is a power of two <= 32, or a multiple of 32)
-  const int span = cpg < 32 ? cpg : 32;
+  // lanes sharing a group: cpg / 4 consecutive lanes (cpg is a power of two in [4, 32])
+  const int span = cpg >> 2;
   for (int o = span >> 1; o > 0; o >>= 1) {
     s += __shfl_xor_sync(0xffffffffu, s, o);
     q += __shfl_xor_sync(0xffffffffu, q, o);
   }
-  // CTA-level reduction in shared memory, then one fp64 atomic pair per group per CTA
   __shared__ float sh[64];
   if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
   __syncthreads();
@@ -87,8 +86,10 @@ int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta,
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: channels per group must be a power of two in [4, 32]");
   cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 2 * groups, stream);
   if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_nhwc: memset");
-  gn_nhwc_stats_kernel<<<(P + kGnRows - 1) / kGnRows, 256, 0, stream>>>(x, P, C, cpg,
-                                                                       static_cast<double*>(workspace));
+  int rows = (P + 591) / 592;                    // ~4 CTAs per SM at large P ...
+  if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
+  gn_nhwc_stats_kernel<<<(P + rows - 1) / rows, 256, 0, stream>>>(x, P, C, cpg, rows,
+                                                                 static_cast<double*>(workspace));
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   int blocks = static_cast<int>((total4 + 255) / 256);

@@ -85,11 +85,11 @@ int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0,
 }
 
 // ------------------------------------------------------------------------------------------------
-// 5x5 depth-wise conv, channels-last.  Thread = (channel pair, pixel row, strip of 16 pixels): the 25
+// 5x5 depth-wise conv, channels-last.  Thread = (channel pair, pixel row, strip of kDwStrip pixels): the 25
 // weights of its two channels and a sliding 5x5 window live in registers, so every output costs five
 // new 4-byte loads (coalesced: consecutive lanes = consecutive channel pairs) and 25 packed f32x2 FMAs.
 // Weights tap-major [25][C].
-constexpr int kDwStrip = 16;
+constexpr int kDwStrip = 6;
 
 __device__ __forceinline__ void fma2(float2& d, const float2 a, const float2 b) {
   asm("{\n\t.reg .b64 ra, rb, rc;\n\t"

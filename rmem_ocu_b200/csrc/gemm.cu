@@ -4,21 +4,30 @@
 // 209; fuse_key_value_id, transformer.py:1238-1244) with their surrounding element-wise ops
 // (SiLU, residual add, output split / concat) folded into the epilogue.
 //
-// bf16 operands (both K-major), fp32 accumulation in TMEM.  128x128 output tile per CTA,
-// 64-wide K blocks through a 4-stage TMA ring, tcgen05.mma issued by one thread, four epilogue
-// warps read the accumulator with tcgen05.ld (one row per thread).
+// bf16 operands (both K-major), fp32 accumulation in TMEM.  128 x {128, 64} output tile per CTA,
+// 64-wide K blocks through a 4-stage TMA ring, tcgen05.mma issued by one thread, eight epilogue
+// warps read the accumulator with tcgen05.ld (one row per thread) and store through a transposing
+// shared-memory tile so global accesses are contiguous per row.
 #include "sm100_ptx.cuh"
 #include "rmem_internal.h"
 
 namespace rmem {
 using namespace sm100;
 
-constexpr int kGM = 128, kGN = 128, kGK = 64, kGStages = 4;
+constexpr int kGM = 128, kGK = 64;
 constexpr uint32_t kGABytes = kGM * kGK * 2;   // 16 KB
-constexpr uint32_t kGBBytes = kGN * kGK * 2;   // 16 KB
-constexpr uint32_t kGStageBytes = kGABytes + kGBBytes;
-constexpr uint32_t kGSmem = kGStages * kGStageBytes + 1024 + 128;
-constexpr int kGThreads = 192;
+constexpr int kGEpiWarps = 8;                  // two per TMEM lane quarter, each owning half of the tile's columns
+constexpr int kGThreads = 64 + 32 * kGEpiWarps;
+constexpr int kGTileLd = 36;                   // floats per staged row: 16-byte aligned, conflict-free for 128-bit accesses
+
+template <int BN, int kGStages>
+struct GemmCfg {
+  static constexpr uint32_t kBBytes = BN * kGK * 2;
+  static constexpr uint32_t kStageBytes = kGABytes + kBBytes;
+  static constexpr uint32_t kEpiBytes = kGEpiWarps * 32 * kGTileLd * 4;   // staging tiles: reuse the (idle) ring
+  static_assert(kEpiBytes <= kGStages * kStageBytes, "epilogue staging must fit in the pipeline ring");
+  static constexpr uint32_t kSmem = kGStages * kStageBytes + BN * 4 + 1024 + 128;
+};
 
 struct GemmParams {
   int M, N, K;
@@ -27,22 +36,27 @@ struct GemmParams {
   rmem_gemm_segment seg[RMEM_GEMM_MAX_SEGMENTS];
 };
 
-__device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
-
+// BN = 128 for wide outputs, 64 when that would leave most SMs idle (M is only ~13 row tiles on this path).
+// Three stages keep two (BN 128) or three (BN 64) CTAs on an SM so main loops and epilogues overlap; the
+// long-K narrow GEMMs (fewer CTAs than SMs, 16-32 K blocks each) instead get a six-deep ring to cover TMA latency.
+template <int BN, int kGStages>
 __global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
                     const GemmParams p) {
+  using Cfg = GemmCfg<BN, kGStages>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGStages * kGStageBytes);
-  uint64_t* full = bars;                  // [4]
-  uint64_t* empty = bars + kGStages;      // [4]
+  float* epi = reinterpret_cast<float*>(smem);          // valid once acc_full fired: every stage is idle then
+  float* bias_s = reinterpret_cast<float*>(smem + kGStages * Cfg::kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + BN);
+  uint64_t* full = bars;                  // [kGStages]
+  uint64_t* empty = bars + kGStages;      // [kGStages]
   uint64_t* acc_full = bars + 2 * kGStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kGStages + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * kGM, n0 = blockIdx.x * kGN;
+  const int m0 = blockIdx.y * kGM, n0 = blockIdx.x * BN;
   const int kb = (p.K + kGK - 1) / kGK;
 
   if (warp == 0 && lane == 0) {
@@ -52,7 +66,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     mbar_init(acc_full, 1);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  if (warp == 1) tmem_alloc<BN>(tmem_slot);
+  if (warp >= 2) {
+    // bias of this column tile, staged once (the main loop is running meanwhile)
+    const int t = threadIdx.x - 64;
+    if (t < BN) {
+      const int cg = n0 + t;
+      bias_s[t] = (p.bias && cg < p.N) ? __ldg(p.bias + cg) : 0.f;
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -63,20 +85,20 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       for (int k = 0; k < kb; ++k) {
         const int st = k % kGStages;
         if (k >= kGStages) mbar_wait(empty + st, ((k / kGStages) - 1) & 1);
-        uint8_t* a = smem + st * kGStageBytes;
-        mbar_expect_tx(full + st, kGStageBytes);
+        uint8_t* a = smem + st * Cfg::kStageBytes;
+        mbar_expect_tx(full + st, Cfg::kStageBytes);
         tma_load_2d(a, &tm_a, full + st, k * kGK, m0);
         tma_load_2d(a + kGABytes, &tm_w, full + st, k * kGK, n0);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kGM, kGN, 0, 0);
+      constexpr uint32_t idesc = make_idesc_bf16(kGM, BN, 0, 0);
       for (int k = 0; k < kb; ++k) {
         const int st = k % kGStages;
         mbar_wait(full + st, (k / kGStages) & 1);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + st * kGStageBytes);
+        const uint32_t a_addr = smem_u32(smem + st * Cfg::kStageBytes);
         const uint32_t b_addr = a_addr + kGABytes;
 #pragma unroll
         for (int ks = 0; ks < kGK / 16; ++ks) {
@@ -88,34 +110,27 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       tc_commit(acc_full);
     }
   } else {
-    // ---------------------------------------------------------------- epilogue (4 warps, 32 rows each)
-    // Phase 1: the thread that owns TMEM lane r (= output row) reads 32 accumulator columns, adds the
-    // bias and applies the activation in registers, and parks them in a per-warp shared-memory tile.
-    // Phase 2: the warp re-reads the tile transposed -- half a warp per row, two adjacent columns per
-    // lane -- so every global access (store, or load + add + store for the accumulate mode) is a
-    // contiguous 64 B / 128 B run instead of 32 scattered rows.
+    // ---------------------------------------------------------------- epilogue (8 warps)
+    // Warp (quarter, half) owns TMEM lanes [32 quarter, +32) = 32 output rows and half of the tile's columns.
+    // Per 32-column block: phase 1, the thread that owns row r reads its accumulator columns, adds the bias,
+    // applies the activation and parks them in the warp's staging tile with 128-bit stores; phase 2, the warp
+    // re-reads the tile with eight lanes per row (four columns each), so every global access is a contiguous
+    // 64 B / 128 B run per row; the accumulate mode issues all its loads before the first add.
+    const int ew = warp - 2;
     const int quarter = warp & 3;
-    const int row_l = quarter * 32 + lane;
+    const int half = ew >> 2;
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-    float* tile = reinterpret_cast<float*>(smem) + quarter * (32 * 33);      // [32 rows][33] (stage 0 is idle)
-    float* bias_s = reinterpret_cast<float*>(smem + kGStageBytes);           // [128]        (stage 1 is idle)
+    float* tile = epi + ew * (32 * kGTileLd);
+    constexpr int kCbPerWarp = BN / 64;            // 32-column blocks per warp
+    const int r_sub = lane >> 3;                   // phase 2: row within a group of four
+    const int c4 = (lane & 7) * 4;                 // phase 2: first of this lane's four columns
     mbar_wait(acc_full, 0);
     tc_fence_after();
-    // every MMA has completed, so every TMA load has landed and the stage buffers are free
-    if (p.bias) {
-      const int cg = n0 + row_l;
-      bias_s[row_l] = cg < p.N ? __ldg(p.bias + cg) : 0.f;
-    } else {
-      bias_s[row_l] = 0.f;
-    }
-    named_bar_sync(1, 128);
-    const int c2 = 2 * (lane & 15);        // column pair of this lane in phase 2
-    const int rpar = lane >> 4;            // row parity of this half-warp
 #pragma unroll 1
-    for (int cb = 0; cb < kGN / 32; ++cb) {
+    for (int cbi = 0; cbi < kCbPerWarp; ++cbi) {
+      const int cb = half * kCbPerWarp + cbi;
       const int c0 = n0 + cb * 32;
       if (c0 >= p.N) break;                       // warp-uniform
-      // segment lookup (warp-uniform: segments start on multiples of 32 columns)
       int si = -1;
       for (int sgi = 0; sgi < p.n_seg; ++sgi)
         if (c0 >= p.seg[sgi].col_begin && c0 < p.seg[sgi].col_end) si = sgi;
@@ -128,36 +143,65 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       tmem_ld_wait();
       __syncwarp();                               // phase 2 of the previous block has finished with `tile`
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        float x = __uint_as_float(r[i]) + bias_s[cb * 32 + i];
-        if (sg.act == RMEM_ACT_SILU) x = __fdividef(x, 1.f + __expf(-x));
-        tile[lane * 33 + i] = x;
+      for (int i = 0; i < 32; i += 4) {
+        float4 x;
+        x.x = __uint_as_float(r[i]) + bias_s[cb * 32 + i];
+        x.y = __uint_as_float(r[i + 1]) + bias_s[cb * 32 + i + 1];
+        x.z = __uint_as_float(r[i + 2]) + bias_s[cb * 32 + i + 2];
+        x.w = __uint_as_float(r[i + 3]) + bias_s[cb * 32 + i + 3];
+        if (sg.act == RMEM_ACT_SILU) {
+          x.x = __fdividef(x.x, 1.f + __expf(-x.x));
+          x.y = __fdividef(x.y, 1.f + __expf(-x.y));
+          x.z = __fdividef(x.z, 1.f + __expf(-x.z));
+          x.w = __fdividef(x.w, 1.f + __expf(-x.w));
+        }
+        *reinterpret_cast<float4*>(tile + lane * kGTileLd + i) = x;
       }
       __syncwarp();
-      const bool ok0 = c2 < ncol, ok1 = c2 + 1 < ncol;
-      const size_t col_off = static_cast<size_t>(sg.dst_col0 + (c0 - sg.col_begin) + c2);
+      const size_t col_off = static_cast<size_t>(sg.dst_col0 + (c0 - sg.col_begin) + c4);
+      const int nc = ncol - c4;                    // valid columns of this lane's four (<= 0: none)
+      const int row_base = m0 + quarter * 32 + r_sub;
+      const bool vec_ok = nc >= 4 && ((sg.ld | sg.dst_col0) & 3) == 0 &&
+                          (reinterpret_cast<uintptr_t>(sg.dst) & 15) == 0;     // 16 B (f32) / 8 B (bf16) accesses
+      if (sg.mode == RMEM_OUT_BF16) {
+        __nv_bfloat16* base = static_cast<__nv_bfloat16*>(sg.dst) + col_off;
 #pragma unroll
-      for (int it = 0; it < 16; ++it) {
-        const int rl = 2 * it + rpar;
-        const int row = m0 + quarter * 32 + rl;
-        const float v0 = tile[rl * 33 + c2], v1 = tile[rl * 33 + c2 + 1];
-        if (row >= p.M || !ok0) continue;
-        const size_t off = static_cast<size_t>(row) * sg.ld + col_off;
-        if (sg.mode == RMEM_OUT_BF16) {
-          __nv_bfloat16* d = static_cast<__nv_bfloat16*>(sg.dst) + off;
-          if (ok1) *reinterpret_cast<uint32_t*>(d) = pack_bf16x2(v0, v1);
-          else d[0] = __float2bfloat16(v0);
-        } else {
-          float* d = static_cast<float*>(sg.dst) + off;
-          if (ok1) {
-            float2 o = make_float2(v0, v1);
-            if (sg.mode == RMEM_OUT_F32_ACCUM) {
-              const float2 old = *reinterpret_cast<const float2*>(d);
-              o.x += old.x; o.y += old.y;
-            }
-            *reinterpret_cast<float2*>(d) = o;
+        for (int it = 0; it < 8; ++it) {
+          const int row = row_base + it * 4;
+          const float4 v = *reinterpret_cast<const float4*>(tile + (it * 4 + r_sub) * kGTileLd + c4);
+          if (row >= p.M || nc <= 0) continue;
+          __nv_bfloat16* d = base + static_cast<size_t>(row) * sg.ld;
+          if (vec_ok) {
+            *reinterpret_cast<uint2*>(d) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
           } else {
-            d[0] = (sg.mode == RMEM_OUT_F32_ACCUM) ? d[0] + v0 : v0;
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            for (int e = 0; e < 4 && e < nc; ++e) d[e] = __float2bfloat16(vv[e]);
+          }
+        }
+      } else {
+        float* base = static_cast<float*>(sg.dst) + col_off;
+        const bool accum = sg.mode == RMEM_OUT_F32_ACCUM;
+        float4 old[8];
+        if (accum && vec_ok) {
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int row = row_base + it * 4;
+            old[it] = row < p.M ? *reinterpret_cast<const float4*>(base + static_cast<size_t>(row) * sg.ld)
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int row = row_base + it * 4;
+          float4 v = *reinterpret_cast<const float4*>(tile + (it * 4 + r_sub) * kGTileLd + c4);
+          if (row >= p.M || nc <= 0) continue;
+          float* d = base + static_cast<size_t>(row) * sg.ld;
+          if (vec_ok) {
+            if (accum) { v.x += old[it].x; v.y += old[it].y; v.z += old[it].z; v.w += old[it].w; }
+            *reinterpret_cast<float4*>(d) = v;
+          } else {
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            for (int e = 0; e < 4 && e < nc; ++e) d[e] = accum ? d[e] + vv[e] : vv[e];
           }
         }
       }
@@ -167,7 +211,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<128>(tmem_base);
+    tmem_dealloc<BN>(tmem_base);
   }
 }
 
@@ -201,18 +245,34 @@ int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bia
         (reinterpret_cast<uintptr_t>(segs[s].dst) % (segs[s].mode == RMEM_OUT_BF16 ? 4 : 8)))
       return set_error(RMEM_ERR_ARG, "gemm: destination ld / column offset must be even and the base 8-byte aligned");
   }
+  // column-tile width: 128 unless that leaves fewer CTAs than SMs (the row dimension gives only ceil(M/128) tiles)
+  const int m_tiles = (M + kGM - 1) / kGM;
+  const bool narrow = m_tiles * ((N + 127) / 128) < 120;
+  const int bn = narrow ? 64 : 128;
   CUtensorMap tm_a, tm_w;
   if (int e = encode_2d(&tm_a, a, K, M, static_cast<uint64_t>(lda) * 2, kGM)) return e;
-  if (int e = encode_2d(&tm_w, w, K, N, static_cast<uint64_t>(ldw) * 2, kGN)) return e;
+  if (int e = encode_2d(&tm_w, w, K, N, static_cast<uint64_t>(ldw) * 2, bn)) return e;
+  const bool deep = narrow && K >= 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tn_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmem);
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         GemmCfg<128, 3>::kSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               GemmCfg<64, 3>::kSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<64, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               GemmCfg<64, 6>::kSmem);
     if (e != cudaSuccess) return set_cuda_error(e, "gemm: cudaFuncSetAttribute");
     attr_set = true;
   }
-  dim3 grid((N + kGN - 1) / kGN, (M + kGM - 1) / kGM);
-  gemm_bf16_tn_kernel<<<grid, kGThreads, kGSmem, stream>>>(tm_a, tm_w, p);
+  dim3 grid((N + bn - 1) / bn, m_tiles);
+  if (deep)
+    gemm_bf16_tn_kernel<64, 6><<<grid, kGThreads, GemmCfg<64, 6>::kSmem, stream>>>(tm_a, tm_w, p);
+  else if (narrow)
+    gemm_bf16_tn_kernel<64, 3><<<grid, kGThreads, GemmCfg<64, 3>::kSmem, stream>>>(tm_a, tm_w, p);
+  else
+    gemm_bf16_tn_kernel<128, 3><<<grid, kGThreads, GemmCfg<128, 3>::kSmem, stream>>>(tm_a, tm_w, p);
   return check_launch("gemm_bf16_tn_kernel");
 }
 

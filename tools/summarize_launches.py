@@ -2,6 +2,20 @@
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: total time and launch count per kernel."""
 import csv, sys, re, collections
 
+def short(name):
+    """Drop template arguments and parameter lists, keep the last two scopes."""
+    out, depth = [], 0
+    for ch in name:
+        if ch in "<(":
+            depth += 1
+        elif ch in ">)":
+            depth -= 1
+        elif depth == 0:
+            out.append(ch)
+    n = "".join(out).replace("void ", "").strip()
+    return "::".join(n.split("::")[-2:])[-80:]
+
+
 def main(path, top=40):
     tot = collections.defaultdict(float); cnt = collections.Counter()
     with open(path, newline="") as f:
@@ -10,8 +24,7 @@ def main(path, top=40):
         if r.get("Metric Name") != "gpu__time_duration.sum":
             continue
         name = r["Kernel Name"]
-        name = re.sub(r"\(.*", "", name)
-        name = re.sub(r"<.*", "", name)[-70:]
+        name = short(name)
         tot[name] += float(r["Metric Value"].replace(",", "")) / 1e3
         cnt[name] += 1
     total = sum(tot.values())
