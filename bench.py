@@ -113,9 +113,14 @@ class ClockSampler:
 
 def frame_step(eng, img_dev, out_hw):
     """One step: read path + write path of one frame (device-resident image in, label map out)."""
+    from rmem_ocu_b200 import ops
     logit = eng.match_propogate_one_frame(img_dev, output_size=out_hw)
-    label = torch.argmax(logit, dim=1, keepdim=True).float()     # = argmax(softmax(.)), evaluator.py:430-441
-    eng.update_memory(F.interpolate(label, size=eng.input_size_2d, mode="nearest"))
+    label = ops.argmax_label(logit)                              # = argmax(softmax(.)), evaluator.py:430-441
+    if tuple(label.shape[-2:]) != tuple(eng.input_size_2d):
+        label_in = F.interpolate(label, size=eng.input_size_2d, mode="nearest")      # evaluator.py:518-522
+    else:
+        label_in = label                                         # nearest resize to the same size = identity
+    eng.update_memory(label_in)
     return label
 
 

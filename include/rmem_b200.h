@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 1
+#define RMEM_ABI_VERSION 2
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -262,13 +262,25 @@ int rmem_id_embed(const float* label, int H, int W, const float* prefix, const f
  * (align_corners=True) upsampling + shortcut add (fpn.py:49-60) run here on the channels-last
  * [H*W][C] view.
  *   rmem_groupnorm_nhwc: x, y f32 [P][C] (C = 64 / 128 / 256, C/groups a power of two in [4,32]);
- *       gamma/beta f32 [C]; relu != 0 applies max(.,0); workspace 16*groups bytes (zeroed by the call).
- *   rmem_upsample_add_nhwc: out[ho*wo][C] = a[ho*wo][C] (or 0 when NULL) + bilinear(x[hi*wi][C]).
+ *       pre_bias f32 [C] or NULL is added to x first (the conv bias of ConvGN, so the convolution itself runs
+ *       without a separate bias pass); gamma/beta f32 [C]; relu != 0 applies max(.,0); workspace 16*groups
+ *       bytes (zeroed by the call).
+ *   rmem_upsample_add_nhwc: out[ho*wo][C] = a[ho*wo][C] (or 0 when NULL) + a_bias[C] (or 0) + bilinear(x[hi*wi][C]).
  */
-int rmem_groupnorm_nhwc(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
-                        int groups, int relu, void* workspace, void* stream);
-int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, float* out, int ho, int wo, int C,
-                           void* stream);
+int rmem_groupnorm_nhwc(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                        int P, int C, int groups, int relu, void* workspace, void* stream);
+int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, const float* a_bias, float* out,
+                           int ho, int wo, int C, void* stream);
+
+/* Tail of decode_current_logits (aot_engine.py:451-463): pred[c][y][x] = conv[c*sc + y*sy + x*sx] + bias[c] for
+ * c < n_valid, -1e10 for the channels beyond the sequence's objects (:455-457); then, when out != NULL, the
+ * bilinear align_corners=True resize pred [C][Hs][Ws] -> out [C][Ho][Wo] (:459-463).  Strides in elements. */
+int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, const float* bias, float* pred,
+                       int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, void* stream);
+
+/* label[i] = (f32) argmax_c logits[c][i], first maximum -- the evaluator's softmax + argmax over the object
+ * channel (networks/managers/evaluator.py:430-441); logits f32 [C][HW], label f32 [HW]. */
+int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream);
 
 /* fg[q] = 1 - softmax_c(bilinear_align_corners(pred_id_logits -> (h,w)))[0]
  * (aot_engine.py:355-362).  logits f32 [C][Hs][Ws] -> fg f32 [h*w]. */

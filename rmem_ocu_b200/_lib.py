@@ -78,8 +78,12 @@ _SIGNATURES = {
     "rmem_tpe_prepare": [_c_void_p] * 5 + [_c_int] * 2 + [_c_void_p],
     "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_local_attn_aggregate": [_c_void_p] * 4 + [_c_int, _c_int, _c_void_p],
-    "rmem_groupnorm_nhwc": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 2,
-    "rmem_upsample_add_nhwc": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_void_p],
+    "rmem_groupnorm_nhwc": [_c_void_p] * 5 + [_c_int] * 4 + [_c_void_p] * 2,
+    "rmem_upsample_add_nhwc": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int, _c_int,
+                               _c_void_p],
+    "rmem_finish_logits": [_c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, _c_void_p, _c_void_p] +
+                          [_c_int] * 4 + [_c_void_p, _c_int, _c_int, _c_void_p],
+    "rmem_argmax_label": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
     "rmem_bank_init": [_c_void_p, _c_int, _c_void_p],
     "rmem_bank_tick": [_c_void_p, _c_void_p],
     "rmem_id_embed": [_c_void_p, _c_int, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],

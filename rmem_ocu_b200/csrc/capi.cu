@@ -126,13 +126,20 @@ int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gat
                               int h, int w, void* stream) {
   return local_aggregate_launch(probs, v, gate, out, h, w, ST(stream));
 }
-int rmem_groupnorm_nhwc(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
-                        int groups, int relu, void* workspace, void* stream) {
-  return groupnorm_nhwc_launch(x, gamma, beta, y, P, C, groups, relu, workspace, ST(stream));
+int rmem_groupnorm_nhwc(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                        int P, int C, int groups, int relu, void* workspace, void* stream) {
+  return groupnorm_nhwc_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, workspace, ST(stream));
 }
-int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, float* out, int ho, int wo, int C,
-                           void* stream) {
-  return upsample_add_nhwc_launch(x, hi, wi, a, out, ho, wo, C, ST(stream));
+int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, const float* a_bias, float* out,
+                           int ho, int wo, int C, void* stream) {
+  return upsample_add_nhwc_launch(x, hi, wi, a, a_bias, out, ho, wo, C, ST(stream));
+}
+int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, const float* bias, float* pred,
+                       int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, void* stream) {
+  return finish_logits_launch(conv, sc, sy, sx, bias, pred, C, Hs, Ws, n_valid, out, Ho, Wo, ST(stream));
+}
+int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream) {
+  return argmax_label_launch(logits, C, HW, label, ST(stream));
 }
 int rmem_bank_tick(void* bank_state, void* stream) { return bank_tick_launch(bank_state, ST(stream)); }
 int rmem_id_embed(const float* label, int H, int W, const float* prefix, const float* bias,

@@ -16,8 +16,8 @@ namespace rmem {
 // shuffles, over the CTA in shared memory, and added to the fp64 workspace with one atomic pair per
 // (CTA, group).  The range per CTA is sized so the grid is ~4 CTAs per SM whatever the resolution.
 __global__ void __launch_bounds__(256)
-gn_nhwc_stats_kernel(const float* __restrict__ x, int P, int C, int cpg, int rows_per_cta,
-                     double* __restrict__ ws) {
+gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias, int P, int C, int cpg,
+                     int rows_per_cta, double* __restrict__ ws) {
   const int tpp = C >> 2;                        // threads per pixel (C = 64, 128, 256 -> 16, 32, 64)
   const int ppb = 256 / tpp;                     // pixels per step
   const int c = (threadIdx.x % tpp) * 4;
@@ -25,9 +25,11 @@ gn_nhwc_stats_kernel(const float* __restrict__ x, int P, int C, int cpg, int row
   const int p0 = blockIdx.x * rows_per_cta;
   const int p1 = min(p0 + rows_per_cta, P);
   float s = 0.f, q = 0.f;
+  const float4 pb = pre_bias ? *reinterpret_cast<const float4*>(pre_bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
   for (int pix = p0 + ph; pix < p1; pix += ppb) {
-    const float4 v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    float4 v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    v.x += pb.x; v.y += pb.y; v.z += pb.z; v.w += pb.w;
     s += (v.x + v.y) + (v.z + v.w);
     q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
   }
@@ -51,9 +53,9 @@ gn_nhwc_stats_kernel(const float* __restrict__ x, int P, int C, int cpg, int row
 }
 
 __global__ void __launch_bounds__(256)
-gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                     const float* __restrict__ beta, float* __restrict__ y, int P, int C, int cpg,
-                     int relu, const double* __restrict__ ws) {
+gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
+                     int P, int C, int cpg, int relu, const double* __restrict__ ws) {
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   const double cnt = static_cast<double>(cpg) * P;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
@@ -64,7 +66,11 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamm
     const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
     const float mean = static_cast<float>(mean_d);
     const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
-    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    float4 v = reinterpret_cast<const float4*>(x)[i];
+    if (pre_bias) {
+      const float4 pb = *reinterpret_cast<const float4*>(pre_bias + c);
+      v.x += pb.x; v.y += pb.y; v.z += pb.z; v.w += pb.w;
+    }
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
     const float4 be = *reinterpret_cast<const float4*>(beta + c);
     float4 o;
@@ -77,8 +83,8 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamm
   }
 }
 
-int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
-                          int groups, int relu, void* workspace, cudaStream_t stream) {
+int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                          int P, int C, int groups, int relu, void* workspace, cudaStream_t stream) {
   if (groups < 1 || groups > 32 || (C % groups) || (C != 64 && C != 128 && C != 256) || P < 1)
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: C must be 64 / 128 / 256");
   const int cpg = C / groups;
@@ -88,13 +94,13 @@ int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta,
   if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_nhwc: memset");
   int rows = (P + 591) / 592;                    // ~4 CTAs per SM at large P ...
   if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
-  gn_nhwc_stats_kernel<<<(P + rows - 1) / rows, 256, 0, stream>>>(x, P, C, cpg, rows,
+  gn_nhwc_stats_kernel<<<(P + rows - 1) / rows, 256, 0, stream>>>(x, pre_bias, P, C, cpg, rows,
                                                                  static_cast<double*>(workspace));
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   int blocks = static_cast<int>((total4 + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  gn_nhwc_apply_kernel<<<blocks, 256, 0, stream>>>(x, gamma, beta, y, P, C, cpg, relu,
+  gn_nhwc_apply_kernel<<<blocks, 256, 0, stream>>>(x, pre_bias, gamma, beta, y, P, C, cpg, relu,
                                                    static_cast<const double*>(workspace));
   return check_launch("gn_nhwc_apply_kernel");
 }
@@ -103,7 +109,7 @@ int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta,
 // out[y][x][c] = a[y][x][c] + bilinear(x_in)[y][x][c], align_corners = True (F.interpolate, fpn.py:49-60)
 __global__ void __launch_bounds__(256)
 upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const float* __restrict__ a,
-                         float* __restrict__ out, int ho, int wo, int C) {
+                         const float* __restrict__ a_bias, float* __restrict__ out, int ho, int wo, int C) {
   const int c4 = C / 4;
   const size_t total = static_cast<size_t>(ho) * wo * c4;
   const float sy = ho > 1 ? static_cast<float>(hi - 1) / static_cast<float>(ho - 1) : 0.f;
@@ -123,6 +129,10 @@ upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const fl
     const float4 v11 = *reinterpret_cast<const float4*>(xin + (static_cast<size_t>(y1) * wi + x1) * C + c);
     float4 o = a ? *reinterpret_cast<const float4*>(a + static_cast<size_t>(pix) * C + c)
                  : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a_bias) {
+      const float4 ab = *reinterpret_cast<const float4*>(a_bias + c);
+      o.x += ab.x; o.y += ab.y; o.z += ab.z; o.w += ab.w;
+    }
     o.x += hy * (hx * v00.x + lx * v01.x) + ly * (hx * v10.x + lx * v11.x);
     o.y += hy * (hx * v00.y + lx * v01.y) + ly * (hx * v10.y + lx * v11.y);
     o.z += hy * (hx * v00.z + lx * v01.z) + ly * (hx * v10.z + lx * v11.z);
@@ -131,15 +141,121 @@ upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const fl
   }
 }
 
-int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, float* out, int ho, int wo,
-                             int C, cudaStream_t stream) {
+int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
+                             int ho, int wo, int C, cudaStream_t stream) {
   if ((C % 4) || hi < 1 || wi < 1 || ho < 1 || wo < 1)
     return set_error(RMEM_ERR_ARG, "upsample_add_nhwc: C must be a multiple of 4");
   const size_t total = static_cast<size_t>(ho) * wo * (C / 4);
   int blocks = static_cast<int>((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  upsample_add_nhwc_kernel<<<blocks, 256, 0, stream>>>(xin, hi, wi, a, out, ho, wo, C);
+  upsample_add_nhwc_kernel<<<blocks, 256, 0, stream>>>(xin, hi, wi, a, a_bias, out, ho, wo, C);
   return check_launch("upsample_add_nhwc_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// decode_current_logits tail (aot_engine.py:451-463): logits = conv_out + bias, channels beyond the
+// sequence's objects masked to -1e10, kept as pred_id_logits [C][Hs][Ws]; then the bilinear
+// (align_corners = True) resize to the output size, [C][Ho][Wo].
+__global__ void __launch_bounds__(256)
+finish_logits_kernel(const float* __restrict__ conv, long long sc, long long sy, long long sx,
+                     const float* __restrict__ bias, float* __restrict__ pred, int C, int Hs, int Ws, int n_valid) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = C * Hs * Ws;
+  if (i >= total) return;
+  const int c = i / (Hs * Ws), r = i - c * (Hs * Ws);
+  const int y = r / Ws, x = r - y * Ws;
+  const float v = conv[c * sc + y * sy + x * sx] + (bias ? bias[c] : 0.f);
+  pred[i] = c < n_valid ? v : -1e10f;
+}
+
+__global__ void __launch_bounds__(256)
+upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, float* __restrict__ out, int Ho,
+                       int Wo) {
+  // thread = 4 consecutive output pixels of one row, all C channels (weights computed once per pixel)
+  const int wq = (Wo + 3) / 4;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Ho * wq) return;
+  const int y = i / wq, x4 = (i - y * wq) * 4;
+  const float sy = Ho > 1 ? static_cast<float>(Hs - 1) / static_cast<float>(Ho - 1) : 0.f;
+  const float sx = Wo > 1 ? static_cast<float>(Ws - 1) / static_cast<float>(Wo - 1) : 0.f;
+  const float fy = sy * y;
+  const int y0 = static_cast<int>(fy), y1 = min(y0 + 1, Hs - 1);
+  const float ly = fy - y0, hy = 1.f - ly;
+  int x0[4], x1[4];
+  float lx[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float fx = sx * (x4 + k);
+    x0[k] = min(static_cast<int>(fx), Ws - 1);
+    x1[k] = min(x0[k] + 1, Ws - 1);
+    lx[k] = fx - x0[k];
+  }
+  const bool full = x4 + 3 < Wo && (Wo & 3) == 0;
+  for (int c = 0; c < C; ++c) {
+    const float* r0 = pred + (static_cast<size_t>(c) * Hs + y0) * Ws;
+    const float* r1 = pred + (static_cast<size_t>(c) * Hs + y1) * Ws;
+    float o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      o[k] = hy * ((1.f - lx[k]) * r0[x0[k]] + lx[k] * r0[x1[k]]) + ly * ((1.f - lx[k]) * r1[x0[k]] + lx[k] * r1[x1[k]]);
+    float* d = out + (static_cast<size_t>(c) * Ho + y) * Wo + x4;
+    if (full) {
+      *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
+    } else {
+      for (int k = 0; k < 4 && x4 + k < Wo; ++k) d[k] = o[k];
+    }
+  }
+}
+
+int finish_logits_launch(const float* conv, long long sc, long long sy, long long sx, const float* bias, float* pred,
+                         int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream) {
+  if (C < 1 || Hs < 1 || Ws < 1) return set_error(RMEM_ERR_ARG, "finish_logits: bad shape");
+  const int total = C * Hs * Ws;
+  finish_logits_kernel<<<(total + 255) / 256, 256, 0, stream>>>(conv, sc, sy, sx, bias, pred, C, Hs, Ws, n_valid);
+  if (int r = check_launch("finish_logits_kernel")) return r;
+  if (out) {
+    const int n = Ho * ((Wo + 3) / 4);
+    upsample_logits_kernel<<<(n + 255) / 256, 256, 0, stream>>>(pred, C, Hs, Ws, out, Ho, Wo);
+    return check_launch("upsample_logits_kernel");
+  }
+  return RMEM_OK;
+}
+
+// label[y][x] = argmax_c logits[c][y][x] (first maximum, like torch.argmax) as f32 -- the evaluator's
+// softmax + argmax (networks/managers/evaluator.py:430-441; softmax is monotone, so it is skipped).
+__global__ void __launch_bounds__(256)
+argmax_label_kernel(const float* __restrict__ logits, int C, int HW, float* __restrict__ label) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= HW) return;
+  if (i + 3 < HW && (HW & 3) == 0) {
+    float4 best = *reinterpret_cast<const float4*>(logits + i);
+    float4 arg = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = 1; c < C; ++c) {
+      const float4 v = *reinterpret_cast<const float4*>(logits + static_cast<size_t>(c) * HW + i);
+      if (v.x > best.x) { best.x = v.x; arg.x = c; }
+      if (v.y > best.y) { best.y = v.y; arg.y = c; }
+      if (v.z > best.z) { best.z = v.z; arg.z = c; }
+      if (v.w > best.w) { best.w = v.w; arg.w = c; }
+    }
+    *reinterpret_cast<float4*>(label + i) = arg;
+  } else {
+    for (int k = i; k < HW && k < i + 4; ++k) {
+      float best = logits[k];
+      int arg = 0;
+      for (int c = 1; c < C; ++c) {
+        const float v = logits[static_cast<size_t>(c) * HW + k];
+        if (v > best) { best = v; arg = c; }
+      }
+      label[k] = static_cast<float>(arg);
+    }
+  }
+}
+
+int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream) {
+  if (C < 1 || HW < 1) return set_error(RMEM_ERR_ARG, "argmax_label: bad shape");
+  const int n = (HW + 3) / 4;
+  argmax_label_kernel<<<(n + 255) / 256, 256, 0, stream>>>(logits, C, HW, label);
+  return check_launch("argmax_label_kernel");
 }
 
 }  // namespace rmem

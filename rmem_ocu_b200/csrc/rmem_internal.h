@@ -62,10 +62,13 @@ int local_scores_launch(const void* q, const void* k, const float* rel, int ld_r
                         int w, cudaStream_t stream);
 int local_aggregate_launch(const float* probs, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream);
-int groupnorm_nhwc_launch(const float* x, const float* gamma, const float* beta, float* y, int P, int C,
-                          int groups, int relu, void* workspace, cudaStream_t stream);
-int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, float* out, int ho, int wo,
-                             int C, cudaStream_t stream);
+int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                          int P, int C, int groups, int relu, void* workspace, cudaStream_t stream);
+int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
+                             int ho, int wo, int C, cudaStream_t stream);
+int finish_logits_launch(const float* conv, long long sc, long long sy, long long sx, const float* bias, float* pred,
+                         int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream);
+int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream);
 int bank_tick_launch(void* state, cudaStream_t stream);
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
                     const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,

@@ -129,19 +129,21 @@ class InferenceFPN:
         return x.permute(0, 2, 3, 1).reshape(h * w, c)
 
     def _conv_gn_relu(self, x, name):
+        """ConvGN + ReLU: the conv bias is applied inside the GroupNorm kernels (no separate bias pass)."""
         w, b, g, be = self.w[name]
-        y = F.conv2d(x, w, b, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
+        y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
         t = self._tok(y)
-        ops.groupnorm_nhwc(t, g, be, t, 8, True, self.gn_ws)          # in place
+        ops.groupnorm_nhwc(t, g, be, t, 8, True, self.gn_ws, pre_bias=b)          # in place
         return y
 
     def _up_add(self, x, shortcut, name):
+        """adapter(shortcut) + bias + bilinear(x) (identity resample when the sizes agree)."""
         w, b = self.w[name]
-        a = F.conv2d(shortcut, w, b).contiguous(memory_format=torch.channels_last)
+        a = F.conv2d(shortcut, w, None).contiguous(memory_format=torch.channels_last)
         hi, wi = x.shape[-2:]
         ho, wo = a.shape[-2:]
         ta = self._tok(a)
-        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo)   # a += bilinear(x), in place
+        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b)     # in place
         return a
 
     def __call__(self, inputs, shortcuts):
@@ -149,12 +151,11 @@ class InferenceFPN:
         x = x.float().contiguous(memory_format=torch.channels_last)
         sc = [s.float().contiguous(memory_format=torch.channels_last) for s in shortcuts]
         x = self._conv_gn_relu(x, "conv_in")
-        w, b = self.w["adapter_16x"]
-        x = self._conv_gn_relu(F.conv2d(sc[-2], w, b) + x, "conv_16x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x"), "conv_16x")
         x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x"), "conv_8x")
         x = self._conv_gn_relu(self._up_add(x, sc[-4], "adapter_4x"), "conv_4x")
         w, b = self.w["conv_out"]
-        return F.conv2d(x, w, b)
+        return F.conv2d(x, w, None), b          # the caller adds the bias while finishing the logits
 
 
 class InferenceResNet:
@@ -179,7 +180,13 @@ class InferenceResNet:
             stage = []
             for blk in getattr(enc, "layer%d" % li):
                 down = cv(blk.downsample[0]) if blk.downsample is not None else None
-                stage.append((cv(blk.conv1), cv(blk.conv2), cv(blk.conv3), down))
+                c3 = cv(blk.conv3)
+                if down is not None:
+                    # relu(conv3(y) + b3 + down(x) + bd): both biases ride on conv3's fused epilogue
+                    b3 = (blk.conv3.bias.detach().float() + blk.downsample[0].bias.detach().float())
+                    c3 = (c3[0], b3.to(device=device, dtype=dtype), c3[2], c3[3])
+                    down = (down[0], None, down[2], down[3])
+                stage.append((cv(blk.conv1), cv(blk.conv2), c3, down))
             self.blocks.append(stage)
         self.proj = cv(projector)
         self.fused = hasattr(torch, "cudnn_convolution_relu") and os_env_flag("RMEM_FUSED_CONV", True)
@@ -526,18 +533,19 @@ class DeAOTEngine:
 
     def _decode(self, embs, lstt_out, output_size):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
-        logits = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs)
-        for b, on in enumerate(self.obj_nums):
-            if on + 1 < logits.shape[1]:
-                logits[b, on + 1:] = -1e10
+        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs)
         ws = self.ws
-        if ws.pred_logits is None or ws.pred_logits.shape != logits.shape:
-            ws.pred_logits = torch.empty_like(logits, memory_format=torch.contiguous_format)
-        ws.pred_logits.copy_(logits)                                      # persistent buffer (read by the write path)
-        self.pred_id_logits = ws.pred_logits
+        if ws.pred_logits is None or ws.pred_logits.shape != conv.shape:
+            ws.pred_logits = torch.empty(conv.shape, device=conv.device, dtype=torch.float32)
+        out = None
         if output_size is not None:
-            logits = F.interpolate(logits, size=output_size, mode="bilinear", align_corners=self.align_corners)
-        return logits
+            out = torch.empty(1, conv.shape[1], output_size[0], output_size[1], device=conv.device,
+                              dtype=torch.float32)
+        # + conv bias, channels beyond the objects -> -1e10 (aot_engine.py:455-457), persistent pred_id_logits
+        # (read by the write path), bilinear resize to the output size (:459-463)
+        ops.finish_logits(conv, bias, ws.pred_logits, int(self.obj_nums[0]) + 1, out)
+        self.pred_id_logits = ws.pred_logits
+        return ws.pred_logits if out is None else out
 
     # ------------------------------------------------------------------ CUDA graphs
     def _run(self, key, body, inputs):

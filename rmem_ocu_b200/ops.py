@@ -80,20 +80,43 @@ def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
     _count("rmem_groupnorm_tokens")
 
 
-def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace):
-    """GroupNorm(+ReLU) of a channels-last [1, C, H, W] f32 tensor viewed as [H*W, C]."""
+def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace, pre_bias=None):
+    """GroupNorm(+ReLU) of (x + pre_bias), a channels-last [1, C, H, W] f32 tensor viewed as [H*W, C]."""
     P, C = x.shape
-    _lib.check(_lib.lib().rmem_groupnorm_nhwc(_p(x), _p(gamma), _p(beta), _p(y), P, C, groups, 1 if relu else 0,
-                                              _p(workspace), _stream()), "rmem_groupnorm_nhwc")
+    _lib.check(_lib.lib().rmem_groupnorm_nhwc(_p(x), _p(pre_bias), _p(gamma), _p(beta), _p(y), P, C, groups,
+                                              1 if relu else 0, _p(workspace), _stream()), "rmem_groupnorm_nhwc")
     _count("rmem_groupnorm_nhwc")
 
 
-def upsample_add_nhwc(x, hi, wi, a, out, ho, wo):
-    """out = a + bilinear_align_corners(x); x f32 [hi*wi, C], a / out f32 [ho*wo, C]."""
+def upsample_add_nhwc(x, hi, wi, a, out, ho, wo, a_bias=None):
+    """out = a + a_bias + bilinear_align_corners(x); x f32 [hi*wi, C], a / out f32 [ho*wo, C]."""
     C = x.shape[1]
-    _lib.check(_lib.lib().rmem_upsample_add_nhwc(_p(x), hi, wi, _p(a), _p(out), ho, wo, C, _stream()),
+    _lib.check(_lib.lib().rmem_upsample_add_nhwc(_p(x), hi, wi, _p(a), _p(a_bias), _p(out), ho, wo, C, _stream()),
                "rmem_upsample_add_nhwc")
     _count("rmem_upsample_add_nhwc")
+
+
+def finish_logits(conv, bias, pred, n_valid, out=None):
+    """conv: f32 [1, C, Hs, Ws] (any strides) -> pred f32 [1, C, Hs, Ws] contiguous (+ bias, channels >= n_valid
+    set to -1e10) and, if given, out f32 [1, C, Ho, Wo] = bilinear align_corners resize of pred."""
+    _, C, Hs, Ws = conv.shape
+    Ho, Wo = (out.shape[-2], out.shape[-1]) if out is not None else (0, 0)
+    _lib.check(_lib.lib().rmem_finish_logits(_p(conv), conv.stride(1), conv.stride(2), conv.stride(3), _p(bias),
+                                             _p(pred), C, Hs, Ws, n_valid, _p(out), Ho, Wo, _stream()),
+               "rmem_finish_logits")
+    global LAUNCHES
+    LAUNCHES += 2 if out is not None else 1
+
+
+def argmax_label(logits, label=None):
+    """logits f32 [1, C, H, W] contiguous -> label f32 [1, 1, H, W] (argmax over the object channel)."""
+    _chk_cuda(logits)
+    _, C, H, W = logits.shape
+    if label is None:
+        label = torch.empty(1, 1, H, W, device=logits.device, dtype=torch.float32)
+    _lib.check(_lib.lib().rmem_argmax_label(_p(logits), C, H * W, _p(label), _stream()), "rmem_argmax_label")
+    _count("rmem_argmax_label")
+    return label
 
 
 def tpe_prepare(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias):

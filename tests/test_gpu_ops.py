@@ -173,12 +173,18 @@ def test_groupnorm_nhwc(lib_built, C, H, W):
     torch.manual_seed(8)
     x = (torch.randn(1, C, H, W, device="cuda") * 2 + 0.3).contiguous(memory_format=torch.channels_last)
     g, b = torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
-    ref = F.relu(F.group_norm(x, 8, g, b, 1e-5))
+    pb = torch.randn(C, device="cuda")                       # the conv bias, folded into the norm
+    ref = F.relu(F.group_norm(x + pb.view(1, C, 1, 1), 8, g, b, 1e-5))
+    ref0 = F.relu(F.group_norm(x, 8, g, b, 1e-5))
     t = x.permute(0, 2, 3, 1).reshape(H * W, C)
+    y = torch.empty_like(t)
     ws = torch.empty(16, device="cuda", dtype=torch.float64)
-    ops.groupnorm_nhwc(t, g, b, t, 8, True, ws)
+    ops.groupnorm_nhwc(t, g, b, y, 8, True, ws, pre_bias=pb)
     torch.cuda.synchronize()
-    assert (x - ref).abs().max().item() < 2e-4
+    assert (y.view(1, H, W, C).permute(0, 3, 1, 2) - ref).abs().max().item() < 2e-4
+    ops.groupnorm_nhwc(t, g, b, t, 8, True, ws)             # in place, no bias
+    torch.cuda.synchronize()
+    assert (x - ref0).abs().max().item() < 2e-4
 
 
 @pytest.mark.parametrize("C,hi,wi,ho,wo", [(256, 30, 54, 60, 108), (128, 60, 108, 120, 216), (128, 31, 55, 61, 109)])
@@ -188,11 +194,36 @@ def test_upsample_add_nhwc(lib_built, C, hi, wi, ho, wo):
     torch.manual_seed(9)
     x = torch.randn(1, C, hi, wi, device="cuda").contiguous(memory_format=torch.channels_last)
     a = torch.randn(1, C, ho, wo, device="cuda").contiguous(memory_format=torch.channels_last)
-    ref = a + F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
+    ab = torch.randn(C, device="cuda")
+    ref = a + ab.view(1, C, 1, 1) + F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
     ta = a.permute(0, 2, 3, 1).reshape(ho * wo, C)
-    ops.upsample_add_nhwc(x.permute(0, 2, 3, 1).reshape(hi * wi, C), hi, wi, ta, ta, ho, wo)
+    ops.upsample_add_nhwc(x.permute(0, 2, 3, 1).reshape(hi * wi, C), hi, wi, ta, ta, ho, wo, a_bias=ab)
     torch.cuda.synchronize()
     assert (a - ref).abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("Hs,Ws,Ho,Wo,n_valid", [(120, 216, 480, 864, 6), (32, 48, 128, 192, 2), (31, 55, 121, 217, 11)])
+def test_finish_logits_and_argmax(lib_built, Hs, Ws, Ho, Wo, n_valid):
+    """Tail of decode_current_logits (aot_engine.py:451-463): bias, -1e10 masking of unused object channels,
+    bilinear align_corners resize; and the evaluator's argmax over channels (evaluator.py:430-441)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(12)
+    C = 11
+    conv = torch.randn(1, C, Hs, Ws, device="cuda").contiguous(memory_format=torch.channels_last)
+    bias = torch.randn(C, device="cuda")
+    ref = conv + bias.view(1, C, 1, 1)
+    ref[:, n_valid:] = -1e10
+    ref_up = F.interpolate(ref, size=(Ho, Wo), mode="bilinear", align_corners=True)
+    pred = torch.empty(1, C, Hs, Ws, device="cuda")
+    out = torch.empty(1, C, Ho, Wo, device="cuda")
+    ops.finish_logits(conv, bias, pred, n_valid, out)
+    label = ops.argmax_label(out)
+    torch.cuda.synchronize()
+    assert torch.equal(pred, ref.contiguous())
+    assert (out[:, :n_valid] - ref_up[:, :n_valid]).abs().max().item() < 1e-4
+    assert (out[:, n_valid:] < -9e9).all()
+    assert torch.equal(label, torch.argmax(out, 1, keepdim=True).float())
+    assert (label == torch.argmax(ref_up, 1, keepdim=True).float()).float().mean().item() > 0.9999
 
 
 def test_decoder_head_vs_oracle(lib_built):
@@ -211,6 +242,7 @@ def test_decoder_head_vs_oracle(lib_built):
     fpn = InferenceFPN(sd, torch.device("cuda"), intermediate=False)
     cl = lambda t: t.cuda().contiguous(memory_format=torch.channels_last)
     with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
-        out = fpn([cl(embs[-1]), cl(lstt)], [cl(e) for e in embs])
+        conv, bias = fpn([cl(embs[-1]), cl(lstt)], [cl(e) for e in embs])
+    out = conv + bias.view(1, -1, 1, 1)
     torch.cuda.synchronize()
     assert _rel(out.cpu(), ref) < 1e-4
