@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 2
+#define RMEM_ABI_VERSION 3
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -190,13 +190,18 @@ int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_p
  * Stage 1 (scores): probs[q][t] = softmax_t( q.k[nbr(q,t)]/sqrt(128) + rel_bias[q][t] ) over the
  *   in-image taps (out-of-image taps get probability 0, as exp(-1e8) does in fp32).
  *   q, k bf16 [h*w][128];  rel_bias f32 [h*w][ld_rel] (= q W_rel^T + b_rel, from rmem_linear);
- *   probs f32 [h*w][225]  (this is local_attn[0,0,:,q] of the reference, transposed)
+ *   probs f32 [h*w][225] or NULL (this is local_attn[0,0,:,q] of the reference, transposed);
+ *   banded bf16 [rmem_local_banded_elems(h, w)] or NULL: the same probabilities in the per-tile banded
+ *   layout stage 2 multiplies with (8x16 query tiles, 11 blocks of 2 halo rows x 32 key slots; see
+ *   csrc/local_attn.cu).  Only in-window slots are written: the CALLER zero-fills the buffer once
+ *   (per sequence / geometry); it stays valid across frames.
  * Stage 2 (aggregate): out[q][c] = gate[q][c] * sum_t probs[q][t] * v[nbr(q,t)][c]
- *   v bf16 [h*w][1024];  gate bf16 [h*w][1024] or NULL;  out bf16 [h*w][1024]
+ *   banded from stage 1;  v bf16 [h*w][1024];  gate bf16 [h*w][1024] or NULL;  out bf16 [h*w][1024]
  */
+int64_t rmem_local_banded_elems(int h, int w);
 int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, int ld_rel,
-                           float* probs, int h, int w, void* stream);
-int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gate, void* out,
+                           float* probs, void* banded, int h, int w, void* stream);
+int rmem_local_attn_aggregate(const void* banded, const void* v, const void* gate, void* out,
                               int h, int w, void* stream);
 
 /* ---------------------------------------------------------------------------------------------

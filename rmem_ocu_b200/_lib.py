@@ -36,7 +36,7 @@ def build(force=False, verbose=False):
     if not force and not _stale():
         return LIB_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB_PATH] + sources()
+    cmd = [nvcc] + NVCC_FLAGS + os.environ.get("RMEM_NVCC_EXTRA", "").split() + ["-o", LIB_PATH] + sources()
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -76,7 +76,8 @@ _SIGNATURES = {
                      _c_int, _c_void_p],
     "rmem_groupnorm_tokens": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p] * 2,
     "rmem_tpe_prepare": [_c_void_p] * 5 + [_c_int] * 2 + [_c_void_p],
-    "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_int, _c_int, _c_void_p],
+    "rmem_local_banded_elems": [_c_int, _c_int],
+    "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_local_attn_aggregate": [_c_void_p] * 4 + [_c_int, _c_int, _c_void_p],
     "rmem_groupnorm_nhwc": [_c_void_p] * 5 + [_c_int] * 4 + [_c_void_p] * 2,
     "rmem_upsample_add_nhwc": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int, _c_int,
@@ -105,7 +106,7 @@ MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8
 ACT_NONE, ACT_SILU = 0, 1
 OUT_BF16, OUT_F32, OUT_F32_ACCUM = 0, 1, 2
-_RESTYPES = {"rmem_last_error": ctypes.c_char_p}
+_RESTYPES = {"rmem_last_error": ctypes.c_char_p, "rmem_local_banded_elems": ctypes.c_int64}
 
 
 def declared_symbols():

@@ -118,13 +118,14 @@ int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_p
                      void* q_time, float* tpe_bias, int L, int C, void* stream) {
   return tpe_prepare_launch(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias, L, C, ST(stream));
 }
+int64_t rmem_local_banded_elems(int h, int w) { return static_cast<int64_t>(local_banded_elems(h, w)); }
 int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, int ld_rel,
-                           float* probs, int h, int w, void* stream) {
-  return local_scores_launch(q, k, rel_bias, ld_rel, probs, h, w, ST(stream));
+                           float* probs, void* banded, int h, int w, void* stream) {
+  return local_scores_launch(q, k, rel_bias, ld_rel, probs, banded, h, w, ST(stream));
 }
-int rmem_local_attn_aggregate(const float* probs, const void* v, const void* gate, void* out,
+int rmem_local_attn_aggregate(const void* banded, const void* v, const void* gate, void* out,
                               int h, int w, void* stream) {
-  return local_aggregate_launch(probs, v, gate, out, h, w, ST(stream));
+  return local_aggregate_launch(banded, v, gate, out, h, w, ST(stream));
 }
 int rmem_groupnorm_nhwc(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
                         int P, int C, int groups, int relu, void* workspace, void* stream) {

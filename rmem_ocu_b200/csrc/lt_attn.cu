@@ -205,6 +205,11 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       const int b = j & 1;
       mbar_wait(s_full + b, (j >> 1) & 1);
       tc_fence_after();
+#ifdef LT_EXP_NOSOFTMAX
+      tc_fence_before();
+      mbar_arrive(p_full + b);
+      continue;
+#endif
       uint32_t sr[64];
       {
         uint32_t(&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
@@ -214,6 +219,12 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         tmem_ld32(s_addr + 32, hi);
         tmem_ld_wait();
       }
+#ifdef LT_EXP_LDONLY
+      if (sr[0] == 0x12345678u && sr[63] == 0x9abcdef0u) l_sum += 1.f;
+      tc_fence_before();
+      mbar_arrive(p_full + b);
+      continue;
+#endif
       const int valid = key_len - j * kBlockN - hf * 64;   // valid columns in this half (may be <= 0)
       if (valid < 64) {                                       // warp-uniform: only the chunk's last tile
 #pragma unroll

@@ -58,9 +58,10 @@ int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* 
                        int L, int C, cudaStream_t stream);
 int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
                            cudaStream_t stream);
-int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, int h,
-                        int w, cudaStream_t stream);
-int local_aggregate_launch(const float* probs, const void* v, const void* gate, void* out, int h, int w,
+size_t local_banded_elems(int h, int w);
+int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
+                        int h, int w, cudaStream_t stream);
+int local_aggregate_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream);
 int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
                           int P, int C, int groups, int relu, void* workspace, cudaStream_t stream);

@@ -279,7 +279,8 @@ class _Workspace:
         self.qt, self.tpe_bias = z(L, 128), z(L, 4, dt=f32)
         self.gated_a, self.gated_b = z(L, 1024), z(L, 1024)
         self.dw = z(L, 2048)
-        self.rel, self.probs = z(L, 256, dt=f32), z(L, 225, dt=f32)
+        self.rel = z(L, 256, dt=f32)
+        self.banded = ops.local_banded_buffer(h, w, device)   # local-attention probabilities, banded per tile
         self.sa_qk, self.sa_v, self.sa_u = z(L, 128), z(L, 1024), z(L, 1024)
         n_chunks = max(T * _chunks_per_frame(T, L) for T in range(1, n_slots + 1))
         self.part_o = z(n_chunks, L, 1024, dt=f32)
@@ -472,8 +473,8 @@ class DeAOTEngine:
                                          ws.gated_a, mass)
             # short-term 15x15 local attention over the previous frame
             ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
-            ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, ws.probs, h, w)
-            ops.local_attn_aggregate(ws.probs, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
+            ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
+            ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
             # gate -> dw5x5 -> (projection_lt + projection_st) -> residual adds, one GEMM
             ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
             ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)

@@ -144,14 +144,21 @@ def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate,
     _count("rmem_lt_attn_deaot_combine")
 
 
-def local_attn_scores(q, k, rel_bias, probs, h, w):
-    _lib.check(_lib.lib().rmem_local_attn_scores(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs), h, w,
-                                                 _stream()), "rmem_local_attn_scores")
+def local_banded_buffer(h, w, device):
+    """Zero-filled bf16 buffer for the banded probabilities of one (h, w) token grid (zero-fill once: the
+    scores kernel only ever writes the in-window slots)."""
+    n = _lib.lib().rmem_local_banded_elems(h, w)
+    return torch.zeros(n, device=device, dtype=torch.bfloat16)
+
+
+def local_attn_scores(q, k, rel_bias, probs, banded, h, w):
+    _lib.check(_lib.lib().rmem_local_attn_scores(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs),
+                                                 _p(banded), h, w, _stream()), "rmem_local_attn_scores")
     _count("rmem_local_attn_scores")
 
 
-def local_attn_aggregate(probs, v, gate, out, h, w):
-    _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(probs), _p(v), _p(gate), _p(out), h, w, _stream()),
+def local_attn_aggregate(banded, v, gate, out, h, w):
+    _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(banded), _p(v), _p(gate), _p(out), h, w, _stream()),
                "rmem_local_attn_aggregate")
     _count("rmem_local_attn_aggregate")
 

@@ -85,8 +85,9 @@ def test_local_attention_vs_oracle(lib_built, h, w):
     ops.linear(qd, _bf(rel_w.view(225, 128)).cuda(), rel_b.cuda(), [(0, 225, ops.ACT_NONE, ops.OUT_F32, rel, 0)])
     probs = torch.empty(L, 225, device="cuda")
     out = torch.empty(L, 1024, device="cuda", dtype=torch.bfloat16)
-    ops.local_attn_scores(qd, kd, rel, probs, h, w)
-    ops.local_attn_aggregate(probs, vd, ud, out, h, w)
+    banded = ops.local_banded_buffer(h, w, "cuda")
+    ops.local_attn_scores(qd, kd, rel, probs, banded, h, w)
+    ops.local_attn_aggregate(banded, vd, ud, out, h, w)
     torch.cuda.synchronize()
     assert (probs.cpu() - probs_ref).abs().max().item() < 2e-3
     assert (probs.sum(1) - 1).abs().max().item() < 1e-4

@@ -108,8 +108,9 @@ def test_deaot_attention_operators_vs_reference(lib_built):
         ops.linear(q2, _bf(sd[p + "short_term_attn.relative_emb_k.weight"].reshape(225, 128)).to(dev),
                    sd[p + "short_term_attn.relative_emb_k.bias"].to(dev), [(0, 225, ops.ACT_NONE, ops.OUT_F32, rel, 0)])
         probs = torch.empty(L, 225, device=dev)
-        ops.local_attn_scores(q2, k2, rel, probs, h, w)
-        ops.local_attn_aggregate(probs, v2, u, gated, h, w)
+        banded = ops.local_banded_buffer(h, w, dev)
+        ops.local_attn_scores(q2, k2, rel, probs, banded, h, w)
+        ops.local_attn_aggregate(banded, v2, u, gated, h, w)
         out = tail(gated, "short_term_attn")
         torch.cuda.synchronize()
         assert (probs[::RS].cpu() - torch.from_numpy(g["st_%s_attn" % tag])).abs().max().item() < 5e-3, tag

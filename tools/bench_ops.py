@@ -70,8 +70,9 @@ v = [bf(L, 1024) for _ in range(NB)]
 u = [bf(L, 1024) for _ in range(NB)]
 rel = [f32(L, 256) * 0.1 for _ in range(NB)]
 probs = [torch.empty(L, 225, device=dev) for _ in range(NB)]
-timed("local scores", lambda i: ops.local_attn_scores(q[i], k[i], rel[i], probs[i], h, w))
-timed("local aggregate", lambda i: ops.local_attn_aggregate(probs[i], v[i], u[i], y[i], h, w))
+banded = [ops.local_banded_buffer(h, w, dev) for _ in range(NB)]
+timed("local scores", lambda i: ops.local_attn_scores(q[i], k[i], rel[i], None, banded[i], h, w))
+timed("local aggregate", lambda i: ops.local_attn_aggregate(banded[i], v[i], u[i], y[i], h, w))
 for T in (1, 5):
     from rmem_ocu_b200.engine import _chunks_per_frame
     cpf = _chunks_per_frame(T, L)
