@@ -283,6 +283,10 @@ int rmem_upsample_add_nhwc(const float* x, int hi, int wi, const float* a, const
 int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, const float* bias, float* pred,
                        int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, void* stream);
 
+/* Encoder input packing (AOT.encode_image front, networks/models/aot.py:116-119 + encoders/resnet.py:150-153):
+ * img f32 [3][H][W] -> out bf16 [H][W][8] channels-last, channels 3..7 zero. */
+int rmem_pack_image(const float* img, int H, int W, void* out, void* stream);
+
 /* label[i] = (f32) argmax_c logits[c][i], first maximum -- the evaluator's softmax + argmax over the object
  * channel (networks/managers/evaluator.py:430-441); logits f32 [C][HW], label f32 [HW]. */
 int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream);

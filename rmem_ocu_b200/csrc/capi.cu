@@ -139,6 +139,9 @@ int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, co
                        int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, void* stream) {
   return finish_logits_launch(conv, sc, sy, sx, bias, pred, C, Hs, Ws, n_valid, out, Ho, Wo, ST(stream));
 }
+int rmem_pack_image(const float* img, int H, int W, void* out, void* stream) {
+  return pack_image_launch(img, H, W, out, ST(stream));
+}
 int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream) {
   return argmax_label_launch(logits, C, HW, label, ST(stream));
 }

@@ -221,6 +221,28 @@ int finish_logits_launch(const float* conv, long long sc, long long sy, long lon
   return RMEM_OK;
 }
 
+// Encoder input: f32 planes [3][H][W] -> bf16 channels-last [H][W][8] with channels 3..7 zero (the padded first
+// convolution reads 8-channel pixels so the tensor-core conv kernels apply; the extra weights are zero).
+__global__ void __launch_bounds__(256)
+pack_image_kernel(const float* __restrict__ img, int HW, __nv_bfloat16* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= HW) return;
+  const __nv_bfloat162 a = __floats2bfloat162_rn(img[i], img[HW + i]);
+  const __nv_bfloat162 b = __floats2bfloat162_rn(img[2 * HW + i], 0.f);
+  uint4 pk;
+  pk.x = *reinterpret_cast<const uint32_t*>(&a);
+  pk.y = *reinterpret_cast<const uint32_t*>(&b);
+  pk.z = 0u; pk.w = 0u;
+  reinterpret_cast<uint4*>(out)[i] = pk;
+}
+
+int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t stream) {
+  if (H < 1 || W < 1) return set_error(RMEM_ERR_ARG, "pack_image: bad shape");
+  const int HW = H * W;
+  pack_image_kernel<<<(HW + 255) / 256, 256, 0, stream>>>(img, HW, static_cast<__nv_bfloat16*>(out));
+  return check_launch("pack_image_kernel");
+}
+
 // label[y][x] = argmax_c logits[c][y][x] (first maximum, like torch.argmax) as f32 -- the evaluator's
 // softmax + argmax (networks/managers/evaluator.py:430-441; softmax is monotone, so it is skipped).
 __global__ void __launch_bounds__(256)

@@ -44,20 +44,34 @@ __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
     cls_sh[ky][kx] = cls;
   }
   __syncthreads();
-  float acc = p.bias[c];
-  for (int ky = 0; ky < kIdK; ++ky) {
-    int run_start = 0;
-    int run_cls = cls_sh[ky][0];
+  // runs of equal labels per window row, found once per CTA (one thread per row) instead of by every channel
+  __shared__ short run_cls[kIdK][kIdK], run_lo[kIdK][kIdK], run_hi[kIdK][kIdK];
+  __shared__ int n_runs[kIdK];
+  if (threadIdx.x < kIdK) {
+    const int ky = threadIdx.x;
+    int n = 0, run_start = 0, rc = cls_sh[ky][0];
     for (int kx = 1; kx <= kIdK; ++kx) {
       const int cur = (kx < kIdK) ? cls_sh[ky][kx] : -2;
-      if (cur != run_cls) {
-        if (run_cls >= 0) {
-          const float* base = p.prefix + (static_cast<size_t>(run_cls) * kIdK + ky) * (kIdK + 1) * kIdC + c;
-          acc += base[kx * kIdC] - base[run_start * kIdC];
+      if (cur != rc) {
+        if (rc >= 0) {
+          run_cls[ky][n] = static_cast<short>(rc);
+          run_lo[ky][n] = static_cast<short>(run_start);
+          run_hi[ky][n] = static_cast<short>(kx);
+          ++n;
         }
         run_start = kx;
-        run_cls = cur;
+        rc = cur;
       }
+    }
+    n_runs[ky] = n;
+  }
+  __syncthreads();
+  float acc = p.bias[c];
+  for (int ky = 0; ky < kIdK; ++ky) {
+    const int n = n_runs[ky];
+    for (int r = 0; r < n; ++r) {
+      const float* base = p.prefix + (static_cast<size_t>(run_cls[ky][r]) * kIdK + ky) * (kIdK + 1) * kIdC + c;
+      acc += base[run_hi[ky][r] * kIdC] - base[run_lo[ky][r] * kIdC];
     }
   }
   float out = acc;

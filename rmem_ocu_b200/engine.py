@@ -206,8 +206,13 @@ class InferenceResNet:
 
     def _forward(self, img):
         n, c, h, w = img.shape
-        x = torch.zeros(n, 8, h, w, device=img.device, dtype=self.dtype).contiguous(memory_format=torch.channels_last)
-        x[:, :3] = img
+        if self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
+            x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
+            ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
+        else:
+            x = torch.zeros(n, 8, h, w, device=img.device, dtype=self.dtype).contiguous(
+                memory_format=torch.channels_last)
+            x[:, :3] = img
         if self.fused:
             x = self._conv(x, self.conv1, True)
         else:
@@ -268,10 +273,11 @@ class _Workspace:
         self.tgt, self.tgt_id = z(L, 256, dt=f32), z(L, 256, dt=f32)
         self.xn = z(L, 512)                                   # LayerNorm outputs (norm | id_norm)
         self.idcat = [z(L, 512) for _ in range(nl)]           # [curr_ID_V | id_emb] per layer
-        self.kcur = [z(L, 128) for _ in range(nl)]
-        self.vcur = [z(L, 1024) for _ in range(nl)]           # V | ID_V
-        self.kprev = [z(L, 128) for _ in range(nl)]           # short-term memory (previous frame)
-        self.vprev = [z(L, 1024) for _ in range(nl)]
+        # K and V | ID_V of a frame, two sets: the valid short-term memory (previous frame) and the set the
+        # current frame is written into; the write path completes ID_V in place and the roles swap (no copies)
+        self.kst = [[z(L, 128) for _ in range(nl)] for _ in range(2)]
+        self.vst = [[z(L, 1024) for _ in range(nl)] for _ in range(2)]
+        self.bind(0)
         self.kbank = [z(n_slots, L, 128) for _ in range(nl)]  # long-term bank
         self.vbank = [z(n_slots, L, 1024) for _ in range(nl)]
         self.u = [z(L, 1024) for _ in range(nl)]              # cat_curr_U
@@ -307,6 +313,15 @@ def _chunks_per_frame(T, L, n_sms=148):
         if best_cost is None or cost < best_cost:
             best, best_cost = cpf, cost
     return best
+
+
+def _ws_bind(ws, st):
+    """Point kprev / vprev at short-term set `st` and kcur / vcur at the other one."""
+    ws.kprev, ws.vprev = ws.kst[st], ws.vst[st]
+    ws.kcur, ws.vcur = ws.kst[1 - st], ws.vst[1 - st]
+
+
+_Workspace.bind = _ws_bind
 
 
 class DeAOTEngine:
@@ -369,6 +384,7 @@ class DeAOTEngine:
         self.enc_hw = None
         self.input_size_2d = None
         self.pred_id_logits = None if getattr(self, "ws", None) is None else self.ws.pred_logits
+        self.st = 0                # which K / V set holds the valid short-term memory (host mirror)
         self.T = 0                 # frames in the long-term bank (host mirror; deterministic)
         self.T_recorded = 0        # bank length when record_attn_weight was last written
         self.n_long_updates = 0
@@ -506,26 +522,27 @@ class DeAOTEngine:
         return ws.gn_out
 
     # ------------------------------------------------------------------ device work (graph-capturable)
-    def _read_body(self, img, img_embs, T, output_size):
-        """Everything match_propogate_one_frame puts on the stream; a pure function of (T, output_size)."""
+    def _read_body(self, img, img_embs, T, output_size, st):
+        """Everything match_propogate_one_frame puts on the stream; a pure function of (T, output_size, st)."""
+        self.ws.bind(st)
         ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device
         embs = self.encode_image(img) if img_embs is None else img_embs
         lstt_out = self._lstt_forward(embs[-1], False, True, T)
         return self._decode(embs, lstt_out, output_size)
 
-    def _write_body(self, label_hw, T, update_long, do_evict):
-        """Everything update_short_term_memory puts on the stream (transformer.py:826-991)."""
+    def _write_body(self, label_hw, T, update_long, do_evict, st):
+        """Everything update_short_term_memory puts on the stream (transformer.py:826-991).  The frame's K and
+        V already sit in the "current" set; fusing ID_V into it completes the new short-term memory, and the
+        caller swaps the roles of the two sets afterwards."""
         ws = self.ws
+        ws.bind(st)
         self._id_embed(label_hw)
         for i in range(self.prep.num_layers):
-            # short-term memory <- this frame's K, V and the freshly fused ID_V
-            ws.kprev[i].copy_(ws.kcur[i])
-            ws.vprev[i][:, :512].copy_(ws.vcur[i][:, :512])
-            self._id_value(i, ws.vprev[i])
+            self._id_value(i, ws.vcur[i])
         if update_long:
             srcs, dsts = [], []
             for i in range(self.prep.num_layers):
-                srcs += [ws.kprev[i], ws.vprev[i]]
+                srcs += [ws.kcur[i], ws.vcur[i]]
                 dsts += [ws.kbank[i], ws.vbank[i]]
             ops.bank_append(ws.bank_state, T, -1, srcs, dsts)           # frame id from the device counter
             if do_evict:
@@ -598,10 +615,14 @@ class DeAOTEngine:
         return len(self._graphs) - len(saved)
 
     def _variants(self, T, output_size, img, label):
-        yield (("read", T, output_size), lambda x, T=T: self._read_body(x, None, T, output_size), [img])
-        yield (("write", T, False, False), lambda m, T=T: self._write_body(m, T, False, False), [label])
         ev = self.deaot or T + 1 > self.capacity
-        yield (("write", T, True, ev), lambda m, T=T, ev=ev: self._write_body(m, T, True, ev), [label])
+        for st in ((0, 1) if self.deaot else (0,)):
+            yield (("read", T, output_size, st), lambda x, T=T, st=st: self._read_body(x, None, T, output_size, st),
+                   [img])
+            yield (("write", T, False, False, st), lambda m, T=T, st=st: self._write_body(m, T, False, False, st),
+                   [label])
+            yield (("write", T, True, ev, st), lambda m, T=T, ev=ev, st=st: self._write_body(m, T, True, ev, st),
+                   [label])
 
     # ------------------------------------------------------------------ public frame API
     def add_reference_frame(self, img=None, mask=None, frame_step=-1, obj_nums=None, img_embs=None):
@@ -624,6 +645,8 @@ class DeAOTEngine:
         self._id_embed(label)
         ops.bank_init(self.ws.bank_state, self.frame_step)
         self.T = 1
+        self.st = 0
+        self.ws.bind(0)
         lstt_out = self._lstt_forward(curr_enc_embs[-1], True, False, 1)
         self.last_mem_step = frame_step
         self._decode(curr_enc_embs, lstt_out, None)
@@ -636,9 +659,10 @@ class DeAOTEngine:
         T = self.T
         self.T_recorded = T
         osz = tuple(output_size) if output_size is not None else None
+        st = self.st
         if img_embs is not None:
-            return self._read_body(None, img_embs, T, osz)
-        return self._run(("read", T, osz), lambda x: self._read_body(x, None, T, osz), [img])
+            return self._read_body(None, img_embs, T, osz, st)
+        return self._run(("read", T, osz, st), lambda x: self._read_body(x, None, T, osz, st), [img])
 
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
         emb = curr_lstt_embs[-1] if isinstance(curr_lstt_embs, (list, tuple)) else curr_lstt_embs
@@ -657,8 +681,11 @@ class DeAOTEngine:
         do_evict = update_long and (self.deaot or T + 1 > self.capacity)
         if do_evict and self.T_recorded != T:
             raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
-        self._run(("write", T, update_long, do_evict),
-                  lambda m: self._write_body(m, T, update_long, do_evict), [label])
+        st = self.st
+        self._run(("write", T, update_long, do_evict, st),
+                  lambda m: self._write_body(m, T, update_long, do_evict, st), [label])
+        if self.deaot:
+            self.st = 1 - st                                      # the set just completed is the short-term memory now
         if update_long:
             self.T = min(T + 1, self.capacity)
             self.n_long_updates += 1

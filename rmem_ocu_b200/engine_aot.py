@@ -137,6 +137,9 @@ class WorkspaceAOT:
         self.zero_order = z(1, dt=torch.int32)
         self.pred_logits = None
 
+    def bind(self, st):
+        pass
+
 
 def mha_chunks_per_frame(T, L, n_sms=148):
     """Split-KV granularity of the multi-head attention grid (q tiles x 4 head pairs x T x cpf CTAs, one CTA
@@ -230,8 +233,9 @@ class AOTBodies:
             tr.setdefault("layers", []).append(dict(
                 curr_Q=ws.kcur[i].float().cpu(), tgt3=mem[:, 512:].float().cpu(), tgt=ws.tgt.cpu().clone()))
 
-    def _write_body(self, label_hw, T, update_long, do_evict):
-        """update_short_memories + update_long_term_memory + restrict_long_memories (transformer.py:269-436)."""
+    def _write_body(self, label_hw, T, update_long, do_evict, st=0):
+        """update_short_memories + update_long_term_memory + restrict_long_memories (transformer.py:269-436).
+        (`st` is the DeAOT workspace's double-buffer index; the AOT short-term memory is produced by a GEMM.)"""
         ws = self.ws
         A, BF = ops.ACT_NONE, ops.OUT_BF16
         self._id_embed(label_hw)

@@ -108,6 +108,16 @@ def finish_logits(conv, bias, pred, n_valid, out=None):
     LAUNCHES += 2 if out is not None else 1
 
 
+def pack_image(img, out):
+    """img f32 [1, 3, H, W] contiguous -> out bf16 [1, 8, H, W] channels-last (channels 3..7 zero)."""
+    _chk_cuda(img, out)
+    if not img.is_contiguous():
+        img = img.contiguous()
+    H, W = img.shape[-2:]
+    _lib.check(_lib.lib().rmem_pack_image(_p(img), H, W, _p(out), _stream()), "rmem_pack_image")
+    _count("rmem_pack_image")
+
+
 def argmax_label(logits, label=None):
     """logits f32 [1, C, H, W] contiguous -> label f32 [1, 1, H, W] (argmax over the object channel)."""
     _chk_cuda(logits)

@@ -246,3 +246,14 @@ def test_decoder_head_vs_oracle(lib_built):
     out = conv + bias.view(1, -1, 1, 1)
     torch.cuda.synchronize()
     assert _rel(out.cpu(), ref) < 1e-4
+
+
+def test_pack_image(lib_built):
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(13)
+    img = torch.randn(1, 3, 37, 53, device="cuda")
+    out = torch.empty(1, 8, 37, 53, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ops.pack_image(img, out)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, :3], img.to(torch.bfloat16))
+    assert (out[:, 3:] == 0).all()
