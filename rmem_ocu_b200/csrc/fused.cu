@@ -2,6 +2,7 @@
 // coalesced): LayerNorm (dual stream, bf16 out at a column offset), 5x5 depth-wise conv over the
 // token grid, token GroupNorm, TPE query preparation, foreground probability for the eviction rule.
 #include <cuda_bf16.h>
+#include "sm100_ptx.cuh"
 #include "rmem_internal.h"
 
 namespace rmem {
@@ -85,11 +86,16 @@ int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0,
 }
 
 // ------------------------------------------------------------------------------------------------
-// 5x5 depth-wise conv, channels-last.  Thread = (channel pair, pixel row, strip of kDwStrip pixels): the 25
-// weights of its two channels and a sliding 5x5 window live in registers, so every output costs five
-// new 4-byte loads (coalesced: consecutive lanes = consecutive channel pairs) and 25 packed f32x2 FMAs.
-// Weights tap-major [25][C].
-constexpr int kDwStrip = 6;
+// 5x5 depth-wise conv over the (h, w) token grid, channels-last bf16, zero padding 2.
+// CTA = (band of kDwRows token rows, 64 channels): one TMA box brings the band plus its 2-pixel halo into
+// shared memory -- rows / columns outside the image are zero-filled by the TMA unit, which IS the padding --
+// so the global-memory latency is paid once per CTA.  Thread = (channel pair, group of columns): the 25
+// weights of its two channels live in registers and a 5x5 window slides along each row, so an output costs
+// five 4-byte shared-memory loads (conflict-free: consecutive lanes = consecutive channel pairs) and 25
+// packed f32x2 FMAs.  Weights tap-major [25][C].
+constexpr int kDwRows = 2;          // output rows per CTA
+constexpr int kDwCh = 64;           // channels per CTA (128-byte rows in shared memory)
+constexpr int kDwThreads = 256;     // 32 channel pairs x 8 column groups
 
 __device__ __forceinline__ void fma2(float2& d, const float2 a, const float2 b) {
   asm("{\n\t.reg .b64 ra, rb, rc;\n\t"
@@ -100,56 +106,99 @@ __device__ __forceinline__ void fma2(float2& d, const float2 a, const float2 b) 
       : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
 }
 
-__global__ void __launch_bounds__(128)
-dwconv5_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int xcol0, const float* __restrict__ wt,
-               __nv_bfloat16* __restrict__ y, int ldy, int ycol0, int h, int w, int C) {
-  const int c = (blockIdx.z * 128 + threadIdx.x) * 2;
-  if (c >= C) return;
-  const int py = blockIdx.y;
-  const int x0 = blockIdx.x * kDwStrip;
+__global__ void __launch_bounds__(kDwThreads)
+dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict__ wt,
+               __nv_bfloat16* __restrict__ y, int ldy, int ycol0, int h, int w, int C, int box_w) {
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(dw_smem);
+  const uint8_t* tile = dw_smem + 128;                         // [kDwRows + 4][box_w][64 ch] bf16
+  const int y0 = blockIdx.x * kDwRows;
+  const int c0 = blockIdx.y * kDwCh;
+  if (threadIdx.x == 0) {
+    sm100::tma_prefetch_desc(&tm_x);
+    sm100::mbar_init(bar, 1);
+    sm100::mbar_fence_init();
+    sm100::mbar_expect_tx(bar, static_cast<uint32_t>((kDwRows + 4) * box_w * kDwCh * 2));
+    sm100::tma_load_3d(dw_smem + 128, &tm_x, bar, c0, -2, y0 - 2);
+  }
+  const int cp = threadIdx.x & 31;              // channel pair inside the CTA's 64 channels
+  const int grp = threadIdx.x >> 5;             // column group
+  const int c = c0 + 2 * cp;
   float2 wgt[25];
 #pragma unroll
   for (int t = 0; t < 25; ++t) wgt[t] = *reinterpret_cast<const float2*>(wt + t * C + c);
-  const __nv_bfloat16* xc = x + xcol0 + c;
-  auto ld = [&](int yy, int xx) -> float2 {
-    if (yy < 0 || yy >= h || xx < 0 || xx >= w) return make_float2(0.f, 0.f);
-    const uint32_t raw = *reinterpret_cast<const uint32_t*>(xc + static_cast<size_t>(yy * w + xx) * ldx);
+  const int per = (w + 7) / 8;                  // columns per group
+  const int xa = grp * per, xb = min(xa + per, w);
+  __syncthreads();                              // barrier init visible
+  sm100::mbar_wait(bar, 0);
+  auto ld = [&](int ry, int sx) -> float2 {     // ry: tile row (0 = y0 - 2), sx: tile column (0 = x = -2)
+    const uint32_t raw = *reinterpret_cast<const uint32_t*>(tile + (static_cast<size_t>(ry) * box_w + sx) * 128 + cp * 4);
     return make_float2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
   };
-  float2 win[5][5];        // win[dy][k]: input at (py + dy - 2, xx + k - 2)
+#pragma unroll 1
+  for (int r = 0; r < kDwRows; ++r) {
+    const int py = y0 + r;
+    if (py >= h || xa >= xb) break;
+    // col[slot][dy]: window column; output j of a chunk of five uses slots (j + k) % 5 for tap column k and
+    // loads its new rightmost column into slot (j + 4) % 5 -- static indices, so the window never moves.
+    float2 col[5][5];
 #pragma unroll
-  for (int dy = 0; dy < 5; ++dy) {
-    win[dy][0] = make_float2(0.f, 0.f);
+    for (int k = 0; k < 4; ++k) {
 #pragma unroll
-    for (int k = 1; k < 5; ++k) win[dy][k] = ld(py + dy - 2, x0 + k - 3);
-  }
+      for (int dy = 0; dy < 5; ++dy) col[k][dy] = ld(r + dy, xa + k);
+    }
+#pragma unroll 1
+    for (int xc = xa; xc < xb; xc += 5) {
 #pragma unroll
-  for (int i = 0; i < kDwStrip; ++i) {
-    const int xx = x0 + i;
-    if (xx < w) {
-      float2 acc = make_float2(0.f, 0.f);
+      for (int j = 0; j < 5; ++j) {
+        const int xx = xc + j;
+        if (xx < xb) {
 #pragma unroll
-      for (int dy = 0; dy < 5; ++dy) {
+          for (int dy = 0; dy < 5; ++dy) col[(j + 4) % 5][dy] = ld(r + dy, xx + 4);
+          float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) win[dy][k] = win[dy][k + 1];
-        win[dy][4] = ld(py + dy - 2, xx + 2);
+          for (int dy = 0; dy < 5; ++dy) {
 #pragma unroll
-        for (int k = 0; k < 5; ++k) fma2(acc, win[dy][k], wgt[dy * 5 + k]);
+            for (int k = 0; k < 5; ++k) fma2(acc, col[(j + k) % 5][dy], wgt[dy * 5 + k]);
+          }
+          const __nv_bfloat162 o = __floats2bfloat162_rn(acc.x, acc.y);
+          *reinterpret_cast<__nv_bfloat162*>(y + static_cast<size_t>(py * w + xx) * ldy + ycol0 + c) = o;
+        }
       }
-      const __nv_bfloat162 o = __floats2bfloat162_rn(acc.x, acc.y);
-      *reinterpret_cast<__nv_bfloat162*>(y + static_cast<size_t>(py * w + xx) * ldy + ycol0 + c) = o;
     }
   }
 }
 
 int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
                    int h, int w, int C, cudaStream_t stream) {
-  if ((C % 8) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1)
-    return set_error(RMEM_ERR_ARG, "dwconv5: C / ld / col offsets must be multiples of 8");
-  dim3 grid((w + kDwStrip - 1) / kDwStrip, h, (C + 255) / 256);
-  dwconv5_kernel<<<grid, 128, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(x), ldx, xcol0, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0,
-      h, w, C);
+  if ((C % kDwCh) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1 || w + 4 > 256)
+    return set_error(RMEM_ERR_ARG, "dwconv5: C must be a multiple of 64, ld / col offsets multiples of 8, w <= 252");
+  auto fn = get_tensor_map_encoder();
+  if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
+  const int box_w = w + 4;
+  CUtensorMap tm_x;
+  {
+    const uint64_t dims[3] = {static_cast<uint64_t>(C), static_cast<uint64_t>(w), static_cast<uint64_t>(h)};
+    const uint64_t strides[2] = {static_cast<uint64_t>(ldx) * 2, static_cast<uint64_t>(w) * ldx * 2};
+    const uint32_t box[3] = {kDwCh, static_cast<uint32_t>(box_w), kDwRows + 4};
+    const uint32_t es[3] = {1, 1, 1};
+    const void* base = static_cast<const __nv_bfloat16*>(x) + xcol0;
+    CUresult r = fn(&tm_x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (dwconv5) failed");
+  }
+  const size_t smem = 128 + static_cast<size_t>(kDwRows + 4) * box_w * kDwCh * 2;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(dwconv5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return set_cuda_error(e, "dwconv5: cudaFuncSetAttribute");
+    smem_set = smem;
+  }
+  dim3 grid((h + kDwRows - 1) / kDwRows, C / kDwCh);
+  dwconv5_kernel<<<grid, kDwThreads, smem, stream>>>(tm_x, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0, h, w,
+                                                     C, box_w);
   return check_launch("dwconv5_kernel");
 }
 
