@@ -287,6 +287,16 @@ int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, co
  * img f32 [3][H][W] -> out bf16 [H][W][8] channels-last, channels 3..7 zero. */
 int rmem_pack_image(const float* img, int H, int W, void* out, void* stream);
 
+/* Encoder input packing for the space-to-depth form of the stem convolution (resnet.py:150-151: the 7x7 stride-2
+ * conv on 3 channels == a 4x4 stride-1 conv on the 2x2 space-to-depth image): img f32 [3][H][W] -> out bf16
+ * channels-last [Hs+3][Ws+3][16], Hs = (H+1)/2, Ws = (W+1)/2, out[y'+2][x'+2][(dy*2+dx)*3+c] = img[c][2y'+dy][2x'+dx],
+ * zero elsewhere (conv padding, out-of-image pixels, channels 12..15). */
+int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream);
+
+/* Encoder stem max-pool, MaxPool2d(kernel 3, stride 2, padding 1) (networks/encoders/resnet.py:154):
+ * x bf16 channels-last [H][W][C] -> y bf16 [(H-1)/2+1][(W-1)/2+1][C]; C a multiple of 8. */
+int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, void* y, void* stream);
+
 /* label[i] = (f32) argmax_c logits[c][i], first maximum -- the evaluator's softmax + argmax over the object
  * channel (networks/managers/evaluator.py:430-441); logits f32 [C][HW], label f32 [HW]. */
 int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream);

@@ -142,6 +142,12 @@ int rmem_finish_logits(const float* conv, int64_t sc, int64_t sy, int64_t sx, co
 int rmem_pack_image(const float* img, int H, int W, void* out, void* stream) {
   return pack_image_launch(img, H, W, out, ST(stream));
 }
+int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream) {
+  return pack_image_s2d_launch(img, H, W, out, ST(stream));
+}
+int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, void* y, void* stream) {
+  return maxpool3s2_nhwc_launch(x, H, W, C, y, ST(stream));
+}
 int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream) {
   return argmax_label_launch(logits, C, HW, label, ST(stream));
 }

@@ -243,6 +243,90 @@ int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t st
   return check_launch("pack_image_kernel");
 }
 
+// Encoder input for the space-to-depth form of the stem: the 7x7 stride-2 convolution on 3 channels equals a 4x4
+// stride-1 convolution on the 2x2 space-to-depth image (12 channels, padded to 16), which the tensor-core
+// convolution kernels run ~4x faster than the 8-channel strided form.  f32 planes [3][H][W] -> bf16 channels-last
+// [Hs+3][Ws+3][16], Hs = ceil(H/2): out[y'+2][x'+2][(dy*2+dx)*3+c] = img[c][2y'+dy][2x'+dx]; the two leading / one
+// trailing border rows and columns (the convolution's padding), out-of-image pixels and channels 12..15 are zero.
+__global__ void __launch_bounds__(256)
+pack_image_s2d_kernel(const float* __restrict__ img, int H, int W, int Hs, int Ws, __nv_bfloat16* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int Wp = Ws + 3;
+  if (i >= (Hs + 3) * Wp) return;
+  const int yp = i / Wp - 2, xp = i % Wp - 2;
+  float v[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) v[k] = 0.f;
+  if (yp >= 0 && yp < Hs && xp >= 0 && xp < Ws) {
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int y = 2 * yp + dy, x = 2 * xp + dx;
+        if (y < H && x < W) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) v[(dy * 2 + dx) * 3 + c] = img[(static_cast<size_t>(c) * H + y) * W + x];
+        }
+      }
+    }
+  }
+  uint4 pk[2];
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+  reinterpret_cast<uint4*>(out)[2 * i] = pk[0];
+  reinterpret_cast<uint4*>(out)[2 * i + 1] = pk[1];
+}
+
+int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream) {
+  if (H < 1 || W < 1) return set_error(RMEM_ERR_ARG, "pack_image_s2d: bad shape");
+  const int Hs = (H + 1) / 2, Ws = (W + 1) / 2;
+  const int n = (Hs + 3) * (Ws + 3);
+  pack_image_s2d_kernel<<<(n + 255) / 256, 256, 0, stream>>>(img, H, W, Hs, Ws, static_cast<__nv_bfloat16*>(out));
+  return check_launch("pack_image_s2d_kernel");
+}
+
+// Encoder stem max-pool (encoders/resnet.py:154, MaxPool2d(3, stride 2, padding 1)) on bf16 channels-last
+// [H][W][C] -> [Ho][Wo][C]: one thread per output pixel and 8-channel group, 128-bit loads and stores.
+__global__ void __launch_bounds__(256)
+maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8, __nv_bfloat16* __restrict__ y,
+                       int Ho, int Wo) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Ho * Wo * C8) return;
+  const int c8 = i % C8, pix = i / C8;
+  const int ox = pix % Wo, oy = pix / Wo;
+  const __nv_bfloat162 ninf = __floats2bfloat162_rn(-INFINITY, -INFINITY);
+  __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
+#pragma unroll
+  for (int dy = 0; dy < 3; ++dy) {
+    const int iy = 2 * oy - 1 + dy;
+    if (iy < 0 || iy >= H) continue;
+#pragma unroll
+    for (int dx = 0; dx < 3; ++dx) {
+      const int ix = 2 * ox - 1 + dx;
+      if (ix < 0 || ix >= W) continue;
+      const uint4 v = *reinterpret_cast<const uint4*>(x + (static_cast<size_t>(iy) * W + ix) * (C8 * 8) + c8 * 8);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) m[e] = __hmax2(m[e], h[e]);
+    }
+  }
+  uint4 o;
+  __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) oh[e] = m[e];
+  *reinterpret_cast<uint4*>(y + static_cast<size_t>(pix) * (C8 * 8) + c8 * 8) = o;
+}
+
+int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, void* y, cudaStream_t stream) {
+  if (H < 1 || W < 1 || C < 8 || (C & 7)) return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const int n = Ho * Wo * (C / 8);
+  maxpool3s2_nhwc_kernel<<<(n + 255) / 256, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), H, W, C / 8,
+                                                                static_cast<__nv_bfloat16*>(y), Ho, Wo);
+  return check_launch("maxpool3s2_nhwc_kernel");
+}
+
 // label[y][x] = argmax_c logits[c][y][x] (first maximum, like torch.argmax) as f32 -- the evaluator's
 // softmax + argmax (networks/managers/evaluator.py:430-441; softmax is monotone, so it is skipped).
 __global__ void __launch_bounds__(256)

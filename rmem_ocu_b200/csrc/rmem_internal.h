@@ -70,6 +70,8 @@ int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, c
 int finish_logits_launch(const float* conv, long long sc, long long sy, long long sx, const float* bias, float* pred,
                          int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream);
 int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
+int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
+int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, void* y, cudaStream_t stream);
 int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream);
 int bank_tick_launch(void* state, cudaStream_t stream);
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,

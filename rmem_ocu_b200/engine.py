@@ -120,6 +120,10 @@ class InferenceFPN:
                             f(sd[prefix + name + ".gn.weight"]), f(sd[prefix + name + ".gn.bias"]))
         for name in ("adapter_16x", "adapter_8x", "adapter_4x", "conv_out"):
             self.w[name] = (cl(sd[prefix + name + ".weight"]), f(sd[prefix + name + ".bias"]))
+        # the 1x1 adapters read the encoder's bf16 feature maps: as [Cout, Cin] bf16 matrices they run on the
+        # tcgen05 GEMM straight off those maps (no f32 copies of the shortcuts, no f32 convolution)
+        self.wb = {name: _bf(sd[prefix + name + ".weight"].reshape(sd[prefix + name + ".weight"].shape[0], -1), device)
+                   for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
         self.gn_ws = torch.zeros(16, device=device, dtype=torch.float64)
 
     @staticmethod
@@ -139,17 +143,25 @@ class InferenceFPN:
     def _up_add(self, x, shortcut, name):
         """adapter(shortcut) + bias + bilinear(x) (identity resample when the sizes agree)."""
         w, b = self.w[name]
-        a = F.conv2d(shortcut, w, None).contiguous(memory_format=torch.channels_last)
+        if shortcut.dtype == BF16:
+            shortcut = shortcut.contiguous(memory_format=torch.channels_last)
+            ho, wo = shortcut.shape[-2:]
+            a = torch.empty(1, ho, wo, w.shape[0], device=x.device, dtype=torch.float32).permute(0, 3, 1, 2)
+            ta = self._tok(a)
+            ops.linear(self._tok(shortcut), self.wb[name], b, [(0, w.shape[0], ops.ACT_NONE, ops.OUT_F32, ta, 0)])
+            b = None                                                                # added by the GEMM epilogue
+        else:
+            a = F.conv2d(shortcut.float(), w, None).contiguous(memory_format=torch.channels_last)
+            ta = self._tok(a)
         hi, wi = x.shape[-2:]
         ho, wo = a.shape[-2:]
-        ta = self._tok(a)
         ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b)     # in place
         return a
 
     def __call__(self, inputs, shortcuts):
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
         x = x.float().contiguous(memory_format=torch.channels_last)
-        sc = [s.float().contiguous(memory_format=torch.channels_last) for s in shortcuts]
+        sc = shortcuts
         x = self._conv_gn_relu(x, "conv_in")
         x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x"), "conv_16x")
         x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x"), "conv_8x")
@@ -175,6 +187,22 @@ class InferenceResNet:
         w1p[:, :3] = w1
         self.conv1 = (w1p.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
                       enc.conv1.bias.detach().to(device=device, dtype=dtype), enc.conv1.stride, enc.conv1.padding)
+        # space-to-depth form of the stem (exact algebra): out[y,x] = sum_{a,b in -2..1} sum_{dy,dx,c}
+        # W[c][2a+dy+3][2b+dx+3] X[c][2(y+a)+dy][2(x+b)+dx] -- a 4x4 stride-1 conv over 12 (padded to 16) channels
+        # of the 2x2 space-to-depth image that ops.pack_image_s2d writes (with the zero border built in)
+        self.conv1_s2d = None
+        if tuple(w1.shape[1:]) == (3, 7, 7) and tuple(enc.conv1.stride) == (2, 2) and tuple(enc.conv1.padding) == (3, 3):
+            ws = torch.zeros(w1.shape[0], 16, 4, 4)
+            for dy in range(2):
+                for dx in range(2):
+                    ch = (dy * 2 + dx) * 3
+                    for a in range(-2, 2):
+                        for b in range(-2, 2):
+                            i, j = 2 * a + dy + 3, 2 * b + dx + 3
+                            if 0 <= i < 7 and 0 <= j < 7:
+                                ws[:, ch:ch + 3, a + 2, b + 2] = w1[:, :, i, j]
+            self.conv1_s2d = (ws.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
+                              self.conv1[1], (1, 1), (0, 0))
         self.blocks = []
         for li in (1, 2, 3):
             stage = []
@@ -206,18 +234,31 @@ class InferenceResNet:
 
     def _forward(self, img):
         n, c, h, w = img.shape
-        if self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
+        s2d = (self.dtype == BF16 and n == 1 and img.dtype == torch.float32 and self.fused
+               and self.conv1_s2d is not None)
+        if s2d:
+            x = torch.empty(1, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device, dtype=BF16).permute(0, 3, 1, 2)
+            ops.pack_image_s2d(img, x)              # f32 planes -> bf16 space-to-depth image, conv padding built in
+        elif self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
             x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
             ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
         else:
             x = torch.zeros(n, 8, h, w, device=img.device, dtype=self.dtype).contiguous(
                 memory_format=torch.channels_last)
             x[:, :3] = img
-        if self.fused:
+        if s2d:
+            x = self._conv(x, self.conv1_s2d, True)
+        elif self.fused:
             x = self._conv(x, self.conv1, True)
         else:
             x = F.relu(F.conv2d(x, self.conv1[0], self.conv1[1], self.conv1[2], self.conv1[3]))
-        x = F.max_pool2d(x, 3, 2, 1)
+        if self.dtype == BF16 and n == 1:
+            pooled = torch.empty(1, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
+                                 device=x.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
+            ops.maxpool3s2_nhwc(x.contiguous(memory_format=torch.channels_last), pooled)
+            x = pooled
+        else:
+            x = F.max_pool2d(x, 3, 2, 1)
         xs = []
         for stage in self.blocks:
             for (c1, c2, c3, down) in stage:

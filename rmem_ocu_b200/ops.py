@@ -118,6 +118,28 @@ def pack_image(img, out):
     _count("rmem_pack_image")
 
 
+def pack_image_s2d(img, out):
+    """img f32 [1, 3, H, W] contiguous -> out bf16 [1, 16, (H+1)//2+3, (W+1)//2+3] channels-last: the 2x2
+    space-to-depth image with the stem convolution's zero padding built in (see include/rmem_b200.h)."""
+    _chk_cuda(img, out)
+    if not img.is_contiguous():
+        img = img.contiguous()
+    H, W = img.shape[-2:]
+    _lib.check(_lib.lib().rmem_pack_image_s2d(_p(img), H, W, _p(out), _stream()), "rmem_pack_image_s2d")
+    _count("rmem_pack_image_s2d")
+
+
+def maxpool3s2_nhwc(x, out):
+    """x bf16 [1, C, H, W] channels-last -> out bf16 [1, C, (H-1)//2+1, (W-1)//2+1] channels-last:
+    MaxPool2d(3, 2, 1) of the encoder stem."""
+    _chk_cuda(x, out)
+    n, C, H, W = x.shape
+    if n != 1 or x.dtype != torch.bfloat16 or not x.is_contiguous(memory_format=torch.channels_last):
+        raise ValueError("maxpool3s2_nhwc: expects one bf16 channels-last image")
+    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc(_p(x), H, W, C, _p(out), _stream()), "rmem_maxpool3s2_nhwc")
+    _count("rmem_maxpool3s2_nhwc")
+
+
 def argmax_label(logits, label=None):
     """logits f32 [1, C, H, W] contiguous -> label f32 [1, 1, H, W] (argmax over the object channel)."""
     _chk_cuda(logits)

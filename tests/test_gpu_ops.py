@@ -248,6 +248,29 @@ def test_decoder_head_vs_oracle(lib_built):
     assert _rel(out.cpu(), ref) < 1e-4
 
 
+def test_decoder_head_bf16_shortcuts(lib_built):
+    """Production form of the head: the encoder's feature maps arrive in bf16 and the three 1x1 adapters run on
+    the tcgen05 GEMM (bf16 weights, f32 accumulate).  Against the oracle on the same bf16-rounded inputs."""
+    from oracle import restate as R
+    from rmem_ocu_b200.engine import InferenceFPN
+    from tests import _synth
+    _, sd = _synth.models(2)
+    torch.manual_seed(11)
+    h, w = 15, 27
+    embs = [_bf(torch.randn(1, 256, 4 * h, 4 * w)), _bf(torch.randn(1, 512, 2 * h, 2 * w)),
+            _bf(torch.randn(1, 1024, h, w)), _bf(torch.randn(1, 256, h, w))]
+    lstt = _bf(torch.randn(1, 512, h, w))
+    with torch.no_grad():
+        ref = R.fpn_decoder([embs[-1].float(), lstt.float()], [e.float() for e in embs], sd, intermediate=False)
+    fpn = InferenceFPN(sd, torch.device("cuda"), intermediate=False)
+    cl = lambda t: t.cuda().contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        conv, bias = fpn([cl(embs[-1]), cl(lstt)], [cl(e) for e in embs])
+    out = conv + bias.view(1, -1, 1, 1)
+    torch.cuda.synchronize()
+    assert _rel(out.cpu(), ref) < 5e-3          # bf16 adapter weights + TF32 cuDNN convolutions
+
+
 def test_pack_image(lib_built):
     from rmem_ocu_b200 import ops
     torch.manual_seed(13)
@@ -257,3 +280,48 @@ def test_pack_image(lib_built):
     torch.cuda.synchronize()
     assert torch.equal(out[:, :3], img.to(torch.bfloat16))
     assert (out[:, 3:] == 0).all()
+
+
+@pytest.mark.parametrize("C,H,W", [(64, 240, 432), (64, 241, 433), (8, 5, 7)])
+def test_maxpool3s2_nhwc(lib_built, C, H, W):
+    """Encoder stem MaxPool2d(3, 2, 1) on bf16 channels-last: bit-exact against torch (a max is exact)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(5)
+    x = torch.randn(1, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    ref = F.max_pool2d(x.float(), 3, 2, 1).to(torch.bfloat16)
+    out = torch.empty_like(ref).contiguous(memory_format=torch.channels_last)
+    ops.maxpool3s2_nhwc(x, out)
+    assert torch.equal(out, ref)
+
+
+@pytest.mark.parametrize("H,W", [(480, 864), (481, 865), (37, 54)])
+def test_pack_image_s2d_and_stem_equivalence(lib_built, H, W):
+    """Space-to-depth packing is bit-exact against a torch construction, and the 4x4 stride-1 convolution on it
+    equals the reference's 7x7 stride-2 stem convolution (encoders/resnet.py:150-151) on the same bf16 inputs."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import InferenceResNet
+    from rmem_ocu_b200.model import DeAOTModel, RMemConfig, deterministic_init_
+    torch.manual_seed(17)
+    img = torch.randn(1, 3, H, W, device="cuda")
+    Hs, Ws = (H + 1) // 2, (W + 1) // 2
+    out = torch.empty(1, Hs + 3, Ws + 3, 16, device="cuda", dtype=torch.bfloat16).permute(0, 3, 1, 2)
+    ops.pack_image_s2d(img, out)
+    ref = torch.zeros(1, 16, Hs + 3, Ws + 3, device="cuda")
+    for dy in range(2):
+        for dx in range(2):
+            sub = img[:, :, dy::2, dx::2]
+            ch = (dy * 2 + dx) * 3
+            ref[:, ch:ch + 3, 2:2 + sub.shape[2], 2:2 + sub.shape[3]] = sub
+    assert torch.equal(out.float(), ref.to(torch.bfloat16).float())
+    m = DeAOTModel(RMemConfig(latter_mem_len=1))
+    deterministic_init_(m.state_dict(), 3)
+    enc = InferenceResNet(m.encoder, m.encoder_projector, torch.device("cuda"))
+    assert enc.conv1_s2d is not None
+    w8, b8, stride, pad = enc.conv1
+    with torch.no_grad():
+        y_s2d = F.relu(F.conv2d(out.float(), enc.conv1_s2d[0].float(), enc.conv1_s2d[1].float()))
+        x8 = torch.zeros(1, 8, H, W, device="cuda")
+        x8[:, :3] = img.to(torch.bfloat16).float()
+        y_ref = F.relu(F.conv2d(x8, w8.float(), b8.float(), stride, pad))
+    assert y_s2d.shape == y_ref.shape
+    assert _rel(y_s2d, y_ref) < 1e-5
