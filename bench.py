@@ -197,6 +197,13 @@ def kernel_rooflines(dev):
         with open(pk) as f:
             j = json.load(f)
         peaks = {"hbm_gbs": j["hbm_gbs"], "bf16_tflops": j["bf16_tflops"], "src": "measured"}
+    # per-launch DRAM traffic and tensor-pipe utilisation of the same kernels from the committed `ncu --set full`
+    # capture of `bench.py --kernel-only` (tools/ncu_summary.py -> profiles/ncu_headline.json); never measured here
+    ncu = {}
+    nj = os.path.join(ROOT, "profiles", "ncu_headline.json")
+    if os.path.exists(nj):
+        with open(nj) as f:
+            ncu = json.load(f)
     h, w = H // 16, W // 16
     L, T = h * w, LATTER + 1
     ncopy, iters = 6, 30
@@ -235,6 +242,13 @@ def kernel_rooflines(dev):
     lt = {"bound": "tensor", "achieved": flops / t_lt / 1e12, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
           "frac": flops / t_lt / 1e12 / peaks["bf16_tflops"], "traffic": None, "kernel": "lt_attn_partial_kernel",
           "us": t_lt * 1e6, "shape": {"L": L, "T": T}, "peak_src": peaks["src"] + " burst"}
+    k = ncu.get("lt_attn_partial_kernel")
+    if k:
+        lt["traffic"] = k.get("dram_traffic_bytes")
+        lt["algorithmic_bytes"] = 2.0 * (128 * L * (1 + T) + 1024 * L * T)       # bf16 q, K, V read once
+        lt["ncu"] = {"tensor_pipe_pct_active": k.get("tensor_pipe_pct_active"),
+                     "tensor_pipe_pct_elapsed": k.get("tensor_pipe_pct_elapsed"), "us": k.get("duration_us"),
+                     "src": "profiles/ncu_headline.json"}
     # local attention, batched over sequences so the working set exceeds L2
     nb = 12
     lq, lk = [mk(L, 128) for _ in range(nb)], [mk(L, 128) for _ in range(nb)]
@@ -253,7 +267,13 @@ def kernel_rooflines(dev):
     bytes_alg = 2.0 * (2 * 128 * L + 3 * 1024 * L) + 4.0 * (225 * 128 + 225)
     loc = {"bound": "hbm", "achieved": bytes_alg / t_loc / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
            "frac": bytes_alg / t_loc / 1e9 / peaks["hbm_gbs"], "traffic": None,
-           "kernel": "local_scores_kernel+local_aggregate_kernel", "us": t_loc * 1e6, "peak_src": peaks["src"]}
+           "kernel": "local_scores_kernel+local_aggregate_kernel", "us": t_loc * 1e6, "peak_src": peaks["src"],
+           "algorithmic_bytes": bytes_alg}
+    ks = [ncu.get(n) for n in ("local_scores_kernel", "local_aggregate_kernel", "local_attn_kernel")]
+    ks = [k for k in ks if k]
+    if ks:
+        loc["traffic"] = sum(k.get("dram_traffic_bytes", 0.0) for k in ks)
+        loc["ncu"] = {"us": sum(k.get("duration_us", 0.0) for k in ks), "src": "profiles/ncu_headline.json"}
     return lt, loc
 
 

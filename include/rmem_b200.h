@@ -114,7 +114,8 @@ int rmem_layernorm_ex(const void* xa, int lda, const void* xb, int ldb, int in_b
                       int col_f32, int L, int C, void* stream);
 
 /* GroupNorm(groups, C = 32 * groups) + exact GELU over a token matrix x f32 [L][C] -> bf16 [L][C]
- * (GNActDWConv2d front half, layers/basic.py:15-35).  workspace: 16 * groups bytes (zeroed by the call). */
+ * (GNActDWConv2d front half, layers/basic.py:15-35).  workspace: 16 * groups + 8 bytes, 8-byte
+ * aligned, ZERO on first use; the call leaves it zero again (the last CTA re-zeroes it: no memset node per call). */
 int rmem_groupnorm_gelu_tokens(const float* x, const float* gamma, const float* beta, void* out, int L,
                                int C, int groups, void* workspace, void* stream);
 
@@ -167,7 +168,8 @@ int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, in
 /* GroupNorm over an [L][C] token matrix viewed as [1, C, L] (GroupNorm1D, layers/basic.py:6-12):
  * statistics per group over (C/groups channels x L tokens).  Replaces DualBranchGPM's
  * decoder_norms[-1] (transformer.py:806-808).  x = cat(x_a[L][Ca], x_b[L][C-Ca]) f32, out bf16.
- *   workspace: 16 * groups bytes, 8-byte aligned (fp64 sum / sum of squares; zeroed by the call)
+ *   workspace: 16 * groups + 8 bytes, 8-byte aligned (fp64 sum / sum of squares + an arrival counter); the
+ *   caller zero-fills it once, every call leaves it zero again
  */
 int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const float* gamma,
                           const float* beta, void* out, int L, int C, int groups, void* workspace,
@@ -252,8 +254,10 @@ int rmem_bank_score_evict(void* bank_state, const float* attn_mass, const float*
  * (utils/image.py:69-74, aot_engine.py:208-225) + the 17x17 stride-16 pad-8 patch_wise_id_bank conv
  * (models/aot.py:64-83, 111-114) + optionally DeAOT's id_norm LayerNorm (models/deaot.py:65-69).
  *   label  f32 [H][W]: 0..n_cls-2 object ids, 255 = ignore (class n_cls-1), anything else = no class
- *   prefix f32 [n_cls][17][18][256]: row-prefix sums of conv.weight: prefix[k][ky][j][c] =
- *          sum_{kx<j} weight[c][k][ky][kx];   bias f32 [256];  gamma/beta f32 [256] or NULL
+ *   prefix f32: [n_cls][17][18][256] row-prefix sums of conv.weight, prefix[k][ky][j][c] =
+ *          sum_{kx<j} weight[c][k][ky][kx], followed by [n_cls][18][18][256] 2-D prefix sums
+ *          prefix2[k][i][j][c] = sum_{ky<i, kx<j} weight[c][k][ky][kx] (window rows with the same run structure
+ *          are summed as rectangles);   bias f32 [256];  gamma/beta f32 [256] or NULL
  *   dst_host: HOST array of n_dst (<= 4) bf16 destinations [h*w][ld_host[i]], written at col0_host[i]
  */
 int rmem_id_embed(const float* label, int H, int W, const float* prefix, const float* bias,
@@ -268,8 +272,8 @@ int rmem_id_embed(const float* label, int H, int W, const float* prefix, const f
  * [H*W][C] view.
  *   rmem_groupnorm_nhwc: x, y f32 [P][C] (C = 64 / 128 / 256, C/groups a power of two in [4,32]);
  *       pre_bias f32 [C] or NULL is added to x first (the conv bias of ConvGN, so the convolution itself runs
- *       without a separate bias pass); gamma/beta f32 [C]; relu != 0 applies max(.,0); workspace 16*groups
- *       bytes (zeroed by the call).
+ *       without a separate bias pass); gamma/beta f32 [C]; relu != 0 applies max(.,0); workspace 16*groups + 8
+ *       bytes, zero on first use, left zero by the call.
  *   rmem_upsample_add_nhwc: out[ho*wo][C] = a[ho*wo][C] (or 0 when NULL) + a_bias[C] (or 0) + bilinear(x[hi*wi][C]).
  */
 int rmem_groupnorm_nhwc(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
@@ -294,8 +298,10 @@ int rmem_pack_image(const float* img, int H, int W, void* out, void* stream);
 int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream);
 
 /* Encoder stem max-pool, MaxPool2d(kernel 3, stride 2, padding 1) (networks/encoders/resnet.py:154):
- * x bf16 channels-last [H][W][C] -> y bf16 [(H-1)/2+1][(W-1)/2+1][C]; C a multiple of 8. */
-int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, void* y, void* stream);
+ * x bf16 channels-last [H][W][C] -> y bf16 [(H-1)/2+1][(W-1)/2+1][C]; C a multiple of 8.  bias f32 [C] (or NULL)
+ * and relu != 0 give y = relu(maxpool(x) + bias) = maxpool(relu(x + bias)): the stem's conv bias (folded BN,
+ * resnet.py:151-153) and ReLU applied after the pool, on a quarter of the pixels. */
+int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, const float* bias, int relu, void* y, void* stream);
 
 /* label[i] = (f32) argmax_c logits[c][i], first maximum -- the evaluator's softmax + argmax over the object
  * channel (networks/managers/evaluator.py:430-441); logits f32 [C][HW], label f32 [HW]. */

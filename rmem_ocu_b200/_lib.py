@@ -86,7 +86,7 @@ _SIGNATURES = {
                           [_c_int] * 4 + [_c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_pack_image": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
     "rmem_pack_image_s2d": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
-    "rmem_maxpool3s2_nhwc": [_c_void_p, _c_int, _c_int, _c_int, _c_void_p, _c_void_p],
+    "rmem_maxpool3s2_nhwc": [_c_void_p, _c_int, _c_int, _c_int, _c_void_p, _c_int, _c_void_p, _c_void_p],
     "rmem_argmax_label": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
     "rmem_bank_init": [_c_void_p, _c_int, _c_void_p],
     "rmem_bank_tick": [_c_void_p, _c_void_p],

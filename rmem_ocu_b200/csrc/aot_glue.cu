@@ -148,7 +148,7 @@ gn32_stats_kernel(const float* __restrict__ x, int L, int C, double* __restrict_
 __global__ void __launch_bounds__(256)
 gn32_gelu_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                        const float* __restrict__ beta, __nv_bfloat16* __restrict__ out, int L, int C,
-                       const double* __restrict__ ws) {
+                       double* __restrict__ ws) {
   const double cnt = 32.0 * L;
   const size_t total4 = static_cast<size_t>(L) * C / 4;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
@@ -172,18 +172,17 @@ gn32_gelu_apply_kernel(const float* __restrict__ x, const float* __restrict__ ga
     o[1] = __floats2bfloat162_rn(y[2], y[3]);
     *reinterpret_cast<uint2*>(out + i * 4) = pk;
   }
+  gn_ws_release(ws, 2 * (C >> 5));
 }
 
 int groupnorm_gelu_tokens_launch(const float* x, const float* gamma, const float* beta, void* out, int L, int C,
                                  int groups, void* workspace, cudaStream_t stream) {
   if (groups < 1 || C > 1024 || (C % 256) || C != groups * 32 || L < 1)
     return set_error(RMEM_ERR_ARG, "groupnorm_gelu_tokens: needs C = 32 * groups, C a multiple of 256 <= 1024");
-  cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 2 * groups, stream);
-  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_gelu_tokens: memset");
   gn32_stats_kernel<<<(L + 7) / 8, 256, 0, stream>>>(x, L, C, static_cast<double*>(workspace));
   if (int r = check_launch("gn32_stats_kernel")) return r;
   gn32_gelu_apply_kernel<<<592, 256, 0, stream>>>(x, gamma, beta, static_cast<__nv_bfloat16*>(out), L, C,
-                                                   static_cast<const double*>(workspace));
+                                                   static_cast<double*>(workspace));
   return check_launch("gn32_gelu_apply_kernel");
 }
 

@@ -145,8 +145,8 @@ int rmem_pack_image(const float* img, int H, int W, void* out, void* stream) {
 int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream) {
   return pack_image_s2d_launch(img, H, W, out, ST(stream));
 }
-int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, void* y, void* stream) {
-  return maxpool3s2_nhwc_launch(x, H, W, C, y, ST(stream));
+int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, const float* bias, int relu, void* y, void* stream) {
+  return maxpool3s2_nhwc_launch(x, H, W, C, bias, relu, y, ST(stream));
 }
 int rmem_argmax_label(const float* logits, int C, int HW, float* label, void* stream) {
   return argmax_label_launch(logits, C, HW, label, ST(stream));

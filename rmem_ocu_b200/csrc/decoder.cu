@@ -55,7 +55,7 @@ gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_
 __global__ void __launch_bounds__(256)
 gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
-                     int P, int C, int cpg, int relu, const double* __restrict__ ws) {
+                     int P, int C, int cpg, int relu, double* __restrict__ ws) {
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   const double cnt = static_cast<double>(cpg) * P;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
@@ -81,6 +81,7 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_
     if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
     reinterpret_cast<float4*>(y)[i] = o;
   }
+  gn_ws_release(ws, 2 * (C / cpg));
 }
 
 int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
@@ -90,8 +91,6 @@ int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* ga
   const int cpg = C / groups;
   if ((cpg & (cpg - 1)) || cpg < 4 || cpg > 32)
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: channels per group must be a power of two in [4, 32]");
-  cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 2 * groups, stream);
-  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_nhwc: memset");
   int rows = (P + 591) / 592;                    // ~4 CTAs per SM at large P ...
   if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
   gn_nhwc_stats_kernel<<<(P + rows - 1) / rows, 256, 0, stream>>>(x, pre_bias, P, C, cpg, rows,
@@ -101,7 +100,7 @@ int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* ga
   int blocks = static_cast<int>((total4 + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   gn_nhwc_apply_kernel<<<blocks, 256, 0, stream>>>(x, pre_bias, gamma, beta, y, P, C, cpg, relu,
-                                                   static_cast<const double*>(workspace));
+                                                   static_cast<double*>(workspace));
   return check_launch("gn_nhwc_apply_kernel");
 }
 
@@ -287,10 +286,12 @@ int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_
 }
 
 // Encoder stem max-pool (encoders/resnet.py:154, MaxPool2d(3, stride 2, padding 1)) on bf16 channels-last
-// [H][W][C] -> [Ho][Wo][C]: one thread per output pixel and 8-channel group, 128-bit loads and stores.
+// [H][W][C] -> [Ho][Wo][C]: one thread per output pixel and 8-channel group, 128-bit loads and stores.  With a
+// bias and / or relu it computes relu(maxpool(x) + bias) = maxpool(relu(x + bias)) (both maps are monotone per
+// channel), so the stem convolution can run without its own bias + ReLU pass over the full-resolution map.
 __global__ void __launch_bounds__(256)
-maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8, __nv_bfloat16* __restrict__ y,
-                       int Ho, int Wo) {
+maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8, const float* __restrict__ bias,
+                       int relu, __nv_bfloat16* __restrict__ y, int Ho, int Wo) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Ho * Wo * C8) return;
   const int c8 = i % C8, pix = i / C8;
@@ -314,16 +315,26 @@ maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8
   uint4 o;
   __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
-  for (int e = 0; e < 4; ++e) oh[e] = m[e];
+  for (int e = 0; e < 4; ++e) {
+    if (bias || relu) {
+      float2 f = __bfloat1622float2(m[e]);
+      if (bias) { f.x += bias[c8 * 8 + 2 * e]; f.y += bias[c8 * 8 + 2 * e + 1]; }
+      if (relu) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); }
+      oh[e] = __floats2bfloat162_rn(f.x, f.y);
+    } else {
+      oh[e] = m[e];
+    }
+  }
   *reinterpret_cast<uint4*>(y + static_cast<size_t>(pix) * (C8 * 8) + c8 * 8) = o;
 }
 
-int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, void* y, cudaStream_t stream) {
+int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y,
+                           cudaStream_t stream) {
   if (H < 1 || W < 1 || C < 8 || (C & 7)) return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
   const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
   const int n = Ho * Wo * (C / 8);
   maxpool3s2_nhwc_kernel<<<(n + 255) / 256, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), H, W, C / 8,
-                                                                static_cast<__nv_bfloat16*>(y), Ho, Wo);
+                                                                bias, relu, static_cast<__nv_bfloat16*>(y), Ho, Wo);
   return check_launch("maxpool3s2_nhwc_kernel");
 }
 

@@ -245,7 +245,7 @@ gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
-                __nv_bfloat16* __restrict__ out, int L, int C, int groups, const double* __restrict__ ws) {
+                __nv_bfloat16* __restrict__ out, int L, int C, int groups, double* __restrict__ ws) {
   const int cpg = C / groups;
   const double cnt = static_cast<double>(cpg) * L;
   const size_t total = static_cast<size_t>(L) * C;
@@ -260,6 +260,7 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
                            : xb[static_cast<size_t>(row) * (C - Ca) + (c - Ca)];
     out[i] = __float2bfloat16((v - static_cast<float>(mean)) * rstd * gamma[c] + beta[c]);
   }
+  gn_ws_release(ws, 2 * groups);
 }
 
 int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
@@ -268,13 +269,11 @@ int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const floa
   if (groups < 1 || groups > 8 || C > 1024 || (C % groups) || ((C / groups) % 32) || Ca > C ||
       (Ca < C && !xb))
     return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
-  cudaError_t e = cudaMemsetAsync(workspace, 0, sizeof(double) * 2 * groups, stream);
-  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_tokens: memset");
   gn_stats_kernel<<<(L + 7) / 8, 256, 0, stream>>>(xa, Ca, xb, L, C, groups,
                                                     static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
   gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta, static_cast<__nv_bfloat16*>(out), L,
-                                           C, groups, static_cast<const double*>(workspace));
+                                           C, groups, static_cast<double*>(workspace));
   return check_launch("gn_apply_kernel");
 }
 

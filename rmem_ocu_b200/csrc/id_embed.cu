@@ -6,7 +6,9 @@
 // A one-hot input makes the convolution a table lookup: out[token][c] = bias[c] +
 // sum over the token's 17x17 window of W[c][class(y,x)][ky][kx].  The weights are repacked as
 // row-prefix sums P[class][ky][kx'][c] = sum_{kx < kx'} W[c][class][ky][kx], so a run of equal labels
-// in a window row costs two loads instead of one per tap (label maps are piecewise constant).
+// in a window row costs two loads instead of one per tap (label maps are piecewise constant).  Behind them sit
+// the 2-D prefix sums P2[class][ky'][kx'][c] = sum_{ky < ky', kx < kx'} W[c][class][ky][kx]: rows with the same
+// run structure collapse into rectangles.
 #include <cuda_bf16.h>
 #include "rmem_internal.h"
 
@@ -16,7 +18,7 @@ constexpr int kIdK = 17, kIdStride = 16, kIdPad = 8, kIdC = 256;
 
 struct IdEmbedParams {
   const float* label;      // [H][W] label map: 0..max_obj = object id, 255 = ignore, others = nothing
-  const float* prefix;     // [n_cls][17][18][256]
+  const float* prefix;     // [n_cls][17][18][256] row prefixes, then [n_cls][18][18][256] 2-D prefixes
   const float* bias;       // [256]
   const float* gamma;      // LayerNorm weight [256] or nullptr (AOT: no norm)
   const float* beta;
@@ -66,12 +68,46 @@ __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
     n_runs[ky] = n;
   }
   __syncthreads();
+  // consecutive window rows with identical run lists form a group: its contribution is a rectangle sum, four
+  // loads from the 2-D prefix table whatever the group's height (an interior window of a single object is one
+  // group with one run); a lone row uses the row-prefix table (two loads per run)
+  __shared__ short grp_lo[kIdK], grp_hi[kIdK];
+  __shared__ int n_grp;
+  if (threadIdx.x == 0) {
+    int n = 0, r0 = 0;
+    for (int ky = 1; ky <= kIdK; ++ky) {
+      bool same = ky < kIdK && n_runs[ky] == n_runs[r0];
+      if (same) {
+        for (int r = 0; r < n_runs[r0]; ++r)
+          same = same && run_cls[ky][r] == run_cls[r0][r] && run_lo[ky][r] == run_lo[r0][r] &&
+                 run_hi[ky][r] == run_hi[r0][r];
+      }
+      if (!same) {
+        if (n_runs[r0] > 0) { grp_lo[n] = static_cast<short>(r0); grp_hi[n] = static_cast<short>(ky); ++n; }
+        r0 = ky;
+      }
+    }
+    n_grp = n;
+  }
+  __syncthreads();
+  const float* prefix2 = p.prefix + static_cast<size_t>(p.n_cls) * kIdK * (kIdK + 1) * kIdC;
   float acc = p.bias[c];
-  for (int ky = 0; ky < kIdK; ++ky) {
-    const int n = n_runs[ky];
-    for (int r = 0; r < n; ++r) {
-      const float* base = p.prefix + (static_cast<size_t>(run_cls[ky][r]) * kIdK + ky) * (kIdK + 1) * kIdC + c;
-      acc += base[run_hi[ky][r] * kIdC] - base[run_lo[ky][r] * kIdC];
+  const int ng = n_grp;
+  for (int g = 0; g < ng; ++g) {
+    const int r0 = grp_lo[g], r1 = grp_hi[g];
+    const int n = n_runs[r0];
+    if (r1 - r0 == 1) {
+      for (int r = 0; r < n; ++r) {
+        const float* base = p.prefix + (static_cast<size_t>(run_cls[r0][r]) * kIdK + r0) * (kIdK + 1) * kIdC + c;
+        acc += base[run_hi[r0][r] * kIdC] - base[run_lo[r0][r] * kIdC];
+      }
+    } else {
+      for (int r = 0; r < n; ++r) {
+        const float* base = prefix2 + static_cast<size_t>(run_cls[r0][r]) * (kIdK + 1) * (kIdK + 1) * kIdC + c;
+        const int lo = run_lo[r0][r], hi = run_hi[r0][r];
+        acc += (base[(r1 * (kIdK + 1) + hi) * kIdC] - base[(r0 * (kIdK + 1) + hi) * kIdC]) -
+               (base[(r1 * (kIdK + 1) + lo) * kIdC] - base[(r0 * (kIdK + 1) + lo) * kIdC]);
+      }
     }
   }
   float out = acc;

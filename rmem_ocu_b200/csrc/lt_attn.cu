@@ -12,9 +12,8 @@
 //       tiles through two 2-stage rings; one elected thread issues tcgen05.mma: S = Q K^T into a
 //       double-buffered 128-column TMEM tile, O += P V into a 256-column TMEM accumulator with P
 //       read straight from TMEM (the bf16 probabilities overwrite the S tile in place, so P never
-//       touches shared memory).  Sixteen softmax warps -- four per TMEM lane quarter, each thread
-//       owning a quarter of one query row (the softmax is latency-bound per warp, so the work is
-//       spread over many warps) -- read S with tcgen05.ld, exchange the row max through
+//       touches shared memory).  Eight softmax warps -- two per TMEM lane quarter, each thread
+//       owning half of one query row -- read S with tcgen05.ld, exchange the row max through
 //       shared memory, exponentiate with packed f32x2 FMAs + MUFU.EX2, rescale O lazily and
 //       write P with tcgen05.st.  Output: un-normalised O, running max m (log2 units) and sum l.
 //   rmem_lt_attn_combine : merges the chunk partials, adds the per-frame TPE bias
@@ -32,20 +31,14 @@ constexpr int kDK = 128;          // d_att
 constexpr int kDV = 1024;         // expand_d_vu (V | ID_V)
 constexpr int kDVTile = 256;      // value channels per CTA (TMEM accumulator columns)
 constexpr int kDVSplits = kDV / kDVTile;
-
 constexpr int kKStages = 2, kVStages = 2;
-constexpr int kSoftmaxWarps = 16;
-constexpr int kParts = kSoftmaxWarps / 4;           // threads per query row
-constexpr int kPartCols = kBlockN / kParts;         // S columns per thread and tile (32)
-constexpr int kPartDV = 256 / kParts;               // O columns per thread (64)
-static_assert(kParts == 4, "the softmax warps use the x32 load / x16 store TMEM shapes");
-constexpr int kThreads = 64 + 32 * kSoftmaxWarps;   // warp0 TMA, warp1 MMA, warps2-17 softmax/epilogue
+constexpr int kSoftmaxWarps = 8;
+constexpr int kThreads = 64 + 32 * kSoftmaxWarps;   // warp0 TMA, warp1 MMA, warps2-9 softmax/epilogue
 
 constexpr uint32_t kQBytes = kBlockM * kDK * 2;            // 32 KB  [2][128][64]
 constexpr uint32_t kKBytes = kBlockN * kDK * 2;            // 32 KB  [2][128][64]
 constexpr uint32_t kVBytes = kBlockN * kDVTile * 2;        // 64 KB  [4][128][64]
-constexpr uint32_t kXchBytes = 2 * kParts * kBlockM * 2;   // row-max exchange (bf16), one buffer per S buffer;
-                                                           // reused once as [kParts][128] fp32 for the row sums
+constexpr uint32_t kXchBytes = 2 * 2 * kBlockM * 4;        // row-max exchange, one buffer per S buffer
 constexpr uint32_t kSmemData = kQBytes + kKStages * kKBytes + kVStages * kVBytes;
 constexpr uint32_t kSmemTotal = kSmemData + kXchBytes + 256 /*barriers*/;
 static_assert(kSmemTotal <= 232448, "exceeds the 227 KB shared memory of an sm_100 CTA");
@@ -66,7 +59,6 @@ struct LtParams {
   float* part_m;         // [n_chunks][L]
   float* part_l;         // [n_chunks][L]
   float scale_log2;      // log2(e) / sqrt(d_att)
-  int exp_mode;          // DEV EXPERIMENT knob (RMEM_LT_EXP): 1 = no K/V loads after the first ring fill, 2 = no softmax
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -80,8 +72,8 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + kQBytes;
   uint8_t* sV = sK + kKStages * kKBytes;
-  __nv_bfloat16* xch = reinterpret_cast<__nv_bfloat16*>(sV + kVStages * kVBytes);   // [2][kParts][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kVStages * kVBytes + kXchBytes);
+  float* xch = reinterpret_cast<float*>(sV + kVStages * kVBytes);   // [2][2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xch + 2 * 2 * kBlockM);
   uint64_t* q_full = bars + 0;
   uint64_t* k_full = bars + 1;             // [2]
   uint64_t* k_empty = bars + 3;            // [2]
@@ -145,13 +137,11 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         const int st = j & 1;
         const uint32_t ph = ((j >> 1) - 1) & 1;
         if (j >= 2) mbar_wait(k_empty + st, ph);
-        if (p.exp_mode == 1 && j >= 2) { mbar_arrive(k_full + st); } else {
         mbar_expect_tx(k_full + st, kKBytes);
-        tma_load_4d(sK + st * kKBytes, &tm_k, k_full + st, 0, key_begin + j * kBlockN, 0, slot); }
+        tma_load_4d(sK + st * kKBytes, &tm_k, k_full + st, 0, key_begin + j * kBlockN, 0, slot);
         if (j >= 2) mbar_wait(v_empty + st, ph);
-        if (p.exp_mode == 1 && j >= 2) { mbar_arrive(v_full + st); } else {
         mbar_expect_tx(v_full + st, kVBytes);
-        tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot); }
+        tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot);
       }
     }
   } else if (warp == 1) {
@@ -201,13 +191,11 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     }
   } else {
     // ------------------------------------------------------------------ softmax + epilogue
-    // kParts threads per query row: warp w serves TMEM lane quarter w % 4 (the hardware's access rule) and
-    // column part (w - 2) / 4 of every S tile, O tile and output block.
-    const int quarter = warp & 3;
-    const int part = (warp - 2) >> 2;
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+    const int hf = (warp - 2) >> 2;               // which half of the row's columns this thread owns
     const int row = quarter * 32 + lane;          // query row inside the tile
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-    const uint32_t row_bar = 1 + quarter;         // named barrier shared by the kParts warps of a quarter
+    const uint32_t pair_bar = 1 + quarter;        // named barrier shared by the two warps of a quarter
     const int q_global = q_tile * kBlockM + row;
     float m_used = -INFINITY;
     float l_sum = 0.f;
@@ -217,31 +205,40 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       const int b = j & 1;
       mbar_wait(s_full + b, (j >> 1) & 1);
       tc_fence_after();
-      if (p.exp_mode == 2) { tc_fence_before(); mbar_arrive(p_full + b); continue; }
-      uint32_t sr[kPartCols];
-      tmem_ld32(tmem_base + lane_addr + kTmemS0 + b * kBlockN + part * kPartCols, sr);
-      tmem_ld_wait();
-      const int valid = key_len - j * kBlockN - part * kPartCols;   // valid columns of this part (may be <= 0)
-      if (valid < kPartCols) {                                      // warp-uniform: only the chunk's last tile
-#pragma unroll
-        for (int i = 0; i < kPartCols; ++i)
-          if (i >= valid) sr[i] = 0xff800000u;                      // -inf
+#ifdef LT_EXP_NOSOFTMAX
+      tc_fence_before();
+      mbar_arrive(p_full + b);
+      continue;
+#endif
+      uint32_t sr[64];
+      {
+        uint32_t(&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[0]);
+        uint32_t(&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sr[32]);
+        const uint32_t s_addr = tmem_base + lane_addr + kTmemS0 + b * kBlockN + hf * 64;
+        tmem_ld32(s_addr, lo);
+        tmem_ld32(s_addr + 32, hi);
+        tmem_ld_wait();
       }
-      float mx0 = -INFINITY, mx1 = -INFINITY;
+#ifdef LT_EXP_LDONLY
+      if (sr[0] == 0x12345678u && sr[63] == 0x9abcdef0u) l_sum += 1.f;
+      tc_fence_before();
+      mbar_arrive(p_full + b);
+      continue;
+#endif
+      const int valid = key_len - j * kBlockN - hf * 64;   // valid columns in this half (may be <= 0)
+      if (valid < 64) {                                       // warp-uniform: only the chunk's last tile
 #pragma unroll
-      for (int i = 0; i < kPartCols; i += 4) {
-        mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sr[i]), __uint_as_float(sr[i + 1])));
-        mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3])));
+        for (int i = 0; i < 64; ++i)
+          if (i >= valid) sr[i] = 0xff800000u;                // -inf
       }
-      // row max across the parts (the partner threads live in warps +-4, +-8, ...).  The reference max only
-      // has to be the same number in every thread of the row and close to the true max, so the exchange
-      // carries bf16 (rounded up): every part, this one included, uses the rounded values.
-      xch[(b * kParts + part) * kBlockM + row] = __float2bfloat16_ru(fmaxf(mx0, mx1));
-      named_bar_sync(row_bar, 32 * kParts);
       float mx = -INFINITY;
 #pragma unroll
-      for (int k = 0; k < kParts; ++k) mx = fmaxf(mx, __bfloat162float(xch[(b * kParts + k) * kBlockM + row]));
-      mx *= c;
+      for (int i = 0; i < 64; i += 2)
+        mx = fmaxf(mx, fmaxf(__uint_as_float(sr[i]), __uint_as_float(sr[i + 1])));
+      // row max across the two halves (the partner thread lives in warp +-4)
+      xch[(b * 2 + hf) * kBlockM + row] = mx;
+      named_bar_sync(pair_bar, 64);
+      mx = fmaxf(mx, xch[(b * 2 + (hf ^ 1)) * kBlockM + row]) * c;
       // lazy rescale: keep the reference max unless it grew by more than the threshold
       const bool grow = mx > m_used + kRescaleThreshold;
       float scale = 1.f;
@@ -250,12 +247,12 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         m_new = mx;
         scale = fast_exp2(m_used - m_new);            // 0 when m_used == -inf
       }
-      if (j > 0 && __any_sync(0xffffffffu, grow)) {    // same decision in every warp of the quarter
+      if (j > 0 && __any_sync(0xffffffffu, grow)) {    // same decision in both warps of the pair
         mbar_wait(pv_done + ((j - 1) & 1), ((j - 1) >> 1) & 1);
         tc_fence_after();
-        const uint32_t o_addr = tmem_base + lane_addr + kTmemO + part * kPartDV;
+        const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
 #pragma unroll 1
-        for (int cb = 0; cb < kPartDV / 32; ++cb) {
+        for (int cb = 0; cb < kDVTile / 64; ++cb) {
           uint32_t orow[32];
           tmem_ld32(o_addr + cb * 32, orow);
           tmem_ld_wait();
@@ -268,9 +265,9 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       m_used = m_new;
       const float neg_m = -m_used;
       float acc0 = 0.f, acc1 = 0.f;
-      uint32_t packed[kPartCols / 2];
+      uint32_t packed[32];
 #pragma unroll
-      for (int i = 0; i < kPartCols; i += 2) {
+      for (int i = 0; i < 64; i += 2) {
         float x0, x1;
         fma_f32x2(x0, x1, __uint_as_float(sr[i]), __uint_as_float(sr[i + 1]), c, c, neg_m, neg_m);
         float p0, p1;
@@ -284,9 +281,9 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         packed[i >> 1] = pack_bf16x2(p0, p1);
       }
       l_sum += acc0 + acc1;
-      // P (bf16, 64 columns) overwrites the first half of this S buffer; every thread of the row has its S
-      // values in registers (it passed tcgen05.wait::ld before the row barrier).
-      tmem_st16(tmem_base + lane_addr + kTmemS0 + b * kBlockN + part * (kPartCols / 2), packed);
+      // P (bf16, 64 columns) overwrites the first half of this S buffer; both partner threads have
+      // their S values in registers (they passed tcgen05.wait::ld before the pair barrier).
+      tmem_st32(tmem_base + lane_addr + kTmemS0 + b * kBlockN + hf * 32, packed);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full + b);
@@ -297,23 +294,20 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       mbar_wait(o_full, 0);
       tc_fence_after();
     }
-    // l of the parts: exchanged as fp32 through the whole exchange area, after every reader of the last
-    // tile's row maxima has passed this barrier
-    named_bar_sync(row_bar, 32 * kParts);
-    float* xl = reinterpret_cast<float*>(xch);
-    xl[part * kBlockM + row] = l_sum;
-    named_bar_sync(row_bar, 32 * kParts);
-    float l_tot = 0.f;
-#pragma unroll
-    for (int k = 0; k < kParts; ++k) l_tot += xl[k * kBlockM + row];
+    // l of the two halves: exchanged through the buffer the last tile did NOT use (its last readers
+    // passed the last tile's pair barrier)
+    const int xb = (n_tiles & 1);                 // last tile used buffer (n_tiles - 1) & 1
+    xch[(xb * 2 + hf) * kBlockM + row] = l_sum;
+    named_bar_sync(pair_bar, 64);
+    const float l_tot = l_sum + xch[(xb * 2 + (hf ^ 1)) * kBlockM + row];
     const bool row_ok = q_global < p.L;
     // O tile -> shared memory (the K / V rings are idle now: o_full means every MMA has completed) as
     // eight [128 rows][32 fp32] blocks in the 128B-swizzled layout, then one thread issues TMA stores:
     // full-line writes, rows beyond L clipped by the tensor map.
     uint8_t* stage = sK;
-    const uint32_t o_addr = tmem_base + lane_addr + kTmemO + part * kPartDV;
+    const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
 #pragma unroll 1
-    for (int cb = 0; cb < kPartDV / 32; ++cb) {
+    for (int cb = 0; cb < kDVTile / 64; ++cb) {
       uint32_t orow[32];
       if (n_tiles > 0) {
         tmem_ld32(o_addr + cb * 32, orow);
@@ -322,7 +316,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
 #pragma unroll
         for (int i = 0; i < 32; ++i) orow[i] = 0u;
       }
-      uint8_t* blk = stage + (part * (kPartDV / 32) + cb) * (kBlockM * 128);
+      uint8_t* blk = stage + (hf * 4 + cb) * (kBlockM * 128);
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch)
         *reinterpret_cast<uint4*>(blk + sw128_offset(row, ch)) =
@@ -337,7 +331,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       tma_store_commit();
       tma_store_wait_read();
     }
-    if (row_ok && dv_split == 0 && part == 0) {
+    if (row_ok && dv_split == 0 && hf == 0) {
       p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;
       p.part_l[static_cast<size_t>(chunk) * p.L + q_global] = l_tot;
     }
@@ -513,7 +507,6 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
   p.part_m = part_m;
   p.part_l = part_l;
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
-  { const char* e = getenv("RMEM_LT_EXP"); p.exp_mode = e ? atoi(e) : 0; }
   dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, p.n_chunks);
   lt_attn_partial_kernel<<<grid, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, tm_o, p);
   return check_launch("lt_attn_partial_kernel");

@@ -71,7 +71,8 @@ int finish_logits_launch(const float* conv, long long sc, long long sy, long lon
                          int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream);
 int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
 int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
-int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, void* y, cudaStream_t stream);
+int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y,
+                           cudaStream_t stream);
 int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream);
 int bank_tick_launch(void* state, cudaStream_t stream);
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
@@ -82,5 +83,25 @@ int bank_append_launch(void* state, int T, int frame_step, const void* const* sr
                        const int64_t* row_bytes, int n_tensors, cudaStream_t stream);
 int bank_score_evict_launch(void* state, const float* attn_mass, const float* fg, int L, int T_old,
                             int capacity, cudaStream_t stream);
+
+
+#ifdef __CUDACC__
+// GroupNorm statistics workspace: 2 * groups fp64 accumulators followed by one 8-byte arrival counter.  The caller
+// provides it zero-filled once; every apply kernel CTA calls this after its last read and the last CTA to arrive
+// re-zeroes accumulators and counter, so no memset node sits in front of each GroupNorm (a memset node costs
+// ~7 us inside a CUDA graph -- more than the statistics kernel).
+__device__ __forceinline__ void gn_ws_release(double* ws, int n_stats) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* counter = reinterpret_cast<unsigned int*>(ws + n_stats);
+    __threadfence();
+    if (atomicAdd(counter, 1u) == gridDim.x - 1) {
+      for (int i = 0; i < n_stats; ++i) ws[i] = 0.0;
+      *counter = 0u;
+      __threadfence();
+    }
+  }
+}
+#endif
 
 }  // namespace rmem

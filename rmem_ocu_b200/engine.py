@@ -91,9 +91,7 @@ class PreparedDeAOT:
         # ID bank as a lookup table: row-prefix sums of the 17x17 kernel per class (csrc/id_embed.cu)
         wid = sd["patch_wise_id_bank.weight"].detach().float().cpu()            # [256, n_cls, 17, 17]
         self.n_id_cls = wid.shape[1]
-        pref = torch.zeros(self.n_id_cls, 17, 18, 256)
-        pref[:, :, 1:, :] = torch.cumsum(wid.permute(1, 2, 3, 0).double(), dim=2).float()
-        self.id_prefix = pref.contiguous().to(device)
+        self.id_prefix = ops.id_prefix_table(wid).to(device)
         self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
         # black boxes (library calls): encoder / projector in bf16 channels-last with the frozen BN folded
         # into the convs, FPN head in fp32 (it decides the argmax mask)
@@ -124,7 +122,7 @@ class InferenceFPN:
         # tcgen05 GEMM straight off those maps (no f32 copies of the shortcuts, no f32 convolution)
         self.wb = {name: _bf(sd[prefix + name + ".weight"].reshape(sd[prefix + name + ".weight"].shape[0], -1), device)
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
-        self.gn_ws = torch.zeros(16, device=device, dtype=torch.float64)
+        self.gn_ws = torch.zeros(17, device=device, dtype=torch.float64)    # 2 x 8 group sums + arrival counter
 
     @staticmethod
     def _tok(x):
@@ -203,6 +201,7 @@ class InferenceResNet:
                                 ws[:, ch:ch + 3, a + 2, b + 2] = w1[:, :, i, j]
             self.conv1_s2d = (ws.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
                               self.conv1[1], (1, 1), (0, 0))
+            self.conv1_bias_f32 = enc.conv1.bias.detach().to(device=device, dtype=torch.float32)
         self.blocks = []
         for li in (1, 2, 3):
             stage = []
@@ -247,7 +246,9 @@ class InferenceResNet:
                 memory_format=torch.channels_last)
             x[:, :3] = img
         if s2d:
-            x = self._conv(x, self.conv1_s2d, True)
+            # bias + ReLU commute with the max-pool (monotone per channel): applied by the pool kernel on a
+            # quarter of the pixels instead of by a separate pass over the full-resolution map
+            x = F.conv2d(x, self.conv1_s2d[0], None)
         elif self.fused:
             x = self._conv(x, self.conv1, True)
         else:
@@ -255,7 +256,10 @@ class InferenceResNet:
         if self.dtype == BF16 and n == 1:
             pooled = torch.empty(1, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
                                  device=x.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
-            ops.maxpool3s2_nhwc(x.contiguous(memory_format=torch.channels_last), pooled)
+            c_, h_, w_ = x.shape[1:]
+            if x.stride()[1:] != (1, w_ * c_, c_):                   # cuDNN returns NHWC strides; never copy then
+                x = x.contiguous(memory_format=torch.channels_last)
+            ops.maxpool3s2_nhwc(x, pooled, self.conv1_bias_f32 if s2d else None, s2d)
             x = pooled
         else:
             x = F.max_pool2d(x, 3, 2, 1)
@@ -334,7 +338,7 @@ class _Workspace:
         self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
         self.mass = z(L * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight [L, T]
         self.gn_out = z(L, 512)
-        self.gn_ws = z(4, dt=torch.float64)
+        self.gn_ws = z(5, dt=torch.float64)                   # 2 x 2 group sums + arrival counter
         self.fg = z(L, dt=f32)
         self.id_emb = z(L, 256)
         self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
@@ -396,6 +400,8 @@ class DeAOTEngine:
         self.ws = None
         self.trace = None          # optional dict: per-layer intermediates for the parity tests
         self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
+        self.fork_branches = os_env_flag("RMEM_FORK_BRANCHES", True)
+        self._side = None
         self._graphs = {}
         self._graph_pool = None
         self.restart_engine()
@@ -496,6 +502,23 @@ class DeAOTEngine:
         ops.lt_attn_combine(ws.part_o, ws.part_m, ws.part_l, ws.tpe_bias if tpe else None,
                             tpe_row_indices(T) if tpe else None, T, ws.L, cpf, gate, out, mass)
 
+    def _fork(self):
+        """Make the side stream wait for everything issued so far on the current stream."""
+        if not self.fork_branches:
+            return False
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._side.wait_event(ev)
+        return True
+
+    def _join(self):
+        """Make the current stream wait for everything issued on the side stream."""
+        ev = torch.cuda.Event()
+        ev.record(self._side)
+        torch.cuda.current_stream().wait_event(ev)
+
     def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):
         """DualBranchGPM.forward + GatedPropagationModule.forward (transformer.py:765-824, 1091-1236)."""
         ws, prep = self.ws, self.prep
@@ -521,20 +544,28 @@ class DeAOTEngine:
                 self._id_value(i, ws.vcur[i])
                 ws.kprev[i].copy_(ws.kcur[i]); ws.vprev[i].copy_(ws.vcur[i])
                 ws.kbank[i][0].copy_(ws.kcur[i]); ws.vbank[i][0].copy_(ws.vcur[i])
-            # long-term attention over the bank (TPE folded into a per-frame score bias)
+            # The long-term and the short-term branch only share their inputs (K = Q, U) and meet again in the
+            # projection GEMM: the short-term branch is forked onto a side stream (a parallel branch of the
+            # captured graph), so its sub-wave kernels fill the SMs the long-term attention's ragged second wave
+            # leaves idle.
+            forked = self._fork()
+            with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
+                # short-term 15x15 local attention over the previous frame, gate, dw5x5
+                ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
+                ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
+                ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
+                ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
+            # long-term attention over the bank (TPE folded into a per-frame score bias), gate, dw5x5
             ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
             mass = None
             if save_atten_weights and i == 0:
                 mass = ws.mass
             self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
                                          ws.gated_a, mass)
-            # short-term 15x15 local attention over the previous frame
-            ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
-            ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
-            ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
-            # gate -> dw5x5 -> (projection_lt + projection_st) -> residual adds, one GEMM
             ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
-            ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
+            if forked:
+                self._join()
+            # (projection_lt + projection_st) -> residual adds, one GEMM
             if tr is not None:
                 tr.setdefault("layers", []).append(dict(
                     curr_Q=ws.kcur[i].float().cpu(), curr_V=ws.vcur[i][:, :512].float().cpu(),

@@ -89,9 +89,7 @@ class PreparedAOT:
         self.mem_pos_emb = _f32(sd["mem_pos_emb"], device)
         wid = sd["patch_wise_id_bank.weight"].detach().float().cpu()            # [256, n_cls, 17, 17]
         self.n_id_cls = wid.shape[1]
-        pref = torch.zeros(self.n_id_cls, 17, 18, 256)
-        pref[:, :, 1:, :] = torch.cumsum(wid.permute(1, 2, 3, 0).double(), dim=2).float()
-        self.id_prefix = pref.contiguous().to(device)
+        self.id_prefix = ops.id_prefix_table(wid).to(device)
         self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
         self.id_norm = (None, None)                                             # AOT: no LayerNorm on the id embedding
         self.encoder = encoder_cls(model.encoder, model.encoder_projector, device, enc_dtype)
@@ -131,7 +129,7 @@ class WorkspaceAOT:
         self.part_m, self.part_l = z(n_chunks, 8, L, dt=f32), z(n_chunks, 8, L, dt=f32)
         self.mass = z(L * _lib.MAX_BANK, dt=f32)                   # layer-0 record_attn_weight [L, T]
         self.dec_in = z(L, 256 * (nl + 1), dt=f32)                 # channels-last decoder input [emb | out_0 | out_1 | out_2]
-        self.gn_ws = z(64, dt=torch.float64)
+        self.gn_ws = z(65, dt=torch.float64)                  # 2 x 32 group sums + arrival counter
         self.fg = z(L, dt=f32)
         self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
         self.zero_order = z(1, dt=torch.int32)

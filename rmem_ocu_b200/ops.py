@@ -129,14 +129,15 @@ def pack_image_s2d(img, out):
     _count("rmem_pack_image_s2d")
 
 
-def maxpool3s2_nhwc(x, out):
+def maxpool3s2_nhwc(x, out, bias=None, relu=False):
     """x bf16 [1, C, H, W] channels-last -> out bf16 [1, C, (H-1)//2+1, (W-1)//2+1] channels-last:
-    MaxPool2d(3, 2, 1) of the encoder stem."""
+    MaxPool2d(3, 2, 1) of the encoder stem; with bias (f32 [C]) / relu: relu(maxpool(x) + bias)."""
     _chk_cuda(x, out)
     n, C, H, W = x.shape
-    if n != 1 or x.dtype != torch.bfloat16 or not x.is_contiguous(memory_format=torch.channels_last):
+    if n != 1 or x.dtype != torch.bfloat16 or x.stride()[1:] != (1, W * C, C):
         raise ValueError("maxpool3s2_nhwc: expects one bf16 channels-last image")
-    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc(_p(x), H, W, C, _p(out), _stream()), "rmem_maxpool3s2_nhwc")
+    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc(_p(x), H, W, C, _p(bias), 1 if relu else 0, _p(out), _stream()),
+               "rmem_maxpool3s2_nhwc")
     _count("rmem_maxpool3s2_nhwc")
 
 
@@ -204,6 +205,18 @@ def bank_init(state, frame_step):
 def bank_tick(state):
     _lib.check(_lib.lib().rmem_bank_tick(_p(state), _stream()), "rmem_bank_tick")
     _count("rmem_bank_tick")
+
+
+def id_prefix_table(weight):
+    """patch_wise_id_bank.weight [256, n_cls, 17, 17] -> the lookup table rmem_id_embed reads (host f32, flat):
+    row prefixes [n_cls][17][18][256] followed by 2-D prefixes [n_cls][18][18][256] (include/rmem_b200.h)."""
+    wk = weight.detach().double().cpu().permute(1, 2, 3, 0)                 # [n_cls, ky, kx, c]
+    n_cls = wk.shape[0]
+    p1 = torch.zeros(n_cls, 17, 18, 256, dtype=torch.float64)
+    p1[:, :, 1:, :] = torch.cumsum(wk, dim=2)
+    p2 = torch.zeros(n_cls, 18, 18, 256, dtype=torch.float64)
+    p2[:, 1:, :, :] = torch.cumsum(p1, dim=1)
+    return torch.cat([p1.reshape(-1), p2.reshape(-1)]).float().contiguous()
 
 
 def id_embed(label, prefix, bias, gamma, beta, n_cls, dsts, h, w):

@@ -97,7 +97,7 @@ def test_groupnorm_tokens(lib_built):
     xb = torch.randn(L, 256, device="cuda") * 0.3 - 1
     g, b = torch.randn(512, device="cuda"), torch.randn(512, device="cuda")
     out = torch.empty(L, 512, device="cuda", dtype=torch.bfloat16)
-    ws = torch.empty(4, device="cuda", dtype=torch.float64)
+    ws = torch.zeros(5, device="cuda", dtype=torch.float64)
     ops.groupnorm_tokens(xa, xb, g, b, out, 2, ws)
     torch.cuda.synchronize()
     x = torch.cat([xa, xb], 1)
@@ -156,8 +156,7 @@ def test_id_embed_vs_oracle(lib_built, H, W):
     ref = R.get_id_emb(torch.cat((one_hot, ignore), 1), sd, True)          # [1, 256, h, w]
     h, w = ref.shape[-2:]
     ref = ref.permute(0, 2, 3, 1).reshape(h * w, 256)
-    pref = torch.zeros(12, 17, 18, 256)
-    pref[:, :, 1:, :] = torch.cumsum(wt.permute(1, 2, 3, 0).double(), dim=2).float()
+    pref = ops.id_prefix_table(wt)
     out = torch.zeros(h * w, 512, device="cuda", dtype=torch.bfloat16)
     out2 = torch.zeros(h * w, 256, device="cuda", dtype=torch.bfloat16)
     ops.id_embed(lab[0, 0].cuda(), pref.cuda(), bias.cuda(), g.cuda(), b.cuda(), 12, [(out, 256), (out2, 0)], h, w)
@@ -178,7 +177,7 @@ def test_groupnorm_nhwc(lib_built, C, H, W):
     ref0 = F.relu(F.group_norm(x, 8, g, b, 1e-5))
     t = x.permute(0, 2, 3, 1).reshape(H * W, C)
     y = torch.empty_like(t)
-    ws = torch.empty(16, device="cuda", dtype=torch.float64)
+    ws = torch.zeros(17, device="cuda", dtype=torch.float64)
     ops.groupnorm_nhwc(t, g, b, y, 8, True, ws, pre_bias=pb)
     torch.cuda.synchronize()
     assert (y.view(1, H, W, C).permute(0, 3, 1, 2) - ref).abs().max().item() < 2e-4
@@ -292,6 +291,11 @@ def test_maxpool3s2_nhwc(lib_built, C, H, W):
     out = torch.empty_like(ref).contiguous(memory_format=torch.channels_last)
     ops.maxpool3s2_nhwc(x, out)
     assert torch.equal(out, ref)
+    # fused form: relu(maxpool(x) + bias) == maxpool(relu(x + bias)) up to the final bf16 rounding
+    bias = torch.randn(C, device="cuda")
+    ops.maxpool3s2_nhwc(x, out, bias, True)
+    ref2 = F.max_pool2d(F.relu(x.float() + bias.view(1, -1, 1, 1)), 3, 2, 1)
+    assert torch.equal(out, ref2.to(torch.bfloat16))
 
 
 @pytest.mark.parametrize("H,W", [(480, 864), (481, 865), (37, 54)])

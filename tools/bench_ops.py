@@ -94,7 +94,7 @@ for T in (1, 5):
     timed("mha partial T=%d cpf=%d" % (T, cpf), lambda i: ops.mha_partial(q2[i], kb2[i], vb2[i], order, T, cpf, po2, pm2, pl2))
     timed("mha combine T=%d cpf=%d" % (T, cpf), lambda i: ops.mha_combine(po2, pm2, pl2, None, None, T, L, cpf, o[i], 0, mass))
 xf = [f32(L, 1024) for _ in range(NB)]
-ws = torch.zeros(64, device=dev, dtype=torch.float64)
+ws = torch.zeros(65, device=dev, dtype=torch.float64)
 g1, b1 = f32(1024), f32(1024)
 timed("gn32+gelu tokens (2 kernels)", lambda i: ops.groupnorm_gelu_tokens(xf[i], g1, b1, y[i], 32, ws))
 P = 120 * 216
