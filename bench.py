@@ -127,6 +127,7 @@ def frame_step(eng, img_dev, out_hw):
 def run_b200(args, rank, world):
     from rmem_ocu_b200 import ops
     from rmem_ocu_b200.engine import DeAOTInferEngine
+    from rmem_ocu_b200.pipeline import FrameStreamer
     import torch.distributed as dist
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local_rank)
@@ -156,26 +157,43 @@ def run_b200(args, rank, world):
             barrier()
             launches0 = ops.LAUNCHES
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            first = 1 + args.warmup
             with ClockSampler(local_rank) as clk:
                 e0.record()
-                for f in range(1 + args.warmup, n_frames):
+                if mode == "e2e":
+                    # host frames in, host masks out, every frame: uploads and read-backs are double-buffered on
+                    # copy streams (rmem_ocu_b200/pipeline.py), each mask is consumed on the host one frame late
+                    fs = FrameStreamer(dev)
+                    fs.stage(imgs[first])
+                for f in range(first, n_frames):
                     if mode == "device" and args.profile_steps:
-                        if f == 1 + args.warmup:
+                        if f == first:
                             torch.cuda.profiler.start()
-                        elif f == 1 + args.warmup + args.profile_steps:
+                        elif f == first + args.profile_steps:
                             torch.cuda.synchronize()
                             torch.cuda.profiler.stop()
                     if mode == "device":
                         label = frame_step(eng, dev_imgs[f], (H, W))
                     else:
-                        label = frame_step(eng, imgs[f], (H, W))            # pinned host image: H2D inside
-                        host_out.copy_(label[0, 0].to(torch.uint8), non_blocking=True)   # D2H of the result
-                        torch.cuda.current_stream().synchronize()
+                        x = fs.acquire()
+                        if f + 1 < n_frames:
+                            fs.stage(imgs[f + 1])                            # pinned host image -> device
+                        label = frame_step(eng, x, (H, W))
+                        fs.release()
+                        fs.push_result(label[0, 0].to(torch.uint8))          # device label map -> pinned host
+                        if fs.pending_results() > 1:
+                            host_out = fs.pop_result()
+                if mode == "e2e":
+                    while fs.pending_results():
+                        host_out = fs.pop_result()
+                    host_sum = int(host_out.sum())
                 e1.record()
                 barrier()
             ms = e0.elapsed_time(e1)
         results[mode] = dict(ms=ms, launches=ops.LAUNCHES - launches0, clocks=clk.summary(),
                              idx=eng.aot_engines[0].long_memories_indexes, checksum=int(label.sum().item()))
+        if mode == "e2e" and host_sum != results[mode]["checksum"]:
+            raise RuntimeError("e2e: the mask read back on the host differs from the device label map")
         del eng, dev_imgs
     # max over ranks
     t = torch.tensor([results["device"]["ms"], results["e2e"]["ms"]], device=dev, dtype=torch.float64)

@@ -239,7 +239,7 @@ class InferenceResNet:
             x = torch.empty(1, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device, dtype=BF16).permute(0, 3, 1, 2)
             ops.pack_image_s2d(img, x)              # f32 planes -> bf16 space-to-depth image, conv padding built in
         elif self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
-            x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
+            x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16, memory_format=torch.channels_last)
             ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
         else:
             x = torch.zeros(n, 8, h, w, device=img.device, dtype=self.dtype).contiguous(
@@ -255,7 +255,7 @@ class InferenceResNet:
             x = F.relu(F.conv2d(x, self.conv1[0], self.conv1[1], self.conv1[2], self.conv1[3]))
         if self.dtype == BF16 and n == 1:
             pooled = torch.empty(1, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
-                                 device=x.device, dtype=BF16).contiguous(memory_format=torch.channels_last)
+                                 device=x.device, dtype=BF16, memory_format=torch.channels_last)
             c_, h_, w_ = x.shape[1:]
             if x.stride()[1:] != (1, w_ * c_, c_):                   # cuDNN returns NHWC strides; never copy then
                 x = x.contiguous(memory_format=torch.channels_last)
@@ -402,6 +402,12 @@ class DeAOTEngine:
         self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
         self.fork_branches = os_env_flag("RMEM_FORK_BRANCHES", True)
         self._side = None
+        # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
+        # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
+        self.async_write = os_env_flag("RMEM_ASYNC_WRITE", True)
+        self._wstream = None
+        self._w_done = None
+        self._graph_pool_w = None
         self._graphs = {}
         self._graph_pool = None
         self.restart_engine()
@@ -444,17 +450,20 @@ class DeAOTEngine:
         n_slots = self.capacity + 1
         if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
             self.ws = self._new_workspace(h, w, n_slots)
-            self._graphs, self._graph_pool = {}, None             # graphs bake the workspace pointers
+            self._wait_write()
+            self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
 
     @property
     def long_memories_indexes(self):
         """Frame ids in the bank, oldest first (host mirror; reading it synchronises)."""
         if self.ws is None or self.T == 0:
             return []
+        self._wait_write()
         st = self.ws.bank_state.cpu()
         return [int(st[_lib.MAX_BANK + int(st[t])]) for t in range(self.T)]
 
     def eviction_debug(self):
+        self._wait_write()
         st = self.ws.bank_state.cpu()
         base = 5 * _lib.MAX_BANK
         return dict(last_drop=int(st[base]), last_drop_frame=int(st[base + 1]),
@@ -638,26 +647,46 @@ class DeAOTEngine:
         return ws.pred_logits if out is None else out
 
     # ------------------------------------------------------------------ CUDA graphs
-    def _run(self, key, body, inputs):
+    def _wait_write(self):
+        """Order the current stream after the last write path (it runs on its own stream)."""
+        if self._w_done is not None:
+            torch.cuda.current_stream().wait_event(self._w_done)
+
+    def _capture(self, key, body, inputs, alias=False):
+        """Capture ``body`` into a CUDA graph.  ``alias``: the inputs are outputs of another graph of this
+        engine (stable addresses), so they are baked in as they are and never copied.  Write-path graphs use
+        their own memory pool: they replay concurrently with the next frame's encoder graph."""
+        static_in = list(inputs) if alias else [torch.empty(t.shape, dtype=t.dtype, device=self.device)
+                                                 for t in inputs]
+        is_write = key[0] == "write"
+        pool = self._graph_pool_w if is_write else self._graph_pool
+        launches0 = ops.LAUNCHES
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, pool=pool):
+            out = body(*static_in)
+        ent = (g, static_in, out, ops.LAUNCHES - launches0)
+        ops.LAUNCHES = launches0
+        self._graphs[key] = ent
+        if is_write and self._graph_pool_w is None:
+            self._graph_pool_w = g.pool()
+        elif not is_write and self._graph_pool is None:
+            self._graph_pool = g.pool()
+        return ent
+
+    def _run(self, key, body, inputs, alias=False):
         """Run ``body(*static_inputs)`` eagerly, or through a CUDA graph captured once per key."""
         if not self.use_cuda_graphs or self.frame_step < 2 or self.trace is not None:
             return body(*inputs)                                  # frame 1 is eager: cuDNN picks its algorithms
         ent = self._graphs.get(key)
+        if ent is not None and alias and any(s.data_ptr() != t.data_ptr() for s, t in zip(ent[1], inputs)):
+            return body(*inputs)                                  # not the tensors the graph was recorded on
         if ent is None:
-            static_in = [torch.empty(t.shape, dtype=t.dtype, device=self.device) for t in inputs]
-            launches0 = ops.LAUNCHES
-            g = torch.cuda.CUDAGraph()
-            torch.cuda.synchronize()
-            with torch.cuda.graph(g, pool=self._graph_pool):
-                out = body(*static_in)
-            ent = (g, static_in, out, ops.LAUNCHES - launches0)
-            ops.LAUNCHES = launches0
-            self._graphs[key] = ent
-            if self._graph_pool is None:
-                self._graph_pool = g.pool()
+            ent = self._capture(key, body, inputs, alias)
         g, static_in, out, n_kernels = ent
-        for s, t in zip(static_in, inputs):
-            s.copy_(t, non_blocking=True)
+        if not alias:
+            for s, t in zip(static_in, inputs):
+                s.copy_(t, non_blocking=True)
         g.replay()
         ops.LAUNCHES += n_kernels
         return out
@@ -671,36 +700,32 @@ class DeAOTEngine:
         img = torch.zeros(1, 3, H, W, device=self.device)
         label = torch.zeros(H, W, device=self.device)
         saved = dict(self._graphs)
+        self._wait_write()
+        if ("enc",) not in self._graphs:
+            self._capture(("enc",), self.encode_image, [img])
+        embs = list(self._graphs[("enc",)][2])                    # the encoder graph's outputs feed the read graphs
         for T in range(1, self.capacity + 1):
-            for key, body, inputs in self._variants(T, output_size, img, label):
+            for key, body, inputs, alias in self._variants(T, output_size, embs, label):
                 if key not in self._graphs:
-                    static_in = [torch.empty_like(t) for t in inputs]
-                    launches0 = ops.LAUNCHES
-                    g = torch.cuda.CUDAGraph()
-                    torch.cuda.synchronize()
-                    with torch.cuda.graph(g, pool=self._graph_pool):
-                        out = body(*static_in)
-                    self._graphs[key] = (g, static_in, out, ops.LAUNCHES - launches0)
-                    ops.LAUNCHES = launches0
-                    if self._graph_pool is None:
-                        self._graph_pool = g.pool()
+                    self._capture(key, body, inputs, alias)
         return len(self._graphs) - len(saved)
 
-    def _variants(self, T, output_size, img, label):
+    def _variants(self, T, output_size, embs, label):
         ev = self.deaot or T + 1 > self.capacity
         for st in ((0, 1) if self.deaot else (0,)):
-            yield (("read", T, output_size, st), lambda x, T=T, st=st: self._read_body(x, None, T, output_size, st),
-                   [img])
+            yield (("read", T, output_size, st),
+                   lambda *e, T=T, st=st: self._read_body(None, list(e), T, output_size, st), embs, True)
             yield (("write", T, False, False, st), lambda m, T=T, st=st: self._write_body(m, T, False, False, st),
-                   [label])
+                   [label], False)
             yield (("write", T, True, ev, st), lambda m, T=T, ev=ev, st=st: self._write_body(m, T, True, ev, st),
-                   [label])
+                   [label], False)
 
     # ------------------------------------------------------------------ public frame API
     def add_reference_frame(self, img=None, mask=None, frame_step=-1, obj_nums=None, img_embs=None):
         """aot_engine.py:241-325 (always eager: once per sequence)."""
         if self.obj_nums is None and obj_nums is None:
             raise ValueError("No objects for reference frame!")
+        self._wait_write()
         if obj_nums is not None:
             self.obj_nums = obj_nums
         if frame_step == -1:
@@ -733,8 +758,14 @@ class DeAOTEngine:
         osz = tuple(output_size) if output_size is not None else None
         st = self.st
         if img_embs is not None:
+            self._wait_write()
             return self._read_body(None, img_embs, T, osz, st)
-        return self._run(("read", T, osz, st), lambda x: self._read_body(x, None, T, osz, st), [img])
+        # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
+        # running on its own stream) and, after waiting for that write path, LSTT + decoder
+        embs = self._run(("enc",), self.encode_image, [img])
+        self._wait_write()
+        return self._run(("read", T, osz, st), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
+                         alias=True)
 
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
         emb = curr_lstt_embs[-1] if isinstance(curr_lstt_embs, (list, tuple)) else curr_lstt_embs
@@ -754,8 +785,20 @@ class DeAOTEngine:
         if do_evict and self.T_recorded != T:
             raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
         st = self.st
-        self._run(("write", T, update_long, do_evict, st),
-                  lambda m: self._write_body(m, T, update_long, do_evict, st), [label])
+        body = lambda m: self._write_body(m, T, update_long, do_evict, st)
+        if self.async_write:
+            if self._wstream is None:
+                self._wstream = torch.cuda.Stream(device=self.device)
+            ready = torch.cuda.Event()
+            ready.record()                                        # the label (and this frame's read path) is done
+            self._wstream.wait_event(ready)
+            label.record_stream(self._wstream)
+            with torch.cuda.stream(self._wstream):
+                self._run(("write", T, update_long, do_evict, st), body, [label])
+                self._w_done = torch.cuda.Event()
+                self._w_done.record()
+        else:
+            self._run(("write", T, update_long, do_evict, st), body, [label])
         if self.deaot:
             self.st = 1 - st                                      # the set just completed is the short-term memory now
         if update_long:

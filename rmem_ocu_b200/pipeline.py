@@ -1,0 +1,81 @@
+"""Host <-> device staging around an engine for a video stream.
+
+The engines take device tensors (like the reference's, whose evaluator calls ``.cuda()`` on every frame,
+networks/managers/evaluator.py:385-390).  A host loop that copies frame f, runs it, and reads its mask back
+before touching frame f+1 leaves the GPU idle during both copies.  ``FrameStreamer`` double-buffers both
+directions with two copy streams: the upload of frame f+1 runs while frame f computes, and the label map of
+frame f is read back while frame f+1 computes (results are consumed one frame late).  Every frame is still
+uploaded from pinned host memory and every result is still read on the host.
+"""
+import collections
+
+import torch
+
+
+class FrameStreamer:
+    def __init__(self, device, depth=2):
+        self.device = torch.device(device)
+        self.depth = depth
+        self._up = torch.cuda.Stream(device=self.device)
+        self._down = torch.cuda.Stream(device=self.device)
+        self._bufs = [None] * depth           # device image buffers
+        self._free = [None] * depth           # event: the compute stream is done with buffer i
+        self._staged = collections.deque()    # (buffer index, upload-done event)
+        self._next = 0
+        self._results = collections.deque()   # (pinned host tensor, device source kept alive, done event)
+        self._host = [None] * (depth + 1)
+        self._host_next = 0
+
+    # ---------------------------------------------------------------- uploads
+    def stage(self, host_img):
+        """Start the upload of a pinned host image; returns immediately."""
+        i = self._next
+        self._next = (i + 1) % self.depth
+        if self._bufs[i] is None or self._bufs[i].shape != host_img.shape:
+            self._bufs[i] = torch.empty(host_img.shape, dtype=host_img.dtype, device=self.device)
+        if self._free[i] is not None:
+            self._up.wait_event(self._free[i])            # the frame that last used this buffer has been consumed
+        with torch.cuda.stream(self._up):
+            self._bufs[i].copy_(host_img, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        self._staged.append((i, ev))
+
+    def acquire(self):
+        """Oldest staged image as a device tensor; the current stream waits for its upload."""
+        i, ev = self._staged.popleft()
+        torch.cuda.current_stream().wait_event(ev)
+        self._cur = i
+        return self._bufs[i]
+
+    def release(self):
+        """Call after the work reading the acquired image has been enqueued on the current stream."""
+        ev = torch.cuda.Event()
+        ev.record()
+        self._free[self._cur] = ev
+
+    # ---------------------------------------------------------------- results
+    def push_result(self, dev_tensor):
+        """Start the read-back of a device tensor (e.g. the uint8 label map) into pinned host memory."""
+        j = self._host_next
+        self._host_next = (j + 1) % len(self._host)
+        if self._host[j] is None or self._host[j].shape != dev_tensor.shape or self._host[j].dtype != dev_tensor.dtype:
+            self._host[j] = torch.empty(dev_tensor.shape, dtype=dev_tensor.dtype).pin_memory()
+        ready = torch.cuda.Event()
+        ready.record()
+        self._down.wait_event(ready)
+        dev_tensor.record_stream(self._down)
+        with torch.cuda.stream(self._down):
+            self._host[j].copy_(dev_tensor, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+        self._results.append((self._host[j], dev_tensor, done))
+
+    def pending_results(self):
+        return len(self._results)
+
+    def pop_result(self):
+        """Oldest result as a pinned host tensor (blocks until its copy has landed)."""
+        host, _, done = self._results.popleft()
+        done.synchronize()
+        return host
