@@ -686,7 +686,12 @@ class DeAOTEngine:
         g, static_in, out, n_kernels = ent
         if not alias:
             for s, t in zip(static_in, inputs):
-                s.copy_(t, non_blocking=True)
+                if t.is_cuda and t.is_floating_point() and t.is_contiguous():
+                    # an SM kernel, not a copy-engine memcpy: the copy engines may be busy with a caller's
+                    # upload of the next frame (pipeline.FrameStreamer) and this copy is on the critical path
+                    torch.mul(t, 1, out=s)
+                else:
+                    s.copy_(t, non_blocking=True)
         g.replay()
         ops.LAUNCHES += n_kernels
         return out

@@ -3,8 +3,9 @@
 The engines take device tensors (like the reference's, whose evaluator calls ``.cuda()`` on every frame,
 networks/managers/evaluator.py:385-390).  A host loop that copies frame f, runs it, and reads its mask back
 before touching frame f+1 leaves the GPU idle during both copies.  ``FrameStreamer`` double-buffers both
-directions with two copy streams: the upload of frame f+1 runs while frame f computes, and the label map of
-frame f is read back while frame f+1 computes (results are consumed one frame late).  Every frame is still
+directions with two copy streams: the upload of frame f+1 starts as soon as the host asks for it (three device
+buffers, so it normally lands while frame f-1 is still computing), and the label map of frame f is read back
+while frame f+1 computes (results are consumed one frame late).  Every frame is still
 uploaded from pinned host memory and every result is still read on the host.
 """
 import collections
@@ -13,7 +14,7 @@ import torch
 
 
 class FrameStreamer:
-    def __init__(self, device, depth=2):
+    def __init__(self, device, depth=3):
         self.device = torch.device(device)
         self.depth = depth
         self._up = torch.cuda.Stream(device=self.device)
@@ -25,6 +26,15 @@ class FrameStreamer:
         self._results = collections.deque()   # (pinned host tensor, device source kept alive, done event)
         self._host = [None] * (depth + 1)
         self._host_next = 0
+
+    def preallocate(self, image_shape, result_shape, image_dtype=torch.float32, result_dtype=torch.uint8):
+        """Allocate the device image buffers and the pinned result buffers now (pinning host memory costs
+        milliseconds; do it before the stream starts, not on the first frames)."""
+        for i in range(self.depth):
+            self._bufs[i] = torch.empty(image_shape, dtype=image_dtype, device=self.device)
+        for j in range(len(self._host)):
+            self._host[j] = torch.empty(result_shape, dtype=result_dtype).pin_memory()
+        return self
 
     # ---------------------------------------------------------------- uploads
     def stage(self, host_img):
