@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=9)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--seqs-per-gpu", type=int, default=2,
+                    help="extra leg at N=1: S concurrent sequences on one GPU (0 / 1 = skip)")
     ap.add_argument("--kernel-only", action="store_true", help="only the isolated kernel rooflines")
     ap.add_argument("--profile-steps", type=int, default=0,
                     help="bracket the first N timed steps with cudaProfilerStart/Stop (ncu --profile-from-start off)")
@@ -206,6 +208,50 @@ def run_b200(args, rank, world):
         dist.all_gather_object(gathered, dict(rank=rank, frames=args.steps, checksum=results["device"]["checksum"]))
     results["device"]["ms_max"], results["e2e"]["ms_max"] = float(t[0]), float(t[1])
     return results
+
+
+def run_multi_sequence(args, local_rank, S):
+    """S independent sequences on one GPU (BASELINE.json configs 3 / 4 run 2 sequences per GPU): one engine and one
+    stream per sequence, the host interleaves their frames; sub-wave kernels of one sequence fill SMs the other
+    leaves idle.  Returns aggregate frames/s over the S sequences (device events, inputs resident)."""
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    dev = torch.device("cuda", local_rank)
+    model = build_model()
+    n_frames = 1 + args.warmup + args.steps
+    gap = gap_rule(100 if n_frames <= 100 else n_frames)
+    engines, streams, clips = [], [], []
+    for q in range(S):
+        imgs, lab = make_clip(n_frames, 2000 + q)
+        clips.append(([im.to(dev) for im in imgs], lab.to(dev)))
+        engines.append(DeAOTInferEngine(model, local_rank, long_term_mem_gap=gap))
+        streams.append(torch.cuda.Stream(device=dev))
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        for q in range(S):
+            with torch.cuda.stream(streams[q]):
+                engines[q].add_reference_frame(clips[q][0][0], clips[q][1], obj_nums=[N_OBJ], frame_step=0)
+                for f in range(1, 1 + args.warmup):
+                    frame_step(engines[q], clips[q][0][f], (H, W))
+                    if f == 1:
+                        engines[q].precapture((H, W))
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for st in streams:
+            st.wait_event(e0)
+        for f in range(1 + args.warmup, n_frames):
+            for q in range(S):
+                with torch.cuda.stream(streams[q]):
+                    frame_step(engines[q], clips[q][0][f], (H, W))
+        for q, st in enumerate(streams):
+            done = torch.cuda.Event()
+            with torch.cuda.stream(st):
+                engines[q].aot_engines[0]._wait_write()          # the last write path belongs to the timed work
+                done.record()
+            torch.cuda.current_stream().wait_event(done)
+        e1.record()
+        torch.cuda.synchronize()
+    return S * args.steps / (e0.elapsed_time(e1) * 1e-3)
 
 
 def kernel_rooflines(dev):
@@ -378,6 +424,11 @@ def main():
                 "host_enqueue_ms_per_step": res["device"]["host_ms"] / args.steps, "roofline": lt,
                 "roofline_local": loc,
                 "bank_indexes": res["device"]["idx"]}
+        if world == 1 and args.seqs_per_gpu > 1:
+            line["multi_sequence"] = {"sequences_per_gpu": args.seqs_per_gpu, "unit": "frames/s",
+                                      "value": run_multi_sequence(args, local_rank, args.seqs_per_gpu),
+                                      "note": "same workload, S independent clips interleaved on S streams "
+                                              "(configs 3 / 4 shard 2 sequences per GPU); not the headline"}
         if world == 1 and not args.no_cpu_baseline:
             fps, cores = cpu_port_fps(12)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",

