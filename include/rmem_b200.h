@@ -206,6 +206,14 @@ int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, 
 int rmem_local_attn_aggregate(const void* banded, const void* v, const void* gate, void* out,
                               int h, int w, void* stream);
 
+/* The same operator in ONE kernel (flash-attention form, csrc/local_attn_fused.cu): scores, relative-position
+ * bias, border / window mask, softmax, aggregation and gate without materialising the probabilities --
+ *   out[q][c] = gate[q][c] * sum_t softmax_t( q.k[nbr(q,t)]/sqrt(128) + rel_bias[q][t] ) v[nbr(q,t)][c]
+ * q, k bf16 [h*w][128]; v, gate (or NULL), out bf16 [h*w][1024]; rel_bias f32 [h*w][ld_rel], ld_rel >= 225.
+ * This is what the engines call; the two-stage form above remains for callers that want local_attn itself. */
+int rmem_local_attn(const void* q, const void* k, const void* v, const float* rel_bias, int ld_rel,
+                    const void* gate, void* out, int h, int w, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Restricted long-term bank.  State lives on the device so the frame loop never synchronises:
  *   order     i32 [RMEM_MAX_BANK]  logical position (oldest first) -> slot; order[T..] = free slots

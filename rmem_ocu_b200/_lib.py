@@ -79,6 +79,7 @@ _SIGNATURES = {
     "rmem_local_banded_elems": [_c_int, _c_int],
     "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_local_attn_aggregate": [_c_void_p] * 4 + [_c_int, _c_int, _c_void_p],
+    "rmem_local_attn": [_c_void_p] * 4 + [_c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_groupnorm_nhwc": [_c_void_p] * 5 + [_c_int] * 4 + [_c_void_p] * 2,
     "rmem_upsample_add_nhwc": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int, _c_int,
                                _c_void_p],

@@ -123,6 +123,10 @@ int rmem_local_attn_scores(const void* q, const void* k, const float* rel_bias, 
                            float* probs, void* banded, int h, int w, void* stream) {
   return local_scores_launch(q, k, rel_bias, ld_rel, probs, banded, h, w, ST(stream));
 }
+int rmem_local_attn(const void* q, const void* k, const void* v, const float* rel_bias, int ld_rel,
+                    const void* gate, void* out, int h, int w, void* stream) {
+  return local_attn_fused_launch(q, k, v, rel_bias, ld_rel, gate, out, h, w, ST(stream));
+}
 int rmem_local_attn_aggregate(const void* banded, const void* v, const void* gate, void* out,
                               int h, int w, void* stream) {
   return local_aggregate_launch(banded, v, gate, out, h, w, ST(stream));

@@ -207,13 +207,15 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
 // pass 2 normalises. x = cat(x_a [L][Ca], x_b [L][C-Ca]).
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int L, int C,
-                int groups, double* __restrict__ ws) {
-  // block handles 8 rows; thread t covers channels t, t+256, ... (C <= 1024)
+                int groups, int rows_per_cta, double* __restrict__ ws) {
+  // block handles rows_per_cta rows (few CTAs: every CTA ends in fp64 atomics on the same 2 * groups words, and
+  // hundreds of contending atomics cost more than the reduction); thread t covers channels t, t+256, ... (C <= 1024)
   const int cpg = C / groups;
   __shared__ float sh_s[8][8], sh_q[8][8];   // [group][warp]
   float s[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int r = 0; r < 8; ++r) {
-    const int row = blockIdx.x * 8 + r;
+#pragma unroll 4
+  for (int r = 0; r < rows_per_cta; ++r) {
+    const int row = blockIdx.x * rows_per_cta + r;
     if (row >= L) break;
     int k = 0;
     for (int c = threadIdx.x; c < C; c += 256, ++k) {
@@ -246,19 +248,27 @@ __global__ void __launch_bounds__(256)
 gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 __nv_bfloat16* __restrict__ out, int L, int C, int groups, double* __restrict__ ws) {
+  // a thread owns four consecutive channels (one float4 in, four bf16 out); Ca, C and C / groups are multiples of 4
   const int cpg = C / groups;
   const double cnt = static_cast<double>(cpg) * L;
-  const size_t total = static_cast<size_t>(L) * C;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+  const size_t total4 = static_cast<size_t>(L) * C / 4;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int row = static_cast<int>(i / C), c = static_cast<int>(i - static_cast<size_t>(row) * C);
+    const int row = static_cast<int>((i * 4) / C), c = static_cast<int>(i * 4 - static_cast<size_t>(row) * C);
     const int g = c / cpg;
-    const double mean = ws[2 * g] / cnt;
-    const double var = ws[2 * g + 1] / cnt - mean * mean;
+    const double mean_d = ws[2 * g] / cnt;
+    const double var = ws[2 * g + 1] / cnt - mean_d * mean_d;
+    const float mean = static_cast<float>(mean_d);
     const float rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
-    const float v = c < Ca ? xa[static_cast<size_t>(row) * Ca + c]
-                           : xb[static_cast<size_t>(row) * (C - Ca) + (c - Ca)];
-    out[i] = __float2bfloat16((v - static_cast<float>(mean)) * rstd * gamma[c] + beta[c]);
+    const float4 v = c < Ca ? *reinterpret_cast<const float4*>(xa + static_cast<size_t>(row) * Ca + c)
+                            : *reinterpret_cast<const float4*>(xb + static_cast<size_t>(row) * (C - Ca) + (c - Ca));
+    const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+    const float4 be = *reinterpret_cast<const float4*>(beta + c);
+    uint2 pk;
+    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
+    o[0] = __floats2bfloat162_rn((v.x - mean) * rstd * ga.x + be.x, (v.y - mean) * rstd * ga.y + be.y);
+    o[1] = __floats2bfloat162_rn((v.z - mean) * rstd * ga.z + be.z, (v.w - mean) * rstd * ga.w + be.w);
+    *reinterpret_cast<uint2*>(out + i * 4) = pk;
   }
   gn_ws_release(ws, 2 * groups);
 }
@@ -267,10 +277,11 @@ int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const floa
                             const float* beta, void* out, int L, int C, int groups, void* workspace,
                             cudaStream_t stream) {
   if (groups < 1 || groups > 8 || C > 1024 || (C % groups) || ((C / groups) % 32) || Ca > C ||
-      (Ca < C && !xb))
+      (Ca < C && !xb) || (Ca & 3) || (C & 3))
     return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
-  gn_stats_kernel<<<(L + 7) / 8, 256, 0, stream>>>(xa, Ca, xb, L, C, groups,
-                                                    static_cast<double*>(workspace));
+  const int rows = (L + 63) / 64 < 8 ? 8 : (L + 63) / 64;        // ~64 CTAs
+  gn_stats_kernel<<<(L + rows - 1) / rows, 256, 0, stream>>>(xa, Ca, xb, L, C, groups, rows,
+                                                              static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
   gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta, static_cast<__nv_bfloat16*>(out), L,
                                            C, groups, static_cast<double*>(workspace));

@@ -61,6 +61,8 @@ int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg
 size_t local_banded_elems(int h, int w);
 int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
                         int h, int w, cudaStream_t stream);
+int local_attn_fused_launch(const void* q, const void* k, const void* v, const float* rel, int ld_rel,
+                            const void* gate, void* out, int h, int w, cudaStream_t stream);
 int local_aggregate_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream);
 int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,

@@ -404,6 +404,9 @@ class DeAOTEngine:
         self.trace = None          # optional dict: per-layer intermediates for the parity tests
         self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
         self.fork_branches = os_env_flag("RMEM_FORK_BRANCHES", True)
+        # single-kernel local attention (csrc/local_attn_fused.cu): parity-green but 19 us against 16.5 us for
+        # the scores + aggregation pair at 480p, so it is opt-in until it wins
+        self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False)
         self._side = None
         # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
         # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
@@ -564,8 +567,11 @@ class DeAOTEngine:
             with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
                 # short-term 15x15 local attention over the previous frame, gate, dw5x5
                 ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
-                ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
-                ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
+                if self.local_fused:
+                    ops.local_attn(ws.kcur[i], ws.kprev[i], ws.vprev[i], ws.rel, ws.u[i], ws.gated_b, h, w)
+                else:
+                    ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
+                    ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
                 ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
             # long-term attention over the bank (TPE folded into a per-frame score bias), gate, dw5x5
             ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)

@@ -190,6 +190,14 @@ def local_attn_scores(q, k, rel_bias, probs, banded, h, w):
     _count("rmem_local_attn_scores")
 
 
+def local_attn(q, k, v, rel_bias, gate, out, h, w):
+    """Fused 15x15 local gated attention: q, k bf16 [L,128]; v, gate, out bf16 [L,1024]; rel_bias f32 [L, ld]."""
+    _chk_cuda(q, k, v, rel_bias, out)
+    _lib.check(_lib.lib().rmem_local_attn(_p(q), _p(k), _p(v), _p(rel_bias), rel_bias.stride(0), _p(gate), _p(out),
+                                          h, w, _stream()), "rmem_local_attn")
+    _count("rmem_local_attn")
+
+
 def local_attn_aggregate(banded, v, gate, out, h, w):
     _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(banded), _p(v), _p(gate), _p(out), h, w, _stream()),
                "rmem_local_attn_aggregate")

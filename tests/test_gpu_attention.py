@@ -92,6 +92,15 @@ def test_local_attention_vs_oracle(lib_built, h, w):
     assert (probs.cpu() - probs_ref).abs().max().item() < 2e-3
     assert (probs.sum(1) - 1).abs().max().item() < 1e-4
     assert _rel(out.cpu(), gated_ref) < 2e-2
+    # the fused single-kernel form (what the engines call) -- also without a gate
+    out_f = torch.empty_like(out)
+    ops.local_attn(qd, kd, vd, rel, ud, out_f, h, w)
+    out_n = torch.empty_like(out)
+    ops.local_attn(qd, kd, vd, rel, None, out_n, h, w)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out_f.float()).all()
+    assert _rel(out_f.cpu(), gated_ref) < 2e-2
+    assert _rel(out_n.cpu(), agg_ref.view(L, 1024)) < 2e-2
 
 
 def test_bank_score_evict_bit_exact_vs_oracle(lib_built):

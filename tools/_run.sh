@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu.log
-timeout 600 python tools/bench_ksweep.py > gpurun_out/ksweep.jsonl 2> gpurun_out/ksweep.err; echo "ksweep exit $?"; cat gpurun_out/ksweep.jsonl | cut -c1-200
+timeout 200 python bench.py --kernel-only > gpurun_out/plain_k.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'local_attn_kernel' -s 3 -c 2 -o gpurun_out/prof_local_fused python bench.py --kernel-only > gpurun_out/ncu_full3.log 2>&1; echo "ncu full local exit $?"
