@@ -206,3 +206,22 @@ def test_720p_ten_objects_vs_oracle(lib_built, monkeypatch):
     agree = [(a == b).float().mean().item() for a, b in zip(masks, o_masks)]
     print("720p mask agreement", [round(a, 5) for a in agree])
     assert min(agree) >= 0.999, agree
+
+
+def test_fused_local_attention_in_the_engine(lib_built, monkeypatch):
+    """RMEM_LOCAL_FUSED=1 swaps the scores + aggregation kernels for the single flash-style kernel
+    (csrc/local_attn_fused.cu); the clip must come out the same (indexes equal, masks >= 99.9 %, logits 1e-2:
+    the fused kernel rounds its probabilities per key block, the pair rounds them once)."""
+    H, W, n, latter = 240, 432, 8, 2
+    imgs, lab = _clip(H, W, n, 3)
+    outs = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("RMEM_LOCAL_FUSED", fused)
+        m, _ = _models(latter)
+        outs.append(_run_infer(m, imgs, lab, H, W, 3, gap=1))
+    (ma, la, ia, ea), (mb, lb, ib, eb) = outs
+    assert not ea.aot_engines[0].local_fused and eb.aot_engines[0].local_fused
+    assert ia == ib
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-2, f
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999

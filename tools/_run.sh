@@ -1,3 +1,6 @@
 mkdir -p gpurun_out
-timeout 200 python bench.py --kernel-only > gpurun_out/plain_k.log 2>&1 &&
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:'local_attn_kernel' -s 3 -c 2 -o gpurun_out/prof_local_fused python bench.py --kernel-only > gpurun_out/ncu_full3.log 2>&1; echo "ncu full local exit $?"
+timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py > gpurun_out/bench_default.log 2>&1; echo "bench exit $?"; tail -1 gpurun_out/bench_default.log | cut -c1-200
+for n in 8; do
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 90 --warmup 9 > gpurun_out/bench_n$n.log 2>&1; echo "bench n$n exit $?"; tail -1 gpurun_out/bench_n$n.log | cut -c1-200
+done
