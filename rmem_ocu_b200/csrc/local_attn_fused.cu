@@ -5,11 +5,11 @@
 // (the two-kernel form of csrc/local_attn.cu writes them to a banded buffer and reads them back 8 times).
 //
 // A CTA owns an 8 x 16 query tile (128 queries = the 128 TMEM lanes) and 128 value channels.  Its 22 x 30 key
-// halo is cut into 11 blocks of two halo rows (2 x 32 key slots, 64 keys); per block
-//   TMA     : K block [64 keys][128 ch] and V block [64 keys][128 ch] as 4-D boxes straight out of the
+// halo is cut into 6 blocks of four halo rows (4 x 32 key slots, 128 keys); per block
+//   TMA     : K block [128 keys][128 ch] and V block [128 keys][128 ch] as 4-D boxes straight out of the
 //             token-major maps; out-of-image keys are zero-filled (= the reference's F.pad) and masked below
-//   tcgen05 : S_b = Q K_b^T (128 x 64, TMEM, double buffered), then O += P_b V_b with P_b read from TMEM
-//   softmax : 16 warps, four threads per query; a thread owns half of ONE halo row (16 key slots), adds the
+//   tcgen05 : S_b = Q K_b^T (128 x 128, TMEM, double buffered), then O += P_b V_b with P_b read from TMEM
+//   softmax : 16 warps, four threads per query; a thread owns ONE halo row of the block (32 key slots), adds the
 //             relative-position bias rel[q][dy*15 + dx], masks slots outside the query's window or the image
 //             (-1e8 in the reference: probability exactly 0 in fp32), keeps a running max / sum with lazy
 //             rescaling of O, and writes bf16 P over the S tile.
@@ -26,12 +26,14 @@ constexpr int kWin = 15, kMaxDis = 7;
 constexpr int kTileH = 8, kTileW = 16;                  // 128 queries
 constexpr int kHaloH = kTileH + 2 * kMaxDis;            // 22 halo rows
 constexpr int kBoxW = 32;                               // 30 halo columns + 2
-constexpr int kBlocks = kHaloH / 2;                     // 11 key blocks of 64 keys
+constexpr int kBlockRows = 4;                           // halo rows per key block
+constexpr int kBlockKeys = kBlockRows * kBoxW;          // 128 key slots per block
+constexpr int kBlocks = (kHaloH + kBlockRows - 1) / kBlockRows;   // 6 (the last block's rows 22, 23 are masked)
 constexpr int kDV = 128;                                // value channels per CTA
-constexpr int kStages = 4;
+constexpr int kStages = 2;
 constexpr uint32_t kQBytes = 128 * 128 * 2;             // [2 cblk][128 q][64 ch]
-constexpr uint32_t kKBytes = 64 * 128 * 2;              // [2 cblk][64 keys][64 ch]
-constexpr uint32_t kVBytes = 64 * kDV * 2;              // [2 cblk][64 keys][64 ch]
+constexpr uint32_t kKBytes = kBlockKeys * 128 * 2;      // [2 cblk][128 keys][64 ch]
+constexpr uint32_t kVBytes = kBlockKeys * kDV * 2;      // [2 cblk][128 keys][64 ch]
 constexpr int kSoftmaxWarps = 16;
 constexpr int kParts = kSoftmaxWarps / 4;               // threads per query
 constexpr uint32_t kXchBytes = 2 * kParts * 128 * 4;    // row-max exchange, one buffer per S buffer
@@ -40,8 +42,8 @@ constexpr uint32_t kRelBytes = 128 * kRelLd * 2;        // 58 KB: rel[q][tap] * 
 constexpr uint32_t kSmem = kQBytes + kStages * (kKBytes + kVBytes) + kRelBytes + kXchBytes + 256 + 1024;
 static_assert(kSmem <= 232448, "exceeds the 227 KB shared memory of an sm_100 CTA");
 constexpr int kThreads = 64 + 32 * kSoftmaxWarps;
-constexpr uint32_t kTmemCols = 256;                     // S: 2 x 64, O: 128
-constexpr uint32_t kTmemS = 0, kTmemO = 128;
+constexpr uint32_t kTmemCols = 512;                     // S: 2 x 128, O: 128
+constexpr uint32_t kTmemS = 0, kTmemO = 256;
 constexpr float kRescale = 8.0f;
 
 struct Params {
@@ -114,16 +116,17 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         const uint32_t ph = ((b / kStages) - 1) & 1;
         if (b >= kStages) mbar_wait(k_empty + st, ph);
         mbar_expect_tx(k_full + st, kKBytes);
-        tma_load_4d(sK + st * kKBytes, &tm_k, k_full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, 0);
+        tma_load_4d(sK + st * kKBytes, &tm_k, k_full + st, 0, x0 - kMaxDis, y0 - kMaxDis + kBlockRows * b, 0);
         if (b >= kStages) mbar_wait(v_empty + st, ph);
         mbar_expect_tx(v_full + st, kVBytes);
-        tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, dv * (kDV / 64));
+        tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, x0 - kMaxDis, y0 - kMaxDis + kBlockRows * b,
+                    dv * (kDV / 64));
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t idesc_qk = make_idesc_bf16(128, kBlockKeys, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, kDV, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
       auto issue_qk = [&](int b) {
@@ -131,12 +134,12 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         mbar_wait(k_full + st, (b / kStages) & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + st * kKBytes);
-        const uint32_t d = tmem_base + kTmemS + (b & 1) * 64;
+        const uint32_t d = tmem_base + kTmemS + (b & 1) * kBlockKeys;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
           const uint32_t blk = ks >> 2, within = ks & 3;
           mma_bf16_ss(d, make_desc_sw128(q_addr + blk * (128 * 128) + within * 32, 16, 1024),
-                      make_desc_sw128(k_addr + blk * (64 * 128) + within * 32, 16, 1024), idesc_qk, ks > 0);
+                      make_desc_sw128(k_addr + blk * (kBlockKeys * 128) + within * 32, 16, 1024), idesc_qk, ks > 0);
         }
         tc_commit(k_empty + st);
         tc_commit(s_full + (b & 1));
@@ -152,11 +155,11 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         mbar_wait(v_full + st, (b / kStages) & 1);
         tc_fence_after();
         const uint32_t v_addr = smem_u32(sV + st * kVBytes);
-        const uint32_t p_tmem = tmem_base + kTmemS + (b & 1) * 64;       // bf16 P: 32 columns
+        const uint32_t p_tmem = tmem_base + kTmemS + (b & 1) * kBlockKeys;       // bf16 P: 64 columns
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-          mma_bf16_ts(tmem_base + kTmemO, p_tmem + ks * 8, make_desc_sw128(v_addr + ks * (16 * 128), 64 * 128, 1024),
-                      idesc_pv, (b > 0) || (ks > 0));
+        for (int ks = 0; ks < kBlockKeys / 16; ++ks)
+          mma_bf16_ts(tmem_base + kTmemO, p_tmem + ks * 8,
+                      make_desc_sw128(v_addr + ks * (16 * 128), kBlockKeys * 128, 1024), idesc_pv, (b > 0) || (ks > 0));
         tc_commit(v_empty + st);
         tc_commit(pv_done + (b & 1));
       }
@@ -165,11 +168,11 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   } else {
     // ------------------------------------------------------------------ softmax + epilogue
     // 16 warps, four threads per query: warp w serves TMEM lane quarter w % 4; part = (w - 2) / 4 selects the halo
-    // row of the block (hf) and which 16 of its 32 key slots (cq) the thread owns.  The per-element work (bias
+    // row of the block (32 key slots) the thread owns.  The per-element work (bias
     // fetch, mask, exponential) is instruction- and latency-bound, so it is spread over many warps.
     const int quarter = warp & 3;
     const int part = (warp - 2) >> 2;
-    const int hf = part >> 1, cq = part & 1;
+    const int hr = part;                          // halo row of the block this thread owns (32 key slots)
     const int row = quarter * 32 + lane;          // query inside the tile = TMEM lane
     const int qy_l = row >> 4, qx_l = row & 15;
     const int gy = y0 + qy_l, gx = x0 + qx_l;
@@ -198,13 +201,11 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     }
     named_bar_sync(5, 32 * kSoftmaxWarps);
     const __half* rel_q = srel + row * kRelLd;
-    // key slots (of this thread's 16) the query may attend to, whatever the halo row: inside its 15-wide window
-    // and inside the image
+    // key slots of a halo row the query may attend to, whatever the row: inside its 15-wide window and the image
     uint32_t colmask = 0;
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int slot = cq * 16 + i;
-      const int dx = slot - qx_l, kx = x0 - kMaxDis + slot;
+    for (int i = 0; i < 32; ++i) {
+      const int dx = i - qx_l, kx = x0 - kMaxDis + i;
       if (q_ok && dx >= 0 && dx < kWin && kx >= 0 && kx < p.w) colmask |= 1u << i;
     }
     const uint32_t o_addr = tmem_base + lane_addr + kTmemO + part * (kDV / kParts);
@@ -212,28 +213,28 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     for (int b = 0; b < kBlocks; ++b) {
       const int sb = b & 1;
       // this thread's halo row: window row dy of the query, image row ky; per slot: window column slot - qx_l
-      const int hy = 2 * b + hf;
+      const int hy = kBlockRows * b + hr;
       const int dy = hy - qy_l;
       const int ky = y0 - kMaxDis + hy;
       const bool row_in = dy >= 0 && dy < kWin && ky >= 0 && ky < p.h;
       const uint32_t mask = row_in ? colmask : 0u;
       const bool live = __any_sync(0xffffffffu, mask != 0u);   // does any query of this warp see these slots?
-      float x[16];
+      float x[32];
       float mx = -INFINITY;
       if (live) {
         // relative-position bias of the taps (shared memory), fetched while S is still being computed
-        float bias[16];
-        const __half* rel_row = rel_q + dy * kWin + cq * 16 - qx_l;
+        float bias[32];
+        const __half* rel_row = rel_q + dy * kWin - qx_l;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) bias[i] = (mask >> i) & 1u ? __half2float(rel_row[i]) : -INFINITY;
+        for (int i = 0; i < 32; ++i) bias[i] = (mask >> i) & 1u ? __half2float(rel_row[i]) : -INFINITY;
         mbar_wait(s_full + sb, (b >> 1) & 1);
         tc_fence_after();
-        uint32_t sr[16];
-        tmem_ld16(tmem_base + lane_addr + kTmemS + sb * 64 + hf * 32 + cq * 16, sr);
+        uint32_t sr[32];
+        tmem_ld32(tmem_base + lane_addr + kTmemS + sb * kBlockKeys + hr * 32, sr);
         tmem_ld_wait();
         float mx1 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 16; i += 2) {
+        for (int i = 0; i < 32; i += 2) {
           x[i] = fmaf(__uint_as_float(sr[i]), c, bias[i]);      // -inf where masked
           x[i + 1] = fmaf(__uint_as_float(sr[i + 1]), c, bias[i + 1]);
           mx = fmaxf(mx, x[i]);
@@ -266,12 +267,12 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       }
       l_sum *= scale;
       m_used = m_new;
-      uint32_t packed[8];
+      uint32_t packed[16];
       if (live) {
         const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;     // no valid key yet: exp2(-inf + 0) = 0
         float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
-        for (int i = 0; i < 16; i += 2) {
+        for (int i = 0; i < 32; i += 2) {
           const float p0 = fast_exp2(x[i] + neg_m), p1 = fast_exp2(x[i + 1] + neg_m);
           acc0 += p0;
           acc1 += p1;
@@ -280,11 +281,11 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         l_sum += acc0 + acc1;
       } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) packed[i] = 0u;
+        for (int i = 0; i < 16; ++i) packed[i] = 0u;
       }
-      // P (bf16, 32 columns) overwrites the first half of this S buffer; every thread of the row holds its S
+      // P (bf16, 64 columns) overwrites the first half of this S buffer; every thread of the row holds its S
       // values in registers (it passed tcgen05.wait::ld before the row barrier)
-      tmem_st8(tmem_base + lane_addr + kTmemS + sb * 64 + hf * 16 + cq * 8, packed);
+      tmem_st16(tmem_base + lane_addr + kTmemS + sb * kBlockKeys + hr * 16, packed);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full + sb);
@@ -299,12 +300,13 @@ local_attn_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     }
     mbar_wait(o_full, 0);
     tc_fence_after();
-    // the last block used exchange buffer (kBlocks - 1) & 1 = 0; its readers may still be there: use buffer 1
-    xch[(1 * kParts + part) * 128 + row] = l_sum;
+    // the last block used exchange buffer (kBlocks - 1) & 1; its readers may still be there: use the other one
+    constexpr int kLBuf = kBlocks & 1;
+    xch[(kLBuf * kParts + part) * 128 + row] = l_sum;
     named_bar_sync(row_bar, 32 * kParts);
     float l_tot = 0.f;
 #pragma unroll
-    for (int k = 0; k < kParts; ++k) l_tot += xch[(1 * kParts + k) * 128 + row];
+    for (int k = 0; k < kParts; ++k) l_tot += xch[(kLBuf * kParts + k) * 128 + row];
     const float inv = l_tot > 0.f ? 1.f / l_tot : 0.f;
     {
       uint32_t orow[32];
@@ -355,7 +357,7 @@ int local_attn_fused_launch(const void* q, const void* k, const void* v, const f
     const uint64_t dims[4] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 2};
     const uint64_t strides[3] = {128 * 2, static_cast<uint64_t>(w) * 128 * 2, 128};
     const uint32_t box_q[4] = {64, kTileW, kTileH, 2};
-    const uint32_t box_k[4] = {64, kBoxW, 2, 2};
+    const uint32_t box_k[4] = {64, kBoxW, kBlockRows, 2};
     CUresult r = fn(&tm_q, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(q), dims, strides, box_q, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -368,7 +370,7 @@ int local_attn_fused_launch(const void* q, const void* k, const void* v, const f
   {
     const uint64_t dims[4] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 16};
     const uint64_t strides[3] = {1024 * 2, static_cast<uint64_t>(w) * 1024 * 2, 128};
-    const uint32_t box[4] = {64, kBoxW, 2, kDV / 64};
+    const uint32_t box[4] = {64, kBoxW, kBlockRows, kDV / 64};
     CUresult r = fn(&tm_v, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v), dims, strides, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

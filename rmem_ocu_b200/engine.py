@@ -404,7 +404,7 @@ class DeAOTEngine:
         self.trace = None          # optional dict: per-layer intermediates for the parity tests
         self.use_cuda_graphs = os_env_flag("RMEM_CUDA_GRAPHS", True)
         self.fork_branches = os_env_flag("RMEM_FORK_BRANCHES", True)
-        # single-kernel local attention (csrc/local_attn_fused.cu): parity-green but 19 us against 16.5 us for
+        # single-kernel local attention (csrc/local_attn_fused.cu): parity-green but 17.5 us against 16.5 us for
         # the scores + aggregation pair at 480p, so it is opt-in until it wins
         self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False)
         self._side = None

@@ -1,6 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py > gpurun_out/bench_default.log 2>&1; echo "bench exit $?"; tail -1 gpurun_out/bench_default.log | cut -c1-200
-for n in 8; do
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 90 --warmup 9 > gpurun_out/bench_n$n.log 2>&1; echo "bench n$n exit $?"; tail -1 gpurun_out/bench_n$n.log | cut -c1-200
-done
+timeout 600 python -m pytest tests/test_gpu_attention.py tests/test_gpu_engine.py -x -q -m gpu -k "local" > gpurun_out/pytest_local.log 2>&1; echo "pytest local exit $?"; tail -3 gpurun_out/pytest_local.log | cut -c1-300
+timeout 200 python bench.py --kernel-only > gpurun_out/plain_k.log 2>&1; tail -1 gpurun_out/plain_k.log | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print(d['roofline_local'])"
