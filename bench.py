@@ -78,11 +78,20 @@ class ClockSampler:
         self._stop = threading.Event()
         self._t = None
 
+    def _nvml_open(self):
+        """NVML is initialised on the caller's thread BEFORE the timed region: nvmlInit takes ~100 ms and contends
+        with kernel launches for driver locks."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index))
+        except Exception:
+            self._nvml = None
+
     def _run_nvml(self):
-        """NVML polling every ~5 ms (an nvidia-smi process takes longer to start than a short timed region)."""
-        import pynvml
-        pynvml.nvmlInit()
-        hnd = pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
+        """NVML polling every 20 ms (an nvidia-smi process takes longer to start than a short timed region; faster
+        polling measurably slows the launching thread)."""
+        pynvml, hnd = self._nvml
         mx = float(pynvml.nvmlDeviceGetMaxClockInfo(hnd, pynvml.NVML_CLOCK_SM))
         bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
         while not self._stop.is_set():
@@ -91,13 +100,14 @@ class ClockSampler:
             for n, b in bits.items():
                 if r & b:
                     self.reasons.add(n)
-            self._stop.wait(0.005)
+            self._stop.wait(0.02)
 
     def _run(self):
-        try:
-            return self._run_nvml()
-        except Exception:
-            pass
+        if self._nvml is not None:
+            try:
+                return self._run_nvml()
+            except Exception:
+                pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -116,6 +126,7 @@ class ClockSampler:
             self._stop.wait(0.2)
 
     def __enter__(self):
+        self._nvml_open()
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
         return self

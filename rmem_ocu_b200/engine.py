@@ -220,6 +220,10 @@ class InferenceResNet:
             self.blocks.append(stage)
         self.proj = cv(projector)
         self.fused = hasattr(torch, "cudnn_convolution_relu") and os_env_flag("RMEM_FUSED_CONV", True)
+        # measured: forking the three projection shortcuts costs ~2 % (980 vs 1000 frames/s) -- the convolutions
+        # already fill the GPU and the extra graph edges add latency -- so it stays off
+        self.fork = self.fused and os_env_flag("RMEM_FORK_ENCODER", False)
+        self._side_streams = {}                    # one side stream per calling stream (engines may run concurrently)
 
     @staticmethod
     def _conv(x, c, relu):
@@ -269,9 +273,30 @@ class InferenceResNet:
         xs = []
         for stage in self.blocks:
             for (c1, c2, c3, down) in stage:
-                idt = x if down is None else F.conv2d(x, down[0], down[1], down[2], down[3])
+                forked = down is not None and self.fork
+                if forked:
+                    # the projection shortcut only shares its input with conv1 -> conv2: a parallel branch (side
+                    # stream; inside a captured graph a parallel path) that meets the trunk again in conv3's add
+                    cur = torch.cuda.current_stream()
+                    side = self._side_streams.get(cur.cuda_stream)
+                    if side is None:
+                        side = self._side_streams[cur.cuda_stream] = torch.cuda.Stream(device=x.device)
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    side.wait_event(ev)
+                    with torch.cuda.stream(side):
+                        idt = F.conv2d(x, down[0], down[1], down[2], down[3])
+                        done = torch.cuda.Event()
+                        done.record()
+                    if not torch.cuda.is_current_stream_capturing():      # graph pools never recycle mid-capture
+                        x.record_stream(side)
+                        idt.record_stream(cur)
+                else:
+                    idt = x if down is None else F.conv2d(x, down[0], down[1], down[2], down[3])
                 if self.fused:
                     y = self._conv(self._conv(x, c1, True), c2, True)
+                    if forked:
+                        torch.cuda.current_stream().wait_event(done)
                     x = torch.cudnn_convolution_add_relu(y, c3[0], idt, 1.0, c3[1], c3[2], c3[3], (1, 1), 1)
                 else:
                     y = F.relu(F.conv2d(x, c1[0], c1[1], c1[2], c1[3]))

@@ -1,4 +1,5 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_attention.py tests/test_gpu_engine.py -x -q -m gpu -k "local" > gpurun_out/pytest_local.log 2>&1; echo "pytest local exit $?"; tail -3 gpurun_out/pytest_local.log | cut -c1-300
-timeout 200 python bench.py --kernel-only > gpurun_out/plain_k.log 2>&1; tail -1 gpurun_out/plain_k.log | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print(d['roofline_local'])"
+for v in "RMEM_FORK_ENCODER=1" "RMEM_FORK_ENCODER=0" "RMEM_FORK_ENCODER=1" "RMEM_FORK_ENCODER=0"; do
+env $v timeout 400 python bench.py --steps 90 --warmup 9 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/bench9.log 2>&1; python -c "
+import json; d=json.loads(open('gpurun_out/bench9.log').read().strip().splitlines()[-1]); print('$v', d['value'], d['e2e']['value'], d['host_enqueue_ms_per_step'])"
+done
