@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=9)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefetch", action="store_true",
+                    help="do not start the next frame's encoder pass during the current frame")
     ap.add_argument("--seqs-per-gpu", type=int, default=2,
                     help="extra leg at N=1: S concurrent sequences on one GPU (0 / 1 = skip)")
     ap.add_argument("--kernel-only", action="store_true", help="only the isolated kernel rooflines")
@@ -143,10 +145,12 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(sm)}
 
 
-def frame_step(eng, img_dev, out_hw):
-    """One step: read path + write path of one frame (device-resident image in, label map out)."""
+def frame_step(eng, img_dev, out_hw, next_img=None):
+    """One step: read path + write path of one frame (device-resident image in, label map out).  ``next_img``:
+    the following frame, whose encoder pass the engine starts now on a second stream (it is part of the NEXT
+    step's work, overlapped with this step's LSTT + decoder; every step still runs exactly one encoder pass)."""
     from rmem_ocu_b200 import ops
-    logit = eng.match_propogate_one_frame(img_dev, output_size=out_hw)
+    logit = eng.match_propogate_one_frame(img_dev, output_size=out_hw, next_img=next_img)
     label = ops.argmax_label(logit)                              # = argmax(softmax(.)), evaluator.py:430-441
     if tuple(label.shape[-2:]) != tuple(eng.input_size_2d):
         label_in = F.interpolate(label, size=eng.input_size_2d, mode="nearest")      # evaluator.py:518-522
@@ -167,7 +171,10 @@ def run_b200(args, rank, world):
     model = build_model()
     n_frames = 1 + args.warmup + args.steps
     gap = gap_rule(100 if n_frames <= 100 else n_frames)
-    imgs, lab = make_clip(n_frames, 1000 + rank, pinned=True)
+    # one image beyond the clip: the last timed step also starts an encoder pass ahead, so that the timed region
+    # holds exactly `steps` encoder passes (the first timed frame's pass ran during the last warm-up step)
+    imgs, lab = make_clip(n_frames + 1, 1000 + rank, pinned=True)
+    pf = not args.no_prefetch
 
     def barrier():
         torch.cuda.synchronize()
@@ -182,10 +189,11 @@ def run_b200(args, rank, world):
         host_out = torch.empty(H, W, dtype=torch.uint8).pin_memory()
         with torch.no_grad():
             eng.add_reference_frame(imgs[0].to(dev), lab.to(dev), obj_nums=[N_OBJ], frame_step=0)
+            warm = dev_imgs if dev_imgs is not None else [None] + [imgs[f].to(dev) for f in range(1, 2 + args.warmup)]
             for f in range(1, 1 + args.warmup):
-                frame_step(eng, imgs[f].to(dev) if dev_imgs is None else dev_imgs[f], (H, W))
+                frame_step(eng, warm[f], (H, W), warm[f + 1] if pf else None)
                 if f == 1:
-                    eng.precapture((H, W))      # CUDA graphs for every bank length, recorded during warm-up
+                    eng.precapture((H, W), prefetch=pf)   # CUDA graphs for every bank length, recorded during warm-up
             barrier()
             launches0 = ops.LAUNCHES
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -198,6 +206,8 @@ def run_b200(args, rank, world):
                     # host frames in, host masks out, every frame: uploads and read-backs are double-buffered on
                     # copy streams (rmem_ocu_b200/pipeline.py), each mask is consumed on the host one frame late
                     fs.stage(imgs[first])
+                    fs.stage(imgs[first + 1])
+                    x = fs.acquire()
                 for f in range(first, n_frames):
                     if mode == "device" and args.profile_steps:
                         if f == first:
@@ -206,13 +216,14 @@ def run_b200(args, rank, world):
                             torch.cuda.synchronize()
                             torch.cuda.profiler.stop()
                     if mode == "device":
-                        label = frame_step(eng, dev_imgs[f], (H, W))
+                        label = frame_step(eng, dev_imgs[f], (H, W), dev_imgs[f + 1] if pf else None)
                     else:
-                        x = fs.acquire()
-                        if f + 1 < n_frames:
-                            fs.stage(imgs[f + 1])                            # pinned host image -> device
-                        label = frame_step(eng, x, (H, W))
-                        fs.release()
+                        x_next = fs.acquire()                                # frame f + 1 (uploaded a step ago)
+                        if f + 2 <= n_frames:
+                            fs.stage(imgs[f + 2])                            # pinned host image -> device
+                        label = frame_step(eng, x, (H, W), x_next if pf else None)
+                        fs.release(x)                  # the current stream has waited for the pass that read x
+                        x = x_next
                         fs.push_result(label[0, 0].to(torch.uint8))          # device label map -> pinned host
                         if fs.pending_results() > 1:
                             host_out = fs.pop_result()

@@ -439,6 +439,14 @@ class DeAOTEngine:
         self._wstream = None
         self._w_done = None
         self._graph_pool_w = None
+        # encoder prefetch (match_propogate_one_frame(..., next_img=)): the next frame's encoder runs on its own
+        # stream, into a staging set of embeddings, while this frame's LSTT + decoder run
+        self._estream = None
+        self._enc_done = None        # event: the prefetched embeddings are complete
+        self._stage_free = None      # event: the staging set has been copied out, the encoder may overwrite it
+        self._prefetched = None      # staging embeddings of the frame encoded ahead (list) or None
+        self._cur_embs = None        # the set the LSTT / decoder graphs read in prefetch mode
+        self._graph_pool_e = None
         self._graphs = {}
         self._graph_pool = None
         self.restart_engine()
@@ -483,6 +491,7 @@ class DeAOTEngine:
             self.ws = self._new_workspace(h, w, n_slots)
             self._wait_write()
             self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
+            self._graph_pool_e, self._cur_embs, self._prefetched = None, None, None
 
     @property
     def long_memories_indexes(self):
@@ -695,6 +704,8 @@ class DeAOTEngine:
         static_in = list(inputs) if alias else [torch.empty(t.shape, dtype=t.dtype, device=self.device)
                                                  for t in inputs]
         is_write = key[0] == "write"
+        if key[0] == "enc":                                       # may replay concurrently with the read graphs
+            return self._capture_enc(key, body, static_in)
         pool = self._graph_pool_w if is_write else self._graph_pool
         launches0 = ops.LAUNCHES
         g = torch.cuda.CUDAGraph()
@@ -708,6 +719,19 @@ class DeAOTEngine:
             self._graph_pool_w = g.pool()
         elif not is_write and self._graph_pool is None:
             self._graph_pool = g.pool()
+        return ent
+
+    def _capture_enc(self, key, body, static_in):
+        launches0 = ops.LAUNCHES
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, pool=self._graph_pool_e):
+            out = body(*static_in)
+        ent = (g, static_in, out, ops.LAUNCHES - launches0)
+        ops.LAUNCHES = launches0
+        self._graphs[key] = ent
+        if self._graph_pool_e is None:
+            self._graph_pool_e = g.pool()
         return ent
 
     def _run(self, key, body, inputs, alias=False):
@@ -732,9 +756,43 @@ class DeAOTEngine:
         ops.LAUNCHES += n_kernels
         return out
 
-    def precapture(self, output_size=None):
+    def _launch_encoder(self, img):
+        """Encode ``img`` on the encoder stream (ordered after the point the current stream has reached and after
+        the staging set was last copied out); the result waits in the staging set."""
+        if self._estream is None:
+            self._estream = torch.cuda.Stream(device=self.device)
+        es = self._estream
+        ready = torch.cuda.Event()
+        ready.record()
+        es.wait_event(ready)
+        if self._stage_free is not None:
+            es.wait_event(self._stage_free)
+        if img.is_cuda:
+            img.record_stream(es)
+        with torch.cuda.stream(es):
+            embs = list(self._run(("enc",), self.encode_image, [img]))
+            self._enc_done = torch.cuda.Event()
+            self._enc_done.record()
+        self._prefetched = embs
+
+    def _take_prefetched(self):
+        """Staging set -> the set the read graphs are recorded on (SM copies on the current stream)."""
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._enc_done)
+        embs, self._prefetched = self._prefetched, None
+        if self._cur_embs is None or any(c.shape != e.shape for c, e in zip(self._cur_embs, embs)):
+            self._cur_embs = [torch.empty_like(e) for e in embs]
+        for dst, src in zip(self._cur_embs, embs):
+            src.record_stream(cur)
+            torch.mul(src, 1, out=dst)
+        self._stage_free = torch.cuda.Event()
+        self._stage_free.record()
+        return self._cur_embs
+
+    def precapture(self, output_size=None, prefetch=False):
         """Capture the read / write graphs of every bank length now (capturing records, it does not
-        execute, so the sequence state is untouched). Call after the first propagated frame."""
+        execute, so the sequence state is untouched). Call after the first propagated frame.  ``prefetch``: record
+        the read graphs on the embedding set used by ``match_propogate_one_frame(..., next_img=)``."""
         if not self.use_cuda_graphs or self.frame_step < 1:
             return 0
         H, W = self.input_size_2d
@@ -745,6 +803,10 @@ class DeAOTEngine:
         if ("enc",) not in self._graphs:
             self._capture(("enc",), self.encode_image, [img])
         embs = list(self._graphs[("enc",)][2])                    # the encoder graph's outputs feed the read graphs
+        if prefetch:
+            if self._cur_embs is None:
+                self._cur_embs = [torch.empty_like(e) for e in embs]
+            embs = self._cur_embs
         for T in range(1, self.capacity + 1):
             for key, body, inputs, alias in self._variants(T, output_size, embs, label):
                 if key not in self._graphs:
@@ -767,6 +829,9 @@ class DeAOTEngine:
         if self.obj_nums is None and obj_nums is None:
             raise ValueError("No objects for reference frame!")
         self._wait_write()
+        if self._prefetched is not None:                         # an encoder pass left over from another sequence
+            torch.cuda.current_stream().wait_event(self._enc_done)
+            self._prefetched = None
         if obj_nums is not None:
             self.obj_nums = obj_nums
         if frame_step == -1:
@@ -789,10 +854,14 @@ class DeAOTEngine:
         self.last_mem_step = frame_step
         self._decode(curr_enc_embs, lstt_out, None)
 
-    def match_propogate_one_frame(self, img=None, img_embs=None, mask=None, output_size=None):
+    def match_propogate_one_frame(self, img=None, img_embs=None, mask=None, output_size=None, next_img=None):
         """aot_engine.py:398-436 (save_atten_weights=True in eval). With CUDA graphs the returned logits
         live in a buffer that the next call overwrites -- consume them (softmax / argmax) first, as the
-        reference's evaluator does."""
+        reference's evaluator does.
+
+        ``next_img`` (optional, not in the reference): the frame that will be passed to the NEXT call.  Its
+        encoder pass starts now on a second stream and overlaps this frame's LSTT + decoder (the encoder depends
+        on nothing but the image); the next call must then be given that same frame."""
         self.frame_step += 1
         T = self.T
         self.T_recorded = T
@@ -803,7 +872,14 @@ class DeAOTEngine:
             return self._read_body(None, img_embs, T, osz, st)
         # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
         # running on its own stream) and, after waiting for that write path, LSTT + decoder
-        embs = self._run(("enc",), self.encode_image, [img])
+        if next_img is not None or self._prefetched is not None:
+            if self._prefetched is None:
+                self._launch_encoder(img)                 # first frame of a prefetching loop: nothing encoded ahead
+            embs = self._take_prefetched()
+            if next_img is not None:
+                self._launch_encoder(next_img)
+        else:
+            embs = self._run(("enc",), self.encode_image, [img])
         self._wait_write()
         return self._run(("read", T, osz, st), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
                          alias=True)
@@ -945,11 +1021,11 @@ class DeAOTInferEngine:
                                        img_embs=img_embs)
         self.update_size()
 
-    def match_propogate_one_frame(self, img=None, mask=None, output_size=None):
-        if len(self.aot_engines) == 1:                      # <= 10 objects: whole frame in one CUDA graph
+    def match_propogate_one_frame(self, img=None, mask=None, output_size=None, next_img=None):
+        if len(self.aot_engines) == 1:                      # <= 10 objects: one engine, CUDA graphs end to end
             eng = self.aot_engines[0]
             eng.long_term_mem_gap = self.long_term_mem_gap
-            return eng.match_propogate_one_frame(img, mask=mask, output_size=output_size)
+            return eng.match_propogate_one_frame(img, mask=mask, output_size=output_size, next_img=next_img)
         img_embs = None
         all_logits = []
         for engine in self.aot_engines:
@@ -964,8 +1040,8 @@ class DeAOTInferEngine:
         for engine, m in zip(self.aot_engines, self.separate_mask(curr_mask)):
             engine.update_short_term_memory(m)
 
-    def precapture(self, output_size=None):
-        return sum(e.precapture(output_size) or 0 for e in self.aot_engines[:1])
+    def precapture(self, output_size=None, prefetch=False):
+        return sum(e.precapture(output_size, prefetch) or 0 for e in self.aot_engines[:1])
 
     def update_size(self):
         self.input_size_2d = self.aot_engines[0].input_size_2d

@@ -58,11 +58,15 @@ class FrameStreamer:
         self._cur = i
         return self._bufs[i]
 
-    def release(self):
-        """Call after the work reading the acquired image has been enqueued on the current stream."""
+    def release(self, tensor=None):
+        """Call after the work reading an acquired image has been enqueued on (or is awaited by) the current
+        stream; ``tensor`` names the image (default: the one acquired last)."""
+        idx = self._cur
+        if tensor is not None:
+            idx = next(i for i, b in enumerate(self._bufs) if b is tensor)
         ev = torch.cuda.Event()
         ev.record()
-        self._free[self._cur] = ev
+        self._free[idx] = ev
 
     # ---------------------------------------------------------------- results
     def push_result(self, dev_tensor):

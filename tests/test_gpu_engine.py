@@ -124,14 +124,16 @@ def test_full_path_images(lib_built):
     assert min(agree) >= 0.98, agree
 
 
-def _run_infer(m, imgs, lab, H, W, n_obj, gap):
+def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False):
     from rmem_ocu_b200.engine import DeAOTInferEngine
     eng = DeAOTInferEngine(m, 0, long_term_mem_gap=gap)
     masks, logits, idx = [], [], []
     with torch.no_grad():
         eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[n_obj], frame_step=0)
+        dimgs = [im.cuda() for im in imgs]
         for f in range(1, len(imgs)):
-            lg = eng.match_propogate_one_frame(imgs[f].cuda(), output_size=(H, W))
+            nxt = dimgs[f + 1] if prefetch and f + 1 < len(imgs) else None
+            lg = eng.match_propogate_one_frame(dimgs[f], output_size=(H, W), next_img=nxt)
             logits.append(lg.clone())
             label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
             masks.append(label[0, 0].to(torch.uint8).cpu())
@@ -224,4 +226,21 @@ def test_fused_local_attention_in_the_engine(lib_built, monkeypatch):
     assert ia == ib
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-2, f
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+
+
+def test_encoder_prefetch_matches_sequential(lib_built):
+    """match_propogate_one_frame(..., next_img=) starts the next frame's encoder on a second stream while this
+    frame's LSTT + decoder run: same kernels on the same data, so the clip must come out the same (slot indexes
+    equal, logits to 1e-3, masks >= 99.9 %: cuDNN may choose other algorithms on the other stream)."""
+    H, W, n, latter = 240, 432, 12, 2
+    imgs, lab = _clip(H, W, n, 3)
+    m, _ = _models(latter)
+    ma, la, ia, ea = _run_infer(m, imgs, lab, H, W, 3, gap=2)
+    m2, _ = _models(latter)
+    mb, lb, ib, eb = _run_infer(m2, imgs, lab, H, W, 3, gap=2, prefetch=True)
+    assert eb.aot_engines[0]._estream is not None and ("enc",) in eb.aot_engines[0]._graphs
+    assert ia == ib
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-3, f
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
