@@ -20,15 +20,17 @@ eng = DeAOTInferEngine(model, 0, long_term_mem_gap=5)
 dimgs = [im.to(dev) for im in imgs]
 with torch.no_grad():
     eng.add_reference_frame(dimgs[0], lab.to(dev), obj_nums=[bench.N_OBJ], frame_step=0)
+    PF = "--prefetch" in sys.argv
+    nxt = (lambda f: dimgs[f + 1]) if PF else (lambda f: None)
     for f in range(1, 30):
-        bench.frame_step(eng, dimgs[f], (bench.H, bench.W))
+        bench.frame_step(eng, dimgs[f], (bench.H, bench.W), nxt(f))
         if f == 1:
-            eng.precapture((bench.H, bench.W))
+            eng.precapture((bench.H, bench.W), prefetch=PF)
     torch.cuda.synchronize()
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         for f in range(30, 36):
-            bench.frame_step(eng, dimgs[f], (bench.H, bench.W))
+            bench.frame_step(eng, dimgs[f], (bench.H, bench.W), nxt(f))
         torch.cuda.synchronize()
 out = os.path.join(ROOT, "gpurun_out", "trace.json")
 prof.export_chrome_trace(out)
@@ -46,6 +48,7 @@ if len(starts) >= 4:
     print("frame span %.1f us, kernel busy %.1f us, gaps %.1f us, kernels %d" % (span, busy, span - busy, len(fr)))
     prev_end = t0
     for e in fr:
-        print("%8.1f %7.2f gap %6.2f  %s" % (e["ts"] - t0, e["dur"], e["ts"] - prev_end, e["name"][:70]))
+        print("%8.1f %7.2f gap %6.2f  s%-3s %s" % (e["ts"] - t0, e["dur"], e["ts"] - prev_end,
+                                                   e.get("args", {}).get("stream", "?"), e["name"][:70]))
         prev_end = e["ts"] + e["dur"]
 os.remove(out)
