@@ -7,8 +7,8 @@
 // sum over the token's 17x17 window of W[c][class(y,x)][ky][kx].  The weights are repacked as
 // row-prefix sums P[class][ky][kx'][c] = sum_{kx < kx'} W[c][class][ky][kx], so a run of equal labels
 // in a window row costs two loads instead of one per tap (label maps are piecewise constant).  Behind them sit
-// the 2-D prefix sums P2[class][ky'][kx'][c] = sum_{ky < ky', kx < kx'} W[c][class][ky][kx]: rows with the same
-// run structure collapse into rectangles.
+// the 2-D prefix sums P2[class][ky'][kx'][c] = sum_{ky < ky', kx < kx'} W[c][class][ky][kx]: identical rows
+// collapse into rectangles.
 #include <cuda_bf16.h>
 #include "rmem_internal.h"
 
@@ -46,73 +46,76 @@ __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
     cls_sh[ky][kx] = cls;
   }
   __syncthreads();
-  // runs of equal labels per window row, found once per CTA (one thread per row) instead of by every channel
-  __shared__ short run_cls[kIdK][kIdK], run_lo[kIdK][kIdK], run_hi[kIdK][kIdK];
-  __shared__ int n_runs[kIdK];
-  if (threadIdx.x < kIdK) {
-    const int ky = threadIdx.x;
-    int n = 0, run_start = 0, rc = cls_sh[ky][0];
-    for (int kx = 1; kx <= kIdK; ++kx) {
-      const int cur = (kx < kIdK) ? cls_sh[ky][kx] : -2;
-      if (cur != rc) {
-        if (rc >= 0) {
-          run_cls[ky][n] = static_cast<short>(rc);
-          run_lo[ky][n] = static_cast<short>(run_start);
-          run_hi[ky][n] = static_cast<short>(kx);
-          ++n;
-        }
-        run_start = kx;
-        rc = cur;
-      }
+  // The window is cut into rectangles of one class: maximal runs of equal labels in a row, extended downwards
+  // over the following rows that are identical to it.  A rectangle costs four loads from the 2-D prefix table
+  // whatever its size (an interior window of a single object is one rectangle), a one-row rectangle two loads
+  // from the row-prefix table.  The cutting is warp-parallel (ballots over the 17 columns of a row), the list is
+  // built in (row, column) order so the summation order -- and the fp32 result -- does not depend on timing.
+  __shared__ unsigned run_mask[kIdK];       // bit kx: a run starts at column kx of row ky
+  __shared__ int row_new[kIdK];             // row ky differs from row ky - 1 (or ky == 0): it opens a row group
+  __shared__ int rect_cnt[kIdK];            // rectangles opened by row ky
+  __shared__ int rect_cls[kIdK * kIdK];
+  __shared__ uchar4 rect_box[kIdK * kIdK];  // ky0, ky1, kx0, kx1
+  __shared__ int n_rect_sh;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int ky = warp; ky < kIdK; ky += kIdC / 32) {
+    const bool in = lane < kIdK;
+    const int cur = in ? cls_sh[ky][lane] : -3;
+    const int left = (in && lane > 0) ? cls_sh[ky][lane - 1] : -2;
+    const bool differs_up = in && (ky == 0 || cur != cls_sh[ky - 1][lane]);
+    const bool start = in && cur != left;
+    const unsigned starts = __ballot_sync(0xffffffffu, start);
+    const unsigned opens = __ballot_sync(0xffffffffu, start && cur >= 0);
+    const bool is_new = __any_sync(0xffffffffu, differs_up);
+    if (lane == 0) {
+      run_mask[ky] = starts;
+      row_new[ky] = is_new ? 1 : 0;
+      rect_cnt[ky] = is_new ? __popc(opens) : 0;
     }
-    n_runs[ky] = n;
   }
   __syncthreads();
-  // consecutive window rows with identical run lists form a group: its contribution is a rectangle sum, four
-  // loads from the 2-D prefix table whatever the group's height (an interior window of a single object is one
-  // group with one run); a lone row uses the row-prefix table (two loads per run)
-  __shared__ short grp_lo[kIdK], grp_hi[kIdK];
-  __shared__ int n_grp;
-  if (threadIdx.x == 0) {
-    int n = 0, r0 = 0;
-    for (int ky = 1; ky <= kIdK; ++ky) {
-      bool same = ky < kIdK && n_runs[ky] == n_runs[r0];
-      if (same) {
-        for (int r = 0; r < n_runs[r0]; ++r)
-          same = same && run_cls[ky][r] == run_cls[r0][r] && run_lo[ky][r] == run_lo[r0][r] &&
-                 run_hi[ky][r] == run_hi[r0][r];
-      }
-      if (!same) {
-        if (n_runs[r0] > 0) { grp_lo[n] = static_cast<short>(r0); grp_hi[n] = static_cast<short>(ky); ++n; }
-        r0 = ky;
-      }
+  for (int ky = warp; ky < kIdK; ky += kIdC / 32) {
+    const unsigned rows = __ballot_sync(0xffffffffu, lane < kIdK && row_new[lane] != 0);
+    int before = (lane < ky) ? rect_cnt[lane] : 0;      // ky <= 16 < 32: one lane per earlier row
+    for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+    if (!((rows >> ky) & 1u)) continue;                  // warp-uniform
+    const unsigned later_rows = rows >> (ky + 1);
+    const int ky1 = later_rows ? ky + __ffs(later_rows) : kIdK;
+    const unsigned starts = run_mask[ky];
+    const int cur = lane < kIdK ? cls_sh[ky][lane] : -3;
+    const bool opens = ((starts >> lane) & 1u) && cur >= 0;
+    const unsigned open_mask = __ballot_sync(0xffffffffu, opens);
+    if (opens) {
+      const unsigned later = starts >> (lane + 1);
+      const int kx1 = later ? lane + __ffs(later) : kIdK;
+      const int slot = before + __popc(open_mask & ((1u << lane) - 1u));
+      rect_cls[slot] = cur;
+      rect_box[slot] = make_uchar4(ky, ky1, lane, kx1);
     }
-    n_grp = n;
+  }
+  if (threadIdx.x == 0) {
+    int n = 0;
+    for (int ky = 0; ky < kIdK; ++ky) n += rect_cnt[ky];
+    n_rect_sh = n;
   }
   __syncthreads();
   const float* prefix2 = p.prefix + static_cast<size_t>(p.n_cls) * kIdK * (kIdK + 1) * kIdC;
   float acc = p.bias[c];
-  const int ng = n_grp;
-  for (int g = 0; g < ng; ++g) {
-    const int r0 = grp_lo[g], r1 = grp_hi[g];
-    const int n = n_runs[r0];
+  const int n_rect = n_rect_sh;
+  for (int r = 0; r < n_rect; ++r) {
+    const uchar4 bx = rect_box[r];
+    const int r0 = bx.x, r1 = bx.y, lo = bx.z, hi = bx.w;
     if (r1 - r0 == 1) {
-      for (int r = 0; r < n; ++r) {
-        const float* base = p.prefix + (static_cast<size_t>(run_cls[r0][r]) * kIdK + r0) * (kIdK + 1) * kIdC + c;
-        acc += base[run_hi[r0][r] * kIdC] - base[run_lo[r0][r] * kIdC];
-      }
+      const float* base = p.prefix + (static_cast<size_t>(rect_cls[r]) * kIdK + r0) * (kIdK + 1) * kIdC + c;
+      acc += base[hi * kIdC] - base[lo * kIdC];
     } else {
-      for (int r = 0; r < n; ++r) {
-        const float* base = prefix2 + static_cast<size_t>(run_cls[r0][r]) * (kIdK + 1) * (kIdK + 1) * kIdC + c;
-        const int lo = run_lo[r0][r], hi = run_hi[r0][r];
-        acc += (base[(r1 * (kIdK + 1) + hi) * kIdC] - base[(r0 * (kIdK + 1) + hi) * kIdC]) -
-               (base[(r1 * (kIdK + 1) + lo) * kIdC] - base[(r0 * (kIdK + 1) + lo) * kIdC]);
-      }
+      const float* base = prefix2 + static_cast<size_t>(rect_cls[r]) * (kIdK + 1) * (kIdK + 1) * kIdC + c;
+      acc += (base[(r1 * (kIdK + 1) + hi) * kIdC] - base[(r0 * (kIdK + 1) + hi) * kIdC]) -
+             (base[(r1 * (kIdK + 1) + lo) * kIdC] - base[(r0 * (kIdK + 1) + lo) * kIdC]);
     }
   }
   float out = acc;
   if (p.gamma) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float s = acc;
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (lane == 0) red[0][warp] = s;

@@ -443,10 +443,8 @@ class DeAOTEngine:
         # stream, into a staging set of embeddings, while this frame's LSTT + decoder run
         self._estream = None
         self._enc_done = None        # event: the prefetched embeddings are complete
-        self._stage_free = None      # event: the staging set has been copied out, the encoder may overwrite it
-        self._prefetched = None      # staging embeddings of the frame encoded ahead (list) or None
-        self._cur_embs = None        # the set the LSTT / decoder graphs read in prefetch mode
-        self._graph_pool_e = None
+        self._prefetched = None      # (embeddings, set index) of the frame encoded ahead, or None
+        self._enc_set = 0            # the embedding set (encoder graph 0 / 1) the next prefetch writes
         self._hp_stream = None
         self._graphs = {}
         self._graph_pool = None
@@ -492,7 +490,7 @@ class DeAOTEngine:
             self.ws = self._new_workspace(h, w, n_slots)
             self._wait_write()
             self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
-            self._graph_pool_e, self._cur_embs, self._prefetched = None, None, None
+            self._prefetched, self._enc_set = None, 0
 
     @property
     def long_memories_indexes(self):
@@ -662,8 +660,14 @@ class DeAOTEngine:
         ws = self.ws
         ws.bind(st)
         self._id_embed(label_hw)
+        # the layers' ID_V GEMMs are independent and sub-wave: every second one goes to the side stream (a parallel
+        # branch of the captured graph); the next frame's LSTT waits for this whole path
+        forked = self.prep.num_layers > 1 and self._fork()
         for i in range(self.prep.num_layers):
-            self._id_value(i, ws.vcur[i])
+            with torch.cuda.stream(self._side if forked and i % 2 == 1 else torch.cuda.current_stream()):
+                self._id_value(i, ws.vcur[i])
+        if forked:
+            self._join()
         if update_long:
             srcs, dsts = [], []
             for i in range(self.prep.num_layers):
@@ -731,13 +735,13 @@ class DeAOTEngine:
         launches0 = ops.LAUNCHES
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
-        with torch.cuda.graph(g, pool=self._graph_pool_e):
+        # one memory pool per encoder graph: graphs sharing a pool reuse each other's scratch, and encoder graph
+        # 0 replays while the outputs of encoder graph 1 are being read (and the other way round)
+        with torch.cuda.graph(g):
             out = body(*static_in)
         ent = (g, static_in, out, ops.LAUNCHES - launches0)
         ops.LAUNCHES = launches0
         self._graphs[key] = ent
-        if self._graph_pool_e is None:
-            self._graph_pool_e = g.pool()
         return ent
 
     def _run(self, key, body, inputs, alias=False):
@@ -763,37 +767,33 @@ class DeAOTEngine:
         return out
 
     def _launch_encoder(self, img):
-        """Encode ``img`` on the encoder stream (ordered after the point the current stream has reached and after
-        the staging set was last copied out); the result waits in the staging set."""
+        """Encode ``img`` on the encoder stream, ordered after the point the current stream has reached.  Two
+        encoder graphs with their own output sets alternate: the set written now was last read by the frame
+        before the current one, which the current stream has already passed, so nothing is ever copied."""
         if self._estream is None:
             self._estream = torch.cuda.Stream(device=self.device)
         es = self._estream
         ready = torch.cuda.Event()
         ready.record()
         es.wait_event(ready)
-        if self._stage_free is not None:
-            es.wait_event(self._stage_free)
         if img.is_cuda:
             img.record_stream(es)
+        p = self._enc_set
+        self._enc_set = 1 - p
         with torch.cuda.stream(es):
-            embs = list(self._run(("enc",), self.encode_image, [img]))
+            embs = list(self._run(("enc", p), self.encode_image, [img]))
             self._enc_done = torch.cuda.Event()
             self._enc_done.record()
-        self._prefetched = embs
+        self._prefetched = (embs, p)
 
     def _take_prefetched(self):
-        """Staging set -> the set the read graphs are recorded on (SM copies on the current stream)."""
+        """The embeddings encoded ahead and the index of their set; the current stream waits for the encoder."""
         cur = torch.cuda.current_stream()
         cur.wait_event(self._enc_done)
-        embs, self._prefetched = self._prefetched, None
-        if self._cur_embs is None or any(c.shape != e.shape for c, e in zip(self._cur_embs, embs)):
-            self._cur_embs = [torch.empty_like(e) for e in embs]
-        for dst, src in zip(self._cur_embs, embs):
-            src.record_stream(cur)
-            torch.mul(src, 1, out=dst)
-        self._stage_free = torch.cuda.Event()
-        self._stage_free.record()
-        return self._cur_embs
+        (embs, p), self._prefetched = self._prefetched, None
+        for e in embs:
+            e.record_stream(cur)
+        return embs, p
 
     def precapture(self, output_size=None, prefetch=False):
         """Capture the read / write graphs of every bank length now (capturing records, it does not
@@ -806,24 +806,23 @@ class DeAOTEngine:
         label = torch.zeros(H, W, device=self.device)
         saved = dict(self._graphs)
         self._wait_write()
-        if ("enc",) not in self._graphs:
-            self._capture(("enc",), self.encode_image, [img])
-        embs = list(self._graphs[("enc",)][2])                    # the encoder graph's outputs feed the read graphs
-        if prefetch:
-            if self._cur_embs is None:
-                self._cur_embs = [torch.empty_like(e) for e in embs]
-            embs = self._cur_embs
+        sets = {}
+        for p in ((0, 1) if prefetch else (0,)):                  # prefetching alternates between two sets
+            if ("enc", p) not in self._graphs:
+                self._capture(("enc", p), self.encode_image, [img])
+            sets[p] = list(self._graphs[("enc", p)][2])           # the encoder graphs' outputs feed the read graphs
         for T in range(1, self.capacity + 1):
-            for key, body, inputs, alias in self._variants(T, output_size, embs, label):
+            for key, body, inputs, alias in self._variants(T, output_size, sets, label):
                 if key not in self._graphs:
                     self._capture(key, body, inputs, alias)
         return len(self._graphs) - len(saved)
 
-    def _variants(self, T, output_size, embs, label):
+    def _variants(self, T, output_size, sets, label):
         ev = self.deaot or T + 1 > self.capacity
         for st in ((0, 1) if self.deaot else (0,)):
-            yield (("read", T, output_size, st),
-                   lambda *e, T=T, st=st: self._read_body(None, list(e), T, output_size, st), embs, True)
+            for p, embs in sets.items():
+                yield (("read", T, output_size, st, p),
+                       lambda *e, T=T, st=st: self._read_body(None, list(e), T, output_size, st), embs, True)
             yield (("write", T, False, False, st), lambda m, T=T, st=st: self._write_body(m, T, False, False, st),
                    [label], False)
             yield (("write", T, True, ev, st), lambda m, T=T, ev=ev, st=st: self._write_body(m, T, True, ev, st),
@@ -835,7 +834,7 @@ class DeAOTEngine:
         if self.obj_nums is None and obj_nums is None:
             raise ValueError("No objects for reference frame!")
         self._wait_write()
-        if self._prefetched is not None:                         # an encoder pass left over from another sequence
+        if self._enc_done is not None:                           # an encoder pass left over from another sequence
             torch.cuda.current_stream().wait_event(self._enc_done)
             self._prefetched = None
         if obj_nums is not None:
@@ -881,13 +880,13 @@ class DeAOTEngine:
         if next_img is not None or self._prefetched is not None:
             if self._prefetched is None:
                 self._launch_encoder(img)                 # first frame of a prefetching loop: nothing encoded ahead
-            embs = self._take_prefetched()
+            embs, p = self._take_prefetched()
             if next_img is not None:
                 self._launch_encoder(next_img)
         else:
-            embs = self._run(("enc",), self.encode_image, [img])
+            embs, p = self._run(("enc", 0), self.encode_image, [img]), 0
         self._wait_write()
-        return self._run(("read", T, osz, st), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
+        return self._run(("read", T, osz, st, p), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
                          alias=True)
 
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):

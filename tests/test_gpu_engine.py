@@ -239,7 +239,7 @@ def test_encoder_prefetch_matches_sequential(lib_built):
     ma, la, ia, ea = _run_infer(m, imgs, lab, H, W, 3, gap=2)
     m2, _ = _models(latter)
     mb, lb, ib, eb = _run_infer(m2, imgs, lab, H, W, 3, gap=2, prefetch=True)
-    assert eb.aot_engines[0]._estream is not None and ("enc",) in eb.aot_engines[0]._graphs
+    assert eb.aot_engines[0]._estream is not None and ("enc", 1) in eb.aot_engines[0]._graphs
     assert ia == ib
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-3, f
