@@ -439,6 +439,15 @@ class DeAOTEngine:
         self._wstream = None
         self._w_done = None
         self._graph_pool_w = None
+        # deferred write path (DeAOT): update_short_term_memory only stores the label map; the next
+        # match_propogate_one_frame replays ONE graph holding that write path as a parallel branch of the LSTT
+        # (joined where the new short-term memory is first read), which removes two graph boundaries from the
+        # frame-to-frame dependency chain and hides the write path behind layer 0's long-term attention.
+        # Anything else that reads the memory (reference frames, bank indexes) runs the pending write path first.
+        self.lazy_write = self.deaot and os_env_flag("RMEM_LAZY_WRITE", True)
+        self._wside = None
+        self._label_buf = None
+        self._w_events = None
         # encoder prefetch (match_propogate_one_frame(..., next_img=)): the next frame's encoder runs on its own
         # stream, into a staging set of embeddings, while this frame's LSTT + decoder run
         self._estream = None
@@ -478,6 +487,7 @@ class DeAOTEngine:
         self.st = 0                # which K / V set holds the valid short-term memory (host mirror)
         self.T = 0                 # frames in the long-term bank (host mirror; deterministic)
         self.T_recorded = 0        # bank length when record_attn_weight was last written
+        self._pending_w = None     # (T, update_long, do_evict, st) of a deferred write path
         self.n_long_updates = 0
 
     def update_size(self, input_size, enc_size):
@@ -573,7 +583,15 @@ class DeAOTEngine:
         h, w, L = ws.h, ws.w, ws.L
         ws.tgt.copy_(self._tokens(curr_emb16))
         tr = self.trace
+        we = self._w_events
+        if we is not None and prep.num_layers == 1:
+            we["l0"] = we["all"]
         for i, Lw in enumerate(prep.layers):
+            if we is not None and i == 1 and not we["waited"]:
+                # a deferred write path is running beside layer 0: its ID_V GEMMs read curr_ID_V of the previous
+                # frame, which the next LayerNorm overwrites, and write the short-term values layers 1.. read
+                torch.cuda.current_stream().wait_event(we["all"])
+                we["waited"] = True
             # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
             if i == 0:
                 ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0)
@@ -600,6 +618,8 @@ class DeAOTEngine:
             with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
                 # short-term 15x15 local attention over the previous frame, gate, dw5x5
                 ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
+                if we is not None and i == 0 and not we["waited"]:
+                    torch.cuda.current_stream().wait_event(we["l0"])     # ID_V of layer 0 (deferred write path)
                 if self.local_fused:
                     ops.local_attn(ws.kcur[i], ws.kprev[i], ws.vprev[i], ws.rel, ws.u[i], ws.gated_b, h, w)
                 else:
@@ -640,6 +660,9 @@ class DeAOTEngine:
                         (256, 512, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt_id, 0)])
             if tr is not None:
                 tr["layers"][-1].update(tgt=ws.tgt.cpu().clone(), tgt_id=ws.tgt_id.cpu().clone())
+        if we is not None and not we["waited"]:
+            torch.cuda.current_stream().wait_event(we["all"])
+            we["waited"] = True
         # the single output GroupNorm1D(512, 2) (transformer.py:806-808)
         ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws)
         return ws.gn_out
@@ -648,12 +671,35 @@ class DeAOTEngine:
     def _read_body(self, img, img_embs, T, output_size, st):
         """Everything match_propogate_one_frame puts on the stream; a pure function of (T, output_size, st)."""
         self.ws.bind(st)
+        we = self._w_events
+        if we is not None and we["update_long"]:
+            # the deferred write path appends to / evicts from the bank this frame reads, and stamps the slot with
+            # the device frame counter: it has to be complete before the counter ticks
+            torch.cuda.current_stream().wait_event(we["all"])
+            we["waited"] = True
         ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device
         embs = self.encode_image(img) if img_embs is None else img_embs
         lstt_out = self._lstt_forward(embs[-1], False, True, T)
         return self._decode(embs, lstt_out, output_size)
 
-    def _write_body(self, label_hw, T, update_long, do_evict, st):
+    def _fused_body(self, label_hw, embs, Tw, update_long, do_evict, st_w, T, output_size, st):
+        """The previous frame's write path as a parallel branch + this frame's read path."""
+        if self._wside is None:
+            self._wside = torch.cuda.Stream(device=self.device)
+        start = torch.cuda.Event()
+        start.record()
+        self._wside.wait_event(start)
+        we = dict(l0=torch.cuda.Event(), all=torch.cuda.Event(), update_long=update_long, waited=False)
+        with torch.cuda.stream(self._wside):
+            self._write_body(label_hw, Tw, update_long, do_evict, st_w, events=we)
+            we["all"].record()
+        self._w_events = we
+        try:
+            return self._read_body(None, embs, T, output_size, st)
+        finally:
+            self._w_events = None
+
+    def _write_body(self, label_hw, T, update_long, do_evict, st, events=None):
         """Everything update_short_term_memory puts on the stream (transformer.py:826-991).  The frame's K and
         V already sit in the "current" set; fusing ID_V into it completes the new short-term memory, and the
         caller swaps the roles of the two sets afterwards."""
@@ -662,8 +708,10 @@ class DeAOTEngine:
         self._id_embed(label_hw)
         # the layers' ID_V GEMMs are independent and sub-wave: every second one goes to the side stream (a parallel
         # branch of the captured graph); the next frame's LSTT waits for this whole path
-        forked = self.prep.num_layers > 1 and self._fork()
+        forked = events is None and self.prep.num_layers > 1 and self._fork()
         for i in range(self.prep.num_layers):
+            if events is not None and i == 1:
+                events["l0"].record()                             # layer 0's short-term memory is complete
             with torch.cuda.stream(self._side if forked and i % 2 == 1 else torch.cuda.current_stream()):
                 self._id_value(i, ws.vcur[i])
         if forked:
@@ -698,7 +746,11 @@ class DeAOTEngine:
 
     # ------------------------------------------------------------------ CUDA graphs
     def _wait_write(self):
-        """Order the current stream after the last write path (it runs on its own stream)."""
+        """Order the current stream after the last write path (it runs on its own stream, or is still deferred)."""
+        if self._pending_w is not None:
+            (T, update_long, do_evict, st), self._pending_w = self._pending_w, None
+            self._run(("write", T, update_long, do_evict, st),
+                      lambda m: self._write_body(m, T, update_long, do_evict, st), [self._label_buf])
         if self._w_done is not None:
             torch.cuda.current_stream().wait_event(self._w_done)
 
@@ -817,8 +869,25 @@ class DeAOTEngine:
                     self._capture(key, body, inputs, alias)
         return len(self._graphs) - len(saved)
 
+    def _label_buffer(self, like):
+        if self._label_buf is None or self._label_buf.shape != like.shape:
+            self._label_buf = torch.empty(like.shape, dtype=torch.float32, device=self.device)
+        return self._label_buf
+
     def _variants(self, T, output_size, sets, label):
         ev = self.deaot or T + 1 > self.capacity
+        if self.lazy_write:
+            # steady state of the deferred schedule: write path of the previous frame (bank length T, with or
+            # without a long-term update) + read path of this frame; the stand-alone graphs are recorded on demand
+            buf = self._label_buffer(label)
+            for st in (0, 1):
+                for p, embs in sets.items():
+                    for ul, de, Tr in ((False, False, T), (True, ev, min(T + 1, self.capacity))):
+                        yield (("wr", T, ul, de, st, Tr, output_size, 1 - st, p),
+                               lambda m, *e, T=T, ul=ul, de=de, st=st, Tr=Tr: self._fused_body(
+                                   m, list(e), T, ul, de, st, Tr, output_size, 1 - st),
+                               [buf] + embs, True)
+            return
         for st in ((0, 1) if self.deaot else (0,)):
             for p, embs in sets.items():
                 yield (("read", T, output_size, st, p),
@@ -885,6 +954,11 @@ class DeAOTEngine:
                 self._launch_encoder(next_img)
         else:
             embs, p = self._run(("enc", 0), self.encode_image, [img]), 0
+        if self._pending_w is not None:
+            pend, self._pending_w = self._pending_w, None
+            return self._run(("wr",) + pend + (T, osz, st, p),
+                             lambda m, *e: self._fused_body(m, list(e), *pend, T, osz, st),
+                             [self._label_buf] + list(embs), alias=True)
         self._wait_write()
         return self._run(("read", T, osz, st, p), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
                          alias=True)
@@ -908,7 +982,11 @@ class DeAOTEngine:
             raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
         st = self.st
         body = lambda m: self._write_body(m, T, update_long, do_evict, st)
-        if self.async_write:
+        if self.lazy_write:
+            self._wait_write()                                    # an earlier deferred write path, if any
+            torch.mul(label, 1, out=self._label_buffer(label))    # SM copy (see _run)
+            self._pending_w = (T, update_long, do_evict, st)
+        elif self.async_write:
             if self._wstream is None:
                 self._wstream = torch.cuda.Stream(device=self.device)
             ready = torch.cuda.Event()

@@ -124,7 +124,7 @@ def test_full_path_images(lib_built):
     assert min(agree) >= 0.98, agree
 
 
-def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False):
+def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=True):
     from rmem_ocu_b200.engine import DeAOTInferEngine
     eng = DeAOTInferEngine(m, 0, long_term_mem_gap=gap)
     masks, logits, idx = [], [], []
@@ -138,7 +138,8 @@ def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False):
             label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
             masks.append(label[0, 0].to(torch.uint8).cpu())
             eng.update_memory(F.interpolate(label, size=eng.input_size_2d, mode="nearest"))
-            idx.append([list(e.long_memories_indexes) for e in eng.aot_engines])
+            if idx_every_frame or f == len(imgs) - 1:      # reading the bank runs a deferred write path at once
+                idx.append([list(e.long_memories_indexes) for e in eng.aot_engines])
     torch.cuda.synchronize()
     return masks, [l.cpu() for l in logits], idx, eng
 
@@ -150,8 +151,9 @@ def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
     H, W, n, latter = 240, 432, 14, 2
     imgs, lab = _clip(H, W, n, 3)
     outs = []
-    for flags in ({}, {"RMEM_CUDA_GRAPHS": "0", "RMEM_ASYNC_WRITE": "0", "RMEM_FORK_BRANCHES": "0"}):
-        for k in ("RMEM_CUDA_GRAPHS", "RMEM_ASYNC_WRITE", "RMEM_FORK_BRANCHES"):
+    for flags in ({"RMEM_LAZY_WRITE": "0"},
+                  {"RMEM_CUDA_GRAPHS": "0", "RMEM_ASYNC_WRITE": "0", "RMEM_FORK_BRANCHES": "0", "RMEM_LAZY_WRITE": "0"}):
+        for k in ("RMEM_CUDA_GRAPHS", "RMEM_ASYNC_WRITE", "RMEM_FORK_BRANCHES", "RMEM_LAZY_WRITE"):
             monkeypatch.delenv(k, raising=False)
         for k, v in flags.items():
             monkeypatch.setenv(k, v)
@@ -165,6 +167,34 @@ def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
     # not bit-equal: cuDNN may pick other convolution algorithms under capture and the GroupNorm statistics are
     # fp64 atomics (order-dependent in the last bit), which flips isolated bf16 roundings downstream; anything a
     # mis-ordered stream would cause is orders of magnitude larger
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-3, f
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+
+
+@pytest.mark.parametrize("prefetch", [False, True])
+def test_deferred_write_path_matches_immediate(lib_built, monkeypatch, prefetch):
+    """Default DeAOT schedule: update_short_term_memory defers its work into the next frame's graph, where it runs
+    as a branch beside layer 0 of the LSTT (engine._fused_body).  Against the plain eager single-stream run: same
+    logits (1e-3) and masks on every frame, same bank at the end -- with long-term updates and evictions on the
+    way (gap 2, 1 + 2 slots, 14 frames) and the bank only read at the end, so the deferred path really runs."""
+    H, W, n, latter = 240, 432, 14, 2
+    imgs, lab = _clip(H, W, n, 3)
+    outs = []
+    for flags in ({}, {"RMEM_CUDA_GRAPHS": "0", "RMEM_ASYNC_WRITE": "0", "RMEM_FORK_BRANCHES": "0", "RMEM_LAZY_WRITE": "0"}):
+        for k in ("RMEM_CUDA_GRAPHS", "RMEM_ASYNC_WRITE", "RMEM_FORK_BRANCHES", "RMEM_LAZY_WRITE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in flags.items():
+            monkeypatch.setenv(k, v)
+        m, _ = _models(latter)
+        outs.append(_run_infer(m, imgs, lab, H, W, 3, gap=2, prefetch=prefetch and not flags,
+                               idx_every_frame=False))
+    (ma, la, ia, ea), (mb, lb, ib, eb) = outs
+    assert ea.aot_engines[0].lazy_write and not eb.aot_engines[0].lazy_write
+    keys = [k for k in ea.aot_engines[0]._graphs if k[0] == "wr"]
+    assert any(k[2] for k in keys) and any(not k[2] for k in keys)   # with and without a long-term update
+    assert ia == ib and len(ia[-1][0]) == 3
+    assert ea.aot_engines[0].eviction_debug()["n_evictions"] == eb.aot_engines[0].eviction_debug()["n_evictions"] > 0
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-3, f
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
