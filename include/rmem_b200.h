@@ -167,13 +167,14 @@ int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, in
 
 /* GroupNorm over an [L][C] token matrix viewed as [1, C, L] (GroupNorm1D, layers/basic.py:6-12):
  * statistics per group over (C/groups channels x L tokens).  Replaces DualBranchGPM's
- * decoder_norms[-1] (transformer.py:806-808).  x = cat(x_a[L][Ca], x_b[L][C-Ca]) f32, out bf16.
+ * decoder_norms[-1] (transformer.py:806-808).  x = cat(x_a[L][Ca], x_b[L][C-Ca]) f32; out [L][C] bf16, or
+ * f32 when out_f32 != 0 (the decoder's convolutions take f32).  Ca, C and C / groups are multiples of 4.
  *   workspace: 16 * groups + 8 bytes, 8-byte aligned (fp64 sum / sum of squares + an arrival counter); the
  *   caller zero-fills it once, every call leaves it zero again
  */
 int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const float* gamma,
-                          const float* beta, void* out, int L, int C, int groups, void* workspace,
-                          void* stream);
+                          const float* beta, void* out, int out_f32, int L, int C, int groups,
+                          void* workspace, void* stream);
 
 /* Per-query temporal-PE score bias and the time-shifted query (transformer.py:1142-1172):
  *   q_time = bf16(q + cur_pos_emb);  tpe_bias[q][r] = log2e/sqrt(C) * ((q + cur_pos_emb) . mem_pos_emb[r])

@@ -110,9 +110,9 @@ int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, in
   return dwconv5_launch(x, ldx, xcol0, wt, y, ldy, ycol0, h, w, C, ST(stream));
 }
 int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const float* gamma,
-                          const float* beta, void* out, int L, int C, int groups, void* workspace,
-                          void* stream) {
-  return groupnorm_tokens_launch(x_a, Ca, x_b, gamma, beta, out, L, C, groups, workspace, ST(stream));
+                          const float* beta, void* out, int out_f32, int L, int C, int groups,
+                          void* workspace, void* stream) {
+  return groupnorm_tokens_launch(x_a, Ca, x_b, gamma, beta, out, out_f32, L, C, groups, workspace, ST(stream));
 }
 int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_pos_emb,
                      void* q_time, float* tpe_bias, int L, int C, void* stream) {

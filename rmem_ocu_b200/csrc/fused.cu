@@ -208,47 +208,50 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int L, int C,
                 int groups, int rows_per_cta, double* __restrict__ ws) {
-  // block handles rows_per_cta rows (few CTAs: every CTA ends in fp64 atomics on the same 2 * groups words, and
-  // hundreds of contending atomics cost more than the reduction); thread t covers channels t, t+256, ... (C <= 1024)
+  // One CTA per SM, rows_per_cta rows each.  A thread owns four consecutive channels (one float4 per row; Ca, C
+  // and C / groups are multiples of 4), so C / 4 threads cover a row and 1024 / C rows are in flight per pass.
+  // Every CTA ends in 2 * groups fp64 atomics: ~150 CTAs keep that contention below the cost of the reduction.
   const int cpg = C / groups;
-  __shared__ float sh_s[8][8], sh_q[8][8];   // [group][warp]
-  float s[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+  const int tpr = C >> 2;                         // threads per row (<= 256)
+  const int c = (threadIdx.x % tpr) << 2;
+  const int r_in_pass = threadIdx.x / tpr, rows_per_pass = 256 / tpr;
+  const bool active = r_in_pass < rows_per_pass;  // 256 % tpr threads idle when tpr does not divide 256
+  const float* src = c < Ca ? xa + c : xb + (c - Ca);
+  const int ld = c < Ca ? Ca : C - Ca;
+  const int row0 = blockIdx.x * rows_per_cta, row1 = min(row0 + rows_per_cta, L);
+  float s = 0.f, q = 0.f;
+  if (active) {
 #pragma unroll 4
-  for (int r = 0; r < rows_per_cta; ++r) {
-    const int row = blockIdx.x * rows_per_cta + r;
-    if (row >= L) break;
-    int k = 0;
-    for (int c = threadIdx.x; c < C; c += 256, ++k) {
-      const float v = c < Ca ? xa[static_cast<size_t>(row) * Ca + c]
-                             : xb[static_cast<size_t>(row) * (C - Ca) + (c - Ca)];
-      s[k] += v; q[k] += v * v;
+    for (int row = row0 + r_in_pass; row < row1; row += rows_per_pass) {
+      const float4 v = *reinterpret_cast<const float4*>(src + static_cast<size_t>(row) * ld);
+      s += (v.x + v.y) + (v.z + v.w);
+      q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
     }
   }
-  // channel c = threadIdx.x + 256*k belongs to group c / cpg; reduce per (k) then add to its group.
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x < 64) { sh_s[threadIdx.x >> 3][threadIdx.x & 7] = 0.f; sh_q[threadIdx.x >> 3][threadIdx.x & 7] = 0.f; }
+  __shared__ float sh_s[8], sh_q[8];
+  if (threadIdx.x < 8) { sh_s[threadIdx.x] = 0.f; sh_q[threadIdx.x] = 0.f; }
   __syncthreads();
-  int k = 0;
-  for (int c0 = 0; c0 < C; c0 += 256, ++k) {
-    // all lanes of a warp share the group when cpg is a multiple of 32
-    const int g = (c0 + warp * 32) / cpg;
-    const float ws_ = warp_sum(s[k]), wq_ = warp_sum(q[k]);
-    if (lane == 0) { atomicAdd(&sh_s[g][warp], ws_); atomicAdd(&sh_q[g][warp], wq_); }
+  const int g = c / cpg;
+  if ((cpg & 127) == 0 && (tpr & 31) == 0) {      // a warp's 128 channels lie in one group
+    const float ws_ = warp_sum(s), wq_ = warp_sum(q);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&sh_s[g], ws_); atomicAdd(&sh_q[g], wq_); }
+  } else if (active) {
+    atomicAdd(&sh_s[g], s); atomicAdd(&sh_q[g], q);
   }
   __syncthreads();
   if (threadIdx.x < groups) {
-    double ts = 0.0, tq = 0.0;
-    for (int wv = 0; wv < 8; ++wv) { ts += sh_s[threadIdx.x][wv]; tq += sh_q[threadIdx.x][wv]; }
-    atomicAdd(ws + 2 * threadIdx.x, ts);
-    atomicAdd(ws + 2 * threadIdx.x + 1, tq);
+    atomicAdd(ws + 2 * threadIdx.x, static_cast<double>(sh_s[threadIdx.x]));
+    atomicAdd(ws + 2 * threadIdx.x + 1, static_cast<double>(sh_q[threadIdx.x]));
   }
 }
 
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
-                __nv_bfloat16* __restrict__ out, int L, int C, int groups, double* __restrict__ ws) {
-  // a thread owns four consecutive channels (one float4 in, four bf16 out); Ca, C and C / groups are multiples of 4
+                __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32, int L, int C, int groups,
+                double* __restrict__ ws) {
+  // a thread owns four consecutive channels (one float4 in, four bf16 or f32 out); Ca, C and C / groups are
+  // multiples of 4
   const int cpg = C / groups;
   const double cnt = static_cast<double>(cpg) * L;
   const size_t total4 = static_cast<size_t>(L) * C / 4;
@@ -264,27 +267,35 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
                             : *reinterpret_cast<const float4*>(xb + static_cast<size_t>(row) * (C - Ca) + (c - Ca));
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
     const float4 be = *reinterpret_cast<const float4*>(beta + c);
-    uint2 pk;
-    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
-    o[0] = __floats2bfloat162_rn((v.x - mean) * rstd * ga.x + be.x, (v.y - mean) * rstd * ga.y + be.y);
-    o[1] = __floats2bfloat162_rn((v.z - mean) * rstd * ga.z + be.z, (v.w - mean) * rstd * ga.w + be.w);
-    *reinterpret_cast<uint2*>(out + i * 4) = pk;
+    const float4 y = make_float4((v.x - mean) * rstd * ga.x + be.x, (v.y - mean) * rstd * ga.y + be.y,
+                                 (v.z - mean) * rstd * ga.z + be.z, (v.w - mean) * rstd * ga.w + be.w);
+    if (out_f32) {
+      *reinterpret_cast<float4*>(out_f32 + i * 4) = y;
+    } else {
+      uint2 pk;
+      __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
+      o[0] = __floats2bfloat162_rn(y.x, y.y);
+      o[1] = __floats2bfloat162_rn(y.z, y.w);
+      *reinterpret_cast<uint2*>(out + i * 4) = pk;
+    }
   }
   gn_ws_release(ws, 2 * groups);
 }
 
 int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
-                            const float* beta, void* out, int L, int C, int groups, void* workspace,
-                            cudaStream_t stream) {
+                            const float* beta, void* out, int out_f32, int L, int C, int groups,
+                            void* workspace, cudaStream_t stream) {
   if (groups < 1 || groups > 8 || C > 1024 || (C % groups) || ((C / groups) % 32) || Ca > C ||
       (Ca < C && !xb) || (Ca & 3) || (C & 3))
     return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
-  const int rows = (L + 63) / 64 < 8 ? 8 : (L + 63) / 64;        // ~64 CTAs
+  const int rows = (L + 147) / 148 < 4 ? 4 : (L + 147) / 148;     // one CTA per SM
   gn_stats_kernel<<<(L + rows - 1) / rows, 256, 0, stream>>>(xa, Ca, xb, L, C, groups, rows,
                                                               static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
-  gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta, static_cast<__nv_bfloat16*>(out), L,
-                                           C, groups, static_cast<double*>(workspace));
+  gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta,
+                                           out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out),
+                                           out_f32 ? static_cast<float*>(out) : nullptr, L, C, groups,
+                                           static_cast<double*>(workspace));
   return check_launch("gn_apply_kernel");
 }
 

@@ -140,15 +140,32 @@ class InferenceFPN:
         ops.groupnorm_nhwc(t, g, be, t, 8, True, self._ws, pre_bias=b)            # in place
         return y
 
-    def _up_add(self, x, shortcut, name):
+    ADAPTERS = (("adapter_16x", -2), ("adapter_8x", -3), ("adapter_4x", -4))
+
+    def _adapter(self, shortcut, name):
+        """1x1 adapter convolution of a bf16 shortcut as a GEMM (+ bias in the epilogue) -> f32 channels-last."""
+        w, b = self.w[name]
+        shortcut = shortcut.contiguous(memory_format=torch.channels_last)
+        ho, wo = shortcut.shape[-2:]
+        a = torch.empty(1, ho, wo, w.shape[0], device=shortcut.device, dtype=torch.float32).permute(0, 3, 1, 2)
+        ops.linear(self._tok(shortcut), self.wb[name], b, [(0, w.shape[0], ops.ACT_NONE, ops.OUT_F32, self._tok(a), 0)])
+        return a
+
+    def adapters(self, shortcuts):
+        """The three adapter outputs, which depend on the encoder alone: the engine computes them at the end of
+        the encoder pass (off the LSTT -> decoder chain when the encoder runs ahead) and hands them to __call__."""
+        if any(shortcuts[i].dtype != BF16 for _, i in self.ADAPTERS):
+            return None
+        return [self._adapter(shortcuts[i], name) for name, i in self.ADAPTERS]
+
+    def _up_add(self, x, shortcut, name, pre=None):
         """adapter(shortcut) + bias + bilinear(x) (identity resample when the sizes agree)."""
         w, b = self.w[name]
-        if shortcut.dtype == BF16:
-            shortcut = shortcut.contiguous(memory_format=torch.channels_last)
-            ho, wo = shortcut.shape[-2:]
-            a = torch.empty(1, ho, wo, w.shape[0], device=x.device, dtype=torch.float32).permute(0, 3, 1, 2)
+        if pre is not None:
+            a, ta, b = pre, self._tok(pre), None
+        elif shortcut.dtype == BF16:
+            a = self._adapter(shortcut, name)
             ta = self._tok(a)
-            ops.linear(self._tok(shortcut), self.wb[name], b, [(0, w.shape[0], ops.ACT_NONE, ops.OUT_F32, ta, 0)])
             b = None                                                                # added by the GEMM epilogue
         else:
             a = F.conv2d(shortcut.float(), w, None).contiguous(memory_format=torch.channels_last)
@@ -158,15 +175,16 @@ class InferenceFPN:
         ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b)     # in place
         return a
 
-    def __call__(self, inputs, shortcuts, gn_ws=None):
+    def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None):
         self._ws = self.gn_ws if gn_ws is None else gn_ws
+        pre = adapters if adapters is not None else (None, None, None)
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
         x = x.float().contiguous(memory_format=torch.channels_last)
         sc = shortcuts
         x = self._conv_gn_relu(x, "conv_in")
-        x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x"), "conv_16x")
-        x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x"), "conv_8x")
-        x = self._conv_gn_relu(self._up_add(x, sc[-4], "adapter_4x"), "conv_4x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x", pre[0]), "conv_16x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x", pre[1]), "conv_8x")
+        x = self._conv_gn_relu(self._up_add(x, sc[-4], "adapter_4x", pre[2]), "conv_4x")
         w, b = self.w["conv_out"]
         return F.conv2d(x, w, None), b          # the caller adds the bias while finishing the logits
 
@@ -365,7 +383,7 @@ class _Workspace:
         self.part_o = z(n_chunks, L, 1024, dt=f32)
         self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
         self.mass = z(L * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight [L, T]
-        self.gn_out = z(L, 512)
+        self.gn_out = z(L, 512, dt=f32)                       # f32: feeds the decoder's f32 convolutions as it is
         self.gn_ws = z(5, dt=torch.float64)                   # 2 x 2 group sums + arrival counter
         self.fg = z(L, dt=f32)
         self.id_emb = z(L, 256)
@@ -524,6 +542,13 @@ class DeAOTEngine:
         """ResNet-50 trunk + encoder_projector (cuDNN, bf16 channels-last) -> [x4, x8, x16, emb16]."""
         return self.prep.encoder(img.to(device=self.device, non_blocking=True))
 
+    def _encode_body(self, img):
+        """The encoder graph: encode_image + the decoder's adapter convolutions of its shortcuts (they depend on
+        the encoder alone) -> [x4, x8, x16, emb16, a16, a8, a4]."""
+        embs = list(self.encode_image(img))
+        pre = self.prep.decoder.adapters(embs)
+        return embs + pre if pre is not None else embs
+
     def _tokens(self, x_nchw):
         """[1, C, h, w] channels-last tensor -> [L, C] view of the same memory."""
         n, c, h, w = x_nchw.shape
@@ -678,9 +703,10 @@ class DeAOTEngine:
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
         ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device
-        embs = self.encode_image(img) if img_embs is None else img_embs
+        embs = self._encode_body(img) if img_embs is None else img_embs
+        embs, pre = (embs[:4], embs[4:]) if len(embs) == 7 else (embs, None)
         lstt_out = self._lstt_forward(embs[-1], False, True, T)
-        return self._decode(embs, lstt_out, output_size)
+        return self._decode(embs, lstt_out, output_size, adapters=pre)
 
     def _fused_body(self, label_hw, embs, Tw, update_long, do_evict, st_w, T, output_size, st):
         """The previous frame's write path as a parallel branch + this frame's read path."""
@@ -726,11 +752,12 @@ class DeAOTEngine:
                 ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
                 ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T, self.capacity)
 
-    def _decode(self, embs, lstt_out, output_size):
+    def _decode(self, embs, lstt_out, output_size, adapters=None):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
         if getattr(self, "_dec_gn_ws", None) is None:
             self._dec_gn_ws = torch.zeros(17, device=self.device, dtype=torch.float64)
-        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws)
+        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws,
+                                       adapters=adapters)
         ws = self.ws
         if ws.pred_logits is None or ws.pred_logits.shape != conv.shape:
             ws.pred_logits = torch.empty(conv.shape, device=conv.device, dtype=torch.float32)
@@ -833,7 +860,7 @@ class DeAOTEngine:
         p = self._enc_set
         self._enc_set = 1 - p
         with torch.cuda.stream(es):
-            embs = list(self._run(("enc", p), self.encode_image, [img]))
+            embs = list(self._run(("enc", p), self._encode_body, [img]))
             self._enc_done = torch.cuda.Event()
             self._enc_done.record()
         self._prefetched = (embs, p)
@@ -861,7 +888,7 @@ class DeAOTEngine:
         sets = {}
         for p in ((0, 1) if prefetch else (0,)):                  # prefetching alternates between two sets
             if ("enc", p) not in self._graphs:
-                self._capture(("enc", p), self.encode_image, [img])
+                self._capture(("enc", p), self._encode_body, [img])
             sets[p] = list(self._graphs[("enc", p)][2])           # the encoder graphs' outputs feed the read graphs
         for T in range(1, self.capacity + 1):
             for key, body, inputs, alias in self._variants(T, output_size, sets, label):
@@ -953,7 +980,7 @@ class DeAOTEngine:
             if next_img is not None:
                 self._launch_encoder(next_img)
         else:
-            embs, p = self._run(("enc", 0), self.encode_image, [img]), 0
+            embs, p = self._run(("enc", 0), self._encode_body, [img]), 0
         if self._pending_w is not None:
             pend, self._pending_w = self._pending_w, None
             return self._run(("wr",) + pend + (T, osz, st, p),

@@ -75,8 +75,11 @@ def dwconv5(x, xcol0, wt, y, ycol0, h, w, C):
 def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
     L, Ca = xa.shape
     C = Ca + (xb.shape[1] if xb is not None else 0)
-    _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), L, C,
-                                                groups, _p(workspace), _stream()), "rmem_groupnorm_tokens")
+    if out.dtype not in (torch.bfloat16, torch.float32):
+        raise _lib.RmemError("groupnorm_tokens: out must be bf16 or f32")
+    _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
+                                                int(out.dtype == torch.float32), L, C, groups, _p(workspace),
+                                                _stream()), "rmem_groupnorm_tokens")
     _count("rmem_groupnorm_tokens")
 
 

@@ -99,10 +99,23 @@ def test_groupnorm_tokens(lib_built):
     out = torch.empty(L, 512, device="cuda", dtype=torch.bfloat16)
     ws = torch.zeros(5, device="cuda", dtype=torch.float64)
     ops.groupnorm_tokens(xa, xb, g, b, out, 2, ws)
+    out32 = torch.empty(L, 512, device="cuda")
+    ops.groupnorm_tokens(xa, xb, g, b, out32, 2, ws)             # the workspace cleans itself
     torch.cuda.synchronize()
     x = torch.cat([xa, xb], 1)
     ref = F.group_norm(x.t().unsqueeze(0), 2, g, b, 1e-5)[0].t()
     assert _rel(out, ref) < 4e-3
+    assert _rel(out32, ref) < 1e-5
+    # other shapes: one input, groups that split a warp's channels, rows that do not fill the last CTA
+    for (Ca, Cb, groups, L2) in ((256, 0, 8, 333), (192, 64, 2, 77), (1024, 0, 4, 1620)):
+        xa2 = torch.randn(L2, Ca, device="cuda") + 0.3
+        xb2 = torch.randn(L2, Cb, device="cuda") * 2 if Cb else None
+        g2, b2 = torch.randn(Ca + Cb, device="cuda"), torch.randn(Ca + Cb, device="cuda")
+        o2 = torch.empty(L2, Ca + Cb, device="cuda")
+        ops.groupnorm_tokens(xa2, xb2, g2, b2, o2, groups, ws)
+        x2 = torch.cat([xa2, xb2], 1) if Cb else xa2
+        ref2 = F.group_norm(x2.t().unsqueeze(0), groups, g2, b2, 1e-5)[0].t()
+        assert _rel(o2, ref2) < 1e-5, (Ca, Cb, groups, L2)
 
 
 def test_tpe_prepare(lib_built):
