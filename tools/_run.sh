@@ -1,7 +1,2 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_engine.py -m gpu -x -q > gpurun_out/pytest_part.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/pytest_part.log
-for v in 1 0 1 0; do
-RMEM_ENC_GATE=$v timeout 400 python bench.py --steps 90 --warmup 9 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/bench11.log 2>&1; python -c "
-import json; d=json.loads(open('gpurun_out/bench11.log').read().strip().splitlines()[-1]); print('gate=$v', d['value'], d['e2e']['value'], d['host_enqueue_ms_per_step'], d.get('bank_indexes'))" || tail -5 gpurun_out/bench11.log
-done
-RMEM_ENC_GATE=1 timeout 400 python tools/dev_trace.py --prefetch > gpurun_out/trace_pf4.txt 2>&1; echo rc=$?
+timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv python bench.py --steps 12 --warmup 3 --profile-steps 10 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/ncu.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu.log | cut -c1-200
