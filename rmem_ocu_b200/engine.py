@@ -467,7 +467,7 @@ class DeAOTEngine:
         self._label_buf = None
         self._w_events = None
         # encoder prefetch (match_propogate_one_frame(..., next_img=)): the next frame's encoder runs on its own
-        # stream, into a staging set of embeddings, while this frame's LSTT + decoder run
+        # stream, into one of two alternating sets of embeddings, while this frame's LSTT + decoder run
         self._estream = None
         self._enc_done = None        # event: the prefetched embeddings are complete
         self._prefetched = None      # (embeddings, set index) of the frame encoded ahead, or None

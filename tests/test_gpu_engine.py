@@ -145,7 +145,7 @@ def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=T
 
 
 def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
-    """The production schedule (three CUDA graphs per frame, write path on its own stream overlapping the next
+    """The RMEM_LAZY_WRITE=0 schedule (three CUDA graphs per frame, write path on its own stream overlapping the next
     encoder, short-term branch forked inside the LSTT graph) against the plain single-stream eager run of the
     same kernels: same slot indexes after every frame, masks >= 99.9 % equal (random-init logit margins are near zero), logits equal to 1e-3."""
     H, W, n, latter = 240, 432, 14, 2
