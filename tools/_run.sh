@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-N=${NG:-2}
-timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 90 --warmup 9 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "rc=$?"; cut -c1-200 gpurun_out/bench_n$N.json
+timeout 900 ncu --profile-from-start off -k regex:gemm_bf16_tn_kernel -c 23 --set full --clock-control none --import-source on -f -o gpurun_out/r01_gemm python bench.py --steps 5 --warmup 3 --profile-steps 1 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/ncu_gemm.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_gemm.log | cut -c1-200; ls -la gpurun_out/*.ncu-rep
