@@ -578,10 +578,12 @@ class DeAOTEngine:
         a = ws.idcat[i][:, 256:] if i == 0 else ws.idcat[i]
         ops.linear(a, Lw["w_idv"], Lw["b_idv"], [(0, 512, ops.ACT_SILU, ops.OUT_BF16, dst, 512)])
 
-    def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass):
+    def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass, gate_ready=None):
         ws = self.ws
         cpf = _chunks_per_frame(T, ws.L)
         ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
+        if gate_ready is not None:
+            torch.cuda.current_stream().wait_event(gate_ready)    # the gate is computed on another branch
         ops.lt_attn_combine(ws.part_o, ws.part_m, ws.part_l, ws.tpe_bias if tpe else None,
                             tpe_row_indices(T) if tpe else None, T, ws.L, cpf, gate, out, mass)
 
@@ -627,9 +629,10 @@ class DeAOTEngine:
                        [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.kcur[i], 0),
                         (128, 640, ops.ACT_SILU, ops.OUT_BF16, ws.vcur[i], 0),
                         (640, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 0)])
-            if i > 0:
-                ops.linear(ws.idcat[i][:, :256], Lw["w_idu"], Lw["b_idu"],
-                           [(0, 512, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 512)])
+            idu = (lambda: ops.linear(ws.idcat[i][:, :256], Lw["w_idu"], Lw["b_idu"],
+                                      [(0, 512, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 512)])) if i > 0 else None
+            if idu is not None and not self.fork_branches:
+                idu()
             if is_reference:
                 # the reference frame is its own long- and short-term memory (transformer.py:1125-1135)
                 self._id_value(i, ws.vcur[i])
@@ -640,7 +643,14 @@ class DeAOTEngine:
             # captured graph), so its sub-wave kernels fill the SMs the long-term attention's ragged second wave
             # leaves idle.
             forked = self._fork()
+            idu_done = None
             with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
+                if idu is not None and forked:
+                    # the ID half of the gate U is first read by the attention epilogues (combine / aggregate):
+                    # its GEMM leaves the long-term chain for the short-term branch, which has slack
+                    idu()
+                    idu_done = torch.cuda.Event()
+                    idu_done.record()
                 # short-term 15x15 local attention over the previous frame, gate, dw5x5
                 ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
                 if we is not None and i == 0 and not we["waited"]:
@@ -657,7 +667,7 @@ class DeAOTEngine:
             if save_atten_weights and i == 0:
                 mass = ws.mass
             self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
-                                         ws.gated_a, mass)
+                                         ws.gated_a, mass, gate_ready=idu_done)
             ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
             if forked:
                 self._join()

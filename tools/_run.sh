@@ -1,2 +1,6 @@
 mkdir -p gpurun_out
-timeout 900 ncu --profile-from-start off -k regex:gemm_bf16_tn_kernel -c 23 --set full --clock-control none --import-source on -f -o gpurun_out/r01_gemm python bench.py --steps 5 --warmup 3 --profile-steps 1 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/ncu_gemm.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_gemm.log | cut -c1-200; ls -la gpurun_out/*.ncu-rep
+timeout 900 python -m pytest tests/test_gpu_engine.py -m gpu -x -q > gpurun_out/pytest_part.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/pytest_part.log
+for v in 1 2; do
+timeout 400 python bench.py --steps 90 --warmup 9 --no-cpu-baseline --seqs-per-gpu 0 > gpurun_out/bench11.log 2>&1; python -c "
+import json; d=json.loads(open('gpurun_out/bench11.log').read().strip().splitlines()[-1]); print('run$v', d['value'], d['e2e']['value'], d['host_enqueue_ms_per_step'], d.get('bank_indexes'))" || tail -5 gpurun_out/bench11.log
+done
