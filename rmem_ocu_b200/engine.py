@@ -506,6 +506,7 @@ class DeAOTEngine:
         self.T = 0                 # frames in the long-term bank (host mirror; deterministic)
         self.T_recorded = 0        # bank length when record_attn_weight was last written
         self._pending_w = None     # (T, update_long, do_evict, st) of a deferred write path
+        self._prefetching = False  # the last propagated frame started the next frame's encoder
         self.n_long_updates = 0
 
     def update_size(self, input_size, enc_size):
@@ -913,8 +914,8 @@ class DeAOTEngine:
 
     def _variants(self, T, output_size, sets, label):
         ev = self.deaot or T + 1 > self.capacity
-        if self.lazy_write:
-            # steady state of the deferred schedule: write path of the previous frame (bank length T, with or
+        if self.lazy_write and len(sets) > 1:
+            # steady state of the deferred schedule (prefetching loops): write path of the previous frame (bank length T, with or
             # without a long-term update) + read path of this frame; the stand-alone graphs are recorded on demand
             buf = self._label_buffer(label)
             for st in (0, 1):
@@ -983,6 +984,7 @@ class DeAOTEngine:
             return self._read_body(None, img_embs, T, osz, st)
         # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
         # running on its own stream) and, after waiting for that write path, LSTT + decoder
+        self._prefetching = next_img is not None
         if next_img is not None or self._prefetched is not None:
             if self._prefetched is None:
                 self._launch_encoder(img)                 # first frame of a prefetching loop: nothing encoded ahead
@@ -1019,7 +1021,9 @@ class DeAOTEngine:
             raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
         st = self.st
         body = lambda m: self._write_body(m, T, update_long, do_evict, st)
-        if self.lazy_write:
+        if self.lazy_write and self._prefetching:
+            # (a loop that does not prefetch keeps the write path on its own stream: there it overlaps the next
+            # frame's encoder, which is worth more than the two graph boundaries -- 1055 vs 1017 frames/s)
             self._wait_write()                                    # an earlier deferred write path, if any
             torch.mul(label, 1, out=self._label_buffer(label))    # SM copy (see _run)
             self._pending_w = (T, update_long, do_evict, st)

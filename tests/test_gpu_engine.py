@@ -174,8 +174,9 @@ def test_graph_and_stream_schedule_matches_eager(lib_built, monkeypatch):
 
 @pytest.mark.parametrize("prefetch", [False, True])
 def test_deferred_write_path_matches_immediate(lib_built, monkeypatch, prefetch):
-    """Default DeAOT schedule: update_short_term_memory defers its work into the next frame's graph, where it runs
-    as a branch beside layer 0 of the LSTT (engine._fused_body).  Against the plain eager single-stream run: same
+    """Default DeAOT schedule of a prefetching loop: update_short_term_memory defers its work into the next frame's
+    graph, where it runs as a branch beside layer 0 of the LSTT (engine._fused_body); a loop that does not prefetch
+    keeps the write path on its own stream.  Against the plain eager single-stream run: same
     logits (1e-3) and masks on every frame, same bank at the end -- with long-term updates and evictions on the
     way (gap 2, 1 + 2 slots, 14 frames) and the bank only read at the end, so the deferred path really runs."""
     H, W, n, latter = 240, 432, 14, 2
@@ -191,7 +192,7 @@ def test_deferred_write_path_matches_immediate(lib_built, monkeypatch, prefetch)
                                idx_every_frame=False))
     (ma, la, ia, ea), (mb, lb, ib, eb) = outs
     assert ea.aot_engines[0].lazy_write and not eb.aot_engines[0].lazy_write
-    keys = [k for k in ea.aot_engines[0]._graphs if k[0] == "wr"]
+    keys = [k for k in ea.aot_engines[0]._graphs if k[0] == ("wr" if prefetch else "write")]
     assert any(k[2] for k in keys) and any(not k[2] for k in keys)   # with and without a long-term update
     assert ia == ib and len(ia[-1][0]) == 3
     assert ea.aot_engines[0].eviction_debug()["n_evictions"] == eb.aot_engines[0].eviction_debug()["n_evictions"] > 0
