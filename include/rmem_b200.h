@@ -176,6 +176,24 @@ int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const floa
                           const float* beta, void* out, int out_f32, int L, int C, int groups,
                           void* workspace, void* stream);
 
+/* rmem_groupnorm_tokens without a caller workspace, for callers that cannot allocate device memory (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  This entry point has NO counterpart
+ * in the reference.  Same arguments and results as
+ * rmem_groupnorm_tokens minus `workspace`: the statistics scratch is a 256-byte file-scope `static __device__`
+ * array inside the library (csrc/fused.cu), resident on every GPU that loads the library until the process exits;
+ * its device address is resolved once per device (cudaGetSymbolAddress, on the first call with that device
+ * current).  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); it issues one
+ * cudaMemsetAsync of the scratch on `stream` and the two GroupNorm kernels.
+ *   Limit: groups <= RMEM_GN_STATIC_MAX_GROUPS (the scratch holds 16 * groups + 8 bytes), else RMEM_ERR_ARG with
+ *   an explanatory rmem_last_error().
+ *   Sharing: every call on a device uses the SAME array, which keeps the last call's contents (each call clears it
+ *   first).  Calls that overlap on the GPU (different streams, or graph branches) race on it and give wrong
+ *   results: serialise them, or use rmem_groupnorm_tokens with one workspace per concurrent call. */
+#define RMEM_GN_STATIC_MAX_GROUPS 8
+int rmem_groupnorm_tokens_static(const float* x_a, int Ca, const float* x_b, const float* gamma,
+                                 const float* beta, void* out, int out_f32, int L, int C, int groups,
+                                 void* stream);
+
 /* Per-query temporal-PE score bias and the time-shifted query (transformer.py:1142-1172):
  *   q_time = bf16(q + cur_pos_emb);  tpe_bias[q][r] = log2e/sqrt(C) * ((q + cur_pos_emb) . mem_pos_emb[r])
  *   q bf16 [L][C] (C = 128);  cur_pos_emb f32 [C];  mem_pos_emb f32 [4][C]

@@ -75,6 +75,7 @@ _SIGNATURES = {
     "rmem_dwconv5": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int,
                      _c_int, _c_void_p],
     "rmem_groupnorm_tokens": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 2,
+    "rmem_groupnorm_tokens_static": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p],
     "rmem_tpe_prepare": [_c_void_p] * 5 + [_c_int] * 2 + [_c_void_p],
     "rmem_local_banded_elems": [_c_int, _c_int],
     "rmem_local_attn_scores": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_void_p],

@@ -114,6 +114,11 @@ int rmem_groupnorm_tokens(const float* x_a, int Ca, const float* x_b, const floa
                           void* workspace, void* stream) {
   return groupnorm_tokens_launch(x_a, Ca, x_b, gamma, beta, out, out_f32, L, C, groups, workspace, ST(stream));
 }
+int rmem_groupnorm_tokens_static(const float* x_a, int Ca, const float* x_b, const float* gamma,
+                                 const float* beta, void* out, int out_f32, int L, int C, int groups,
+                                 void* stream) {
+  return groupnorm_tokens_static_launch(x_a, Ca, x_b, gamma, beta, out, out_f32, L, C, groups, ST(stream));
+}
 int rmem_tpe_prepare(const void* q, const float* cur_pos_emb, const float* mem_pos_emb,
                      void* q_time, float* tpe_bias, int L, int C, void* stream) {
   return tpe_prepare_launch(q, cur_pos_emb, mem_pos_emb, q_time, tpe_bias, L, C, ST(stream));

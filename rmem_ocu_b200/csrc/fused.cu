@@ -2,6 +2,7 @@
 // coalesced): LayerNorm (dual stream, bf16 out at a column offset), 5x5 depth-wise conv over the
 // token grid, token GroupNorm, TPE query preparation, foreground probability for the eviction rule.
 #include <cuda_bf16.h>
+#include <mutex>
 #include "sm100_ptx.cuh"
 #include "rmem_internal.h"
 
@@ -297,6 +298,56 @@ int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const floa
                                            out_f32 ? static_cast<float*>(out) : nullptr, L, C, groups,
                                            static_cast<double*>(workspace));
   return check_launch("gn_apply_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
+// Token GroupNorm without a caller workspace (rmem_groupnorm_tokens_static): the statistics scratch is a
+// file-scope device array instead of a pointer the caller allocated.  Every GPU that loads the library holds
+// these kGnStaticBytes bytes until the process exits.
+//
+// In HOST code the name `g_gn_static_ws` is only a host-side stand-in for the symbol, not a device address:
+// handing it to a kernel would fault (or, where the GPU can reach host memory, silently use the wrong memory).
+// The device address is looked up once per device with cudaGetSymbolAddress, with that device current, and it
+// is that pointer the kernels receive.
+constexpr int kGnStaticMaxGroups = RMEM_GN_STATIC_MAX_GROUPS;
+constexpr size_t kGnStaticBytes = 256;                    // >= 16 * kGnStaticMaxGroups + 8, one 256-byte line
+static_assert(16 * kGnStaticMaxGroups + 8 <= kGnStaticBytes, "static GroupNorm scratch too small");
+static __device__ __align__(256) unsigned char g_gn_static_ws[kGnStaticBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_gn_static_ptr[kMaxDevices];                // device address of g_gn_static_ws, per device
+static std::mutex g_gn_static_mu;
+
+static int gn_static_scratch(void** ptr) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_tokens_static: cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return set_error(RMEM_ERR_ARG, "groupnorm_tokens_static: device ordinal >= 64");
+  std::lock_guard<std::mutex> lock(g_gn_static_mu);
+  if (!g_gn_static_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_gn_static_ws);         // the current device's copy of the array
+    if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_tokens_static: cudaGetSymbolAddress");
+    if (!p) return set_error(RMEM_ERR_CUDA, "groupnorm_tokens_static: cudaGetSymbolAddress returned NULL");
+    g_gn_static_ptr[dev] = p;
+  }
+  *ptr = g_gn_static_ptr[dev];
+  return RMEM_OK;
+}
+
+int groupnorm_tokens_static_launch(const float* xa, int Ca, const float* xb, const float* gamma, const float* beta,
+                                   void* out, int out_f32, int L, int C, int groups, cudaStream_t stream) {
+  if (groups < 1 || groups > kGnStaticMaxGroups)
+    return set_error(RMEM_ERR_ARG, "groupnorm_tokens_static: groups exceeds RMEM_GN_STATIC_MAX_GROUPS (8): the "
+                                   "built-in scratch holds 16 * groups + 8 <= 256 bytes");
+  if (L < 1) return set_error(RMEM_ERR_ARG, "groupnorm_tokens_static: L must be >= 1");
+  void* ws = nullptr;
+  if (int r = gn_static_scratch(&ws)) return r;
+  // the array is shared by every call on this device and keeps the last call's contents: the accumulators and
+  // the arrival counter must start at zero (a memset is not an allocation; it is ordered on `stream`)
+  cudaError_t e = cudaMemsetAsync(ws, 0, kGnStaticBytes, stream);
+  if (e != cudaSuccess) return set_cuda_error(e, "groupnorm_tokens_static: cudaMemsetAsync");
+  return groupnorm_tokens_launch(xa, Ca, xb, gamma, beta, out, out_f32, L, C, groups, ws, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

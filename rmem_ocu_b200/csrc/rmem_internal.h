@@ -54,6 +54,8 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
 int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
                             const float* beta, void* out, int out_f32, int L, int C, int groups,
                             void* workspace, cudaStream_t stream);
+int groupnorm_tokens_static_launch(const float* xa, int Ca, const float* xb, const float* gamma, const float* beta,
+                                   void* out, int out_f32, int L, int C, int groups, cudaStream_t stream);
 int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* q_time, float* bias,
                        int L, int C, cudaStream_t stream);
 int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg, int h, int w,
