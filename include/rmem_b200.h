@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 3
+#define RMEM_ABI_VERSION 4
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -70,6 +70,29 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
                                const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
                                int chunks_per_frame, const void* gate, void* out,
                                float* attn_mass, void* stream);
+
+/* The same operator, second generation (csrc/lt_attn_sk.cu): one persistent, stream-K scheduled kernel on 2-CTA
+ * clusters that share every K / V tile by TMA multicast, followed by the merge of its segment partials.  It replaces
+ * the same reference code as the pair above (attention.py:174-193, 206; transformer.py:1140-1172, 1183-1192); the
+ * temporal-PE bias is added to the scores inside the kernel, so the combine step needs neither it nor T-many
+ * per-frame partials.  Results equal the first generation's to bf16 rounding.
+ *
+ *   n_clusters  0: one 2-CTA cluster per SM pair (the kernel then owns every SM while it runs); k > 0: at most k
+ *               clusters, which leaves SMs to kernels running on other streams.  The three calls of one attention
+ *               must be given the same value.
+ *   workspace   rmem_lt_attn_deaot_sk_workspace_bytes(L, T, n_clusters) bytes (take the maximum over the bank
+ *               lengths T in use), 256-byte aligned, owned by the caller, contents irrelevant on entry; partial
+ *               writes it, combine reads it -- one workspace per attention call in flight
+ *   tpe_bias    f32 [L][4] (log2 units, from rmem_tpe_prepare) or NULL;  tpe_rows_host  HOST i32 [T]
+ *   record      != 0: also write the per-(segment, frame) sums that attn_mass is built from
+ *   gate / out  bf16 [L][1024];  attn_mass f32 [L][T] or NULL (needs record != 0 in the partial call)
+ */
+int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int n_clusters);
+int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order, int T,
+                                  int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host,
+                                  int record, int n_clusters, void* workspace, int64_t workspace_bytes, void* stream);
+int rmem_lt_attn_deaot_sk_combine(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+                                  const void* workspace, int64_t workspace_bytes, void* stream);
 
 
 /* ---------------------------------------------------------------------------------------------
@@ -145,6 +168,12 @@ typedef struct rmem_gemm_segment {
 } rmem_gemm_segment;
 int rmem_linear(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N,
                 int K, const rmem_gemm_segment* segments_host, int n_segments, void* stream);
+
+/* rmem_linear with IEEE fp16 operands when ab_f16 != 0 (a and w fp16 instead of bf16; everything else as above):
+ * the decoder's 1x1 adapter convolutions (decoders/fpn.py:49-60) read the backbone's feature maps, which are fp16
+ * in the default configuration (fp16 keeps the masks within 99.9 % of the fp32 reference, bf16 does not). */
+int rmem_linear_ex(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
+                   const rmem_gemm_segment* segments_host, int n_segments, int ab_f16, void* stream);
 
 /* LayerNorm over the last dim (C = 256) of up to two [L][C] streams in one launch, bf16 output
  * written at a column offset of a wider buffer (so norm2 | id_norm2 land concatenated).
@@ -324,11 +353,23 @@ int rmem_pack_image(const float* img, int H, int W, void* out, void* stream);
  * zero elsewhere (conv padding, out-of-image pixels, channels 12..15). */
 int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream);
 
+/* The same packing with a choice of input and output types.  img_u8_hwc != 0: img is u8 interleaved [H][W][3]
+ * (a decoded frame as it comes off the host) and the normalisation of the reference's dataloader
+ * (dataloaders/video_transforms.py ToTensor: (x / 255 - mean) / std) happens here, (u8 / 255 - mean_host[c]) *
+ * inv_std_host[c] with mean_host / inv_std_host HOST arrays of 3 floats -- a quarter of the upload bytes of the f32
+ * planes; img_u8_hwc == 0: f32 planes as above.  out_f16 != 0 writes IEEE fp16 instead of bf16. */
+int rmem_pack_image_s2d_ex(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                           int H, int W, void* out, int out_f16, void* stream);
+
 /* Encoder stem max-pool, MaxPool2d(kernel 3, stride 2, padding 1) (networks/encoders/resnet.py:154):
  * x bf16 channels-last [H][W][C] -> y bf16 [(H-1)/2+1][(W-1)/2+1][C]; C a multiple of 8.  bias f32 [C] (or NULL)
  * and relu != 0 give y = relu(maxpool(x) + bias) = maxpool(relu(x + bias)): the stem's conv bias (folded BN,
  * resnet.py:151-153) and ReLU applied after the pool, on a quarter of the pixels. */
 int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, const float* bias, int relu, void* y, void* stream);
+
+/* rmem_maxpool3s2_nhwc on IEEE fp16 maps when f16 != 0 (bf16 otherwise). */
+int rmem_maxpool3s2_nhwc_ex(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                            void* stream);
 
 /* label[i] = (f32) argmax_c logits[c][i], first maximum -- the evaluator's softmax + argmax over the object
  * channel (networks/managers/evaluator.py:430-441); logits f32 [C][HW], label f32 [HW]. */

@@ -47,6 +47,17 @@ CLIPS = {
 }
 
 
+# free-running long clips (BASELINE.json configs 1 and 3 regimes): masks kept for every `mask_every`-th frame,
+# bank indexes after EVERY frame.  name -> (model, H, W, n_frames, n_obj, latter, gap, repeat, clip_seed, mask_every)
+#   clip_deaot_cfg2   : config 2 as written -- 480x864, 5 objects, K = 4, 100 frames, evaluator gap rule (5)
+#   clip_deaot_long   : config 4's regime -- K = 8 (eval_vost.sh:28), gap 67, 1150 frames at reduced resolution
+#                       (17 appends, 9 evictions)
+LONG_CLIPS = {
+    "clip_deaot_cfg2": ("r50_deaotl", 480, 864, 100, 5, 4, 5, 0, 1000, 10),
+    "clip_deaot_long": ("r50_deaotl", 160, 256, 1150, 3, 8, 67, 0, 1007, 50),
+}
+
+
 def _np(t):
     return t.detach().cpu().numpy()
 
@@ -60,7 +71,11 @@ def ref_model(name, latter, seed=0):
 
 # ------------------------------------------------------------------------------------------------
 def gen_clip(name):
-    mname, H, W, n, n_obj, latter, gap, repeat, cseed = CLIPS[name]
+    mask_every = 1
+    if name in LONG_CLIPS:
+        mname, H, W, n, n_obj, latter, gap, repeat, cseed, mask_every = LONG_CLIPS[name]
+    else:
+        mname, H, W, n, n_obj, latter, gap, repeat, cseed = CLIPS[name]
     cfg, model = ref_model(mname, latter)
     imgs, lab = _synth.clip(H, W, n, n_obj, cseed, repeat)
     eng = RL.build_engine(model, cfg, long_term_mem_gap=gap)
@@ -72,7 +87,8 @@ def gen_clip(name):
             lg = eng.match_propogate_one_frame(imgs[f], output_size=(H, W))
             prob = torch.softmax(lg, dim=1)
             label = torch.argmax(prob, dim=1, keepdim=True).float()
-            masks.append(_np(label[0, 0].to(torch.uint8)))
+            if f % mask_every == 0 or f == n - 1:
+                masks.append(_np(label[0, 0].to(torch.uint8)))
             if f in (1, n - 1):
                 logits[f] = _np(eng.aot_engines[0].pred_id_logits[0])
             eng.update_memory(F.interpolate(label, size=eng.input_size_2d, mode="nearest"))
@@ -84,6 +100,8 @@ def gen_clip(name):
     out = dict(meta=np.array([H, W, n, n_obj, latter, gap, repeat, cseed], np.int64),
                model=np.array(mname), masks=np.stack(masks), indexes=idx_arr,
                logits_ref_frame=logits[0], logits_first=logits[1], logits_last=logits[n - 1])
+    if name in LONG_CLIPS:
+        out["mask_frames"] = np.array([f for f in range(1, n) if f % mask_every == 0 or f == n - 1], np.int32)
     out["margins"] = oracle_margins(name, idx_log)
     return out
 
@@ -94,7 +112,7 @@ def oracle_margins(name, ref_idx_log):
     Doubles as a cross-check: the oracle's bank indexes must equal the reference's after every frame.  The GPU
     tests use it to assert that a fixture has no near-tie a bf16 kernel could not resolve."""
     from oracle import restate as R
-    mname, H, W, n, n_obj, latter, gap, repeat, cseed = CLIPS[name]
+    mname, H, W, n, n_obj, latter, gap, repeat, cseed = (LONG_CLIPS[name][:9] if name in LONG_CLIPS else CLIPS[name])
     kind = "deaot" if "deaot" in mname else "aot"
     _, sd = _synth.models(latter, vos=kind)
     imgs, lab = _synth.clip(H, W, n, n_obj, cseed, repeat)
@@ -216,6 +234,7 @@ GENERATORS = {"evict_aot": lambda: gen_evict("aot"), "evict_deaot": lambda: gen_
               "ops_deaot": gen_ops_deaot, "ops_aot": gen_ops_aot,
               "layer_aot": lambda: gen_layer("aot"), "layer_deaot": lambda: gen_layer("deaot")}
 GENERATORS.update({k: (lambda k=k: gen_clip(k)) for k in CLIPS})
+GENERATORS.update({k: (lambda k=k: gen_clip(k)) for k in LONG_CLIPS})
 
 
 def main():

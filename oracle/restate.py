@@ -68,16 +68,16 @@ def one_hot_mask(mask, cls_num):
     return (mask == idx).float(), (mask == 255).float()
 
 
-def position_embedding_sine(h, w, num_pos_feats=128, temperature=10000.0):
+def position_embedding_sine(h, w, num_pos_feats=128, temperature=10000.0, device=None):
     # networks/layers/position.py:35-79 with normalize=True, scale=2*pi (models/aot.py:87-90)
-    gy, gx = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    gy, gx = torch.meshgrid(torch.arange(h, device=device), torch.arange(w, device=device), indexing="ij")
     y_embed = gy.unsqueeze(0).float()
     x_embed = gx.unsqueeze(0).float()
     eps = 1e-6
     scale = 2 * math.pi
     y_embed = y_embed / (y_embed[:, -1:, :] + eps) * scale
     x_embed = x_embed / (x_embed[:, :, -1:] + eps) * scale
-    dim_t = torch.arange(num_pos_feats, dtype=torch.float32)
+    dim_t = torch.arange(num_pos_feats, dtype=torch.float32, device=device)
     dim_t = temperature ** (2 * torch.div(dim_t, 2, rounding_mode="trunc") / num_pos_feats)
     pos_x = x_embed[:, :, :, None] / dim_t
     pos_y = y_embed[:, :, :, None] / dim_t
@@ -183,9 +183,9 @@ def local_gated_propagation(q, k, v, u, size_2d, sd, prefix, d_att=128, max_dis=
     qs = q / (d_att ** 0.5)                                   # (:317)
     kp = F.pad(k, (max_dis,) * 4)
     vp = F.pad(v, (max_dis,) * 4)
-    ones = F.pad(torch.ones(1, 1, h, w), (max_dis,) * 4)
-    qk = torch.empty(n, win * win, h, w)
-    inside = torch.empty(1, win * win, h, w)
+    ones = F.pad(torch.ones(1, 1, h, w, device=q.device), (max_dis,) * 4)
+    qk = torch.empty(n, win * win, h, w, device=q.device)
+    inside = torch.empty(1, win * win, h, w, device=q.device)
     for dy in range(win):
         for dx in range(win):
             t = dy * win + dx                                 # F.unfold tap order (:409-412)
@@ -195,7 +195,7 @@ def local_gated_propagation(q, k, v, u, size_2d, sd, prefix, d_att=128, max_dis=
     qk = qk - (1 - inside.view(1, win * win, h * w)) * 1e8    # (:344), fp32 constant
     attn = torch.softmax(qk, dim=1)                           # over the 225 taps (:346)
     a4 = attn.view(n, win * win, h, w)
-    agg = torch.zeros(n, c, h, w)
+    agg = torch.zeros(n, c, h, w, device=q.device)
     for dy in range(win):
         for dx in range(win):
             t = dy * win + dx
@@ -234,6 +234,9 @@ def eviction_scores(W, fg, idx, state):
     idx: long_memories_indexes (len T_old + 1, newest last).  Mutates `state`.
     Returns (drop_idx, detail dict)."""
     T_old = W.shape[1]
+    W = W.float().cpu()                       # the reference synchronises here too (transformer.py:353 / 906)
+    if fg is not None:
+        fg = fg.float().cpu()
     attn_weight = torch.stack([W, W]).mean(dim=0)
     if fg is not None:
         attn_weight = attn_weight * fg.reshape(-1, 1)
@@ -615,7 +618,7 @@ class Engine:
     def assign_identity(self, one_hot, ignore_mask=None):
         # aot_engine.py:208-232 with MODEL_IGNORE_TOKEN = True, no id shuffle
         if ignore_mask is None:
-            ignore_mask = torch.zeros(one_hot.shape[0], 1, one_hot.shape[2], one_hot.shape[3])
+            ignore_mask = torch.zeros(one_hot.shape[0], 1, one_hot.shape[2], one_hot.shape[3], device=one_hot.device)
         one_hot = one_hot.clone()
         one_hot[:, 0] = one_hot[:, 0] * (ignore_mask == 0).float().squeeze()
         x = torch.cat((one_hot, ignore_mask), 1)
@@ -640,7 +643,8 @@ class Engine:
             self.enc_hw = self.enc_size_2d[0] * self.enc_size_2d[1]
         if self.pos_emb is None:
             h, w = self.enc_size_2d
-            self.pos_emb = position_embedding_sine(h, w).view(1, -1, self.enc_hw).permute(2, 0, 1)
+            self.pos_emb = position_embedding_sine(h, w, device=embs[-1].device).view(
+                1, -1, self.enc_hw).permute(2, 0, 1)
         id_emb = self.assign_identity(one_hot)
         out = self._lstt_forward(embs, id_emb, False)
         self.last_mem_step = frame_step
@@ -687,6 +691,81 @@ class Engine:
             if d is not None:
                 d["frame_step"] = self.frame_step
                 self.evict_log.append(d)
+
+
+class InferEngine:
+    """AOTInferEngine / DeAOTInferEngine (aot_engine.py:571-725, deaot_engine.py:20-56): more than
+    ``max_aot_obj_num`` objects are split over several engines whose logits are merged every frame.
+
+    One deliberate difference from the reference: there every AOTEngine of the list drives the SAME model object,
+    and the memory banks hang off ``model.LSTT`` (transformer.py:306-322, 438-443), so with two object groups the
+    second engine re-initialises and overwrites the first one's memories ("ownership").  That
+    is an artefact of where the reference keeps its state, not part of the algorithm; here (and in the product)
+    every object group owns its memories -- the single-group case, which is what every fixture pins, is identical."""
+
+    def __init__(self, sd, deaot, former=1, latter=4, long_term_mem_gap=9999, max_aot_obj_num=10):
+        self.sd, self.deaot, self.former, self.latter = sd, deaot, former, latter
+        self.long_term_mem_gap = long_term_mem_gap
+        self.max_aot_obj_num = max_aot_obj_num
+        self.aot_engines = []
+        self.obj_nums = None
+
+    def separate_mask(self, mask):
+        # aot_engine.py:604-628 (label-map branch; the probability branch is reachable with batch > 1 only)
+        if mask is None:
+            return [None] * len(self.aot_engines)
+        if len(self.aot_engines) == 1:
+            return [mask]
+        out = []
+        for idx in range(len(self.aot_engines)):
+            start_id = idx * self.max_aot_obj_num + 1
+            end_id = (idx + 1) * self.max_aot_obj_num
+            fg_mask = ((mask >= start_id) & (mask <= end_id)).float()
+            out.append((fg_mask * mask - start_id + 1) * fg_mask)
+        return out
+
+    def soft_logit_aggregation(self, all_logits):
+        # aot_engine.py:650-673
+        if len(all_logits) == 1:
+            return all_logits[0]
+        fg_probs, bg_probs = [], []
+        for logit in all_logits:
+            prob = torch.softmax(logit, dim=1)
+            bg_probs.append(prob[:, 0:1])
+            fg_probs.append(prob[:, 1:1 + self.max_aot_obj_num])
+        bg_prob = torch.prod(torch.cat(bg_probs, dim=1), dim=1, keepdim=True)
+        merged_prob = torch.cat([bg_prob] + fg_probs, dim=1).clamp(1e-5, 1 - 1e-5)
+        return torch.logit(merged_prob)
+
+    def add_reference_frame(self, img, mask, obj_nums, frame_step=-1):
+        # aot_engine.py:675-702
+        if isinstance(obj_nums, list):
+            obj_nums = obj_nums[0]
+        self.obj_nums = obj_nums
+        aot_num = max(int(math.ceil(obj_nums / self.max_aot_obj_num)), 1)
+        while aot_num > len(self.aot_engines):
+            self.aot_engines.append(Engine(self.sd, self.deaot, self.former, self.latter, self.long_term_mem_gap,
+                                           self.max_aot_obj_num))
+        embs = encode_image(img, self.sd)                     # the same image for every group
+        for eng, m in zip(self.aot_engines, self.separate_mask(mask)):
+            eng.long_term_mem_gap = self.long_term_mem_gap
+            if eng.input_size_2d is None:
+                eng.input_size_2d = tuple(img.shape[2:])
+                eng.enc_size_2d = tuple(embs[-1].shape[2:])
+                eng.enc_hw = eng.enc_size_2d[0] * eng.enc_size_2d[1]
+            eng.add_reference_frame(img, m, obj_nums=[self.max_aot_obj_num], frame_step=frame_step, img_embs=embs)
+        self.input_size_2d = self.aot_engines[0].input_size_2d
+
+    def match_propogate_one_frame(self, img=None, output_size=None):
+        # aot_engine.py:704-712
+        embs = encode_image(img, self.sd)
+        return self.soft_logit_aggregation([eng.match_propogate_one_frame(img, img_embs=embs, output_size=output_size)
+                                            for eng in self.aot_engines])
+
+    def update_memory(self, curr_mask):
+        # aot_engine.py:714-720
+        for eng, m in zip(self.aot_engines, self.separate_mask(curr_mask)):
+            eng.update_short_term_memory(m)
 
 
 def run_clip(engine, images, label0, n_obj, output_size=None):

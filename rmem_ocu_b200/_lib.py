@@ -56,11 +56,17 @@ _c_int = ctypes.c_int
 _c_float = ctypes.c_float
 
 # name -> argtypes; every function returns int (status) unless listed in _RESTYPES
+_c_float_p = ctypes.POINTER(ctypes.c_float)
 _SIGNATURES = {
     "rmem_abi_version": [],
     "rmem_last_error": [],
     "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
+    "rmem_lt_attn_deaot_sk_workspace_bytes": [_c_int, _c_int, _c_int],
+    "rmem_lt_attn_deaot_sk_partial": [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p, _c_void_p, _c_int, _c_int, _c_void_p,
+                                                                     ctypes.c_int64, _c_void_p],
+    "rmem_lt_attn_deaot_sk_combine": [_c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p,
+                                      ctypes.c_int64, _c_void_p],
     "rmem_mha_partial": [_c_void_p, _c_int, _c_void_p, _c_int, ctypes.c_int64, _c_void_p, _c_int, ctypes.c_int64,
                          _c_void_p] + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_mha_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
@@ -71,6 +77,8 @@ _SIGNATURES = {
     "rmem_groupnorm_gelu_tokens": [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p] * 2,
     "rmem_linear": [_c_void_p, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_int,
                     _c_void_p, _c_int, _c_void_p],
+    "rmem_linear_ex": [_c_void_p, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_int,
+                       _c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_layernorm": [_c_void_p] * 4 + [_c_int] * 2 + [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p],
     "rmem_dwconv5": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int,
                      _c_int, _c_void_p],
@@ -88,6 +96,8 @@ _SIGNATURES = {
                           [_c_int] * 4 + [_c_void_p, _c_int, _c_int, _c_void_p],
     "rmem_pack_image": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
     "rmem_pack_image_s2d": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
+    "rmem_pack_image_s2d_ex": [_c_void_p, _c_int, _c_float_p, _c_float_p, _c_int, _c_int, _c_void_p, _c_int, _c_void_p],
+    "rmem_maxpool3s2_nhwc_ex": [_c_void_p, _c_int, _c_int, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_void_p],
     "rmem_maxpool3s2_nhwc": [_c_void_p, _c_int, _c_int, _c_int, _c_void_p, _c_int, _c_void_p, _c_void_p],
     "rmem_argmax_label": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
     "rmem_bank_init": [_c_void_p, _c_int, _c_void_p],
@@ -106,12 +116,14 @@ class GemmSegment(ctypes.Structure):
                 ("dst_col0", ctypes.c_int32)]
 
 
+ABI_VERSION = 4          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
 MAX_BANK = 16
 MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8
 ACT_NONE, ACT_SILU = 0, 1
 OUT_BF16, OUT_F32, OUT_F32_ACCUM = 0, 1, 2
-_RESTYPES = {"rmem_last_error": ctypes.c_char_p, "rmem_local_banded_elems": ctypes.c_int64}
+_RESTYPES = {"rmem_last_error": ctypes.c_char_p, "rmem_local_banded_elems": ctypes.c_int64,
+             "rmem_lt_attn_deaot_sk_workspace_bytes": ctypes.c_int64}
 
 
 def declared_symbols():
@@ -136,6 +148,12 @@ def lib():
         fn = getattr(handle, name)  # AttributeError if the symbol is missing: fail loudly
         fn.argtypes = argtypes
         fn.restype = _RESTYPES.get(name, _c_int)
+    got = handle.rmem_abi_version()
+    if got != ABI_VERSION:
+        # a stale binary (the .so is git-ignored and shipped out of band) would be called with mismatched
+        # signatures / struct layouts and corrupt memory silently
+        raise RuntimeError("librmem_b200.so has ABI version %d, the Python binding expects %d: rebuild it "
+                           "(python -c 'import __graft_entry__ as g; g.build()')" % (got, ABI_VERSION))
     _lib = handle
     return _lib
 

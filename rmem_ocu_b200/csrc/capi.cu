@@ -25,16 +25,29 @@ int check_launch(const char* kernel_name) {
 }
 
 TensorMapEncodeFn get_tensor_map_encoder() {
-  static TensorMapEncodeFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
+  // function-local static with an initialiser: resolved once, thread-safe (C++11)
+  static const TensorMapEncodeFn fn = []() -> TensorMapEncodeFn {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult qres;
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
-    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<TensorMapEncodeFn>(p);
-  }
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) return reinterpret_cast<TensorMapEncodeFn>(p);
+    return nullptr;
+  }();
   return fn;
+}
+
+int ensure_dynamic_smem(const void* kernel, SmemOptIn* rec, int bytes, const char* what) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_cuda_error(e, what);
+  if (dev < 0 || dev >= kMaxDevices) return set_error(RMEM_ERR_ARG, "device ordinal >= 64");
+  if (rec->granted[dev].load(std::memory_order_acquire) >= bytes) return RMEM_OK;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return set_cuda_error(e, what);
+  // racing threads both set the attribute (idempotent); the record only ever grows
+  int seen = rec->granted[dev].load(std::memory_order_relaxed);
+  while (seen < bytes && !rec->granted[dev].compare_exchange_weak(seen, bytes, std::memory_order_release)) {}
+  return RMEM_OK;
 }
 
 }  // namespace rmem
@@ -64,6 +77,20 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
 }
 
 #define ST(s) static_cast<cudaStream_t>(s)
+
+int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int n_clusters) {
+  return lt_attn_sk_workspace_bytes(L, T, n_clusters);
+}
+int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order, int T,
+                                  int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host,
+                                  int record, int n_clusters, void* workspace, int64_t workspace_bytes, void* stream) {
+  return lt_attn_sk_partial_launch(q, kbank, vbank, order, T, L, n_slots, tpe_bias, tpe_rows_host, record, n_clusters,
+                                   workspace, workspace_bytes, ST(stream));
+}
+int rmem_lt_attn_deaot_sk_combine(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+                                  const void* workspace, int64_t workspace_bytes, void* stream) {
+  return lt_attn_sk_combine_launch(T, L, gate, out, attn_mass, n_clusters, workspace, workspace_bytes, ST(stream));
+}
 
 int rmem_mha_partial(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride,
                      const void* v, int ldv, int64_t v_slot_stride, const int32_t* order, int T, int L,
@@ -98,6 +125,10 @@ int rmem_groupnorm_gelu_tokens(const float* x, const float* gamma, const float* 
 int rmem_linear(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N,
                 int K, const rmem_gemm_segment* segments_host, int n_segments, void* stream) {
   return gemm_launch(a, lda, w, ldw, bias, M, N, K, segments_host, n_segments, ST(stream));
+}
+int rmem_linear_ex(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
+                   const rmem_gemm_segment* segments_host, int n_segments, int ab_f16, void* stream) {
+  return gemm_ex_launch(a, lda, w, ldw, bias, M, N, K, segments_host, n_segments, ab_f16, ST(stream));
 }
 int rmem_layernorm(const void* x0, const float* gamma0, const float* beta0, void* out0, int ld0,
                    int col0, const void* x1, const float* gamma1, const float* beta1, void* out1,
@@ -153,6 +184,14 @@ int rmem_pack_image(const float* img, int H, int W, void* out, void* stream) {
 }
 int rmem_pack_image_s2d(const float* img, int H, int W, void* out, void* stream) {
   return pack_image_s2d_launch(img, H, W, out, ST(stream));
+}
+int rmem_pack_image_s2d_ex(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                           int H, int W, void* out, int out_f16, void* stream) {
+  return pack_image_s2d_ex_launch(img, img_u8_hwc, mean_host, inv_std_host, H, W, out, out_f16, ST(stream));
+}
+int rmem_maxpool3s2_nhwc_ex(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                            void* stream) {
+  return maxpool3s2_nhwc_ex_launch(x, H, W, C, bias, relu, y, f16, ST(stream));
 }
 int rmem_maxpool3s2_nhwc(const void* x, int H, int W, int C, const float* bias, int relu, void* y, void* stream) {
   return maxpool3s2_nhwc_launch(x, H, W, C, bias, relu, y, ST(stream));

@@ -6,6 +6,7 @@
 //   gn_nhwc_stats / gn_nhwc_apply : GroupNorm over (C/groups channels x H*W pixels) + optional ReLU
 //   upsample_add_nhwc             : out = a + bilinear_align_corners(x)   (adapter(shortcut) + upsampled x)
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include "rmem_internal.h"
 
 namespace rmem {
@@ -242,13 +243,32 @@ int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t st
   return check_launch("pack_image_kernel");
 }
 
+// 16-bit activation types of the cuDNN backbone: bf16 or IEEE fp16 (same storage size, same tensor-core rate; fp16
+// carries 3 more mantissa bits, which is what keeps the masks within 99.9 % of the fp32 reference).
+template <typename T2> struct Pair16;
+template <> struct Pair16<__nv_bfloat162> {
+  static __device__ __forceinline__ __nv_bfloat162 from(float a, float b) { return __floats2bfloat162_rn(a, b); }
+  static __device__ __forceinline__ float2 to(__nv_bfloat162 v) { return __bfloat1622float2(v); }
+};
+template <> struct Pair16<__half2> {
+  static __device__ __forceinline__ __half2 from(float a, float b) { return __floats2half2_rn(a, b); }
+  static __device__ __forceinline__ float2 to(__half2 v) { return __half22float2(v); }
+};
+
 // Encoder input for the space-to-depth form of the stem: the 7x7 stride-2 convolution on 3 channels equals a 4x4
 // stride-1 convolution on the 2x2 space-to-depth image (12 channels, padded to 16), which the tensor-core
-// convolution kernels run ~4x faster than the 8-channel strided form.  f32 planes [3][H][W] -> bf16 channels-last
-// [Hs+3][Ws+3][16], Hs = ceil(H/2): out[y'+2][x'+2][(dy*2+dx)*3+c] = img[c][2y'+dy][2x'+dx]; the two leading / one
-// trailing border rows and columns (the convolution's padding), out-of-image pixels and channels 12..15 are zero.
+// convolution kernels run ~4x faster than the 8-channel strided form.  f32 planes [3][H][W] -- or u8 interleaved
+// [H][W][3] pixels, normalised here as (u8 / 255 - mean[c]) * inv_std[c] so a caller uploads a quarter of the bytes
+// -- -> 16-bit channels-last [Hs+3][Ws+3][16], Hs = ceil(H/2): out[y'+2][x'+2][(dy*2+dx)*3+c] = img[c][2y'+dy][2x'+dx];
+// the two leading / one trailing border rows and columns (the convolution's padding), out-of-image pixels and
+// channels 12..15 are zero.
+struct PackNorm {
+  float mean[3], inv_std[3];
+};
+
+template <typename T2, bool kU8>
 __global__ void __launch_bounds__(256)
-pack_image_s2d_kernel(const float* __restrict__ img, int H, int W, int Hs, int Ws, __nv_bfloat16* __restrict__ out) {
+pack_image_s2d_kernel(const void* __restrict__ img_, PackNorm nrm, int H, int W, int Hs, int Ws, T2* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int Wp = Ws + 3;
   if (i >= (Hs + 3) * Wp) return;
@@ -263,41 +283,67 @@ pack_image_s2d_kernel(const float* __restrict__ img, int H, int W, int Hs, int W
       for (int dx = 0; dx < 2; ++dx) {
         const int y = 2 * yp + dy, x = 2 * xp + dx;
         if (y < H && x < W) {
+          if (kU8) {
+            const uint8_t* px = static_cast<const uint8_t*>(img_) + (static_cast<size_t>(y) * W + x) * 3;
 #pragma unroll
-          for (int c = 0; c < 3; ++c) v[(dy * 2 + dx) * 3 + c] = img[(static_cast<size_t>(c) * H + y) * W + x];
+            for (int c = 0; c < 3; ++c)
+              v[(dy * 2 + dx) * 3 + c] = (static_cast<float>(px[c]) * (1.f / 255.f) - nrm.mean[c]) * nrm.inv_std[c];
+          } else {
+            const float* img = static_cast<const float*>(img_);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) v[(dy * 2 + dx) * 3 + c] = img[(static_cast<size_t>(c) * H + y) * W + x];
+          }
         }
       }
     }
   }
   uint4 pk[2];
-  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+  T2* h = reinterpret_cast<T2*>(pk);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+  for (int k = 0; k < 8; ++k) h[k] = Pair16<T2>::from(v[2 * k], v[2 * k + 1]);
   reinterpret_cast<uint4*>(out)[2 * i] = pk[0];
   reinterpret_cast<uint4*>(out)[2 * i + 1] = pk[1];
 }
 
-int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream) {
+int pack_image_s2d_ex_launch(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                             int H, int W, void* out, int out_f16, cudaStream_t stream) {
   if (H < 1 || W < 1) return set_error(RMEM_ERR_ARG, "pack_image_s2d: bad shape");
+  if (img_u8_hwc && (!mean_host || !inv_std_host))
+    return set_error(RMEM_ERR_ARG, "pack_image_s2d: u8 input needs mean / inv_std");
+  PackNorm nrm = {{0.f, 0.f, 0.f}, {1.f, 1.f, 1.f}};
+  if (img_u8_hwc)
+    for (int c = 0; c < 3; ++c) { nrm.mean[c] = mean_host[c]; nrm.inv_std[c] = inv_std_host[c]; }
   const int Hs = (H + 1) / 2, Ws = (W + 1) / 2;
   const int n = (Hs + 3) * (Ws + 3);
-  pack_image_s2d_kernel<<<(n + 255) / 256, 256, 0, stream>>>(img, H, W, Hs, Ws, static_cast<__nv_bfloat16*>(out));
+  const int grid = (n + 255) / 256;
+  if (out_f16) {
+    if (img_u8_hwc) pack_image_s2d_kernel<__half2, true><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__half2*>(out));
+    else pack_image_s2d_kernel<__half2, false><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__half2*>(out));
+  } else {
+    if (img_u8_hwc) pack_image_s2d_kernel<__nv_bfloat162, true><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__nv_bfloat162*>(out));
+    else pack_image_s2d_kernel<__nv_bfloat162, false><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__nv_bfloat162*>(out));
+  }
   return check_launch("pack_image_s2d_kernel");
 }
 
-// Encoder stem max-pool (encoders/resnet.py:154, MaxPool2d(3, stride 2, padding 1)) on bf16 channels-last
+int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream) {
+  return pack_image_s2d_ex_launch(img, 0, nullptr, nullptr, H, W, out, 0, stream);
+}
+
+// Encoder stem max-pool (encoders/resnet.py:154, MaxPool2d(3, stride 2, padding 1)) on 16-bit channels-last
 // [H][W][C] -> [Ho][Wo][C]: one thread per output pixel and 8-channel group, 128-bit loads and stores.  With a
 // bias and / or relu it computes relu(maxpool(x) + bias) = maxpool(relu(x + bias)) (both maps are monotone per
 // channel), so the stem convolution can run without its own bias + ReLU pass over the full-resolution map.
+template <typename T2>
 __global__ void __launch_bounds__(256)
-maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8, const float* __restrict__ bias,
-                       int relu, __nv_bfloat16* __restrict__ y, int Ho, int Wo) {
+maxpool3s2_nhwc_kernel(const T2* __restrict__ x, int H, int W, int C8, const float* __restrict__ bias,
+                       int relu, T2* __restrict__ y, int Ho, int Wo) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Ho * Wo * C8) return;
   const int c8 = i % C8, pix = i / C8;
   const int ox = pix % Wo, oy = pix / Wo;
-  const __nv_bfloat162 ninf = __floats2bfloat162_rn(-INFINITY, -INFINITY);
-  __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
+  const T2 ninf = Pair16<T2>::from(-INFINITY, -INFINITY);
+  T2 m[4] = {ninf, ninf, ninf, ninf};
 #pragma unroll
   for (int dy = 0; dy < 3; ++dy) {
     const int iy = 2 * oy - 1 + dy;
@@ -306,36 +352,45 @@ maxpool3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int H, int W, int C8
     for (int dx = 0; dx < 3; ++dx) {
       const int ix = 2 * ox - 1 + dx;
       if (ix < 0 || ix >= W) continue;
-      const uint4 v = *reinterpret_cast<const uint4*>(x + (static_cast<size_t>(iy) * W + ix) * (C8 * 8) + c8 * 8);
-      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+      const uint4 v = *reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(iy) * W + ix) * C8 + c8) * 4);
+      const T2* h = reinterpret_cast<const T2*>(&v);
 #pragma unroll
       for (int e = 0; e < 4; ++e) m[e] = __hmax2(m[e], h[e]);
     }
   }
   uint4 o;
-  __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+  T2* oh = reinterpret_cast<T2*>(&o);
 #pragma unroll
   for (int e = 0; e < 4; ++e) {
     if (bias || relu) {
-      float2 f = __bfloat1622float2(m[e]);
+      float2 f = Pair16<T2>::to(m[e]);
       if (bias) { f.x += bias[c8 * 8 + 2 * e]; f.y += bias[c8 * 8 + 2 * e + 1]; }
       if (relu) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); }
-      oh[e] = __floats2bfloat162_rn(f.x, f.y);
+      oh[e] = Pair16<T2>::from(f.x, f.y);
     } else {
       oh[e] = m[e];
     }
   }
-  *reinterpret_cast<uint4*>(y + static_cast<size_t>(pix) * (C8 * 8) + c8 * 8) = o;
+  *reinterpret_cast<uint4*>(y + (static_cast<size_t>(pix) * C8 + c8) * 4) = o;
+}
+
+int maxpool3s2_nhwc_ex_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                              cudaStream_t stream) {
+  if (H < 1 || W < 1 || C < 8 || (C & 7)) return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const int n = Ho * Wo * (C / 8);
+  if (f16)
+    maxpool3s2_nhwc_kernel<__half2><<<(n + 255) / 256, 256, 0, stream>>>(static_cast<const __half2*>(x), H, W, C / 8, bias,
+                                                                        relu, static_cast<__half2*>(y), Ho, Wo);
+  else
+    maxpool3s2_nhwc_kernel<__nv_bfloat162><<<(n + 255) / 256, 256, 0, stream>>>(
+        static_cast<const __nv_bfloat162*>(x), H, W, C / 8, bias, relu, static_cast<__nv_bfloat162*>(y), Ho, Wo);
+  return check_launch("maxpool3s2_nhwc_kernel");
 }
 
 int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y,
                            cudaStream_t stream) {
-  if (H < 1 || W < 1 || C < 8 || (C & 7)) return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
-  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
-  const int n = Ho * Wo * (C / 8);
-  maxpool3s2_nhwc_kernel<<<(n + 255) / 256, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), H, W, C / 8,
-                                                                bias, relu, static_cast<__nv_bfloat16*>(y), Ho, Wo);
-  return check_launch("maxpool3s2_nhwc_kernel");
+  return maxpool3s2_nhwc_ex_launch(x, H, W, C, bias, relu, y, 0, stream);
 }
 
 // label[y][x] = argmax_c logits[c][y][x] (first maximum, like torch.argmax) as f32 -- the evaluator's

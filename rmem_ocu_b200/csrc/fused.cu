@@ -190,13 +190,10 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (dwconv5) failed");
   }
   const size_t smem = 128 + static_cast<size_t>(kDwRows + 4) * box_w * kDwCh * 2;
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    cudaError_t e = cudaFuncSetAttribute(dwconv5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(smem));
-    if (e != cudaSuccess) return set_cuda_error(e, "dwconv5: cudaFuncSetAttribute");
-    smem_set = smem;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(dwconv5_kernel), &optin, static_cast<int>(smem),
+                                  "dwconv5: cudaFuncSetAttribute"))
+    return r;
   dim3 grid((h + kDwRows - 1) / kDwRows, C / kDwCh);
   dwconv5_kernel<<<grid, kDwThreads, smem, stream>>>(tm_x, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0, h, w,
                                                      C, box_w);
@@ -314,7 +311,6 @@ constexpr size_t kGnStaticBytes = 256;                    // >= 16 * kGnStaticMa
 static_assert(16 * kGnStaticMaxGroups + 8 <= kGnStaticBytes, "static GroupNorm scratch too small");
 static __device__ __align__(256) unsigned char g_gn_static_ws[kGnStaticBytes];
 
-constexpr int kMaxDevices = 64;
 static void* g_gn_static_ptr[kMaxDevices];                // device address of g_gn_static_ws, per device
 static std::mutex g_gn_static_mu;
 
@@ -369,9 +365,14 @@ tpe_prepare_kernel(const __nv_bfloat16* __restrict__ q, const float* __restrict_
   o[0] = __floats2bfloat162_rn(v[0], v[1]);
   o[1] = __floats2bfloat162_rn(v[2], v[3]);
   *reinterpret_cast<uint2*>(q_time + static_cast<size_t>(row) * 128 + lane * 4) = pk;
-  // the bias uses the same bf16-rounded q' the tensor cores will see, so both score terms agree
+  // the bias is a rank-1 term kept in f32: it uses the un-rounded q' (the reference adds the embedding to K in
+  // fp32, transformer.py:1142-1172), so it carries only the bf16 rounding q already has
+#ifdef RMEM_TPE_BIAS_FROM_ROUNDED_Q
   const float r0 = __bfloat162float(o[0].x), r1 = __bfloat162float(o[0].y);
   const float r2 = __bfloat162float(o[1].x), r3 = __bfloat162float(o[1].y);
+#else
+  const float r0 = v[0], r1 = v[1], r2 = v[2], r3 = v[3];
+#endif
 #pragma unroll
   for (int r = 0; r < RMEM_TPE_ROWS; ++r) {
     const float4 m4 = *reinterpret_cast<const float4*>(mem + r * 128 + lane * 4);

@@ -33,6 +33,7 @@ struct GemmParams {
   int M, N, K;
   const float* bias;   // [N] or nullptr
   int n_seg;
+  int ab_f16;          // A and W are IEEE fp16 instead of bf16 (the backbone's feature maps feeding the adapters)
   rmem_gemm_segment seg[RMEM_GEMM_MAX_SEGMENTS];
 };
 
@@ -93,7 +94,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kGM, BN, 0, 0);
+      const uint32_t idesc = make_idesc_16(kGM, BN, 0, 0, p.ab_f16);
       for (int k = 0; k < kb; ++k) {
         const int st = k % kGStages;
         mbar_wait(full + st, (k / kGStages) & 1);
@@ -232,10 +233,15 @@ static int encode_2d(CUtensorMap* map, const void* base, uint64_t inner, uint64_
 
 int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
                 const rmem_gemm_segment* segs, int n_seg, cudaStream_t stream) {
+  return gemm_ex_launch(a, lda, w, ldw, bias, M, N, K, segs, n_seg, 0, stream);
+}
+
+int gemm_ex_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
+                   const rmem_gemm_segment* segs, int n_seg, int ab_f16, cudaStream_t stream) {
   if (M < 1 || N < 1 || K < 1 || (lda % 8) || (ldw % 8) || n_seg < 1 || n_seg > RMEM_GEMM_MAX_SEGMENTS)
     return set_error(RMEM_ERR_ARG, "gemm: bad shape / leading dimension / segment count");
   GemmParams p;
-  p.M = M; p.N = N; p.K = K; p.bias = bias; p.n_seg = n_seg;
+  p.M = M; p.N = N; p.K = K; p.bias = bias; p.n_seg = n_seg; p.ab_f16 = ab_f16 ? 1 : 0;
   for (int s = 0; s < n_seg; ++s) {
     p.seg[s] = segs[s];
     if (segs[s].col_begin % 32 || segs[s].col_end <= segs[s].col_begin || segs[s].col_end > N ||
@@ -253,18 +259,15 @@ int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bia
   if (int e = encode_2d(&tm_a, a, K, M, static_cast<uint64_t>(lda) * 2, kGM)) return e;
   if (int e = encode_2d(&tm_w, w, K, N, static_cast<uint64_t>(ldw) * 2, bn)) return e;
   const bool deep = narrow && K >= 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         GemmCfg<128, 3>::kSmem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               GemmCfg<64, 3>::kSmem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_bf16_tn_kernel<64, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               GemmCfg<64, 6>::kSmem);
-    if (e != cudaSuccess) return set_cuda_error(e, "gemm: cudaFuncSetAttribute");
-    attr_set = true;
+  static SmemOptIn optin_128_3, optin_64_3, optin_64_6;
+  {
+    int r = deep ? ensure_dynamic_smem(reinterpret_cast<const void*>(gemm_bf16_tn_kernel<64, 6>), &optin_64_6,
+                                       GemmCfg<64, 6>::kSmem, "gemm: cudaFuncSetAttribute")
+          : narrow ? ensure_dynamic_smem(reinterpret_cast<const void*>(gemm_bf16_tn_kernel<64, 3>), &optin_64_3,
+                                         GemmCfg<64, 3>::kSmem, "gemm: cudaFuncSetAttribute")
+                   : ensure_dynamic_smem(reinterpret_cast<const void*>(gemm_bf16_tn_kernel<128, 3>), &optin_128_3,
+                                         GemmCfg<128, 3>::kSmem, "gemm: cudaFuncSetAttribute");
+    if (r) return r;
   }
   dim3 grid((N + bn - 1) / bn, m_tiles);
   if (deep)

@@ -196,12 +196,10 @@ int local_scores_launch(const void* q, const void* k, const float* rel, int ld_r
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (local K) failed");
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(local_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSSmem);
-    if (e != cudaSuccess) return set_cuda_error(e, "local_scores: cudaFuncSetAttribute");
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_scores_kernel), &optin, kSSmem,
+                                  "local_scores: cudaFuncSetAttribute"))
+    return r;
   dim3 grid((w + kSTileW - 1) / kSTileW, (h + kSTileH - 1) / kSTileH);
   local_scores_kernel<<<grid, 256, kSSmem, stream>>>(tm_k, static_cast<const __nv_bfloat16*>(q), rel, ld_rel,
                                                      probs, static_cast<__nv_bfloat16*>(banded), h, w);
@@ -366,12 +364,10 @@ int local_aggregate_launch(const void* banded, const void* v, const void* gate, 
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (banded P) failed");
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(local_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kASmem);
-    if (e != cudaSuccess) return set_cuda_error(e, "local_aggregate: cudaFuncSetAttribute");
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_aggregate_kernel), &optin, kASmem,
+                                  "local_aggregate: cudaFuncSetAttribute"))
+    return r;
   AggParams p;
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out); p.h = h; p.w = w;

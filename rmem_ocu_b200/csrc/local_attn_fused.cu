@@ -376,12 +376,10 @@ int local_attn_fused_launch(const void* q, const void* k, const void* v, const f
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (local V) failed");
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(local_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-    if (e != cudaSuccess) return set_cuda_error(e, "local_attn: cudaFuncSetAttribute");
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_attn_kernel), &optin, kSmem,
+                                  "local_attn: cudaFuncSetAttribute"))
+    return r;
   Params p;
   p.rel = rel; p.ld_rel = ld_rel;
   p.gate = static_cast<const __nv_bfloat16*>(gate);

@@ -491,13 +491,10 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (partial O) failed");
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(lt_attn_partial_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
-    if (e != cudaSuccess) return set_cuda_error(e, "lt_attn: cudaFuncSetAttribute");
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(lt_attn_partial_kernel), &optin, kSmemTotal,
+                                  "lt_attn: cudaFuncSetAttribute"))
+    return r;
   LtParams p;
   p.L = L;
   p.n_chunks = T * chunks_per_frame;

@@ -423,13 +423,10 @@ int mha_partial_launch(const void* q, int ldq, const void* k, int ldk, int64_t k
     const uint32_t box[4] = {64, kBlockN, 1, 1};
     if (int e = mha_encode(&tm_v, v, 4, dims, strides, box)) return e;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mha_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemTotal);
-    if (e != cudaSuccess) return set_cuda_error(e, "mha: cudaFuncSetAttribute");
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(mha_partial_kernel), &optin, kSmemTotal,
+                                  "mha: cudaFuncSetAttribute"))
+    return r;
   Params p;
   p.L = L;
   p.n_chunks = T * chunks_per_frame;

@@ -3,6 +3,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include "../../include/rmem_b200.h"
 
 namespace rmem {
@@ -18,6 +19,15 @@ typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint3
                                       CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 TensorMapEncodeFn get_tensor_map_encoder();
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to a (kernel, device) pair: one record per kernel holds the
+// size already granted on every device, so engines on several GPUs of one process (and several host threads)
+// all get the opt-in.  Zero-initialised static storage is the valid start state.
+constexpr int kMaxDevices = 64;
+struct SmemOptIn {
+  std::atomic<int> granted[kMaxDevices];
+};
+int ensure_dynamic_smem(const void* kernel, SmemOptIn* rec, int bytes, const char* what);
+
 // ---- launchers (one per kernel family); all asynchronous on `stream`
 int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
                            const int32_t* order_dev, int T, int L, int n_slots,
@@ -27,6 +37,13 @@ int lt_attn_combine_launch(const float* part_o, const float* part_m, const float
                            const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
                            int chunks_per_frame, const void* gate, void* out, float* attn_mass,
                            cudaStream_t stream);
+
+int64_t lt_attn_sk_workspace_bytes(int L, int T, int n_clusters);
+int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vbank, const int32_t* order_dev, int T,
+                              int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host, int record,
+                              int n_clusters, void* workspace, int64_t workspace_bytes, cudaStream_t stream);
+int lt_attn_sk_combine_launch(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+                              const void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 
 int mha_partial_launch(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride, const void* v,
                        int ldv, int64_t v_slot_stride, const int32_t* order_dev, int T, int L, int n_slots,
@@ -46,6 +63,8 @@ int groupnorm_gelu_tokens_launch(const float* x, const float* gamma, const float
 
 int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
                 const rmem_gemm_segment* segs, int n_seg, cudaStream_t stream);
+int gemm_ex_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
+                   const rmem_gemm_segment* segs, int n_seg, int ab_f16, cudaStream_t stream);
 int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
                      const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
                      int L, int C, int in_bf16, cudaStream_t stream);
@@ -75,6 +94,10 @@ int finish_logits_launch(const float* conv, long long sc, long long sy, long lon
                          int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream);
 int pack_image_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
 int pack_image_s2d_launch(const float* img, int H, int W, void* out, cudaStream_t stream);
+int pack_image_s2d_ex_launch(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                             int H, int W, void* out, int out_f16, cudaStream_t stream);
+int maxpool3s2_nhwc_ex_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                              cudaStream_t stream);
 int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y,
                            cudaStream_t stream);
 int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream);

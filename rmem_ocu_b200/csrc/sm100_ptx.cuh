@@ -313,6 +313,13 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t M, uint32_t N, u
          ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// Same descriptor with IEEE fp16 A/B (format code 0) when ab_f16 != 0.
+__host__ __device__ constexpr uint32_t make_idesc_16(uint32_t M, uint32_t N, uint32_t a_mn_major,
+                                                     uint32_t b_mn_major, uint32_t ab_f16) {
+  return (1u << 4) | ((ab_f16 ? 0u : 1u) << 7) | ((ab_f16 ? 0u : 1u) << 10) | (a_mn_major << 15) |
+         (b_mn_major << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
 // Byte offset of element (row, 16-byte chunk) inside a tile stored as rows of 128 bytes with the
 // 128B swizzle TMA / UMMA use (chunk index XOR row%8). Tile base must be 1024-byte aligned.
 __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t chunk16) {

@@ -11,7 +11,8 @@ State layout (per engine = per video sequence, one object group of <= 10 objects
 The frame path issues no host synchronisation; ``long_memories_indexes`` is mirrored lazily.
 There is no CPU / PyTorch fallback: without CUDA or the shared library the engines raise.
 """
-import copy
+
+import functools
 
 import torch
 import torch.nn.functional as F
@@ -28,6 +29,17 @@ def _bf(t, dev):
 
 def _f32(t, dev):
     return t.detach().to(device=dev, dtype=torch.float32).contiguous()
+
+
+def _on_device(fn):
+    """Run a public engine method with the engine's GPU current: the kernels launch on
+    ``torch.cuda.current_stream()`` and set per-device kernel attributes, so an engine built for ``gpu_id`` must
+    not depend on which device the calling thread happens to have selected."""
+    @functools.wraps(fn)
+    def wrapped(self, *args, **kwargs):
+        with torch.cuda.device(self.device):
+            return fn(self, *args, **kwargs)
+    return wrapped
 
 
 class PreparedDeAOT:
@@ -98,9 +110,8 @@ class PreparedDeAOT:
         import os
         # RMEM_ENCODER_DTYPE=fp32 runs the cuDNN trunk in fp32 (TF32 off): used by the parity tests so mask
         # agreement measures the hot-path kernels, not the black-box backbone's bf16 rounding
-        enc_dtype = torch.float32 if os.environ.get("RMEM_ENCODER_DTYPE", "bf16") == "fp32" else BF16
-        self.encoder = InferenceResNet(model.encoder, model.encoder_projector, device, enc_dtype)
-        self.decoder = InferenceFPN(sd, device, intermediate=False)
+        self.encoder = InferenceResNet(model.encoder, model.encoder_projector, device, encoder_dtype())
+        self.decoder = InferenceFPN(sd, device, intermediate=False, shortcut_dtype=self.encoder.dtype)
 
 
 class InferenceFPN:
@@ -108,8 +119,9 @@ class InferenceFPN:
     the argmax mask): the convolutions are cuDNN calls (a black box of this tier, TF32 as PyTorch's default),
     GroupNorm(8)+ReLU and the bilinear upsample + shortcut add run in csrc/decoder.cu."""
 
-    def __init__(self, sd, device, intermediate, prefix="decoder."):
+    def __init__(self, sd, device, intermediate, prefix="decoder.", shortcut_dtype=BF16):
         self.intermediate = intermediate
+        self.shortcut_dtype = shortcut_dtype if shortcut_dtype in (BF16, torch.float16) else BF16
         cl = lambda w: w.detach().to(device=device, dtype=torch.float32).contiguous(memory_format=torch.channels_last)
         f = lambda t: _f32(t, device)
         self.w = {}
@@ -120,7 +132,9 @@ class InferenceFPN:
             self.w[name] = (cl(sd[prefix + name + ".weight"]), f(sd[prefix + name + ".bias"]))
         # the 1x1 adapters read the encoder's bf16 feature maps: as [Cout, Cin] bf16 matrices they run on the
         # tcgen05 GEMM straight off those maps (no f32 copies of the shortcuts, no f32 convolution)
-        self.wb = {name: _bf(sd[prefix + name + ".weight"].reshape(sd[prefix + name + ".weight"].shape[0], -1), device)
+        # (in the backbone's 16-bit type: fp16 by default)
+        self.wb = {name: sd[prefix + name + ".weight"].detach().reshape(sd[prefix + name + ".weight"].shape[0], -1)
+                   .to(device=device, dtype=self.shortcut_dtype).contiguous()
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
         self.gn_ws = torch.zeros(17, device=device, dtype=torch.float64)    # 2 x 8 group sums + arrival counter
         self._ws = self.gn_ws       # the workspace of the call in flight (engines pass their own: they may run
@@ -154,7 +168,7 @@ class InferenceFPN:
     def adapters(self, shortcuts):
         """The three adapter outputs, which depend on the encoder alone: the engine computes them at the end of
         the encoder pass (off the LSTT -> decoder chain when the encoder runs ahead) and hands them to __call__."""
-        if any(shortcuts[i].dtype != BF16 for _, i in self.ADAPTERS):
+        if any(shortcuts[i].dtype != self.shortcut_dtype for _, i in self.ADAPTERS):
             return None
         return [self._adapter(shortcuts[i], name) for name, i in self.ADAPTERS]
 
@@ -163,7 +177,7 @@ class InferenceFPN:
         w, b = self.w[name]
         if pre is not None:
             a, ta, b = pre, self._tok(pre), None
-        elif shortcut.dtype == BF16:
+        elif shortcut.dtype == self.shortcut_dtype:
             a = self._adapter(shortcut, name)
             ta = self._tok(a)
             b = None                                                                # added by the GEMM epilogue
@@ -195,17 +209,36 @@ class InferenceResNet:
     fused cuDNN calls where the installed PyTorch exposes them.  A black box of this tier (cuDNN)."""
 
     def __init__(self, enc, projector, device, dtype=BF16):
-        enc = copy.deepcopy(enc).float()
-        enc.fold_bn_()
+        # `enc` may be the repo's ResNet50S16 or the reference's own ResNet (networks/encoders/resnet.py:71-194,
+        # BatchNorm = FrozenBatchNorm2d, networks/layers/normalization.py:6-45, or nn.BatchNorm2d in eval mode): the
+        # frozen BN affine is folded into this object's own copies of the conv weights -- the caller's module is
+        # neither mutated nor deep-copied
         self.dtype = dtype
-        cv = lambda c: (c.weight.detach().to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
-                        c.bias.detach().to(device=device, dtype=dtype), c.stride, c.padding)
-        w1 = enc.conv1.weight.detach()
+
+        def folded(conv, bn):
+            """(w * s, shift + b * s) in f32 for conv -> bn with frozen statistics (exact algebra)."""
+            w = conv.weight.detach().float()
+            if bn is None:
+                b = conv.bias.detach().float() if conv.bias is not None else torch.zeros(w.shape[0])
+                return w, b
+            eps = float(getattr(bn, "epsilon", getattr(bn, "eps", 1e-5)))
+            s = bn.weight.detach().float() * (bn.running_var.detach().float() + eps).rsqrt()
+            b = bn.bias.detach().float() - bn.running_mean.detach().float() * s
+            if conv.bias is not None:
+                b = b + conv.bias.detach().float() * s
+            return w * s.view(-1, 1, 1, 1), b
+
+        def cv(conv, bn=None):
+            w, b = folded(conv, bn)
+            return (w.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
+                    b.to(device=device, dtype=dtype), tuple(conv.stride), tuple(conv.padding))
+
+        w1, b1 = folded(enc.conv1, enc.bn1)
         # 3 input channels starve the tensor-core conv kernels: pad to 8 (zeros) -> same result
         w1p = torch.zeros(w1.shape[0], 8, *w1.shape[2:])
         w1p[:, :3] = w1
         self.conv1 = (w1p.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
-                      enc.conv1.bias.detach().to(device=device, dtype=dtype), enc.conv1.stride, enc.conv1.padding)
+                      b1.to(device=device, dtype=dtype), tuple(enc.conv1.stride), tuple(enc.conv1.padding))
         # space-to-depth form of the stem (exact algebra): out[y,x] = sum_{a,b in -2..1} sum_{dy,dx,c}
         # W[c][2a+dy+3][2b+dx+3] X[c][2(y+a)+dy][2(x+b)+dx] -- a 4x4 stride-1 conv over 12 (padded to 16) channels
         # of the 2x2 space-to-depth image that ops.pack_image_s2d writes (with the zero border built in)
@@ -222,22 +255,27 @@ class InferenceResNet:
                                 ws[:, ch:ch + 3, a + 2, b + 2] = w1[:, :, i, j]
             self.conv1_s2d = (ws.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last),
                               self.conv1[1], (1, 1), (0, 0))
-            self.conv1_bias_f32 = enc.conv1.bias.detach().to(device=device, dtype=torch.float32)
+            self.conv1_bias_f32 = b1.to(device=device, dtype=torch.float32)
         self.blocks = []
         for li in (1, 2, 3):
             stage = []
             for blk in getattr(enc, "layer%d" % li):
-                down = cv(blk.downsample[0]) if blk.downsample is not None else None
-                c3 = cv(blk.conv3)
-                if down is not None:
+                if tuple(getattr(blk.conv2, "dilation", (1, 1))) != (1, 1):
+                    raise _lib.RmemError("InferenceResNet: dilated bottlenecks (output stride 8) are not on the path")
+                down = None
+                c3 = cv(blk.conv3, blk.bn3)
+                if blk.downsample is not None:
                     # relu(conv3(y) + b3 + down(x) + bd): both biases ride on conv3's fused epilogue
-                    b3 = (blk.conv3.bias.detach().float() + blk.downsample[0].bias.detach().float())
-                    c3 = (c3[0], b3.to(device=device, dtype=dtype), c3[2], c3[3])
-                    down = (down[0], None, down[2], down[3])
-                stage.append((cv(blk.conv1), cv(blk.conv2), c3, down))
+                    wd, bd = folded(blk.downsample[0], blk.downsample[1])
+                    _, b3 = folded(blk.conv3, blk.bn3)
+                    c3 = (c3[0], (b3 + bd).to(device=device, dtype=dtype), c3[2], c3[3])
+                    down = (wd.to(device=device, dtype=dtype).contiguous(memory_format=torch.channels_last), None,
+                            tuple(blk.downsample[0].stride), tuple(blk.downsample[0].padding))
+                stage.append((cv(blk.conv1, blk.bn1), cv(blk.conv2, blk.bn2), c3, down))
             self.blocks.append(stage)
         self.proj = cv(projector)
-        self.fused = hasattr(torch, "cudnn_convolution_relu") and os_env_flag("RMEM_FUSED_CONV", True)
+        self.fused = (hasattr(torch, "cudnn_convolution_relu") and os_env_flag("RMEM_FUSED_CONV", True)
+                      and torch.device(device).type == "cuda")
         # measured: forking the three projection shortcuts costs ~2 % (980 vs 1000 frames/s) -- the convolutions
         # already fill the GPU and the extra graph edges add latency -- so it stays off
         self.fork = self.fused and os_env_flag("RMEM_FORK_ENCODER", False)
@@ -256,13 +294,26 @@ class InferenceResNet:
                 return self._forward(img)
         return self._forward(img)
 
+    # normalisation of the reference's dataloader (dataloaders/video_transforms.py:537-539, 676-678), applied on
+    # the device when a caller hands the engine a decoded u8 frame [1, H, W, 3] instead of normalised f32 planes
+    U8_MEAN, U8_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+
     def _forward(self, img):
-        n, c, h, w = img.shape
-        s2d = (self.dtype == BF16 and n == 1 and img.dtype == torch.float32 and self.fused
+        half = self.dtype in (BF16, torch.float16)
+        if img.dtype == torch.uint8:
+            n, h, w = (1,) + tuple(img.shape[-3:-1])
+        else:
+            n, c, h, w = img.shape
+        s2d = (half and n == 1 and img.dtype in (torch.float32, torch.uint8) and self.fused
                and self.conv1_s2d is not None)
+        if img.dtype == torch.uint8 and not s2d:
+            img = img.reshape(1, h, w, 3).permute(0, 3, 1, 2).float().div(255.0)
+            img = (img - img.new_tensor(self.U8_MEAN).view(1, 3, 1, 1)) / img.new_tensor(self.U8_STD).view(1, 3, 1, 1)
         if s2d:
-            x = torch.empty(1, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device, dtype=BF16).permute(0, 3, 1, 2)
-            ops.pack_image_s2d(img, x)              # f32 planes -> bf16 space-to-depth image, conv padding built in
+            x = torch.empty(1, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device,
+                            dtype=self.dtype).permute(0, 3, 1, 2)
+            # f32 planes / u8 pixels -> 16-bit space-to-depth image, conv padding built in
+            ops.pack_image_s2d(img, x, self.U8_MEAN, self.U8_STD)
         elif self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
             x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16, memory_format=torch.channels_last)
             ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
@@ -278,9 +329,9 @@ class InferenceResNet:
             x = self._conv(x, self.conv1, True)
         else:
             x = F.relu(F.conv2d(x, self.conv1[0], self.conv1[1], self.conv1[2], self.conv1[3]))
-        if self.dtype == BF16 and n == 1:
+        if half and n == 1:
             pooled = torch.empty(1, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
-                                 device=x.device, dtype=BF16, memory_format=torch.channels_last)
+                                 device=x.device, dtype=self.dtype, memory_format=torch.channels_last)
             c_, h_, w_ = x.shape[1:]
             if x.stride()[1:] != (1, w_ * c_, c_):                   # cuDNN returns NHWC strides; never copy then
                 x = x.contiguous(memory_format=torch.channels_last)
@@ -325,6 +376,22 @@ class InferenceResNet:
         return xs
 
 
+# fp16, not bf16: same storage and tensor-core rate, 3 more mantissa bits -- measured on the reference fixtures,
+# masks agree >= 99.92 % with the fp32 reference on every frame with an fp16 backbone and only 99.78-99.85 % with a
+# bf16 one (profiles/r02_exp_encoder_dtype.log); the reference's own --amp path is fp16 autocast as well
+ENCODER_DTYPE_DEFAULT = "fp16"
+
+
+def encoder_dtype():
+    """Arithmetic type of the cuDNN backbone (a black box of this tier): RMEM_ENCODER_DTYPE = bf16 | fp16 | fp32."""
+    import os
+    name = os.environ.get("RMEM_ENCODER_DTYPE", ENCODER_DTYPE_DEFAULT)
+    try:
+        return {"bf16": BF16, "fp16": torch.float16, "fp32": torch.float32}[name]
+    except KeyError:
+        raise _lib.RmemError("RMEM_ENCODER_DTYPE must be bf16, fp16 or fp32, not %r" % name)
+
+
 def os_env_flag(name, default):
     import os
     v = os.environ.get(name)
@@ -334,14 +401,14 @@ def os_env_flag(name, default):
 def prepare(model, device):
     cache = model.__dict__.setdefault("_rmem_prepared", {})
     import os
-    key = (str(device), os.environ.get("RMEM_ENCODER_DTYPE", "bf16"), os.environ.get("RMEM_DECODER_DTYPE", "fp32"))
+    key = (str(device), os.environ.get("RMEM_ENCODER_DTYPE", ENCODER_DTYPE_DEFAULT),
+           os.environ.get("RMEM_DECODER_DTYPE", "fp32"))
     if key not in cache:
         if is_deaot_model(model):
             cache[key] = PreparedDeAOT(model, device)
         else:
             from .engine_aot import PreparedAOT
-            enc_dtype = torch.float32 if key[1] == "fp32" else BF16
-            cache[key] = PreparedAOT(model, device, InferenceResNet, InferenceFPN, enc_dtype)
+            cache[key] = PreparedAOT(model, device, InferenceResNet, InferenceFPN, encoder_dtype())
     return cache[key]
 
 
@@ -389,6 +456,7 @@ class _Workspace:
         self.id_emb = z(L, 256)
         self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
         self.zero_order = z(1, dt=torch.int32)
+        self.sk_ws = None                                     # stream-K attention workspace, allocated on first use
         self.pred_logits = None                               # [1, 11, H/4, W/4] f32, allocated on first decode
 
 
@@ -450,6 +518,11 @@ class DeAOTEngine:
         # single-kernel local attention (csrc/local_attn_fused.cu): parity-green but 17.5 us against 16.5 us for
         # the scores + aggregation pair at 480p, so it is opt-in until it wins
         self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False)
+        import os
+        self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
+        # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
+        # long-term attention finds free SMs
+        self.lt_sk_clusters = int(os.environ.get("RMEM_LT_SK_CLUSTERS", "0"))
         self._side = None
         # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
         # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
@@ -509,6 +582,7 @@ class DeAOTEngine:
         self._prefetching = False  # the last propagated frame started the next frame's encoder
         self.n_long_updates = 0
 
+    @_on_device
     def update_size(self, input_size, enc_size):
         self.input_size_2d = tuple(input_size)
         self.enc_size_2d = tuple(enc_size)
@@ -517,6 +591,8 @@ class DeAOTEngine:
         n_slots = self.capacity + 1
         if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
             self.ws = self._new_workspace(h, w, n_slots)
+            if self.lt_streamk:          # allocated here, never inside a graph capture
+                self.ws.sk_ws = ops.lt_attn_sk_workspace(self.ws.L, n_slots, self.device, self.lt_sk_clusters)
             self._wait_write()
             self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
             self._prefetched, self._enc_set = None, 0
@@ -526,10 +602,12 @@ class DeAOTEngine:
         """Frame ids in the bank, oldest first (host mirror; reading it synchronises)."""
         if self.ws is None or self.T == 0:
             return []
-        self._wait_write()
-        st = self.ws.bank_state.cpu()
+        with torch.cuda.device(self.device):
+            self._wait_write()
+            st = self.ws.bank_state.cpu()
         return [int(st[_lib.MAX_BANK + int(st[t])]) for t in range(self.T)]
 
+    @_on_device
     def eviction_debug(self):
         self._wait_write()
         st = self.ws.bank_state.cpu()
@@ -539,6 +617,7 @@ class DeAOTEngine:
                     last_choice=int(st[base + 4]))
 
     # ------------------------------------------------------------------ black boxes
+    @_on_device
     def encode_image(self, img):
         """ResNet-50 trunk + encoder_projector (cuDNN, bf16 channels-last) -> [x4, x8, x16, emb16]."""
         return self.prep.encoder(img.to(device=self.device, non_blocking=True))
@@ -581,6 +660,16 @@ class DeAOTEngine:
 
     def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass, gate_ready=None):
         ws = self.ws
+        if self.lt_streamk and T >= 2:
+            # second-generation kernel (csrc/lt_attn_sk.cu): persistent stream-K on 2-CTA clusters; wins from two
+            # frames in the bank on (T = 1, i.e. the self-attention and a fresh bank, stays on the first generation)
+            ops.lt_attn_sk_partial(q, kbank, vbank, order, T, ws.tpe_bias if tpe else None,
+                                   tpe_row_indices(T) if tpe else None, mass is not None, ws.sk_ws,
+                                   self.lt_sk_clusters)
+            if gate_ready is not None:
+                torch.cuda.current_stream().wait_event(gate_ready)
+            ops.lt_attn_sk_combine(T, ws.L, gate, out, mass, ws.sk_ws, self.lt_sk_clusters)
+            return
         cpf = _chunks_per_frame(T, ws.L)
         ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
         if gate_ready is not None:
@@ -606,102 +695,110 @@ class DeAOTEngine:
         torch.cuda.current_stream().wait_event(ev)
 
     def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):
-        """DualBranchGPM.forward + GatedPropagationModule.forward (transformer.py:765-824, 1091-1236)."""
+        """DualBranchGPM.forward (transformer.py:765-824): three GatedPropagationModule blocks + output norm."""
         ws, prep = self.ws, self.prep
-        h, w, L = ws.h, ws.w, ws.L
         ws.tgt.copy_(self._tokens(curr_emb16))
-        tr = self.trace
         we = self._w_events
         if we is not None and prep.num_layers == 1:
             we["l0"] = we["all"]
-        for i, Lw in enumerate(prep.layers):
-            if we is not None and i == 1 and not we["waited"]:
-                # a deferred write path is running beside layer 0: its ID_V GEMMs read curr_ID_V of the previous
-                # frame, which the next LayerNorm overwrites, and write the short-term values layers 1.. read
-                torch.cuda.current_stream().wait_event(we["all"])
-                we["waited"] = True
-            # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
-            if i == 0:
-                ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0)
-            else:
-                ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0, ws.tgt_id, *Lw["id_norm1"], ws.idcat[i], 0)
-            # K (= Q) | silu(V) | silu(U) in one GEMM
-            ops.linear(ws.xn[:, :256], Lw["w_qvu"], Lw["b_qvu"],
-                       [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.kcur[i], 0),
-                        (128, 640, ops.ACT_SILU, ops.OUT_BF16, ws.vcur[i], 0),
-                        (640, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 0)])
-            idu = (lambda: ops.linear(ws.idcat[i][:, :256], Lw["w_idu"], Lw["b_idu"],
-                                      [(0, 512, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 512)])) if i > 0 else None
-            if idu is not None and not self.fork_branches:
-                idu()
-            if is_reference:
-                # the reference frame is its own long- and short-term memory (transformer.py:1125-1135)
-                self._id_value(i, ws.vcur[i])
-                ws.kprev[i].copy_(ws.kcur[i]); ws.vprev[i].copy_(ws.vcur[i])
-                ws.kbank[i][0].copy_(ws.kcur[i]); ws.vbank[i][0].copy_(ws.vcur[i])
-            # The long-term and the short-term branch only share their inputs (K = Q, U) and meet again in the
-            # projection GEMM: the short-term branch is forked onto a side stream (a parallel branch of the
-            # captured graph), so its sub-wave kernels fill the SMs the long-term attention's ragged second wave
-            # leaves idle.
-            forked = self._fork()
-            idu_done = None
-            with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
-                if idu is not None and forked:
-                    # the ID half of the gate U is first read by the attention epilogues (combine / aggregate):
-                    # its GEMM leaves the long-term chain for the short-term branch, which has slack
-                    idu()
-                    idu_done = torch.cuda.Event()
-                    idu_done.record()
-                # short-term 15x15 local attention over the previous frame, gate, dw5x5
-                ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
-                if we is not None and i == 0 and not we["waited"]:
-                    torch.cuda.current_stream().wait_event(we["l0"])     # ID_V of layer 0 (deferred write path)
-                if self.local_fused:
-                    ops.local_attn(ws.kcur[i], ws.kprev[i], ws.vprev[i], ws.rel, ws.u[i], ws.gated_b, h, w)
-                else:
-                    ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
-                    ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
-                ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
-            # long-term attention over the bank (TPE folded into a per-frame score bias), gate, dw5x5
-            ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
-            mass = None
-            if save_atten_weights and i == 0:
-                mass = ws.mass
-            self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
-                                         ws.gated_a, mass, gate_ready=idu_done)
-            ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
-            if forked:
-                self._join()
-            # (projection_lt + projection_st) -> residual adds, one GEMM
-            if tr is not None:
-                tr.setdefault("layers", []).append(dict(
-                    curr_Q=ws.kcur[i].float().cpu(), curr_V=ws.vcur[i][:, :512].float().cpu(),
-                    cat_curr_U=ws.u[i].float().cpu(), lt_gated=ws.gated_a.float().cpu(),
-                    st_gated=ws.gated_b.float().cpu()))
-            id_mode = ops.OUT_F32 if i == 0 else ops.OUT_F32_ACCUM
-            ops.linear(ws.dw, Lw["w_proj_ls"], Lw["b_proj_ls"],
-                       [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
-                        (256, 512, ops.ACT_NONE, id_mode, ws.tgt_id, 0)])
-            # self-attention (gated, d_att 128, value width 1024)
-            ops.layernorm(ws.tgt, *Lw["norm2"], ws.xn, 0, ws.tgt_id, *Lw["id_norm2"], ws.xn, 256)
-            ops.linear(ws.xn, Lw["w_sa"], Lw["b_sa"],
-                       [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.sa_qk, 0),
-                        (128, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.sa_v, 0),
-                        (1152, 2176, ops.ACT_SILU, ops.OUT_BF16, ws.sa_u, 0)])
-            self._gated_global_attention(ws.sa_qk, ws.sa_qk.view(1, L, 128), ws.sa_v.view(1, L, 1024),
-                                         ws.zero_order, 1, False, ws.sa_u, ws.gated_a, None)
-            ops.dwconv5(ws.gated_a, 0, Lw["dw_sa"], ws.dw, 0, h, w, 1024)
-            ops.linear(ws.dw[:, :1024], Lw["w_proj_sa"], Lw["b_proj_sa"],
-                       [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
-                        (256, 512, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt_id, 0)])
-            if tr is not None:
-                tr["layers"][-1].update(tgt=ws.tgt.cpu().clone(), tgt_id=ws.tgt_id.cpu().clone())
+        for i in range(prep.num_layers):
+            self._block_forward(i, is_reference, save_atten_weights and i == 0, T)
         if we is not None and not we["waited"]:
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
         # the single output GroupNorm1D(512, 2) (transformer.py:806-808)
         ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws)
         return ws.gn_out
+
+    def _block_forward(self, i, is_reference, record, T):
+        """GatedPropagationModule.forward (transformer.py:1091-1236) of layer ``i`` on the workspace's residual
+        streams; ``record``: write this layer's record_attn_weight into ws.mass (the engines record layer 0)."""
+        ws, prep = self.ws, self.prep
+        h, w, L = ws.h, ws.w, ws.L
+        Lw = prep.layers[i]
+        tr = self.trace
+        we = self._w_events
+        if we is not None and i == 1 and not we["waited"]:
+            # a deferred write path is running beside layer 0: its ID_V GEMMs read curr_ID_V of the previous
+            # frame, which the next LayerNorm overwrites, and write the short-term values layers 1.. read
+            torch.cuda.current_stream().wait_event(we["all"])
+            we["waited"] = True
+        # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
+        if i == 0:
+            ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0)
+        else:
+            ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0, ws.tgt_id, *Lw["id_norm1"], ws.idcat[i], 0)
+        # K (= Q) | silu(V) | silu(U) in one GEMM
+        ops.linear(ws.xn[:, :256], Lw["w_qvu"], Lw["b_qvu"],
+                   [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.kcur[i], 0),
+                    (128, 640, ops.ACT_SILU, ops.OUT_BF16, ws.vcur[i], 0),
+                    (640, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 0)])
+        idu = (lambda: ops.linear(ws.idcat[i][:, :256], Lw["w_idu"], Lw["b_idu"],
+                                  [(0, 512, ops.ACT_SILU, ops.OUT_BF16, ws.u[i], 512)])) if i > 0 else None
+        if idu is not None and not self.fork_branches:
+            idu()
+        if is_reference:
+            # the reference frame is its own long- and short-term memory (transformer.py:1125-1135)
+            self._id_value(i, ws.vcur[i])
+            ws.kprev[i].copy_(ws.kcur[i]); ws.vprev[i].copy_(ws.vcur[i])
+            ws.kbank[i][0].copy_(ws.kcur[i]); ws.vbank[i][0].copy_(ws.vcur[i])
+        # The long-term and the short-term branch only share their inputs (K = Q, U) and meet again in the
+        # projection GEMM: the short-term branch is forked onto a side stream (a parallel branch of the
+        # captured graph), so its sub-wave kernels fill the SMs the long-term attention's ragged second wave
+        # leaves idle.
+        forked = self._fork()
+        idu_done = None
+        with torch.cuda.stream(self._side if forked else torch.cuda.current_stream()):
+            if idu is not None and forked:
+                # the ID half of the gate U is first read by the attention epilogues (combine / aggregate):
+                # its GEMM leaves the long-term chain for the short-term branch, which has slack
+                idu()
+                idu_done = torch.cuda.Event()
+                idu_done.record()
+            # short-term 15x15 local attention over the previous frame, gate, dw5x5
+            ops.linear(ws.kcur[i], Lw["w_rel"], Lw["b_rel"], [(0, 225, ops.ACT_NONE, ops.OUT_F32, ws.rel, 0)])
+            if we is not None and i == 0 and not we["waited"]:
+                torch.cuda.current_stream().wait_event(we["l0"])     # ID_V of layer 0 (deferred write path)
+            if self.local_fused:
+                ops.local_attn(ws.kcur[i], ws.kprev[i], ws.vprev[i], ws.rel, ws.u[i], ws.gated_b, h, w)
+            else:
+                ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
+                ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
+            ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
+        # long-term attention over the bank (TPE folded into a per-frame score bias), gate, dw5x5
+        ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
+        mass = None
+        if record:
+            mass = ws.mass
+        self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
+                                     ws.gated_a, mass, gate_ready=idu_done)
+        ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
+        if forked:
+            self._join()
+        # (projection_lt + projection_st) -> residual adds, one GEMM
+        if tr is not None:
+            tr.setdefault("layers", []).append(dict(
+                curr_Q=ws.kcur[i].float().cpu(), curr_V=ws.vcur[i][:, :512].float().cpu(),
+                cat_curr_U=ws.u[i].float().cpu(), lt_gated=ws.gated_a.float().cpu(),
+                st_gated=ws.gated_b.float().cpu()))
+        id_mode = ops.OUT_F32 if i == 0 else ops.OUT_F32_ACCUM
+        ops.linear(ws.dw, Lw["w_proj_ls"], Lw["b_proj_ls"],
+                   [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
+                    (256, 512, ops.ACT_NONE, id_mode, ws.tgt_id, 0)])
+        # self-attention (gated, d_att 128, value width 1024)
+        ops.layernorm(ws.tgt, *Lw["norm2"], ws.xn, 0, ws.tgt_id, *Lw["id_norm2"], ws.xn, 256)
+        ops.linear(ws.xn, Lw["w_sa"], Lw["b_sa"],
+                   [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.sa_qk, 0),
+                    (128, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.sa_v, 0),
+                    (1152, 2176, ops.ACT_SILU, ops.OUT_BF16, ws.sa_u, 0)])
+        self._gated_global_attention(ws.sa_qk, ws.sa_qk.view(1, L, 128), ws.sa_v.view(1, L, 1024),
+                                     ws.zero_order, 1, False, ws.sa_u, ws.gated_a, None)
+        ops.dwconv5(ws.gated_a, 0, Lw["dw_sa"], ws.dw, 0, h, w, 1024)
+        ops.linear(ws.dw[:, :1024], Lw["w_proj_sa"], Lw["b_proj_sa"],
+                   [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
+                    (256, 512, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt_id, 0)])
+        if tr is not None:
+            tr["layers"][-1].update(tgt=ws.tgt.cpu().clone(), tgt_id=ws.tgt_id.cpu().clone())
 
     # ------------------------------------------------------------------ device work (graph-capturable)
     def _read_body(self, img, img_embs, T, output_size, st):
@@ -885,6 +982,7 @@ class DeAOTEngine:
             e.record_stream(cur)
         return embs, p
 
+    @_on_device
     def precapture(self, output_size=None, prefetch=False):
         """Capture the read / write graphs of every bank length now (capturing records, it does not
         execute, so the sequence state is untouched). Call after the first propagated frame.  ``prefetch``: record
@@ -936,6 +1034,7 @@ class DeAOTEngine:
                    [label], False)
 
     # ------------------------------------------------------------------ public frame API
+    @_on_device
     def add_reference_frame(self, img=None, mask=None, frame_step=-1, obj_nums=None, img_embs=None):
         """aot_engine.py:241-325 (always eager: once per sequence)."""
         if self.obj_nums is None and obj_nums is None:
@@ -955,7 +1054,9 @@ class DeAOTEngine:
         curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
         label = self._label_map(mask.to(self.device)).float()
         if self.input_size_2d is None:
-            in_size = img.shape[2:] if img is not None else mask.shape[-2:]
+            # (a decoded u8 frame is [1, H, W, 3]; normalised f32 planes are [1, 3, H, W])
+            in_size = (img.shape[-3:-1] if img.dtype == torch.uint8 else img.shape[2:]) if img is not None \
+                else mask.shape[-2:]
             self.update_size(in_size, curr_enc_embs[-1].shape[2:])
         self._id_embed(label)
         ops.bank_init(self.ws.bank_state, self.frame_step)
@@ -966,6 +1067,7 @@ class DeAOTEngine:
         self.last_mem_step = frame_step
         self._decode(curr_enc_embs, lstt_out, None)
 
+    @_on_device
     def match_propogate_one_frame(self, img=None, img_embs=None, mask=None, output_size=None, next_img=None):
         """aot_engine.py:398-436 (save_atten_weights=True in eval). With CUDA graphs the returned logits
         live in a buffer that the next call overwrites -- consume them (softmax / argmax) first, as the
@@ -1002,10 +1104,12 @@ class DeAOTEngine:
         return self._run(("read", T, osz, st, p), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
                          alias=True)
 
+    @_on_device
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
         emb = curr_lstt_embs[-1] if isinstance(curr_lstt_embs, (list, tuple)) else curr_lstt_embs
         return self._decode(curr_enc_embs, emb, output_size)
 
+    @_on_device
     def update_short_term_memory(self, curr_mask, curr_id_emb=None, step=0):
         """aot_engine.py:327-369."""
         if curr_id_emb is not None:

@@ -93,7 +93,7 @@ class PreparedAOT:
         self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
         self.id_norm = (None, None)                                             # AOT: no LayerNorm on the id embedding
         self.encoder = encoder_cls(model.encoder, model.encoder_projector, device, enc_dtype)
-        self.decoder = decoder_cls(sd, device, intermediate=True)
+        self.decoder = decoder_cls(sd, device, intermediate=True, shortcut_dtype=self.encoder.dtype)
 
 
 class WorkspaceAOT:

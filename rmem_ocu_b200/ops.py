@@ -45,12 +45,19 @@ def linear(a, w, bias, segments, M=None):
     M = a.shape[0] if M is None else M
     K = a.shape[1]
     N = w.shape[0]
+    if a.dtype != w.dtype or a.dtype not in (torch.bfloat16, torch.float16):
+        raise _lib.RmemError("linear: a and w must both be bf16 or both fp16")
     segs = (GemmSegment * len(segments))()
     for i, (c0, c1, act, mode, dst, dcol) in enumerate(segments):
         segs[i] = GemmSegment(c0, c1, act, mode, dst.data_ptr(), dst.stride(0), dcol)
-    _lib.check(_lib.lib().rmem_linear(_p(a), a.stride(0), _p(w), w.stride(0), _p(bias), M, N, K,
-                                      ctypes.cast(segs, ctypes.c_void_p), len(segments), _stream()),
-               "rmem_linear")
+    if a.dtype == torch.float16:
+        _lib.check(_lib.lib().rmem_linear_ex(_p(a), a.stride(0), _p(w), w.stride(0), _p(bias), M, N, K,
+                                             ctypes.cast(segs, ctypes.c_void_p), len(segments), 1, _stream()),
+                   "rmem_linear_ex")
+    else:
+        _lib.check(_lib.lib().rmem_linear(_p(a), a.stride(0), _p(w), w.stride(0), _p(bias), M, N, K,
+                                          ctypes.cast(segs, ctypes.c_void_p), len(segments), _stream()),
+                   "rmem_linear")
     _count("rmem_linear")
 
 
@@ -121,14 +128,32 @@ def pack_image(img, out):
     _count("rmem_pack_image")
 
 
-def pack_image_s2d(img, out):
-    """img f32 [1, 3, H, W] contiguous -> out bf16 [1, 16, (H+1)//2+3, (W+1)//2+3] channels-last: the 2x2
+def pack_image_s2d(img, out, mean=None, std=None):
+    """img f32 [1, 3, H, W] contiguous -- or u8 [1, H, W, 3] / [H, W, 3] interleaved pixels, normalised here as
+    (u8 / 255 - mean) / std -- -> out bf16 or fp16 [1, 16, (H+1)//2+3, (W+1)//2+3] channels-last: the 2x2
     space-to-depth image with the stem convolution's zero padding built in (see include/rmem_b200.h)."""
     _chk_cuda(img, out)
     if not img.is_contiguous():
         img = img.contiguous()
-    H, W = img.shape[-2:]
-    _lib.check(_lib.lib().rmem_pack_image_s2d(_p(img), H, W, _p(out), _stream()), "rmem_pack_image_s2d")
+    u8 = img.dtype == torch.uint8
+    if u8:
+        if img.shape[-1] != 3:
+            raise _lib.RmemError("pack_image_s2d: u8 frames are interleaved [H, W, 3]")
+        H, W = img.shape[-3:-1]
+        mean = (0.0, 0.0, 0.0) if mean is None else mean
+        std = (1.0, 1.0, 1.0) if std is None else std
+        m3 = (ctypes.c_float * 3)(*[float(v) for v in mean])
+        s3 = (ctypes.c_float * 3)(*[1.0 / float(v) for v in std])
+    else:
+        if img.dtype != torch.float32:
+            raise _lib.RmemError("pack_image_s2d: img must be f32 planes or u8 pixels")
+        H, W = img.shape[-2:]
+        m3 = s3 = None
+    if out.dtype not in (torch.bfloat16, torch.float16):
+        raise _lib.RmemError("pack_image_s2d: out must be bf16 or fp16")
+    _lib.check(_lib.lib().rmem_pack_image_s2d_ex(_p(img), int(u8), m3, s3, H, W, _p(out),
+                                                 int(out.dtype == torch.float16), _stream()),
+               "rmem_pack_image_s2d_ex")
     _count("rmem_pack_image_s2d")
 
 
@@ -137,10 +162,13 @@ def maxpool3s2_nhwc(x, out, bias=None, relu=False):
     MaxPool2d(3, 2, 1) of the encoder stem; with bias (f32 [C]) / relu: relu(maxpool(x) + bias)."""
     _chk_cuda(x, out)
     n, C, H, W = x.shape
-    if n != 1 or x.dtype != torch.bfloat16 or x.stride()[1:] != (1, W * C, C):
-        raise ValueError("maxpool3s2_nhwc: expects one bf16 channels-last image")
-    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc(_p(x), H, W, C, _p(bias), 1 if relu else 0, _p(out), _stream()),
-               "rmem_maxpool3s2_nhwc")
+    if n != 1 or x.dtype not in (torch.bfloat16, torch.float16) or x.stride()[1:] != (1, W * C, C):
+        raise ValueError("maxpool3s2_nhwc: expects one bf16 / fp16 channels-last image")
+    if out.dtype != x.dtype:
+        raise ValueError("maxpool3s2_nhwc: out must have the input's dtype")
+    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc_ex(_p(x), H, W, C, _p(bias), 1 if relu else 0, _p(out),
+                                                  int(x.dtype == torch.float16), _stream()),
+               "rmem_maxpool3s2_nhwc_ex")
     _count("rmem_maxpool3s2_nhwc")
 
 
@@ -178,6 +206,30 @@ def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate,
                                                      _p(out), _p(attn_mass), _stream()),
                "rmem_lt_attn_deaot_combine")
     _count("rmem_lt_attn_deaot_combine")
+
+
+def lt_attn_sk_workspace(L, T_max, device, n_clusters=0):
+    """Workspace of the stream-K long-term attention for up to T_max frames in the bank (uint8 tensor)."""
+    n = max(_lib.lib().rmem_lt_attn_deaot_sk_workspace_bytes(L, T, n_clusters) for T in range(1, T_max + 1))
+    return torch.empty(n, device=device, dtype=torch.uint8)
+
+
+def lt_attn_sk_partial(q, kbank, vbank, order, T, tpe_bias, tpe_rows, record, workspace, n_clusters=0):
+    L = q.shape[0]
+    rows = (ctypes.c_int32 * max(T, 1))(*(tpe_rows if tpe_rows is not None else [0] * T))
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_partial(_p(q), _p(kbank), _p(vbank), _p(order), T, L, kbank.shape[0],
+                                                        _p(tpe_bias), ctypes.cast(rows, ctypes.c_void_p),
+                                                        1 if record else 0, n_clusters, _p(workspace),
+                                                        workspace.numel(), _stream()),
+               "rmem_lt_attn_deaot_sk_partial")
+    _count("rmem_lt_attn_deaot_sk_partial")
+
+
+def lt_attn_sk_combine(T, L, gate, out, attn_mass, workspace, n_clusters=0):
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_combine(T, L, _p(gate), _p(out), _p(attn_mass), n_clusters,
+                                                        _p(workspace), workspace.numel(), _stream()),
+               "rmem_lt_attn_deaot_sk_combine")
+    _count("rmem_lt_attn_deaot_sk_combine")
 
 
 def local_banded_buffer(h, w, device):

@@ -58,6 +58,51 @@ def test_long_term_attention_vs_oracle(lib_built, L, T, cpf, qscale):
     assert (mass.sum(1) - 1).abs().max().item() < 1e-4
 
 
+@pytest.mark.parametrize("L,T,qscale,use_tpe,use_gate,record", [
+    (1620, 5, 1.0, True, True, True),        # BASELINE config 2, steady state
+    (1705, 5, 3.0, True, True, True), (1620, 1, 1.0, False, True, False),   # self-attention form (T = 1, no TPE)
+    (1620, 9, 2.0, True, True, True),        # K = 8
+    (333, 9, 6.0, True, False, True), (64, 2, 1.0, True, True, True), (42, 12, 1.0, True, True, True),
+    (3600, 2, 2.0, True, True, True), (3600, 11, 1.0, True, True, True), (129, 1, 1.0, True, True, True)])
+def test_long_term_attention_streamk_vs_oracle(lib_built, L, T, qscale, use_tpe, use_gate, record):
+    """Second-generation long-term attention (persistent stream-K kernel on 2-CTA clusters with multicast K / V,
+    csrc/lt_attn_sk.cu): the same oracle and tolerances as the first generation -- relative Frobenius error <= 2e-2
+    on the output, <= 5e-3 absolute on the per-frame masses -- over shapes whose segments start / end inside
+    frames, span several frames, and leave clusters without work."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(L + T)
+    n_slots = T + 1
+    q = _bf(torch.randn(L, 128, device="cuda") * qscale)
+    kb = _bf(torch.randn(n_slots, L, 128, device="cuda"))
+    vb = _bf(torch.randn(n_slots, L, 1024, device="cuda"))
+    gate = _bf(torch.randn(L, 1024, device="cuda")) if use_gate else None
+    perm = torch.randperm(n_slots)[:T]
+    order = perm.to(device="cuda", dtype=torch.int32)
+    rows = [min(t, 3) for t in range(T)]
+    bias_nat = torch.randn(L, 4, device="cuda") * 0.5 if use_tpe else torch.zeros(L, 4, device="cuda")
+    ws = ops.lt_attn_sk_workspace(L, T, "cuda")
+    ws.fill_(0xff)                                          # NaN patterns: nothing may be read before it is written
+    out = torch.empty(L, 1024, device="cuda", dtype=torch.bfloat16)
+    mass = torch.empty(L, T, device="cuda") if record else None
+    for _ in range(2):                                      # twice: the kernel keeps no state between launches
+        ops.lt_attn_sk_partial(q, kb, vb, order, T, (bias_nat * math.log2(math.e)).contiguous() if use_tpe else None,
+                               rows if use_tpe else None, record, ws)
+        ops.lt_attn_sk_combine(T, L, gate, out, mass, ws)
+    torch.cuda.synchronize()
+    s = torch.cat([q.float() @ kb[perm[t]].float().t() / math.sqrt(128.0) + bias_nat[:, rows[t]][:, None]
+                   for t in range(T)], 1)
+    a = torch.softmax(s, -1)
+    o_ref = a @ torch.cat([vb[perm[t]].float() for t in range(T)], 0)
+    if use_gate:
+        o_ref = o_ref * gate.float()
+    assert torch.isfinite(out.float()).all()
+    assert _rel(out, o_ref) < 2e-2
+    if record:
+        m_ref = a.view(L, T, L).sum(-1)
+        assert (mass - m_ref).abs().max().item() < 5e-3
+        assert (mass.sum(1) - 1).abs().max().item() < 1e-4
+
+
 @pytest.mark.parametrize("h,w", [(31, 55), (30, 54), (9, 20), (45, 80)])
 def test_local_attention_vs_oracle(lib_built, h, w):
     """LocalGatedPropagation (15x15 window) against the oracle's direct windowed restatement."""

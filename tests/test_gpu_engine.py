@@ -100,8 +100,8 @@ def test_lstt_path_same_embeddings(lib_built, H, W, n, latter, repeat):
 
 
 def test_full_path_images(lib_built):
-    """Images in, masks out (bf16 cuDNN backbone): indexes must still match; mask agreement is reported
-    against the fp32 oracle with the looser bound a bf16 backbone allows."""
+    """Images in, masks out in the default configuration (fp16 cuDNN backbone): indexes must match and the masks
+    meet the north-star criterion, >= 99.9 % per frame against the fp32 oracle."""
     from oracle import restate as R
     from rmem_ocu_b200.engine import DeAOTInferEngine
     H, W, n, latter = 240, 432, 8, 2
@@ -121,7 +121,7 @@ def test_full_path_images(lib_built):
     assert eng.aot_engines[0].long_memories_indexes == o.long_memories_indexes
     agree = [(a == b).float().mean().item() for a, b in zip(p_masks, o_masks)]
     print("full-path mask agreement per frame:", agree)
-    assert min(agree) >= 0.98, agree
+    assert min(agree) >= 0.999, agree
 
 
 def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=True):
@@ -201,21 +201,65 @@ def test_deferred_write_path_matches_immediate(lib_built, monkeypatch, prefetch)
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
 
 
-def test_more_than_ten_objects_runs_two_engines(lib_built):
-    """12 objects -> two engines of 10 + 2 (aot_engine.py:675-703): every object id can appear in the merged
-    masks, both engines keep the same bank schedule."""
-    H, W, n = 240, 432, 6
-    m, _ = _models(2)
+def test_more_than_ten_objects_vs_oracle(lib_built, monkeypatch):
+    """12 objects -> two engines of 10 + 2 whose logits are merged every frame (aot_engine.py:604-628, 650-673,
+    675-720) against the oracle's InferEngine on the same clip: merged masks >= 99.9 % equal on every frame, merged
+    logits within 5e-2, both object groups keep the oracle's bank indexes (fp32 cuDNN backbone: the comparison
+    measures the kernels and the merge)."""
+    from oracle import restate as R
+    monkeypatch.setenv("RMEM_ENCODER_DTYPE", "fp32")
+    H, W, n, latter = 240, 432, 6, 2
+    m, sd = _models(latter)
     g = torch.Generator().manual_seed(3)
     imgs = [torch.randn(1, 3, H, W, generator=g) for _ in range(n)]
     lab = torch.zeros(1, 1, H, W, dtype=torch.int32)
     for o in range(1, 13):
         lab[:, :, 10 + 18 * (o - 1):10 + 18 * o, 20 + 30 * (o - 1):60 + 30 * (o - 1)] = o
-    masks, logits, idx, eng = _run_infer(m, imgs, lab, H, W, 12, gap=1)
-    assert len(eng.aot_engines) == 2
+    oe = R.InferEngine(sd, True, 1, latter, long_term_mem_gap=1)
+    o_masks, o_logits = [], []
+    with torch.no_grad():
+        oe.add_reference_frame(imgs[0], lab.float(), obj_nums=[12], frame_step=0)
+        for f in range(1, n):
+            lg = oe.match_propogate_one_frame(imgs[f], output_size=(H, W))
+            label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
+            o_masks.append(label[0, 0].to(torch.uint8))
+            o_logits.append(lg.clone())
+            oe.update_memory(F.interpolate(label, size=(H, W), mode="nearest"))
+    # the product is fed the ORACLE's label maps (teacher forcing): 21 nearly uniform channels of a random-init model
+    # make the argmax ill-conditioned, and a free-running loop would feed every flipped pixel back into the memory
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    eng = DeAOTInferEngine(m, 0, long_term_mem_gap=1)
+    masks, logits = [], []
+    with torch.no_grad():
+        eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[12], frame_step=0)
+        for f in range(1, n):
+            lg = eng.match_propogate_one_frame(imgs[f].cuda(), output_size=(H, W))
+            logits.append(lg.cpu())
+            masks.append(torch.argmax(lg, 1)[0].to(torch.uint8).cpu())
+            eng.update_memory(o_masks[f - 1].float().view(1, 1, H, W).cuda())
+    idx = [[list(e.long_memories_indexes) for e in eng.aot_engines]]
+    assert len(eng.aot_engines) == 2 == len(oe.aot_engines)
     assert logits[0].shape[1] == 21                                    # background + 2 x 10 object channels
-    assert all(i[0] == i[1] for i in idx)
-    assert int(max(mk.max() for mk in masks)) <= 20
+    assert idx[-1] == [list(e.long_memories_indexes) for e in oe.aot_engines]
+    assert int(max(mk.max() for mk in o_masks)) > 10                   # the second group's objects are tracked
+    # the merge ends in logit(clamp(p, 1e-5, 1 - 1e-5)): compare the probabilities it encodes
+    rel = [((torch.sigmoid(a) - torch.sigmoid(b)).norm() / torch.sigmoid(b).norm()).item()
+           for a, b in zip(logits, o_logits)]
+    # 21 channels of a random-init model are nearly uniform, and the 8 unused channels of the second group tie with
+    # each other: the argmax is only meaningful where the oracle's decision has a margin.  Decisive pixels = top-1
+    # minus top-2 merged probability > 2e-3 (the measured probability error is ~2e-3 RELATIVE, i.e. ~1e-4 absolute)
+    agree, frac = [], []
+    for mk, om, ol in zip(masks, o_masks, o_logits):
+        top2 = torch.sigmoid(ol[0]).topk(2, dim=0).values
+        decisive = (top2[0] - top2[1]) > 2e-3
+        frac.append(decisive.float().mean().item())
+        agree.append((mk == om)[decisive].float().mean().item())
+    raw = [(a == b).float().mean().item() for a, b in zip(masks, o_masks)]
+    print("12-object mask agreement on decisive pixels", [round(a, 5) for a in agree], "decisive fraction",
+          [round(f, 3) for f in frac], "all pixels", [round(a, 4) for a in raw], "rel prob err", [round(r, 4) for r in rel])
+    assert min(frac) > 0.1, frac
+    assert min(agree) >= 0.999, agree
+    assert max(rel) < 5e-2, rel
 
 
 def test_720p_ten_objects_vs_oracle(lib_built, monkeypatch):
@@ -275,3 +319,62 @@ def test_encoder_prefetch_matches_sequential(lib_built):
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-3, f
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+
+
+def test_u8_frames_match_normalised_planes(lib_built):
+    """A caller may hand the engine decoded u8 frames [1, H, W, 3]; the dataloader's normalisation
+    (video_transforms.py:537-539) then runs inside the packing kernel.  Same clip as normalised f32 planes: same
+    bank, logits to 1e-2 (one 16-bit rounding of the input differs), masks >= 99.9 %."""
+    from rmem_ocu_b200.engine import DeAOTInferEngine, InferenceResNet
+    H, W, n, latter = 240, 432, 7, 2
+    g = torch.Generator().manual_seed(11)
+    u8 = [torch.randint(0, 256, (1, H, W, 3), generator=g, dtype=torch.uint8) for _ in range(n)]
+    mean = torch.tensor(InferenceResNet.U8_MEAN).view(1, 3, 1, 1)
+    std = torch.tensor(InferenceResNet.U8_STD).view(1, 3, 1, 1)
+    planes = [((x.permute(0, 3, 1, 2).float() / 255.0 - mean) / std).contiguous() for x in u8]
+    _, lab = _clip(H, W, 1, 3)
+    outs = []
+    for frames in (u8, planes):
+        m, _ = _models(latter)
+        eng = DeAOTInferEngine(m, 0, long_term_mem_gap=2)
+        logits = []
+        with torch.no_grad():
+            eng.add_reference_frame(frames[0].cuda(), lab.cuda(), obj_nums=[3], frame_step=0)
+            assert tuple(eng.input_size_2d) == (H, W)
+            for f in range(1, n):
+                lg = eng.match_propogate_one_frame(frames[f].cuda(), output_size=(H, W))
+                logits.append(lg.clone())
+                label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
+                eng.update_memory(label)
+        outs.append((logits, eng.aot_engines[0].long_memories_indexes))
+    (la, ia), (lb, ib) = outs
+    assert ia == ib
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-2, f
+        assert (a.argmax(1) == b.argmax(1)).float().mean().item() >= 0.999, f
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_engine_on_second_device_of_one_process(lib_built):
+    """Engines take a gpu_id: one built for cuda:1 must work while the calling thread has cuda:0 selected (per-device
+    kernel attributes, launches on the engine's device's current stream) and give cuda:0's results."""
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    H, W, n, latter = 240, 432, 6, 2
+    imgs, lab = _clip(H, W, n, 3)
+    outs = []
+    for dev in (0, 1):
+        torch.cuda.set_device(0)                                   # the caller never switches devices
+        m, _ = _models(latter)
+        eng = DeAOTInferEngine(m, dev, long_term_mem_gap=1)
+        masks = []
+        with torch.no_grad():
+            eng.add_reference_frame(imgs[0].cuda(dev), lab.cuda(dev), obj_nums=[3], frame_step=0)
+            for f in range(1, n):
+                lg = eng.match_propogate_one_frame(imgs[f].cuda(dev), output_size=(H, W))
+                assert lg.device.index == dev
+                label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
+                masks.append(label[0, 0].to(torch.uint8).cpu())
+                eng.update_memory(label)
+        outs.append((masks, eng.aot_engines[0].long_memories_indexes))
+    assert outs[0][1] == outs[1][1]
+    assert min((a == b).float().mean().item() for a, b in zip(outs[0][0], outs[1][0])) >= 0.999

@@ -117,6 +117,82 @@ def test_deaot_attention_operators_vs_reference(lib_built):
         assert _rel(out[::RS], g["st_%s_out" % tag][:, 0]) < 2e-2, tag
 
 
+def test_deaot_gated_self_attention_vs_reference(lib_built):
+    """GatedPropagation as self_attn (transformer.py:1222-1232; attention.py:151-172 use_linear=True: linear_QK,
+    block-diagonal V1|V2 and U1|U2 with SiLU, attention with Q = K, gate, 5x5 depth-wise conv, projection) through
+    the engine's packed weights against the reference module's outputs (`sa_*_out` of ops_deaot.npz).
+    Tolerance: relative Frobenius error <= 2e-2 (bf16 tensor-core kernels vs the fp32 reference)."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import prepare
+    g = _load("ops_deaot")
+    m, _ = _synth.models(4, vos="deaot")
+    dev = torch.device("cuda", 0)
+    Lw = prepare(m, dev).layers[1]
+    for tag in _synth.OPS_DEAOT_CASES:
+        i = _synth.ops_deaot_inputs(tag)
+        h, w, L = i["h"], i["w"], i["L"]
+        x = _bf(i["X"][:, 0]).to(dev)
+        qk = torch.empty(L, 128, device=dev, dtype=torch.bfloat16)
+        v = torch.empty(L, 1024, device=dev, dtype=torch.bfloat16)
+        u = torch.empty(L, 1024, device=dev, dtype=torch.bfloat16)
+        ops.linear(x, Lw["w_sa"], Lw["b_sa"], [(0, 128, ops.ACT_NONE, ops.OUT_BF16, qk, 0),
+                                               (128, 1152, ops.ACT_SILU, ops.OUT_BF16, v, 0),
+                                               (1152, 2176, ops.ACT_SILU, ops.OUT_BF16, u, 0)])
+        po = torch.empty(1, L, 1024, device=dev)
+        pm, pl = torch.empty(1, L, device=dev), torch.empty(1, L, device=dev)
+        gated = torch.empty(L, 1024, device=dev, dtype=torch.bfloat16)
+        order = torch.zeros(1, device=dev, dtype=torch.int32)
+        ops.lt_attn_partial(qk, qk.view(1, L, 128), v.view(1, L, 1024), order, 1, 1, po, pm, pl)
+        ops.lt_attn_combine(po, pm, pl, None, None, 1, L, 1, u, gated, None)
+        dw = torch.empty(L, 1024, device=dev, dtype=torch.bfloat16)
+        ops.dwconv5(gated, 0, Lw["dw_sa"], dw, 0, h, w, 1024)
+        out = torch.empty(L, 512, device=dev)
+        ops.linear(dw, Lw["w_proj_sa"], Lw["b_proj_sa"], [(0, 512, ops.ACT_NONE, ops.OUT_F32, out, 0)])
+        torch.cuda.synchronize()
+        assert _rel(out[::RS], g["sa_%s_out" % tag][:, 0]) < 2e-2, tag
+
+
+def test_deaot_block_vs_reference_all_bank_lengths(lib_built):
+    """One GatedPropagationModule forward (layer 1: both branches, id_norm1 / linear_ID_U in play) per bank length
+    T = 1..12 against the reference block's outputs: pins the temporal-PE row selection incl. the T > 4 nearest
+    resample (transformer.py:1140-1175), the recorded masses, both residual streams.  Tolerance: 2e-2 relative
+    Frobenius on features; 1e-2 absolute on W -- this fixture multiplies the temporal embeddings by 20 so that a wrong
+    row would be unmistakable (a wrong row moves W by > 0.1), which also amplifies the bf16 rounding of q in the
+    single-head score; at the model's own scale W is held to 5e-3 (test_deaot_attention_operators_vs_reference)."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import DeAOTEngine
+    g = _load("layer_deaot")
+    m, _ = _synth.models(11, vos="deaot")
+    eng = DeAOTEngine(m, 0)
+    h, w = _synth.LAYER_HW
+    L = h * w
+    eng.update_size((h * 16, w * 16), (h, w))
+    eng.prep.cur_pos_emb.mul_(20.0)
+    eng.prep.mem_pos_emb.mul_(20.0)
+    ws = eng.ws
+    bf = lambda t: t.to(device="cuda", dtype=torch.bfloat16)
+    tok = lambda x: x[0].permute(1, 2, 0).reshape(L, -1)            # [1, C, h, w] -> [L, C]
+    try:
+        for T in range(1, 13):
+            i = _synth.layer_inputs("deaot", T)
+            ops.bank_init(ws.bank_state, 0)
+            ws.tgt.copy_(i["tgt"][:, 0].cuda())
+            ws.tgt_id.copy_(i["tgt_id"][:, 0].cuda())
+            ws.kbank[1][:T].copy_(bf(i["gK"][:, :, 0]))
+            ws.vbank[1][:T].copy_(bf(torch.cat([i["gV"][:, :, 0], i["gI"][:, :, 0]], -1)))
+            ws.kprev[1].copy_(bf(tok(i["lK"])))
+            ws.vprev[1].copy_(bf(torch.cat([tok(i["lV"]), tok(i["lI"])], -1)))
+            eng._block_forward(1, False, True, T)
+            torch.cuda.synchronize()
+            W = ws.mass[:L * T].view(L, T).cpu()
+            assert _rel(ws.tgt, g["T%d_out" % T][:, 0]) < 2e-2, T
+            assert _rel(ws.tgt_id, g["T%d_out_id" % T][:, 0]) < 2e-2, T
+            assert (W - torch.from_numpy(g["T%d_W" % T])).abs().max().item() < 1e-2, T
+    finally:
+        eng.prep.cur_pos_emb.div_(20.0)                              # `prepare` caches per model object
+        eng.prep.mem_pos_emb.div_(20.0)
+
+
 # ------------------------------------------------------------------------------------------------
 def _run_product(g, monkeypatch, encoder_dtype):
     from rmem_ocu_b200.engine import build_engine
@@ -175,16 +251,82 @@ def test_deaot_engine_clip_vs_reference(lib_built, monkeypatch, name):
     assert max(rel) < 5e-2, (name, rel)
 
 
-def test_deaot_engine_clip_bf16_backbone(lib_built, monkeypatch):
-    """Same clip with the production bf16 backbone: indexes still bit-exact; mask agreement reported
-    with the looser bound a bf16 ResNet allows on random-init weights."""
+def _run_long(g, monkeypatch, encoder_dtype, prefetch):
+    """Free-running clip through the drop-in engine the way bench.py drives it (CUDA graphs, argmax kernel, optional
+    encoder prefetch): masks on the fixture's sampled frames, bank indexes after EVERY frame (read from the device
+    slot table at the frames where the fixture's indexes change, and at the end -- reading synchronises)."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import build_engine
+    monkeypatch.setenv("RMEM_ENCODER_DTYPE", encoder_dtype)
+    H, W, n, n_obj, latter, gap, repeat, cseed = [int(v) for v in g["meta"]]
+    m, _ = _synth.models(latter, vos="deaot")
+    imgs, lab = _synth.clip(H, W, n, n_obj, cseed, repeat)
+    want_idx = [[int(v) for v in row if v >= 0] for row in g["indexes"]]
+    check_at = {f for f in range(1, n) if f == n - 1 or f == 1 or want_idx[f - 1] != want_idx[f - 2]}
+    frames = [int(f) for f in g["mask_frames"]]
+    eng = build_engine("deaotengine", phase="eval", aot_model=m, gpu_id=0, long_term_mem_gap=gap)
+    agree, bad_idx = [], []
+    with torch.no_grad():
+        eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[n_obj], frame_step=0)
+        nxt = imgs[1].cuda()
+        for f in range(1, n):
+            cur, nxt = nxt, (imgs[f + 1].cuda() if f + 1 < n else None)
+            lg = eng.match_propogate_one_frame(cur, output_size=(H, W), next_img=nxt if prefetch else None)
+            label = ops.argmax_label(lg)
+            if f in frames:
+                agree.append(float((label[0, 0].to(torch.uint8).cpu().numpy() == g["masks"][frames.index(f)]).mean()))
+            eng.update_memory(label)
+            if f in check_at and list(eng.aot_engines[0].long_memories_indexes) != want_idx[f - 1]:
+                bad_idx.append((f, list(eng.aot_engines[0].long_memories_indexes), want_idx[f - 1]))
+    return agree, bad_idx, eng
+
+
+@pytest.mark.parametrize("name,encoder_dtype,prefetch", [
+    ("clip_deaot_cfg2", "fp32", False),      # BASELINE.json config 2 as written: 480x864, 5 objects, K = 4, 100 frames, gap 5
+    ("clip_deaot_cfg2", "fp16", True),       # ... in the configuration bench.py times (production backbone, prefetch)
+    ("clip_deaot_long", "fp32", False),      # config 4's regime: K = 8, gap 67, 1150 frames, 9 evictions
+    ("clip_deaot_long", "fp16", True),
+])
+def test_deaot_long_clip_vs_reference(lib_built, monkeypatch, name, encoder_dtype, prefetch):
+    """Free-running long clips against the reference's own run (fixtures from oracle/make_golden.py): the bank's
+    frame ids bit-exact at every long-term update over the whole clip, >= 99.9 % argmax mask agreement on every
+    sampled frame -- no drift of the recurrent bf16 short-term memory over 100 / 1150 frames."""
+    g = _load(name)
+    _well_conditioned(g, name)
+    agree, bad_idx, eng = _run_long(g, monkeypatch, encoder_dtype, prefetch)
+    print(name, encoder_dtype, "mask agreement min %.5f over %d sampled frames" % (min(agree), len(agree)),
+          [round(a, 5) for a in agree])
+    assert not bad_idx, bad_idx[:3]
+    n_app = sum(1 for a, b in zip(g["indexes"][1:], g["indexes"][:-1]) if (a != b).any())
+    assert eng.aot_engines[0].n_long_updates == n_app + (1 if (g["indexes"][0] >= 0).sum() > 1 else 0)
+    assert min(agree) >= 0.999, (name, agree)
+
+
+@pytest.mark.parametrize("name", DEAOT_CLIPS)
+def test_deaot_engine_clip_production_backbone(lib_built, monkeypatch, name):
+    """The same clips in the configuration bench.py times (the default: fp16 cuDNN backbone, bf16 kernels on the
+    path): indexes bit-exact after every frame and the north-star mask criterion, >= 99.9 % per frame."""
+    from rmem_ocu_b200 import engine as E
+    assert E.ENCODER_DTYPE_DEFAULT == "fp16"
+    g = _load(name)
+    masks, idx_log, logits, n = _run_product(g, monkeypatch, E.ENCODER_DTYPE_DEFAULT)
+    for f, idx in enumerate(idx_log):
+        assert idx == [int(v) for v in g["indexes"][f] if v >= 0], (f + 1, idx)
+    agree = [float((m == gm).mean()) for m, gm in zip(masks, g["masks"])]
+    print(name, "production-backbone mask agreement", [round(a, 5) for a in agree])
+    assert min(agree) >= 0.999, agree
+
+
+def test_deaot_engine_clip_bf16_backbone_is_looser(lib_built, monkeypatch):
+    """RMEM_ENCODER_DTYPE=bf16 stays available; on random-init weights (logit margins near zero) a bf16 ResNet
+    costs 0.1-0.2 % of the mask pixels, which is why it is not the default.  Indexes still bit-exact."""
     g = _load("clip_deaot_mid")
     masks, idx_log, logits, n = _run_product(g, monkeypatch, "bf16")
     for f, idx in enumerate(idx_log):
         assert idx == [int(v) for v in g["indexes"][f] if v >= 0], (f + 1, idx)
     agree = [float((m == gm).mean()) for m, gm in zip(masks, g["masks"])]
     print("bf16-backbone mask agreement", [round(a, 5) for a in agree])
-    assert min(agree) >= 0.97, agree
+    assert min(agree) >= 0.99, agree
 
 
 # ------------------------------------------------------------------------------------------------ AOT

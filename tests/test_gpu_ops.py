@@ -131,7 +131,7 @@ def test_tpe_prepare(lib_built):
     torch.cuda.synchronize()
     qref = q.float() + cur
     assert _rel(qt, qref) < 4e-3
-    bref = (qt.float() @ mem.t()) * (math.log2(math.e) / math.sqrt(128))
+    bref = (qref @ mem.t()) * (math.log2(math.e) / math.sqrt(128))   # f32 q + cur: the bias is not re-rounded
     assert (bias - bref).abs().max().item() < 1e-4
 
 
@@ -294,21 +294,62 @@ def test_pack_image(lib_built):
     assert (out[:, 3:] == 0).all()
 
 
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("C,H,W", [(64, 240, 432), (64, 241, 433), (8, 5, 7)])
-def test_maxpool3s2_nhwc(lib_built, C, H, W):
-    """Encoder stem MaxPool2d(3, 2, 1) on bf16 channels-last: bit-exact against torch (a max is exact)."""
+def test_maxpool3s2_nhwc(lib_built, C, H, W, dt):
+    """Encoder stem MaxPool2d(3, 2, 1) on bf16 / fp16 channels-last: bit-exact against torch (a max is exact)."""
     from rmem_ocu_b200 import ops
     torch.manual_seed(5)
-    x = torch.randn(1, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-    ref = F.max_pool2d(x.float(), 3, 2, 1).to(torch.bfloat16)
+    x = torch.randn(1, C, H, W, device="cuda").to(dt).contiguous(memory_format=torch.channels_last)
+    ref = F.max_pool2d(x.float(), 3, 2, 1).to(dt)
     out = torch.empty_like(ref).contiguous(memory_format=torch.channels_last)
     ops.maxpool3s2_nhwc(x, out)
     assert torch.equal(out, ref)
-    # fused form: relu(maxpool(x) + bias) == maxpool(relu(x + bias)) up to the final bf16 rounding
+    # fused form: relu(maxpool(x) + bias) == maxpool(relu(x + bias)) up to the final 16-bit rounding
     bias = torch.randn(C, device="cuda")
     ops.maxpool3s2_nhwc(x, out, bias, True)
     ref2 = F.max_pool2d(F.relu(x.float() + bias.view(1, -1, 1, 1)), 3, 2, 1)
-    assert torch.equal(out, ref2.to(torch.bfloat16))
+    assert torch.equal(out, ref2.to(dt))
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+def test_pack_image_s2d_u8_frames(lib_built, dt):
+    """Decoded u8 frames [H, W, 3]: the dataloader's normalisation (video_transforms.py:537-539) happens inside the
+    packing kernel; equal to packing the normalised f32 planes up to one rounding of the 16-bit output."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import InferenceResNet
+    torch.manual_seed(19)
+    H, W = 121, 75
+    u8 = torch.randint(0, 256, (1, H, W, 3), device="cuda", dtype=torch.uint8)
+    mean, std = InferenceResNet.U8_MEAN, InferenceResNet.U8_STD
+    planes = (u8.permute(0, 3, 1, 2).float() / 255.0 - torch.tensor(mean, device="cuda").view(1, 3, 1, 1)) \
+        / torch.tensor(std, device="cuda").view(1, 3, 1, 1)
+    Hs, Ws = (H + 1) // 2, (W + 1) // 2
+    a = torch.empty(1, Hs + 3, Ws + 3, 16, device="cuda", dtype=dt).permute(0, 3, 1, 2)
+    b = torch.empty_like(a)
+    ops.pack_image_s2d(u8, a, mean, std)
+    ops.pack_image_s2d(planes.contiguous(), b)
+    torch.cuda.synchronize()
+    eps = 2.0 ** (-8 if dt == torch.bfloat16 else -11)
+    assert (a.float() - b.float()).abs().max().item() <= eps * b.float().abs().max().item()
+    assert (a[:, 12:] == 0).all() and (a[:, :, :2] == 0).all() and (a[:, :, :, :2] == 0).all()
+
+
+def test_linear_fp16_operands(lib_built):
+    """rmem_linear_ex with IEEE fp16 A / W (the decoder adapters read the fp16 backbone's feature maps)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(23)
+    M, K, N = 1620, 1024, 256
+    a = torch.randn(M, K, device="cuda").half()
+    w = (torch.randn(N, K, device="cuda") * 0.05).half()
+    bias = torch.randn(N, device="cuda")
+    out = torch.empty(M, N, device="cuda")
+    ops.linear(a, w, bias, [(0, N, ops.ACT_NONE, ops.OUT_F32, out, 0)])
+    torch.cuda.synchronize()
+    ref = a.float() @ w.float().t() + bias
+    assert _rel(out, ref) < 1e-5                    # exact products, f32 accumulation
+    with pytest.raises(Exception):
+        ops.linear(a, w.to(torch.bfloat16), bias, [(0, N, ops.ACT_NONE, ops.OUT_F32, out, 0)])
 
 
 @pytest.mark.parametrize("H,W", [(480, 864), (481, 865), (37, 54)])
@@ -332,7 +373,7 @@ def test_pack_image_s2d_and_stem_equivalence(lib_built, H, W):
     assert torch.equal(out.float(), ref.to(torch.bfloat16).float())
     m = DeAOTModel(RMemConfig(latter_mem_len=1))
     deterministic_init_(m.state_dict(), 3)
-    enc = InferenceResNet(m.encoder, m.encoder_projector, torch.device("cuda"))
+    enc = InferenceResNet(m.encoder, m.encoder_projector, torch.device("cuda"), torch.bfloat16)
     assert enc.conv1_s2d is not None
     w8, b8, stride, pad = enc.conv1
     with torch.no_grad():
