@@ -5,10 +5,17 @@
 
 A step = one video frame through the hot path: match_propogate_one_frame + update_memory
 (the region the reference's own FPS print times, networks/managers/evaluator.py:399-404, 525-527).
-Workload = BASELINE.json configs[1]: synthetic 480x864 clip, 5 objects, one engine, bank capacity
-1 + 4, evaluator gap rule (gap 5 for a 100-frame clip), random-init (deterministic) weights.
-One sequence per GPU; N GPUs run N independent sequences (weak scaling, no collective on the path,
-one final all_gather of the per-rank results).
+
+Headline workload = BASELINE.json configs[1] ("config 2"): synthetic 480x864 clip, 5 objects, one engine, bank
+capacity 1 + 4, evaluator gap rule (gap 5 for a 100-frame clip), random-init (deterministic) weights, fp16 cuDNN
+backbone + bf16 kernels on the path (the configuration tests/test_gpu_golden.py holds to >= 99.9 % mask agreement
+with the reference).  The bank is filled during untimed frames, so every timed step is steady state (T = 5).
+One sequence per GPU; N GPUs run N independent sequences (weak scaling, no collective on the path, one final
+all_gather of the per-rank results).
+
+Extra legs on the same JSON line (not the headline): `stock_api` (no `next_img=`), `e2e_u8` (decoded u8 frames
+uploaded, normalised on the device), `gpu_eager_port` (the oracle in PyTorch eager on the GPU: the "kernel to beat"),
+`configs` (BASELINE configs 3, 4, 5), `cpu_baseline`.
 """
 import argparse
 import json
@@ -28,6 +35,7 @@ import torch.nn.functional as F  # noqa: E402
 H, W = 480, 864
 N_OBJ = 5
 LATTER = 4
+POOL = 48            # distinct synthetic frames a long clip cycles through (device memory, not the metric)
 
 
 def parse_args():
@@ -42,19 +50,33 @@ def parse_args():
     ap.add_argument("--seqs-per-gpu", type=int, default=2,
                     help="extra leg at N=1: S concurrent sequences on one GPU (0 / 1 = skip)")
     ap.add_argument("--kernel-only", action="store_true", help="only the isolated kernel rooflines")
+    ap.add_argument("--no-extra-legs", action="store_true",
+                    help="skip stock_api / e2e_u8 / gpu_eager_port / configs 3-5 (headline, e2e, rooflines only)")
+    ap.add_argument("--config4-frames", type=int, default=2000)
     ap.add_argument("--profile-steps", type=int, default=0,
                     help="bracket the first N timed steps with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     return ap.parse_args()
 
 
-def make_clip(n_frames, seed, pinned=False):
+def make_clip(n_frames, seed, pinned=False, h=H, w=W, n_obj=N_OBJ, u8=False):
     g = torch.Generator().manual_seed(seed)
-    imgs = [torch.randn(1, 3, H, W, generator=g) for _ in range(n_frames)]
+    if u8:
+        imgs = [torch.randint(0, 256, (1, h, w, 3), generator=g, dtype=torch.uint8) for _ in range(n_frames)]
+    else:
+        imgs = [torch.randn(1, 3, h, w, generator=g) for _ in range(n_frames)]
     if pinned:
         imgs = [im.pin_memory() for im in imgs]
-    lab = torch.zeros(1, 1, H, W, dtype=torch.int32)
-    for o in range(1, N_OBJ + 1):
-        lab[:, :, 40 + 60 * (o - 1):120 + 60 * (o - 1), 100 + 100 * (o - 1):300 + 100 * (o - 1)] = o
+    lab = torch.zeros(1, 1, h, w, dtype=torch.int32)
+    s = h / 480.0
+    if n_obj <= 5:
+        for o in range(1, n_obj + 1):
+            lab[:, :, int((40 + 60 * (o - 1)) * s):int((120 + 60 * (o - 1)) * s),
+                int((100 + 100 * (o - 1)) * s):int((300 + 100 * (o - 1)) * s)] = o
+    else:                                                    # two rows of five rectangles
+        for o in range(n_obj):
+            r, c = divmod(o, 5)
+            lab[:, :, int((40 + 210 * r) * s):int((200 + 210 * r) * s),
+                int((30 + 165 * c) * s):int((150 + 165 * c) * s)] = o + 1
     return imgs, lab
 
 
@@ -63,9 +85,9 @@ def gap_rule(n_frames):
     return max(int(round(n_frames / 30)), 5)
 
 
-def build_model():
-    from rmem_ocu_b200.model import DeAOTModel, RMemConfig, deterministic_init_
-    m = DeAOTModel(RMemConfig(latter_mem_len=LATTER))
+def build_model(latter=LATTER, vos="deaot"):
+    from rmem_ocu_b200.model import AOTModel, DeAOTModel, RMemConfig, deterministic_init_
+    m = (DeAOTModel if vos == "deaot" else AOTModel)(RMemConfig(model_vos=vos, latter_mem_len=latter))
     deterministic_init_(m.state_dict(), 0)
     return m
 
@@ -160,7 +182,21 @@ def frame_step(eng, img_dev, out_hw, next_img=None):
     return label
 
 
-def run_b200(args, rank, world):
+def pin_rank_to_cores(local_rank, world):
+    """Each rank of a box gets its own slice of the host cores (the ranks otherwise all float over the same cores
+    and the launching threads of 8 processes contend: SCALE_r01 lost 5 % of e2e at N = 8)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        if world > 1 and len(cores) >= 2 * world:
+            k = len(cores) // world
+            os.sched_setaffinity(0, cores[local_rank * k:(local_rank + 1) * k])
+            return k
+    except Exception:
+        pass
+    return None
+
+
+def run_b200(args, rank, world, modes=("device", "e2e")):
     from rmem_ocu_b200 import ops
     from rmem_ocu_b200.engine import DeAOTInferEngine
     from rmem_ocu_b200.pipeline import FrameStreamer
@@ -169,12 +205,14 @@ def run_b200(args, rank, world):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     model = build_model()
-    n_frames = 1 + args.warmup + args.steps
-    gap = gap_rule(100 if n_frames <= 100 else n_frames)
+    gap = gap_rule(100)
+    prefill = gap * LATTER                        # untimed: the bank reaches its capacity (T = 1 + LATTER)
+    head = prefill + args.warmup                  # untimed frames after the reference frame
+    n_frames = 1 + head + args.steps
     # one image beyond the clip: the last timed step also starts an encoder pass ahead, so that the timed region
     # holds exactly `steps` encoder passes (the first timed frame's pass ran during the last warm-up step)
     imgs, lab = make_clip(n_frames + 1, 1000 + rank, pinned=True)
-    pf = not args.no_prefetch
+    imgs_u8 = None
 
     def barrier():
         torch.cuda.synchronize()
@@ -183,30 +221,40 @@ def run_b200(args, rank, world):
         torch.cuda.synchronize()
 
     results = {}
-    for mode in ("device", "e2e"):
+    for mode in modes:
+        pf = not args.no_prefetch and mode != "stock"
+        u8 = mode == "e2e_u8"
+        if u8 and imgs_u8 is None:
+            imgs_u8, _ = make_clip(n_frames + 1, 3000 + rank, pinned=True, u8=True)
+        src = imgs_u8 if u8 else imgs
+        host_io = mode in ("e2e", "e2e_u8")
         eng = DeAOTInferEngine(model, local_rank, long_term_mem_gap=gap)
-        dev_imgs = [im.to(dev) for im in imgs] if mode == "device" else None
+        dev_imgs = [im.to(dev) for im in src] if not host_io else None
         host_out = torch.empty(H, W, dtype=torch.uint8).pin_memory()
+        t_seen = []
         with torch.no_grad():
-            eng.add_reference_frame(imgs[0].to(dev), lab.to(dev), obj_nums=[N_OBJ], frame_step=0)
-            warm = dev_imgs if dev_imgs is not None else [None] + [imgs[f].to(dev) for f in range(1, 2 + args.warmup)]
-            for f in range(1, 1 + args.warmup):
+            eng.add_reference_frame(src[0].to(dev), lab.to(dev), obj_nums=[N_OBJ], frame_step=0)
+            warm = dev_imgs if dev_imgs is not None else [None] + [src[f].to(dev) for f in range(1, 2 + head)]
+            for f in range(1, 1 + head):
                 frame_step(eng, warm[f], (H, W), warm[f + 1] if pf else None)
                 if f == 1:
                     eng.precapture((H, W), prefetch=pf)   # CUDA graphs for every bank length, recorded during warm-up
+            del warm
             barrier()
             launches0 = ops.LAUNCHES
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            first = 1 + args.warmup
-            fs = FrameStreamer(dev).preallocate((1, 3, H, W), (H, W)) if mode == "e2e" else None
+            first = 1 + head
+            fs = None
+            if host_io:
+                fs = FrameStreamer(dev).preallocate(tuple(src[0].shape), (H, W), image_dtype=src[0].dtype)
             with ClockSampler(local_rank) as clk:
                 e0.record()
                 t_host0 = time.perf_counter()
-                if mode == "e2e":
+                if host_io:
                     # host frames in, host masks out, every frame: uploads and read-backs are double-buffered on
                     # copy streams (rmem_ocu_b200/pipeline.py), each mask is consumed on the host one frame late
-                    fs.stage(imgs[first])
-                    fs.stage(imgs[first + 1])
+                    fs.stage(src[first])
+                    fs.stage(src[first + 1])
                     x = fs.acquire()
                 for f in range(first, n_frames):
                     if mode == "device" and args.profile_steps:
@@ -215,19 +263,20 @@ def run_b200(args, rank, world):
                         elif f == first + args.profile_steps:
                             torch.cuda.synchronize()
                             torch.cuda.profiler.stop()
-                    if mode == "device":
+                    t_seen.append(eng.aot_engines[0].T)             # frames in the bank this step reads (host mirror)
+                    if not host_io:
                         label = frame_step(eng, dev_imgs[f], (H, W), dev_imgs[f + 1] if pf else None)
                     else:
                         x_next = fs.acquire()                                # frame f + 1 (uploaded a step ago)
                         if f + 2 <= n_frames:
-                            fs.stage(imgs[f + 2])                            # pinned host image -> device
+                            fs.stage(src[f + 2])                             # pinned host image -> device
                         label = frame_step(eng, x, (H, W), x_next if pf else None)
                         fs.release(x)                  # the current stream has waited for the pass that read x
                         x = x_next
                         fs.push_result(label[0, 0].to(torch.uint8))          # device label map -> pinned host
                         if fs.pending_results() > 1:
                             host_out = fs.pop_result()
-                if mode == "e2e":
+                if host_io:
                     while fs.pending_results():
                         host_out = fs.pop_result()
                     torch.cuda.synchronize()
@@ -237,53 +286,63 @@ def run_b200(args, rank, world):
                 barrier()
             ms = e0.elapsed_time(e1)
         results[mode] = dict(ms=ms, host_ms=host_ms, launches=ops.LAUNCHES - launches0, clocks=clk.summary(),
-                             idx=eng.aot_engines[0].long_memories_indexes, checksum=int(label.sum().item()))
-        if mode == "e2e" and host_sum != results[mode]["checksum"]:
+                             idx=eng.aot_engines[0].long_memories_indexes, checksum=int(label.sum().item()),
+                             T=[min(t_seen), max(t_seen)], h2d=src[0].numel() * src[0].element_size())
+        if host_io and host_sum != results[mode]["checksum"]:
             raise RuntimeError("e2e: the mask read back on the host differs from the device label map")
         del eng, dev_imgs
-    # max over ranks
-    t = torch.tensor([results["device"]["ms"], results["e2e"]["ms"]], device=dev, dtype=torch.float64)
+    # max over ranks, and the spread (the straggler is what the metric sees)
+    names = list(modes)
+    t = torch.tensor([results[m]["ms"] for m in names], device=dev, dtype=torch.float64)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        gathered = [None] * world
-        dist.all_gather_object(gathered, dict(rank=rank, frames=args.steps, checksum=results["device"]["checksum"]))
-    results["device"]["ms_max"], results["e2e"]["ms_max"] = float(t[0]), float(t[1])
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        allt = torch.stack(allt)                                                 # [world, modes]
+        from rmem_ocu_b200.shard import gather_results
+        gather_results({rank: dict(frames=args.steps, checksum=results[names[0]]["checksum"])})
+    else:
+        allt = t[None]
+    for i, m in enumerate(names):
+        col = allt[:, i].sort().values
+        results[m]["ms_max"] = float(col[-1])
+        results[m]["ms_per_rank"] = {"min": float(col[0]), "median": float(col[len(col) // 2]), "max": float(col[-1])}
     return results
 
 
-def run_multi_sequence(args, local_rank, S):
-    """S independent sequences on one GPU (BASELINE.json configs 3 / 4 run 2 sequences per GPU): one engine and one
-    stream per sequence, the host interleaves their frames; sub-wave kernels of one sequence fill SMs the other
-    leaves idle.  Returns aggregate frames/s over the S sequences (device events, inputs resident)."""
+def run_sequences(model, local_rank, seq_ids, spec, steps, head, precapture=True):
+    """Several independent sequences on one GPU (BASELINE.json configs 4 / 5 put 2 per GPU): one engine and one
+    stream per sequence, the host interleaves their frames in lock-step; sub-wave kernels of one sequence fill SMs
+    the other leaves idle.  `head` untimed frames, then `steps` timed ones per sequence; frames cycle through a pool
+    of POOL distinct synthetic images.  Returns (ms, per-sequence info)."""
     from rmem_ocu_b200.engine import DeAOTInferEngine
     dev = torch.device("cuda", local_rank)
-    model = build_model()
-    n_frames = 1 + args.warmup + args.steps
-    gap = gap_rule(100 if n_frames <= 100 else n_frames)
+    h, w, n_obj, gap = spec["H"], spec["W"], spec["n_obj"], spec["gap"]
     engines, streams, clips = [], [], []
-    for q in range(S):
-        imgs, lab = make_clip(n_frames, 2000 + q)
+    for q in seq_ids:
+        imgs, lab = make_clip(min(POOL, 1 + head + steps), 2000 + q, h=h, w=w, n_obj=n_obj)
         clips.append(([im.to(dev) for im in imgs], lab.to(dev)))
         engines.append(DeAOTInferEngine(model, local_rank, long_term_mem_gap=gap))
         streams.append(torch.cuda.Stream(device=dev))
+    S = len(seq_ids)
+    img = lambda q, f: clips[q][0][f % len(clips[q][0])]
     torch.cuda.synchronize()
     with torch.no_grad():
         for q in range(S):
             with torch.cuda.stream(streams[q]):
-                engines[q].add_reference_frame(clips[q][0][0], clips[q][1], obj_nums=[N_OBJ], frame_step=0)
-                for f in range(1, 1 + args.warmup):
-                    frame_step(engines[q], clips[q][0][f], (H, W))
-                    if f == 1:
-                        engines[q].precapture((H, W))
+                engines[q].add_reference_frame(clips[q][0][0], clips[q][1], obj_nums=[n_obj], frame_step=0)
+                for f in range(1, 1 + head):
+                    frame_step(engines[q], img(q, f), (h, w))
+                    if f == 1 and precapture:
+                        engines[q].precapture((h, w))
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for st in streams:
             st.wait_event(e0)
-        for f in range(1 + args.warmup, n_frames):
+        for f in range(1 + head, 1 + head + steps):
             for q in range(S):
                 with torch.cuda.stream(streams[q]):
-                    frame_step(engines[q], clips[q][0][f], (H, W))
+                    frame_step(engines[q], img(q, f), (h, w))
         for q, st in enumerate(streams):
             done = torch.cuda.Event()
             with torch.cuda.stream(st):
@@ -292,19 +351,114 @@ def run_multi_sequence(args, local_rank, S):
             torch.cuda.current_stream().wait_event(done)
         e1.record()
         torch.cuda.synchronize()
-    return S * args.steps / (e0.elapsed_time(e1) * 1e-3)
+    info = {seq_ids[q]: dict(frames=steps, bank=engines[q].aot_engines[0].long_memories_indexes,
+                             evictions=engines[q].aot_engines[0].eviction_debug()["n_evictions"])
+            for q in range(S)}
+    return e0.elapsed_time(e1), info
 
 
-def kernel_rooflines(dev):
-    """Isolated timings of the two headline kernels at the workload's steady-state shape, CUDA events on
-    the launching stream, inputs rotated through > L2-size copies so no launch re-reads a warm L2."""
-    from rmem_ocu_b200 import ops
+def config_legs(args, rank, world, local_rank):
+    """BASELINE.json configs 3, 4, 5 as extra legs (not the headline).  4 and 5 shard their sequences over the ranks
+    with rmem_ocu_b200.shard (2 per GPU) and gather the per-sequence results at the end; 3 is rank 0 only."""
+    import torch.distributed as dist
+    from rmem_ocu_b200.shard import assign_sequences, gather_results, max_over_ranks
+    dev = torch.device("cuda", local_rank)
+    out = {}
+    # ---- config 4: long videos, K = 8 (eval_vost.sh:28), gap = round(2000 / 30) = 67, 2 sequences per GPU
+    n4 = args.config4_frames
+    spec4 = dict(H=480, W=864, n_obj=5, gap=gap_rule(n4))
+    seqs = assign_sequences(2 * world, world, rank)
+    head4 = 8
+    ms, info = run_sequences(build_model(latter=8), local_rank, seqs, spec4, n4 - 1 - head4, head4)
+    ms = max_over_ranks(ms, dev)
+    merged = gather_results(info)
+    frames = sum(v["frames"] for v in merged.values())
+    out["4"] = {"workload": "R50 DeAOT-L + RMem, %d-frame synthetic 480x864 clips (pool of %d images), 5 objects, K = 8, "
+                            "gap %d, %d sequences over %d GPU(s)" % (n4, POOL, spec4["gap"], len(merged), world),
+                "value": frames / (ms * 1e-3), "unit": "frames/s", "ms": ms, "sequences": len(merged),
+                "evictions_per_sequence": sorted(v["evictions"] for v in merged.values()),
+                "bank_of_sequence_0": merged[0]["bank"]}
+    # ---- config 5: 720p, 10 objects (one engine), 100-frame clips, 2 per GPU
+    spec5 = dict(H=720, W=1280, n_obj=10, gap=gap_rule(100))
+    head5 = spec5["gap"] * LATTER + 3
+    ms, info = run_sequences(build_model(latter=LATTER), local_rank, seqs, spec5, 100 - 1 - head5, head5)
+    ms = max_over_ranks(ms, dev)
+    merged = gather_results(info)
+    frames = sum(v["frames"] for v in merged.values())
+    out["5"] = {"workload": "R50 DeAOT-L + RMem, 100-frame synthetic 720x1280 clips (L = 3600 tokens), 10 objects, "
+                            "K = 4, gap 5, %d sequences over %d GPU(s); timed at steady state (bank full)"
+                            % (len(merged), world),
+                "value": frames / (ms * 1e-3), "unit": "frames/s", "ms": ms, "sequences": len(merged)}
+    # ---- config 3: AOT-L slot-count sweep K = 2 / 4 / 8 at 480p (rank 0): frames/s + the A1 kernel's roofline
+    if rank == 0:
+        from rmem_ocu_b200 import ops
+        from rmem_ocu_b200.engine_aot import mha_chunks_per_frame
+        peak = load_peaks()["bf16_tflops"]
+        rows = []
+        L = (H // 16) * (W // 16)
+        for K in (2, 4, 8):
+            spec3 = dict(H=H, W=W, n_obj=1, gap=1)
+            ms, info = run_sequences(build_model(latter=K, vos="aot"), local_rank, [0], spec3, 40, K + 4)
+            T = K + 1
+            cpf = mha_chunks_per_frame(T, L)
+            nb = 6
+            bf = lambda *s: torch.randn(*s, device=dev).to(torch.bfloat16)
+            q2 = [bf(L, 256) for _ in range(nb)]
+            kb2, vb2 = [bf(T, L, 256) for _ in range(nb)], [bf(T, L, 256) for _ in range(nb)]
+            po2 = torch.empty(T * cpf, L, 256, device=dev)
+            pm2, pl2 = torch.empty(T * cpf, 8, L, device=dev), torch.empty(T * cpf, 8, L, device=dev)
+            order = torch.arange(T, device=dev, dtype=torch.int32)
+            t = timed_graph(lambda i: ops.mha_partial(q2[i % nb], kb2[i % nb], vb2[i % nb], order, T, cpf, po2, pm2, pl2))
+            fl = 4.0 * L * T * L * 256
+            rows.append({"K": K, "T": T, "frames_per_s": 40 / (ms * 1e-3), "bank": info[0]["bank"],
+                         "mha_partial_us": t * 1e6, "tflops": fl / t / 1e12, "frac_of_tensor_peak": fl / t / 1e12 / peak})
+            del q2, kb2, vb2, po2
+        out["3"] = {"workload": "R50 AOT-L + RMem, synthetic 480x864 clip, 1 object, K = 2 / 4 / 8 (bank full, gap 1); "
+                                "mha_partial_kernel = long-term attention, 8 heads x 32 (MUFU-bound: 16 FLOP per exp)",
+                    "rows": rows}
+    if world > 1:
+        dist.barrier()
+    return out
+
+
+def load_peaks():
     peaks = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "src": "fallback"}
     pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(pk):
         with open(pk) as f:
             j = json.load(f)
         peaks = {"hbm_gbs": j["hbm_gbs"], "bf16_tflops": j["bf16_tflops"], "src": "measured"}
+    return peaks
+
+
+def timed_graph(fn, iters=30, reps=4):
+    """Average device duration of one launch: `iters` launches captured in a CUDA graph (so the host's per-launch
+    cost, which exceeds the kernel time for the small kernels, is outside the measurement), CUDA events around
+    the replays on the launching stream."""
+    for i in range(3):
+        fn(i)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            fn(i)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (iters * reps) * 1e-3
+
+
+def kernel_rooflines(dev):
+    """Isolated timings of the two headline kernels at the workload's steady-state shape, CUDA events on
+    the launching stream, inputs rotated through > L2-size copies so no launch re-reads a warm L2."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import _chunks_per_frame, default_sk_clusters
+    peaks = load_peaks()
     # per-launch DRAM traffic and tensor-pipe utilisation of the same kernels from the committed `ncu --set full`
     # capture of `bench.py --kernel-only` (tools/ncu_summary.py -> profiles/ncu_headline.json); never measured here
     ncu = {}
@@ -314,43 +468,39 @@ def kernel_rooflines(dev):
             ncu = json.load(f)
     h, w = H // 16, W // 16
     L, T = h * w, LATTER + 1
-    ncopy, iters = 6, 30
+    ncopy = 6
     mk = lambda *s: torch.randn(*s, device=dev).to(torch.bfloat16)
     qs = [mk(L, 128) for _ in range(ncopy)]
     kbs = [mk(T, L, 128) for _ in range(ncopy)]
     vbs = [mk(T, L, 1024) for _ in range(ncopy)]
-    pos = [torch.empty(T, L, 1024, device=dev) for _ in range(ncopy)]
-    pm, pl = torch.empty(T, L, device=dev), torch.empty(T, L, device=dev)
     order = torch.arange(T, device=dev, dtype=torch.int32)
-
-    def timed(fn):
-        """Average device duration of one launch: `iters` launches captured in a CUDA graph (so the host's
-        per-launch cost, which exceeds the kernel time for the small kernels, is outside the measurement),
-        CUDA events around the replays on the launching stream."""
-        for i in range(3):
-            fn(i % ncopy)
-        torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            for i in range(iters):
-                fn(i % ncopy)
-        g.replay()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 4
-        e0.record()
-        for _ in range(reps):
-            g.replay()
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / (iters * reps) * 1e-3
-
-    t_lt = timed(lambda i: ops.lt_attn_partial(qs[i], kbs[i], vbs[i], order, T, 1, pos[i], pm, pl))
+    bias = torch.randn(L, 4, device=dev)
+    rows = [min(t, 3) for t in range(T)]
+    gate = mk(L, 1024)
+    out = torch.empty(L, 1024, device=dev, dtype=torch.bfloat16)
+    mass = torch.empty(L, T, device=dev)
+    ws = ops.lt_attn_sk_workspace(L, T, dev)
+    t_lt = timed_graph(lambda i: ops.lt_attn_sk_partial(qs[i % ncopy], kbs[i % ncopy], vbs[i % ncopy], order, T, bias,
+                                                        rows, True, ws))
+    t_cmb = timed_graph(lambda i: ops.lt_attn_sk_combine(T, L, gate, out, mass, ws))
+    nclu = default_sk_clusters(dev)
+    ws2 = ops.lt_attn_sk_workspace(L, T, dev, nclu)
+    t_lt_in = timed_graph(lambda i: ops.lt_attn_sk_partial(qs[i % ncopy], kbs[i % ncopy], vbs[i % ncopy], order, T, bias,
+                                                           rows, True, ws2, nclu))
+    cpf = _chunks_per_frame(T, L)
+    po = torch.empty(T * cpf, L, 1024, device=dev)
+    pm, pl = torch.empty(T * cpf, L, device=dev), torch.empty(T * cpf, L, device=dev)
+    t_g1 = timed_graph(lambda i: ops.lt_attn_partial(qs[i % ncopy], kbs[i % ncopy], vbs[i % ncopy], order, T, cpf, po, pm, pl))
     flops = 2.0 * L * (T * L) * (128 + 1024)
     lt = {"bound": "tensor", "achieved": flops / t_lt / 1e12, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
-          "frac": flops / t_lt / 1e12 / peaks["bf16_tflops"], "traffic": None, "kernel": "lt_attn_partial_kernel",
-          "us": t_lt * 1e6, "shape": {"L": L, "T": T}, "peak_src": peaks["src"] + " burst"}
-    k = ncu.get("lt_attn_partial_kernel")
+          "frac": flops / t_lt / 1e12 / peaks["bf16_tflops"], "traffic": None, "kernel": "lt_attn_sk_kernel",
+          "us": t_lt * 1e6, "shape": {"L": L, "T": T}, "peak_src": peaks["src"] + " burst",
+          "algorithmic_flops": flops, "combine_us": t_cmb * 1e6,
+          "in_frame": {"n_clusters": nclu, "us": t_lt_in * 1e6,
+                       "note": "inside the frame graph the kernel is capped to this many 2-CTA clusters so that the "
+                               "short-term branch and the next frame's encoder find free SMs"},
+          "first_generation_us": t_g1 * 1e6}
+    k = ncu.get("lt_attn_sk_kernel")
     if k:
         lt["traffic"] = k.get("dram_traffic_bytes")
         lt["algorithmic_bytes"] = 2.0 * (128 * L * (1 + T) + 1024 * L * T)       # bf16 q, K, V read once
@@ -363,7 +513,6 @@ def kernel_rooflines(dev):
     lv, lu = [mk(L, 1024) for _ in range(nb)], [mk(L, 1024) for _ in range(nb)]
     rel = [torch.randn(L, 256, device=dev) * 0.1 for _ in range(nb)]
     outs = [torch.empty(L, 1024, device=dev, dtype=torch.bfloat16) for _ in range(nb)]
-
     banded = [ops.local_banded_buffer(h, w, dev) for _ in range(nb)]
 
     def local(i):                    # the path the engines run by default: scores kernel + aggregation kernel
@@ -375,9 +524,8 @@ def kernel_rooflines(dev):
         i = i % nb
         ops.local_attn(lq[i], lk[i], lv[i], rel[i], lu[i], outs[i], h, w)
 
-    ncopy = nb
-    t_loc = timed(local)
-    t_loc_fused = timed(local_fused)
+    t_loc = timed_graph(local)
+    t_loc_fused = timed_graph(local_fused)
     bytes_alg = 2.0 * (2 * 128 * L + 3 * 1024 * L) + 4.0 * (225 * 128 + 225)
     loc = {"bound": "hbm", "achieved": bytes_alg / t_loc / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
            "frac": bytes_alg / t_loc / 1e9 / peaks["hbm_gbs"], "traffic": None,
@@ -392,32 +540,49 @@ def kernel_rooflines(dev):
     return lt, loc
 
 
-def cpu_port_fps(n_frames, seed=1000):
-    """The oracle (CPU restatement of the reference algorithm) on the host cores, same workload."""
+def cpu_port_fps(n_frames, seed=1000, device="cpu", autocast=None):
+    """The oracle (restatement of the reference algorithm in PyTorch eager) on the host cores -- or, with
+    device="cuda", on the GPU: the reference algorithm as PyTorch eager kernels, the number the hand-written path
+    has to beat.  Same workload as the headline."""
     from oracle import restate as R
     model = build_model()
-    sd = {k: v.clone() for k, v in model.state_dict().items()}
-    torch.set_num_threads(os.cpu_count() or 1)
+    sd = {k: v.clone().to(device) for k, v in model.state_dict().items()}
+    if device == "cpu":
+        torch.set_num_threads(os.cpu_count() or 1)
     imgs, lab = make_clip(1 + n_frames, seed)
+    imgs, lab = [im.to(device) for im in imgs], lab.to(device)
     eng = R.Engine(sd, True, 1, LATTER, long_term_mem_gap=gap_rule(100))
-    with torch.no_grad():
+    sync = (lambda: torch.cuda.synchronize()) if device != "cpu" else (lambda: None)
+    import contextlib
+    ctx = torch.autocast("cuda", dtype=autocast) if autocast is not None else contextlib.nullcontext()
+    with torch.no_grad(), ctx:
         eng.add_reference_frame(imgs[0], lab, obj_nums=[10], frame_step=0)
+        sync()
         t0 = time.perf_counter()
         for f in range(1, 1 + n_frames):
             logit = eng.match_propogate_one_frame(imgs[f], output_size=(H, W))
             label = torch.argmax(logit, dim=1, keepdim=True).float()
             eng.update_short_term_memory(F.interpolate(label, size=(H, W), mode="nearest"))
+        sync()
         dt = time.perf_counter() - t0
     return n_frames / dt, torch.get_num_threads()
+
+
+PORT_NOTE = ("oracle/restate.py: the reference's algorithm without its debug work (topk(32) + .cpu().numpy() copies, "
+             "transformer.py:644-648, prints, the F.unfold temporary): faster than the unmodified reference, so "
+             "ratios against it are conservative")
 
 
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
+    prefill = gap_rule(100) * LATTER
     config = {"workload": "R50 DeAOT-L + RMem, synthetic 480x864 clip, 5 objects (1 engine), bank 1+4, gap 5, "
-                          "1 sequence per GPU", "frames_per_clip": 1 + args.warmup + args.steps,
-              "L_tokens": (H // 16) * (W // 16), "sequences_per_gpu": 1,
+                          "1 sequence per GPU; fp16 cuDNN backbone, bf16 kernels on the path; timed at steady state "
+                          "(bank filled during %d untimed frames)" % prefill,
+              "frames_per_clip": 1 + prefill + args.warmup + args.steps,
+              "L_tokens": (H // 16) * (W // 16), "sequences_per_gpu": 1, "encoder_dtype": "fp16",
               "l2": "no explicit flush: every step reads a distinct frame and streams backbone activations + a "
                     "3-layer bank (> 126 MB per step); isolated kernel timings rotate > L2-size input copies"}
 
@@ -434,7 +599,7 @@ def main():
                 "steps": n, "warmup": min(args.warmup, 2), "ms_per_step": 1e3 / fps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                                 "sample": "%d frames of the same 480x864 5-object clip" % n},
+                                 "sample": "%d frames of the same 480x864 5-object clip" % n, "note": PORT_NOTE},
                 "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return 0
@@ -442,10 +607,11 @@ def main():
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py (impl b200) needs a CUDA device: there is no CPU fallback")
     import torch.distributed as dist
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    cores_per_rank = pin_rank_to_cores(local_rank, world)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl")
-    local_rank = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     torch.backends.cudnn.benchmark = True
@@ -457,7 +623,10 @@ def main():
         if rank == 0:
             print(json.dumps({"roofline": lt, "roofline_local": loc}))
         return 0
-    res = run_b200(args, rank, world)
+    extra = not args.no_extra_legs
+    modes = ("device", "e2e") + (("stock", "e2e_u8") if extra else ())
+    res = run_b200(args, rank, world, modes)
+    legs = config_legs(args, rank, world, local_rank) if extra else None
     if rank == 0:
         sec = res["device"]["ms_max"] * 1e-3
         sec_e2e = res["e2e"]["ms_max"] * 1e-3
@@ -467,20 +636,48 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic", "config": config, "clocks": res["device"]["clocks"],
                 "e2e": {"value": total_frames / sec_e2e, "unit": "frames/s",
-                        "h2d_bytes_per_step": 3 * H * W * 4, "d2h_bytes_per_step": H * W},
+                        "h2d_bytes_per_step": res["e2e"]["h2d"], "d2h_bytes_per_step": H * W,
+                        "ms_per_rank": res["e2e"]["ms_per_rank"]},
                 "gpu_launches": res["device"]["launches"],
+                "T_during_timed": res["device"]["T"],
+                "ms_per_rank": res["device"]["ms_per_rank"], "host_cores_per_rank": cores_per_rank,
                 "host_enqueue_ms_per_step": res["device"]["host_ms"] / args.steps, "roofline": lt,
                 "roofline_local": loc,
                 "bank_indexes": res["device"]["idx"]}
-        if world == 1 and args.seqs_per_gpu > 1:
+        if extra:
+            line["stock_api"] = {"value": total_frames / (res["stock"]["ms_max"] * 1e-3), "unit": "frames/s",
+                                 "note": "match_propogate_one_frame(img, output_size=) with the reference's exact "
+                                         "signature (no next_img=): the encoder of frame f+1 cannot start before "
+                                         "frame f returns"}
+            line["e2e_u8"] = {"value": total_frames / (res["e2e_u8"]["ms_max"] * 1e-3), "unit": "frames/s",
+                              "h2d_bytes_per_step": res["e2e_u8"]["h2d"], "d2h_bytes_per_step": H * W,
+                              "ms_per_rank": res["e2e_u8"]["ms_per_rank"],
+                              "note": "decoded u8 frames [H, W, 3] uploaded (a quarter of the f32 bytes), the "
+                                      "dataloader's normalisation runs inside the packing kernel"}
+            line["configs"] = legs
+        if world == 1 and args.seqs_per_gpu > 1 and extra:
+            spec = dict(H=H, W=W, n_obj=N_OBJ, gap=gap_rule(100))
+            ms, _ = run_sequences(build_model(), local_rank, list(range(args.seqs_per_gpu)), spec, args.steps,
+                                  prefill + args.warmup)
             line["multi_sequence"] = {"sequences_per_gpu": args.seqs_per_gpu, "unit": "frames/s",
-                                      "value": run_multi_sequence(args, local_rank, args.seqs_per_gpu),
+                                      "value": args.seqs_per_gpu * args.steps / (ms * 1e-3),
                                       "note": "same workload, S independent clips interleaved on S streams "
-                                              "(configs 3 / 4 shard 2 sequences per GPU); not the headline"}
+                                              "(configs 4 / 5 shard 2 sequences per GPU); not the headline"}
+        if world == 1 and extra:
+            try:
+                f32, _ = cpu_port_fps(10, device="cuda")
+                b16, _ = cpu_port_fps(10, device="cuda", autocast=torch.bfloat16)
+                line["gpu_eager_port"] = {"fp32": f32, "bf16_autocast": b16, "unit": "frames/s",
+                                          "sample": "10 frames of the same clip, oracle/restate.py on cuda:0 in PyTorch "
+                                                    "eager (the reference itself cannot travel to the GPU box)",
+                                          "note": PORT_NOTE}
+            except Exception as e:       # a reported comparison, never a reason to lose the bench line
+                line["gpu_eager_port"] = {"error": repr(e)[:200]}
         if world == 1 and not args.no_cpu_baseline:
             fps, cores = cpu_port_fps(12)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                                    "sample": "12 frames of the same 480x864 5-object clip (oracle/restate.py)"}
+                                    "sample": "12 frames of the same 480x864 5-object clip (oracle/restate.py)",
+                                    "note": PORT_NOTE}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

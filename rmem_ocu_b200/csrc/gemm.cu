@@ -56,7 +56,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   uint64_t* acc_full = bars + 2 * kGStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kGStages + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index made warp-uniform (shuffle from lane 0): the MMA warp below then keeps its descriptors in uniform
+  // registers and each tcgen05.mma is ONE instruction -- inside an `if (lane == 0)` region the compiler wraps every
+  // MMA in an ELECT / R2UR.BROADCAST loop (~90 cycles per MMA, measured on the attention kernel)
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * kGM, n0 = blockIdx.x * BN;
   const int kb = (p.K + kGK - 1) / kGK;
 
@@ -79,7 +82,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -93,23 +96,26 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_16(kGM, BN, 0, 0, p.ab_f16);
-      for (int k = 0; k < kb; ++k) {
-        const int st = k % kGStages;
-        mbar_wait(full + st, (k / kGStages) & 1);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + st * Cfg::kStageBytes);
-        const uint32_t b_addr = a_addr + kGABytes;
+    // the whole warp runs the loop (and the waits); one elected lane issues
+    const uint32_t idesc = make_idesc_16(kGM, BN, 0, 0, p.ab_f16);
+    const uint64_t a_desc0 = make_desc_sw128(smem_u32(smem), 16, 1024);
+    for (int k = 0; k < kb; ++k) {
+      const int st = k % kGStages;
+      mbar_wait(full + st, (k / kGStages) & 1);
+      tc_fence_after();
+      const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((st * Cfg::kStageBytes) >> 4);
+      const uint64_t b_desc = a_desc + static_cast<uint64_t>(kGABytes >> 4);
+      if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < kGK / 16; ++ks) {
-          mma_bf16_ss(tmem_base, make_desc_sw128(a_addr + ks * 32, 16, 1024),
-                      make_desc_sw128(b_addr + ks * 32, 16, 1024), idesc, (k > 0) || (ks > 0));
-        }
+        for (int ks = 0; ks < kGK / 16; ++ks)
+          mma_bf16_ss(tmem_base, a_desc + static_cast<uint64_t>((ks * 32) >> 4),
+                      b_desc + static_cast<uint64_t>((ks * 32) >> 4), idesc, (k > 0) || (ks > 0));
         tc_commit(empty + st);
       }
-      tc_commit(acc_full);
+      __syncwarp();
     }
+    if (elect_one()) tc_commit(acc_full);
+    __syncwarp();
   } else {
     // ---------------------------------------------------------------- epilogue (8 warps)
     // Warp (quarter, half) owns TMEM lanes [32 quarter, +32) = 32 output rows and half of the tile's columns.

@@ -65,7 +65,7 @@ local_scores_kernel(const __grid_constant__ CUtensorMap tm_k, const __nv_bfloat1
   float* sS = reinterpret_cast<float*>(sK + kSSmemK);
   uint64_t* bar = reinterpret_cast<uint64_t*>(sS + 16 * kSLd);
   const int x0 = blockIdx.x * kSTileW, y0 = blockIdx.y * kSTileH;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_k);
     mbar_init(bar, 1);
@@ -250,7 +250,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -264,14 +264,16 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, kADV, 0, 1);
-      for (int b = 0; b < kABlocks; ++b) {
-        const int st = b % kAStages;
-        mbar_wait(full + st, (b / kAStages) & 1);
-        tc_fence_after();
-        const uint32_t p_addr = smem_u32(smem + st * kAStageBytes);
-        const uint32_t v_addr = p_addr + kAPBytes;
+    // whole warp in the loop, one elected lane issues (warp-uniform operands stay in uniform registers: one
+    // instruction per tcgen05.mma instead of an ELECT / R2UR.BROADCAST loop)
+    constexpr uint32_t idesc = make_idesc_bf16(128, kADV, 0, 1);
+    for (int b = 0; b < kABlocks; ++b) {
+      const int st = b % kAStages;
+      mbar_wait(full + st, (b / kAStages) & 1);
+      tc_fence_after();
+      const uint32_t p_addr = smem_u32(smem + st * kAStageBytes);
+      const uint32_t v_addr = p_addr + kAPBytes;
+      if (elect_one()) {
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
           mma_bf16_ss(tmem_base, make_desc_sw128(p_addr + ks * 32, 16, 1024),
@@ -279,8 +281,10 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
         }
         tc_commit(empty + st);
       }
-      tc_commit(o_full);
+      __syncwarp();
     }
+    if (elect_one()) tc_commit(o_full);
+    __syncwarp();
   } else {
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;

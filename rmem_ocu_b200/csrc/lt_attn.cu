@@ -85,7 +85,8 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   uint64_t* o_full = bars + 15;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
-  const int warp = threadIdx.x >> 5;
+  // warp-uniform warp index (shuffle from lane 0), so that the MMA warp's operands live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int q_tile = blockIdx.x;
   const int dv_split = blockIdx.y;
@@ -125,7 +126,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -146,7 +147,10 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && n_tiles > 0) {
+    // The whole warp runs the loop and the waits; one elected lane issues.  (Inside an `if (lane == 0)` region the
+    // compiler has to assume per-thread operands and wraps every tcgen05.mma in an ELECT / R2UR.BROADCAST loop,
+    // ~90 cycles per MMA.)
+    if (n_tiles > 0) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(kBlockM, kBlockN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockM, kDVTile, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
@@ -156,15 +160,18 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + st * kKBytes);
         const uint32_t d = tmem_base + kTmemS0 + (j & 1) * kBlockN;
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < kDK / 16; ++ks) {
-          const uint32_t blk = ks >> 2, within = ks & 3;
-          const uint64_t a = make_desc_sw128(q_addr + blk * (kBlockM * 128) + within * 32, 16, 1024);
-          const uint64_t b = make_desc_sw128(k_addr + blk * (kBlockN * 128) + within * 32, 16, 1024);
-          mma_bf16_ss(d, a, b, idesc_qk, ks > 0);
+          for (int ks = 0; ks < kDK / 16; ++ks) {
+            const uint32_t blk = ks >> 2, within = ks & 3;
+            const uint64_t a = make_desc_sw128(q_addr + blk * (kBlockM * 128) + within * 32, 16, 1024);
+            const uint64_t b = make_desc_sw128(k_addr + blk * (kBlockN * 128) + within * 32, 16, 1024);
+            mma_bf16_ss(d, a, b, idesc_qk, ks > 0);
+          }
+          tc_commit(k_empty + st);
+          tc_commit(s_full + (j & 1));
         }
-        tc_commit(k_empty + st);
-        tc_commit(s_full + (j & 1));
+        __syncwarp();
       };
       mbar_wait(q_full, 0);
       issue_qk(0);
@@ -179,15 +186,19 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         const uint32_t v_addr = smem_u32(sV + st * kVBytes);
         const uint32_t p_tmem = tmem_base + kTmemS0 + (j & 1) * kBlockN;   // bf16 P: 64 columns
         const uint32_t d = tmem_base + kTmemO;
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < kBlockN / 16; ++ks) {
-          const uint64_t b = make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024);
-          mma_bf16_ts(d, p_tmem + ks * 8, b, idesc_pv, (j > 0) || (ks > 0));
+          for (int ks = 0; ks < kBlockN / 16; ++ks) {
+            const uint64_t b = make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024);
+            mma_bf16_ts(d, p_tmem + ks * 8, b, idesc_pv, (j > 0) || (ks > 0));
+          }
+          tc_commit(v_empty + st);
+          tc_commit(pv_done + (j & 1));
         }
-        tc_commit(v_empty + st);
-        tc_commit(pv_done + (j & 1));
+        __syncwarp();
       }
-      tc_commit(o_full);
+      if (elect_one()) tc_commit(o_full);
+      __syncwarp();
     }
   } else {
     // ------------------------------------------------------------------ softmax + epilogue

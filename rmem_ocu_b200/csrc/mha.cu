@@ -67,7 +67,7 @@ mha_partial_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   uint64_t* o_full = pv_done + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
   const int q_tile = blockIdx.x, pair = blockIdx.y, chunk = blockIdx.z;
 
   const int frame_pos = chunk / p.chunks_per_frame;
@@ -95,7 +95,7 @@ mha_partial_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -114,7 +114,9 @@ mha_partial_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && n_tiles > 0) {
+    // whole warp in the loop, one elected lane issues: warp-uniform operands stay in uniform registers (one
+    // instruction per tcgen05.mma instead of an ELECT / R2UR.BROADCAST loop)
+    if (n_tiles > 0) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(kBlockM, kBlockN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockM, 64, 0, 1);
       const uint32_t q_addr = smem_u32(sQ);
@@ -126,13 +128,16 @@ mha_partial_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const uint32_t d = tmem_base + (h * 2 + (j & 1)) * kBlockN;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < kHeadDim / 16; ++ks) {
-            const uint32_t off = h * 64 + ks * 32;     // head h = bytes [64h, 64h+64) of the 128-byte row
-            mma_bf16_ss(d, make_desc_sw128(q_addr + off, 16, 1024), make_desc_sw128(k_addr + off, 16, 1024),
-                        idesc_qk, ks > 0);
+            for (int ks = 0; ks < kHeadDim / 16; ++ks) {
+              const uint32_t off = h * 64 + ks * 32;     // head h = bytes [64h, 64h+64) of the 128-byte row
+              mma_bf16_ss(d, make_desc_sw128(q_addr + off, 16, 1024), make_desc_sw128(k_addr + off, 16, 1024),
+                          idesc_qk, ks > 0);
+            }
+            tc_commit(s_full + h * 2 + (j & 1));
           }
-          tc_commit(s_full + h * 2 + (j & 1));
+          __syncwarp();
         }
       };
       mbar_wait(q_full, 0);
@@ -147,15 +152,20 @@ mha_partial_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
           tc_fence_after();
           const uint32_t p_tmem = tmem_base + (h * 2 + (j & 1)) * kBlockN;   // bf16 P: 32 columns
           const uint32_t d = tmem_base + kTmemO + h * 64;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < kBlockN / 16; ++ks)
-            mma_bf16_ts(d, p_tmem + ks * 8, make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024),
-                        idesc_pv, (j > 0) || (ks > 0));
-          tc_commit(pv_done + h * 2 + (j & 1));
+            for (int ks = 0; ks < kBlockN / 16; ++ks)
+              mma_bf16_ts(d, p_tmem + ks * 8, make_desc_sw128(v_addr + ks * (16 * 128), kBlockN * 128, 1024),
+                          idesc_pv, (j > 0) || (ks > 0));
+            tc_commit(pv_done + h * 2 + (j & 1));
+          }
+          __syncwarp();
         }
-        tc_commit(kv_empty + st);
+        if (elect_one()) tc_commit(kv_empty + st);
+        __syncwarp();
       }
-      tc_commit(o_full);
+      if (elect_one()) tc_commit(o_full);
+      __syncwarp();
     }
   } else {
     // ------------------------------------------------------------------ softmax + epilogue

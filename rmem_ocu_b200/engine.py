@@ -460,6 +460,14 @@ class _Workspace:
         self.pred_logits = None                               # [1, 11, H/4, W/4] f32, allocated on first decode
 
 
+def default_sk_clusters(device):
+    """2-CTA clusters the stream-K long-term attention may occupy inside the frame graph: ~3/8 of the SM pairs
+    (56 on a 148-SM B200; measured 48 / 52 / 56 / 60 / 64 / 68 / all: 56 is the maximum of frames/s) -- the
+    short-term branch and the next frame's encoder run beside it and need SMs of their own."""
+    n_sms = torch.cuda.get_device_properties(device).multi_processor_count
+    return max(1, int(0.38 * n_sms + 0.5))
+
+
 def _chunks_per_frame(T, L, n_sms=148):
     """Split-KV granularity of the long-term attention grid (q tiles x 4 value splits x T x cpf CTAs, one
     CTA per SM): the cpf in 1..4 that minimises waves x key tiles per chunk."""
@@ -522,7 +530,9 @@ class DeAOTEngine:
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
         # long-term attention finds free SMs
-        self.lt_sk_clusters = int(os.environ.get("RMEM_LT_SK_CLUSTERS", "0"))
+        self.lt_sk_clusters = int(os.environ.get("RMEM_LT_SK_CLUSTERS", "-1"))
+        if self.lt_sk_clusters < 0:
+            self.lt_sk_clusters = default_sk_clusters(self.device) if self.fork_branches else 0
         self._side = None
         # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
         # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
@@ -580,6 +590,7 @@ class DeAOTEngine:
         self.T_recorded = 0        # bank length when record_attn_weight was last written
         self._pending_w = None     # (T, update_long, do_evict, st) of a deferred write path
         self._prefetching = False  # the last propagated frame started the next frame's encoder
+        self._img_sig = None       # (dtype, shape) of the sequence's frames, fixed by the reference frame
         self.n_long_updates = 0
 
     @_on_device
@@ -990,7 +1001,12 @@ class DeAOTEngine:
         if not self.use_cuda_graphs or self.frame_step < 1:
             return 0
         H, W = self.input_size_2d
-        img = torch.zeros(1, 3, H, W, device=self.device)
+        # the encoder graphs are recorded for the frame format this sequence uses (normalised f32 planes
+        # [1, 3, H, W] or decoded u8 pixels [1, H, W, 3]); one format per sequence
+        if self._img_sig is not None and self._img_sig[0] == torch.uint8:
+            img = torch.zeros(1, H, W, 3, device=self.device, dtype=torch.uint8)
+        else:
+            img = torch.zeros(1, 3, H, W, device=self.device)
         label = torch.zeros(H, W, device=self.device)
         saved = dict(self._graphs)
         self._wait_write()
@@ -1051,6 +1067,8 @@ class DeAOTEngine:
             raise ValueError("No image for reference frame!")
         if mask is None:
             raise ValueError("No mask for reference frame!")
+        if img is not None:
+            self._img_sig = (img.dtype, tuple(img.shape))
         curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
         label = self._label_map(mask.to(self.device)).float()
         if self.input_size_2d is None:
@@ -1076,6 +1094,9 @@ class DeAOTEngine:
         ``next_img`` (optional, not in the reference): the frame that will be passed to the NEXT call.  Its
         encoder pass starts now on a second stream and overlaps this frame's LSTT + decoder (the encoder depends
         on nothing but the image); the next call must then be given that same frame."""
+        if img is not None and self._img_sig is not None and (img.dtype, tuple(img.shape)) != self._img_sig:
+            raise _lib.RmemError("frames of one sequence must share the reference frame's dtype and shape: got %s %s, "
+                                 "the sequence started with %s %s" % (img.dtype, tuple(img.shape), *self._img_sig))
         self.frame_step += 1
         T = self.T
         self.T_recorded = T
