@@ -1,5 +1,6 @@
 """End-to-end parity of the drop-in engine (CUDA path) against the oracle engine (CPU fp32
 restatement of the reference) on the same seeded synthetic clip and the same deterministic weights."""
+import numpy as np
 import pytest
 import torch
 import torch.nn.functional as F
@@ -378,3 +379,32 @@ def test_engine_on_second_device_of_one_process(lib_built):
         outs.append((masks, eng.aot_engines[0].long_memories_indexes))
     assert outs[0][1] == outs[1][1]
     assert min((a == b).float().mean().item() for a, b in zip(outs[0][0], outs[1][0])) >= 0.999
+
+
+def test_evaluator_loop_vs_oracle(lib_built, tmp_path):
+    """rmem_ocu_b200.evaluation.evaluate_sequence (the shape of Evaluator.evaluating, evaluator.py:318-568) at the
+    evaluator's own input size (MultiRestrictSize: 240x432 -> 241x433, an odd token grid) against the oracle's
+    run_clip: bank equal, masks >= 99.9 %, palette PNGs on disk that read back as the masks."""
+    from PIL import Image
+    from oracle import restate as R
+    from rmem_ocu_b200 import evaluation as E
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    H, W = E.restrict_size(240, 432)
+    assert (H, W) == (241, 433)
+    n, latter = 8, 2
+    m, sd = _models(latter)
+    imgs, lab = _clip(H, W, n, 3, seed=77)
+    o = R.Engine(sd, True, 1, latter, long_term_mem_gap=E.memory_gap(n))
+    o_masks = R.run_clip(o, imgs, lab, 10)
+    eng = DeAOTInferEngine(m, 0)
+    with torch.no_grad():
+        masks = E.evaluate_sequence(eng, imgs, lab.float(), 3, result_dir=str(tmp_path), obj_idx=[0, 5, 9, 30])
+    assert eng.long_term_mem_gap == 5
+    assert eng.aot_engines[0].long_memories_indexes == o.long_memories_indexes
+    agree = [(a == b).float().mean().item() for a, b in zip(masks, o_masks)]
+    print("evaluator-loop mask agreement", [round(a, 5) for a in agree])
+    assert min(agree) >= 0.999, agree
+    png = np.array(Image.open(str(tmp_path / "00003.png")))
+    want = masks[2].numpy()
+    lut = np.array([0, 5, 9, 30] + [0] * 252, np.uint8)              # squeeze_idx: dense ids -> dataset labels
+    assert png.shape == (H, W) and np.array_equal(png, lut[want])
