@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 4
+#define RMEM_ABI_VERSION 5
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -77,6 +77,10 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
  * temporal-PE bias is added to the scores inside the kernel, so the combine step needs neither it nor T-many
  * per-frame partials.  Results equal the first generation's to bf16 rounding.
  *
+ *   S           independent sequences in one launch (grid dimension): q [S][L][128], kbank [S][n_slots][L][128], vbank
+ *               [S][n_slots][L][1024], tpe_bias [S][L][4], gate / out [S][L][1024], attn_mass [S][L][T]; `order` of
+ *               sequence s starts at order + s * order_stride (e.g. RMEM_BANK_STATE_WORDS when the bank states are
+ *               stacked); all sequences share T and the temporal rows.  S = 1 is the single-sequence call.
  *   n_clusters  0: one 2-CTA cluster per SM pair (the kernel then owns every SM while it runs); k > 0: at most k
  *               clusters, which leaves SMs to kernels running on other streams.  The three calls of one attention
  *               must be given the same value.
@@ -87,11 +91,12 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
  *   record      != 0: also write the per-(segment, frame) sums that attn_mass is built from
  *   gate / out  bf16 [L][1024];  attn_mass f32 [L][T] or NULL (needs record != 0 in the partial call)
  */
-int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int n_clusters);
-int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order, int T,
-                                  int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host,
-                                  int record, int n_clusters, void* workspace, int64_t workspace_bytes, void* stream);
-int rmem_lt_attn_deaot_sk_combine(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int S, int n_clusters);
+int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order,
+                                  int order_stride, int T, int L, int n_slots, int S, const float* tpe_bias,
+                                  const int32_t* tpe_rows_host, int record, int n_clusters, void* workspace,
+                                  int64_t workspace_bytes, void* stream);
+int rmem_lt_attn_deaot_sk_combine(int T, int L, int S, const void* gate, void* out, float* attn_mass, int n_clusters,
                                   const void* workspace, int64_t workspace_bytes, void* stream);
 
 
@@ -261,6 +266,28 @@ int rmem_local_attn_aggregate(const void* banded, const void* v, const void* gat
  * This is what the engines call; the two-stage form above remains for callers that want local_attn itself. */
 int rmem_local_attn(const void* q, const void* k, const void* v, const float* rel_bias, int ld_rel,
                     const void* gate, void* out, int h, int w, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Sequence-batched forms: S independent video sequences of the same frame size step in lock-step and share every
+ * launch (the reference asserts batch size 1 on this path, transformer.py:641; one sequence is 1620 tokens -- a
+ * fraction of a wave on 148 SMs -- so independent sequences are what fills the chip).  Each tensor of the
+ * single-sequence call becomes a contiguous stack [S][...] of the same layout; the sequence is a grid dimension.
+ * rmem_linear, rmem_layernorm, rmem_tpe_prepare are row-wise and take the stack as M = S * L rows unchanged.
+ *   rmem_dwconv5_batched               x, y: [S * h * w][ld] rows
+ *   rmem_groupnorm_tokens_batched      statistics per sequence; workspace: S consecutive (16 * groups + 8)-byte blocks
+ *   rmem_local_attn_scores_batched     q, k [S][h*w][128]; rel_bias [S][h*w][ld_rel]; probs [S][h*w][225]; banded
+ *                                      [S][rmem_local_banded_elems(h, w)]
+ *   rmem_local_attn_aggregate_batched  v, gate, out [S][h*w][1024]
+ */
+int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
+                         int C, int S, void* stream);
+int rmem_groupnorm_tokens_batched(const float* x_a, int Ca, const float* x_b, const float* gamma, const float* beta,
+                                  void* out, int out_f32, int L, int C, int groups, int S, void* workspace,
+                                  void* stream);
+int rmem_local_attn_scores_batched(const void* q, const void* k, const float* rel_bias, int ld_rel, float* probs,
+                                   void* banded, int h, int w, int S, void* stream);
+int rmem_local_attn_aggregate_batched(const void* banded, const void* v, const void* gate, void* out, int h, int w,
+                                      int S, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Restricted long-term bank.  State lives on the device so the frame loop never synchronises:

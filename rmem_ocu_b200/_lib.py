@@ -62,11 +62,16 @@ _SIGNATURES = {
     "rmem_last_error": [],
     "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
-    "rmem_lt_attn_deaot_sk_workspace_bytes": [_c_int, _c_int, _c_int],
-    "rmem_lt_attn_deaot_sk_partial": [_c_void_p] * 4 + [_c_int] * 3 + [_c_void_p, _c_void_p, _c_int, _c_int, _c_void_p,
+    "rmem_lt_attn_deaot_sk_workspace_bytes": [_c_int, _c_int, _c_int, _c_int],
+    "rmem_lt_attn_deaot_sk_partial": [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p, _c_void_p, _c_int, _c_int, _c_void_p,
                                                                      ctypes.c_int64, _c_void_p],
-    "rmem_lt_attn_deaot_sk_combine": [_c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p,
+    "rmem_lt_attn_deaot_sk_combine": [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p,
                                       ctypes.c_int64, _c_void_p],
+    "rmem_dwconv5_batched": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int,
+                             _c_int, _c_int, _c_void_p],
+    "rmem_groupnorm_tokens_batched": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p] * 2,
+    "rmem_local_attn_scores_batched": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_void_p],
+    "rmem_local_attn_aggregate_batched": [_c_void_p] * 4 + [_c_int, _c_int, _c_int, _c_void_p],
     "rmem_mha_partial": [_c_void_p, _c_int, _c_void_p, _c_int, ctypes.c_int64, _c_void_p, _c_int, ctypes.c_int64,
                          _c_void_p] + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_mha_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p],
@@ -116,7 +121,7 @@ class GemmSegment(ctypes.Structure):
                 ("dst_col0", ctypes.c_int32)]
 
 
-ABI_VERSION = 4          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
+ABI_VERSION = 5          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
 MAX_BANK = 16
 MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8

@@ -78,18 +78,36 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
 
 #define ST(s) static_cast<cudaStream_t>(s)
 
-int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int n_clusters) {
-  return lt_attn_sk_workspace_bytes(L, T, n_clusters);
+int64_t rmem_lt_attn_deaot_sk_workspace_bytes(int L, int T, int S, int n_clusters) {
+  return lt_attn_sk_workspace_bytes(L, T, S, n_clusters);
 }
-int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order, int T,
-                                  int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host,
-                                  int record, int n_clusters, void* workspace, int64_t workspace_bytes, void* stream) {
-  return lt_attn_sk_partial_launch(q, kbank, vbank, order, T, L, n_slots, tpe_bias, tpe_rows_host, record, n_clusters,
-                                   workspace, workspace_bytes, ST(stream));
+int rmem_lt_attn_deaot_sk_partial(const void* q, const void* kbank, const void* vbank, const int32_t* order,
+                                  int order_stride, int T, int L, int n_slots, int S, const float* tpe_bias,
+                                  const int32_t* tpe_rows_host, int record, int n_clusters, void* workspace,
+                                  int64_t workspace_bytes, void* stream) {
+  return lt_attn_sk_partial_launch(q, kbank, vbank, order, order_stride, T, L, n_slots, S, tpe_bias, tpe_rows_host,
+                                   record, n_clusters, workspace, workspace_bytes, ST(stream));
 }
-int rmem_lt_attn_deaot_sk_combine(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+int rmem_lt_attn_deaot_sk_combine(int T, int L, int S, const void* gate, void* out, float* attn_mass, int n_clusters,
                                   const void* workspace, int64_t workspace_bytes, void* stream) {
-  return lt_attn_sk_combine_launch(T, L, gate, out, attn_mass, n_clusters, workspace, workspace_bytes, ST(stream));
+  return lt_attn_sk_combine_launch(T, L, S, gate, out, attn_mass, n_clusters, workspace, workspace_bytes, ST(stream));
+}
+int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
+                         int C, int S, void* stream) {
+  return dwconv5_batched_launch(x, ldx, xcol0, wt, y, ldy, ycol0, h, w, C, S, ST(stream));
+}
+int rmem_groupnorm_tokens_batched(const float* x_a, int Ca, const float* x_b, const float* gamma, const float* beta,
+                                  void* out, int out_f32, int L, int C, int groups, int S, void* workspace,
+                                  void* stream) {
+  return groupnorm_tokens_batched_launch(x_a, Ca, x_b, gamma, beta, out, out_f32, L, C, groups, S, workspace, ST(stream));
+}
+int rmem_local_attn_scores_batched(const void* q, const void* k, const float* rel_bias, int ld_rel, float* probs,
+                                   void* banded, int h, int w, int S, void* stream) {
+  return local_scores_batched_launch(q, k, rel_bias, ld_rel, probs, banded, h, w, S, ST(stream));
+}
+int rmem_local_attn_aggregate_batched(const void* banded, const void* v, const void* gate, void* out, int h, int w,
+                                      int S, void* stream) {
+  return local_aggregate_batched_launch(banded, v, gate, out, h, w, S, ST(stream));
 }
 
 int rmem_mha_partial(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride,

@@ -110,6 +110,8 @@ __device__ __forceinline__ void fma2(float2& d, const float2 a, const float2 b) 
 __global__ void __launch_bounds__(kDwThreads)
 dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict__ wt,
                __nv_bfloat16* __restrict__ y, int ldy, int ycol0, int h, int w, int C, int box_w) {
+  // blockIdx.z = sequence of a batch of independent token grids stacked as [S][h*w] rows
+  y += static_cast<size_t>(blockIdx.z) * h * w * ldy;
   extern __shared__ __align__(128) uint8_t dw_smem[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(dw_smem);
   const uint8_t* tile = dw_smem + 128;                         // [kDwRows + 4][box_w][64 ch] bf16
@@ -120,7 +122,7 @@ dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict
     sm100::mbar_init(bar, 1);
     sm100::mbar_fence_init();
     sm100::mbar_expect_tx(bar, static_cast<uint32_t>((kDwRows + 4) * box_w * kDwCh * 2));
-    sm100::tma_load_3d(dw_smem + 128, &tm_x, bar, c0, -2, y0 - 2);
+    sm100::tma_load_4d(dw_smem + 128, &tm_x, bar, c0, -2, y0 - 2, static_cast<int>(blockIdx.z));
   }
   const int cp = threadIdx.x & 31;              // channel pair inside the CTA's 64 channels
   const int grp = threadIdx.x >> 5;             // column group
@@ -172,19 +174,27 @@ dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict
 
 int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
                    int h, int w, int C, cudaStream_t stream) {
-  if ((C % kDwCh) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1 || w + 4 > 256)
+  return dwconv5_batched_launch(x, ldx, xcol0, wt, y, ldy, ycol0, h, w, C, 1, stream);
+}
+
+int dwconv5_batched_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                           int h, int w, int C, int S, cudaStream_t stream) {
+  if ((C % kDwCh) || (ldx % 8) || (ldy % 8) || (xcol0 % 8) || (ycol0 % 8) || h < 1 || w < 1 || w + 4 > 256 || S < 1 ||
+      S > 65535)
     return set_error(RMEM_ERR_ARG, "dwconv5: C must be a multiple of 64, ld / col offsets multiples of 8, w <= 252");
   auto fn = get_tensor_map_encoder();
   if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
   const int box_w = w + 4;
   CUtensorMap tm_x;
   {
-    const uint64_t dims[3] = {static_cast<uint64_t>(C), static_cast<uint64_t>(w), static_cast<uint64_t>(h)};
-    const uint64_t strides[2] = {static_cast<uint64_t>(ldx) * 2, static_cast<uint64_t>(w) * ldx * 2};
-    const uint32_t box[3] = {kDwCh, static_cast<uint32_t>(box_w), kDwRows + 4};
-    const uint32_t es[3] = {1, 1, 1};
+    const uint64_t dims[4] = {static_cast<uint64_t>(C), static_cast<uint64_t>(w), static_cast<uint64_t>(h),
+                              static_cast<uint64_t>(S)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(ldx) * 2, static_cast<uint64_t>(w) * ldx * 2,
+                                 static_cast<uint64_t>(h) * w * ldx * 2};
+    const uint32_t box[4] = {kDwCh, static_cast<uint32_t>(box_w), kDwRows + 4, 1};
+    const uint32_t es[4] = {1, 1, 1, 1};
     const void* base = static_cast<const __nv_bfloat16*>(x) + xcol0;
-    CUresult r = fn(&tm_x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es,
+    CUresult r = fn(&tm_x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (dwconv5) failed");
@@ -194,7 +204,7 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
   if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(dwconv5_kernel), &optin, static_cast<int>(smem),
                                   "dwconv5: cudaFuncSetAttribute"))
     return r;
-  dim3 grid((h + kDwRows - 1) / kDwRows, C / kDwCh);
+  dim3 grid((h + kDwRows - 1) / kDwRows, C / kDwCh, S);
   dwconv5_kernel<<<grid, kDwThreads, smem, stream>>>(tm_x, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0, h, w,
                                                      C, box_w);
   return check_launch("dwconv5_kernel");
@@ -206,6 +216,10 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int L, int C,
                 int groups, int rows_per_cta, double* __restrict__ ws) {
+  // blockIdx.y = sequence: inputs stacked [S][L] rows, one (2 groups + 1)-double workspace per sequence
+  xa += static_cast<size_t>(blockIdx.y) * L * Ca;
+  if (xb) xb += static_cast<size_t>(blockIdx.y) * L * (C - Ca);
+  ws += static_cast<size_t>(blockIdx.y) * (2 * groups + 1);
   // One CTA per SM, rows_per_cta rows each.  A thread owns four consecutive channels (one float4 per row; Ca, C
   // and C / groups are multiples of 4), so C / 4 threads cover a row and 1024 / C rows are in flight per pass.
   // Every CTA ends in 2 * groups fp64 atomics: ~150 CTAs keep that contention below the cost of the reduction.
@@ -248,6 +262,11 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32, int L, int C, int groups,
                 double* __restrict__ ws) {
+  xa += static_cast<size_t>(blockIdx.y) * L * Ca;
+  if (xb) xb += static_cast<size_t>(blockIdx.y) * L * (C - Ca);
+  ws += static_cast<size_t>(blockIdx.y) * (2 * groups + 1);
+  if (out) out += static_cast<size_t>(blockIdx.y) * L * C;
+  if (out_f32) out_f32 += static_cast<size_t>(blockIdx.y) * L * C;
   // a thread owns four consecutive channels (one float4 in, four bf16 or f32 out); Ca, C and C / groups are
   // multiples of 4
   const int cpg = C / groups;
@@ -283,14 +302,21 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
 int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
                             const float* beta, void* out, int out_f32, int L, int C, int groups,
                             void* workspace, cudaStream_t stream) {
+  return groupnorm_tokens_batched_launch(xa, Ca, xb, gamma, beta, out, out_f32, L, C, groups, 1, workspace, stream);
+}
+
+int groupnorm_tokens_batched_launch(const float* xa, int Ca, const float* xb, const float* gamma,
+                                    const float* beta, void* out, int out_f32, int L, int C, int groups, int S,
+                                    void* workspace, cudaStream_t stream) {
   if (groups < 1 || groups > 8 || C > 1024 || (C % groups) || ((C / groups) % 32) || Ca > C ||
-      (Ca < C && !xb) || (Ca & 3) || (C & 3))
+      (Ca < C && !xb) || (Ca & 3) || (C & 3) || S < 1 || S > 65535)
     return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
-  const int rows = (L + 147) / 148 < 4 ? 4 : (L + 147) / 148;     // one CTA per SM
-  gn_stats_kernel<<<(L + rows - 1) / rows, 256, 0, stream>>>(xa, Ca, xb, L, C, groups, rows,
-                                                              static_cast<double*>(workspace));
+  const int per = (148 + S - 1) / S;                               // CTAs per sequence: about one per SM in total
+  const int rows = (L + per - 1) / per < 4 ? 4 : (L + per - 1) / per;
+  gn_stats_kernel<<<dim3((L + rows - 1) / rows, S), 256, 0, stream>>>(xa, Ca, xb, L, C, groups, rows,
+                                                                      static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
-  gn_apply_kernel<<<296, 256, 0, stream>>>(xa, Ca, xb, gamma, beta,
+  gn_apply_kernel<<<dim3((296 + S - 1) / S, S), 256, 0, stream>>>(xa, Ca, xb, gamma, beta,
                                            out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out),
                                            out_f32 ? static_cast<float*>(out) : nullptr, L, C, groups,
                                            static_cast<double*>(workspace));

@@ -66,12 +66,22 @@ local_scores_kernel(const __grid_constant__ CUtensorMap tm_k, const __nv_bfloat1
   uint64_t* bar = reinterpret_cast<uint64_t*>(sS + 16 * kSLd);
   const int x0 = blockIdx.x * kSTileW, y0 = blockIdx.y * kSTileH;
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
+  {
+    // blockIdx.z = sequence of a batch of independent frames stacked as [S][h*w] rows ([S][elems] banded buffers)
+    const size_t seq = blockIdx.z, L = static_cast<size_t>(h) * w;
+    q += seq * L * 128;
+    rel += seq * L * ld_rel;
+    if (probs) probs += seq * L * kTaps;
+    if (banded)
+      banded += seq * (static_cast<size_t>((h + kATileH - 1) / kATileH) * ((w + kATileW - 1) / kATileW) *
+                       (kABlocks * kABlockElems));
+  }
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_k);
     mbar_init(bar, 1);
     mbar_fence_init();
     mbar_expect_tx(bar, kSSmemK);
-    tma_load_4d(sK, &tm_k, bar, 0, x0 - kMaxDis, y0 - kMaxDis, 0);
+    tma_load_5d(sK, &tm_k, bar, 0, x0 - kMaxDis, y0 - kMaxDis, 0, static_cast<int>(blockIdx.z));
   }
   // query fragments (A operand, row-major 16 x 16 per k-step) straight from global memory while the halo lands
   uint32_t afrag[8][4];
@@ -181,17 +191,23 @@ local_scores_kernel(const __grid_constant__ CUtensorMap tm_k, const __nv_bfloat1
 
 int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
                         int h, int w, cudaStream_t stream) {
-  if (h < 1 || w < 1 || ld_rel < kTaps || (!probs && !banded))
-    return set_error(RMEM_ERR_ARG, "local_scores: bad h / w / ld_rel, or no output");
+  return local_scores_batched_launch(q, k, rel, ld_rel, probs, banded, h, w, 1, stream);
+}
+
+int local_scores_batched_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
+                                int h, int w, int S, cudaStream_t stream) {
+  if (h < 1 || w < 1 || ld_rel < kTaps || (!probs && !banded) || S < 1 || S > 65535)
+    return set_error(RMEM_ERR_ARG, "local_scores: bad h / w / ld_rel / batch, or no output");
   auto fn = get_tensor_map_encoder();
   if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
   CUtensorMap tm_k;
   {
-    const uint64_t dims[4] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 2};
-    const uint64_t strides[3] = {128 * 2, static_cast<uint64_t>(w) * 128 * 2, 128};
-    const uint32_t box[4] = {64, kSHaloW, kSHaloH, 2};
-    const uint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = fn(&tm_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(k), dims, strides, box, es,
+    const uint64_t dims[5] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 2, static_cast<uint64_t>(S)};
+    const uint64_t strides[4] = {128 * 2, static_cast<uint64_t>(w) * 128 * 2, 128,
+                                 static_cast<uint64_t>(h) * w * 128 * 2};
+    const uint32_t box[5] = {64, kSHaloW, kSHaloH, 2, 1};
+    const uint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(&tm_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(k), dims, strides, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (local K) failed");
@@ -200,7 +216,7 @@ int local_scores_launch(const void* q, const void* k, const float* rel, int ld_r
   if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_scores_kernel), &optin, kSSmem,
                                   "local_scores: cudaFuncSetAttribute"))
     return r;
-  dim3 grid((w + kSTileW - 1) / kSTileW, (h + kSTileH - 1) / kSTileH);
+  dim3 grid((w + kSTileW - 1) / kSTileW, (h + kSTileH - 1) / kSTileH, S);
   local_scores_kernel<<<grid, 256, kSSmem, stream>>>(tm_k, static_cast<const __nv_bfloat16*>(q), rel, ld_rel,
                                                      probs, static_cast<__nv_bfloat16*>(banded), h, w);
   return check_launch("local_scores_kernel");
@@ -235,9 +251,12 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
   uint64_t* o_full = bars + 2 * kAStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kAStages + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int x0 = blockIdx.x * kATileW, y0 = blockIdx.y * kATileH, dv = blockIdx.z;
-  const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform
+  constexpr int kDvSlices = 1024 / kADV;
+  // blockIdx.z = (sequence, value slice): a batch of independent frames stacked as [S][h*w] rows
+  const int x0 = blockIdx.x * kATileW, y0 = blockIdx.y * kATileH, dv = blockIdx.z % kDvSlices;
+  const int seq = blockIdx.z / kDvSlices;
+  const int tile = (seq * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_p);
@@ -260,7 +279,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
         uint8_t* dst = smem + st * kAStageBytes;
         mbar_expect_tx(full + st, kAStageBytes);
         tma_load_2d(dst, &tm_p, full + st, 0, (tile * kABlocks + b) * 128);
-        tma_load_4d(dst + kAPBytes, &tm_v, full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, dv * 2);
+        tma_load_5d(dst + kAPBytes, &tm_v, full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, dv * 2, seq);
       }
     }
   } else if (warp == 1) {
@@ -300,7 +319,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
       tmem_ld32(tmem_base + lane_addr + cb * 32, r);      // warp-collective: all lanes, stores guarded below
       tmem_ld_wait();
       if (q_ok) {
-        const size_t off = static_cast<size_t>(gy * p.w + gx) * 1024 + dv * kADV + cb * 32;
+        const size_t off = (static_cast<size_t>(seq) * p.h * p.w + gy * p.w + gx) * 1024 + dv * kADV + cb * 32;
         uint4 g[4];
         if (p.gate) {
 #pragma unroll
@@ -343,23 +362,30 @@ size_t local_banded_elems(int h, int w) {
 
 int local_aggregate_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w,
                            cudaStream_t stream) {
-  if (h < 1 || w < 1 || !banded) return set_error(RMEM_ERR_ARG, "local_aggregate: bad h / w / banded buffer");
+  return local_aggregate_batched_launch(banded, v, gate, out, h, w, 1, stream);
+}
+
+int local_aggregate_batched_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w, int S,
+                                   cudaStream_t stream) {
+  if (h < 1 || w < 1 || !banded || S < 1 || S * (1024 / kADV) > 65535)
+    return set_error(RMEM_ERR_ARG, "local_aggregate: bad h / w / batch / banded buffer");
   auto fn = get_tensor_map_encoder();
   if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
   const int tiles_x = (w + kATileW - 1) / kATileW, tiles_y = (h + kATileH - 1) / kATileH;
   CUtensorMap tm_v, tm_p;
   {
-    const uint64_t dims[4] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 16};
-    const uint64_t strides[3] = {1024 * 2, static_cast<uint64_t>(w) * 1024 * 2, 128};
-    const uint32_t box[4] = {64, kABoxW, 2, kADV / 64};
-    const uint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = fn(&tm_v, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v), dims, strides, box, es,
+    const uint64_t dims[5] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 16, static_cast<uint64_t>(S)};
+    const uint64_t strides[4] = {1024 * 2, static_cast<uint64_t>(w) * 1024 * 2, 128,
+                                 static_cast<uint64_t>(h) * w * 1024 * 2};
+    const uint32_t box[5] = {64, kABoxW, 2, kADV / 64, 1};
+    const uint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(&tm_v, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v), dims, strides, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (local V) failed");
   }
   {
-    const uint64_t dims[2] = {64, static_cast<uint64_t>(tiles_x) * tiles_y * kABlocks * 128};
+    const uint64_t dims[2] = {64, static_cast<uint64_t>(S) * tiles_x * tiles_y * kABlocks * 128};
     const uint64_t strides[1] = {128};
     const uint32_t box[2] = {64, 128};
     const uint32_t es[2] = {1, 1};
@@ -375,7 +401,7 @@ int local_aggregate_launch(const void* banded, const void* v, const void* gate, 
   AggParams p;
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out); p.h = h; p.w = w;
-  dim3 grid(tiles_x, tiles_y, 1024 / kADV);
+  dim3 grid(tiles_x, tiles_y, (1024 / kADV) * S);
   local_aggregate_kernel<<<grid, kAThreads, kASmem, stream>>>(tm_p, tm_v, p);
   return check_launch("local_aggregate_kernel");
 }

@@ -84,6 +84,9 @@ constexpr size_t kPartFWords = static_cast<size_t>(RMEM_MAX_BANK) * kStatRows * 
 
 struct Params {
   int L, T;
+  int S;             // independent sequences batched in this launch (their tensors stacked along a leading dim)
+  int n_qpairs;      // query-tile pairs per sequence
+  int order_stride;  // int32 words between the `order` arrays of consecutive sequences
   int tpf;           // key tiles per frame = ceil(L / 128)
   int P;             // key tiles per (pair, split) = T * tpf
   long long U;       // units = n_pairs * 4 * P
@@ -113,6 +116,14 @@ __device__ __forceinline__ void tma_load_4d_mc(void* dst, const CUtensorMap* m, 
       "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster "
       "[%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(smem_u32(dst)),
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_5d_mc(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                               int c3, int c4, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%3, %4, %5, %6, %7}], [%2], %8;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "h"(mask)
       : "memory");
 }
 // tcgen05.commit arriving on the barrier at this CTA-relative offset in every CTA of `mask`.
@@ -217,28 +228,33 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       int q_pair_loaded = -1;
       int frame_cached = -1, slot = 0;
       for (int i = 0; i < n; ++i) {
-        const int qpair = it.pair >> 2, dv_split = it.pair & 3;
+        const int gq = it.pair >> 2, dv_split = it.pair & 3;     // gq = (sequence, query-tile pair)
+        const int seq = gq / p.n_qpairs, qpair = gq - seq * p.n_qpairs;
         const int st = i & 1;
-        if (qpair != q_pair_loaded) {
+        if (gq != q_pair_loaded) {
           // the queries change: the last QK^T that read the old ones has completed once tile i-1 released its K
           if (i > 0) mbar_wait(k_empty + ((i - 1) & 1), ((i - 1) >> 1) & 1);
           mbar_expect_tx(q_full, kQBytes);
-          tma_load_3d(sQ, &tm_q, q_full, 0, (2 * qpair + static_cast<int>(rank)) * kBlockM, 0);
-          q_pair_loaded = qpair;
+          tma_load_4d(sQ, &tm_q, q_full, 0, (2 * qpair + static_cast<int>(rank)) * kBlockM, 0, seq);
+          q_pair_loaded = gq;
+          frame_cached = -1;
         }
-        if (it.frame_pos != frame_cached) { slot = p.order[it.frame_pos]; frame_cached = it.frame_pos; }
+        if (it.frame_pos != frame_cached) {
+          slot = p.order[static_cast<size_t>(seq) * p.order_stride + it.frame_pos];
+          frame_cached = it.frame_pos;
+        }
         const uint32_t ph = ((i >> 1) - 1) & 1;
         SK_TR(0, i, 0);
         if (i >= 2) mbar_wait(k_empty + st, ph);
         SK_TR(0, i, 1);
         mbar_expect_tx(k_full + st, kKBytes);
-        tma_load_4d_mc(sK + st * kKBytes + rank * (kKBytes / 2), &tm_k, k_full + st, 0, it.tif * kBlockN,
-                       static_cast<int>(rank), slot, 0x3);
+        tma_load_5d_mc(sK + st * kKBytes + rank * (kKBytes / 2), &tm_k, k_full + st, 0, it.tif * kBlockN,
+                       static_cast<int>(rank), slot, seq, 0x3);
         if (i >= 2) mbar_wait(v_empty + st, ph);
         SK_TR(0, i, 2);
         mbar_expect_tx(v_full + st, kVBytes);
-        tma_load_4d_mc(sV + st * kVBytes + rank * (kVBytes / 2), &tm_v, v_full + st, 0, it.tif * kBlockN,
-                       dv_split * 4 + 2 * static_cast<int>(rank), slot, 0x3);
+        tma_load_5d_mc(sV + st * kVBytes + rank * (kVBytes / 2), &tm_v, v_full + st, 0, it.tif * kBlockN,
+                       dv_split * 4 + 2 * static_cast<int>(rank), slot, seq, 0x3);
         it.next(p.P, p.tpf);
       }
     }
@@ -351,12 +367,13 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       if (first || frame_pos != prev_frame) {
         if (first) {
           m_used = -INFINITY; l_sum = 0.f;
-          q_global = (2 * (it.pair >> 2) + static_cast<int>(rank)) * kBlockM + row;
+          const int gq = it.pair >> 2, seq = gq / p.n_qpairs;
+          q_global = (2 * (gq - seq * p.n_qpairs) + static_cast<int>(rank)) * kBlockM + row;   // row inside its sequence
           slot = static_cast<size_t>(blockIdx.x) * p.max_seg + (it.pair - pair0);
           rec = p.part_f != nullptr && (it.pair & 3) == 0;
           bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
           if (p.tpe_bias && q_global < p.L)
-            bias4 = *reinterpret_cast<const float4*>(p.tpe_bias + static_cast<size_t>(q_global) * 4);
+            bias4 = *reinterpret_cast<const float4*>(p.tpe_bias + (static_cast<size_t>(seq) * p.L + q_global) * 4);
         } else if (rec) {     // close the previous frame's partial mass (relative to the running max at this point)
           float* f = p.part_f + (slot * RMEM_MAX_BANK + prev_frame) * (kStatRows * kBlockM);
           if (part == 0) f[row] = m_used;
@@ -522,6 +539,7 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
 //   W[q, t]   = sum_{s covering frame t} 2^(mf_{s,t} - M) lf_{s,t} / sum_s w_s l_s        (split 0 only)
 struct CombineParams {
   int L, T, tpf, P;
+  int n_q_tiles, n_qpairs;     // per sequence
   long long U;
   int n_clusters, max_seg;
   const float* part_o;
@@ -541,16 +559,18 @@ lt_attn_sk_combine_kernel(const CombineParams p) {
   __shared__ float tile[kBlockM][kCbCols + 1];
   __shared__ int seg_slot[kMaxSegPerPair], seg_a[kMaxSegPerPair], seg_b[kMaxSegPerPair];
   __shared__ int n_seg_sh;
-  const int q_tile = blockIdx.x;
+  const int seq = blockIdx.x / p.n_q_tiles;                // blockIdx.x = (sequence, query tile)
+  const int q_tile = blockIdx.x - seq * p.n_q_tiles;
   const bool mass_cta = blockIdx.y == kDV / kCbCols;       // the extra row of CTAs computes W[q, t] only
   const int dv_split = mass_cta ? 0 : blockIdx.y >> 2;
   const int col0 = (blockIdx.y & 3) * kCbCols;            // inside the split's 256 columns
-  const int pair = (q_tile >> 1) * 4 + dv_split;
+  const int pair = (seq * p.n_qpairs + (q_tile >> 1)) * 4 + dv_split;
   const int rank = q_tile & 1;
+  const size_t seq_row0 = static_cast<size_t>(seq) * p.L;  // first row of this sequence in gate / out / attn_mass
   // the gate does not depend on anything computed here: fetch it first (two threads per row, 64 bytes each)
   const int rr = threadIdx.x >> 1, hh = threadIdx.x & 1;
   const int qq = q_tile * kBlockM + rr;
-  const size_t out_off = static_cast<size_t>(qq) * kDV + dv_split * kDVTile + col0 + hh * 32;
+  const size_t out_off = (seq_row0 + qq) * kDV + dv_split * kDVTile + col0 + hh * 32;
   uint4 g[4];
   if (!mass_cta && p.gate && qq < p.L) {
 #pragma unroll
@@ -642,7 +662,7 @@ lt_attn_sk_combine_kernel(const CombineParams p) {
     // [128][T] is contiguous in attn_mass as well (row-major [L][T]): coalesced copy
     const int n_valid = min(kBlockM, p.L - q_tile * kBlockM) * p.T;
     for (int i = threadIdx.x; i < n_valid; i += 256)
-      p.attn_mass[static_cast<size_t>(q_tile) * kBlockM * p.T + i] = mass_sh[i];
+      p.attn_mass[(seq_row0 + static_cast<size_t>(q_tile) * kBlockM) * p.T + i] = mass_sh[i];
     return;
   }
   if (q < p.L) {
@@ -715,12 +735,12 @@ static int sm_count() {
   return cached[dev];
 }
 
-static Plan make_plan(int L, int T, int n_sms, int n_clusters_req) {
+static Plan make_plan(int L, int T, int S, int n_sms, int n_clusters_req) {
   Plan pl;
   pl.tpf = (L + kBlockN - 1) / kBlockN;
   pl.P = T * pl.tpf;
   const int q_tiles = (L + kBlockM - 1) / kBlockM;
-  pl.n_pairs = (q_tiles + 1) / 2;
+  pl.n_pairs = S * ((q_tiles + 1) / 2);
   pl.U = static_cast<long long>(pl.n_pairs) * kDVSplits * pl.P;
   int nc = n_sms / 2;                       // one cluster per SM pair: everything is resident at once
   if (n_clusters_req > 0 && n_clusters_req < nc) nc = n_clusters_req;   // leave SMs to kernels on other streams
@@ -747,9 +767,9 @@ extern "C" int rmem_dev_sk_trace(long long* out_host) {
 }
 #endif
 
-int64_t lt_attn_sk_workspace_bytes(int L, int T, int n_clusters) {
-  if (L < 1 || T < 1 || T > RMEM_MAX_BANK) return -1;
-  const sk::Plan pl = sk::make_plan(L, T, sk::sm_count(), n_clusters);
+int64_t lt_attn_sk_workspace_bytes(int L, int T, int S, int n_clusters) {
+  if (L < 1 || T < 1 || T > RMEM_MAX_BANK || S < 1) return -1;
+  const sk::Plan pl = sk::make_plan(L, T, S, sk::sm_count(), n_clusters);
   return static_cast<int64_t>(pl.n_ctas) * pl.max_seg * sk::slot_words(true) * 4;
 }
 
@@ -773,13 +793,14 @@ static void sk_split_workspace(const sk::Plan& pl, void* workspace, float** part
   *part_f = *part_ml + n_slots * sk::kPartMLWords;
 }
 
-int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vbank, const int32_t* order_dev, int T,
-                              int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host, int record,
-                              int n_clusters, void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
+int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vbank, const int32_t* order_dev,
+                              int order_stride, int T, int L, int n_slots, int S, const float* tpe_bias,
+                              const int32_t* tpe_rows_host, int record, int n_clusters, void* workspace,
+                              int64_t workspace_bytes, cudaStream_t stream) {
   using namespace sk;
-  if (T < 1 || T > RMEM_MAX_BANK || L < 1 || n_slots < T)
-    return set_error(RMEM_ERR_ARG, "lt_attn_sk: bad T / L / n_slots");
-  const Plan pl = make_plan(L, T, sm_count(), n_clusters);
+  if (T < 1 || T > RMEM_MAX_BANK || L < 1 || n_slots < T || S < 1 || (S > 1 && order_stride < T))
+    return set_error(RMEM_ERR_ARG, "lt_attn_sk: bad T / L / n_slots / batch");
+  const Plan pl = make_plan(L, T, S, sm_count(), n_clusters);
   if (!workspace || workspace_bytes < static_cast<int64_t>(pl.n_ctas) * pl.max_seg * slot_words(true) * 4)
     return set_error(RMEM_ERR_ARG, "lt_attn_sk: workspace smaller than rmem_lt_attn_deaot_sk_workspace_bytes(L, T)");
   if (pl.U * (pl.n_clusters + 1) >= (1ll << 31))
@@ -788,22 +809,25 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
     return set_error(RMEM_ERR_ARG, "lt_attn_sk: a (pair, split) would span more clusters than the combine step scans");
   CUtensorMap tm_q, tm_k, tm_v;
   {
-    const uint64_t dims[3] = {64, static_cast<uint64_t>(L), 2};
-    const uint64_t strides[2] = {kDK * 2, 128};
-    const uint32_t box[3] = {64, kBlockM, 2};
-    if (int e = sk_encode(&tm_q, q, 3, dims, strides, box)) return e;
-  }
-  {
-    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), 2, static_cast<uint64_t>(n_slots)};
+    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), 2, static_cast<uint64_t>(S)};
     const uint64_t strides[3] = {kDK * 2, 128, static_cast<uint64_t>(L) * kDK * 2};
-    const uint32_t box[4] = {64, kBlockN, 1, 1};                 // one 64-channel block: half a K tile per CTA
-    if (int e = sk_encode(&tm_k, kbank, 4, dims, strides, box)) return e;
+    const uint32_t box[4] = {64, kBlockM, 2, 1};
+    if (int e = sk_encode(&tm_q, q, 4, dims, strides, box)) return e;
   }
   {
-    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), kDV / 64, static_cast<uint64_t>(n_slots)};
-    const uint64_t strides[3] = {kDV * 2, 128, static_cast<uint64_t>(L) * kDV * 2};
-    const uint32_t box[4] = {64, kBlockN, 2, 1};                 // two of the split's four blocks per CTA
-    if (int e = sk_encode(&tm_v, vbank, 4, dims, strides, box)) return e;
+    const uint64_t dims[5] = {64, static_cast<uint64_t>(L), 2, static_cast<uint64_t>(n_slots), static_cast<uint64_t>(S)};
+    const uint64_t strides[4] = {kDK * 2, 128, static_cast<uint64_t>(L) * kDK * 2,
+                                 static_cast<uint64_t>(n_slots) * L * kDK * 2};
+    const uint32_t box[5] = {64, kBlockN, 1, 1, 1};              // one 64-channel block: half a K tile per CTA
+    if (int e = sk_encode(&tm_k, kbank, 5, dims, strides, box)) return e;
+  }
+  {
+    const uint64_t dims[5] = {64, static_cast<uint64_t>(L), kDV / 64, static_cast<uint64_t>(n_slots),
+                              static_cast<uint64_t>(S)};
+    const uint64_t strides[4] = {kDV * 2, 128, static_cast<uint64_t>(L) * kDV * 2,
+                                 static_cast<uint64_t>(n_slots) * L * kDV * 2};
+    const uint32_t box[5] = {64, kBlockN, 2, 1, 1};              // two of the split's four blocks per CTA
+    if (int e = sk_encode(&tm_v, vbank, 5, dims, strides, box)) return e;
   }
   static SmemOptIn optin;
   if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(lt_attn_sk_kernel), &optin, kSmemTotal,
@@ -811,6 +835,7 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
     return r;
   Params p;
   p.L = L; p.T = T; p.tpf = pl.tpf; p.P = pl.P; p.U = pl.U; p.n_clusters = pl.n_clusters; p.max_seg = pl.max_seg;
+  p.S = S; p.n_qpairs = pl.n_pairs / S; p.order_stride = order_stride;
   p.order = order_dev;
   p.tpe_bias = tpe_bias;
   for (int t = 0; t < RMEM_MAX_BANK; ++t) p.tpe_rows[t] = (tpe_bias && tpe_rows_host && t < T) ? tpe_rows_host[t] : 0;
@@ -822,22 +847,23 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
   return check_launch("lt_attn_sk_kernel");
 }
 
-int lt_attn_sk_combine_launch(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+int lt_attn_sk_combine_launch(int T, int L, int S, const void* gate, void* out, float* attn_mass, int n_clusters,
                               const void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
   using namespace sk;
-  if (T < 1 || T > RMEM_MAX_BANK || L < 1) return set_error(RMEM_ERR_ARG, "lt_attn_sk_combine: bad T / L");
-  const Plan pl = make_plan(L, T, sm_count(), n_clusters);
+  if (T < 1 || T > RMEM_MAX_BANK || L < 1 || S < 1) return set_error(RMEM_ERR_ARG, "lt_attn_sk_combine: bad T / L / batch");
+  const Plan pl = make_plan(L, T, S, sm_count(), n_clusters);
   if (!workspace || workspace_bytes < static_cast<int64_t>(pl.n_ctas) * pl.max_seg * slot_words(true) * 4)
     return set_error(RMEM_ERR_ARG, "lt_attn_sk_combine: workspace too small");
   CombineParams p;
   p.L = L; p.T = T; p.tpf = pl.tpf; p.P = pl.P; p.U = pl.U; p.n_clusters = pl.n_clusters; p.max_seg = pl.max_seg;
+  p.n_q_tiles = (L + kBlockM - 1) / kBlockM; p.n_qpairs = pl.n_pairs / S;
   float *po, *pml, *pf;
   sk_split_workspace(pl, const_cast<void*>(workspace), &po, &pml, &pf);
   p.part_o = po; p.part_ml = pml; p.part_f = pf;
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out);
   p.attn_mass = attn_mass;
-  dim3 grid((L + kBlockM - 1) / kBlockM, kDV / kCbCols + (attn_mass ? 1 : 0));
+  dim3 grid(S * ((L + kBlockM - 1) / kBlockM), kDV / kCbCols + (attn_mass ? 1 : 0));
   lt_attn_sk_combine_kernel<<<grid, 256, 0, stream>>>(p);
   return check_launch("lt_attn_sk_combine_kernel");
 }

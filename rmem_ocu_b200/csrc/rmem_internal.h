@@ -38,11 +38,12 @@ int lt_attn_combine_launch(const float* part_o, const float* part_m, const float
                            int chunks_per_frame, const void* gate, void* out, float* attn_mass,
                            cudaStream_t stream);
 
-int64_t lt_attn_sk_workspace_bytes(int L, int T, int n_clusters);
-int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vbank, const int32_t* order_dev, int T,
-                              int L, int n_slots, const float* tpe_bias, const int32_t* tpe_rows_host, int record,
-                              int n_clusters, void* workspace, int64_t workspace_bytes, cudaStream_t stream);
-int lt_attn_sk_combine_launch(int T, int L, const void* gate, void* out, float* attn_mass, int n_clusters,
+int64_t lt_attn_sk_workspace_bytes(int L, int T, int S, int n_clusters);
+int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vbank, const int32_t* order_dev,
+                              int order_stride, int T, int L, int n_slots, int S, const float* tpe_bias,
+                              const int32_t* tpe_rows_host, int record, int n_clusters, void* workspace,
+                              int64_t workspace_bytes, cudaStream_t stream);
+int lt_attn_sk_combine_launch(int T, int L, int S, const void* gate, void* out, float* attn_mass, int n_clusters,
                               const void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 
 int mha_partial_launch(const void* q, int ldq, const void* k, int ldk, int64_t k_slot_stride, const void* v,
@@ -73,6 +74,11 @@ int dwconv5_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, 
 int groupnorm_tokens_launch(const float* xa, int Ca, const float* xb, const float* gamma,
                             const float* beta, void* out, int out_f32, int L, int C, int groups,
                             void* workspace, cudaStream_t stream);
+int dwconv5_batched_launch(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0,
+                           int h, int w, int C, int S, cudaStream_t stream);
+int groupnorm_tokens_batched_launch(const float* xa, int Ca, const float* xb, const float* gamma,
+                                    const float* beta, void* out, int out_f32, int L, int C, int groups, int S,
+                                    void* workspace, cudaStream_t stream);
 int groupnorm_tokens_static_launch(const float* xa, int Ca, const float* xb, const float* gamma, const float* beta,
                                    void* out, int out_f32, int L, int C, int groups, cudaStream_t stream);
 int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* q_time, float* bias,
@@ -82,6 +88,10 @@ int foreground_prob_launch(const float* logits, int C, int Hs, int Ws, float* fg
 size_t local_banded_elems(int h, int w);
 int local_scores_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
                         int h, int w, cudaStream_t stream);
+int local_scores_batched_launch(const void* q, const void* k, const float* rel, int ld_rel, float* probs, void* banded,
+                                int h, int w, int S, cudaStream_t stream);
+int local_aggregate_batched_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w, int S,
+                                   cudaStream_t stream);
 int local_attn_fused_launch(const void* q, const void* k, const void* v, const float* rel, int ld_rel,
                             const void* gate, void* out, int h, int w, cudaStream_t stream);
 int local_aggregate_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w,

@@ -73,20 +73,27 @@ def layernorm(x0, g0, b0, out0, col0=0, x1=None, g1=None, b1=None, out1=None, co
     _count("rmem_layernorm")
 
 
-def dwconv5(x, xcol0, wt, y, ycol0, h, w, C):
-    _lib.check(_lib.lib().rmem_dwconv5(_p(x), x.stride(0), xcol0, _p(wt), _p(y), y.stride(0), ycol0, h, w, C,
-                                       _stream()), "rmem_dwconv5")
+def dwconv5(x, xcol0, wt, y, ycol0, h, w, C, S=1):
+    """x, y: [S * h * w, ld] token rows of S stacked (h, w) grids."""
+    _lib.check(_lib.lib().rmem_dwconv5_batched(_p(x), x.stride(0), xcol0, _p(wt), _p(y), y.stride(0), ycol0, h, w, C,
+                                               S, _stream()), "rmem_dwconv5_batched")
     _count("rmem_dwconv5")
 
 
-def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace):
-    L, Ca = xa.shape
+def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace, S=1):
+    """xa / xb / out: [S * L, C] rows of S stacked sequences (statistics per sequence; workspace: S blocks)."""
+    L, Ca = xa.shape[0] // S, xa.shape[1]
     C = Ca + (xb.shape[1] if xb is not None else 0)
     if out.dtype not in (torch.bfloat16, torch.float32):
         raise _lib.RmemError("groupnorm_tokens: out must be bf16 or f32")
-    _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
-                                                int(out.dtype == torch.float32), L, C, groups, _p(workspace),
-                                                _stream()), "rmem_groupnorm_tokens")
+    if S == 1:
+        _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
+                                                    int(out.dtype == torch.float32), L, C, groups, _p(workspace),
+                                                    _stream()), "rmem_groupnorm_tokens")
+    else:
+        _lib.check(_lib.lib().rmem_groupnorm_tokens_batched(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
+                                                            int(out.dtype == torch.float32), L, C, groups, S,
+                                                            _p(workspace), _stream()), "rmem_groupnorm_tokens_batched")
     _count("rmem_groupnorm_tokens")
 
 
@@ -208,40 +215,45 @@ def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate,
     _count("rmem_lt_attn_deaot_combine")
 
 
-def lt_attn_sk_workspace(L, T_max, device, n_clusters=0):
+def lt_attn_sk_workspace(L, T_max, device, n_clusters=0, S=1):
     """Workspace of the stream-K long-term attention for up to T_max frames in the bank (uint8 tensor)."""
-    n = max(_lib.lib().rmem_lt_attn_deaot_sk_workspace_bytes(L, T, n_clusters) for T in range(1, T_max + 1))
+    n = max(_lib.lib().rmem_lt_attn_deaot_sk_workspace_bytes(L, T, S, n_clusters) for T in range(1, T_max + 1))
     return torch.empty(n, device=device, dtype=torch.uint8)
 
 
-def lt_attn_sk_partial(q, kbank, vbank, order, T, tpe_bias, tpe_rows, record, workspace, n_clusters=0):
-    L = q.shape[0]
+def lt_attn_sk_partial(q, kbank, vbank, order, T, tpe_bias, tpe_rows, record, workspace, n_clusters=0, S=1,
+                       order_stride=0):
+    """S = 1: q [L,128], kbank [n_slots,L,128], vbank [n_slots,L,1024].  S > 1: the same with a leading [S] dimension
+    (q may be given as [S*L,128]); `order` of sequence s starts order_stride int32 words after that of s - 1."""
+    L = q.shape[-2] if q.dim() == 3 else q.shape[0] // S
+    n_slots = kbank.shape[-3]
     rows = (ctypes.c_int32 * max(T, 1))(*(tpe_rows if tpe_rows is not None else [0] * T))
-    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_partial(_p(q), _p(kbank), _p(vbank), _p(order), T, L, kbank.shape[0],
-                                                        _p(tpe_bias), ctypes.cast(rows, ctypes.c_void_p),
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_partial(_p(q), _p(kbank), _p(vbank), _p(order), order_stride, T, L,
+                                                        n_slots, S, _p(tpe_bias), ctypes.cast(rows, ctypes.c_void_p),
                                                         1 if record else 0, n_clusters, _p(workspace),
                                                         workspace.numel(), _stream()),
                "rmem_lt_attn_deaot_sk_partial")
     _count("rmem_lt_attn_deaot_sk_partial")
 
 
-def lt_attn_sk_combine(T, L, gate, out, attn_mass, workspace, n_clusters=0):
-    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_combine(T, L, _p(gate), _p(out), _p(attn_mass), n_clusters,
+def lt_attn_sk_combine(T, L, gate, out, attn_mass, workspace, n_clusters=0, S=1):
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_sk_combine(T, L, S, _p(gate), _p(out), _p(attn_mass), n_clusters,
                                                         _p(workspace), workspace.numel(), _stream()),
                "rmem_lt_attn_deaot_sk_combine")
     _count("rmem_lt_attn_deaot_sk_combine")
 
 
-def local_banded_buffer(h, w, device):
-    """Zero-filled bf16 buffer for the banded probabilities of one (h, w) token grid (zero-fill once: the
+def local_banded_buffer(h, w, device, S=1):
+    """Zero-filled bf16 buffer for the banded probabilities of S (h, w) token grids (zero-fill once: the
     scores kernel only ever writes the in-window slots)."""
     n = _lib.lib().rmem_local_banded_elems(h, w)
-    return torch.zeros(n, device=device, dtype=torch.bfloat16)
+    return torch.zeros(S * n, device=device, dtype=torch.bfloat16)
 
 
-def local_attn_scores(q, k, rel_bias, probs, banded, h, w):
-    _lib.check(_lib.lib().rmem_local_attn_scores(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs),
-                                                 _p(banded), h, w, _stream()), "rmem_local_attn_scores")
+def local_attn_scores(q, k, rel_bias, probs, banded, h, w, S=1):
+    _lib.check(_lib.lib().rmem_local_attn_scores_batched(_p(q), _p(k), _p(rel_bias), rel_bias.stride(0), _p(probs),
+                                                         _p(banded), h, w, S, _stream()),
+               "rmem_local_attn_scores_batched")
     _count("rmem_local_attn_scores")
 
 
@@ -253,9 +265,9 @@ def local_attn(q, k, v, rel_bias, gate, out, h, w):
     _count("rmem_local_attn")
 
 
-def local_attn_aggregate(banded, v, gate, out, h, w):
-    _lib.check(_lib.lib().rmem_local_attn_aggregate(_p(banded), _p(v), _p(gate), _p(out), h, w, _stream()),
-               "rmem_local_attn_aggregate")
+def local_attn_aggregate(banded, v, gate, out, h, w, S=1):
+    _lib.check(_lib.lib().rmem_local_attn_aggregate_batched(_p(banded), _p(v), _p(gate), _p(out), h, w, S, _stream()),
+               "rmem_local_attn_aggregate_batched")
     _count("rmem_local_attn_aggregate")
 
 
