@@ -357,6 +357,50 @@ def run_sequences(model, local_rank, seq_ids, spec, steps, head, precapture=True
     return e0.elapsed_time(e1), info
 
 
+def run_lockstep(model, local_rank, seq_ids, spec, steps, head, prefetch=True):
+    """Several independent sequences on one GPU through ONE engine (DeAOTEngine(n_sequences = S)): they step in
+    lock-step and share every launch -- the sequence is a grid dimension of the kernels, the cuDNN convolutions take
+    the batch.  `head` untimed frames, then `steps` timed lock-steps (S frames each).  Returns (ms, per-sequence info)."""
+    from rmem_ocu_b200 import ops
+    from rmem_ocu_b200.engine import DeAOTEngine
+    dev = torch.device("cuda", local_rank)
+    h, w, n_obj, gap = spec["H"], spec["W"], spec["n_obj"], spec["gap"]
+    S = len(seq_ids)
+    n_pool = min(POOL, 2 + head + steps)
+    pools, labs = [], []
+    for q in seq_ids:
+        imgs, lab = make_clip(n_pool, 2000 + q, h=h, w=w, n_obj=n_obj)
+        pools.append(imgs)
+        labs.append(lab)
+    frames = [torch.cat([pools[s][f] for s in range(S)]).to(dev) for f in range(n_pool)]     # [S, 3, h, w] each
+    img = lambda f: frames[f % n_pool]
+    eng = DeAOTEngine(model, local_rank, long_term_mem_gap=gap, n_sequences=S)
+
+    def step(f):
+        lg = eng.match_propogate_one_frame(img(f), output_size=(h, w), next_img=img(f + 1) if prefetch else None)
+        eng.update_short_term_memory(ops.argmax_label(lg))
+
+    with torch.no_grad():
+        eng.add_reference_frame(frames[0], torch.cat(labs).to(dev), obj_nums=[n_obj] * S, frame_step=0)
+        for f in range(1, 1 + head):
+            step(f)
+            if f == 1:
+                eng.precapture((h, w), prefetch=prefetch)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for f in range(1 + head, 1 + head + steps):
+            step(f)
+        eng._wait_write()                                     # the last write path belongs to the timed work
+        e1.record()
+        torch.cuda.synchronize()
+    banks = eng.long_memories_indexes
+    banks = [banks] if S == 1 else banks
+    info = {seq_ids[s]: dict(frames=steps, bank=banks[s], evictions=eng.eviction_debug(s)["n_evictions"])
+            for s in range(S)}
+    return e0.elapsed_time(e1), info
+
+
 def config_legs(args, rank, world, local_rank):
     """BASELINE.json configs 3, 4, 5 as extra legs (not the headline).  4 and 5 shard their sequences over the ranks
     with rmem_ocu_b200.shard (2 per GPU) and gather the per-sequence results at the end; 3 is rank 0 only."""
@@ -369,19 +413,20 @@ def config_legs(args, rank, world, local_rank):
     spec4 = dict(H=480, W=864, n_obj=5, gap=gap_rule(n4))
     seqs = assign_sequences(2 * world, world, rank)
     head4 = 8
-    ms, info = run_sequences(build_model(latter=8), local_rank, seqs, spec4, n4 - 1 - head4, head4)
+    ms, info = run_lockstep(build_model(latter=8), local_rank, seqs, spec4, n4 - 1 - head4, head4)
     ms = max_over_ranks(ms, dev)
     merged = gather_results(info)
     frames = sum(v["frames"] for v in merged.values())
     out["4"] = {"workload": "R50 DeAOT-L + RMem, %d-frame synthetic 480x864 clips (pool of %d images), 5 objects, K = 8, "
-                            "gap %d, %d sequences over %d GPU(s)" % (n4, POOL, spec4["gap"], len(merged), world),
+                            "gap %d, %d sequences over %d GPU(s), the 2 sequences of a GPU in lock-step through one "
+                            "engine (sequence = grid dimension)" % (n4, POOL, spec4["gap"], len(merged), world),
                 "value": frames / (ms * 1e-3), "unit": "frames/s", "ms": ms, "sequences": len(merged),
                 "evictions_per_sequence": sorted(v["evictions"] for v in merged.values()),
                 "bank_of_sequence_0": merged[0]["bank"]}
     # ---- config 5: 720p, 10 objects (one engine), 100-frame clips, 2 per GPU
     spec5 = dict(H=720, W=1280, n_obj=10, gap=gap_rule(100))
     head5 = spec5["gap"] * LATTER + 3
-    ms, info = run_sequences(build_model(latter=LATTER), local_rank, seqs, spec5, 100 - 1 - head5, head5)
+    ms, info = run_lockstep(build_model(latter=LATTER), local_rank, seqs, spec5, 100 - 1 - head5, head5)
     ms = max_over_ranks(ms, dev)
     merged = gather_results(info)
     frames = sum(v["frames"] for v in merged.values())
@@ -532,6 +577,24 @@ def kernel_rooflines(dev):
            "kernel": "local_scores_kernel+local_aggregate_kernel", "us": t_loc * 1e6, "peak_src": peaks["src"],
            "fused_kernel_us": t_loc_fused * 1e6,
            "algorithmic_bytes": bytes_alg}
+    # the same pair on a batch of S = 8 sequences in one launch (sequence = grid dimension): full waves
+    SB = 8
+    bq, bk = mk(2, SB * L, 128), mk(2, SB * L, 128)
+    bv, bu = mk(2, SB * L, 1024), mk(2, SB * L, 1024)
+    brel = torch.randn(2, SB * L, 256, device=dev) * 0.1
+    bout = torch.empty(2, SB * L, 1024, device=dev, dtype=torch.bfloat16)
+    bband = [ops.local_banded_buffer(h, w, dev, SB) for _ in range(2)]
+
+    def local_batched(i):
+        i = i % 2
+        ops.local_attn_scores(bq[i], bk[i], brel[i], None, bband[i], h, w, S=SB)
+        ops.local_attn_aggregate(bband[i], bv[i], bu[i], bout[i], h, w, S=SB)
+
+    t_b = timed_graph(local_batched)
+    loc["batched"] = {"S": SB, "us": t_b * 1e6, "achieved": SB * bytes_alg / t_b / 1e9,
+                      "frac": SB * bytes_alg / t_b / 1e9 / peaks["hbm_gbs"], "working_set_mb": 2 * SB * bytes_alg / 1e6,
+                      "note": "S sequences per launch, two rotating input sets (> L2)"}
+    del bq, bk, bv, bu, brel, bout, bband
     ks = [ncu.get(n) for n in ("local_scores_kernel", "local_aggregate_kernel")]
     ks = [k for k in ks if k]
     if ks:
@@ -657,12 +720,20 @@ def main():
             line["configs"] = legs
         if world == 1 and args.seqs_per_gpu > 1 and extra:
             spec = dict(H=H, W=W, n_obj=N_OBJ, gap=gap_rule(100))
-            ms, _ = run_sequences(build_model(), local_rank, list(range(args.seqs_per_gpu)), spec, args.steps,
-                                  prefill + args.warmup)
+            ms_streams, _ = run_sequences(build_model(), local_rank, list(range(args.seqs_per_gpu)), spec, args.steps,
+                                          prefill + args.warmup)
+            sweep = {}
+            for S in sorted({args.seqs_per_gpu, 4}):
+                ms, _ = run_lockstep(build_model(), local_rank, list(range(S)), spec, args.steps, prefill + args.warmup)
+                sweep[str(S)] = S * args.steps / (ms * 1e-3)
             line["multi_sequence"] = {"sequences_per_gpu": args.seqs_per_gpu, "unit": "frames/s",
-                                      "value": args.seqs_per_gpu * args.steps / (ms * 1e-3),
-                                      "note": "same workload, S independent clips interleaved on S streams "
-                                              "(configs 4 / 5 shard 2 sequences per GPU); not the headline"}
+                                      "value": sweep[str(args.seqs_per_gpu)], "lockstep_by_S": sweep,
+                                      "streams": args.seqs_per_gpu * args.steps / (ms_streams * 1e-3),
+                                      "vs_single_sequence": sweep[str(args.seqs_per_gpu)] / (total_frames / sec),
+                                      "note": "same workload, S independent clips in lock-step through one engine "
+                                              "(sequence = grid dimension of every kernel, cuDNN convolutions "
+                                              "batched); `streams` = the round-1 form, S engines on S streams; "
+                                              "configs 4 / 5 put 2 sequences on a GPU; not the headline"}
         if world == 1 and extra:
             try:
                 f32, _ = cpu_port_fps(10, device="cuda")

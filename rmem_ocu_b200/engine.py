@@ -136,22 +136,26 @@ class InferenceFPN:
         self.wb = {name: sd[prefix + name + ".weight"].detach().reshape(sd[prefix + name + ".weight"].shape[0], -1)
                    .to(device=device, dtype=self.shortcut_dtype).contiguous()
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
-        self.gn_ws = torch.zeros(17, device=device, dtype=torch.float64)    # 2 x 8 group sums + arrival counter
+        self.gn_ws = torch.zeros(1, 17, device=device, dtype=torch.float64)  # per image: 2 x 8 group sums + counter
         self._ws = self.gn_ws       # the workspace of the call in flight (engines pass their own: they may run
                                     # concurrently on different streams and share this object through `prepare`)
 
     @staticmethod
     def _tok(x):
-        """channels-last [1, C, H, W] -> [H*W, C] view of the same memory."""
+        """channels-last [n, C, H, W] -> [n*H*W, C] view of the same memory."""
         n, c, h, w = x.shape
-        return x.permute(0, 2, 3, 1).reshape(h * w, c)
+        return x.permute(0, 2, 3, 1).reshape(n * h * w, c)
 
     def _conv_gn_relu(self, x, name):
         """ConvGN + ReLU: the conv bias is applied inside the GroupNorm kernels (no separate bias pass)."""
         w, b, g, be = self.w[name]
         y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
         t = self._tok(y)
-        ops.groupnorm_nhwc(t, g, be, t, 8, True, self._ws, pre_bias=b)            # in place
+        n = y.shape[0]
+        P = t.shape[0] // n
+        for s in range(n):                       # statistics per image (a batch = independent sequences)
+            ts = t[s * P:(s + 1) * P]
+            ops.groupnorm_nhwc(ts, g, be, ts, 8, True, self._ws[s], pre_bias=b)   # in place
         return y
 
     ADAPTERS = (("adapter_16x", -2), ("adapter_8x", -3), ("adapter_4x", -4))
@@ -161,7 +165,8 @@ class InferenceFPN:
         w, b = self.w[name]
         shortcut = shortcut.contiguous(memory_format=torch.channels_last)
         ho, wo = shortcut.shape[-2:]
-        a = torch.empty(1, ho, wo, w.shape[0], device=shortcut.device, dtype=torch.float32).permute(0, 3, 1, 2)
+        a = torch.empty(shortcut.shape[0], ho, wo, w.shape[0], device=shortcut.device,
+                        dtype=torch.float32).permute(0, 3, 1, 2)
         ops.linear(self._tok(shortcut), self.wb[name], b, [(0, w.shape[0], ops.ACT_NONE, ops.OUT_F32, self._tok(a), 0)])
         return a
 
@@ -186,7 +191,11 @@ class InferenceFPN:
             ta = self._tok(a)
         hi, wi = x.shape[-2:]
         ho, wo = a.shape[-2:]
-        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b)     # in place
+        n = x.shape[0]
+        tx = self._tok(x)
+        for s in range(n):
+            tas = ta[s * ho * wo:(s + 1) * ho * wo]
+            ops.upsample_add_nhwc(tx[s * hi * wi:(s + 1) * hi * wi], hi, wi, tas, tas, ho, wo, a_bias=b)   # in place
         return a
 
     def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None):
@@ -301,19 +310,23 @@ class InferenceResNet:
     def _forward(self, img):
         half = self.dtype in (BF16, torch.float16)
         if img.dtype == torch.uint8:
-            n, h, w = (1,) + tuple(img.shape[-3:-1])
+            if img.dim() == 3:
+                img = img[None]
+            n, h, w = img.shape[0], img.shape[1], img.shape[2]
         else:
             n, c, h, w = img.shape
-        s2d = (half and n == 1 and img.dtype in (torch.float32, torch.uint8) and self.fused
-               and self.conv1_s2d is not None)
+        # n > 1: a batch of independent sequences stepping in lock-step (the convolutions take the batch; the small
+        # per-image kernels around them are issued per image)
+        s2d = (half and img.dtype in (torch.float32, torch.uint8) and self.fused and self.conv1_s2d is not None)
         if img.dtype == torch.uint8 and not s2d:
-            img = img.reshape(1, h, w, 3).permute(0, 3, 1, 2).float().div(255.0)
+            img = img.permute(0, 3, 1, 2).float().div(255.0)
             img = (img - img.new_tensor(self.U8_MEAN).view(1, 3, 1, 1)) / img.new_tensor(self.U8_STD).view(1, 3, 1, 1)
         if s2d:
-            x = torch.empty(1, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device,
+            x = torch.empty(n, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device,
                             dtype=self.dtype).permute(0, 3, 1, 2)
             # f32 planes / u8 pixels -> 16-bit space-to-depth image, conv padding built in
-            ops.pack_image_s2d(img, x, self.U8_MEAN, self.U8_STD)
+            for s in range(n):
+                ops.pack_image_s2d(img[s:s + 1], x[s:s + 1], self.U8_MEAN, self.U8_STD)
         elif self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
             x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16, memory_format=torch.channels_last)
             ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
@@ -329,13 +342,14 @@ class InferenceResNet:
             x = self._conv(x, self.conv1, True)
         else:
             x = F.relu(F.conv2d(x, self.conv1[0], self.conv1[1], self.conv1[2], self.conv1[3]))
-        if half and n == 1:
-            pooled = torch.empty(1, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
+        if half and (n == 1 or s2d):
+            pooled = torch.empty(n, x.shape[1], (x.shape[2] - 1) // 2 + 1, (x.shape[3] - 1) // 2 + 1,
                                  device=x.device, dtype=self.dtype, memory_format=torch.channels_last)
             c_, h_, w_ = x.shape[1:]
             if x.stride()[1:] != (1, w_ * c_, c_):                   # cuDNN returns NHWC strides; never copy then
                 x = x.contiguous(memory_format=torch.channels_last)
-            ops.maxpool3s2_nhwc(x, pooled, self.conv1_bias_f32 if s2d else None, s2d)
+            for s in range(n):
+                ops.maxpool3s2_nhwc(x[s:s + 1], pooled[s:s + 1], self.conv1_bias_f32 if s2d else None, s2d)
             x = pooled
         else:
             x = F.max_pool2d(x, 3, 2, 1)
@@ -420,42 +434,46 @@ def is_deaot_model(model):
 class _Workspace:
     """Per-sequence device buffers for one token grid (h, w); allocated once, reused every frame."""
 
-    def __init__(self, prep, h, w, n_slots, device):
+    def __init__(self, prep, h, w, n_slots, device, S=1):
+        """S = number of independent sequences stepping in lock-step: every token matrix is the stack [S * L, C] of
+        the sequences' matrices (row-wise kernels take it as it is, spatial kernels get S as a grid dimension)."""
         L, nl = h * w, prep.num_layers
         f32 = torch.float32
+        R = S * L                                             # rows of a stacked token matrix
 
         def z(*s, dt=BF16):
             return torch.zeros(*s, device=device, dtype=dt)
 
-        self.h, self.w, self.L, self.n_slots = h, w, L, n_slots
-        self.tgt, self.tgt_id = z(L, 256, dt=f32), z(L, 256, dt=f32)
-        self.xn = z(L, 512)                                   # LayerNorm outputs (norm | id_norm)
-        self.idcat = [z(L, 512) for _ in range(nl)]           # [curr_ID_V | id_emb] per layer
+        self.h, self.w, self.L, self.n_slots, self.S = h, w, L, n_slots, S
+        self.tgt, self.tgt_id = z(R, 256, dt=f32), z(R, 256, dt=f32)
+        self.xn = z(R, 512)                                   # LayerNorm outputs (norm | id_norm)
+        self.idcat = [z(R, 512) for _ in range(nl)]           # [curr_ID_V | id_emb] per layer
         # K and V | ID_V of a frame, two sets: the valid short-term memory (previous frame) and the set the
         # current frame is written into; the write path completes ID_V in place and the roles swap (no copies)
-        self.kst = [[z(L, 128) for _ in range(nl)] for _ in range(2)]
-        self.vst = [[z(L, 1024) for _ in range(nl)] for _ in range(2)]
+        self.kst = [[z(R, 128) for _ in range(nl)] for _ in range(2)]
+        self.vst = [[z(R, 1024) for _ in range(nl)] for _ in range(2)]
         self.bind(0)
-        self.kbank = [z(n_slots, L, 128) for _ in range(nl)]  # long-term bank
-        self.vbank = [z(n_slots, L, 1024) for _ in range(nl)]
-        self.u = [z(L, 1024) for _ in range(nl)]              # cat_curr_U
+        self.kbank = [z(S, n_slots, L, 128) for _ in range(nl)]   # long-term bank, one per sequence
+        self.vbank = [z(S, n_slots, L, 1024) for _ in range(nl)]
+        self.u = [z(R, 1024) for _ in range(nl)]              # cat_curr_U
         self.u[0][:, 512:] = 1.0                              # layer 0: U = [silu(U), 1]
-        self.qt, self.tpe_bias = z(L, 128), z(L, 4, dt=f32)
-        self.gated_a, self.gated_b = z(L, 1024), z(L, 1024)
-        self.dw = z(L, 2048)
-        self.rel = z(L, 256, dt=f32)
-        self.banded = ops.local_banded_buffer(h, w, device)   # local-attention probabilities, banded per tile
-        self.sa_qk, self.sa_v, self.sa_u = z(L, 128), z(L, 1024), z(L, 1024)
-        n_chunks = max(T * _chunks_per_frame(T, L) for T in range(1, n_slots + 1))
-        self.part_o = z(n_chunks, L, 1024, dt=f32)
-        self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
-        self.mass = z(L * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight [L, T]
-        self.gn_out = z(L, 512, dt=f32)                       # f32: feeds the decoder's f32 convolutions as it is
-        self.gn_ws = z(5, dt=torch.float64)                   # 2 x 2 group sums + arrival counter
-        self.fg = z(L, dt=f32)
-        self.id_emb = z(L, 256)
-        self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
-        self.zero_order = z(1, dt=torch.int32)
+        self.qt, self.tpe_bias = z(R, 128), z(R, 4, dt=f32)
+        self.gated_a, self.gated_b = z(R, 1024), z(R, 1024)
+        self.dw = z(R, 2048)
+        self.rel = z(R, 256, dt=f32)
+        self.banded = ops.local_banded_buffer(h, w, device, S)    # local-attention probabilities, banded per tile
+        self.sa_qk, self.sa_v, self.sa_u = z(R, 128), z(R, 1024), z(R, 1024)
+        if S == 1:                                            # partials of the first-generation attention (T = 1)
+            n_chunks = max(T * _chunks_per_frame(T, L) for T in range(1, n_slots + 1))
+            self.part_o = z(n_chunks, L, 1024, dt=f32)
+            self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
+        self.mass = z(R * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight, [S][L][T] packed
+        self.gn_out = z(R, 512, dt=f32)                       # f32: feeds the decoder's f32 convolutions as it is
+        self.gn_ws = z(5 * S, dt=torch.float64)               # per sequence: 2 x 2 group sums + arrival counter
+        self.fg = z(S, L, dt=f32)
+        self.id_emb = z(R, 256)
+        self.bank_state = z(S, _lib.BANK_STATE_WORDS, dt=torch.int32)
+        self.zero_order = z(S, dt=torch.int32)
         self.sk_ws = None                                     # stream-K attention workspace, allocated on first use
         self.pred_logits = None                               # [1, 11, H/4, W/4] f32, allocated on first decode
 
@@ -497,7 +515,12 @@ class DeAOTEngine:
     update_short_term_memory, decode_current_logits, restart_engine, update_size."""
 
     def __init__(self, aot_model, gpu_id=0, long_term_mem_gap=9999, short_term_mem_skip=1,
-                 layer_loss_scaling_ratio=2.):
+                 layer_loss_scaling_ratio=2., n_sequences=1):
+        """``n_sequences`` (not in the reference, whose recorded-attention path asserts batch size 1,
+        transformer.py:641): S > 1 steps S independent sequences of one frame size in lock-step through the same
+        launches -- images [S, 3, H, W], label maps [S, 1, H, W], obj_nums a list of S counts, logits [S, C, H, W],
+        ``long_memories_indexes`` a list of S lists.  Every sequence keeps its own bank and its own eviction history;
+        the sequence is a grid dimension of the kernels (one sequence alone is a fraction of a wave on 148 SMs)."""
         if not torch.cuda.is_available():
             raise _lib.RmemError("rmem_ocu_b200 engines need a CUDA device: there is no CPU fallback")
         _lib.lib()  # fail loudly now if the shared library is missing
@@ -511,11 +534,16 @@ class DeAOTEngine:
         self.device = torch.device("cuda", gpu_id)
         self.long_term_mem_gap = long_term_mem_gap
         self.short_term_mem_skip = short_term_mem_skip
+        self.S = int(n_sequences)
+        if self.S < 1:
+            raise ValueError("n_sequences must be >= 1")
         self.prep = prepare(aot_model, self.device)
         self.capacity = int(self.cfg.FORMER_MEM_LEN) + int(self.cfg.LATTER_MEM_LEN)
         if self.capacity + 1 > _lib.MAX_BANK:
             raise _lib.RmemError("FORMER_MEM_LEN + LATTER_MEM_LEN + 1 exceeds RMEM_MAX_BANK")
         self.deaot = self.prep.deaot
+        if self.S > 1 and not self.deaot:
+            raise NotImplementedError("n_sequences > 1 is implemented for the DeAOT family")
         if self.deaot != self._family_deaot:
             raise _lib.RmemError("%s was given a%s model" % (type(self).__name__, "n AOT" if self._family_deaot
                                                              else " DeAOT"))
@@ -525,7 +553,7 @@ class DeAOTEngine:
         self.fork_branches = os_env_flag("RMEM_FORK_BRANCHES", True)
         # single-kernel local attention (csrc/local_attn_fused.cu): parity-green but 17.5 us against 16.5 us for
         # the scores + aggregation pair at 480p, so it is opt-in until it wins
-        self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False)
+        self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False) and self.S == 1
         import os
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
@@ -563,7 +591,7 @@ class DeAOTEngine:
     _family_deaot = True
 
     def _new_workspace(self, h, w, n_slots):
-        return _Workspace(self.prep, h, w, n_slots, self.device)
+        return _Workspace(self.prep, h, w, n_slots, self.device, self.S)
 
     @staticmethod
     def _tpe_rows(T):
@@ -571,7 +599,7 @@ class DeAOTEngine:
 
     def _decoder_inputs(self, embs, lstt_out):
         n, c, h, w = embs[-1].shape
-        return [embs[-1], lstt_out.view(1, h, w, -1).permute(0, 3, 1, 2)]   # channels-last view, no copy
+        return [embs[-1], lstt_out.view(n, h, w, -1).permute(0, 3, 1, 2)]   # channels-last view, no copy
 
     # ------------------------------------------------------------------ bookkeeping
     def restart_engine(self, batch_size=1, enable_id_shuffle=False):
@@ -603,7 +631,7 @@ class DeAOTEngine:
         if self.ws is None or (self.ws.h, self.ws.w, self.ws.n_slots) != (h, w, n_slots):
             self.ws = self._new_workspace(h, w, n_slots)
             if self.lt_streamk:          # allocated here, never inside a graph capture
-                self.ws.sk_ws = ops.lt_attn_sk_workspace(self.ws.L, n_slots, self.device, self.lt_sk_clusters)
+                self.ws.sk_ws = ops.lt_attn_sk_workspace(self.ws.L, n_slots, self.device, self.lt_sk_clusters, self.S)
             self._wait_write()
             self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
             self._prefetched, self._enc_set = None, 0
@@ -616,12 +644,13 @@ class DeAOTEngine:
         with torch.cuda.device(self.device):
             self._wait_write()
             st = self.ws.bank_state.cpu()
-        return [int(st[_lib.MAX_BANK + int(st[t])]) for t in range(self.T)]
+        per_seq = [[int(st[s, _lib.MAX_BANK + int(st[s, t])]) for t in range(self.T)] for s in range(self.S)]
+        return per_seq[0] if self.S == 1 else per_seq
 
     @_on_device
-    def eviction_debug(self):
+    def eviction_debug(self, sequence=0):
         self._wait_write()
-        st = self.ws.bank_state.cpu()
+        st = self.ws.bank_state[sequence].cpu()
         base = 5 * _lib.MAX_BANK
         return dict(last_drop=int(st[base]), last_drop_frame=int(st[base + 1]),
                     margin=float(st[base + 2:base + 3].view(torch.float32)), n_evictions=int(st[base + 3]),
@@ -641,9 +670,9 @@ class DeAOTEngine:
         return embs + pre if pre is not None else embs
 
     def _tokens(self, x_nchw):
-        """[1, C, h, w] channels-last tensor -> [L, C] view of the same memory."""
+        """[S, C, h, w] channels-last tensor -> [S * L, C] view of the same memory."""
         n, c, h, w = x_nchw.shape
-        return x_nchw.permute(0, 2, 3, 1).reshape(h * w, c)
+        return x_nchw.permute(0, 2, 3, 1).reshape(n * h * w, c)
 
     def _id_embed(self, label_hw):
         """assign_identity + get_id_emb (aot_engine.py:208-232, models/deaot.py:65-69) from a hard label
@@ -651,15 +680,21 @@ class DeAOTEngine:
         for every layer's ID_V GEMM."""
         ws, prep = self.ws, self.prep
         g, b = prep.id_norm
-        dsts = [(ws.id_emb, 0)] + [(ws.idcat[i], 256) for i in range(prep.num_layers)]
-        ops.id_embed(label_hw, prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)
+        L = ws.L
+        for s in range(ws.S):                    # label_hw: [S, H, W]
+            rows = slice(s * L, (s + 1) * L)
+            dsts = [(ws.id_emb[rows], 0)] + [(ws.idcat[i][rows], 256) for i in range(prep.num_layers)]
+            ops.id_embed(label_hw[s], prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)
 
-    @staticmethod
-    def _label_map(mask):
-        """Accepts [H,W], [1,H,W] or [1,1,H,W] label maps; soft / one-hot masks are a training-only form."""
+    def _label_map(self, mask):
+        """Accepts [H,W], [S,H,W] or [S,1,H,W] label maps -> [S, H, W]; soft / one-hot masks are a training-only
+        form (aot_engine.py:330-334 takes that branch for batch > 1 only)."""
         if mask.dim() == 4 and mask.shape[1] != 1:
             raise NotImplementedError("one-hot / probability masks are not on the evaluated path")
-        return mask.reshape(mask.shape[-2], mask.shape[-1])
+        if mask.numel() != self.S * mask.shape[-2] * mask.shape[-1]:
+            raise ValueError("expected label maps for %d sequence(s), got a tensor of shape %s" %
+                             (self.S, tuple(mask.shape)))
+        return mask.reshape(self.S, mask.shape[-2], mask.shape[-1])
 
     # ------------------------------------------------------------------ LSTT (kernels)
     def _id_value(self, i, dst):
@@ -669,19 +704,23 @@ class DeAOTEngine:
         a = ws.idcat[i][:, 256:] if i == 0 else ws.idcat[i]
         ops.linear(a, Lw["w_idv"], Lw["b_idv"], [(0, 512, ops.ACT_SILU, ops.OUT_BF16, dst, 512)])
 
-    def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass, gate_ready=None):
+    def _gated_global_attention(self, q, kbank, vbank, order, T, tpe, gate, out, mass, gate_ready=None,
+                                order_stride=0):
+        """kbank / vbank: [S, n_slots, L, C]; order: int32, sequence s's slot table order_stride words after s - 1's."""
         ws = self.ws
-        if self.lt_streamk and T >= 2:
+        if (self.lt_streamk and T >= 2) or ws.S > 1:
             # second-generation kernel (csrc/lt_attn_sk.cu): persistent stream-K on 2-CTA clusters; wins from two
-            # frames in the bank on (T = 1, i.e. the self-attention and a fresh bank, stays on the first generation)
+            # frames in the bank on (one sequence at T = 1, i.e. its self-attention and a fresh bank, stays on the
+            # first generation); the sequence-batched form exists in this kernel only
             ops.lt_attn_sk_partial(q, kbank, vbank, order, T, ws.tpe_bias if tpe else None,
                                    tpe_row_indices(T) if tpe else None, mass is not None, ws.sk_ws,
-                                   self.lt_sk_clusters)
+                                   self.lt_sk_clusters, ws.S, order_stride)
             if gate_ready is not None:
                 torch.cuda.current_stream().wait_event(gate_ready)
-            ops.lt_attn_sk_combine(T, ws.L, gate, out, mass, ws.sk_ws, self.lt_sk_clusters)
+            ops.lt_attn_sk_combine(T, ws.L, gate, out, mass, ws.sk_ws, self.lt_sk_clusters, ws.S)
             return
         cpf = _chunks_per_frame(T, ws.L)
+        kbank, vbank = kbank.view(-1, ws.L, kbank.shape[-1]), vbank.view(-1, ws.L, vbank.shape[-1])
         ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
         if gate_ready is not None:
             torch.cuda.current_stream().wait_event(gate_ready)    # the gate is computed on another branch
@@ -718,14 +757,14 @@ class DeAOTEngine:
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
         # the single output GroupNorm1D(512, 2) (transformer.py:806-808)
-        ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws)
+        ops.groupnorm_tokens(ws.tgt, ws.tgt_id, *prep.gn_out, ws.gn_out, 2, ws.gn_ws, S=ws.S)
         return ws.gn_out
 
     def _block_forward(self, i, is_reference, record, T):
         """GatedPropagationModule.forward (transformer.py:1091-1236) of layer ``i`` on the workspace's residual
         streams; ``record``: write this layer's record_attn_weight into ws.mass (the engines record layer 0)."""
         ws, prep = self.ws, self.prep
-        h, w, L = ws.h, ws.w, ws.L
+        h, w, L, S = ws.h, ws.w, ws.L, ws.S
         Lw = prep.layers[i]
         tr = self.trace
         we = self._w_events
@@ -752,7 +791,7 @@ class DeAOTEngine:
             # the reference frame is its own long- and short-term memory (transformer.py:1125-1135)
             self._id_value(i, ws.vcur[i])
             ws.kprev[i].copy_(ws.kcur[i]); ws.vprev[i].copy_(ws.vcur[i])
-            ws.kbank[i][0].copy_(ws.kcur[i]); ws.vbank[i][0].copy_(ws.vcur[i])
+            ws.kbank[i][:, 0].copy_(ws.kcur[i].view(S, L, 128)); ws.vbank[i][:, 0].copy_(ws.vcur[i].view(S, L, 1024))
         # The long-term and the short-term branch only share their inputs (K = Q, U) and meet again in the
         # projection GEMM: the short-term branch is forked onto a side stream (a parallel branch of the
         # captured graph), so its sub-wave kernels fill the SMs the long-term attention's ragged second wave
@@ -773,17 +812,17 @@ class DeAOTEngine:
             if self.local_fused:
                 ops.local_attn(ws.kcur[i], ws.kprev[i], ws.vprev[i], ws.rel, ws.u[i], ws.gated_b, h, w)
             else:
-                ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w)
-                ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w)
-            ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024)
+                ops.local_attn_scores(ws.kcur[i], ws.kprev[i], ws.rel, None, ws.banded, h, w, S=S)
+                ops.local_attn_aggregate(ws.banded, ws.vprev[i], ws.u[i], ws.gated_b, h, w, S=S)
+            ops.dwconv5(ws.gated_b, 0, Lw["dw_st"], ws.dw, 1024, h, w, 1024, S=S)
         # long-term attention over the bank (TPE folded into a per-frame score bias), gate, dw5x5
         ops.tpe_prepare(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
         mass = None
         if record:
             mass = ws.mass
         self._gated_global_attention(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, ws.u[i],
-                                     ws.gated_a, mass, gate_ready=idu_done)
-        ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024)
+                                     ws.gated_a, mass, gate_ready=idu_done, order_stride=_lib.BANK_STATE_WORDS)
+        ops.dwconv5(ws.gated_a, 0, Lw["dw_lt"], ws.dw, 0, h, w, 1024, S=S)
         if forked:
             self._join()
         # (projection_lt + projection_st) -> residual adds, one GEMM
@@ -802,9 +841,9 @@ class DeAOTEngine:
                    [(0, 128, ops.ACT_NONE, ops.OUT_BF16, ws.sa_qk, 0),
                     (128, 1152, ops.ACT_SILU, ops.OUT_BF16, ws.sa_v, 0),
                     (1152, 2176, ops.ACT_SILU, ops.OUT_BF16, ws.sa_u, 0)])
-        self._gated_global_attention(ws.sa_qk, ws.sa_qk.view(1, L, 128), ws.sa_v.view(1, L, 1024),
-                                     ws.zero_order, 1, False, ws.sa_u, ws.gated_a, None)
-        ops.dwconv5(ws.gated_a, 0, Lw["dw_sa"], ws.dw, 0, h, w, 1024)
+        self._gated_global_attention(ws.sa_qk, ws.sa_qk.view(S, 1, L, 128), ws.sa_v.view(S, 1, L, 1024),
+                                     ws.zero_order, 1, False, ws.sa_u, ws.gated_a, None, order_stride=1)
+        ops.dwconv5(ws.gated_a, 0, Lw["dw_sa"], ws.dw, 0, h, w, 1024, S=S)
         ops.linear(ws.dw[:, :1024], Lw["w_proj_sa"], Lw["b_proj_sa"],
                    [(0, 256, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt, 0),
                     (256, 512, ops.ACT_NONE, ops.OUT_F32_ACCUM, ws.tgt_id, 0)])
@@ -821,7 +860,8 @@ class DeAOTEngine:
             # the device frame counter: it has to be complete before the counter ticks
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
-        ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device
+        for s in range(self.ws.S):
+            ops.bank_tick(self.ws.bank_state[s])                        # frame_step += 1 on the device
         embs = self._encode_body(img) if img_embs is None else img_embs
         embs, pre = (embs[:4], embs[4:]) if len(embs) == 7 else (embs, None)
         lstt_out = self._lstt_forward(embs[-1], False, True, T)
@@ -862,19 +902,22 @@ class DeAOTEngine:
         if forked:
             self._join()
         if update_long:
-            srcs, dsts = [], []
-            for i in range(self.prep.num_layers):
-                srcs += [ws.kcur[i], ws.vcur[i]]
-                dsts += [ws.kbank[i], ws.vbank[i]]
-            ops.bank_append(ws.bank_state, T, -1, srcs, dsts)           # frame id from the device counter
-            if do_evict:
-                ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
-                ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T, self.capacity)
+            L = ws.L
+            for s in range(ws.S):                # every sequence owns its bank, slot table and eviction history
+                srcs, dsts = [], []
+                for i in range(self.prep.num_layers):
+                    srcs += [ws.kcur[i][s * L:(s + 1) * L], ws.vcur[i][s * L:(s + 1) * L]]
+                    dsts += [ws.kbank[i][s], ws.vbank[i][s]]
+                ops.bank_append(ws.bank_state[s], T, -1, srcs, dsts)    # frame id from the device counter
+                if do_evict:
+                    ops.foreground_prob(self.pred_id_logits[s], ws.fg[s], ws.h, ws.w)
+                    ops.bank_score_evict(ws.bank_state[s], ws.mass[s * L * T:(s + 1) * L * T], ws.fg[s], L, T,
+                                         self.capacity)
 
     def _decode(self, embs, lstt_out, output_size, adapters=None):
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
         if getattr(self, "_dec_gn_ws", None) is None:
-            self._dec_gn_ws = torch.zeros(17, device=self.device, dtype=torch.float64)
+            self._dec_gn_ws = torch.zeros(self.S, 17, device=self.device, dtype=torch.float64)
         conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws,
                                        adapters=adapters)
         ws = self.ws
@@ -882,11 +925,13 @@ class DeAOTEngine:
             ws.pred_logits = torch.empty(conv.shape, device=conv.device, dtype=torch.float32)
         out = None
         if output_size is not None:
-            out = torch.empty(1, conv.shape[1], output_size[0], output_size[1], device=conv.device,
+            out = torch.empty(conv.shape[0], conv.shape[1], output_size[0], output_size[1], device=conv.device,
                               dtype=torch.float32)
         # + conv bias, channels beyond the objects -> -1e10 (aot_engine.py:455-457), persistent pred_id_logits
         # (read by the write path), bilinear resize to the output size (:459-463)
-        ops.finish_logits(conv, bias, ws.pred_logits, int(self.obj_nums[0]) + 1, out)
+        for s in range(conv.shape[0]):
+            ops.finish_logits(conv[s:s + 1], bias, ws.pred_logits[s:s + 1], int(self.obj_nums[s]) + 1,
+                              None if out is None else out[s:s + 1])
         self.pred_id_logits = ws.pred_logits
         return ws.pred_logits if out is None else out
 
@@ -1004,10 +1049,10 @@ class DeAOTEngine:
         # the encoder graphs are recorded for the frame format this sequence uses (normalised f32 planes
         # [1, 3, H, W] or decoded u8 pixels [1, H, W, 3]); one format per sequence
         if self._img_sig is not None and self._img_sig[0] == torch.uint8:
-            img = torch.zeros(1, H, W, 3, device=self.device, dtype=torch.uint8)
+            img = torch.zeros(self.S, H, W, 3, device=self.device, dtype=torch.uint8)
         else:
-            img = torch.zeros(1, 3, H, W, device=self.device)
-        label = torch.zeros(H, W, device=self.device)
+            img = torch.zeros(self.S, 3, H, W, device=self.device)
+        label = torch.zeros(self.S, H, W, device=self.device)
         saved = dict(self._graphs)
         self._wait_write()
         sets = {}
@@ -1076,8 +1121,11 @@ class DeAOTEngine:
             in_size = (img.shape[-3:-1] if img.dtype == torch.uint8 else img.shape[2:]) if img is not None \
                 else mask.shape[-2:]
             self.update_size(in_size, curr_enc_embs[-1].shape[2:])
+        if len(self.obj_nums) != self.S:
+            raise ValueError("obj_nums must list one object count per sequence (%d)" % self.S)
         self._id_embed(label)
-        ops.bank_init(self.ws.bank_state, self.frame_step)
+        for s in range(self.S):
+            ops.bank_init(self.ws.bank_state[s], self.frame_step)
         self.T = 1
         self.st = 0
         self.ws.bind(0)

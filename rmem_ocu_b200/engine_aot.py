@@ -131,7 +131,8 @@ class WorkspaceAOT:
         self.dec_in = z(L, 256 * (nl + 1), dt=f32)                 # channels-last decoder input [emb | out_0 | out_1 | out_2]
         self.gn_ws = z(65, dt=torch.float64)                  # 2 x 32 group sums + arrival counter
         self.fg = z(L, dt=f32)
-        self.bank_state = z(_lib.BANK_STATE_WORDS, dt=torch.int32)
+        self.S = 1                                                  # the AOT engine runs one sequence per engine
+        self.bank_state = z(1, _lib.BANK_STATE_WORDS, dt=torch.int32)   # [sequence][words], as the DeAOT workspace
         self.zero_order = z(1, dt=torch.int32)
         self.pred_logits = None
 
@@ -168,7 +169,7 @@ class AOTBodies:
         id_emb next to curr_V / tgt3 of every layer (the A operand of linear_V / linear_VMem)."""
         ws, prep = self.ws, self.prep
         dsts = [(ws.mem[i], 256) for i in range(prep.num_layers)]
-        ops.id_embed(label_hw, prep.id_prefix, prep.id_bias, None, None, prep.n_id_cls, dsts, ws.h, ws.w)
+        ops.id_embed(label_hw[0], prep.id_prefix, prep.id_bias, None, None, prep.n_id_cls, dsts, ws.h, ws.w)
 
     def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):
         """LongShortTermTransformer.forward + SimplifiedTransformerBlock.forward (transformer.py:199-267, 553-692)."""
@@ -207,7 +208,7 @@ class AOTBodies:
         # long-term attention over the bank (TPE as a per-(head, frame) score bias)
         ops.tpe_prepare_mha(ws.kcur[i], prep.cur_pos_emb, prep.mem_pos_emb, ws.qt, ws.tpe_bias)
         mass = ws.mass if record else None
-        self._mha(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state, T, True, 0, mass)
+        self._mha(ws.qt, ws.kbank[i], ws.vbank[i], ws.bank_state[0], T, True, 0, mass)
         # short-term attention over norm4(previous frame's K / V + current K / V)
         ops.layernorm_ex(ws.kprev[i], *Lw["norm4"], xb=ws.kcur[i], out=ws.st_kv, col_out=0)
         ops.layernorm_ex(ws.vprev[i], *Lw["norm4"], xb=mem[:, :256], out=ws.st_kv, col_out=256)
@@ -247,10 +248,10 @@ class AOTBodies:
             for i in range(self.prep.num_layers):
                 srcs += [ws.kcur[i], ws.vcur[i]]
                 dsts += [ws.kbank[i], ws.vbank[i]]
-            ops.bank_append(ws.bank_state, T, -1, srcs, dsts)
+            ops.bank_append(ws.bank_state[0], T, -1, srcs, dsts)
             if do_evict:
                 ops.foreground_prob(self.pred_id_logits[0], ws.fg, ws.h, ws.w)
-                ops.bank_score_evict(ws.bank_state, ws.mass, ws.fg, ws.L, T, self.capacity)
+                ops.bank_score_evict(ws.bank_state[0], ws.mass, ws.fg, ws.L, T, self.capacity)
 
     def _decoder_inputs(self, embs, lstt_out):
         h, w = embs[-1].shape[-2:]

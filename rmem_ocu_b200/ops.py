@@ -182,11 +182,12 @@ def maxpool3s2_nhwc(x, out, bias=None, relu=False):
 def argmax_label(logits, label=None):
     """logits f32 [1, C, H, W] contiguous -> label f32 [1, 1, H, W] (argmax over the object channel)."""
     _chk_cuda(logits)
-    _, C, H, W = logits.shape
+    n, C, H, W = logits.shape
     if label is None:
-        label = torch.empty(1, 1, H, W, device=logits.device, dtype=torch.float32)
-    _lib.check(_lib.lib().rmem_argmax_label(_p(logits), C, H * W, _p(label), _stream()), "rmem_argmax_label")
-    _count("rmem_argmax_label")
+        label = torch.empty(n, 1, H, W, device=logits.device, dtype=torch.float32)
+    for s in range(n):                            # a batch = independent sequences
+        _lib.check(_lib.lib().rmem_argmax_label(_p(logits[s]), C, H * W, _p(label[s]), _stream()), "rmem_argmax_label")
+        _count("rmem_argmax_label")
     return label
 
 

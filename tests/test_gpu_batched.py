@@ -107,3 +107,70 @@ def test_batched_token_groupnorm(lib_built):
         x = torch.cat([xa[s * L:(s + 1) * L], xb[s * L:(s + 1) * L]], 1)
         ref = F.group_norm(x.t().unsqueeze(0), 2, g, b, 1e-5)[0].t()
         assert _rel(out[s * L:(s + 1) * L], ref) < 1e-5, s
+
+
+def _clip(H, W, n, n_obj, seed):
+    g = torch.Generator().manual_seed(seed)
+    imgs = [torch.randn(1, 3, H, W, generator=g) for _ in range(n)]
+    lab = torch.zeros(1, 1, H, W)
+    s = H / 480.0
+    for o in range(1, n_obj + 1):
+        lab[:, :, int((40 + 60 * (o - 1)) * s):int((120 + 60 * (o - 1)) * s),
+            int((100 + 100 * (o - 1)) * s):int((300 + 100 * (o - 1)) * s)] = o
+    return imgs, lab.int()
+
+
+@pytest.mark.parametrize("prefetch", [False, True])
+def test_lockstep_engine_vs_single_engines_and_oracle(lib_built, monkeypatch, prefetch):
+    """DeAOTEngine(n_sequences = 3): three different clips (different object counts) through one set of launches,
+    against (a) three single-sequence engines -- same banks, masks >= 99.9 %, logits to 2e-2 (the stream-K partition
+    and the batched cuDNN algorithms differ) -- and (b) the oracle on every clip: bank indexes equal, masks >= 99.9 %
+    (fp32 cuDNN backbone, so that the comparison measures the batched kernels of the path)."""
+    monkeypatch.setenv("RMEM_ENCODER_DTYPE", "fp32")
+    import torch.nn.functional as F
+    from oracle import restate as R
+    from rmem_ocu_b200.engine import DeAOTEngine
+    from rmem_ocu_b200.model import DeAOTModel, RMemConfig, deterministic_init_
+    H, W, n, latter, S = 240, 432, 9, 2, 3
+    m = DeAOTModel(RMemConfig(latter_mem_len=latter))
+    deterministic_init_(m.state_dict(), 0)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    n_objs = [3, 1, 2]
+    clips = [_clip(H, W, n, n_objs[s], 500 + s) for s in range(S)]
+
+    def run(engine, idxs):
+        imgs = lambda f: torch.cat([clips[s][0][f] for s in idxs]).cuda()
+        labs = torch.cat([clips[s][1] for s in idxs]).cuda()
+        masks, logits = [], []
+        with torch.no_grad():
+            engine.add_reference_frame(imgs(0), labs, obj_nums=[n_objs[s] for s in idxs], frame_step=0)
+            for f in range(1, n):
+                kw = {"next_img": imgs(f + 1)} if (prefetch and f + 1 < n) else {}
+                lg = engine.match_propogate_one_frame(imgs(f), output_size=(H, W), **kw)
+                logits.append(lg.clone())
+                label = torch.argmax(lg, 1, keepdim=True).float()
+                masks.append(label[:, 0].to(torch.uint8).cpu())
+                engine.update_short_term_memory(label)
+        return masks, logits, engine.long_memories_indexes
+
+    bm, bl, bidx = run(DeAOTEngine(m, 0, long_term_mem_gap=2, n_sequences=S), list(range(S)))
+    assert len(bidx) == S and bl[0].shape == (S, 11, H, W)
+    for s in range(S):
+        sm, sl, sidx = run(DeAOTEngine(m, 0, long_term_mem_gap=2), [s])
+        assert bidx[s] == sidx, s
+        for f in range(n - 1):
+            assert ((bl[f][s] - sl[f][0]).norm() / sl[f][0].norm()).item() < 2e-2, (s, f)
+            assert (bm[f][s] == sm[f][0]).float().mean().item() >= 0.999, (s, f)
+        o = R.Engine(sd, True, 1, latter, long_term_mem_gap=2)
+        o_masks = []
+        with torch.no_grad():
+            o.add_reference_frame(clips[s][0][0], clips[s][1], obj_nums=[n_objs[s]], frame_step=0)
+            for f in range(1, n):
+                lg = o.match_propogate_one_frame(clips[s][0][f], output_size=(H, W))
+                label = torch.argmax(lg, 1, keepdim=True).float()
+                o_masks.append(label[0, 0].to(torch.uint8))
+                o.update_short_term_memory(label)
+        assert bidx[s] == o.long_memories_indexes, s
+        agree = [(bm[f][s] == o_masks[f]).float().mean().item() for f in range(n - 1)]
+        print("sequence", s, "lock-step engine vs oracle", [round(a, 5) for a in agree])
+        assert min(agree) >= 0.999, (s, agree)

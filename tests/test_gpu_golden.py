@@ -175,11 +175,11 @@ def test_deaot_block_vs_reference_all_bank_lengths(lib_built):
     try:
         for T in range(1, 13):
             i = _synth.layer_inputs("deaot", T)
-            ops.bank_init(ws.bank_state, 0)
+            ops.bank_init(ws.bank_state[0], 0)
             ws.tgt.copy_(i["tgt"][:, 0].cuda())
             ws.tgt_id.copy_(i["tgt_id"][:, 0].cuda())
-            ws.kbank[1][:T].copy_(bf(i["gK"][:, :, 0]))
-            ws.vbank[1][:T].copy_(bf(torch.cat([i["gV"][:, :, 0], i["gI"][:, :, 0]], -1)))
+            ws.kbank[1][0, :T].copy_(bf(i["gK"][:, :, 0]))                 # banks are [sequence, slot, L, C]
+            ws.vbank[1][0, :T].copy_(bf(torch.cat([i["gV"][:, :, 0], i["gI"][:, :, 0]], -1)))
             ws.kprev[1].copy_(bf(tok(i["lK"])))
             ws.vprev[1].copy_(bf(torch.cat([tok(i["lV"]), tok(i["lI"])], -1)))
             eng._block_forward(1, False, True, T)
@@ -420,7 +420,7 @@ def test_aot_block_vs_reference_all_bank_lengths(lib_built):
     bf = lambda t: t.to(device="cuda", dtype=torch.bfloat16)
     for T in range(1, 13):
         i = _synth.layer_inputs("aot", T)
-        ops.bank_init(ws.bank_state, 0)
+        ops.bank_init(ws.bank_state[0], 0)
         ws.tgt.copy_(i["tgt"][:, 0].cuda())
         ws.pos.copy_(i["pos"][:, 0].cuda())
         ws.kbank[1][:T].copy_(bf(i["gK"][:, :, 0]))
