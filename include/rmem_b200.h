@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 5
+#define RMEM_ABI_VERSION 6
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -278,7 +278,31 @@ int rmem_local_attn(const void* q, const void* k, const void* v, const float* re
  *   rmem_local_attn_scores_batched     q, k [S][h*w][128]; rel_bias [S][h*w][ld_rel]; probs [S][h*w][225]; banded
  *                                      [S][rmem_local_banded_elems(h, w)]
  *   rmem_local_attn_aggregate_batched  v, gate, out [S][h*w][1024]
+ *   rmem_bank_tick_batched             bank_states [S][RMEM_BANK_STATE_WORDS]
+ *   rmem_id_embed_batched              labels [S][H][W]; destination rows [S * h * w][ld]
+ *   rmem_groupnorm_nhwc_batched        x, y [S][P][C], statistics per image; workspace: S consecutive blocks
+ *   rmem_upsample_add_nhwc_batched     x [S][hi*wi][C]; a, out [S][ho*wo][C]
+ *   rmem_finish_logits_batched         conv image s at conv + s * sn; pred [S][C][Hs][Ws]; out [S][C][Ho][Wo];
+ *                                      n_valid_host: HOST i32 [S] valid channels per image; S <= 64
+ *   rmem_pack_image_s2d_batched, rmem_maxpool3s2_nhwc_batched, rmem_argmax_label_batched   image stacks
  */
+int rmem_bank_tick_batched(void* bank_states, int S, void* stream);
+int rmem_id_embed_batched(const float* labels, int H, int W, const float* prefix, const float* bias,
+                          const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                          const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w, int S,
+                          void* stream);
+int rmem_groupnorm_nhwc_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                                int P, int C, int groups, int relu, int S, void* workspace, void* stream);
+int rmem_upsample_add_nhwc_batched(const float* x, int hi, int wi, const float* a, const float* a_bias, float* out,
+                                   int ho, int wo, int C, int S, void* stream);
+int rmem_finish_logits_batched(const float* conv, int64_t sn, int64_t sc, int64_t sy, int64_t sx, const float* bias,
+                               float* pred, int C, int Hs, int Ws, const int32_t* n_valid_host, int S, float* out,
+                               int Ho, int Wo, void* stream);
+int rmem_pack_image_s2d_batched(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                                int H, int W, void* out, int out_f16, int S, void* stream);
+int rmem_maxpool3s2_nhwc_batched(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                                 int S, void* stream);
+int rmem_argmax_label_batched(const float* logits, int C, int HW, float* label, int S, void* stream);
 int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
                          int C, int S, void* stream);
 int rmem_groupnorm_tokens_batched(const float* x_a, int Ca, const float* x_b, const float* gamma, const float* beta,

@@ -67,6 +67,19 @@ _SIGNATURES = {
                                                                      ctypes.c_int64, _c_void_p],
     "rmem_lt_attn_deaot_sk_combine": [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p,
                                       ctypes.c_int64, _c_void_p],
+    "rmem_bank_tick_batched": [_c_void_p, _c_int, _c_void_p],
+    "rmem_id_embed_batched": [_c_void_p, _c_int, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 3 + [_c_int] * 4 +
+                             [_c_void_p],
+    "rmem_groupnorm_nhwc_batched": [_c_void_p] * 5 + [_c_int] * 5 + [_c_void_p] * 2,
+    "rmem_upsample_add_nhwc_batched": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int,
+                                       _c_int, _c_int, _c_void_p],
+    "rmem_finish_logits_batched": [_c_void_p] + [ctypes.c_int64] * 4 + [_c_void_p, _c_void_p] + [_c_int] * 3 +
+                                  [_c_void_p, _c_int, _c_void_p, _c_int, _c_int, _c_void_p],
+    "rmem_pack_image_s2d_batched": [_c_void_p, _c_int, _c_float_p, _c_float_p, _c_int, _c_int, _c_void_p, _c_int,
+                                    _c_int, _c_void_p],
+    "rmem_maxpool3s2_nhwc_batched": [_c_void_p, _c_int, _c_int, _c_int, _c_void_p, _c_int, _c_void_p, _c_int, _c_int,
+                                     _c_void_p],
+    "rmem_argmax_label_batched": [_c_void_p, _c_int, _c_int, _c_void_p, _c_int, _c_void_p],
     "rmem_dwconv5_batched": [_c_void_p, _c_int, _c_int, _c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int,
                              _c_int, _c_int, _c_void_p],
     "rmem_groupnorm_tokens_batched": [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p] * 2,
@@ -121,7 +134,7 @@ class GemmSegment(ctypes.Structure):
                 ("dst_col0", ctypes.c_int32)]
 
 
-ABI_VERSION = 5          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
+ABI_VERSION = 6          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
 MAX_BANK = 16
 MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8

@@ -43,10 +43,14 @@ __global__ void bank_init_kernel(BankState* st, int frame_step) {
   }
 }
 
-__global__ void bank_tick_kernel(BankState* st) { st->cur_frame += 1; }
+__global__ void bank_tick_kernel(BankState* st) { st[blockIdx.x].cur_frame += 1; }   // one state per sequence
 
-int bank_tick_launch(void* state, cudaStream_t stream) {
-  bank_tick_kernel<<<1, 1, 0, stream>>>(static_cast<BankState*>(state));
+int bank_tick_launch(void* state, cudaStream_t stream) { return bank_tick_batched_launch(state, 1, stream); }
+
+int bank_tick_batched_launch(void* state, int S, cudaStream_t stream) {
+  static_assert(sizeof(BankState) == RMEM_BANK_STATE_WORDS * 4, "bank states are stacked RMEM_BANK_STATE_WORDS apart");
+  if (S < 1) return set_error(RMEM_ERR_ARG, "bank_tick: bad batch");
+  bank_tick_kernel<<<S, 1, 0, stream>>>(static_cast<BankState*>(state));
   return check_launch("bank_tick_kernel");
 }
 

@@ -92,6 +92,41 @@ int rmem_lt_attn_deaot_sk_combine(int T, int L, int S, const void* gate, void* o
                                   const void* workspace, int64_t workspace_bytes, void* stream) {
   return lt_attn_sk_combine_launch(T, L, S, gate, out, attn_mass, n_clusters, workspace, workspace_bytes, ST(stream));
 }
+int rmem_bank_tick_batched(void* bank_states, int S, void* stream) {
+  return bank_tick_batched_launch(bank_states, S, ST(stream));
+}
+int rmem_id_embed_batched(const float* labels, int H, int W, const float* prefix, const float* bias,
+                          const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                          const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w, int S,
+                          void* stream) {
+  return id_embed_batched_launch(labels, H, W, prefix, bias, gamma, beta, n_cls, dst_host, ld_host, col0_host, n_dst,
+                                 h, w, S, ST(stream));
+}
+int rmem_groupnorm_nhwc_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
+                                int P, int C, int groups, int relu, int S, void* workspace, void* stream) {
+  return groupnorm_nhwc_batched_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, S, workspace, ST(stream));
+}
+int rmem_upsample_add_nhwc_batched(const float* x, int hi, int wi, const float* a, const float* a_bias, float* out,
+                                   int ho, int wo, int C, int S, void* stream) {
+  return upsample_add_nhwc_batched_launch(x, hi, wi, a, a_bias, out, ho, wo, C, S, ST(stream));
+}
+int rmem_finish_logits_batched(const float* conv, int64_t sn, int64_t sc, int64_t sy, int64_t sx, const float* bias,
+                               float* pred, int C, int Hs, int Ws, const int32_t* n_valid_host, int S, float* out,
+                               int Ho, int Wo, void* stream) {
+  return finish_logits_batched_launch(conv, sn, sc, sy, sx, bias, pred, C, Hs, Ws, n_valid_host, S, out, Ho, Wo,
+                                      ST(stream));
+}
+int rmem_pack_image_s2d_batched(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                                int H, int W, void* out, int out_f16, int S, void* stream) {
+  return pack_image_s2d_batched_launch(img, img_u8_hwc, mean_host, inv_std_host, H, W, out, out_f16, S, ST(stream));
+}
+int rmem_maxpool3s2_nhwc_batched(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                                 int S, void* stream) {
+  return maxpool3s2_nhwc_batched_launch(x, H, W, C, bias, relu, y, f16, S, ST(stream));
+}
+int rmem_argmax_label_batched(const float* logits, int C, int HW, float* label, int S, void* stream) {
+  return argmax_label_batched_launch(logits, C, HW, label, S, ST(stream));
+}
 int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
                          int C, int S, void* stream) {
   return dwconv5_batched_launch(x, ldx, xcol0, wt, y, ldy, ycol0, h, w, C, S, ST(stream));

@@ -19,6 +19,9 @@ namespace rmem {
 __global__ void __launch_bounds__(256)
 gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias, int P, int C, int cpg,
                      int rows_per_cta, double* __restrict__ ws) {
+  // blockIdx.y = image of a batch [S][P][C] (independent sequences): statistics and workspace per image
+  x += static_cast<size_t>(blockIdx.y) * P * C;
+  ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
   const int tpp = C >> 2;                        // threads per pixel (C = 64, 128, 256 -> 16, 32, 64)
   const int ppb = 256 / tpp;                     // pixels per step
   const int c = (threadIdx.x % tpp) * 4;
@@ -57,6 +60,9 @@ __global__ void __launch_bounds__(256)
 gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
                      int P, int C, int cpg, int relu, double* __restrict__ ws) {
+  x += static_cast<size_t>(blockIdx.y) * P * C;
+  y += static_cast<size_t>(blockIdx.y) * P * C;
+  ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   const double cnt = static_cast<double>(cpg) * P;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
@@ -87,21 +93,28 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_
 
 int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
                           int P, int C, int groups, int relu, void* workspace, cudaStream_t stream) {
-  if (groups < 1 || groups > 32 || (C % groups) || (C != 64 && C != 128 && C != 256) || P < 1)
+  return groupnorm_nhwc_batched_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, 1, workspace, stream);
+}
+
+int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta,
+                                  float* y, int P, int C, int groups, int relu, int S, void* workspace,
+                                  cudaStream_t stream) {
+  if (groups < 1 || groups > 32 || (C % groups) || (C != 64 && C != 128 && C != 256) || P < 1 || S < 1 || S > 65535)
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: C must be 64 / 128 / 256");
   const int cpg = C / groups;
   if ((cpg & (cpg - 1)) || cpg < 4 || cpg > 32)
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: channels per group must be a power of two in [4, 32]");
-  int rows = (P + 591) / 592;                    // ~4 CTAs per SM at large P ...
+  const int per = (592 + S - 1) / S;             // ~4 CTAs per SM at large P over the whole batch ...
+  int rows = (P + per - 1) / per;
   if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
-  gn_nhwc_stats_kernel<<<(P + rows - 1) / rows, 256, 0, stream>>>(x, pre_bias, P, C, cpg, rows,
-                                                                 static_cast<double*>(workspace));
+  gn_nhwc_stats_kernel<<<dim3((P + rows - 1) / rows, S), 256, 0, stream>>>(x, pre_bias, P, C, cpg, rows,
+                                                                          static_cast<double*>(workspace));
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   int blocks = static_cast<int>((total4 + 255) / 256);
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  gn_nhwc_apply_kernel<<<blocks, 256, 0, stream>>>(x, pre_bias, gamma, beta, y, P, C, cpg, relu,
-                                                   static_cast<double*>(workspace));
+  if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
+  gn_nhwc_apply_kernel<<<dim3(blocks, S), 256, 0, stream>>>(x, pre_bias, gamma, beta, y, P, C, cpg, relu,
+                                                            static_cast<double*>(workspace));
   return check_launch("gn_nhwc_apply_kernel");
 }
 
@@ -110,6 +123,10 @@ int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* ga
 __global__ void __launch_bounds__(256)
 upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const float* __restrict__ a,
                          const float* __restrict__ a_bias, float* __restrict__ out, int ho, int wo, int C) {
+  // blockIdx.y = image of a batch: xin [S][hi*wi][C], a / out [S][ho*wo][C]
+  xin += static_cast<size_t>(blockIdx.y) * hi * wi * C;
+  if (a) a += static_cast<size_t>(blockIdx.y) * ho * wo * C;
+  out += static_cast<size_t>(blockIdx.y) * ho * wo * C;
   const int c4 = C / 4;
   const size_t total = static_cast<size_t>(ho) * wo * c4;
   const float sy = ho > 1 ? static_cast<float>(hi - 1) / static_cast<float>(ho - 1) : 0.f;
@@ -143,12 +160,17 @@ upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const fl
 
 int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
                              int ho, int wo, int C, cudaStream_t stream) {
-  if ((C % 4) || hi < 1 || wi < 1 || ho < 1 || wo < 1)
+  return upsample_add_nhwc_batched_launch(xin, hi, wi, a, a_bias, out, ho, wo, C, 1, stream);
+}
+
+int upsample_add_nhwc_batched_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
+                                     int ho, int wo, int C, int S, cudaStream_t stream) {
+  if ((C % 4) || hi < 1 || wi < 1 || ho < 1 || wo < 1 || S < 1 || S > 65535)
     return set_error(RMEM_ERR_ARG, "upsample_add_nhwc: C must be a multiple of 4");
   const size_t total = static_cast<size_t>(ho) * wo * (C / 4);
   int blocks = static_cast<int>((total + 255) / 256);
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  upsample_add_nhwc_kernel<<<blocks, 256, 0, stream>>>(xin, hi, wi, a, a_bias, out, ho, wo, C);
+  if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
+  upsample_add_nhwc_kernel<<<dim3(blocks, S), 256, 0, stream>>>(xin, hi, wi, a, a_bias, out, ho, wo, C);
   return check_launch("upsample_add_nhwc_kernel");
 }
 
@@ -156,12 +178,21 @@ int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, c
 // decode_current_logits tail (aot_engine.py:451-463): logits = conv_out + bias, channels beyond the
 // sequence's objects masked to -1e10, kept as pred_id_logits [C][Hs][Ws]; then the bilinear
 // (align_corners = True) resize to the output size, [C][Ho][Wo].
+struct ValidCounts {
+  int n[64];                 // valid channels (objects + 1) per image of the batch
+};
+
 __global__ void __launch_bounds__(256)
-finish_logits_kernel(const float* __restrict__ conv, long long sc, long long sy, long long sx,
-                     const float* __restrict__ bias, float* __restrict__ pred, int C, int Hs, int Ws, int n_valid) {
+finish_logits_kernel(const float* __restrict__ conv, long long sn, long long sc, long long sy, long long sx,
+                     const float* __restrict__ bias, float* __restrict__ pred, int C, int Hs, int Ws,
+                     const ValidCounts valid) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int total = C * Hs * Ws;
   if (i >= total) return;
+  // blockIdx.y = image of a batch: conv strided by sn, pred [S][C][Hs][Ws]
+  conv += blockIdx.y * sn;
+  pred += static_cast<size_t>(blockIdx.y) * total;
+  const int n_valid = valid.n[blockIdx.y];
   const int c = i / (Hs * Ws), r = i - c * (Hs * Ws);
   const int y = r / Ws, x = r - y * Ws;
   const float v = conv[c * sc + y * sy + x * sx] + (bias ? bias[c] : 0.f);
@@ -171,6 +202,8 @@ finish_logits_kernel(const float* __restrict__ conv, long long sc, long long sy,
 __global__ void __launch_bounds__(256)
 upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, float* __restrict__ out, int Ho,
                        int Wo) {
+  pred += static_cast<size_t>(blockIdx.y) * C * Hs * Ws;
+  out += static_cast<size_t>(blockIdx.y) * C * Ho * Wo;
   // thread = 4 consecutive output pixels of one row, all C channels (weights computed once per pixel)
   const int wq = (Wo + 3) / 4;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -209,13 +242,23 @@ upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, fl
 
 int finish_logits_launch(const float* conv, long long sc, long long sy, long long sx, const float* bias, float* pred,
                          int C, int Hs, int Ws, int n_valid, float* out, int Ho, int Wo, cudaStream_t stream) {
-  if (C < 1 || Hs < 1 || Ws < 1) return set_error(RMEM_ERR_ARG, "finish_logits: bad shape");
+  return finish_logits_batched_launch(conv, 0, sc, sy, sx, bias, pred, C, Hs, Ws, &n_valid, 1, out, Ho, Wo, stream);
+}
+
+int finish_logits_batched_launch(const float* conv, long long sn, long long sc, long long sy, long long sx,
+                                 const float* bias, float* pred, int C, int Hs, int Ws, const int* n_valid_host, int S,
+                                 float* out, int Ho, int Wo, cudaStream_t stream) {
+  if (C < 1 || Hs < 1 || Ws < 1 || S < 1 || S > 64 || !n_valid_host)
+    return set_error(RMEM_ERR_ARG, "finish_logits: bad shape (at most 64 images per call)");
+  ValidCounts valid;
+  for (int s = 0; s < 64; ++s) valid.n[s] = s < S ? n_valid_host[s] : 0;
   const int total = C * Hs * Ws;
-  finish_logits_kernel<<<(total + 255) / 256, 256, 0, stream>>>(conv, sc, sy, sx, bias, pred, C, Hs, Ws, n_valid);
+  finish_logits_kernel<<<dim3((total + 255) / 256, S), 256, 0, stream>>>(conv, sn, sc, sy, sx, bias, pred, C, Hs, Ws,
+                                                                        valid);
   if (int r = check_launch("finish_logits_kernel")) return r;
   if (out) {
     const int n = Ho * ((Wo + 3) / 4);
-    upsample_logits_kernel<<<(n + 255) / 256, 256, 0, stream>>>(pred, C, Hs, Ws, out, Ho, Wo);
+    upsample_logits_kernel<<<dim3((n + 255) / 256, S), 256, 0, stream>>>(pred, C, Hs, Ws, out, Ho, Wo);
     return check_launch("upsample_logits_kernel");
   }
   return RMEM_OK;
@@ -272,6 +315,9 @@ pack_image_s2d_kernel(const void* __restrict__ img_, PackNorm nrm, int H, int W,
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int Wp = Ws + 3;
   if (i >= (Hs + 3) * Wp) return;
+  // blockIdx.y = image of a batch: img [S][3][H][W] f32 or [S][H][W][3] u8, out [S][Hs+3][Ws+3][16]
+  img_ = static_cast<const uint8_t*>(img_) + static_cast<size_t>(blockIdx.y) * 3 * H * W * (kU8 ? 1 : 4);
+  out += static_cast<size_t>(blockIdx.y) * (Hs + 3) * Wp * 8;
   const int yp = i / Wp - 2, xp = i % Wp - 2;
   float v[16];
 #pragma unroll
@@ -307,7 +353,12 @@ pack_image_s2d_kernel(const void* __restrict__ img_, PackNorm nrm, int H, int W,
 
 int pack_image_s2d_ex_launch(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
                              int H, int W, void* out, int out_f16, cudaStream_t stream) {
-  if (H < 1 || W < 1) return set_error(RMEM_ERR_ARG, "pack_image_s2d: bad shape");
+  return pack_image_s2d_batched_launch(img, img_u8_hwc, mean_host, inv_std_host, H, W, out, out_f16, 1, stream);
+}
+
+int pack_image_s2d_batched_launch(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                                  int H, int W, void* out, int out_f16, int S, cudaStream_t stream) {
+  if (H < 1 || W < 1 || S < 1 || S > 65535) return set_error(RMEM_ERR_ARG, "pack_image_s2d: bad shape");
   if (img_u8_hwc && (!mean_host || !inv_std_host))
     return set_error(RMEM_ERR_ARG, "pack_image_s2d: u8 input needs mean / inv_std");
   PackNorm nrm = {{0.f, 0.f, 0.f}, {1.f, 1.f, 1.f}};
@@ -315,7 +366,7 @@ int pack_image_s2d_ex_launch(const void* img, int img_u8_hwc, const float* mean_
     for (int c = 0; c < 3; ++c) { nrm.mean[c] = mean_host[c]; nrm.inv_std[c] = inv_std_host[c]; }
   const int Hs = (H + 1) / 2, Ws = (W + 1) / 2;
   const int n = (Hs + 3) * (Ws + 3);
-  const int grid = (n + 255) / 256;
+  const dim3 grid((n + 255) / 256, S);
   if (out_f16) {
     if (img_u8_hwc) pack_image_s2d_kernel<__half2, true><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__half2*>(out));
     else pack_image_s2d_kernel<__half2, false><<<grid, 256, 0, stream>>>(img, nrm, H, W, Hs, Ws, static_cast<__half2*>(out));
@@ -340,6 +391,8 @@ maxpool3s2_nhwc_kernel(const T2* __restrict__ x, int H, int W, int C8, const flo
                        int relu, T2* __restrict__ y, int Ho, int Wo) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Ho * Wo * C8) return;
+  x += static_cast<size_t>(blockIdx.y) * H * W * C8 * 4;          // blockIdx.y = image of a batch
+  y += static_cast<size_t>(blockIdx.y) * Ho * Wo * C8 * 4;
   const int c8 = i % C8, pix = i / C8;
   const int ox = pix % Wo, oy = pix / Wo;
   const T2 ninf = Pair16<T2>::from(-INFINITY, -INFINITY);
@@ -376,14 +429,21 @@ maxpool3s2_nhwc_kernel(const T2* __restrict__ x, int H, int W, int C8, const flo
 
 int maxpool3s2_nhwc_ex_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
                               cudaStream_t stream) {
-  if (H < 1 || W < 1 || C < 8 || (C & 7)) return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
+  return maxpool3s2_nhwc_batched_launch(x, H, W, C, bias, relu, y, f16, 1, stream);
+}
+
+int maxpool3s2_nhwc_batched_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                                   int S, cudaStream_t stream) {
+  if (H < 1 || W < 1 || C < 8 || (C & 7) || S < 1 || S > 65535)
+    return set_error(RMEM_ERR_ARG, "maxpool3s2: bad shape (C % 8 != 0)");
   const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
   const int n = Ho * Wo * (C / 8);
+  const dim3 grid((n + 255) / 256, S);
   if (f16)
-    maxpool3s2_nhwc_kernel<__half2><<<(n + 255) / 256, 256, 0, stream>>>(static_cast<const __half2*>(x), H, W, C / 8, bias,
-                                                                        relu, static_cast<__half2*>(y), Ho, Wo);
+    maxpool3s2_nhwc_kernel<__half2><<<grid, 256, 0, stream>>>(static_cast<const __half2*>(x), H, W, C / 8, bias,
+                                                             relu, static_cast<__half2*>(y), Ho, Wo);
   else
-    maxpool3s2_nhwc_kernel<__nv_bfloat162><<<(n + 255) / 256, 256, 0, stream>>>(
+    maxpool3s2_nhwc_kernel<__nv_bfloat162><<<grid, 256, 0, stream>>>(
         static_cast<const __nv_bfloat162*>(x), H, W, C / 8, bias, relu, static_cast<__nv_bfloat162*>(y), Ho, Wo);
   return check_launch("maxpool3s2_nhwc_kernel");
 }
@@ -399,6 +459,8 @@ __global__ void __launch_bounds__(256)
 argmax_label_kernel(const float* __restrict__ logits, int C, int HW, float* __restrict__ label) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= HW) return;
+  logits += static_cast<size_t>(blockIdx.y) * C * HW;              // blockIdx.y = image of a batch
+  label += static_cast<size_t>(blockIdx.y) * HW;
   if (i + 3 < HW && (HW & 3) == 0) {
     float4 best = *reinterpret_cast<const float4*>(logits + i);
     float4 arg = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -424,9 +486,13 @@ argmax_label_kernel(const float* __restrict__ logits, int C, int HW, float* __re
 }
 
 int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaStream_t stream) {
-  if (C < 1 || HW < 1) return set_error(RMEM_ERR_ARG, "argmax_label: bad shape");
+  return argmax_label_batched_launch(logits, C, HW, label, 1, stream);
+}
+
+int argmax_label_batched_launch(const float* logits, int C, int HW, float* label, int S, cudaStream_t stream) {
+  if (C < 1 || HW < 1 || S < 1 || S > 65535) return set_error(RMEM_ERR_ARG, "argmax_label: bad shape");
   const int n = (HW + 3) / 4;
-  argmax_label_kernel<<<(n + 255) / 256, 256, 0, stream>>>(logits, C, HW, label);
+  argmax_label_kernel<<<dim3((n + 255) / 256, S), 256, 0, stream>>>(logits, C, HW, label);
   return check_launch("argmax_label_kernel");
 }
 

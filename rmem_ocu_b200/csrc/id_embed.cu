@@ -31,15 +31,18 @@ struct IdEmbedParams {
 __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
   __shared__ int cls_sh[kIdK][kIdK + 1];
   __shared__ float red[2][kIdC / 32];
-  const int tok = blockIdx.x;
+  // blockIdx.x = (sequence, token): label maps stacked [S][H][W], destination rows stacked [S][h*w]
+  const int seq = blockIdx.x / (p.h * p.w);
+  const int tok = blockIdx.x - seq * (p.h * p.w);
   const int ty = tok / p.w, tx = tok - ty * p.w;
   const int c = threadIdx.x;
+  const float* label = p.label + static_cast<size_t>(seq) * p.H * p.W;
   for (int i = threadIdx.x; i < kIdK * kIdK; i += kIdC) {
     const int ky = i / kIdK, kx = i - ky * kIdK;
     const int y = ty * kIdStride - kIdPad + ky, x = tx * kIdStride - kIdPad + kx;
     int cls = -1;
     if (y >= 0 && y < p.H && x >= 0 && x < p.W) {
-      const int l = __float2int_rn(p.label[static_cast<size_t>(y) * p.W + x]);
+      const int l = __float2int_rn(label[static_cast<size_t>(y) * p.W + x]);
       if (l >= 0 && l < p.n_cls - 1) cls = l;
       else if (l == 255) cls = p.n_cls - 1;
     }
@@ -133,14 +136,20 @@ __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
     out = d * rsqrtf(var * (1.f / kIdC) + 1e-5f) * p.gamma[c] + p.beta[c];
   }
   const __nv_bfloat16 ob = __float2bfloat16(out);
-  for (int i = 0; i < p.n_dst; ++i) p.dst[i][static_cast<size_t>(tok) * p.ld[i] + p.col0[i] + c] = ob;
+  for (int i = 0; i < p.n_dst; ++i) p.dst[i][static_cast<size_t>(blockIdx.x) * p.ld[i] + p.col0[i] + c] = ob;
 }
 
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
                     const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
                     const int* col0, int n_dst, int h, int w, cudaStream_t stream) {
+  return id_embed_batched_launch(label, H, W, prefix, bias, gamma, beta, n_cls, dst, ld, col0, n_dst, h, w, 1, stream);
+}
+
+int id_embed_batched_launch(const float* label, int H, int W, const float* prefix, const float* bias,
+                            const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
+                            const int* col0, int n_dst, int h, int w, int S, cudaStream_t stream) {
   if (n_dst < 1 || n_dst > 4 || n_cls < 2 || h != (H + 2 * kIdPad - kIdK) / kIdStride + 1 ||
-      w != (W + 2 * kIdPad - kIdK) / kIdStride + 1)
+      w != (W + 2 * kIdPad - kIdK) / kIdStride + 1 || S < 1)
     return set_error(RMEM_ERR_ARG, "id_embed: bad destination count / class count / token grid");
   IdEmbedParams p;
   p.label = label; p.prefix = prefix; p.bias = bias; p.gamma = gamma; p.beta = beta;
@@ -150,7 +159,7 @@ int id_embed_launch(const float* label, int H, int W, const float* prefix, const
     p.ld[i] = i < n_dst ? ld[i] : 0;
     p.col0[i] = i < n_dst ? col0[i] : 0;
   }
-  id_embed_kernel<<<h * w, kIdC, 0, stream>>>(p);
+  id_embed_kernel<<<S * h * w, kIdC, 0, stream>>>(p);
   return check_launch("id_embed_kernel");
 }
 

@@ -116,6 +116,23 @@ int id_embed_launch(const float* label, int H, int W, const float* prefix, const
                     const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
                     const int* col0, int n_dst, int h, int w, cudaStream_t stream);
 int bank_init_launch(void* state, int frame_step, cudaStream_t stream);
+int bank_tick_batched_launch(void* state, int S, cudaStream_t stream);
+int id_embed_batched_launch(const float* label, int H, int W, const float* prefix, const float* bias,
+                            const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
+                            const int* col0, int n_dst, int h, int w, int S, cudaStream_t stream);
+int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta,
+                                  float* y, int P, int C, int groups, int relu, int S, void* workspace,
+                                  cudaStream_t stream);
+int upsample_add_nhwc_batched_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
+                                     int ho, int wo, int C, int S, cudaStream_t stream);
+int finish_logits_batched_launch(const float* conv, long long sn, long long sc, long long sy, long long sx,
+                                 const float* bias, float* pred, int C, int Hs, int Ws, const int* n_valid_host, int S,
+                                 float* out, int Ho, int Wo, cudaStream_t stream);
+int pack_image_s2d_batched_launch(const void* img, int img_u8_hwc, const float* mean_host, const float* inv_std_host,
+                                  int H, int W, void* out, int out_f16, int S, cudaStream_t stream);
+int maxpool3s2_nhwc_batched_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
+                                   int S, cudaStream_t stream);
+int argmax_label_batched_launch(const float* logits, int C, int HW, float* label, int S, cudaStream_t stream);
 int bank_append_launch(void* state, int T, int frame_step, const void* const* src, void* const* dst,
                        const int64_t* row_bytes, int n_tensors, cudaStream_t stream);
 int bank_score_evict_launch(void* state, const float* attn_mass, const float* fg, int L, int T_old,

@@ -151,11 +151,8 @@ class InferenceFPN:
         w, b, g, be = self.w[name]
         y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
         t = self._tok(y)
-        n = y.shape[0]
-        P = t.shape[0] // n
-        for s in range(n):                       # statistics per image (a batch = independent sequences)
-            ts = t[s * P:(s + 1) * P]
-            ops.groupnorm_nhwc(ts, g, be, ts, 8, True, self._ws[s], pre_bias=b)   # in place
+        # statistics per image (a batch = independent sequences), in place
+        ops.groupnorm_nhwc(t, g, be, t, 8, True, self._ws, pre_bias=b, S=y.shape[0])
         return y
 
     ADAPTERS = (("adapter_16x", -2), ("adapter_8x", -3), ("adapter_4x", -4))
@@ -191,11 +188,7 @@ class InferenceFPN:
             ta = self._tok(a)
         hi, wi = x.shape[-2:]
         ho, wo = a.shape[-2:]
-        n = x.shape[0]
-        tx = self._tok(x)
-        for s in range(n):
-            tas = ta[s * ho * wo:(s + 1) * ho * wo]
-            ops.upsample_add_nhwc(tx[s * hi * wi:(s + 1) * hi * wi], hi, wi, tas, tas, ho, wo, a_bias=b)   # in place
+        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b, S=x.shape[0])   # in place
         return a
 
     def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None):
@@ -325,8 +318,7 @@ class InferenceResNet:
             x = torch.empty(n, (h + 1) // 2 + 3, (w + 1) // 2 + 3, 16, device=img.device,
                             dtype=self.dtype).permute(0, 3, 1, 2)
             # f32 planes / u8 pixels -> 16-bit space-to-depth image, conv padding built in
-            for s in range(n):
-                ops.pack_image_s2d(img[s:s + 1], x[s:s + 1], self.U8_MEAN, self.U8_STD)
+            ops.pack_image_s2d(img, x, self.U8_MEAN, self.U8_STD)
         elif self.dtype == BF16 and n == 1 and img.dtype == torch.float32:
             x = torch.empty(1, 8, h, w, device=img.device, dtype=BF16, memory_format=torch.channels_last)
             ops.pack_image(img, x)                  # f32 planes -> bf16 channels-last, channels 3..7 = 0
@@ -348,8 +340,7 @@ class InferenceResNet:
             c_, h_, w_ = x.shape[1:]
             if x.stride()[1:] != (1, w_ * c_, c_):                   # cuDNN returns NHWC strides; never copy then
                 x = x.contiguous(memory_format=torch.channels_last)
-            for s in range(n):
-                ops.maxpool3s2_nhwc(x[s:s + 1], pooled[s:s + 1], self.conv1_bias_f32 if s2d else None, s2d)
+            ops.maxpool3s2_nhwc(x, pooled, self.conv1_bias_f32 if s2d else None, s2d)
             x = pooled
         else:
             x = F.max_pool2d(x, 3, 2, 1)
@@ -680,11 +671,8 @@ class DeAOTEngine:
         for every layer's ID_V GEMM."""
         ws, prep = self.ws, self.prep
         g, b = prep.id_norm
-        L = ws.L
-        for s in range(ws.S):                    # label_hw: [S, H, W]
-            rows = slice(s * L, (s + 1) * L)
-            dsts = [(ws.id_emb[rows], 0)] + [(ws.idcat[i][rows], 256) for i in range(prep.num_layers)]
-            ops.id_embed(label_hw[s], prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)
+        dsts = [(ws.id_emb, 0)] + [(ws.idcat[i], 256) for i in range(prep.num_layers)]
+        ops.id_embed(label_hw, prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)   # [S, H, W] labels
 
     def _label_map(self, mask):
         """Accepts [H,W], [S,H,W] or [S,1,H,W] label maps -> [S, H, W]; soft / one-hot masks are a training-only
@@ -860,8 +848,7 @@ class DeAOTEngine:
             # the device frame counter: it has to be complete before the counter ticks
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
-        for s in range(self.ws.S):
-            ops.bank_tick(self.ws.bank_state[s])                        # frame_step += 1 on the device
+        ops.bank_tick(self.ws.bank_state)                               # frame_step += 1 on the device (every sequence)
         embs = self._encode_body(img) if img_embs is None else img_embs
         embs, pre = (embs[:4], embs[4:]) if len(embs) == 7 else (embs, None)
         lstt_out = self._lstt_forward(embs[-1], False, True, T)
@@ -929,9 +916,7 @@ class DeAOTEngine:
                               dtype=torch.float32)
         # + conv bias, channels beyond the objects -> -1e10 (aot_engine.py:455-457), persistent pred_id_logits
         # (read by the write path), bilinear resize to the output size (:459-463)
-        for s in range(conv.shape[0]):
-            ops.finish_logits(conv[s:s + 1], bias, ws.pred_logits[s:s + 1], int(self.obj_nums[s]) + 1,
-                              None if out is None else out[s:s + 1])
+        ops.finish_logits(conv, bias, ws.pred_logits, [int(n) + 1 for n in self.obj_nums], out)
         self.pred_id_logits = ws.pred_logits
         return ws.pred_logits if out is None else out
 

@@ -97,32 +97,41 @@ def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace, S=1):
     _count("rmem_groupnorm_tokens")
 
 
-def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace, pre_bias=None):
-    """GroupNorm(+ReLU) of (x + pre_bias), a channels-last [1, C, H, W] f32 tensor viewed as [H*W, C]."""
-    P, C = x.shape
-    _lib.check(_lib.lib().rmem_groupnorm_nhwc(_p(x), _p(pre_bias), _p(gamma), _p(beta), _p(y), P, C, groups,
-                                              1 if relu else 0, _p(workspace), _stream()), "rmem_groupnorm_nhwc")
+def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace, pre_bias=None, S=1):
+    """GroupNorm(+ReLU) of (x + pre_bias), a channels-last [S, C, H, W] f32 tensor viewed as [S*H*W, C]; statistics
+    per image, workspace: S consecutive (2 * groups + 1)-double blocks."""
+    P, C = x.shape[0] // S, x.shape[1]
+    _lib.check(_lib.lib().rmem_groupnorm_nhwc_batched(_p(x), _p(pre_bias), _p(gamma), _p(beta), _p(y), P, C, groups,
+                                                      1 if relu else 0, S, _p(workspace), _stream()),
+               "rmem_groupnorm_nhwc_batched")
     _count("rmem_groupnorm_nhwc")
 
 
-def upsample_add_nhwc(x, hi, wi, a, out, ho, wo, a_bias=None):
-    """out = a + a_bias + bilinear_align_corners(x); x f32 [hi*wi, C], a / out f32 [ho*wo, C]."""
+def upsample_add_nhwc(x, hi, wi, a, out, ho, wo, a_bias=None, S=1):
+    """out = a + a_bias + bilinear_align_corners(x); x f32 [S*hi*wi, C], a / out f32 [S*ho*wo, C]."""
     C = x.shape[1]
-    _lib.check(_lib.lib().rmem_upsample_add_nhwc(_p(x), hi, wi, _p(a), _p(a_bias), _p(out), ho, wo, C, _stream()),
-               "rmem_upsample_add_nhwc")
+    _lib.check(_lib.lib().rmem_upsample_add_nhwc_batched(_p(x), hi, wi, _p(a), _p(a_bias), _p(out), ho, wo, C, S,
+                                                         _stream()), "rmem_upsample_add_nhwc_batched")
     _count("rmem_upsample_add_nhwc")
 
 
 def finish_logits(conv, bias, pred, n_valid, out=None):
-    """conv: f32 [1, C, Hs, Ws] (any strides) -> pred f32 [1, C, Hs, Ws] contiguous (+ bias, channels >= n_valid
-    set to -1e10) and, if given, out f32 [1, C, Ho, Wo] = bilinear align_corners resize of pred."""
-    _, C, Hs, Ws = conv.shape
+    """conv: f32 [S, C, Hs, Ws] (any strides) -> pred f32 [S, C, Hs, Ws] contiguous (+ bias, channels >= n_valid[s]
+    set to -1e10) and, if given, out f32 [S, C, Ho, Wo] = bilinear align_corners resize of pred.  n_valid: an int
+    (S = 1) or a list of S ints."""
+    S, C, Hs, Ws = conv.shape
     Ho, Wo = (out.shape[-2], out.shape[-1]) if out is not None else (0, 0)
-    _lib.check(_lib.lib().rmem_finish_logits(_p(conv), conv.stride(1), conv.stride(2), conv.stride(3), _p(bias),
-                                             _p(pred), C, Hs, Ws, n_valid, _p(out), Ho, Wo, _stream()),
-               "rmem_finish_logits")
-    global LAUNCHES
-    LAUNCHES += 2 if out is not None else 1
+    nv = [int(n_valid)] * S if not isinstance(n_valid, (list, tuple)) else [int(v) for v in n_valid]
+    for s0 in range(0, S, 64):                    # the kernel takes up to 64 images per call
+        s1 = min(S, s0 + 64)
+        arr = (ctypes.c_int32 * (s1 - s0))(*nv[s0:s1])
+        _lib.check(_lib.lib().rmem_finish_logits_batched(_p(conv[s0:]), conv.stride(0), conv.stride(1), conv.stride(2),
+                                                         conv.stride(3), _p(bias), _p(pred[s0:]), C, Hs, Ws,
+                                                         ctypes.cast(arr, ctypes.c_void_p), s1 - s0,
+                                                         _p(out[s0:]) if out is not None else None, Ho, Wo, _stream()),
+                   "rmem_finish_logits_batched")
+        global LAUNCHES
+        LAUNCHES += 2 if out is not None else 1
 
 
 def pack_image(img, out):
@@ -143,6 +152,7 @@ def pack_image_s2d(img, out, mean=None, std=None):
     if not img.is_contiguous():
         img = img.contiguous()
     u8 = img.dtype == torch.uint8
+    S = out.shape[0]
     if u8:
         if img.shape[-1] != 3:
             raise _lib.RmemError("pack_image_s2d: u8 frames are interleaved [H, W, 3]")
@@ -158,9 +168,11 @@ def pack_image_s2d(img, out, mean=None, std=None):
         m3 = s3 = None
     if out.dtype not in (torch.bfloat16, torch.float16):
         raise _lib.RmemError("pack_image_s2d: out must be bf16 or fp16")
-    _lib.check(_lib.lib().rmem_pack_image_s2d_ex(_p(img), int(u8), m3, s3, H, W, _p(out),
-                                                 int(out.dtype == torch.float16), _stream()),
-               "rmem_pack_image_s2d_ex")
+    if img.numel() != S * 3 * H * W:
+        raise _lib.RmemError("pack_image_s2d: image / output batch mismatch")
+    _lib.check(_lib.lib().rmem_pack_image_s2d_batched(_p(img), int(u8), m3, s3, H, W, _p(out),
+                                                      int(out.dtype == torch.float16), S, _stream()),
+               "rmem_pack_image_s2d_batched")
     _count("rmem_pack_image_s2d")
 
 
@@ -169,13 +181,14 @@ def maxpool3s2_nhwc(x, out, bias=None, relu=False):
     MaxPool2d(3, 2, 1) of the encoder stem; with bias (f32 [C]) / relu: relu(maxpool(x) + bias)."""
     _chk_cuda(x, out)
     n, C, H, W = x.shape
-    if n != 1 or x.dtype not in (torch.bfloat16, torch.float16) or x.stride()[1:] != (1, W * C, C):
-        raise ValueError("maxpool3s2_nhwc: expects one bf16 / fp16 channels-last image")
+    if (x.dtype not in (torch.bfloat16, torch.float16) or x.stride()[1:] != (1, W * C, C)
+            or (n > 1 and x.stride(0) != H * W * C)):
+        raise ValueError("maxpool3s2_nhwc: expects bf16 / fp16 channels-last images")
     if out.dtype != x.dtype:
         raise ValueError("maxpool3s2_nhwc: out must have the input's dtype")
-    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc_ex(_p(x), H, W, C, _p(bias), 1 if relu else 0, _p(out),
-                                                  int(x.dtype == torch.float16), _stream()),
-               "rmem_maxpool3s2_nhwc_ex")
+    _lib.check(_lib.lib().rmem_maxpool3s2_nhwc_batched(_p(x), H, W, C, _p(bias), 1 if relu else 0, _p(out),
+                                                       int(x.dtype == torch.float16), n, _stream()),
+               "rmem_maxpool3s2_nhwc_batched")
     _count("rmem_maxpool3s2_nhwc")
 
 
@@ -185,9 +198,9 @@ def argmax_label(logits, label=None):
     n, C, H, W = logits.shape
     if label is None:
         label = torch.empty(n, 1, H, W, device=logits.device, dtype=torch.float32)
-    for s in range(n):                            # a batch = independent sequences
-        _lib.check(_lib.lib().rmem_argmax_label(_p(logits[s]), C, H * W, _p(label[s]), _stream()), "rmem_argmax_label")
-        _count("rmem_argmax_label")
+    _lib.check(_lib.lib().rmem_argmax_label_batched(_p(logits), C, H * W, _p(label), n, _stream()),
+               "rmem_argmax_label_batched")
+    _count("rmem_argmax_label")
     return label
 
 
@@ -279,7 +292,9 @@ def bank_init(state, frame_step):
 
 
 def bank_tick(state):
-    _lib.check(_lib.lib().rmem_bank_tick(_p(state), _stream()), "rmem_bank_tick")
+    """state: int32 [BANK_STATE_WORDS] or a stack [S, BANK_STATE_WORDS] (one launch)."""
+    S = state.shape[0] if state.dim() == 2 else 1
+    _lib.check(_lib.lib().rmem_bank_tick_batched(_p(state), S, _stream()), "rmem_bank_tick_batched")
     _count("rmem_bank_tick")
 
 
@@ -296,15 +311,17 @@ def id_prefix_table(weight):
 
 
 def id_embed(label, prefix, bias, gamma, beta, n_cls, dsts, h, w):
-    """label: f32 [H, W]; dsts: list of (bf16 tensor [h*w, ld], col0)."""
+    """label: f32 [H, W] or a stack [S, H, W]; dsts: list of (bf16 tensor [S*h*w, ld], col0)."""
     H, W = label.shape[-2:]
+    S = label.shape[0] if label.dim() == 3 else 1
     n = len(dsts)
     dp = (ctypes.c_void_p * n)(*[d.data_ptr() for d, _ in dsts])
     ld = (ctypes.c_int32 * n)(*[d.stride(0) for d, _ in dsts])
     c0 = (ctypes.c_int32 * n)(*[c for _, c in dsts])
-    _lib.check(_lib.lib().rmem_id_embed(_p(label), H, W, _p(prefix), _p(bias), _p(gamma), _p(beta), n_cls,
-                                        ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(ld, ctypes.c_void_p),
-                                        ctypes.cast(c0, ctypes.c_void_p), n, h, w, _stream()), "rmem_id_embed")
+    _lib.check(_lib.lib().rmem_id_embed_batched(_p(label), H, W, _p(prefix), _p(bias), _p(gamma), _p(beta), n_cls,
+                                                ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(ld, ctypes.c_void_p),
+                                                ctypes.cast(c0, ctypes.c_void_p), n, h, w, S, _stream()),
+               "rmem_id_embed_batched")
     _count("rmem_id_embed")
 
 
