@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 6
+#define RMEM_ABI_VERSION 7
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -70,6 +70,17 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
                                const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
                                int chunks_per_frame, const void* gate, void* out,
                                float* attn_mass, void* stream);
+
+/* The same operator when the keys are ONE frame (a layer's self-attention, attention.py:174-206 called from
+ * transformer.py:1208-1216; or a bank that holds one frame and needs no recording): every key sits in one chunk, so
+ * the softmax completes inside the kernel and its epilogue normalises, applies the gate and writes bf16 -- one launch,
+ * no partials.  A temporal-PE bias would be a per-row constant here and is therefore not an argument.
+ *
+ *   q     bf16 [L][128]     k  bf16 [L][128]     v  bf16 [L][1024]
+ *   gate  bf16 [L][1024] or NULL                 out bf16 [L][1024]
+ */
+int rmem_lt_attn_deaot_single(const void* q, const void* k, const void* v, int L, const void* gate, void* out,
+                              void* stream);
 
 /* The same operator, second generation (csrc/lt_attn_sk.cu): one persistent, stream-K scheduled kernel on 2-CTA
  * clusters that share every K / V tile by TMA multicast, followed by the merge of its segment partials.  It replaces

@@ -62,6 +62,7 @@ _SIGNATURES = {
     "rmem_last_error": [],
     "rmem_lt_attn_deaot_partial": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 4,
     "rmem_lt_attn_deaot_combine": [_c_void_p] * 5 + [_c_int] * 3 + [_c_void_p] * 4,
+    "rmem_lt_attn_deaot_single": [_c_void_p] * 3 + [_c_int] + [_c_void_p] * 3,
     "rmem_lt_attn_deaot_sk_workspace_bytes": [_c_int, _c_int, _c_int, _c_int],
     "rmem_lt_attn_deaot_sk_partial": [_c_void_p] * 4 + [_c_int] * 5 + [_c_void_p, _c_void_p, _c_int, _c_int, _c_void_p,
                                                                      ctypes.c_int64, _c_void_p],
@@ -134,7 +135,7 @@ class GemmSegment(ctypes.Structure):
                 ("dst_col0", ctypes.c_int32)]
 
 
-ABI_VERSION = 6          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
+ABI_VERSION = 7          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
 MAX_BANK = 16
 MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8

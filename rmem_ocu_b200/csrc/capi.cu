@@ -1,3 +1,4 @@
+#include <cstdlib>
 // extern "C" surface of librmem_b200.so (declared in include/rmem_b200.h) + error plumbing.
 #include <stdio.h>
 #include <string.h>
@@ -54,6 +55,16 @@ int ensure_dynamic_smem(const void* kernel, SmemOptIn* rec, int bytes, const cha
 
 using namespace rmem;
 
+namespace rmem {
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("RMEM_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+}  // namespace rmem
+
 extern "C" {
 
 int rmem_abi_version(void) { return RMEM_ABI_VERSION; }
@@ -74,6 +85,11 @@ int rmem_lt_attn_deaot_combine(const float* part_o, const float* part_m, const f
   return lt_attn_combine_launch(part_o, part_m, part_l, tpe_bias, tpe_rows_host, T, L,
                                 chunks_per_frame, gate, out, attn_mass,
                                 static_cast<cudaStream_t>(stream));
+}
+
+int rmem_lt_attn_deaot_single(const void* q, const void* k, const void* v, int L, const void* gate, void* out,
+                              void* stream) {
+  return lt_attn_direct_launch(q, k, v, L, gate, out, static_cast<cudaStream_t>(stream));
 }
 
 #define ST(s) static_cast<cudaStream_t>(s)

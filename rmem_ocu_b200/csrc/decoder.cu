@@ -19,6 +19,8 @@ namespace rmem {
 __global__ void __launch_bounds__(256)
 gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias, int P, int C, int cpg,
                      int rows_per_cta, double* __restrict__ ws) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   // blockIdx.y = image of a batch [S][P][C] (independent sequences): statistics and workspace per image
   x += static_cast<size_t>(blockIdx.y) * P * C;
   ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
@@ -60,6 +62,8 @@ __global__ void __launch_bounds__(256)
 gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
                      int P, int C, int cpg, int relu, double* __restrict__ ws) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   x += static_cast<size_t>(blockIdx.y) * P * C;
   y += static_cast<size_t>(blockIdx.y) * P * C;
   ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
@@ -107,13 +111,13 @@ int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const f
   const int per = (592 + S - 1) / S;             // ~4 CTAs per SM at large P over the whole batch ...
   int rows = (P + per - 1) / per;
   if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
-  gn_nhwc_stats_kernel<<<dim3((P + rows - 1) / rows, S), 256, 0, stream>>>(x, pre_bias, P, C, cpg, rows,
+  launch_k(gn_nhwc_stats_kernel, dim3((P + rows - 1) / rows, S), 256, 0, stream, x, pre_bias, P, C, cpg, rows,
                                                                           static_cast<double*>(workspace));
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   int blocks = static_cast<int>((total4 + 255) / 256);
   if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  gn_nhwc_apply_kernel<<<dim3(blocks, S), 256, 0, stream>>>(x, pre_bias, gamma, beta, y, P, C, cpg, relu,
+  launch_k(gn_nhwc_apply_kernel, dim3(blocks, S), 256, 0, stream, x, pre_bias, gamma, beta, y, P, C, cpg, relu,
                                                             static_cast<double*>(workspace));
   return check_launch("gn_nhwc_apply_kernel");
 }
@@ -123,6 +127,8 @@ int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const f
 __global__ void __launch_bounds__(256)
 upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const float* __restrict__ a,
                          const float* __restrict__ a_bias, float* __restrict__ out, int ho, int wo, int C) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   // blockIdx.y = image of a batch: xin [S][hi*wi][C], a / out [S][ho*wo][C]
   xin += static_cast<size_t>(blockIdx.y) * hi * wi * C;
   if (a) a += static_cast<size_t>(blockIdx.y) * ho * wo * C;
@@ -170,7 +176,7 @@ int upsample_add_nhwc_batched_launch(const float* xin, int hi, int wi, const flo
   const size_t total = static_cast<size_t>(ho) * wo * (C / 4);
   int blocks = static_cast<int>((total + 255) / 256);
   if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  upsample_add_nhwc_kernel<<<dim3(blocks, S), 256, 0, stream>>>(xin, hi, wi, a, a_bias, out, ho, wo, C);
+  launch_k(upsample_add_nhwc_kernel, dim3(blocks, S), 256, 0, stream, xin, hi, wi, a, a_bias, out, ho, wo, C);
   return check_launch("upsample_add_nhwc_kernel");
 }
 
@@ -186,6 +192,8 @@ __global__ void __launch_bounds__(256)
 finish_logits_kernel(const float* __restrict__ conv, long long sn, long long sc, long long sy, long long sx,
                      const float* __restrict__ bias, float* __restrict__ pred, int C, int Hs, int Ws,
                      const ValidCounts valid) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int total = C * Hs * Ws;
   if (i >= total) return;
@@ -202,6 +210,8 @@ finish_logits_kernel(const float* __restrict__ conv, long long sn, long long sc,
 __global__ void __launch_bounds__(256)
 upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, float* __restrict__ out, int Ho,
                        int Wo) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   pred += static_cast<size_t>(blockIdx.y) * C * Hs * Ws;
   out += static_cast<size_t>(blockIdx.y) * C * Ho * Wo;
   // thread = 4 consecutive output pixels of one row, all C channels (weights computed once per pixel)
@@ -253,12 +263,12 @@ int finish_logits_batched_launch(const float* conv, long long sn, long long sc, 
   ValidCounts valid;
   for (int s = 0; s < 64; ++s) valid.n[s] = s < S ? n_valid_host[s] : 0;
   const int total = C * Hs * Ws;
-  finish_logits_kernel<<<dim3((total + 255) / 256, S), 256, 0, stream>>>(conv, sn, sc, sy, sx, bias, pred, C, Hs, Ws,
+  launch_k(finish_logits_kernel, dim3((total + 255) / 256, S), 256, 0, stream, conv, sn, sc, sy, sx, bias, pred, C, Hs, Ws,
                                                                         valid);
   if (int r = check_launch("finish_logits_kernel")) return r;
   if (out) {
     const int n = Ho * ((Wo + 3) / 4);
-    upsample_logits_kernel<<<dim3((n + 255) / 256, S), 256, 0, stream>>>(pred, C, Hs, Ws, out, Ho, Wo);
+    launch_k(upsample_logits_kernel, dim3((n + 255) / 256, S), 256, 0, stream, pred, C, Hs, Ws, out, Ho, Wo);
     return check_launch("upsample_logits_kernel");
   }
   return RMEM_OK;
@@ -457,6 +467,8 @@ int maxpool3s2_nhwc_launch(const void* x, int H, int W, int C, const float* bias
 // softmax + argmax (networks/managers/evaluator.py:430-441; softmax is monotone, so it is skipped).
 __global__ void __launch_bounds__(256)
 argmax_label_kernel(const float* __restrict__ logits, int C, int HW, float* __restrict__ label) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= HW) return;
   logits += static_cast<size_t>(blockIdx.y) * C * HW;              // blockIdx.y = image of a batch
@@ -492,7 +504,7 @@ int argmax_label_launch(const float* logits, int C, int HW, float* label, cudaSt
 int argmax_label_batched_launch(const float* logits, int C, int HW, float* label, int S, cudaStream_t stream) {
   if (C < 1 || HW < 1 || S < 1 || S > 65535) return set_error(RMEM_ERR_ARG, "argmax_label: bad shape");
   const int n = (HW + 3) / 4;
-  argmax_label_kernel<<<dim3((n + 255) / 256, S), 256, 0, stream>>>(logits, C, HW, label);
+  launch_k(argmax_label_kernel, dim3((n + 255) / 256, S), 256, 0, stream, logits, C, HW, label);
   return check_launch("argmax_label_kernel");
 }
 

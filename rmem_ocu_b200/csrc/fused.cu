@@ -32,6 +32,8 @@ __global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
   const LnStream st = p.s[blockIdx.y];
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_trigger();
   if (row >= p.L) return;
   float v[8];
   if (p.in_bf16) {
@@ -82,7 +84,7 @@ int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0,
   p.s[0] = {x0, g0, b0, static_cast<__nv_bfloat16*>(o0), ld0, c0};
   p.s[1] = {x1, g1, b1, static_cast<__nv_bfloat16*>(o1), ld1, c1};
   dim3 grid((L + 7) / 8, x1 ? 2 : 1);
-  layernorm256_kernel<<<grid, 256, 0, stream>>>(p);
+  launch_k(layernorm256_kernel, grid, 256, 0, stream, p);
   return check_launch("layernorm256_kernel");
 }
 
@@ -121,8 +123,6 @@ dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict
     sm100::tma_prefetch_desc(&tm_x);
     sm100::mbar_init(bar, 1);
     sm100::mbar_fence_init();
-    sm100::mbar_expect_tx(bar, static_cast<uint32_t>((kDwRows + 4) * box_w * kDwCh * 2));
-    sm100::tma_load_4d(dw_smem + 128, &tm_x, bar, c0, -2, y0 - 2, static_cast<int>(blockIdx.z));
   }
   const int cp = threadIdx.x & 31;              // channel pair inside the CTA's 64 channels
   const int grp = threadIdx.x >> 5;             // column group
@@ -130,6 +130,12 @@ dwconv5_kernel(const __grid_constant__ CUtensorMap tm_x, const float* __restrict
   float2 wgt[25];
 #pragma unroll
   for (int t = 0; t < 25; ++t) wgt[t] = *reinterpret_cast<const float2*>(wt + t * C + c);
+  pdl_wait();                                   // weights above; activations from here on
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    sm100::mbar_expect_tx(bar, static_cast<uint32_t>((kDwRows + 4) * box_w * kDwCh * 2));
+    sm100::tma_load_4d(dw_smem + 128, &tm_x, bar, c0, -2, y0 - 2, static_cast<int>(blockIdx.z));
+  }
   const int per = (w + 7) / 8;                  // columns per group
   const int xa = grp * per, xb = min(xa + per, w);
   __syncthreads();                              // barrier init visible
@@ -205,8 +211,8 @@ int dwconv5_batched_launch(const void* x, int ldx, int xcol0, const float* wt, v
                                   "dwconv5: cudaFuncSetAttribute"))
     return r;
   dim3 grid((h + kDwRows - 1) / kDwRows, C / kDwCh, S);
-  dwconv5_kernel<<<grid, kDwThreads, smem, stream>>>(tm_x, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0, h, w,
-                                                     C, box_w);
+  launch_k(dwconv5_kernel, grid, kDwThreads, smem, stream, tm_x, wt, static_cast<__nv_bfloat16*>(y), ldy, ycol0, h, w,
+           C, box_w);
   return check_launch("dwconv5_kernel");
 }
 
@@ -216,6 +222,8 @@ int dwconv5_batched_launch(const void* x, int ldx, int xcol0, const float* wt, v
 __global__ void __launch_bounds__(256)
 gn_stats_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb, int L, int C,
                 int groups, int rows_per_cta, double* __restrict__ ws) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   // blockIdx.y = sequence: inputs stacked [S][L] rows, one (2 groups + 1)-double workspace per sequence
   xa += static_cast<size_t>(blockIdx.y) * L * Ca;
   if (xb) xb += static_cast<size_t>(blockIdx.y) * L * (C - Ca);
@@ -262,6 +270,8 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32, int L, int C, int groups,
                 double* __restrict__ ws) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   xa += static_cast<size_t>(blockIdx.y) * L * Ca;
   if (xb) xb += static_cast<size_t>(blockIdx.y) * L * (C - Ca);
   ws += static_cast<size_t>(blockIdx.y) * (2 * groups + 1);
@@ -313,10 +323,10 @@ int groupnorm_tokens_batched_launch(const float* xa, int Ca, const float* xb, co
     return set_error(RMEM_ERR_ARG, "groupnorm_tokens: unsupported C / groups");
   const int per = (148 + S - 1) / S;                               // CTAs per sequence: about one per SM in total
   const int rows = (L + per - 1) / per < 4 ? 4 : (L + per - 1) / per;
-  gn_stats_kernel<<<dim3((L + rows - 1) / rows, S), 256, 0, stream>>>(xa, Ca, xb, L, C, groups, rows,
+  launch_k(gn_stats_kernel, dim3((L + rows - 1) / rows, S), 256, 0, stream, xa, Ca, xb, L, C, groups, rows,
                                                                       static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
-  gn_apply_kernel<<<dim3((296 + S - 1) / S, S), 256, 0, stream>>>(xa, Ca, xb, gamma, beta,
+  launch_k(gn_apply_kernel, dim3((296 + S - 1) / S, S), 256, 0, stream, xa, Ca, xb, gamma, beta,
                                            out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out),
                                            out_f32 ? static_cast<float*>(out) : nullptr, L, C, groups,
                                            static_cast<double*>(workspace));
@@ -378,6 +388,8 @@ __global__ void __launch_bounds__(256)
 tpe_prepare_kernel(const __nv_bfloat16* __restrict__ q, const float* __restrict__ cur,
                    const float* __restrict__ mem, __nv_bfloat16* __restrict__ q_time,
                    float* __restrict__ bias, int L, float scale) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= L) return;
@@ -410,7 +422,7 @@ tpe_prepare_kernel(const __nv_bfloat16* __restrict__ q, const float* __restrict_
 int tpe_prepare_launch(const void* q, const float* cur, const float* mem, void* q_time, float* bias,
                        int L, int C, cudaStream_t stream) {
   if (C != 128) return set_error(RMEM_ERR_ARG, "tpe_prepare: C must be 128");
-  tpe_prepare_kernel<<<(L + 7) / 8, 256, 0, stream>>>(
+  launch_k(tpe_prepare_kernel, (L + 7) / 8, 256, 0, stream, 
       static_cast<const __nv_bfloat16*>(q), cur, mem, static_cast<__nv_bfloat16*>(q_time), bias, L,
       1.4426950408889634f / sqrtf(128.f));
   return check_launch("tpe_prepare_kernel");

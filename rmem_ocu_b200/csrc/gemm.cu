@@ -83,6 +83,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();       // everything above touched parameters and the bias (a weight) only
+  pdl_trigger();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -277,11 +279,11 @@ int gemm_ex_launch(const void* a, int lda, const void* w, int ldw, const float* 
   }
   dim3 grid((N + bn - 1) / bn, m_tiles);
   if (deep)
-    gemm_bf16_tn_kernel<64, 6><<<grid, kGThreads, GemmCfg<64, 6>::kSmem, stream>>>(tm_a, tm_w, p);
+    launch_k(gemm_bf16_tn_kernel<64, 6>, grid, kGThreads, GemmCfg<64, 6>::kSmem, stream, tm_a, tm_w, p);
   else if (narrow)
-    gemm_bf16_tn_kernel<64, 3><<<grid, kGThreads, GemmCfg<64, 3>::kSmem, stream>>>(tm_a, tm_w, p);
+    launch_k(gemm_bf16_tn_kernel<64, 3>, grid, kGThreads, GemmCfg<64, 3>::kSmem, stream, tm_a, tm_w, p);
   else
-    gemm_bf16_tn_kernel<128, 3><<<grid, kGThreads, GemmCfg<128, 3>::kSmem, stream>>>(tm_a, tm_w, p);
+    launch_k(gemm_bf16_tn_kernel<128, 3>, grid, kGThreads, GemmCfg<128, 3>::kSmem, stream, tm_a, tm_w, p);
   return check_launch("gemm_bf16_tn_kernel");
 }
 

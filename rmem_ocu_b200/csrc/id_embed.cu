@@ -29,6 +29,8 @@ struct IdEmbedParams {
 };
 
 __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   __shared__ int cls_sh[kIdK][kIdK + 1];
   __shared__ float red[2][kIdC / 32];
   // blockIdx.x = (sequence, token): label maps stacked [S][H][W], destination rows stacked [S][h*w]
@@ -159,7 +161,7 @@ int id_embed_batched_launch(const float* label, int H, int W, const float* prefi
     p.ld[i] = i < n_dst ? ld[i] : 0;
     p.col0[i] = i < n_dst ? col0[i] : 0;
   }
-  id_embed_kernel<<<S * h * w, kIdC, 0, stream>>>(p);
+  launch_k(id_embed_kernel, S * h * w, kIdC, 0, stream, p);
   return check_launch("id_embed_kernel");
 }
 

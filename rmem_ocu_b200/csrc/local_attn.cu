@@ -80,6 +80,10 @@ local_scores_kernel(const __grid_constant__ CUtensorMap tm_k, const __nv_bfloat1
     tma_prefetch_desc(&tm_k);
     mbar_init(bar, 1);
     mbar_fence_init();
+  }
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
+  if (threadIdx.x == 0) {
     mbar_expect_tx(bar, kSSmemK);
     tma_load_5d(sK, &tm_k, bar, 0, x0 - kMaxDis, y0 - kMaxDis, 0, static_cast<int>(blockIdx.z));
   }
@@ -217,7 +221,7 @@ int local_scores_batched_launch(const void* q, const void* k, const float* rel, 
                                   "local_scores: cudaFuncSetAttribute"))
     return r;
   dim3 grid((w + kSTileW - 1) / kSTileW, (h + kSTileH - 1) / kSTileH, S);
-  local_scores_kernel<<<grid, 256, kSSmem, stream>>>(tm_k, static_cast<const __nv_bfloat16*>(q), rel, ld_rel,
+  launch_k(local_scores_kernel, grid, 256, kSSmem, stream, tm_k, static_cast<const __nv_bfloat16*>(q), rel, ld_rel,
                                                      probs, static_cast<__nv_bfloat16*>(banded), h, w);
   return check_launch("local_scores_kernel");
 }
@@ -270,6 +274,8 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -402,7 +408,7 @@ int local_aggregate_batched_launch(const void* banded, const void* v, const void
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out); p.h = h; p.w = w;
   dim3 grid(tiles_x, tiles_y, (1024 / kADV) * S);
-  local_aggregate_kernel<<<grid, kAThreads, kASmem, stream>>>(tm_p, tm_v, p);
+  launch_k(local_aggregate_kernel, grid, kAThreads, kASmem, stream, tm_p, tm_v, p);
   return check_launch("local_aggregate_kernel");
 }
 

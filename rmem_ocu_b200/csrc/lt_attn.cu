@@ -59,6 +59,10 @@ struct LtParams {
   float* part_m;         // [n_chunks][L]
   float* part_l;         // [n_chunks][L]
   float scale_log2;      // log2(e) / sqrt(d_att)
+  // direct mode (n_chunks == 1: the one chunk holds every key, so the softmax is complete in this CTA): the epilogue
+  // normalises, applies the gate and writes bf16 -- no partials, no combine launch
+  const __nv_bfloat16* direct_gate;   // [L][1024] or nullptr
+  __nv_bfloat16* direct_out;          // [L][1024]; nullptr = partial mode
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -127,11 +131,13 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && n_tiles > 0) {   // never leave a bulk copy in flight when there is no consumer
-      const int slot = p.order[frame_pos];
+      const int slot = p.order ? p.order[frame_pos] : 0;
       mbar_expect_tx(q_full, kQBytes);
       tma_load_3d(sQ, &tm_q, q_full, 0, q_tile * kBlockM, 0);
       for (int j = 0; j < n_tiles; ++j) {
@@ -317,6 +323,47 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     // full-line writes, rows beyond L clipped by the tensor map.
     uint8_t* stage = sK;
     const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
+    if (p.direct_out != nullptr) {
+      // this thread: row q_global, value channels [dv_split * 256 + hf * 128, +128): 64-byte runs per 32 channels
+      const float inv = (n_tiles > 0 && l_tot > 0.f) ? 1.f / l_tot : 0.f;
+      const size_t base = static_cast<size_t>(q_global) * kDV + dv_split * kDVTile + hf * (kDVTile / 2);
+#pragma unroll 1
+      for (int cb = 0; cb < kDVTile / 64; ++cb) {
+        uint32_t orow[32];
+        if (n_tiles > 0) {
+          tmem_ld32(o_addr + cb * 32, orow);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) orow[i] = 0u;
+        }
+        if (row_ok) {
+          uint4 g[4];
+          if (p.direct_gate) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v)
+              g[v] = *reinterpret_cast<const uint4*>(p.direct_gate + base + cb * 32 + v * 8);
+          }
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float a = __uint_as_float(orow[v * 8 + 2 * e]) * inv;
+              float b = __uint_as_float(orow[v * 8 + 2 * e + 1]) * inv;
+              if (p.direct_gate) {
+                const uint32_t gw = (&g[v].x)[e];
+                const __nv_bfloat162 g2 = *reinterpret_cast<const __nv_bfloat162*>(&gw);
+                a *= __bfloat162float(g2.x);
+                b *= __bfloat162float(g2.y);
+              }
+              w[e] = pack_bf16x2(a, b);
+            }
+            *reinterpret_cast<uint4*>(p.direct_out + base + cb * 32 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      }
+    } else {
 #pragma unroll 1
     for (int cb = 0; cb < kDVTile / 64; ++cb) {
       uint32_t orow[32];
@@ -346,6 +393,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       p.part_m[static_cast<size_t>(chunk) * p.L + q_global] = m_used;
       p.part_l[static_cast<size_t>(chunk) * p.L + q_global] = l_tot;
     }
+    }  // partial mode
     tc_fence_before();
   }
 
@@ -375,6 +423,8 @@ constexpr int kMaxChunks = RMEM_MAX_BANK * RMEM_MAX_CHUNKS_PER_FRAME;   // 64
 
 __global__ void __launch_bounds__(256)
 lt_attn_combine_kernel(const CombineParams p) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   const int q = blockIdx.x;
   const int n_chunks = p.T * p.chunks_per_frame;
   __shared__ float w_sh[kMaxChunks];      // w_c / denom
@@ -515,9 +565,55 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
   p.part_m = part_m;
   p.part_l = part_l;
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
+  p.direct_gate = nullptr;
+  p.direct_out = nullptr;
   dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, p.n_chunks);
-  lt_attn_partial_kernel<<<grid, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, tm_o, p);
+  launch_k(lt_attn_partial_kernel, grid, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, tm_o, p);
   return check_launch("lt_attn_partial_kernel");
+}
+
+// One frame of keys (a layer's self-attention, or a bank holding one frame), complete in one launch:
+// out = gate * softmax(q k^T / sqrt(d)) v as bf16.  Grid: (query tiles, 4 value splits).
+int lt_attn_direct_launch(const void* q, const void* k, const void* v, int L, const void* gate, void* out,
+                          cudaStream_t stream) {
+  if (L < 1) return set_error(RMEM_ERR_ARG, "lt_attn_direct: bad L");
+  CUtensorMap tm_q, tm_k, tm_v;
+  {
+    const uint64_t dims[3] = {64, static_cast<uint64_t>(L), 2};
+    const uint64_t strides[2] = {kDK * 2, 128};
+    const uint32_t box[3] = {64, kBlockM, 2};
+    if (int e = encode_map(&tm_q, q, 3, dims, strides, box)) return e;
+  }
+  {
+    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), 2, 1};
+    const uint64_t strides[3] = {kDK * 2, 128, static_cast<uint64_t>(L) * kDK * 2};
+    const uint32_t box[4] = {64, kBlockN, 2, 1};
+    if (int e = encode_map(&tm_k, k, 4, dims, strides, box)) return e;
+  }
+  {
+    const uint64_t dims[4] = {64, static_cast<uint64_t>(L), kDV / 64, 1};
+    const uint64_t strides[3] = {kDV * 2, 128, static_cast<uint64_t>(L) * kDV * 2};
+    const uint32_t box[4] = {64, kBlockN, kDVTile / 64, 1};
+    if (int e = encode_map(&tm_v, v, 4, dims, strides, box)) return e;
+  }
+  static SmemOptIn optin;
+  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(lt_attn_partial_kernel), &optin, kSmemTotal,
+                                  "lt_attn_direct: cudaFuncSetAttribute"))
+    return r;
+  LtParams p;
+  p.L = L;
+  p.n_chunks = 1;
+  p.chunks_per_frame = 1;
+  p.order = nullptr;                 // one slot: position 0
+  p.part_o = nullptr;
+  p.part_m = nullptr;
+  p.part_l = nullptr;
+  p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
+  p.direct_gate = static_cast<const __nv_bfloat16*>(gate);
+  p.direct_out = static_cast<__nv_bfloat16*>(out);
+  dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, 1);
+  launch_k(lt_attn_partial_kernel, grid, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, tm_q /*unused*/, p);
+  return check_launch("lt_attn_partial_kernel (direct)");
 }
 
 int lt_attn_combine_launch(const float* part_o, const float* part_m, const float* part_l,
@@ -535,7 +631,7 @@ int lt_attn_combine_launch(const float* part_o, const float* part_m, const float
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out);
   p.attn_mass = attn_mass;
-  lt_attn_combine_kernel<<<L, 256, 0, stream>>>(p);
+  launch_k(lt_attn_combine_kernel, L, 256, 0, stream, p);
   return check_launch("lt_attn_combine_kernel");
 }
 

@@ -219,6 +219,8 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   cluster_sync_all();               // the peer's barriers exist before anything multicasts into them
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -556,6 +558,8 @@ constexpr int kMaxSegPerPair = 16;
 
 __global__ void __launch_bounds__(256)
 lt_attn_sk_combine_kernel(const CombineParams p) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
   __shared__ float tile[kBlockM][kCbCols + 1];
   __shared__ int seg_slot[kMaxSegPerPair], seg_a[kMaxSegPerPair], seg_b[kMaxSegPerPair];
   __shared__ int n_seg_sh;
@@ -843,7 +847,7 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
   sk_split_workspace(pl, workspace, &p.part_o, &p.part_ml, &part_f);
   p.part_f = record ? part_f : nullptr;
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
-  lt_attn_sk_kernel<<<pl.n_ctas, kThreads, kSmemTotal, stream>>>(tm_q, tm_k, tm_v, p);
+  launch_k(lt_attn_sk_kernel, pl.n_ctas, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, p);
   return check_launch("lt_attn_sk_kernel");
 }
 
@@ -864,7 +868,7 @@ int lt_attn_sk_combine_launch(int T, int L, int S, const void* gate, void* out, 
   p.out = static_cast<__nv_bfloat16*>(out);
   p.attn_mass = attn_mass;
   dim3 grid(S * ((L + kBlockM - 1) / kBlockM), kDV / kCbCols + (attn_mass ? 1 : 0));
-  lt_attn_sk_combine_kernel<<<grid, 256, 0, stream>>>(p);
+  launch_k(lt_attn_sk_combine_kernel, grid, 256, 0, stream, p);
   return check_launch("lt_attn_sk_combine_kernel");
 }
 

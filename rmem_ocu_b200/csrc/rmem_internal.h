@@ -13,6 +13,33 @@ int set_error(int code, const char* msg);
 int set_cuda_error(cudaError_t e, const char* where);
 int check_launch(const char* kernel_name);
 
+// Programmatic dependent launch: a kernel launched through launch_k may begin (block scheduling, shared-memory
+// carve-out, barrier / TMEM set-up, descriptor prefetch, weight loads) while its predecessor on the stream is still
+// draining.  The contract every kernel launched this way keeps: pdl_wait() comes before its first access to any global
+// memory another kernel of the frame writes or reads (activations, workspaces, outputs) -- only parameters and weights
+// may be touched earlier -- and pdl_trigger() follows it, so at most one dependent is ever waiting beside a running grid.
+// RMEM_PDL=0 launches everything fully serialised (griddepcontrol.* are no-ops then).
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                       const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                       const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -33,6 +60,8 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
                            const int32_t* order_dev, int T, int L, int n_slots,
                            int chunks_per_frame, float* part_o, float* part_m, float* part_l,
                            cudaStream_t stream);
+int lt_attn_direct_launch(const void* q, const void* k, const void* v, int L, const void* gate, void* out,
+                          cudaStream_t stream);
 int lt_attn_combine_launch(const float* part_o, const float* part_m, const float* part_l,
                            const float* tpe_bias, const int32_t* tpe_rows_host, int T, int L,
                            int chunks_per_frame, const void* gate, void* out, float* attn_mass,

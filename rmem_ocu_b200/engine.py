@@ -547,6 +547,7 @@ class DeAOTEngine:
         self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False) and self.S == 1
         import os
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
+        self.lt_single = os_env_flag("RMEM_LT_SINGLE", True)      # one-launch self-attention (no partials / combine)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
         # long-term attention finds free SMs
         self.lt_sk_clusters = int(os.environ.get("RMEM_LT_SK_CLUSTERS", "-1"))
@@ -707,8 +708,15 @@ class DeAOTEngine:
                 torch.cuda.current_stream().wait_event(gate_ready)
             ops.lt_attn_sk_combine(T, ws.L, gate, out, mass, ws.sk_ws, self.lt_sk_clusters, ws.S)
             return
-        cpf = _chunks_per_frame(T, ws.L)
         kbank, vbank = kbank.view(-1, ws.L, kbank.shape[-1]), vbank.view(-1, ws.L, vbank.shape[-1])
+        if T == 1 and mass is None and order is ws.zero_order and self.lt_single:
+            # one frame of keys in slot 0 and nothing to record (a layer's self-attention): the softmax completes
+            # inside one CTA per (query tile, value split), so the kernel writes the gated bf16 output itself
+            if gate_ready is not None:
+                torch.cuda.current_stream().wait_event(gate_ready)
+            ops.lt_attn_single(q, kbank[0], vbank[0], gate, out)
+            return
+        cpf = _chunks_per_frame(T, ws.L)
         ops.lt_attn_partial(q, kbank, vbank, order, T, cpf, ws.part_o, ws.part_m, ws.part_l)
         if gate_ready is not None:
             torch.cuda.current_stream().wait_event(gate_ready)    # the gate is computed on another branch

@@ -229,6 +229,14 @@ def lt_attn_combine(part_o, part_m, part_l, tpe_bias, tpe_rows, T, L, cpf, gate,
     _count("rmem_lt_attn_deaot_combine")
 
 
+def lt_attn_single(q, k, v, gate, out):
+    """One frame of keys, one launch: out = gate * softmax(q k^T / sqrt(128)) v.  q, k [L,128]; v, gate, out [L,1024]."""
+    L = q.shape[0]
+    _lib.check(_lib.lib().rmem_lt_attn_deaot_single(_p(q), _p(k), _p(v), L, _p(gate), _p(out), _stream()),
+               "rmem_lt_attn_deaot_single")
+    _count("rmem_lt_attn_deaot_single")
+
+
 def lt_attn_sk_workspace(L, T_max, device, n_clusters=0, S=1):
     """Workspace of the stream-K long-term attention for up to T_max frames in the bank (uint8 tensor)."""
     n = max(_lib.lib().rmem_lt_attn_deaot_sk_workspace_bytes(L, T, S, n_clusters) for T in range(1, T_max + 1))

@@ -103,6 +103,31 @@ def test_long_term_attention_streamk_vs_oracle(lib_built, L, T, qscale, use_tpe,
         assert (mass.sum(1) - 1).abs().max().item() < 1e-4
 
 
+@pytest.mark.parametrize("L,qscale,use_gate", [(1620, 1.0, True), (1705, 4.0, True), (128, 1.0, False), (77, 2.0, True),
+                                               (3600, 3.0, True)])
+def test_single_frame_attention_vs_oracle(lib_built, L, qscale, use_gate):
+    """rmem_lt_attn_deaot_single (one launch, no partials): gated self-attention of one frame against fp32 on the
+    bf16-rounded inputs, and against the partial + combine pair it replaces on the path (same kernel body, the
+    pair merges three key chunks: rounding differs, so 1e-2 relative rather than equality)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(L)
+    q = _bf(torch.randn(L, 128, device="cuda") * qscale)
+    v = _bf(torch.randn(L, 1024, device="cuda"))
+    gate = _bf(torch.rand(L, 1024, device="cuda")) if use_gate else None
+    out = torch.full((L, 1024), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.lt_attn_single(q, q, v, gate, out)
+    torch.cuda.synchronize()
+    p = torch.softmax(q.float() @ q.float().t() / math.sqrt(128), -1)
+    ref = p @ v.float()
+    if use_gate:
+        ref = ref * gate.float()
+    assert torch.isfinite(out.float()).all()
+    assert _rel(out, ref) <= 2e-2
+    order = torch.zeros(1, device="cuda", dtype=torch.int32)
+    pair, _ = _lt_run(q, q.view(1, L, 128), v.view(1, L, 1024), order, 1, 3, gate=gate)
+    assert _rel(out, pair) <= 1e-2
+
+
 @pytest.mark.parametrize("h,w", [(31, 55), (30, 54), (9, 20), (45, 80)])
 def test_local_attention_vs_oracle(lib_built, h, w):
     """LocalGatedPropagation (15x15 window) against the oracle's direct windowed restatement."""
