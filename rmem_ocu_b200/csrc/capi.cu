@@ -59,7 +59,7 @@ namespace rmem {
 bool pdl_enabled() {
   static const bool on = [] {
     const char* e = getenv("RMEM_PDL");
-    return !(e && e[0] == '0');
+    return e && e[0] == '1';
   }();
   return on;
 }

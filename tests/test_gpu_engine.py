@@ -408,3 +408,18 @@ def test_evaluator_loop_vs_oracle(lib_built, tmp_path):
     want = masks[2].numpy()
     lut = np.array([0, 5, 9, 30] + [0] * 252, np.uint8)              # squeeze_idx: dense ids -> dataset labels
     assert png.shape == (H, W) and np.array_equal(png, lut[want])
+
+
+def test_programmatic_dependent_launch_is_equivalent(lib_built):
+    """RMEM_PDL=1 (kernels launched with programmatic stream serialisation, csrc/rmem_internal.h) must not change
+    results: every kernel waits (griddepcontrol.wait) before its first access to activations.  Runs the smoke clip in
+    a subprocess with the switch on -- the switch is read once per process -- which checks it against the oracle."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RMEM_PDL="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "__graft_entry__.py"), "smoke"], env=env, cwd=root,
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "smoke ok" in r.stdout

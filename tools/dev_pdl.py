@@ -34,4 +34,4 @@ for _ in range(20):
     a = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
     a.record(); gr.replay(); e.record(); torch.cuda.synchronize(); ts.append(a.elapsed_time(e) * 1e3)
 ts.sort()
-print("RMEM_PDL=%s  graph of 40 launches: %.1f us  (%.2f us / launch)  finite=%s" % (os.environ.get("RMEM_PDL", "1"), ts[10], ts[10] / 40, bool(torch.isfinite(tgt).all())))
+print("RMEM_PDL=%s  graph of 40 launches: %.1f us  (%.2f us / launch)  finite=%s" % (os.environ.get("RMEM_PDL", "0"), ts[10], ts[10] / 40, bool(torch.isfinite(tgt).all())))
