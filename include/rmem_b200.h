@@ -383,6 +383,19 @@ int rmem_id_embed(const float* label, int H, int W, const float* prefix, const f
                   const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w,
                   void* stream);
 
+/* The same embedding from a one-hot or probability mask that already has one channel per identity
+ * (update_short_term_memory's second branch, aot_engine.py:330-336 -> assign_identity :208-232): channel 0 is
+ * multiplied by (ignore == 0) and the ignore map becomes the last class (:214-224), then the 17x17 stride-16 conv
+ * (models/aot.py:111-114) as a weighted sum and DeAOT's id_norm (models/deaot.py:65-69).
+ *   prob   f32 [S][n_ch][H][W], n_ch <= n_cls <= 16 (missing channels count as zero)
+ *   ignore f32 [S][H][W] or NULL
+ *   taps   f32 [n_cls][17][17][256] = conv.weight[c][k][ky][kx] with the output channel innermost
+ *   destinations as rmem_id_embed, rows [S * h * w]
+ */
+int rmem_id_embed_soft(const float* prob, int n_ch, const float* ignore, int H, int W, const float* taps,
+                       const float* bias, const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                       const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w, int S, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Decoding head (FPNSegmentationHead, decoders/fpn.py:36-68): the convolutions stay cuDNN calls; the
  * GroupNorm(8) + ReLU of every ConvGN (layers/basic.py:60-70, fpn.py:44-63) and the bilinear

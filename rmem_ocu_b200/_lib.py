@@ -69,6 +69,8 @@ _SIGNATURES = {
     "rmem_lt_attn_deaot_sk_combine": [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_void_p,
                                       ctypes.c_int64, _c_void_p],
     "rmem_bank_tick_batched": [_c_void_p, _c_int, _c_void_p],
+    "rmem_id_embed_soft": [_c_void_p, _c_int, _c_void_p, _c_int, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 3 +
+                          [_c_int] * 4 + [_c_void_p],
     "rmem_id_embed_batched": [_c_void_p, _c_int, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 3 + [_c_int] * 4 +
                              [_c_void_p],
     "rmem_groupnorm_nhwc_batched": [_c_void_p] * 5 + [_c_int] * 5 + [_c_void_p] * 2,

@@ -118,6 +118,12 @@ int rmem_id_embed_batched(const float* labels, int H, int W, const float* prefix
   return id_embed_batched_launch(labels, H, W, prefix, bias, gamma, beta, n_cls, dst_host, ld_host, col0_host, n_dst,
                                  h, w, S, ST(stream));
 }
+int rmem_id_embed_soft(const float* prob, int n_ch, const float* ignore, int H, int W, const float* taps,
+                       const float* bias, const float* gamma, const float* beta, int n_cls, void* const* dst_host,
+                       const int32_t* ld_host, const int32_t* col0_host, int n_dst, int h, int w, int S, void* stream) {
+  return id_embed_soft_launch(prob, n_ch, ignore, H, W, taps, bias, gamma, beta, n_cls, dst_host, ld_host, col0_host,
+                              n_dst, h, w, S, ST(stream));
+}
 int rmem_groupnorm_nhwc_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, float* y,
                                 int P, int C, int groups, int relu, int S, void* workspace, void* stream) {
   return groupnorm_nhwc_batched_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, S, workspace, ST(stream));

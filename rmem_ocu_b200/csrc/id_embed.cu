@@ -28,6 +28,32 @@ struct IdEmbedParams {
   int H, W, h, w, n_cls;   // n_cls = max_obj + 2 (last class = ignore)
 };
 
+// id_norm LayerNorm over the 256 channels of one token (one channel per thread) + the bf16 stores
+__device__ __forceinline__ void finish_token(float acc, const float* gamma, const float* beta, float (*red)[kIdC / 32],
+                                             __nv_bfloat16* const* dst, const int* ld, const int* col0, int n_dst) {
+  const int c = threadIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float out = acc;
+  if (gamma) {
+    float s = acc;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) red[0][warp] = s;
+    __syncthreads();
+    float mean = 0.f;
+    for (int i = 0; i < kIdC / 32; ++i) mean += red[0][i];
+    mean *= (1.f / kIdC);
+    const float d = acc - mean;
+    float q = d * d;
+    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    if (lane == 0) red[1][warp] = q;
+    __syncthreads();
+    float var = 0.f;
+    for (int i = 0; i < kIdC / 32; ++i) var += red[1][i];
+    out = d * rsqrtf(var * (1.f / kIdC) + 1e-5f) * gamma[c] + beta[c];
+  }
+  const __nv_bfloat16 ob = __float2bfloat16(out);
+  for (int i = 0; i < n_dst; ++i) dst[i][static_cast<size_t>(blockIdx.x) * ld[i] + col0[i] + c] = ob;
+}
+
 __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
@@ -119,26 +145,7 @@ __global__ void __launch_bounds__(kIdC) id_embed_kernel(const IdEmbedParams p) {
              (base[(r1 * (kIdK + 1) + lo) * kIdC] - base[(r0 * (kIdK + 1) + lo) * kIdC]);
     }
   }
-  float out = acc;
-  if (p.gamma) {
-    float s = acc;
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) red[0][warp] = s;
-    __syncthreads();
-    float mean = 0.f;
-    for (int i = 0; i < kIdC / 32; ++i) mean += red[0][i];
-    mean *= (1.f / kIdC);
-    const float d = acc - mean;
-    float q = d * d;
-    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-    if (lane == 0) red[1][warp] = q;
-    __syncthreads();
-    float var = 0.f;
-    for (int i = 0; i < kIdC / 32; ++i) var += red[1][i];
-    out = d * rsqrtf(var * (1.f / kIdC) + 1e-5f) * p.gamma[c] + p.beta[c];
-  }
-  const __nv_bfloat16 ob = __float2bfloat16(out);
-  for (int i = 0; i < p.n_dst; ++i) p.dst[i][static_cast<size_t>(blockIdx.x) * p.ld[i] + p.col0[i] + c] = ob;
+  finish_token(acc, p.gamma, p.beta, red, p.dst, p.ld, p.col0, p.n_dst);
 }
 
 int id_embed_launch(const float* label, int H, int W, const float* prefix, const float* bias,
@@ -163,6 +170,82 @@ int id_embed_batched_launch(const float* label, int H, int W, const float* prefi
   }
   launch_k(id_embed_kernel, S * h * w, kIdC, 0, stream, p);
   return check_launch("id_embed_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same embedding from a one-hot or PROBABILITY mask (aot_engine.py:330-336: a mask that already is
+// [max_obj + 1] channels goes to assign_identity as it is): the convolution is then a real weighted sum,
+// out[token][c] = bias[c] + sum_{k, ky, kx} m[k][y][x] W[c][k][ky][kx].  One CTA per token stages the token's window of
+// every channel in shared memory and walks the taps in (channel, ky, kx) order; taps whose mask value is zero are
+// skipped (CTA-uniform), so a one-hot mask costs 289 weight rows and a saturated probability mask little more.
+struct IdSoftParams {
+  const float* prob;       // [S][n_ch][H][W]
+  const float* ignore;     // [S][H][W] or nullptr: channel 0 is multiplied by (ignore == 0), the ignore map is class n_cls - 1
+  const float* taps;       // [n_cls][17][17][256] = W[c][k][ky][kx] transposed
+  const float* bias;
+  const float* gamma;
+  const float* beta;
+  __nv_bfloat16* dst[4];
+  int ld[4], col0[4];
+  int n_dst;
+  int H, W, h, w, n_ch, n_cls;
+};
+constexpr int kIdMaxCls = 16;
+
+__global__ void __launch_bounds__(kIdC) id_embed_soft_kernel(const IdSoftParams p) {
+  extern __shared__ float win[];                      // [n_cls][17 * 17]
+  __shared__ float red[2][kIdC / 32];
+  const int seq = blockIdx.x / (p.h * p.w);
+  const int tok = blockIdx.x - seq * (p.h * p.w);
+  const int ty = tok / p.w, tx = tok - ty * p.w;
+  const int c = threadIdx.x;
+  const size_t HW = static_cast<size_t>(p.H) * p.W;
+  const float* prob = p.prob + static_cast<size_t>(seq) * p.n_ch * HW;
+  const float* ign = p.ignore ? p.ignore + static_cast<size_t>(seq) * HW : nullptr;
+  constexpr int kWin = kIdK * kIdK;
+  for (int i = threadIdx.x; i < p.n_cls * kWin; i += kIdC) {
+    const int k = i / kWin, t = i - k * kWin;
+    const int ky = t / kIdK, kx = t - ky * kIdK;
+    const int y = ty * kIdStride - kIdPad + ky, x = tx * kIdStride - kIdPad + kx;
+    float v = 0.f;
+    if (y >= 0 && y < p.H && x >= 0 && x < p.W) {
+      const size_t px = static_cast<size_t>(y) * p.W + x;
+      if (k < p.n_ch) {
+        v = prob[static_cast<size_t>(k) * HW + px];
+        if (k == 0 && ign && ign[px] != 0.f) v = 0.f;
+      } else if (k == p.n_cls - 1 && ign) {
+        v = ign[px];
+      }
+    }
+    win[i] = v;
+  }
+  __syncthreads();
+  float acc = p.bias[c];
+  const int n = p.n_cls * kWin;
+  for (int i = 0; i < n; ++i) {
+    const float m = win[i];                           // broadcast read: the branch is CTA-uniform
+    if (m != 0.f) acc = fmaf(m, p.taps[static_cast<size_t>(i) * kIdC + c], acc);
+  }
+  finish_token(acc, p.gamma, p.beta, red, p.dst, p.ld, p.col0, p.n_dst);
+}
+
+int id_embed_soft_launch(const float* prob, int n_ch, const float* ignore, int H, int W, const float* taps,
+                         const float* bias, const float* gamma, const float* beta, int n_cls, void* const* dst,
+                         const int* ld, const int* col0, int n_dst, int h, int w, int S, cudaStream_t stream) {
+  if (n_dst < 1 || n_dst > 4 || n_cls < 2 || n_cls > kIdMaxCls || n_ch < 1 || n_ch > n_cls ||
+      h != (H + 2 * kIdPad - kIdK) / kIdStride + 1 || w != (W + 2 * kIdPad - kIdK) / kIdStride + 1 || S < 1)
+    return set_error(RMEM_ERR_ARG, "id_embed_soft: bad destination count / channel count / token grid");
+  IdSoftParams p;
+  p.prob = prob; p.ignore = ignore; p.taps = taps; p.bias = bias; p.gamma = gamma; p.beta = beta;
+  p.n_dst = n_dst; p.H = H; p.W = W; p.h = h; p.w = w; p.n_ch = n_ch; p.n_cls = n_cls;
+  for (int i = 0; i < 4; ++i) {
+    p.dst[i] = i < n_dst ? static_cast<__nv_bfloat16*>(dst[i]) : nullptr;
+    p.ld[i] = i < n_dst ? ld[i] : 0;
+    p.col0[i] = i < n_dst ? col0[i] : 0;
+  }
+  const size_t smem = static_cast<size_t>(n_cls) * kIdK * kIdK * sizeof(float);     // <= 18.5 KB
+  id_embed_soft_kernel<<<S * h * w, kIdC, smem, stream>>>(p);
+  return check_launch("id_embed_soft_kernel");
 }
 
 }  // namespace rmem

@@ -148,6 +148,9 @@ int id_embed_launch(const float* label, int H, int W, const float* prefix, const
                     const int* col0, int n_dst, int h, int w, cudaStream_t stream);
 int bank_init_launch(void* state, int frame_step, cudaStream_t stream);
 int bank_tick_batched_launch(void* state, int S, cudaStream_t stream);
+int id_embed_soft_launch(const float* prob, int n_ch, const float* ignore, int H, int W, const float* taps,
+                         const float* bias, const float* gamma, const float* beta, int n_cls, void* const* dst,
+                         const int* ld, const int* col0, int n_dst, int h, int w, int S, cudaStream_t stream);
 int id_embed_batched_launch(const float* label, int H, int W, const float* prefix, const float* bias,
                             const float* gamma, const float* beta, int n_cls, void* const* dst, const int* ld,
                             const int* col0, int n_dst, int h, int w, int S, cudaStream_t stream);

@@ -105,6 +105,7 @@ class PreparedDeAOT:
         self.n_id_cls = wid.shape[1]
         self.id_prefix = ops.id_prefix_table(wid).to(device)
         self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
+        self._id_w, self._id_taps = wid, None
         # black boxes (library calls): encoder / projector in bf16 channels-last with the frozen BN folded
         # into the convs, FPN head in fp32 (it decides the argmax mask)
         import os
@@ -113,6 +114,13 @@ class PreparedDeAOT:
         self.encoder = InferenceResNet(model.encoder, model.encoder_projector, device, encoder_dtype())
         self.decoder = InferenceFPN(sd, device, intermediate=False, shortcut_dtype=self.encoder.dtype)
 
+
+    def id_taps(self):
+        """patch_wise_id_bank.weight as [n_cls, 17, 17, 256] fp32 on the device (csrc/id_embed.cu, soft masks); built on
+        first use -- label maps, the evaluated form, never need it."""
+        if self._id_taps is None:
+            self._id_taps = ops.id_tap_table(self._id_w).to(self.device)
+        return self._id_taps
 
 class InferenceFPN:
     """FPNSegmentationHead (reference decoders/fpn.py:36-68) for inference, channels-last fp32 (it decides
@@ -673,13 +681,25 @@ class DeAOTEngine:
         ws, prep = self.ws, self.prep
         g, b = prep.id_norm
         dsts = [(ws.id_emb, 0)] + [(ws.idcat[i], 256) for i in range(prep.num_layers)]
+        if label_hw.dim() == 4:                 # one-hot / probability masks [S, n_ch, H, W]: the conv as a weighted sum
+            ops.id_embed_soft(label_hw, None, prep.id_taps(), prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)
+            return
         ops.id_embed(label_hw, prep.id_prefix, prep.id_bias, g, b, prep.n_id_cls, dsts, ws.h, ws.w)   # [S, H, W] labels
 
-    def _label_map(self, mask):
-        """Accepts [H,W], [S,H,W] or [S,1,H,W] label maps -> [S, H, W]; soft / one-hot masks are a training-only
-        form (aot_engine.py:330-334 takes that branch for batch > 1 only)."""
+    def _label_map(self, mask, allow_soft=False):
+        """Accepts [H,W], [S,H,W] or [S,1,H,W] label maps -> [S, H, W].  With ``allow_soft`` a 4-D tensor with more than
+        one channel is a one-hot / probability mask [S, max_obj + 1, H, W] (update_short_term_memory's second branch,
+        aot_engine.py:330-336; the reference reaches it with batch > 1 only, because it tells the two forms apart by
+        ``size()[0] == 1`` -- here the channel count decides, so one sequence can use it too) and is returned as
+        [S, n_ch, H, W] fp32."""
         if mask.dim() == 4 and mask.shape[1] != 1:
-            raise NotImplementedError("one-hot / probability masks are not on the evaluated path")
+            if not allow_soft:
+                raise ValueError("the reference frame takes a label map (aot_engine.py:162-164), got a %s tensor" %
+                                 (tuple(mask.shape),))
+            if mask.shape[0] != self.S or mask.shape[1] > self.prep.n_id_cls:
+                raise ValueError("expected one-hot / probability masks [%d, <= %d, H, W], got %s" %
+                                 (self.S, self.prep.n_id_cls, tuple(mask.shape)))
+            return mask.float().contiguous()
         if mask.numel() != self.S * mask.shape[-2] * mask.shape[-1]:
             raise ValueError("expected label maps for %d sequence(s), got a tensor of shape %s" %
                              (self.S, tuple(mask.shape)))
@@ -1176,7 +1196,8 @@ class DeAOTEngine:
         """aot_engine.py:327-369."""
         if curr_id_emb is not None:
             raise NotImplementedError("pre-computed id embeddings are a training-only path")
-        label = self._label_map(curr_mask.to(self.device)).float()
+        label = self._label_map(curr_mask.to(self.device), allow_soft=True).float()
+        soft = label.dim() == 4
         update_long = False
         if self.frame_step - self.last_mem_step >= self.long_term_mem_gap:
             update_long = True
@@ -1187,7 +1208,11 @@ class DeAOTEngine:
             raise _lib.RmemError("record_attn_weight is stale: call match_propogate_one_frame first")
         st = self.st
         body = lambda m: self._write_body(m, T, update_long, do_evict, st)
-        if self.lazy_write and self._prefetching:
+        if soft:
+            # rare form: its own graph key (the static input has another shape), on the calling stream
+            self._wait_write()
+            self._run(("write", T, update_long, do_evict, st, tuple(label.shape)), body, [label])
+        elif self.lazy_write and self._prefetching:
             # (a loop that does not prefetch keeps the write path on its own stream: there it overlaps the next
             # frame's encoder, which is worth more than the two graph boundaries -- 1055 vs 1017 frames/s)
             self._wait_write()                                    # an earlier deferred write path, if any

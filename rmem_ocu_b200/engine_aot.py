@@ -89,11 +89,18 @@ class PreparedAOT:
         self.mem_pos_emb = _f32(sd["mem_pos_emb"], device)
         wid = sd["patch_wise_id_bank.weight"].detach().float().cpu()            # [256, n_cls, 17, 17]
         self.n_id_cls = wid.shape[1]
+        self._id_w, self._id_taps = wid, None
         self.id_prefix = ops.id_prefix_table(wid).to(device)
         self.id_bias = _f32(sd["patch_wise_id_bank.bias"], device)
         self.id_norm = (None, None)                                             # AOT: no LayerNorm on the id embedding
         self.encoder = encoder_cls(model.encoder, model.encoder_projector, device, enc_dtype)
         self.decoder = decoder_cls(sd, device, intermediate=True, shortcut_dtype=self.encoder.dtype)
+
+    def id_taps(self):
+        """patch_wise_id_bank.weight as [n_cls, 17, 17, 256] fp32 on the device (soft masks), built on first use."""
+        if self._id_taps is None:
+            self._id_taps = ops.id_tap_table(self._id_w).to(self.device)
+        return self._id_taps
 
 
 class WorkspaceAOT:
@@ -169,6 +176,9 @@ class AOTBodies:
         id_emb next to curr_V / tgt3 of every layer (the A operand of linear_V / linear_VMem)."""
         ws, prep = self.ws, self.prep
         dsts = [(ws.mem[i], 256) for i in range(prep.num_layers)]
+        if label_hw.dim() == 4:                 # one-hot / probability masks [1, n_ch, H, W]
+            ops.id_embed_soft(label_hw, None, prep.id_taps(), prep.id_bias, None, None, prep.n_id_cls, dsts, ws.h, ws.w)
+            return
         ops.id_embed(label_hw[0], prep.id_prefix, prep.id_bias, None, None, prep.n_id_cls, dsts, ws.h, ws.w)
 
     def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):

@@ -333,6 +333,25 @@ def id_embed(label, prefix, bias, gamma, beta, n_cls, dsts, h, w):
     _count("rmem_id_embed")
 
 
+def id_embed_soft(prob, ignore, taps, bias, gamma, beta, n_cls, dsts, h, w):
+    """prob: f32 [S, n_ch, H, W] one-hot or probability masks; ignore: f32 [S, H, W] or None; taps: id_tap_table()."""
+    S, n_ch, H, W = prob.shape
+    n = len(dsts)
+    dp = (ctypes.c_void_p * n)(*[d.data_ptr() for d, _ in dsts])
+    ld = (ctypes.c_int32 * n)(*[d.stride(0) for d, _ in dsts])
+    c0 = (ctypes.c_int32 * n)(*[c for _, c in dsts])
+    _lib.check(_lib.lib().rmem_id_embed_soft(_p(prob), n_ch, _p(ignore), H, W, _p(taps), _p(bias), _p(gamma), _p(beta),
+                                             n_cls, ctypes.cast(dp, ctypes.c_void_p), ctypes.cast(ld, ctypes.c_void_p),
+                                             ctypes.cast(c0, ctypes.c_void_p), n, h, w, S, _stream()),
+               "rmem_id_embed_soft")
+    _count("rmem_id_embed_soft")
+
+
+def id_tap_table(weight):
+    """conv.weight [256, n_cls, 17, 17] -> [n_cls, 17, 17, 256] fp32 (output channel innermost)."""
+    return weight.detach().float().permute(1, 2, 3, 0).contiguous()
+
+
 def bank_append(state, T, frame_step, srcs, dsts):
     """Copy each src tensor (one slot's worth) into slot order[T] of the matching bank tensor."""
     n = len(srcs)

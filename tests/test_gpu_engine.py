@@ -423,3 +423,43 @@ def test_programmatic_dependent_launch_is_equivalent(lib_built):
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "smoke ok" in r.stdout
+
+
+def test_one_hot_masks_match_label_maps(lib_built):
+    """update_short_term_memory with a one-hot mask [1, 11, H, W] (aot_engine.py:330-336, the branch for masks that
+    already have one channel per identity) against the same clip driven with label maps: same bank, logits to 1e-2
+    (the identity embedding is a weighted sum instead of a table look-up: fp32 summation order differs before the
+    bf16 rounding), masks >= 99.9 %.  A probability mask (softmax of the logits) is accepted too and keeps the bank
+    schedule; rmem_id_embed_soft itself is checked against the oracle in test_gpu_ops.py."""
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    H, W, n, latter = 240, 432, 7, 2
+    imgs, lab = _clip(H, W, n, 3, seed=5)
+    outs = []
+    for form in ("label", "one_hot", "prob"):
+        m, _ = _models(latter)
+        eng = DeAOTInferEngine(m, 0, long_term_mem_gap=2)
+        logits = []
+        with torch.no_grad():
+            eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[3], frame_step=0)
+            e = eng.aot_engines[0]
+            for f in range(1, n):
+                lg = eng.match_propogate_one_frame(imgs[f].cuda(), output_size=(H, W))
+                logits.append(lg.clone())
+                prob = torch.softmax(lg, 1)
+                label = torch.argmax(prob, 1, keepdim=True).float()
+                if form == "label":
+                    e.update_short_term_memory(label)
+                elif form == "one_hot":
+                    e.update_short_term_memory(F.one_hot(label[0, 0].long(), 11).permute(2, 0, 1)[None].float())
+                else:
+                    e.update_short_term_memory(prob.contiguous())
+        torch.cuda.synchronize()
+        outs.append((logits, e.long_memories_indexes))
+    (la, ia), (lb, ib), (lc, ic) = outs
+    assert ia == ib and len(ic) == len(ia)
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-2, f
+        assert (a.argmax(1) == b.argmax(1)).float().mean().item() >= 0.999, f
+    assert all(torch.isfinite(x).all() for x in lc)
+    with pytest.raises(ValueError):
+        eng.aot_engines[0].add_reference_frame(imgs[0].cuda(), torch.zeros(1, 11, H, W).cuda(), obj_nums=[3], frame_step=0)

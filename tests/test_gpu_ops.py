@@ -178,6 +178,53 @@ def test_id_embed_vs_oracle(lib_built, H, W):
     assert torch.equal(out[:, 256:], out2) and (out[:, :256] == 0).all()
 
 
+@pytest.mark.parametrize("H,W,S,with_ignore,norm", [(480, 864, 1, True, True), (241, 433, 2, False, True),
+                                                    (113, 97, 1, True, False)])
+def test_id_embed_soft_vs_oracle(lib_built, H, W, S, with_ignore, norm):
+    """Probability / one-hot masks through rmem_id_embed_soft (update_short_term_memory's second branch,
+    aot_engine.py:330-336) against the oracle's assign_identity (fp32 conv + id_norm).  Output is bf16: relative
+    Frobenius error <= 5e-3; a hard one-hot mask must also give what the label-map kernel gives."""
+    from oracle import restate as R
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(11)
+    wt = torch.randn(256, 12, 17, 17) * 0.05
+    bias = torch.randn(256) * 0.1
+    g, b = torch.randn(256), torch.randn(256)
+    sd = {"patch_wise_id_bank.weight": wt, "patch_wise_id_bank.bias": bias, "id_norm.weight": g, "id_norm.bias": b}
+    prob = torch.softmax(torch.randn(S, 11, H, W) * 3, 1)
+    prob[:, :, : H // 3] = F.one_hot(prob[:, :, : H // 3].argmax(1), 11).permute(0, 3, 1, 2).float()   # saturated part
+    ignore = (torch.rand(S, 1, H, W) > 0.97).float() if with_ignore else None
+    h, w = (H + 16 - 17) // 16 + 1, (W + 16 - 17) // 16 + 1
+    refs = []
+    for s in range(S):
+        oh = prob[s:s + 1].clone()
+        ig = ignore[s:s + 1] if with_ignore else torch.zeros(1, 1, H, W)
+        oh[:, 0] = oh[:, 0] * (ig == 0).float().squeeze()
+        r = R.get_id_emb(torch.cat((oh, ig), 1), sd, norm)
+        assert r.shape[-2:] == (h, w)
+        refs.append(r.permute(0, 2, 3, 1).reshape(h * w, 256))
+    ref = torch.cat(refs, 0)
+    taps = ops.id_tap_table(wt).cuda()
+    out = torch.zeros(S * h * w, 512, device="cuda", dtype=torch.bfloat16)
+    out2 = torch.zeros(S * h * w, 256, device="cuda", dtype=torch.bfloat16)
+    gg, bb = (g.cuda(), b.cuda()) if norm else (None, None)
+    ops.id_embed_soft(prob.cuda(), ignore[:, 0].contiguous().cuda() if with_ignore else None, taps, bias.cuda(), gg, bb,
+                      12, [(out, 256), (out2, 0)], h, w)
+    torch.cuda.synchronize()
+    assert _rel(out[:, 256:].cpu(), ref) < 5e-3
+    assert torch.equal(out[:, 256:], out2) and (out[:, :256] == 0).all()
+    if S == 1:
+        # hard masks: the label kernel's table look-up and the weighted sum agree to bf16 rounding of fp32 sums
+        lab = prob.argmax(1).float()
+        hard = F.one_hot(lab.long(), 11).permute(0, 3, 1, 2).float().contiguous()
+        a = torch.zeros(h * w, 256, device="cuda", dtype=torch.bfloat16)
+        c = torch.zeros(h * w, 256, device="cuda", dtype=torch.bfloat16)
+        ops.id_embed_soft(hard.cuda(), None, taps, bias.cuda(), gg, bb, 12, [(a, 0)], h, w)
+        ops.id_embed(lab[0].cuda(), ops.id_prefix_table(wt).cuda(), bias.cuda(), gg, bb, 12, [(c, 0)], h, w)
+        torch.cuda.synchronize()
+        assert _rel(a, c) < 3e-3
+
+
 @pytest.mark.parametrize("C,H,W", [(256, 30, 54), (128, 60, 108), (128, 120, 216), (64, 7, 5)])
 def test_groupnorm_nhwc(lib_built, C, H, W):
     """GroupNorm(8) + ReLU of the decoder's ConvGN blocks (basic.py:60-70, fpn.py:44-63) vs F.group_norm."""
