@@ -12,6 +12,7 @@
 //          of 64 keys, O += P_b V_b accumulates in TMEM; the epilogue applies the gate and writes
 //          bf16.  This replaces unfold / local2global / the dense LxL matmul of attention.py:331-335,
 //          350-353, 363-402.
+#include <cstdlib>
 #include "sm100_ptx.cuh"
 #include "rmem_internal.h"
 
@@ -229,12 +230,23 @@ int local_scores_batched_launch(const void* q, const void* k, const float* rel, 
 // ------------------------------------------------------------------------------------------------
 // Stage 2: O[tile, dv slice] = sum_b P_b V_b with both operands streamed by TMA (P blocks from the banded
 // buffer, V halo blocks as 4-D boxes with out-of-image zero fill), accumulation in TMEM, gate in the epilogue.
-constexpr int kADV = 128;                                // value channels per CTA
-constexpr int kAStages = 4;
-constexpr uint32_t kAVBytes = 64 * kADV * 2;             // 16 KB  [2 cblk][64 keys][64 ch]
+// Variants (value channels per CTA, pipeline stages -> CTAs per SM), timed at 30 x 54 tokens with tools/dev_local.py
+// (aggregate kernel alone, us, S = 1 / 2 / 4 / 8 stacked sequences):
+//   1: 128 ch, 4 stages, 1 CTA/SM   12.2 / 20.0 / 35.8 / 61.0     <- one sequence
+//   2: 256 ch, 4 stages, 1 CTA/SM   16.0 / 16.8 / 29.6 / 54.7
+//   3: 256 ch, 2 stages, 2 CTA/SM   18.7 / 19.0 / 27.4 / 48.2
+//   4: 128 ch, 3 stages, 2 CTA/SM   12.6 / 16.9 / 27.7 / 49.3     <- batches (a second CTA hides the epilogue)
+// At S = 8 the kernel moves 270-360 MB from L2 to shared memory (P blocks re-read per value slice, V halo rows re-read
+// by neighbouring tiles: 5.5x) in ~50 us = 5.5-6 TB/s, about half the measured L2 ceiling; what would cut the traffic
+// itself -- one CTA sweeping a column strip so V rows are fetched once, P multicast across value slices -- is
+// described in DESIGN.md.  RMEM_LOCAL_AGG_VARIANT=1..4 forces a variant.
 constexpr uint32_t kAPBytes = 128 * 64 * 2;              // 16 KB  [128 q][64 keys]
-constexpr uint32_t kAStageBytes = kAVBytes + kAPBytes;
-constexpr uint32_t kASmem = kAStages * kAStageBytes + 1024 + 128;
+template <int kADV, int kAStages> struct AggCfg {
+  static constexpr uint32_t kVBytes = 64 * kADV * 2;     // 16 / 32 KB  [kADV / 64 cblk][64 keys][64 ch]
+  static constexpr uint32_t kStageBytes = kVBytes + kAPBytes;
+  static constexpr uint32_t kSmem = kAStages * kStageBytes + 1024 + 128;
+  static constexpr int kMinCtas = kSmem <= 110 * 1024 ? 2 : 1;
+};
 constexpr int kAThreads = 64 + 128;
 
 struct AggParams {
@@ -243,13 +255,14 @@ struct AggParams {
   int h, w;
 };
 
-__global__ void __launch_bounds__(kAThreads, 1)
+template <int kADV, int kAStages>
+__global__ void __launch_bounds__(kAThreads, AggCfg<kADV, kAStages>::kMinCtas)
 local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_v,
                        const AggParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kAStages * kAStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kAStages * AggCfg<kADV, kAStages>::kStageBytes);
   uint64_t* full = bars;                   // [kAStages]
   uint64_t* empty = bars + kAStages;       // [kAStages]
   uint64_t* o_full = bars + 2 * kAStages;
@@ -269,7 +282,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
     mbar_init(o_full, 1);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  if (warp == 1) tmem_alloc<kADV>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -282,10 +295,10 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
       for (int b = 0; b < kABlocks; ++b) {
         const int st = b % kAStages;
         if (b >= kAStages) mbar_wait(empty + st, ((b / kAStages) - 1) & 1);
-        uint8_t* dst = smem + st * kAStageBytes;
-        mbar_expect_tx(full + st, kAStageBytes);
+        uint8_t* dst = smem + st * AggCfg<kADV, kAStages>::kStageBytes;
+        mbar_expect_tx(full + st, AggCfg<kADV, kAStages>::kStageBytes);
         tma_load_2d(dst, &tm_p, full + st, 0, (tile * kABlocks + b) * 128);
-        tma_load_5d(dst + kAPBytes, &tm_v, full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, dv * 2, seq);
+        tma_load_5d(dst + kAPBytes, &tm_v, full + st, 0, x0 - kMaxDis, y0 - kMaxDis + 2 * b, dv * (kADV / 64), seq);
       }
     }
   } else if (warp == 1) {
@@ -296,7 +309,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
       const int st = b % kAStages;
       mbar_wait(full + st, (b / kAStages) & 1);
       tc_fence_after();
-      const uint32_t p_addr = smem_u32(smem + st * kAStageBytes);
+      const uint32_t p_addr = smem_u32(smem + st * AggCfg<kADV, kAStages>::kStageBytes);
       const uint32_t v_addr = p_addr + kAPBytes;
       if (elect_one()) {
 #pragma unroll
@@ -357,7 +370,7 @@ local_aggregate_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_co
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<128>(tmem_base);
+    tmem_dealloc<kADV>(tmem_base);
   }
 }
 
@@ -373,17 +386,20 @@ int local_aggregate_launch(const void* banded, const void* v, const void* gate, 
 
 int local_aggregate_batched_launch(const void* banded, const void* v, const void* gate, void* out, int h, int w, int S,
                                    cudaStream_t stream) {
-  if (h < 1 || w < 1 || !banded || S < 1 || S * (1024 / kADV) > 65535)
+  if (h < 1 || w < 1 || !banded || S < 1 || S * 8 > 65535)
     return set_error(RMEM_ERR_ARG, "local_aggregate: bad h / w / batch / banded buffer");
   auto fn = get_tensor_map_encoder();
   if (!fn) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled entry point not found");
   const int tiles_x = (w + kATileW - 1) / kATileW, tiles_y = (h + kATileH - 1) / kATileH;
+  static const int forced = [] { const char* e = getenv("RMEM_LOCAL_AGG_VARIANT"); return e ? atoi(e) : 0; }();
+  const int variant = forced ? forced : (S >= 2 ? 4 : 1);
+  const int dv_per_cta = (variant == 2 || variant == 3) ? 256 : 128;
   CUtensorMap tm_v, tm_p;
   {
     const uint64_t dims[5] = {64, static_cast<uint64_t>(w), static_cast<uint64_t>(h), 16, static_cast<uint64_t>(S)};
     const uint64_t strides[4] = {1024 * 2, static_cast<uint64_t>(w) * 1024 * 2, 128,
                                  static_cast<uint64_t>(h) * w * 1024 * 2};
-    const uint32_t box[5] = {64, kABoxW, 2, kADV / 64, 1};
+    const uint32_t box[5] = {64, kABoxW, 2, static_cast<uint32_t>(dv_per_cta / 64), 1};
     const uint32_t es[5] = {1, 1, 1, 1, 1};
     CUresult r = fn(&tm_v, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v), dims, strides, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -400,15 +416,23 @@ int local_aggregate_batched_launch(const void* banded, const void* v, const void
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(RMEM_ERR_DRIVER, "cuTensorMapEncodeTiled (banded P) failed");
   }
-  static SmemOptIn optin;
-  if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_aggregate_kernel), &optin, kASmem,
-                                  "local_aggregate: cudaFuncSetAttribute"))
-    return r;
   AggParams p;
   p.gate = static_cast<const __nv_bfloat16*>(gate);
   p.out = static_cast<__nv_bfloat16*>(out); p.h = h; p.w = w;
-  dim3 grid(tiles_x, tiles_y, (1024 / kADV) * S);
-  launch_k(local_aggregate_kernel, grid, kAThreads, kASmem, stream, tm_p, tm_v, p);
+  dim3 grid(tiles_x, tiles_y, (1024 / dv_per_cta) * S);
+#define RMEM_AGG_LAUNCH(DV, ST)                                                                                    \
+  {                                                                                                                \
+    static SmemOptIn optin;                                                                                        \
+    if (int r = ensure_dynamic_smem(reinterpret_cast<const void*>(local_aggregate_kernel<DV, ST>), &optin,         \
+                                    AggCfg<DV, ST>::kSmem, "local_aggregate: cudaFuncSetAttribute"))               \
+      return r;                                                                                                    \
+    launch_k(local_aggregate_kernel<DV, ST>, grid, kAThreads, AggCfg<DV, ST>::kSmem, stream, tm_p, tm_v, p);       \
+  }
+  if (variant == 1) RMEM_AGG_LAUNCH(128, 4)
+  else if (variant == 2) RMEM_AGG_LAUNCH(256, 4)
+  else if (variant == 3) RMEM_AGG_LAUNCH(256, 2)
+  else RMEM_AGG_LAUNCH(128, 3)
+#undef RMEM_AGG_LAUNCH
   return check_launch("local_aggregate_kernel");
 }
 
