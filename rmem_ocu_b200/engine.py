@@ -14,6 +14,8 @@ There is no CPU / PyTorch fallback: without CUDA or the shared library the engin
 
 import functools
 
+import collections
+
 import torch
 import torch.nn.functional as F
 
@@ -581,7 +583,7 @@ class DeAOTEngine:
         # stream, into one of two alternating sets of embeddings, while this frame's LSTT + decoder run
         self._estream = None
         self._enc_done = None        # event: the prefetched embeddings are complete
-        self._prefetched = None      # (embeddings, set index) of the frame encoded ahead, or None
+        self._pq = collections.deque()   # frames encoded ahead: (embeddings, (set, batch, index)) in call order
         self._enc_set = 0            # the embedding set (encoder graph 0 / 1) the next prefetch writes
         self._hp_stream = None
         self._graphs = {}
@@ -634,7 +636,8 @@ class DeAOTEngine:
                 self.ws.sk_ws = ops.lt_attn_sk_workspace(self.ws.L, n_slots, self.device, self.lt_sk_clusters, self.S)
             self._wait_write()
             self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None   # graphs bake the workspace pointers
-            self._prefetched, self._enc_set = None, 0
+            self._pq.clear()
+            self._enc_set = 0
 
     @property
     def long_memories_indexes(self):
@@ -1023,9 +1026,12 @@ class DeAOTEngine:
         return out
 
     def _launch_encoder(self, img):
-        """Encode ``img`` on the encoder stream, ordered after the point the current stream has reached.  Two
-        encoder graphs with their own output sets alternate: the set written now was last read by the frame
-        before the current one, which the current stream has already passed, so nothing is ever copied."""
+        """Encode ``img`` -- one frame, or a stack of the next B frames of this sequence in ONE batched pass (the cuDNN
+        trunk is latency-bound at one 480p frame: 293 us for one frame, 198 / 179 / 170 us per frame at B = 2 / 3 / 4)
+        -- on the encoder stream, ordered after the point the current stream has reached.  Two encoder graphs with
+        their own output sets alternate: the set written now was last read by the frame before the current one, which
+        the current stream has already passed, so nothing is ever copied.  Frame j of the stack is the batch slice
+        [j:j+1] of every output: B read-graph variants per set, recorded once."""
         if self._estream is None:
             self._estream = torch.cuda.Stream(device=self.device)
         es = self._estream
@@ -1034,28 +1040,38 @@ class DeAOTEngine:
         es.wait_event(ready)
         if img.is_cuda:
             img.record_stream(es)
+        B = img.shape[0] // self.S
+        if B > 1 and self.S > 1:
+            raise NotImplementedError("encoder look-ahead batches are implemented for one sequence per engine")
         p = self._enc_set
         self._enc_set = 1 - p
         with torch.cuda.stream(es):
-            embs = list(self._run(("enc", p), self._encode_body, [img]))
+            embs = list(self._run(("enc", p, B), self._encode_body, [img]))
             self._enc_done = torch.cuda.Event()
             self._enc_done.record()
-        self._prefetched = (embs, p)
+        for j in range(B):
+            self._pq.append(([e[j * self.S:(j + 1) * self.S] for e in embs] if B > 1 else embs, (p, B, j)))
 
     def _take_prefetched(self):
-        """The embeddings encoded ahead and the index of their set; the current stream waits for the encoder."""
+        """The oldest frame encoded ahead and the (set, batch, index) of its embeddings; the current stream waits for
+        the encoder pass that produced them."""
         cur = torch.cuda.current_stream()
         cur.wait_event(self._enc_done)
-        (embs, p), self._prefetched = self._prefetched, None
+        embs, p = self._pq.popleft()
         for e in embs:
             e.record_stream(cur)
         return embs, p
 
+    def frames_ahead(self):
+        """How many frames have been encoded ahead (``next_img``) and not yet consumed."""
+        return len(self._pq)
+
     @_on_device
-    def precapture(self, output_size=None, prefetch=False):
+    def precapture(self, output_size=None, prefetch=False, lookahead=1):
         """Capture the read / write graphs of every bank length now (capturing records, it does not
         execute, so the sequence state is untouched). Call after the first propagated frame.  ``prefetch``: record
-        the read graphs on the embedding set used by ``match_propogate_one_frame(..., next_img=)``."""
+        the read graphs on the embedding sets used by ``match_propogate_one_frame(..., next_img=)``; ``lookahead``: the
+        number of frames a ``next_img`` stack will hold."""
         if not self.use_cuda_graphs or self.frame_step < 1:
             return 0
         H, W = self.input_size_2d
@@ -1070,9 +1086,12 @@ class DeAOTEngine:
         self._wait_write()
         sets = {}
         for p in ((0, 1) if prefetch else (0,)):                  # prefetching alternates between two sets
-            if ("enc", p) not in self._graphs:
-                self._capture(("enc", p), self._encode_body, [img])
-            sets[p] = list(self._graphs[("enc", p)][2])           # the encoder graphs' outputs feed the read graphs
+            for B in sorted({1, lookahead} if prefetch else {1}):
+                if ("enc", p, B) not in self._graphs:
+                    self._capture(("enc", p, B), self._encode_body, [img if B == 1 else torch.cat([img] * B)])
+                outs = list(self._graphs[("enc", p, B)][2])       # the encoder graphs' outputs feed the read graphs
+                for j in range(B):
+                    sets[(p, B, j)] = [e[j * self.S:(j + 1) * self.S] for e in outs] if B > 1 else outs
         for T in range(1, self.capacity + 1):
             for key, body, inputs, alias in self._variants(T, output_size, sets, label):
                 if key not in self._graphs:
@@ -1116,7 +1135,7 @@ class DeAOTEngine:
         self._wait_write()
         if self._enc_done is not None:                           # an encoder pass left over from another sequence
             torch.cuda.current_stream().wait_event(self._enc_done)
-            self._prefetched = None
+            self._pq.clear()
         if obj_nums is not None:
             self.obj_nums = obj_nums
         if frame_step == -1:
@@ -1152,9 +1171,11 @@ class DeAOTEngine:
         live in a buffer that the next call overwrites -- consume them (softmax / argmax) first, as the
         reference's evaluator does.
 
-        ``next_img`` (optional, not in the reference): the frame that will be passed to the NEXT call.  Its
-        encoder pass starts now on a second stream and overlaps this frame's LSTT + decoder (the encoder depends
-        on nothing but the image); the next call must then be given that same frame."""
+        ``next_img`` (optional, not in the reference; its closest relative there is ``offline_encoder``,
+        aot_engine.py:174-196, which encodes a whole clip in one batch): the frame that will be passed to the NEXT call,
+        or a stack of the frames of the next B calls.  Their encoder pass -- one batched pass -- starts now on a second
+        stream and overlaps this frame's LSTT + decoder (the encoder depends on nothing but the images); the next B
+        calls must then be given those same frames, and the next stack comes with the call that consumes the last."""
         if img is not None and self._img_sig is not None and (img.dtype, tuple(img.shape)) != self._img_sig:
             raise _lib.RmemError("frames of one sequence must share the reference frame's dtype and shape: got %s %s, "
                                  "the sequence started with %s %s" % (img.dtype, tuple(img.shape), *self._img_sig))
@@ -1168,15 +1189,18 @@ class DeAOTEngine:
             return self._read_body(None, img_embs, T, osz, st)
         # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
         # running on its own stream) and, after waiting for that write path, LSTT + decoder
-        self._prefetching = next_img is not None
-        if next_img is not None or self._prefetched is not None:
-            if self._prefetched is None:
+        if next_img is not None or self._pq:
+            if not self._pq:
                 self._launch_encoder(img)                 # first frame of a prefetching loop: nothing encoded ahead
             embs, p = self._take_prefetched()
             if next_img is not None:
+                if self._pq:
+                    raise _lib.RmemError("next_img given while %d frame(s) encoded ahead are still waiting: pass the "
+                                         "next stack with the call that consumes the last one" % len(self._pq))
                 self._launch_encoder(next_img)
         else:
-            embs, p = self._run(("enc", 0), self._encode_body, [img]), 0
+            embs, p = self._run(("enc", 0, 1), self._encode_body, [img]), (0, 1, 0)
+        self._prefetching = bool(self._pq)                # the next call finds its embeddings ready
         if self._pending_w is not None:
             pend, self._pending_w = self._pending_w, None
             return self._run(("wr",) + pend + (T, osz, st, p),
@@ -1355,8 +1379,11 @@ class DeAOTInferEngine:
         for engine, m in zip(self.aot_engines, self.separate_mask(curr_mask)):
             engine.update_short_term_memory(m)
 
-    def precapture(self, output_size=None, prefetch=False):
-        return sum(e.precapture(output_size, prefetch) or 0 for e in self.aot_engines[:1])
+    def precapture(self, output_size=None, prefetch=False, lookahead=1):
+        return sum(e.precapture(output_size, prefetch, lookahead) or 0 for e in self.aot_engines[:1])
+
+    def frames_ahead(self):
+        return min(e.frames_ahead() for e in self.aot_engines) if self.aot_engines else 0
 
     def update_size(self):
         self.input_size_2d = self.aot_engines[0].input_size_2d

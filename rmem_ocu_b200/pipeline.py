@@ -51,6 +51,24 @@ class FrameStreamer:
             ev.record()
         self._staged.append((i, ev))
 
+    def stage_stack(self, host_imgs):
+        """Start the upload of several pinned host images into ONE device buffer [n, ...] (the stack an engine takes
+        as ``next_img``: the frames of its next n calls); returns immediately."""
+        i = self._next
+        self._next = (i + 1) % self.depth
+        shape = (len(host_imgs) * host_imgs[0].shape[0],) + tuple(host_imgs[0].shape[1:])
+        if self._bufs[i] is None or tuple(self._bufs[i].shape) != shape or self._bufs[i].dtype != host_imgs[0].dtype:
+            self._bufs[i] = torch.empty(shape, dtype=host_imgs[0].dtype, device=self.device)
+        if self._free[i] is not None:
+            self._up.wait_event(self._free[i])
+        n0 = host_imgs[0].shape[0]
+        with torch.cuda.stream(self._up):
+            for j, im in enumerate(host_imgs):
+                self._bufs[i][j * n0:(j + 1) * n0].copy_(im, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        self._staged.append((i, ev))
+
     def acquire(self):
         """Oldest staged image as a device tensor; the current stream waits for its upload."""
         i, ev = self._staged.popleft()
@@ -63,7 +81,8 @@ class FrameStreamer:
         stream; ``tensor`` names the image (default: the one acquired last)."""
         idx = self._cur
         if tensor is not None:
-            idx = next(i for i, b in enumerate(self._bufs) if b is tensor)
+            idx = next(i for i, b in enumerate(self._bufs)
+                       if b is tensor or (b is not None and tensor.data_ptr() == b.data_ptr()))
         ev = torch.cuda.Event()
         ev.record()
         self._free[idx] = ev

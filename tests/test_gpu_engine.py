@@ -125,7 +125,7 @@ def test_full_path_images(lib_built):
     assert min(agree) >= 0.999, agree
 
 
-def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=True):
+def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=True, lookahead=1):
     from rmem_ocu_b200.engine import DeAOTInferEngine
     eng = DeAOTInferEngine(m, 0, long_term_mem_gap=gap)
     masks, logits, idx = [], [], []
@@ -133,7 +133,11 @@ def _run_infer(m, imgs, lab, H, W, n_obj, gap, prefetch=False, idx_every_frame=T
         eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[n_obj], frame_step=0)
         dimgs = [im.cuda() for im in imgs]
         for f in range(1, len(imgs)):
-            nxt = dimgs[f + 1] if prefetch and f + 1 < len(imgs) else None
+            nxt = None
+            if prefetch and f + 1 < len(imgs) and eng.frames_ahead() <= 1:
+                # the stack of the next `lookahead` frames (the clip's tail: a shorter stack), handed over with the
+                # call that consumes the last frame encoded ahead
+                nxt = torch.cat(dimgs[f + 1:f + 1 + lookahead])
             lg = eng.match_propogate_one_frame(dimgs[f], output_size=(H, W), next_img=nxt)
             logits.append(lg.clone())
             label = torch.argmax(torch.softmax(lg, 1), 1, keepdim=True).float()
@@ -315,11 +319,37 @@ def test_encoder_prefetch_matches_sequential(lib_built):
     ma, la, ia, ea = _run_infer(m, imgs, lab, H, W, 3, gap=2)
     m2, _ = _models(latter)
     mb, lb, ib, eb = _run_infer(m2, imgs, lab, H, W, 3, gap=2, prefetch=True)
-    assert eb.aot_engines[0]._estream is not None and ("enc", 1) in eb.aot_engines[0]._graphs
+    assert eb.aot_engines[0]._estream is not None and ("enc", 1, 1) in eb.aot_engines[0]._graphs
     assert ia == ib
     for f, (a, b) in enumerate(zip(la, lb)):
         assert ((a - b).norm() / b.norm()).item() < 1e-3, f
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+
+
+@pytest.mark.parametrize("lookahead", [2, 3])
+def test_encoder_lookahead_stacks_match_sequential(lib_built, lookahead):
+    """next_img as a STACK of the next B frames: one batched encoder pass feeds the next B calls (frame j = batch
+    slice j of every embedding).  Same clip as frame-by-frame: slot indexes equal after every frame, logits to 1e-2
+    (cuDNN picks other algorithms at batch B), masks >= 99.9 %.  14 frames with B = 3 ends on a shorter stack; a
+    second stack offered while frames are still waiting is refused."""
+    from rmem_ocu_b200 import _lib
+    H, W, n, latter = 240, 432, 14, 2
+    imgs, lab = _clip(H, W, n, 3)
+    m, _ = _models(latter)
+    ma, la, ia, ea = _run_infer(m, imgs, lab, H, W, 3, gap=2)
+    m2, _ = _models(latter)
+    mb, lb, ib, eb = _run_infer(m2, imgs, lab, H, W, 3, gap=2, prefetch=True, lookahead=lookahead)
+    e = eb.aot_engines[0]
+    assert any(k[0] == "enc" and k[2] == lookahead for k in e._graphs) and e.frames_ahead() == 0
+    assert ia == ib
+    for f, (a, b) in enumerate(zip(la, lb)):
+        assert ((a - b).norm() / b.norm()).item() < 1e-2, f
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+    with torch.no_grad():
+        stack = torch.cat([imgs[1].cuda(), imgs[2].cuda()])
+        eb.match_propogate_one_frame(imgs[1].cuda(), output_size=(H, W), next_img=stack)
+        with pytest.raises(_lib.RmemError):
+            eb.match_propogate_one_frame(imgs[1].cuda(), output_size=(H, W), next_img=stack)
 
 
 def test_u8_frames_match_normalised_planes(lib_built):
