@@ -564,6 +564,7 @@ class DeAOTEngine:
         if self.lt_sk_clusters < 0:
             self.lt_sk_clusters = default_sk_clusters(self.device) if self.fork_branches else 0
         self._side = None
+        self._cap_stream = None
         # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
         # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
         self.async_write = os_env_flag("RMEM_ASYNC_WRITE", True)
@@ -977,8 +978,11 @@ class DeAOTEngine:
         # RMEM_HP_CAPTURE=1 records on a high-priority stream (kernel nodes inherit the capture stream's priority,
         # so the frame's own kernels win SMs over the concurrently running encoder of the next frame).  Measured
         # +1.5% device-resident but -1% host-to-host (graph launches cost 0.34 instead of 0.22 ms of host time): off.
-        if self._hp_stream is None and os_env_flag("RMEM_HP_CAPTURE", False):
-            self._hp_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        # (the capture stream is always this engine's own: torch's default capture stream is created once per process
+        # on whichever device was current then, and would move an engine on another device onto that device)
+        if self._hp_stream is None:
+            self._hp_stream = torch.cuda.Stream(device=self.device,
+                                                priority=-1 if os_env_flag("RMEM_HP_CAPTURE", False) else 0)
         with torch.cuda.graph(g, pool=pool, stream=self._hp_stream):
             out = body(*static_in)
         ent = (g, static_in, out, ops.LAUNCHES - launches0)
@@ -996,7 +1000,9 @@ class DeAOTEngine:
         torch.cuda.synchronize()
         # one memory pool per encoder graph: graphs sharing a pool reuse each other's scratch, and encoder graph
         # 0 replays while the outputs of encoder graph 1 are being read (and the other way round)
-        with torch.cuda.graph(g):
+        if self._cap_stream is None:
+            self._cap_stream = torch.cuda.Stream(device=self.device)      # see _capture: never the process-wide default
+        with torch.cuda.graph(g, stream=self._cap_stream):
             out = body(*static_in)
         ent = (g, static_in, out, ops.LAUNCHES - launches0)
         ops.LAUNCHES = launches0
