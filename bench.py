@@ -176,7 +176,9 @@ def frame_step(eng, img_dev, out_hw, next_img=None):
     step's work, overlapped with this step's LSTT + decoder; every step still runs exactly one encoder pass)."""
     from rmem_ocu_b200 import ops
     logit = eng.match_propogate_one_frame(img_dev, output_size=out_hw, next_img=next_img)
-    label = ops.argmax_label(logit)                              # = argmax(softmax(.)), evaluator.py:430-441
+    label = eng.pred_label                                       # = argmax(softmax(.)), evaluator.py:430-441, computed
+    if label is None:                                            # by the decoder's last kernel (one engine), else here
+        label = ops.argmax_label(logit)
     if tuple(label.shape[-2:]) != tuple(eng.input_size_2d):
         label_in = F.interpolate(label, size=eng.input_size_2d, mode="nearest")      # evaluator.py:518-522
     else:
@@ -447,7 +449,7 @@ def run_lockstep(model, local_rank, seq_ids, spec, steps, head, prefetch=True):
 
     def step(f):
         lg = eng.match_propogate_one_frame(img(f), output_size=(h, w), next_img=img(f + 1) if prefetch else None)
-        eng.update_short_term_memory(ops.argmax_label(lg))
+        eng.update_short_term_memory(eng.pred_label if eng.pred_label is not None else ops.argmax_label(lg))
 
     with torch.no_grad():
         eng.add_reference_frame(frames[0], torch.cat(labs).to(dev), obj_nums=[n_obj] * S, frame_step=0)

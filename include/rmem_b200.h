@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 7
+#define RMEM_ABI_VERSION 8
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -314,6 +314,23 @@ int rmem_pack_image_s2d_batched(const void* img, int img_u8_hwc, const float* me
 int rmem_maxpool3s2_nhwc_batched(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
                                  int S, void* stream);
 int rmem_argmax_label_batched(const float* logits, int C, int HW, float* label, int S, void* stream);
+
+/* The decoder's last stage in one pass (decoders/fpn.py:63-68: conv_4x's GroupNorm(8) + ReLU, then the 1x1 conv_out;
+ * aot_engine.py:451-463: classes beyond the sequence's objects -> -1e10, bilinear align_corners resize to the output
+ * size; and the evaluator's argmax, networks/managers/evaluator.py:430-441).  The normalised feature map is never
+ * written: statistics, then GroupNorm + ReLU + the C -> Co dot products + bias + mask straight into pred.
+ *   x        f32 [S][Hs*Ws][C] raw output of the 3x3 conv_4x (channels-last), C = 64 or 128
+ *   pre_bias f32 [C] conv_4x bias or NULL; gamma, beta f32 [C]; groups (8)
+ *   w_out    f32 [Co][C], b_out f32 [Co], Co <= 16
+ *   n_valid_host  HOST i32 [S]: objects + 1 per image;  S <= 64
+ *   pred     f32 [S][Co][Hs][Ws]  (= pred_id_logits)
+ *   out      f32 [S][Co][Ho][Wo] or NULL;  label f32 [S][Ho][Wo] or NULL (argmax over the classes of out, first maximum)
+ *   workspace: as rmem_groupnorm_nhwc_batched (S blocks of 16 * groups + 8 bytes, zero before the first call)
+ */
+int rmem_logits_head_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs, int Ws,
+                             int C, int groups, const float* w_out, const float* b_out, int Co,
+                             const int32_t* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
+                             void* workspace, void* stream);
 int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
                          int C, int S, void* stream);
 int rmem_groupnorm_tokens_batched(const float* x_a, int Ca, const float* x_b, const float* gamma, const float* beta,

@@ -209,11 +209,12 @@ finish_logits_kernel(const float* __restrict__ conv, long long sn, long long sc,
 
 __global__ void __launch_bounds__(256)
 upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, float* __restrict__ out, int Ho,
-                       int Wo) {
+                       int Wo, float* __restrict__ label) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
   pred += static_cast<size_t>(blockIdx.y) * C * Hs * Ws;
   out += static_cast<size_t>(blockIdx.y) * C * Ho * Wo;
+  if (label) label += static_cast<size_t>(blockIdx.y) * Ho * Wo;   // argmax over the channels (first maximum), f32
   // thread = 4 consecutive output pixels of one row, all C channels (weights computed once per pixel)
   const int wq = (Wo + 3) / 4;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -234,18 +235,30 @@ upsample_logits_kernel(const float* __restrict__ pred, int C, int Hs, int Ws, fl
     lx[k] = fx - x0[k];
   }
   const bool full = x4 + 3 < Wo && (Wo & 3) == 0;
+  float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  float arg[4] = {0.f, 0.f, 0.f, 0.f};
   for (int c = 0; c < C; ++c) {
     const float* r0 = pred + (static_cast<size_t>(c) * Hs + y0) * Ws;
     const float* r1 = pred + (static_cast<size_t>(c) * Hs + y1) * Ws;
     float o[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 4; ++k) {
       o[k] = hy * ((1.f - lx[k]) * r0[x0[k]] + lx[k] * r0[x1[k]]) + ly * ((1.f - lx[k]) * r1[x0[k]] + lx[k] * r1[x1[k]]);
+      if (c == 0 || o[k] > best[k]) { best[k] = o[k]; arg[k] = static_cast<float>(c); }
+    }
     float* d = out + (static_cast<size_t>(c) * Ho + y) * Wo + x4;
     if (full) {
       *reinterpret_cast<float4*>(d) = make_float4(o[0], o[1], o[2], o[3]);
     } else {
       for (int k = 0; k < 4 && x4 + k < Wo; ++k) d[k] = o[k];
+    }
+  }
+  if (label) {
+    float* d = label + static_cast<size_t>(y) * Wo + x4;
+    if (full) {
+      *reinterpret_cast<float4*>(d) = make_float4(arg[0], arg[1], arg[2], arg[3]);
+    } else {
+      for (int k = 0; k < 4 && x4 + k < Wo; ++k) d[k] = arg[k];
     }
   }
 }
@@ -268,7 +281,110 @@ int finish_logits_batched_launch(const float* conv, long long sn, long long sc, 
   if (int r = check_launch("finish_logits_kernel")) return r;
   if (out) {
     const int n = Ho * ((Wo + 3) / 4);
-    launch_k(upsample_logits_kernel, dim3((n + 255) / 256, S), 256, 0, stream, pred, C, Hs, Ws, out, Ho, Wo);
+    launch_k(upsample_logits_kernel, dim3((n + 255) / 256, S), 256, 0, stream, pred, C, Hs, Ws, out, Ho, Wo,
+             static_cast<float*>(nullptr));
+    return check_launch("upsample_logits_kernel");
+  }
+  return RMEM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The decoder's last stage in one pass over the conv_4x output (decoders/fpn.py:63-68 + aot_engine.py:451-463):
+// GroupNorm(8) + ReLU of the 3x3 convolution's raw output x [P][C] (statistics from gn_nhwc_stats_kernel), the 1x1
+// conv_out (C -> Co <= 16 classes) as fp32 dot products, + bias, classes beyond the sequence's objects -> -1e10,
+// written as pred_id_logits [Co][P].  The normalised C-channel map is never stored (13 MB at 480p), the cuDNN 1x1
+// convolution and the bias / mask pass disappear.  C / 4 <= 32 lanes share a pixel (four channels each); the Co partial
+// dot products are reduced over them with xor shuffles, lane c writes class c.
+constexpr int kHeadMaxCo = 16;
+struct HeadParams {
+  const float* x;
+  const float* pre_bias;
+  const float* gamma;
+  const float* beta;
+  const float* w_out;        // [Co][C]
+  const float* b_out;        // [Co]
+  float* pred;               // [S][Co][P]
+  double* ws;
+  int P, C, cpg, Co;
+  ValidCounts valid;
+};
+
+__global__ void __launch_bounds__(256) gn_head_kernel(const HeadParams p) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
+  extern __shared__ float w_sh[];                       // [Co][C]
+  const int C = p.C, Co = p.Co, P = p.P;
+  for (int i = threadIdx.x; i < Co * C; i += blockDim.x) w_sh[i] = p.w_out[i];
+  const float* x = p.x + static_cast<size_t>(blockIdx.y) * P * C;
+  float* pred = p.pred + static_cast<size_t>(blockIdx.y) * Co * P;
+  double* ws = p.ws + static_cast<size_t>(blockIdx.y) * (2 * (C / p.cpg) + 1);
+  const int n_valid = p.valid.n[blockIdx.y];
+  const int tpp = C >> 2;                               // lanes per pixel: 16 or 32
+  const int ppb = 256 / tpp;                            // pixels per CTA step
+  const int c = (threadIdx.x % tpp) * 4;
+  const int sub = threadIdx.x % tpp;
+  const int g = c / p.cpg;
+  const double cnt = static_cast<double>(p.cpg) * P;
+  const double mean_d = ws[2 * g] / cnt;
+  const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
+  const float mean = static_cast<float>(mean_d);
+  const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
+  float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.pre_bias) pb = *reinterpret_cast<const float4*>(p.pre_bias + c);
+  const float4 ga = *reinterpret_cast<const float4*>(p.gamma + c);
+  const float4 be = *reinterpret_cast<const float4*>(p.beta + c);
+  const float bo = sub < Co ? p.b_out[sub] : 0.f;
+  __syncthreads();
+  const int steps = (P + ppb - 1) / ppb;                // whole warps stay in the loop (shuffles below)
+  for (int st = blockIdx.x; st < steps; st += gridDim.x) {
+    const int pix = st * ppb + threadIdx.x / tpp;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pix < P) v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    float y0 = fmaxf((v.x + pb.x - mean) * rstd * ga.x + be.x, 0.f);
+    float y1 = fmaxf((v.y + pb.y - mean) * rstd * ga.y + be.y, 0.f);
+    float y2 = fmaxf((v.z + pb.z - mean) * rstd * ga.z + be.z, 0.f);
+    float y3 = fmaxf((v.w + pb.w - mean) * rstd * ga.w + be.w, 0.f);
+    float mine = 0.f;
+    for (int o = 0; o < Co; ++o) {
+      const float4 w = *reinterpret_cast<const float4*>(w_sh + o * C + c);
+      float d = (y0 * w.x + y1 * w.y) + (y2 * w.z + y3 * w.w);
+      for (int m = tpp >> 1; m > 0; m >>= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
+      if (sub == o) mine = d;
+    }
+    if (pix < P && sub < Co) pred[static_cast<size_t>(sub) * P + pix] = sub < n_valid ? mine + bo : -1e10f;
+  }
+  gn_ws_release(ws, 2 * (C / p.cpg));
+}
+
+int logits_head_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs,
+                               int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
+                               const int* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
+                               void* workspace, cudaStream_t stream) {
+  const int P = Hs * Ws;
+  if (groups < 1 || (C % groups) || (C != 64 && C != 128) || Co < 1 || Co > kHeadMaxCo || P < 1 || S < 1 || S > 64 ||
+      !n_valid_host)
+    return set_error(RMEM_ERR_ARG, "logits_head: C must be 64 / 128, at most 16 classes and 64 images");
+  const int cpg = C / groups;
+  if ((cpg & (cpg - 1)) || cpg < 4 || cpg > 32)
+    return set_error(RMEM_ERR_ARG, "logits_head: channels per group must be a power of two in [4, 32]");
+  const int per = (592 + S - 1) / S;
+  int rows = (P + per - 1) / per;
+  if (rows < 8) rows = 8;
+  launch_k(gn_nhwc_stats_kernel, dim3((P + rows - 1) / rows, S), 256, 0, stream, x, pre_bias, P, C, cpg, rows,
+           static_cast<double*>(workspace));
+  if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
+  HeadParams hp;
+  hp.x = x; hp.pre_bias = pre_bias; hp.gamma = gamma; hp.beta = beta; hp.w_out = w_out; hp.b_out = b_out;
+  hp.pred = pred; hp.ws = static_cast<double*>(workspace); hp.P = P; hp.C = C; hp.cpg = cpg; hp.Co = Co;
+  for (int s = 0; s < 64; ++s) hp.valid.n[s] = s < S ? n_valid_host[s] : 0;
+  const int ppb = 256 / (C >> 2);
+  int blocks = (P + ppb - 1) / ppb;
+  if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
+  launch_k(gn_head_kernel, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
+  if (int r = check_launch("gn_head_kernel")) return r;
+  if (out) {
+    const int n = Ho * ((Wo + 3) / 4);
+    launch_k(upsample_logits_kernel, dim3((n + 255) / 256, S), 256, 0, stream, pred, Co, Hs, Ws, out, Ho, Wo, label);
     return check_launch("upsample_logits_kernel");
   }
   return RMEM_OK;

@@ -166,6 +166,10 @@ int pack_image_s2d_batched_launch(const void* img, int img_u8_hwc, const float* 
                                   int H, int W, void* out, int out_f16, int S, cudaStream_t stream);
 int maxpool3s2_nhwc_batched_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
                                    int S, cudaStream_t stream);
+int logits_head_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs,
+                               int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
+                               const int* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
+                               void* workspace, cudaStream_t stream);
 int argmax_label_batched_launch(const float* logits, int C, int HW, float* label, int S, cudaStream_t stream);
 int bank_append_launch(void* state, int T, int frame_step, const void* const* src, void* const* dst,
                        const int64_t* row_bytes, int n_tensors, cudaStream_t stream);

@@ -140,6 +140,7 @@ class InferenceFPN:
                             f(sd[prefix + name + ".gn.weight"]), f(sd[prefix + name + ".gn.bias"]))
         for name in ("adapter_16x", "adapter_8x", "adapter_4x", "conv_out"):
             self.w[name] = (cl(sd[prefix + name + ".weight"]), f(sd[prefix + name + ".bias"]))
+        self.w_head = f(sd[prefix + "conv_out.weight"].reshape(sd[prefix + "conv_out.weight"].shape[0], -1))   # [Co, C]
         # the 1x1 adapters read the encoder's bf16 feature maps: as [Cout, Cin] bf16 matrices they run on the
         # tcgen05 GEMM straight off those maps (no f32 copies of the shortcuts, no f32 convolution)
         # (in the backbone's 16-bit type: fp16 by default)
@@ -201,7 +202,7 @@ class InferenceFPN:
         ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b, S=x.shape[0])   # in place
         return a
 
-    def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None):
+    def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None, head=False):
         self._ws = self.gn_ws if gn_ws is None else gn_ws
         pre = adapters if adapters is not None else (None, None, None)
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
@@ -210,9 +211,14 @@ class InferenceFPN:
         x = self._conv_gn_relu(x, "conv_in")
         x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x", pre[0]), "conv_16x")
         x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x", pre[1]), "conv_8x")
-        x = self._conv_gn_relu(self._up_add(x, sc[-4], "adapter_4x", pre[2]), "conv_4x")
-        w, b = self.w["conv_out"]
-        return F.conv2d(x, w, None), b          # the caller adds the bias while finishing the logits
+        x = self._up_add(x, sc[-4], "adapter_4x", pre[2])
+        if not head:
+            x = self._conv_gn_relu(x, "conv_4x")
+            w, b = self.w["conv_out"]
+            return F.conv2d(x, w, None), b      # the caller adds the bias while finishing the logits
+        # the caller finishes the stage with ops.logits_head: GroupNorm + ReLU + conv_out + bias + class mask in one pass
+        w4 = self.w["conv_4x"][0]
+        return F.conv2d(x, w4, None, 1, w4.shape[-1] // 2).contiguous(memory_format=torch.channels_last), None
 
 
 class InferenceResNet:
@@ -557,6 +563,8 @@ class DeAOTEngine:
         self.local_fused = os_env_flag("RMEM_LOCAL_FUSED", False) and self.S == 1
         import os
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
+        self.fused_head = os_env_flag("RMEM_FUSED_HEAD", True)    # decoder tail: GN + ReLU + conv_out + mask in one pass
+        self.pred_label = None       # argmax of the last frame's logits at the output size (f32 [S, 1, Ho, Wo]) or None
         self.lt_single = os_env_flag("RMEM_LT_SINGLE", True)      # one-launch self-attention (no partials / combine)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
         # long-term attention finds free SMs
@@ -937,20 +945,35 @@ class DeAOTEngine:
         """decode_current_logits body (aot_engine.py:438-465, models/deaot.py:57-63)."""
         if getattr(self, "_dec_gn_ws", None) is None:
             self._dec_gn_ws = torch.zeros(self.S, 17, device=self.device, dtype=torch.float64)
-        conv, bias = self.prep.decoder(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws,
-                                       adapters=adapters)
+        dec = self.prep.decoder
+        fused = self.fused_head and dec.w["conv_4x"][0].shape[0] in (64, 128) and dec.w_head.shape[0] <= 16
+        conv, bias = dec(self._decoder_inputs(embs, lstt_out), embs, gn_ws=self._dec_gn_ws, adapters=adapters,
+                         head=fused)
         ws = self.ws
-        if ws.pred_logits is None or ws.pred_logits.shape != conv.shape:
-            ws.pred_logits = torch.empty(conv.shape, device=conv.device, dtype=torch.float32)
-        out = None
+        n, Co = conv.shape[0], dec.w_head.shape[0]
+        shape = (n, Co) + tuple(conv.shape[-2:])
+        if ws.pred_logits is None or tuple(ws.pred_logits.shape) != shape:
+            ws.pred_logits = torch.empty(shape, device=conv.device, dtype=torch.float32)
+        out = label = None
         if output_size is not None:
-            out = torch.empty(conv.shape[0], conv.shape[1], output_size[0], output_size[1], device=conv.device,
-                              dtype=torch.float32)
+            out = torch.empty(n, Co, output_size[0], output_size[1], device=conv.device, dtype=torch.float32)
+        n_valid = [int(k) + 1 for k in self.obj_nums]
         # + conv bias, channels beyond the objects -> -1e10 (aot_engine.py:455-457), persistent pred_id_logits
         # (read by the write path), bilinear resize to the output size (:459-463)
-        ops.finish_logits(conv, bias, ws.pred_logits, [int(n) + 1 for n in self.obj_nums], out)
+        if fused:
+            # ... and, in the same passes, conv_4x's GroupNorm + ReLU and the 1x1 conv_out (the normalised map is never
+            # stored) and the evaluator's argmax (pred_label)
+            if out is not None:
+                label = torch.empty(n, 1, output_size[0], output_size[1], device=conv.device, dtype=torch.float32)
+            _, b4, g4, be4 = dec.w["conv_4x"]
+            ops.logits_head(conv, b4, g4, be4, dec.w_head, dec.w["conv_out"][1], n_valid, ws.pred_logits, out, label,
+                            self._dec_gn_ws)
+        else:
+            ops.finish_logits(conv, bias, ws.pred_logits, n_valid, out)
         self.pred_id_logits = ws.pred_logits
-        return ws.pred_logits if out is None else out
+        res = ws.pred_logits if out is None else out
+        res._rmem_label = label        # travels with the graph's output tensor: a replay does not re-run this method
+        return res
 
     # ------------------------------------------------------------------ CUDA graphs
     def _wait_write(self):
@@ -1192,7 +1215,7 @@ class DeAOTEngine:
         st = self.st
         if img_embs is not None:
             self._wait_write()
-            return self._read_body(None, img_embs, T, osz, st)
+            return self._logits_out(self._read_body(None, img_embs, T, osz, st))
         # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
         # running on its own stream) and, after waiting for that write path, LSTT + decoder
         if next_img is not None or self._pq:
@@ -1209,12 +1232,17 @@ class DeAOTEngine:
         self._prefetching = bool(self._pq)                # the next call finds its embeddings ready
         if self._pending_w is not None:
             pend, self._pending_w = self._pending_w, None
-            return self._run(("wr",) + pend + (T, osz, st, p),
-                             lambda m, *e: self._fused_body(m, list(e), *pend, T, osz, st),
-                             [self._label_buf] + list(embs), alias=True)
+            return self._logits_out(self._run(("wr",) + pend + (T, osz, st, p),
+                                              lambda m, *e: self._fused_body(m, list(e), *pend, T, osz, st),
+                                              [self._label_buf] + list(embs), alias=True))
         self._wait_write()
-        return self._run(("read", T, osz, st, p), lambda *e: self._read_body(None, list(e), T, osz, st), list(embs),
-                         alias=True)
+        return self._logits_out(self._run(("read", T, osz, st, p),
+                                          lambda *e: self._read_body(None, list(e), T, osz, st), list(embs), alias=True))
+
+    def _logits_out(self, logits):
+        """``pred_label``: the argmax of these logits (f32 [S, 1, Ho, Wo]) when the decoder tail computed it."""
+        self.pred_label = getattr(logits, "_rmem_label", None)
+        return logits
 
     @_on_device
     def decode_current_logits(self, curr_enc_embs, curr_lstt_embs, output_size=None):
@@ -1390,6 +1418,12 @@ class DeAOTInferEngine:
 
     def frames_ahead(self):
         return min(e.frames_ahead() for e in self.aot_engines) if self.aot_engines else 0
+
+    @property
+    def pred_label(self):
+        """argmax of the logits the last match_propogate_one_frame returned, computed inside the decoder tail (one
+        engine, output_size given); None when several engines' logits were merged (more than 10 objects)."""
+        return self.aot_engines[0].pred_label if len(self.aot_engines) == 1 else None
 
     def update_size(self):
         self.input_size_2d = self.aot_engines[0].input_size_2d

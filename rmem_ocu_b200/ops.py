@@ -134,6 +134,26 @@ def finish_logits(conv, bias, pred, n_valid, out=None):
         LAUNCHES += 2 if out is not None else 1
 
 
+def logits_head(x, pre_bias, gamma, beta, w_out, b_out, n_valid, pred, out, label, workspace, groups=8):
+    """x: f32 channels-last [S, C, Hs, Ws] raw conv output; w_out f32 [Co, C]; pred f32 [S, Co, Hs, Ws]; out f32
+    [S, Co, Ho, Wo] or None; label f32 [S, 1, Ho, Wo] or None (with out).  GroupNorm + ReLU + 1x1 conv + bias + class
+    mask (+ resize + argmax): the decoder's last stage in three launches."""
+    S, C, Hs, Ws = x.shape
+    Co = w_out.shape[0]
+    Ho, Wo = (out.shape[-2], out.shape[-1]) if out is not None else (0, 0)
+    nv = [int(n_valid)] * S if not isinstance(n_valid, (list, tuple)) else [int(v) for v in n_valid]
+    arr = (ctypes.c_int32 * S)(*nv)
+    xt = x.permute(0, 2, 3, 1)
+    if not xt.is_contiguous():
+        raise _lib.RmemError("logits_head: x must be channels-last")
+    _lib.check(_lib.lib().rmem_logits_head_batched(_p(x), _p(pre_bias), _p(gamma), _p(beta), Hs, Ws, C, groups, _p(w_out),
+                                                   _p(b_out), Co, ctypes.cast(arr, ctypes.c_void_p), S, _p(pred),
+                                                   _p(out), Ho, Wo, _p(label), _p(workspace), _stream()),
+               "rmem_logits_head_batched")
+    global LAUNCHES
+    LAUNCHES += 3 if out is not None else 2
+
+
 def pack_image(img, out):
     """img f32 [1, 3, H, W] contiguous -> out bf16 [1, 8, H, W] channels-last (channels 3..7 zero)."""
     _chk_cuda(img, out)

@@ -493,3 +493,37 @@ def test_one_hot_masks_match_label_maps(lib_built):
     assert all(torch.isfinite(x).all() for x in lc)
     with pytest.raises(ValueError):
         eng.aot_engines[0].add_reference_frame(imgs[0].cuda(), torch.zeros(1, 11, H, W).cuda(), obj_nums=[3], frame_step=0)
+
+
+def test_fused_decoder_tail_matches_unfused(lib_built, monkeypatch):
+    """RMEM_FUSED_HEAD (default on: conv_4x's GroupNorm + ReLU, conv_out, bias and class mask in one pass, argmax in
+    the resize kernel) against the separate kernels + cuDNN 1x1 convolution: same bank, logits to 2e-3 (conv_out in
+    fp32 FMAs instead of TF32), masks >= 99.9 %, and pred_label equal to the argmax of the returned logits."""
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    H, W, n, latter = 240, 432, 7, 2
+    imgs, lab = _clip(H, W, n, 3, seed=9)
+    outs = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RMEM_FUSED_HEAD", flag)
+        m, _ = _models(latter)
+        eng = DeAOTInferEngine(m, 0, long_term_mem_gap=2)
+        logits, masks = [], []
+        with torch.no_grad():
+            eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[3], frame_step=0)
+            for f in range(1, n):
+                lg = eng.match_propogate_one_frame(imgs[f].cuda(), output_size=(H, W))
+                label = lg.argmax(1, keepdim=True).float()
+                if flag == "1":
+                    assert eng.pred_label is not None and torch.equal(eng.pred_label, label), f
+                else:
+                    assert eng.pred_label is None
+                logits.append(lg.clone())
+                masks.append(label.clone())
+                eng.update_memory(label)
+        outs.append((logits, masks, eng.aot_engines[0].long_memories_indexes))
+    (la, ma, ia), (lb, mb, ib) = outs
+    assert ia == ib
+    for f, (a, b) in enumerate(zip(la, lb)):
+        va = a > -1e9
+        assert ((a[va] - b[va]).norm() / b[va].norm()).item() < 2e-3, f
+    assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999

@@ -225,6 +225,44 @@ def test_id_embed_soft_vs_oracle(lib_built, H, W, S, with_ignore, norm):
         assert _rel(a, c) < 3e-3
 
 
+@pytest.mark.parametrize("C,Hs,Ws,Ho,Wo,S", [(128, 120, 216, 480, 864, 1), (128, 61, 109, 241, 433, 2), (64, 9, 7, 0, 0, 1)])
+def test_logits_head_vs_torch(lib_built, C, Hs, Ws, Ho, Wo, S):
+    """rmem_logits_head_batched -- GroupNorm(8) + ReLU + 1x1 conv_out + bias + class mask (+ bilinear resize + argmax)
+    -- against F.group_norm / F.conv2d / F.interpolate in fp32 (TF32 off): pred to 1e-5 relative, resized logits to
+    1e-5, the label map equal to torch.argmax of the kernel's own resized logits."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(21)
+    Co = 11
+    x = (torch.randn(S, C, Hs, Ws, device="cuda") * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    pb, g, b = (torch.randn(C, device="cuda") for _ in range(3))
+    w = torch.randn(Co, C, device="cuda") * 0.2
+    bo = torch.randn(Co, device="cuda")
+    n_valid = [4, 11][:S]
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        y = F.relu(F.group_norm(x + pb.view(1, C, 1, 1), 8, g, b, 1e-5))
+        ref = F.conv2d(y, w.view(Co, C, 1, 1), bo)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    for s, nv in enumerate(n_valid):
+        ref[s, nv:] = -1e10
+    ws = torch.zeros(S, 17, device="cuda", dtype=torch.float64)
+    pred = torch.empty(S, Co, Hs, Ws, device="cuda")
+    out = torch.empty(S, Co, Ho, Wo, device="cuda") if Ho else None
+    label = torch.empty(S, 1, Ho, Wo, device="cuda") if Ho else None
+    for _ in range(2):                                          # twice: the workspace must clean itself
+        ops.logits_head(x, pb, g, b, w, bo, n_valid, pred, out, label, ws)
+    torch.cuda.synchronize()
+    assert (ws == 0).all()
+    assert _rel(pred, ref) < 1e-5
+    if Ho:
+        ref_out = F.interpolate(pred, size=(Ho, Wo), mode="bilinear", align_corners=True)
+        valid = ref_out > -1e9
+        assert torch.allclose(out[valid], ref_out[valid], rtol=1e-4, atol=1e-4)
+        assert torch.equal(label, out.argmax(1, keepdim=True).float())
+
+
 @pytest.mark.parametrize("C,H,W", [(256, 30, 54), (128, 60, 108), (128, 120, 216), (64, 7, 5)])
 def test_groupnorm_nhwc(lib_built, C, H, W):
     """GroupNorm(8) + ReLU of the decoder's ConvGN blocks (basic.py:60-70, fpn.py:44-63) vs F.group_norm."""
