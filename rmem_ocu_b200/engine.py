@@ -565,6 +565,7 @@ class DeAOTEngine:
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
         self.fused_head = os_env_flag("RMEM_FUSED_HEAD", True)    # decoder tail: GN + ReLU + conv_out + mask in one pass
         self.pred_label = None       # argmax of the last frame's logits at the output size (f32 [S, 1, Ho, Wo]) or None
+        self.check_prefetch = os_env_flag("RMEM_CHECK_PREFETCH", False)   # compare each frame with the one encoded ahead
         self.lt_single = os_env_flag("RMEM_LT_SINGLE", True)      # one-launch self-attention (no partials / combine)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
         # long-term attention finds free SMs
@@ -573,6 +574,7 @@ class DeAOTEngine:
             self.lt_sk_clusters = default_sk_clusters(self.device) if self.fork_branches else 0
         self._side = None
         self._cap_stream = None
+        self._graphs_baked = None
         # the write path (update_short_term_memory) runs on its own stream: the next frame's encoder does not
         # depend on it, so the two overlap; the next frame's LSTT waits for it (self._w_done)
         self.async_write = os_env_flag("RMEM_ASYNC_WRITE", True)
@@ -1079,14 +1081,19 @@ class DeAOTEngine:
             self._enc_done = torch.cuda.Event()
             self._enc_done.record()
         for j in range(B):
-            self._pq.append(([e[j * self.S:(j + 1) * self.S] for e in embs] if B > 1 else embs, (p, B, j)))
+            self._pq.append(([e[j * self.S:(j + 1) * self.S] for e in embs] if B > 1 else embs, (p, B, j),
+                             img[j * self.S:(j + 1) * self.S] if self.check_prefetch else None))
 
-    def _take_prefetched(self):
+    def _take_prefetched(self, img=None):
         """The oldest frame encoded ahead and the (set, batch, index) of its embeddings; the current stream waits for
         the encoder pass that produced them."""
         cur = torch.cuda.current_stream()
         cur.wait_event(self._enc_done)
-        embs, p = self._pq.popleft()
+        embs, p, frame = self._pq.popleft()
+        if frame is not None and img is not None and not torch.equal(frame, img.to(frame.device)):
+            # RMEM_CHECK_PREFETCH=1 (debugging aid; it synchronises): the frame handed over now is not the one that was
+            # encoded ahead for this call
+            raise _lib.RmemError("match_propogate_one_frame: this frame differs from the one passed as next_img")
         for e in embs:
             e.record_stream(cur)
         return embs, p
@@ -1175,6 +1182,13 @@ class DeAOTEngine:
             raise ValueError("No mask for reference frame!")
         if img is not None:
             self._img_sig = (img.dtype, tuple(img.shape))
+        # an engine that is reused for another sequence (restart_engine keeps the workspace and the captured graphs)
+        # drops graphs that bake what has changed: the valid-class counts of the logits kernels, the frame format
+        baked = (tuple(int(n) for n in self.obj_nums), self._img_sig)
+        if self._graphs and self._graphs_baked != baked:
+            self._graphs, self._graph_pool, self._graph_pool_w = {}, None, None
+            self._enc_set = 0
+        self._graphs_baked = baked
         curr_enc_embs = self.encode_image(img) if img_embs is None else img_embs
         label = self._label_map(mask.to(self.device)).float()
         if self.input_size_2d is None:
@@ -1221,7 +1235,7 @@ class DeAOTEngine:
         if next_img is not None or self._pq:
             if not self._pq:
                 self._launch_encoder(img)                 # first frame of a prefetching loop: nothing encoded ahead
-            embs, p = self._take_prefetched()
+            embs, p = self._take_prefetched(img)
             if next_img is not None:
                 if self._pq:
                     raise _lib.RmemError("next_img given while %d frame(s) encoded ahead are still waiting: pass the "
@@ -1335,8 +1349,12 @@ class DeAOTInferEngine:
         return self
 
     def restart_engine(self):
+        """aot_engine.py:688-693 drops the engines; here they go back to a pool: an engine keeps its workspace (~70 MB
+        at 480p) and its captured CUDA graphs, and the next sequence of the same frame size reuses both (a sequence of
+        another size re-allocates in update_size, other object counts / frame formats re-capture)."""
         for engine in self.aot_engines:
             engine.restart_engine()
+        self._pool = self.aot_engines + getattr(self, "_pool", [])
         self.aot_engines = []
         self.obj_nums = None
 
@@ -1382,7 +1400,8 @@ class DeAOTInferEngine:
         self.obj_nums = obj_nums
         aot_num = max(-(-int(obj_nums) // self.max_aot_obj_num), 1)
         while aot_num > len(self.aot_engines):
-            self.aot_engines.append(self._engine_cls(self.AOT, self.gpu_id, self.long_term_mem_gap,
+            self.aot_engines.append(self._pool.pop(0) if self._pool else
+                                    self._engine_cls(self.AOT, self.gpu_id, self.long_term_mem_gap,
                                                      self.short_term_mem_skip))
         separated = self.separate_mask(mask)
         img_embs = None

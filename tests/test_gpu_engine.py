@@ -527,3 +527,57 @@ def test_fused_decoder_tail_matches_unfused(lib_built, monkeypatch):
         va = a > -1e9
         assert ((a[va] - b[va]).norm() / b[va].norm()).item() < 2e-3, f
     assert min((a == b).float().mean().item() for a, b in zip(ma, mb)) >= 0.999
+
+
+def test_engines_are_reused_across_sequences(lib_built, monkeypatch):
+    """restart_engine returns the engines to a pool: the next sequence of the same frame size reuses the workspace and
+    every captured graph (no new captures), and gives what a fresh engine gives (bank equal, logits to 2e-3, masks
+    >= 99.9 %); another object count re-captures.  RMEM_CHECK_PREFETCH=1 catches a loop that hands
+    over another frame than the one it announced as next_img."""
+    from rmem_ocu_b200 import _lib
+    from rmem_ocu_b200.engine import DeAOTInferEngine
+    H, W, n, latter = 240, 432, 9, 2
+    m, _ = _models(latter)
+    clips = [_clip(H, W, n, 3, seed=s) for s in (31, 32)]
+
+    def run(eng, imgs, lab, n_obj=3):
+        out = []
+        with torch.no_grad():
+            eng.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[n_obj], frame_step=0)
+            for f in range(1, n):
+                nxt = imgs[f + 1].cuda() if f + 1 < n else None
+                lg = eng.match_propogate_one_frame(imgs[f].cuda(), output_size=(H, W), next_img=nxt)
+                out.append(lg.clone())
+                eng.update_memory(eng.pred_label)
+        return out, list(eng.aot_engines[0].long_memories_indexes)
+
+    eng = DeAOTInferEngine(m, 0, long_term_mem_gap=2)
+    run(eng, *clips[0])
+    e0 = eng.aot_engines[0]
+    n_graphs, ws = len(e0._graphs), e0.ws
+    eng.restart_engine()
+    assert eng.aot_engines == []
+    second, idx2 = run(eng, *clips[1])
+    assert eng.aot_engines[0] is e0 and e0.ws is ws and len(e0._graphs) == n_graphs
+    fresh, idx_f = run(DeAOTInferEngine(m, 0, long_term_mem_gap=2), *clips[1])
+    assert idx2 == idx_f
+    for a, b in zip(second, fresh):
+        va = b > -1e9
+        # (not bit-equal: the GroupNorm statistics use floating-point atomics, whose order varies from run to run)
+        assert ((a[va] - b[va]).norm() / b[va].norm()).item() < 2e-3
+        assert (a.argmax(1) == b.argmax(1)).float().mean().item() >= 0.999
+    # direct engines with another object count: the graphs bake the valid-class mask, so they are dropped
+    e0.restart_engine()
+    with torch.no_grad():
+        e0.add_reference_frame(clips[0][0][0].cuda(), clips[0][1].cuda(), obj_nums=[2], frame_step=0)
+    assert len(e0._graphs) == 0
+    # the prefetch contract, checked on request
+    monkeypatch.setenv("RMEM_CHECK_PREFETCH", "1")
+    chk = DeAOTInferEngine(m, 0, long_term_mem_gap=2)
+    imgs, lab = clips[0]
+    with torch.no_grad():
+        chk.add_reference_frame(imgs[0].cuda(), lab.cuda(), obj_nums=[3], frame_step=0)
+        chk.match_propogate_one_frame(imgs[1].cuda(), output_size=(H, W), next_img=imgs[2].cuda())
+        chk.update_memory(chk.pred_label)
+        with pytest.raises(_lib.RmemError):
+            chk.match_propogate_one_frame(imgs[3].cuda(), output_size=(H, W))
