@@ -85,11 +85,12 @@ constexpr size_t kPartFWords = static_cast<size_t>(RMEM_MAX_BANK) * kStatRows * 
 struct Params {
   int L, T;
   int S;             // independent sequences batched in this launch (their tensors stacked along a leading dim)
-  int n_qpairs;      // query-tile pairs per sequence
+  int n_full;        // full query-tile pairs per sequence (two different 128-query tiles, one per CTA)
+  int eps;           // work entries per sequence = 4 * n_full + (odd number of query tiles ? 2 : 0)
   int order_stride;  // int32 words between the `order` arrays of consecutive sequences
   int tpf;           // key tiles per frame = ceil(L / 128)
-  int P;             // key tiles per (pair, split) = T * tpf
-  long long U;       // units = n_pairs * 4 * P
+  int P;             // key tiles per entry = T * tpf
+  long long U;       // units = S * eps * P
   int n_clusters;
   int max_seg;       // segment slots per CTA in the workspace (<= kMaxSeg)
   const int32_t* order;
@@ -164,6 +165,33 @@ struct TileIt {
   }
 };
 
+// A work ENTRY is what a cluster processes over one run of P key tiles.  For a full pair of query tiles it is
+// (pair, value split): CTA r holds query tile 2 * pair + r, both CTAs the same value split, and K and V tiles are shared
+// by multicast.  When the number of query tiles is odd (13 at 480p), the last tile would pair with a phantom -- 1/14 of
+// all MMA and softmax work spent on padding -- so it gets entries of another kind instead: BOTH CTAs hold that tile and
+// CTA r takes value split 2 * k + r (k = 0, 1): K tiles are still shared, each CTA loads its own V tile, S = Q K^T is
+// computed twice (as it is across the value splits anyway) and the tile costs 2 P units instead of 4 P.
+struct Entry {
+  int seq, q_tile, split, qid;   // qid: changes exactly when the CTA's query tile changes
+  bool odd;
+};
+__device__ __forceinline__ Entry decode_entry(int e, int rank, int eps, int n_full) {
+  Entry en;
+  en.seq = e / eps;
+  const int es = e - en.seq * eps;
+  en.odd = es >= 4 * n_full;
+  if (!en.odd) {
+    en.q_tile = 2 * (es >> 2) + rank;
+    en.split = es & 3;
+    en.qid = en.seq * (n_full + 1) + (es >> 2);
+  } else {
+    en.q_tile = 2 * n_full;
+    en.split = 2 * (es - 4 * n_full) + rank;
+    en.qid = en.seq * (n_full + 1) + n_full;
+  }
+  return en;
+}
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                   const __grid_constant__ CUtensorMap tm_v, const Params p) {
@@ -230,14 +258,14 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       int q_pair_loaded = -1;
       int frame_cached = -1, slot = 0;
       for (int i = 0; i < n; ++i) {
-        const int gq = it.pair >> 2, dv_split = it.pair & 3;     // gq = (sequence, query-tile pair)
-        const int seq = gq / p.n_qpairs, qpair = gq - seq * p.n_qpairs;
+        const Entry en = decode_entry(it.pair, static_cast<int>(rank), p.eps, p.n_full);
+        const int gq = en.qid, dv_split = en.split, seq = en.seq;
         const int st = i & 1;
         if (gq != q_pair_loaded) {
           // the queries change: the last QK^T that read the old ones has completed once tile i-1 released its K
           if (i > 0) mbar_wait(k_empty + ((i - 1) & 1), ((i - 1) >> 1) & 1);
           mbar_expect_tx(q_full, kQBytes);
-          tma_load_4d(sQ, &tm_q, q_full, 0, (2 * qpair + static_cast<int>(rank)) * kBlockM, 0, seq);
+          tma_load_4d(sQ, &tm_q, q_full, 0, en.q_tile * kBlockM, 0, seq);
           q_pair_loaded = gq;
           frame_cached = -1;
         }
@@ -255,8 +283,14 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         if (i >= 2) mbar_wait(v_empty + st, ph);
         SK_TR(0, i, 2);
         mbar_expect_tx(v_full + st, kVBytes);
-        tma_load_5d_mc(sV + st * kVBytes + rank * (kVBytes / 2), &tm_v, v_full + st, 0, it.tif * kBlockN,
-                       dv_split * 4 + 2 * static_cast<int>(rank), slot, seq, 0x3);
+        if (!en.odd) {
+          tma_load_5d_mc(sV + st * kVBytes + rank * (kVBytes / 2), &tm_v, v_full + st, 0, it.tif * kBlockN,
+                         dv_split * 4 + 2 * static_cast<int>(rank), slot, seq, 0x3);
+        } else {         // the CTAs hold different value splits: each fetches both halves of its own V tile
+          tma_load_5d(sV + st * kVBytes, &tm_v, v_full + st, 0, it.tif * kBlockN, dv_split * 4, slot, seq);
+          tma_load_5d(sV + st * kVBytes + kVBytes / 2, &tm_v, v_full + st, 0, it.tif * kBlockN, dv_split * 4 + 2, slot,
+                      seq);
+        }
         it.next(p.P, p.tpf);
       }
     }
@@ -275,10 +309,11 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       it.init(u0, p.P, p.tpf);
       int q_pair_seen = -1, q_loads = 0;
       for (int j = 0; j < n; ++j) {
-        if ((it.pair >> 2) != q_pair_seen) {
+        const int qid = decode_entry(it.pair, static_cast<int>(rank), p.eps, p.n_full).qid;
+        if (qid != q_pair_seen) {
           mbar_wait(q_full, q_loads & 1);
           ++q_loads;
-          q_pair_seen = it.pair >> 2;
+          q_pair_seen = qid;
         }
         const int st = j & 1;
         // S buffer st last held P(j-2): its aggregation must have completed
@@ -369,10 +404,11 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       if (first || frame_pos != prev_frame) {
         if (first) {
           m_used = -INFINITY; l_sum = 0.f;
-          const int gq = it.pair >> 2, seq = gq / p.n_qpairs;
-          q_global = (2 * (gq - seq * p.n_qpairs) + static_cast<int>(rank)) * kBlockM + row;   // row inside its sequence
+          const Entry en = decode_entry(it.pair, static_cast<int>(rank), p.eps, p.n_full);
+          const int seq = en.seq;
+          q_global = en.q_tile * kBlockM + row;                                                // row inside its sequence
           slot = static_cast<size_t>(blockIdx.x) * p.max_seg + (it.pair - pair0);
-          rec = p.part_f != nullptr && (it.pair & 3) == 0;
+          rec = p.part_f != nullptr && en.split == 0;
           bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
           if (p.tpe_bias && q_global < p.L)
             bias4 = *reinterpret_cast<const float4*>(p.tpe_bias + (static_cast<size_t>(seq) * p.L + q_global) * 4);
@@ -541,7 +577,7 @@ lt_attn_sk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
 //   W[q, t]   = sum_{s covering frame t} 2^(mf_{s,t} - M) lf_{s,t} / sum_s w_s l_s        (split 0 only)
 struct CombineParams {
   int L, T, tpf, P;
-  int n_q_tiles, n_qpairs;     // per sequence
+  int n_q_tiles, n_full, eps;  // per sequence: query tiles, full pairs, work entries (see Entry)
   long long U;
   int n_clusters, max_seg;
   const float* part_o;
@@ -568,8 +604,10 @@ lt_attn_sk_combine_kernel(const CombineParams p) {
   const bool mass_cta = blockIdx.y == kDV / kCbCols;       // the extra row of CTAs computes W[q, t] only
   const int dv_split = mass_cta ? 0 : blockIdx.y >> 2;
   const int col0 = (blockIdx.y & 3) * kCbCols;            // inside the split's 256 columns
-  const int pair = (seq * p.n_qpairs + (q_tile >> 1)) * 4 + dv_split;
-  const int rank = q_tile & 1;
+  // the entry that produced (q_tile, dv_split) and the CTA of the cluster that held it (see Entry)
+  const bool odd_tile = q_tile >= 2 * p.n_full;
+  const int pair = seq * p.eps + (odd_tile ? 4 * p.n_full + (dv_split >> 1) : (q_tile >> 1) * 4 + dv_split);
+  const int rank = odd_tile ? (dv_split & 1) : (q_tile & 1);
   const size_t seq_row0 = static_cast<size_t>(seq) * p.L;  // first row of this sequence in gate / out / attn_mass
   // the gate does not depend on anything computed here: fetch it first (two threads per row, 64 bytes each)
   const int rr = threadIdx.x >> 1, hh = threadIdx.x & 1;
@@ -592,7 +630,7 @@ lt_attn_sk_combine_kernel(const CombineParams p) {
     const int c = c0 + static_cast<int>(threadIdx.x);
     bool hit = false;
     int a = 0, b = 0, sl = 0;
-    if (c < nc) {      // a (pair, split) spans at most n_clusters / (4 n_pairs) + 2 <= 32 clusters (checked by the launcher)
+    if (c < nc) {      // an entry spans at most n_clusters / n_entries + 2 <= 32 clusters (checked by the launcher)
       const int s = (c * U) / nc, e = ((c + 1) * U) / nc;
       a = s > lo ? s : lo;
       b = e < hi ? e : hi;
@@ -721,7 +759,7 @@ lt_attn_sk_combine_kernel(const CombineParams p) {
 
 // ---------------------------------------------------------------------------------------------
 struct Plan {
-  int tpf, P, n_pairs, n_clusters, max_seg, n_ctas;
+  int tpf, P, n_full, eps, n_entries, n_clusters, max_seg, n_ctas;
   long long U;
 };
 
@@ -744,10 +782,16 @@ static Plan make_plan(int L, int T, int S, int n_sms, int n_clusters_req) {
   pl.tpf = (L + kBlockN - 1) / kBlockN;
   pl.P = T * pl.tpf;
   const int q_tiles = (L + kBlockM - 1) / kBlockM;
-  pl.n_pairs = S * ((q_tiles + 1) / 2);
-  pl.U = static_cast<long long>(pl.n_pairs) * kDVSplits * pl.P;
+  pl.n_full = q_tiles / 2;
+  pl.eps = kDVSplits * pl.n_full + (q_tiles & 1 ? kDVSplits / 2 : 0);
+  pl.n_entries = S * pl.eps;
+  pl.U = static_cast<long long>(pl.n_entries) * pl.P;
   int nc = n_sms / 2;                       // one cluster per SM pair: everything is resident at once
   if (n_clusters_req > 0 && n_clusters_req < nc) nc = n_clusters_req;   // leave SMs to kernels on other streams
+  // tiny problems: no more clusters than units, and few enough that an entry's segments fit the combine step's scan
+  // window (an entry spans at most nc / n_entries + 2 clusters; the window is 32)
+  if (nc > pl.U) nc = static_cast<int>(pl.U);
+  if (nc > 30 * pl.n_entries) nc = 30 * pl.n_entries;
   if (nc < 1) nc = 1;
   // a range of R tiles touches at most (R + P - 2) / P + 1 (pair, split)s: keep that within kMaxSeg
   for (;;) {
@@ -809,7 +853,7 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
     return set_error(RMEM_ERR_ARG, "lt_attn_sk: workspace smaller than rmem_lt_attn_deaot_sk_workspace_bytes(L, T)");
   if (pl.U * (pl.n_clusters + 1) >= (1ll << 31))
     return set_error(RMEM_ERR_ARG, "lt_attn_sk: T * L too large for the 32-bit tile arithmetic of the combine step");
-  if (pl.n_clusters / (kDVSplits * pl.n_pairs) + 2 > 32 || T > kMaxSegPerPair)
+  if (pl.n_clusters / pl.n_entries + 2 > 32 || T > kMaxSegPerPair)
     return set_error(RMEM_ERR_ARG, "lt_attn_sk: a (pair, split) would span more clusters than the combine step scans");
   CUtensorMap tm_q, tm_k, tm_v;
   {
@@ -839,7 +883,7 @@ int lt_attn_sk_partial_launch(const void* q, const void* kbank, const void* vban
     return r;
   Params p;
   p.L = L; p.T = T; p.tpf = pl.tpf; p.P = pl.P; p.U = pl.U; p.n_clusters = pl.n_clusters; p.max_seg = pl.max_seg;
-  p.S = S; p.n_qpairs = pl.n_pairs / S; p.order_stride = order_stride;
+  p.S = S; p.n_full = pl.n_full; p.eps = pl.eps; p.order_stride = order_stride;
   p.order = order_dev;
   p.tpe_bias = tpe_bias;
   for (int t = 0; t < RMEM_MAX_BANK; ++t) p.tpe_rows[t] = (tpe_bias && tpe_rows_host && t < T) ? tpe_rows_host[t] : 0;
@@ -860,7 +904,7 @@ int lt_attn_sk_combine_launch(int T, int L, int S, const void* gate, void* out, 
     return set_error(RMEM_ERR_ARG, "lt_attn_sk_combine: workspace too small");
   CombineParams p;
   p.L = L; p.T = T; p.tpf = pl.tpf; p.P = pl.P; p.U = pl.U; p.n_clusters = pl.n_clusters; p.max_seg = pl.max_seg;
-  p.n_q_tiles = (L + kBlockM - 1) / kBlockM; p.n_qpairs = pl.n_pairs / S;
+  p.n_q_tiles = (L + kBlockM - 1) / kBlockM; p.n_full = pl.n_full; p.eps = pl.eps;
   float *po, *pml, *pf;
   sk_split_workspace(pl, const_cast<void*>(workspace), &po, &pml, &pf);
   p.part_o = po; p.part_ml = pml; p.part_f = pf;
