@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 8
+#define RMEM_ABI_VERSION 9
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -319,7 +319,7 @@ int rmem_argmax_label_batched(const float* logits, int C, int HW, float* label, 
  * aot_engine.py:451-463: classes beyond the sequence's objects -> -1e10, bilinear align_corners resize to the output
  * size; and the evaluator's argmax, networks/managers/evaluator.py:430-441).  The normalised feature map is never
  * written: statistics, then GroupNorm + ReLU + the C -> Co dot products + bias + mask straight into pred.
- *   x        f32 [S][Hs*Ws][C] raw output of the 3x3 conv_4x (channels-last), C = 64 or 128
+ *   x        f32 (x_f16 = 0) or fp16 (x_f16 = 1) [S][Hs*Ws][C] raw output of the 3x3 conv_4x (channels-last), C = 64 or 128
  *   pre_bias f32 [C] conv_4x bias or NULL; gamma, beta f32 [C]; groups (8)
  *   w_out    f32 [Co][C], b_out f32 [Co], Co <= 16
  *   n_valid_host  HOST i32 [S]: objects + 1 per image;  S <= 64
@@ -327,10 +327,21 @@ int rmem_argmax_label_batched(const float* logits, int C, int HW, float* label, 
  *   out      f32 [S][Co][Ho][Wo] or NULL;  label f32 [S][Ho][Wo] or NULL (argmax over the classes of out, first maximum)
  *   workspace: as rmem_groupnorm_nhwc_batched (S blocks of 16 * groups + 8 bytes, zero before the first call)
  */
-int rmem_logits_head_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs, int Ws,
-                             int C, int groups, const float* w_out, const float* b_out, int Co,
+int rmem_logits_head_batched(const void* x, int x_f16, const float* pre_bias, const float* gamma, const float* beta, int Hs,
+                             int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
                              const int32_t* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
                              void* workspace, void* stream);
+
+/* rmem_groupnorm_nhwc_batched / rmem_upsample_add_nhwc_batched for a decoder that keeps its activations in fp16
+ * (decoders/fpn.py:44-63 with 16-bit cuDNN convolutions: 62 -> 38 us for the four 3x3 convolutions at 480p, half the
+ * bytes in these kernels; statistics, normalisation and interpolation are computed in fp32 either way).
+ *   f16 = 1: x / y (GroupNorm) and x / out (upsample) are fp16, channels-last; 0: fp32 as the plain entry points.
+ *   the adapter branch `a` (+ a_bias) stays fp32: it comes from a GEMM epilogue and is read once.
+ */
+int rmem_groupnorm_nhwc_ex(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
+                           int C, int groups, int relu, int S, int f16, void* workspace, void* stream);
+int rmem_upsample_add_nhwc_ex(const void* x, int hi, int wi, const float* a, const float* a_bias, void* out, int ho, int wo,
+                              int C, int S, int f16, void* stream);
 int rmem_dwconv5_batched(const void* x, int ldx, int xcol0, const float* wt, void* y, int ldy, int ycol0, int h, int w,
                          int C, int S, void* stream);
 int rmem_groupnorm_tokens_batched(const float* x_a, int Ca, const float* x_b, const float* gamma, const float* beta,

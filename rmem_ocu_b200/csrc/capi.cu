@@ -118,12 +118,20 @@ int rmem_id_embed_batched(const float* labels, int H, int W, const float* prefix
   return id_embed_batched_launch(labels, H, W, prefix, bias, gamma, beta, n_cls, dst_host, ld_host, col0_host, n_dst,
                                  h, w, S, ST(stream));
 }
-int rmem_logits_head_batched(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs, int Ws,
-                             int C, int groups, const float* w_out, const float* b_out, int Co,
+int rmem_logits_head_batched(const void* x, int x_f16, const float* pre_bias, const float* gamma, const float* beta, int Hs,
+                             int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
                              const int32_t* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
                              void* workspace, void* stream) {
-  return logits_head_batched_launch(x, pre_bias, gamma, beta, Hs, Ws, C, groups, w_out, b_out, Co, n_valid_host, S, pred,
-                                    out, Ho, Wo, label, workspace, ST(stream));
+  return logits_head_batched_launch(x, x_f16, pre_bias, gamma, beta, Hs, Ws, C, groups, w_out, b_out, Co, n_valid_host, S,
+                                    pred, out, Ho, Wo, label, workspace, ST(stream));
+}
+int rmem_groupnorm_nhwc_ex(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
+                           int C, int groups, int relu, int S, int f16, void* workspace, void* stream) {
+  return groupnorm_nhwc_ex_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, S, f16, workspace, ST(stream));
+}
+int rmem_upsample_add_nhwc_ex(const void* x, int hi, int wi, const float* a, const float* a_bias, void* out, int ho, int wo,
+                              int C, int S, int f16, void* stream) {
+  return upsample_add_nhwc_ex_launch(x, hi, wi, a, a_bias, out, ho, wo, C, S, f16, ST(stream));
 }
 int rmem_id_embed_soft(const float* prob, int n_ch, const float* ignore, int H, int W, const float* taps,
                        const float* bias, const float* gamma, const float* beta, int n_cls, void* const* dst_host,

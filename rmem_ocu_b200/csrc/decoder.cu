@@ -11,13 +11,34 @@
 
 namespace rmem {
 
+// Four consecutive channels of a channels-last activation, fp32 or fp16 storage (the decoder runs in either).
+template <typename T> __device__ __forceinline__ float4 ld4(const T* p);
+template <> __device__ __forceinline__ float4 ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 ld4<__half>(const __half* p) {
+  const uint2 r = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&r.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&r.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+template <typename T> __device__ __forceinline__ void st4(T* p, float4 v);
+template <> __device__ __forceinline__ void st4<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <> __device__ __forceinline__ void st4<__half>(__half* p, float4 v) {
+  const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  uint2 r;
+  r.x = *reinterpret_cast<const uint32_t*>(&a);
+  r.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
+
 // ------------------------------------------------------------------------------------------------
 // stats: a thread owns four consecutive channels (one float4, always inside one group since cpg % 4 == 0) of
 // every (1024 / C)-th pixel of the CTA's pixel range; partial sums are reduced over the lanes of a group with
 // shuffles, over the CTA in shared memory, and added to the fp64 workspace with one atomic pair per
 // (CTA, group).  The range per CTA is sized so the grid is ~4 CTAs per SM whatever the resolution.
+template <typename T>
 __global__ void __launch_bounds__(256)
-gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias, int P, int C, int cpg,
+gn_nhwc_stats_kernel(const T* __restrict__ x, const float* __restrict__ pre_bias, int P, int C, int cpg,
                      int rows_per_cta, double* __restrict__ ws) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
@@ -34,7 +55,7 @@ gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_
   const float4 pb = pre_bias ? *reinterpret_cast<const float4*>(pre_bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
   for (int pix = p0 + ph; pix < p1; pix += ppb) {
-    float4 v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    float4 v = ld4(x + static_cast<size_t>(pix) * C + c);
     v.x += pb.x; v.y += pb.y; v.z += pb.z; v.w += pb.w;
     s += (v.x + v.y) + (v.z + v.w);
     q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
@@ -58,9 +79,10 @@ gn_nhwc_stats_kernel(const float* __restrict__ x, const float* __restrict__ pre_
   if (threadIdx.x < 2 * groups) atomicAdd(ws + threadIdx.x, static_cast<double>(sh[threadIdx.x]));
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_bias,
-                     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
+gn_nhwc_apply_kernel(const T* __restrict__ x, const float* __restrict__ pre_bias,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
                      int P, int C, int cpg, int relu, double* __restrict__ ws) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
@@ -77,7 +99,7 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_
     const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
     const float mean = static_cast<float>(mean_d);
     const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
-    float4 v = reinterpret_cast<const float4*>(x)[i];
+    float4 v = ld4(x + i * 4);
     if (pre_bias) {
       const float4 pb = *reinterpret_cast<const float4*>(pre_bias + c);
       v.x += pb.x; v.y += pb.y; v.z += pb.z; v.w += pb.w;
@@ -90,7 +112,7 @@ gn_nhwc_apply_kernel(const float* __restrict__ x, const float* __restrict__ pre_
     o.z = (v.z - mean) * rstd * ga.z + be.z;
     o.w = (v.w - mean) * rstd * ga.w + be.w;
     if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-    reinterpret_cast<float4*>(y)[i] = o;
+    st4(y + i * 4, o);
   }
   gn_ws_release(ws, 2 * (C / cpg));
 }
@@ -103,6 +125,11 @@ int groupnorm_nhwc_launch(const float* x, const float* pre_bias, const float* ga
 int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta,
                                   float* y, int P, int C, int groups, int relu, int S, void* workspace,
                                   cudaStream_t stream) {
+  return groupnorm_nhwc_ex_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, S, 0, workspace, stream);
+}
+
+int groupnorm_nhwc_ex_launch(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
+                             int C, int groups, int relu, int S, int f16, void* workspace, cudaStream_t stream) {
   if (groups < 1 || groups > 32 || (C % groups) || (C != 64 && C != 128 && C != 256) || P < 1 || S < 1 || S > 65535)
     return set_error(RMEM_ERR_ARG, "groupnorm_nhwc: C must be 64 / 128 / 256");
   const int cpg = C / groups;
@@ -111,22 +138,29 @@ int groupnorm_nhwc_batched_launch(const float* x, const float* pre_bias, const f
   const int per = (592 + S - 1) / S;             // ~4 CTAs per SM at large P over the whole batch ...
   int rows = (P + per - 1) / per;
   if (rows < 8) rows = 8;                        // ... but never less than two steps of work per CTA
-  launch_k(gn_nhwc_stats_kernel, dim3((P + rows - 1) / rows, S), 256, 0, stream, x, pre_bias, P, C, cpg, rows,
-                                                                          static_cast<double*>(workspace));
+  double* wsd = static_cast<double*>(workspace);
+  const dim3 gs((P + rows - 1) / rows, S);
+  if (f16) launch_k(gn_nhwc_stats_kernel<__half>, gs, 256, 0, stream, static_cast<const __half*>(x), pre_bias, P, C, cpg, rows, wsd);
+  else launch_k(gn_nhwc_stats_kernel<float>, gs, 256, 0, stream, static_cast<const float*>(x), pre_bias, P, C, cpg, rows, wsd);
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   const size_t total4 = static_cast<size_t>(P) * C / 4;
   int blocks = static_cast<int>((total4 + 255) / 256);
   if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  launch_k(gn_nhwc_apply_kernel, dim3(blocks, S), 256, 0, stream, x, pre_bias, gamma, beta, y, P, C, cpg, relu,
-                                                            static_cast<double*>(workspace));
+  if (f16)
+    launch_k(gn_nhwc_apply_kernel<__half>, dim3(blocks, S), 256, 0, stream, static_cast<const __half*>(x), pre_bias, gamma,
+             beta, static_cast<__half*>(y), P, C, cpg, relu, wsd);
+  else
+    launch_k(gn_nhwc_apply_kernel<float>, dim3(blocks, S), 256, 0, stream, static_cast<const float*>(x), pre_bias, gamma,
+             beta, static_cast<float*>(y), P, C, cpg, relu, wsd);
   return check_launch("gn_nhwc_apply_kernel");
 }
 
 // ------------------------------------------------------------------------------------------------
 // out[y][x][c] = a[y][x][c] + bilinear(x_in)[y][x][c], align_corners = True (F.interpolate, fpn.py:49-60)
+template <typename T>
 __global__ void __launch_bounds__(256)
-upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const float* __restrict__ a,
-                         const float* __restrict__ a_bias, float* __restrict__ out, int ho, int wo, int C) {
+upsample_add_nhwc_kernel(const T* __restrict__ xin, int hi, int wi, const float* __restrict__ a,
+                         const float* __restrict__ a_bias, T* __restrict__ out, int ho, int wo, int C) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
   // blockIdx.y = image of a batch: xin [S][hi*wi][C], a / out [S][ho*wo][C]
@@ -146,10 +180,10 @@ upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const fl
     const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
     const int y1 = min(y0 + 1, hi - 1), x1 = min(x0 + 1, wi - 1);
     const float ly = fy - y0, lx = fx - x0, hy = 1.f - ly, hx = 1.f - lx;
-    const float4 v00 = *reinterpret_cast<const float4*>(xin + (static_cast<size_t>(y0) * wi + x0) * C + c);
-    const float4 v01 = *reinterpret_cast<const float4*>(xin + (static_cast<size_t>(y0) * wi + x1) * C + c);
-    const float4 v10 = *reinterpret_cast<const float4*>(xin + (static_cast<size_t>(y1) * wi + x0) * C + c);
-    const float4 v11 = *reinterpret_cast<const float4*>(xin + (static_cast<size_t>(y1) * wi + x1) * C + c);
+    const float4 v00 = ld4(xin + (static_cast<size_t>(y0) * wi + x0) * C + c);
+    const float4 v01 = ld4(xin + (static_cast<size_t>(y0) * wi + x1) * C + c);
+    const float4 v10 = ld4(xin + (static_cast<size_t>(y1) * wi + x0) * C + c);
+    const float4 v11 = ld4(xin + (static_cast<size_t>(y1) * wi + x1) * C + c);
     float4 o = a ? *reinterpret_cast<const float4*>(a + static_cast<size_t>(pix) * C + c)
                  : make_float4(0.f, 0.f, 0.f, 0.f);
     if (a_bias) {
@@ -160,7 +194,7 @@ upsample_add_nhwc_kernel(const float* __restrict__ xin, int hi, int wi, const fl
     o.y += hy * (hx * v00.y + lx * v01.y) + ly * (hx * v10.y + lx * v11.y);
     o.z += hy * (hx * v00.z + lx * v01.z) + ly * (hx * v10.z + lx * v11.z);
     o.w += hy * (hx * v00.w + lx * v01.w) + ly * (hx * v10.w + lx * v11.w);
-    *reinterpret_cast<float4*>(out + static_cast<size_t>(pix) * C + c) = o;
+    st4(out + static_cast<size_t>(pix) * C + c, o);
   }
 }
 
@@ -171,12 +205,22 @@ int upsample_add_nhwc_launch(const float* xin, int hi, int wi, const float* a, c
 
 int upsample_add_nhwc_batched_launch(const float* xin, int hi, int wi, const float* a, const float* a_bias, float* out,
                                      int ho, int wo, int C, int S, cudaStream_t stream) {
+  return upsample_add_nhwc_ex_launch(xin, hi, wi, a, a_bias, out, ho, wo, C, S, 0, stream);
+}
+
+int upsample_add_nhwc_ex_launch(const void* xin, int hi, int wi, const float* a, const float* a_bias, void* out, int ho,
+                                int wo, int C, int S, int f16, cudaStream_t stream) {
   if ((C % 4) || hi < 1 || wi < 1 || ho < 1 || wo < 1 || S < 1 || S > 65535)
     return set_error(RMEM_ERR_ARG, "upsample_add_nhwc: C must be a multiple of 4");
   const size_t total = static_cast<size_t>(ho) * wo * (C / 4);
   int blocks = static_cast<int>((total + 255) / 256);
   if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  launch_k(upsample_add_nhwc_kernel, dim3(blocks, S), 256, 0, stream, xin, hi, wi, a, a_bias, out, ho, wo, C);
+  if (f16)
+    launch_k(upsample_add_nhwc_kernel<__half>, dim3(blocks, S), 256, 0, stream, static_cast<const __half*>(xin), hi, wi, a,
+             a_bias, static_cast<__half*>(out), ho, wo, C);
+  else
+    launch_k(upsample_add_nhwc_kernel<float>, dim3(blocks, S), 256, 0, stream, static_cast<const float*>(xin), hi, wi, a,
+             a_bias, static_cast<float*>(out), ho, wo, C);
   return check_launch("upsample_add_nhwc_kernel");
 }
 
@@ -297,7 +341,7 @@ int finish_logits_batched_launch(const float* conv, long long sn, long long sc, 
 // dot products are reduced over them with xor shuffles, lane c writes class c.
 constexpr int kHeadMaxCo = 16;
 struct HeadParams {
-  const float* x;
+  const void* x;             // fp32 or fp16 [S][P][C]
   const float* pre_bias;
   const float* gamma;
   const float* beta;
@@ -309,13 +353,14 @@ struct HeadParams {
   ValidCounts valid;
 };
 
+template <typename T>
 __global__ void __launch_bounds__(256) gn_head_kernel(const HeadParams p) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
   extern __shared__ float w_sh[];                       // [Co][C]
   const int C = p.C, Co = p.Co, P = p.P;
   for (int i = threadIdx.x; i < Co * C; i += blockDim.x) w_sh[i] = p.w_out[i];
-  const float* x = p.x + static_cast<size_t>(blockIdx.y) * P * C;
+  const T* x = static_cast<const T*>(p.x) + static_cast<size_t>(blockIdx.y) * P * C;
   float* pred = p.pred + static_cast<size_t>(blockIdx.y) * Co * P;
   double* ws = p.ws + static_cast<size_t>(blockIdx.y) * (2 * (C / p.cpg) + 1);
   const int n_valid = p.valid.n[blockIdx.y];
@@ -339,7 +384,7 @@ __global__ void __launch_bounds__(256) gn_head_kernel(const HeadParams p) {
   for (int st = blockIdx.x; st < steps; st += gridDim.x) {
     const int pix = st * ppb + threadIdx.x / tpp;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (pix < P) v = *reinterpret_cast<const float4*>(x + static_cast<size_t>(pix) * C + c);
+    if (pix < P) v = ld4(x + static_cast<size_t>(pix) * C + c);
     float y0 = fmaxf((v.x + pb.x - mean) * rstd * ga.x + be.x, 0.f);
     float y1 = fmaxf((v.y + pb.y - mean) * rstd * ga.y + be.y, 0.f);
     float y2 = fmaxf((v.z + pb.z - mean) * rstd * ga.z + be.z, 0.f);
@@ -356,8 +401,8 @@ __global__ void __launch_bounds__(256) gn_head_kernel(const HeadParams p) {
   gn_ws_release(ws, 2 * (C / p.cpg));
 }
 
-int logits_head_batched_launch(const float* x, const float* pre_bias, const float* gamma, const float* beta, int Hs,
-                               int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
+int logits_head_batched_launch(const void* x, int x_f16, const float* pre_bias, const float* gamma, const float* beta,
+                               int Hs, int Ws, int C, int groups, const float* w_out, const float* b_out, int Co,
                                const int* n_valid_host, int S, float* pred, float* out, int Ho, int Wo, float* label,
                                void* workspace, cudaStream_t stream) {
   const int P = Hs * Ws;
@@ -370,8 +415,12 @@ int logits_head_batched_launch(const float* x, const float* pre_bias, const floa
   const int per = (592 + S - 1) / S;
   int rows = (P + per - 1) / per;
   if (rows < 8) rows = 8;
-  launch_k(gn_nhwc_stats_kernel, dim3((P + rows - 1) / rows, S), 256, 0, stream, x, pre_bias, P, C, cpg, rows,
-           static_cast<double*>(workspace));
+  if (x_f16)
+    launch_k(gn_nhwc_stats_kernel<__half>, dim3((P + rows - 1) / rows, S), 256, 0, stream, static_cast<const __half*>(x),
+             pre_bias, P, C, cpg, rows, static_cast<double*>(workspace));
+  else
+    launch_k(gn_nhwc_stats_kernel<float>, dim3((P + rows - 1) / rows, S), 256, 0, stream, static_cast<const float*>(x),
+             pre_bias, P, C, cpg, rows, static_cast<double*>(workspace));
   if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
   HeadParams hp;
   hp.x = x; hp.pre_bias = pre_bias; hp.gamma = gamma; hp.beta = beta; hp.w_out = w_out; hp.b_out = b_out;
@@ -380,7 +429,8 @@ int logits_head_batched_launch(const float* x, const float* pre_bias, const floa
   const int ppb = 256 / (C >> 2);
   int blocks = (P + ppb - 1) / ppb;
   if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  launch_k(gn_head_kernel, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
+  if (x_f16) launch_k(gn_head_kernel<__half>, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
+  else launch_k(gn_head_kernel<float>, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
   if (int r = check_launch("gn_head_kernel")) return r;
   if (out) {
     const int n = Ho * ((Wo + 3) / 4);

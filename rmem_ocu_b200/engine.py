@@ -15,6 +15,7 @@ There is no CPU / PyTorch fallback: without CUDA or the shared library the engin
 import functools
 
 import collections
+import os
 
 import torch
 import torch.nn.functional as F
@@ -132,7 +133,10 @@ class InferenceFPN:
     def __init__(self, sd, device, intermediate, prefix="decoder.", shortcut_dtype=BF16):
         self.intermediate = intermediate
         self.shortcut_dtype = shortcut_dtype if shortcut_dtype in (BF16, torch.float16) else BF16
-        cl = lambda w: w.detach().to(device=device, dtype=torch.float32).contiguous(memory_format=torch.channels_last)
+        # activations and 3x3 convolutions in fp16 (fp32 accumulation; GroupNorm statistics, normalisation, interpolation
+        # and the logits head in fp32) or, with RMEM_DECODER_DTYPE=fp32, everything in fp32 / TF32
+        self.dtype = torch.float16 if os.environ.get("RMEM_DECODER_DTYPE", "fp16") == "fp16" else torch.float32
+        cl = lambda w: w.detach().to(device=device, dtype=self.dtype).contiguous(memory_format=torch.channels_last)
         f = lambda t: _f32(t, device)
         self.w = {}
         for name in ("conv_in", "conv_16x", "conv_8x", "conv_4x"):
@@ -147,6 +151,7 @@ class InferenceFPN:
         self.wb = {name: sd[prefix + name + ".weight"].detach().reshape(sd[prefix + name + ".weight"].shape[0], -1)
                    .to(device=device, dtype=self.shortcut_dtype).contiguous()
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
+        self._emulate_f16 = os_env_flag("RMEM_EXP_DECODER_F16", False)
         self.gn_ws = torch.zeros(1, 17, device=device, dtype=torch.float64)  # per image: 2 x 8 group sums + counter
         self._ws = self.gn_ws       # the workspace of the call in flight (engines pass their own: they may run
                                     # concurrently on different streams and share this object through `prepare`)
@@ -160,7 +165,11 @@ class InferenceFPN:
     def _conv_gn_relu(self, x, name):
         """ConvGN + ReLU: the conv bias is applied inside the GroupNorm kernels (no separate bias pass)."""
         w, b, g, be = self.w[name]
-        y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
+        if self._emulate_f16:      # experiment: the numerics an fp16 decoder would have (inputs, weights, outputs rounded)
+            y = F.conv2d(x.half().float(), w.half().float(), None, 1, w.shape[-1] // 2).half().float()
+            y = y.contiguous(memory_format=torch.channels_last)
+        else:
+            y = F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
         t = self._tok(y)
         # statistics per image (a batch = independent sequences), in place
         ops.groupnorm_nhwc(t, g, be, t, 8, True, self._ws, pre_bias=b, S=y.shape[0])
@@ -195,18 +204,22 @@ class InferenceFPN:
             ta = self._tok(a)
             b = None                                                                # added by the GEMM epilogue
         else:
-            a = F.conv2d(shortcut.float(), w, None).contiguous(memory_format=torch.channels_last)
+            a = F.conv2d(shortcut.float(), w.float(), None).contiguous(memory_format=torch.channels_last)
             ta = self._tok(a)
         hi, wi = x.shape[-2:]
         ho, wo = a.shape[-2:]
-        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b, S=x.shape[0])   # in place
-        return a
+        if self.dtype == torch.float32:
+            ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, ta, ho, wo, a_bias=b, S=x.shape[0])   # in place
+            return a
+        out = torch.empty(a.shape[0], ho, wo, a.shape[1], device=a.device, dtype=self.dtype).permute(0, 3, 1, 2)
+        ops.upsample_add_nhwc(self._tok(x), hi, wi, ta, self._tok(out), ho, wo, a_bias=b, S=x.shape[0])
+        return out
 
     def __call__(self, inputs, shortcuts, gn_ws=None, adapters=None, head=False):
         self._ws = self.gn_ws if gn_ws is None else gn_ws
         pre = adapters if adapters is not None else (None, None, None)
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
-        x = x.float().contiguous(memory_format=torch.channels_last)
+        x = x.to(self.dtype).contiguous(memory_format=torch.channels_last)
         sc = shortcuts
         x = self._conv_gn_relu(x, "conv_in")
         x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x", pre[0]), "conv_16x")
@@ -215,9 +228,12 @@ class InferenceFPN:
         if not head:
             x = self._conv_gn_relu(x, "conv_4x")
             w, b = self.w["conv_out"]
-            return F.conv2d(x, w, None), b      # the caller adds the bias while finishing the logits
+            return F.conv2d(x, w, None).float(), b      # the caller adds the bias while finishing the logits
         # the caller finishes the stage with ops.logits_head: GroupNorm + ReLU + conv_out + bias + class mask in one pass
         w4 = self.w["conv_4x"][0]
+        if self._emulate_f16:
+            return F.conv2d(x.half().float(), w4.half().float(), None, 1, w4.shape[-1] // 2).half().float().contiguous(
+                memory_format=torch.channels_last), None
         return F.conv2d(x, w4, None, 1, w4.shape[-1] // 2).contiguous(memory_format=torch.channels_last), None
 
 

@@ -101,17 +101,22 @@ def groupnorm_nhwc(x, gamma, beta, y, groups, relu, workspace, pre_bias=None, S=
     """GroupNorm(+ReLU) of (x + pre_bias), a channels-last [S, C, H, W] f32 tensor viewed as [S*H*W, C]; statistics
     per image, workspace: S consecutive (2 * groups + 1)-double blocks."""
     P, C = x.shape[0] // S, x.shape[1]
-    _lib.check(_lib.lib().rmem_groupnorm_nhwc_batched(_p(x), _p(pre_bias), _p(gamma), _p(beta), _p(y), P, C, groups,
-                                                      1 if relu else 0, S, _p(workspace), _stream()),
-               "rmem_groupnorm_nhwc_batched")
+    if x.dtype != y.dtype or x.dtype not in (torch.float32, torch.float16):
+        raise _lib.RmemError("groupnorm_nhwc: x and y must both be fp32 or both fp16")
+    _lib.check(_lib.lib().rmem_groupnorm_nhwc_ex(_p(x), _p(pre_bias), _p(gamma), _p(beta), _p(y), P, C, groups,
+                                                 1 if relu else 0, S, 1 if x.dtype == torch.float16 else 0,
+                                                 _p(workspace), _stream()), "rmem_groupnorm_nhwc_ex")
     _count("rmem_groupnorm_nhwc")
 
 
 def upsample_add_nhwc(x, hi, wi, a, out, ho, wo, a_bias=None, S=1):
-    """out = a + a_bias + bilinear_align_corners(x); x f32 [S*hi*wi, C], a / out f32 [S*ho*wo, C]."""
+    """out = a + a_bias + bilinear_align_corners(x); x [S*hi*wi, C] and out [S*ho*wo, C] fp32 or fp16, a f32."""
     C = x.shape[1]
-    _lib.check(_lib.lib().rmem_upsample_add_nhwc_batched(_p(x), hi, wi, _p(a), _p(a_bias), _p(out), ho, wo, C, S,
-                                                         _stream()), "rmem_upsample_add_nhwc_batched")
+    if x.dtype != out.dtype or x.dtype not in (torch.float32, torch.float16) or (a is not None and a.dtype != torch.float32):
+        raise _lib.RmemError("upsample_add_nhwc: x and out both fp32 or both fp16, a fp32")
+    _lib.check(_lib.lib().rmem_upsample_add_nhwc_ex(_p(x), hi, wi, _p(a), _p(a_bias), _p(out), ho, wo, C, S,
+                                                    1 if x.dtype == torch.float16 else 0, _stream()),
+               "rmem_upsample_add_nhwc_ex")
     _count("rmem_upsample_add_nhwc")
 
 
@@ -135,7 +140,7 @@ def finish_logits(conv, bias, pred, n_valid, out=None):
 
 
 def logits_head(x, pre_bias, gamma, beta, w_out, b_out, n_valid, pred, out, label, workspace, groups=8):
-    """x: f32 channels-last [S, C, Hs, Ws] raw conv output; w_out f32 [Co, C]; pred f32 [S, Co, Hs, Ws]; out f32
+    """x: f32 or fp16 channels-last [S, C, Hs, Ws] raw conv output; w_out f32 [Co, C]; pred f32 [S, Co, Hs, Ws]; out f32
     [S, Co, Ho, Wo] or None; label f32 [S, 1, Ho, Wo] or None (with out).  GroupNorm + ReLU + 1x1 conv + bias + class
     mask (+ resize + argmax): the decoder's last stage in three launches."""
     S, C, Hs, Ws = x.shape
@@ -146,7 +151,10 @@ def logits_head(x, pre_bias, gamma, beta, w_out, b_out, n_valid, pred, out, labe
     xt = x.permute(0, 2, 3, 1)
     if not xt.is_contiguous():
         raise _lib.RmemError("logits_head: x must be channels-last")
-    _lib.check(_lib.lib().rmem_logits_head_batched(_p(x), _p(pre_bias), _p(gamma), _p(beta), Hs, Ws, C, groups, _p(w_out),
+    if x.dtype not in (torch.float32, torch.float16):
+        raise _lib.RmemError("logits_head: x must be fp32 or fp16")
+    _lib.check(_lib.lib().rmem_logits_head_batched(_p(x), 1 if x.dtype == torch.float16 else 0, _p(pre_bias), _p(gamma),
+                                                   _p(beta), Hs, Ws, C, groups, _p(w_out),
                                                    _p(b_out), Co, ctypes.cast(arr, ctypes.c_void_p), S, _p(pred),
                                                    _p(out), Ho, Wo, _p(label), _p(workspace), _stream()),
                "rmem_logits_head_batched")

@@ -225,8 +225,34 @@ def test_id_embed_soft_vs_oracle(lib_built, H, W, S, with_ignore, norm):
         assert _rel(a, c) < 3e-3
 
 
+@pytest.mark.parametrize("C,hi,wi,ho,wo,S", [(256, 30, 54, 30, 54, 1), (128, 30, 54, 60, 108, 2), (128, 31, 55, 61, 109, 1)])
+def test_fp16_decoder_glue_vs_torch(lib_built, C, hi, wi, ho, wo, S):
+    """The fp16-activation forms of the decoder glue (rmem_groupnorm_nhwc_ex / rmem_upsample_add_nhwc_ex, f16 = 1):
+    GroupNorm(8) + ReLU and adapter + bilinear resize computed in fp32 from fp16 storage, against torch in fp32 on
+    the same rounded inputs; outputs are fp16: 1e-3 relative."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(31)
+    x = (torch.randn(S, C, hi, wi, device="cuda") * 2 + 0.3).half().contiguous(memory_format=torch.channels_last)
+    pb, g, b = (torch.randn(C, device="cuda") for _ in range(3))
+    ref = F.relu(F.group_norm(x.float() + pb.view(1, C, 1, 1), 8, g, b, 1e-5))
+    tok = lambda t: t.permute(0, 2, 3, 1).reshape(-1, t.shape[1])
+    y = torch.empty_like(x)
+    ws = torch.zeros(S, 17, device="cuda", dtype=torch.float64)
+    ops.groupnorm_nhwc(tok(x), g, b, tok(y), 8, True, ws, pre_bias=pb, S=S)
+    torch.cuda.synchronize()
+    assert y.dtype == torch.float16 and _rel(y, ref) < 1e-3 and (ws == 0).all()
+    a = torch.randn(S, C, ho, wo, device="cuda").contiguous(memory_format=torch.channels_last)
+    ab = torch.randn(C, device="cuda")
+    out = torch.empty(S, C, ho, wo, device="cuda", dtype=torch.float16).contiguous(memory_format=torch.channels_last)
+    ops.upsample_add_nhwc(tok(y), hi, wi, tok(a), tok(out), ho, wo, a_bias=ab, S=S)
+    torch.cuda.synchronize()
+    ref2 = a + ab.view(1, C, 1, 1) + F.interpolate(y.float(), size=(ho, wo), mode="bilinear", align_corners=True)
+    assert _rel(out, ref2) < 1e-3
+
+
+@pytest.mark.parametrize("f16", [False, True])
 @pytest.mark.parametrize("C,Hs,Ws,Ho,Wo,S", [(128, 120, 216, 480, 864, 1), (128, 61, 109, 241, 433, 2), (64, 9, 7, 0, 0, 1)])
-def test_logits_head_vs_torch(lib_built, C, Hs, Ws, Ho, Wo, S):
+def test_logits_head_vs_torch(lib_built, C, Hs, Ws, Ho, Wo, S, f16):
     """rmem_logits_head_batched -- GroupNorm(8) + ReLU + 1x1 conv_out + bias + class mask (+ bilinear resize + argmax)
     -- against F.group_norm / F.conv2d / F.interpolate in fp32 (TF32 off): pred to 1e-5 relative, resized logits to
     1e-5, the label map equal to torch.argmax of the kernel's own resized logits."""
@@ -234,6 +260,11 @@ def test_logits_head_vs_torch(lib_built, C, Hs, Ws, Ho, Wo, S):
     torch.manual_seed(21)
     Co = 11
     x = (torch.randn(S, C, Hs, Ws, device="cuda") * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    if f16:                                    # fp16 storage of the conv output; the reference sees the same rounded values
+        xk = x.half()
+        x = xk.float()
+    else:
+        xk = x
     pb, g, b = (torch.randn(C, device="cuda") for _ in range(3))
     w = torch.randn(Co, C, device="cuda") * 0.2
     bo = torch.randn(Co, device="cuda")
@@ -252,7 +283,7 @@ def test_logits_head_vs_torch(lib_built, C, Hs, Ws, Ho, Wo, S):
     out = torch.empty(S, Co, Ho, Wo, device="cuda") if Ho else None
     label = torch.empty(S, 1, Ho, Wo, device="cuda") if Ho else None
     for _ in range(2):                                          # twice: the workspace must clean itself
-        ops.logits_head(x, pb, g, b, w, bo, n_valid, pred, out, label, ws)
+        ops.logits_head(xk, pb, g, b, w, bo, n_valid, pred, out, label, ws)
     torch.cuda.synchronize()
     assert (ws == 0).all()
     assert _rel(pred, ref) < 1e-5
@@ -323,8 +354,12 @@ def test_finish_logits_and_argmax(lib_built, Hs, Ws, Ho, Wo, n_valid):
     assert (label == torch.argmax(ref_up, 1, keepdim=True).float()).float().mean().item() > 0.9999
 
 
-def test_decoder_head_vs_oracle(lib_built):
-    """InferenceFPN (cuDNN convs + csrc/decoder.cu) against the oracle's restatement of fpn.py:36-68."""
+@pytest.mark.parametrize("dec_dtype,tol", [("fp32", 1e-4), ("fp16", 3e-3)])
+def test_decoder_head_vs_oracle(lib_built, monkeypatch, dec_dtype, tol):
+    """InferenceFPN (cuDNN convs + csrc/decoder.cu) against the oracle's restatement of fpn.py:36-68: everything in
+    fp32 (RMEM_DECODER_DTYPE=fp32) to 1e-4, the default fp16-activation form (fp32 accumulation, statistics,
+    normalisation, interpolation and logits) to 3e-3."""
+    monkeypatch.setenv("RMEM_DECODER_DTYPE", dec_dtype)
     from oracle import restate as R
     from rmem_ocu_b200.engine import InferenceFPN
     from tests import _synth
@@ -342,7 +377,7 @@ def test_decoder_head_vs_oracle(lib_built):
         conv, bias = fpn([cl(embs[-1]), cl(lstt)], [cl(e) for e in embs])
     out = conv + bias.view(1, -1, 1, 1)
     torch.cuda.synchronize()
-    assert _rel(out.cpu(), ref) < 1e-4
+    assert _rel(out.cpu(), ref) < tol
 
 
 def test_decoder_head_bf16_shortcuts(lib_built):
