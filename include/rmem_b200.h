@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 9
+#define RMEM_ABI_VERSION 10
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -338,6 +338,13 @@ int rmem_logits_head_batched(const void* x, int x_f16, const float* pre_bias, co
  *   f16 = 1: x / y (GroupNorm) and x / out (upsample) are fp16, channels-last; 0: fp32 as the plain entry points.
  *   the adapter branch `a` (+ a_bias) stays fp32: it comes from a GEMM epilogue and is read once.
  */
+/* One decoder stage in one pass (decoders/fpn.py:44-63): GroupNorm(groups) + ReLU of a convolution's raw output x
+ * [S][hi*wi][C] (+ pre_bias), bilinear align_corners resize to ho x wo, plus the next shortcut's adapter branch a
+ * [S][ho*wo][C] f32 (+ a_bias): two launches (statistics, then everything else); the normalised map is not stored.
+ * f16: x and out are fp16 (else fp32).  workspace as rmem_groupnorm_nhwc_batched. */
+int rmem_gn_upsample_add_nhwc(const void* x, const float* pre_bias, const float* gamma, const float* beta, int hi, int wi,
+                              int C, int groups, const float* a, const float* a_bias, void* out, int ho, int wo, int S,
+                              int f16, void* workspace, void* stream);
 int rmem_groupnorm_nhwc_ex(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
                            int C, int groups, int relu, int S, int f16, void* workspace, void* stream);
 int rmem_upsample_add_nhwc_ex(const void* x, int hi, int wi, const float* a, const float* a_bias, void* out, int ho, int wo,

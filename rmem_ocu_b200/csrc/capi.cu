@@ -125,6 +125,12 @@ int rmem_logits_head_batched(const void* x, int x_f16, const float* pre_bias, co
   return logits_head_batched_launch(x, x_f16, pre_bias, gamma, beta, Hs, Ws, C, groups, w_out, b_out, Co, n_valid_host, S,
                                     pred, out, Ho, Wo, label, workspace, ST(stream));
 }
+int rmem_gn_upsample_add_nhwc(const void* x, const float* pre_bias, const float* gamma, const float* beta, int hi, int wi,
+                              int C, int groups, const float* a, const float* a_bias, void* out, int ho, int wo, int S,
+                              int f16, void* workspace, void* stream) {
+  return gn_upsample_add_nhwc_launch(x, pre_bias, gamma, beta, hi, wi, C, groups, a, a_bias, out, ho, wo, S, f16, workspace,
+                                     ST(stream));
+}
 int rmem_groupnorm_nhwc_ex(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
                            int C, int groups, int relu, int S, int f16, void* workspace, void* stream) {
   return groupnorm_nhwc_ex_launch(x, pre_bias, gamma, beta, y, P, C, groups, relu, S, f16, workspace, ST(stream));

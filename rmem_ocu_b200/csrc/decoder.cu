@@ -225,6 +225,100 @@ int upsample_add_nhwc_ex_launch(const void* xin, int hi, int wi, const float* a,
 }
 
 // ------------------------------------------------------------------------------------------------
+// One decoder stage in one pass (decoders/fpn.py:44-63): GroupNorm(8) + ReLU of a convolution's raw output x, its
+// bilinear (align_corners) resize, and the add of the next shortcut's adapter branch --
+//   out[y][x][c] = a[y][x][c] + a_bias[c] + bilinear(relu(gn(x + pre_bias)))[y][x][c].
+// The four neighbours are normalised on the fly (statistics from gn_nhwc_stats_kernel), so the normalised map is
+// never stored and the stage is two launches (statistics, this) instead of three.
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn_upsample_add_nhwc_kernel(const T* __restrict__ xin, const float* __restrict__ pre_bias,
+                            const float* __restrict__ gamma, const float* __restrict__ beta, int hi, int wi, int cpg,
+                            const float* __restrict__ a, const float* __restrict__ a_bias, T* __restrict__ out, int ho,
+                            int wo, int C, double* __restrict__ ws) {
+  pdl_wait();        // programmatic dependent launch: see rmem_internal.h
+  pdl_trigger();
+  xin += static_cast<size_t>(blockIdx.y) * hi * wi * C;
+  if (a) a += static_cast<size_t>(blockIdx.y) * ho * wo * C;
+  out += static_cast<size_t>(blockIdx.y) * ho * wo * C;
+  ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
+  const int c4 = C / 4;
+  const size_t total = static_cast<size_t>(ho) * wo * c4;
+  const float sy = ho > 1 ? static_cast<float>(hi - 1) / static_cast<float>(ho - 1) : 0.f;
+  const float sx = wo > 1 ? static_cast<float>(wi - 1) / static_cast<float>(wo - 1) : 0.f;
+  const double cnt = static_cast<double>(cpg) * hi * wi;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % c4) * 4;
+    const int pix = static_cast<int>(i / c4);
+    const int g = c / cpg;
+    const double mean_d = ws[2 * g] / cnt;
+    const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
+    const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
+    float4 sc = *reinterpret_cast<const float4*>(gamma + c);          // y = relu(v * sc + sh)
+    sc.x *= rstd; sc.y *= rstd; sc.z *= rstd; sc.w *= rstd;
+    float4 sh = *reinterpret_cast<const float4*>(beta + c);
+    float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pre_bias) pb = *reinterpret_cast<const float4*>(pre_bias + c);
+    const float mean = static_cast<float>(mean_d);
+    sh.x += (pb.x - mean) * sc.x; sh.y += (pb.y - mean) * sc.y; sh.z += (pb.z - mean) * sc.z; sh.w += (pb.w - mean) * sc.w;
+    const int y = pix / wo, x = pix - y * wo;
+    const float fy = sy * y, fx = sx * x;
+    const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
+    const int y1 = min(y0 + 1, hi - 1), x1 = min(x0 + 1, wi - 1);
+    const float ly = fy - y0, lx = fx - x0, hy = 1.f - ly, hx = 1.f - lx;
+    auto nrm = [&](int yy, int xx) {
+      float4 v = ld4(xin + (static_cast<size_t>(yy) * wi + xx) * C + c);
+      v.x = fmaxf(fmaf(v.x, sc.x, sh.x), 0.f); v.y = fmaxf(fmaf(v.y, sc.y, sh.y), 0.f);
+      v.z = fmaxf(fmaf(v.z, sc.z, sh.z), 0.f); v.w = fmaxf(fmaf(v.w, sc.w, sh.w), 0.f);
+      return v;
+    };
+    const float4 v00 = nrm(y0, x0), v01 = nrm(y0, x1), v10 = nrm(y1, x0), v11 = nrm(y1, x1);
+    float4 o = a ? *reinterpret_cast<const float4*>(a + static_cast<size_t>(pix) * C + c)
+                 : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a_bias) {
+      const float4 ab = *reinterpret_cast<const float4*>(a_bias + c);
+      o.x += ab.x; o.y += ab.y; o.z += ab.z; o.w += ab.w;
+    }
+    o.x += hy * (hx * v00.x + lx * v01.x) + ly * (hx * v10.x + lx * v11.x);
+    o.y += hy * (hx * v00.y + lx * v01.y) + ly * (hx * v10.y + lx * v11.y);
+    o.z += hy * (hx * v00.z + lx * v01.z) + ly * (hx * v10.z + lx * v11.z);
+    o.w += hy * (hx * v00.w + lx * v01.w) + ly * (hx * v10.w + lx * v11.w);
+    st4(out + static_cast<size_t>(pix) * C + c, o);
+  }
+  gn_ws_release(ws, 2 * (C / cpg));
+}
+
+int gn_upsample_add_nhwc_launch(const void* x, const float* pre_bias, const float* gamma, const float* beta, int hi, int wi,
+                                int C, int groups, const float* a, const float* a_bias, void* out, int ho, int wo, int S,
+                                int f16, void* workspace, cudaStream_t stream) {
+  if (groups < 1 || (C % groups) || (C != 64 && C != 128 && C != 256) || hi < 1 || wi < 1 || ho < 1 || wo < 1 || S < 1 ||
+      S > 65535)
+    return set_error(RMEM_ERR_ARG, "gn_upsample_add_nhwc: C must be 64 / 128 / 256");
+  const int cpg = C / groups, P = hi * wi;
+  if ((cpg & (cpg - 1)) || cpg < 4 || cpg > 32)
+    return set_error(RMEM_ERR_ARG, "gn_upsample_add_nhwc: channels per group must be a power of two in [4, 32]");
+  const int per = (592 + S - 1) / S;
+  int rows = (P + per - 1) / per;
+  if (rows < 8) rows = 8;
+  double* wsd = static_cast<double*>(workspace);
+  const dim3 gs((P + rows - 1) / rows, S);
+  if (f16) launch_k(gn_nhwc_stats_kernel<__half>, gs, 256, 0, stream, static_cast<const __half*>(x), pre_bias, P, C, cpg, rows, wsd);
+  else launch_k(gn_nhwc_stats_kernel<float>, gs, 256, 0, stream, static_cast<const float*>(x), pre_bias, P, C, cpg, rows, wsd);
+  if (int r = check_launch("gn_nhwc_stats_kernel")) return r;
+  const size_t total = static_cast<size_t>(ho) * wo * (C / 4);
+  int blocks = static_cast<int>((total + 255) / 256);
+  if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
+  if (f16)
+    launch_k(gn_upsample_add_nhwc_kernel<__half>, dim3(blocks, S), 256, 0, stream, static_cast<const __half*>(x), pre_bias,
+             gamma, beta, hi, wi, cpg, a, a_bias, static_cast<__half*>(out), ho, wo, C, wsd);
+  else
+    launch_k(gn_upsample_add_nhwc_kernel<float>, dim3(blocks, S), 256, 0, stream, static_cast<const float*>(x), pre_bias,
+             gamma, beta, hi, wi, cpg, a, a_bias, static_cast<float*>(out), ho, wo, C, wsd);
+  return check_launch("gn_upsample_add_nhwc_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------
 // decode_current_logits tail (aot_engine.py:451-463): logits = conv_out + bias, channels beyond the
 // sequence's objects masked to -1e10, kept as pred_id_logits [C][Hs][Ws]; then the bilinear
 // (align_corners = True) resize to the output size, [C][Ho][Wo].

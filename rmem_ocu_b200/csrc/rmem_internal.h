@@ -166,6 +166,9 @@ int pack_image_s2d_batched_launch(const void* img, int img_u8_hwc, const float* 
                                   int H, int W, void* out, int out_f16, int S, cudaStream_t stream);
 int maxpool3s2_nhwc_batched_launch(const void* x, int H, int W, int C, const float* bias, int relu, void* y, int f16,
                                    int S, cudaStream_t stream);
+int gn_upsample_add_nhwc_launch(const void* x, const float* pre_bias, const float* gamma, const float* beta, int hi, int wi,
+                                int C, int groups, const float* a, const float* a_bias, void* out, int ho, int wo, int S,
+                                int f16, void* workspace, cudaStream_t stream);
 int groupnorm_nhwc_ex_launch(const void* x, const float* pre_bias, const float* gamma, const float* beta, void* y, int P,
                              int C, int groups, int relu, int S, int f16, void* workspace, cudaStream_t stream);
 int upsample_add_nhwc_ex_launch(const void* xin, int hi, int wi, const float* a, const float* a_bias, void* out, int ho,

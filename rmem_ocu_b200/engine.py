@@ -152,6 +152,7 @@ class InferenceFPN:
                    .to(device=device, dtype=self.shortcut_dtype).contiguous()
                    for name in ("adapter_16x", "adapter_8x", "adapter_4x")}
         self._emulate_f16 = os_env_flag("RMEM_EXP_DECODER_F16", False)
+        self.fused_stage = os_env_flag("RMEM_FUSED_GN_UP", True)
         self.gn_ws = torch.zeros(1, 17, device=device, dtype=torch.float64)  # per image: 2 x 8 group sums + counter
         self._ws = self.gn_ws       # the workspace of the call in flight (engines pass their own: they may run
                                     # concurrently on different streams and share this object through `prepare`)
@@ -194,6 +195,27 @@ class InferenceFPN:
             return None
         return [self._adapter(shortcuts[i], name) for name, i in self.ADAPTERS]
 
+    def _conv(self, x, name):
+        w = self.w[name][0]
+        return F.conv2d(x, w, None, 1, w.shape[-1] // 2).contiguous(memory_format=torch.channels_last)
+
+    def _gn_up_add(self, x, gn_name, shortcut, name, pre=None):
+        """relu(GroupNorm(x + conv bias)) resized to the shortcut's size + adapter(shortcut): statistics + one kernel."""
+        _, cb, g, be = self.w[gn_name]
+        w, b = self.w[name]
+        if pre is not None:
+            a, b = pre, None
+        elif shortcut.dtype == self.shortcut_dtype:
+            a, b = self._adapter(shortcut, name), None                              # bias added by the GEMM epilogue
+        else:
+            a = F.conv2d(shortcut.float(), w.float(), None).contiguous(memory_format=torch.channels_last)
+        hi, wi = x.shape[-2:]
+        ho, wo = a.shape[-2:]
+        out = torch.empty(a.shape[0], ho, wo, a.shape[1], device=a.device, dtype=self.dtype).permute(0, 3, 1, 2)
+        ops.gn_upsample_add_nhwc(self._tok(x), cb, g, be, hi, wi, self._tok(a), self._tok(out), ho, wo, self._ws,
+                                 a_bias=b, S=x.shape[0])
+        return out
+
     def _up_add(self, x, shortcut, name, pre=None):
         """adapter(shortcut) + bias + bilinear(x) (identity resample when the sizes agree)."""
         w, b = self.w[name]
@@ -221,10 +243,16 @@ class InferenceFPN:
         x = torch.cat(inputs, dim=1) if (self.intermediate and len(inputs) > 1) else inputs[-1]
         x = x.to(self.dtype).contiguous(memory_format=torch.channels_last)
         sc = shortcuts
-        x = self._conv_gn_relu(x, "conv_in")
-        x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x", pre[0]), "conv_16x")
-        x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x", pre[1]), "conv_8x")
-        x = self._up_add(x, sc[-4], "adapter_4x", pre[2])
+        if self.fused_stage and not self._emulate_f16:
+            # a stage = convolution (cuDNN) + statistics + one kernel for GroupNorm, ReLU, resize and adapter add
+            x = self._gn_up_add(self._conv(x, "conv_in"), "conv_in", sc[-2], "adapter_16x", pre[0])
+            x = self._gn_up_add(self._conv(x, "conv_16x"), "conv_16x", sc[-3], "adapter_8x", pre[1])
+            x = self._gn_up_add(self._conv(x, "conv_8x"), "conv_8x", sc[-4], "adapter_4x", pre[2])
+        else:
+            x = self._conv_gn_relu(x, "conv_in")
+            x = self._conv_gn_relu(self._up_add(x, sc[-2], "adapter_16x", pre[0]), "conv_16x")
+            x = self._conv_gn_relu(self._up_add(x, sc[-3], "adapter_8x", pre[1]), "conv_8x")
+            x = self._up_add(x, sc[-4], "adapter_4x", pre[2])
         if not head:
             x = self._conv_gn_relu(x, "conv_4x")
             w, b = self.w["conv_out"]

@@ -120,6 +120,19 @@ def upsample_add_nhwc(x, hi, wi, a, out, ho, wo, a_bias=None, S=1):
     _count("rmem_upsample_add_nhwc")
 
 
+def gn_upsample_add_nhwc(x, pre_bias, gamma, beta, hi, wi, a, out, ho, wo, workspace, a_bias=None, groups=8, S=1):
+    """out = a + a_bias + bilinear_align_corners(relu(groupnorm(x + pre_bias))): x [S*hi*wi, C] raw conv output and out
+    [S*ho*wo, C] fp32 or fp16, a f32; statistics per image."""
+    C = x.shape[1]
+    if x.dtype != out.dtype or x.dtype not in (torch.float32, torch.float16) or (a is not None and a.dtype != torch.float32):
+        raise _lib.RmemError("gn_upsample_add_nhwc: x and out both fp32 or both fp16, a fp32")
+    _lib.check(_lib.lib().rmem_gn_upsample_add_nhwc(_p(x), _p(pre_bias), _p(gamma), _p(beta), hi, wi, C, groups, _p(a),
+                                                    _p(a_bias), _p(out), ho, wo, S, 1 if x.dtype == torch.float16 else 0,
+                                                    _p(workspace), _stream()), "rmem_gn_upsample_add_nhwc")
+    global LAUNCHES
+    LAUNCHES += 2
+
+
 def finish_logits(conv, bias, pred, n_valid, out=None):
     """conv: f32 [S, C, Hs, Ws] (any strides) -> pred f32 [S, C, Hs, Ws] contiguous (+ bias, channels >= n_valid[s]
     set to -1e10) and, if given, out f32 [S, C, Ho, Wo] = bilinear align_corners resize of pred.  n_valid: an int

@@ -248,6 +248,14 @@ def test_fp16_decoder_glue_vs_torch(lib_built, C, hi, wi, ho, wo, S):
     torch.cuda.synchronize()
     ref2 = a + ab.view(1, C, 1, 1) + F.interpolate(y.float(), size=(ho, wo), mode="bilinear", align_corners=True)
     assert _rel(out, ref2) < 1e-3
+    # the two steps as one stage (rmem_gn_upsample_add_nhwc), fp16 and fp32 storage; the normalised map is never stored
+    ref3 = a + ab.view(1, C, 1, 1) + F.interpolate(ref, size=(ho, wo), mode="bilinear", align_corners=True)
+    for xin, tol in ((x, 1e-3), (x.float(), 1e-5)):
+        o3 = torch.empty(S, C, ho, wo, device="cuda", dtype=xin.dtype).contiguous(memory_format=torch.channels_last)
+        for _ in range(2):                                       # twice: the workspace cleans itself
+            ops.gn_upsample_add_nhwc(tok(xin), pb, g, b, hi, wi, tok(a), tok(o3), ho, wo, ws, a_bias=ab, S=S)
+        torch.cuda.synchronize()
+        assert _rel(o3, ref3) < tol and (ws == 0).all()
 
 
 @pytest.mark.parametrize("f16", [False, True])
