@@ -149,16 +149,14 @@ __global__ void __launch_bounds__(256)
 gn32_gelu_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                        const float* __restrict__ beta, __nv_bfloat16* __restrict__ out, int L, int C,
                        double* __restrict__ ws) {
-  const double cnt = 32.0 * L;
   const size_t total4 = static_cast<size_t>(L) * C / 4;
+  __shared__ float gmean[32], grstd[32];
+  gn_group_stats(ws, C >> 5, 32.0 * L, gmean, grstd);
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int c = static_cast<int>((i * 4) % C);
     const int g = c >> 5;
-    const double mean_d = ws[2 * g] / cnt;
-    const double var = ws[2 * g + 1] / cnt - mean_d * mean_d;
-    const float mean = static_cast<float>(mean_d);
-    const float rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
+    const float mean = gmean[g], rstd = grstd[g];
     const float4 v = *reinterpret_cast<const float4*>(x + i * 4);
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
     const float4 be = *reinterpret_cast<const float4*>(beta + c);

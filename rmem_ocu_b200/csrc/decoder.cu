@@ -90,15 +90,13 @@ gn_nhwc_apply_kernel(const T* __restrict__ x, const float* __restrict__ pre_bias
   y += static_cast<size_t>(blockIdx.y) * P * C;
   ws += static_cast<size_t>(blockIdx.y) * (2 * (C / cpg) + 1);
   const size_t total4 = static_cast<size_t>(P) * C / 4;
-  const double cnt = static_cast<double>(cpg) * P;
+  __shared__ float gmean[32], grstd[32];
+  gn_group_stats(ws, C / cpg, static_cast<double>(cpg) * P, gmean, grstd);
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int c = static_cast<int>((i * 4) % C);      // 4 consecutive channels, same group (cpg % 4 == 0)
     const int g = c / cpg;
-    const double mean_d = ws[2 * g] / cnt;
-    const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
-    const float mean = static_cast<float>(mean_d);
-    const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
+    const float mean = gmean[g], rstd = grstd[g];
     float4 v = ld4(x + i * 4);
     if (pre_bias) {
       const float4 pb = *reinterpret_cast<const float4*>(pre_bias + c);
@@ -246,21 +244,20 @@ gn_upsample_add_nhwc_kernel(const T* __restrict__ xin, const float* __restrict__
   const size_t total = static_cast<size_t>(ho) * wo * c4;
   const float sy = ho > 1 ? static_cast<float>(hi - 1) / static_cast<float>(ho - 1) : 0.f;
   const float sx = wo > 1 ? static_cast<float>(wi - 1) / static_cast<float>(wo - 1) : 0.f;
-  const double cnt = static_cast<double>(cpg) * hi * wi;
+  __shared__ float gmean[32], grstd[32];
+  gn_group_stats(ws, C / cpg, static_cast<double>(cpg) * hi * wi, gmean, grstd);
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int c = static_cast<int>(i % c4) * 4;
     const int pix = static_cast<int>(i / c4);
     const int g = c / cpg;
-    const double mean_d = ws[2 * g] / cnt;
-    const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
-    const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
+    const float rstd = grstd[g];
     float4 sc = *reinterpret_cast<const float4*>(gamma + c);          // y = relu(v * sc + sh)
     sc.x *= rstd; sc.y *= rstd; sc.z *= rstd; sc.w *= rstd;
     float4 sh = *reinterpret_cast<const float4*>(beta + c);
     float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
     if (pre_bias) pb = *reinterpret_cast<const float4*>(pre_bias + c);
-    const float mean = static_cast<float>(mean_d);
+    const float mean = gmean[g];
     sh.x += (pb.x - mean) * sc.x; sh.y += (pb.y - mean) * sc.y; sh.z += (pb.z - mean) * sc.z; sh.w += (pb.w - mean) * sc.w;
     const int y = pix / wo, x = pix - y * wo;
     const float fy = sy * y, fx = sx * x;
@@ -431,8 +428,7 @@ int finish_logits_batched_launch(const float* conv, long long sn, long long sc, 
 // GroupNorm(8) + ReLU of the 3x3 convolution's raw output x [P][C] (statistics from gn_nhwc_stats_kernel), the 1x1
 // conv_out (C -> Co <= 16 classes) as fp32 dot products, + bias, classes beyond the sequence's objects -> -1e10,
 // written as pred_id_logits [Co][P].  The normalised C-channel map is never stored (13 MB at 480p), the cuDNN 1x1
-// convolution and the bias / mask pass disappear.  C / 4 <= 32 lanes share a pixel (four channels each); the Co partial
-// dot products are reduced over them with xor shuffles, lane c writes class c.
+// convolution and the bias / mask pass disappear.
 constexpr int kHeadMaxCo = 16;
 struct HeadParams {
   const void* x;             // fp32 or fp16 [S][P][C]
@@ -447,50 +443,126 @@ struct HeadParams {
   ValidCounts valid;
 };
 
+// Four threads per pixel: thread j takes the 8-channel chunks q = j (mod 4), normalises them and folds them into up to
+// 16 class sums held in registers (weights, scales and shifts are shared-memory reads: the four threads of a pixel read
+// four different rows, laid out 32 bytes apart modulo the bank width so a warp's access is conflict-free); two xor
+// shuffles per class finish the sums.  A thread carries four pixels at once, so a weight row read from shared memory
+// feeds 64 FMAs instead of 16 (with one pixel per thread the kernel was bound by those reads).  (The first version spread a pixel over a whole warp and reduced 11 partial sums
+// over 32 lanes: 99 shuffle / shared-memory wavefronts per pixel made it MIO-bound at 24 us; one thread per pixel left
+// 5 warps per SM and was latency-bound at 14 us.)
+constexpr int kHeadThreads = 128;
+constexpr int kHeadSplit = 4;                           // threads per pixel
+template <typename T> struct Vec8;
+template <> struct Vec8<float> {
+  static __device__ __forceinline__ void load(const float* p, float* v) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+template <> struct Vec8<__half> {
+  static __device__ __forceinline__ void load(const __half* p, float* v) {
+    const uint4 r = *reinterpret_cast<const uint4*>(p);
+    const __half2* h = reinterpret_cast<const __half2*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(h[i]);
+      v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+  }
+};
+// shared-memory float offset of the weight row of channel c: rows of one thread-of-a-pixel are contiguous (16 floats
+// each), the four groups of rows start 8 floats (32 bytes) further apart than a multiple of the bank width
+__device__ __forceinline__ int head_row(int c, int C) {
+  const int q = c >> 3, k = c & 7;                      // chunk, channel inside it
+  const int j = q & (kHeadSplit - 1), r = (q >> 2) * 8 + k;
+  return j * ((C / kHeadSplit) * kHeadMaxCo + 8) + r * kHeadMaxCo;
+}
+
 template <typename T>
-__global__ void __launch_bounds__(256) gn_head_kernel(const HeadParams p) {
+__global__ void __launch_bounds__(kHeadThreads) gn_head_kernel(const HeadParams p) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
-  extern __shared__ float w_sh[];                       // [Co][C]
+  extern __shared__ __align__(16) float head_sh[];      // weight rows (see head_row) | scale [C] | shift [C]
+  __shared__ float gmean[32], grstd[32];
   const int C = p.C, Co = p.Co, P = p.P;
-  for (int i = threadIdx.x; i < Co * C; i += blockDim.x) w_sh[i] = p.w_out[i];
+  float* w_t = head_sh;
+  float* scale = head_sh + C * kHeadMaxCo + kHeadSplit * 8;
+  float* shift = scale + C;
   const T* x = static_cast<const T*>(p.x) + static_cast<size_t>(blockIdx.y) * P * C;
   float* pred = p.pred + static_cast<size_t>(blockIdx.y) * Co * P;
   double* ws = p.ws + static_cast<size_t>(blockIdx.y) * (2 * (C / p.cpg) + 1);
   const int n_valid = p.valid.n[blockIdx.y];
-  const int tpp = C >> 2;                               // lanes per pixel: 16 or 32
-  const int ppb = 256 / tpp;                            // pixels per CTA step
-  const int c = (threadIdx.x % tpp) * 4;
-  const int sub = threadIdx.x % tpp;
-  const int g = c / p.cpg;
-  const double cnt = static_cast<double>(p.cpg) * P;
-  const double mean_d = ws[2 * g] / cnt;
-  const double var_d = ws[2 * g + 1] / cnt - mean_d * mean_d;
-  const float mean = static_cast<float>(mean_d);
-  const float rstd = rsqrtf(static_cast<float>(var_d) + 1e-5f);
-  float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (p.pre_bias) pb = *reinterpret_cast<const float4*>(p.pre_bias + c);
-  const float4 ga = *reinterpret_cast<const float4*>(p.gamma + c);
-  const float4 be = *reinterpret_cast<const float4*>(p.beta + c);
-  const float bo = sub < Co ? p.b_out[sub] : 0.f;
+  gn_group_stats(ws, C / p.cpg, static_cast<double>(p.cpg) * P, gmean, grstd);
+  // (global reads coalesced along c: read the other way round, every CTA issued 2048 single-sector requests and the
+  // fill alone cost 10 us over the grid)
+  for (int i = threadIdx.x; i < C * kHeadMaxCo; i += kHeadThreads) {
+    const int o = i / C, c = i - o * C;
+    w_t[head_row(c, C) + o] = o < Co ? p.w_out[o * C + c] : 0.f;
+  }
+  for (int c = threadIdx.x; c < C; c += kHeadThreads) {
+    const int g = c / p.cpg;
+    const float sc = p.gamma[c] * grstd[g];
+    scale[c] = sc;
+    shift[c] = p.beta[c] + ((p.pre_bias ? p.pre_bias[c] : 0.f) - gmean[g]) * sc;
+  }
   __syncthreads();
-  const int steps = (P + ppb - 1) / ppb;                // whole warps stay in the loop (shuffles below)
-  for (int st = blockIdx.x; st < steps; st += gridDim.x) {
-    const int pix = st * ppb + threadIdx.x / tpp;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (pix < P) v = ld4(x + static_cast<size_t>(pix) * C + c);
-    float y0 = fmaxf((v.x + pb.x - mean) * rstd * ga.x + be.x, 0.f);
-    float y1 = fmaxf((v.y + pb.y - mean) * rstd * ga.y + be.y, 0.f);
-    float y2 = fmaxf((v.z + pb.z - mean) * rstd * ga.z + be.z, 0.f);
-    float y3 = fmaxf((v.w + pb.w - mean) * rstd * ga.w + be.w, 0.f);
-    float mine = 0.f;
-    for (int o = 0; o < Co; ++o) {
-      const float4 w = *reinterpret_cast<const float4*>(w_sh + o * C + c);
-      float d = (y0 * w.x + y1 * w.y) + (y2 * w.z + y3 * w.w);
-      for (int m = tpp >> 1; m > 0; m >>= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
-      if (sub == o) mine = d;
+  const int j = threadIdx.x & (kHeadSplit - 1);
+  const int rounds = C / (8 * kHeadSplit);              // 8-channel chunks per thread: 2 (C = 64) or 4 (C = 128)
+  constexpr int kPix = 4;                               // pixels per thread: every weight row read feeds 4 pixels
+  constexpr int kStepPix = kHeadThreads / kHeadSplit * kPix;   // pixels per CTA step (128)
+  const int n_steps = (P + kStepPix - 1) / kStepPix;
+  for (int step = blockIdx.x; step < n_steps; step += gridDim.x) {   // whole warps stay in the loop (shuffles below)
+    // the thread's pixels: pix0 + 32 i (i = 0..3), so that for a fixed i a warp's 8 pixel groups are consecutive pixels
+    const int pix0 = step * kStepPix + (threadIdx.x >> 2);
+    float acc[kPix][kHeadMaxCo];
+#pragma unroll
+    for (int i = 0; i < kPix; ++i)
+#pragma unroll
+      for (int o = 0; o < kHeadMaxCo; ++o) acc[i][o] = 0.f;
+#pragma unroll 1
+    for (int r = 0; r < rounds; ++r) {
+      float v[kPix][8];
+#pragma unroll
+      for (int i = 0; i < kPix; ++i) {
+        const int pix = pix0 + i * (kHeadThreads / kHeadSplit);
+        Vec8<T>::load(x + static_cast<size_t>(pix < P ? pix : 0) * C + (r * kHeadSplit + j) * 8, v[i]);
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c = (r * kHeadSplit + j) * 8 + k;
+        const float sc = scale[c], sh = shift[c];
+        const float4* wr = reinterpret_cast<const float4*>(w_t + j * ((C / kHeadSplit) * kHeadMaxCo + 8) +
+                                                           (r * 8 + k) * kHeadMaxCo);
+        float y[kPix];
+#pragma unroll
+        for (int i = 0; i < kPix; ++i) y[i] = fmaxf(fmaf(v[i][k], sc, sh), 0.f);
+#pragma unroll
+        for (int q = 0; q < kHeadMaxCo / 4; ++q) {
+          const float4 w4 = wr[q];
+#pragma unroll
+          for (int i = 0; i < kPix; ++i) {
+            acc[i][4 * q] = fmaf(y[i], w4.x, acc[i][4 * q]);
+            acc[i][4 * q + 1] = fmaf(y[i], w4.y, acc[i][4 * q + 1]);
+            acc[i][4 * q + 2] = fmaf(y[i], w4.z, acc[i][4 * q + 2]);
+            acc[i][4 * q + 3] = fmaf(y[i], w4.w, acc[i][4 * q + 3]);
+          }
+        }
+      }
     }
-    if (pix < P && sub < Co) pred[static_cast<size_t>(sub) * P + pix] = sub < n_valid ? mine + bo : -1e10f;
+#pragma unroll
+    for (int i = 0; i < kPix; ++i) {
+      const int pix = pix0 + i * (kHeadThreads / kHeadSplit);
+#pragma unroll
+      for (int o = 0; o < kHeadMaxCo; ++o) {
+        acc[i][o] += __shfl_xor_sync(0xffffffffu, acc[i][o], 1);
+        acc[i][o] += __shfl_xor_sync(0xffffffffu, acc[i][o], 2);
+      }
+      // thread j of the pixel writes classes j, j + 4, ...: for a fixed class the warp's 8 pixels are one 32-byte run
+#pragma unroll
+      for (int o = 0; o < kHeadMaxCo; ++o)
+        if (pix < P && (o & (kHeadSplit - 1)) == j && o < Co)
+          pred[static_cast<size_t>(o) * P + pix] = o < n_valid ? acc[i][o] + p.b_out[o] : -1e10f;
+    }
   }
   gn_ws_release(ws, 2 * (C / p.cpg));
 }
@@ -520,11 +592,12 @@ int logits_head_batched_launch(const void* x, int x_f16, const float* pre_bias, 
   hp.x = x; hp.pre_bias = pre_bias; hp.gamma = gamma; hp.beta = beta; hp.w_out = w_out; hp.b_out = b_out;
   hp.pred = pred; hp.ws = static_cast<double*>(workspace); hp.P = P; hp.C = C; hp.cpg = cpg; hp.Co = Co;
   for (int s = 0; s < 64; ++s) hp.valid.n[s] = s < S ? n_valid_host[s] : 0;
-  const int ppb = 256 / (C >> 2);
-  int blocks = (P + ppb - 1) / ppb;
-  if (blocks > (148 * 8 + S - 1) / S) blocks = (148 * 8 + S - 1) / S;
-  if (x_f16) launch_k(gn_head_kernel<__half>, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
-  else launch_k(gn_head_kernel<float>, dim3(blocks, S), 256, static_cast<size_t>(Co) * C * sizeof(float), stream, hp);
+  const int ppc = kHeadThreads / kHeadSplit * 4;                        // pixels per CTA step (4 per thread)
+  int blocks = (P + ppc - 1) / ppc;                                     // 203 steps at 480p
+  if (blocks > (148 * 2 + S - 1) / S) blocks = (148 * 2 + S - 1) / S;   // every CTA ends in one same-address atomic
+  const size_t smem = (static_cast<size_t>(C) * (kHeadMaxCo + 2) + kHeadSplit * 8) * sizeof(float);
+  if (x_f16) launch_k(gn_head_kernel<__half>, dim3(blocks, S), kHeadThreads, smem, stream, hp);
+  else launch_k(gn_head_kernel<float>, dim3(blocks, S), kHeadThreads, smem, stream, hp);
   if (int r = check_launch("gn_head_kernel")) return r;
   if (out) {
     const int n = Ho * ((Wo + 3) / 4);

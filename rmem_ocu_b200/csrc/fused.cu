@@ -280,16 +280,14 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
   // a thread owns four consecutive channels (one float4 in, four bf16 or f32 out); Ca, C and C / groups are
   // multiples of 4
   const int cpg = C / groups;
-  const double cnt = static_cast<double>(cpg) * L;
   const size_t total4 = static_cast<size_t>(L) * C / 4;
+  __shared__ float gmean[32], grstd[32];
+  gn_group_stats(ws, groups, static_cast<double>(cpg) * L, gmean, grstd);
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int row = static_cast<int>((i * 4) / C), c = static_cast<int>(i * 4 - static_cast<size_t>(row) * C);
     const int g = c / cpg;
-    const double mean_d = ws[2 * g] / cnt;
-    const double var = ws[2 * g + 1] / cnt - mean_d * mean_d;
-    const float mean = static_cast<float>(mean_d);
-    const float rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
+    const float mean = gmean[g], rstd = grstd[g];
     const float4 v = c < Ca ? *reinterpret_cast<const float4*>(xa + static_cast<size_t>(row) * Ca + c)
                             : *reinterpret_cast<const float4*>(xb + static_cast<size_t>(row) * (C - Ca) + (c - Ca));
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);

@@ -189,6 +189,17 @@ int bank_score_evict_launch(void* state, const float* attn_mass, const float* fg
 // provides it zero-filled once; every apply kernel CTA calls this after its last read and the last CTA to arrive
 // re-zeroes accumulators and counter, so no memset node sits in front of each GroupNorm (a memset node costs
 // ~7 us inside a CUDA graph -- more than the statistics kernel).
+// mean / rstd of every group from the fp64 sums, once per CTA into shared memory (instead of fp64 divisions in
+// every thread, or -- in grid-stride loops -- in every iteration)
+__device__ __forceinline__ void gn_group_stats(const double* ws, int groups, double cnt, float* mean_sh, float* rstd_sh) {
+  if (static_cast<int>(threadIdx.x) < groups) {
+    const double m = ws[2 * threadIdx.x] / cnt;
+    const double var = ws[2 * threadIdx.x + 1] / cnt - m * m;
+    mean_sh[threadIdx.x] = static_cast<float>(m);
+    rstd_sh[threadIdx.x] = rsqrtf(static_cast<float>(var) + 1e-5f);
+  }
+  __syncthreads();
+}
 __device__ __forceinline__ void gn_ws_release(double* ws, int n_stats) {
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -14,41 +14,47 @@ from rmem_ocu_b200.engine import DeAOTInferEngine  # noqa: E402
 dev = torch.device("cuda", 0)
 torch.backends.cudnn.benchmark = True
 model = bench.build_model()
-n_frames = 40
-imgs, lab = bench.make_clip(n_frames, 1000)
+n_frames = 44
+la = 2
+imgs, lab = bench.make_clip(n_frames + la, 1000)
 eng = DeAOTInferEngine(model, 0, long_term_mem_gap=5)
-dimgs = [im.to(dev) for im in imgs]
+clip = torch.cat(imgs).to(dev)
 with torch.no_grad():
-    eng.add_reference_frame(dimgs[0], lab.to(dev), obj_nums=[bench.N_OBJ], frame_step=0)
-    PF = "--prefetch" in sys.argv
-    nxt = (lambda f: dimgs[f + 1]) if PF else (lambda f: None)
-    for f in range(1, 30):
-        bench.frame_step(eng, dimgs[f], (bench.H, bench.W), nxt(f))
+    eng.add_reference_frame(clip[0:1], lab.to(dev), obj_nums=[bench.N_OBJ], frame_step=0)
+    PF = "--no-prefetch" not in sys.argv
+    nxt = (lambda f: clip[f + 1:f + 1 + la] if eng.frames_ahead() <= 1 else None) if PF else (lambda f: None)
+    for f in range(1, 32):
+        bench.frame_step(eng, clip[f:f + 1], (bench.H, bench.W), nxt(f))
         if f == 1:
-            eng.precapture((bench.H, bench.W), prefetch=PF)
+            eng.precapture((bench.H, bench.W), prefetch=PF, lookahead=la)
     torch.cuda.synchronize()
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-        for f in range(30, 36):
-            bench.frame_step(eng, dimgs[f], (bench.H, bench.W), nxt(f))
+        for f in range(32, 40):
+            bench.frame_step(eng, clip[f:f + 1], (bench.H, bench.W), nxt(f))
         torch.cuda.synchronize()
 out = os.path.join(ROOT, "gpurun_out", "trace.json")
 prof.export_chrome_trace(out)
 ev = [e for e in json.load(open(out))["traceEvents"] if e.get("cat") == "kernel"]
 ev.sort(key=lambda e: e["ts"])
-# frames: split at pack_image
-starts = [i for i, e in enumerate(ev) if "pack_image" in e["name"]]
+# frames: split at the device frame counter's tick (first kernel of a frame's read path)
+starts = [i for i, e in enumerate(ev) if "bank_tick" in e["name"]]
 print("kernels", len(ev), "frame starts", starts)
-if len(starts) >= 4:
-    a, b = starts[2], starts[3]
+for k in range(2, len(starts) - 1):
+    a, b = starts[k], starts[k + 1]
     fr = ev[a:b]
+    alone = not any("pack_image" in e["name"] for e in fr)
     t0 = fr[0]["ts"]
-    busy = sum(e["dur"] for e in fr)
     span = ev[b]["ts"] - t0
-    print("frame span %.1f us, kernel busy %.1f us, gaps %.1f us, kernels %d" % (span, busy, span - busy, len(fr)))
-    prev_end = t0
-    for e in fr:
-        print("%8.1f %7.2f gap %6.2f  s%-3s %s" % (e["ts"] - t0, e["dur"], e["ts"] - prev_end,
-                                                   e.get("args", {}).get("stream", "?"), e["name"][:70]))
-        prev_end = e["ts"] + e["dur"]
+    print("frame %d: span %.1f us, %d kernels, %s" % (k, span, len(fr), "alone" if alone else "beside an encoder pass"))
+    if alone and "--all" not in sys.argv and k >= 3:
+        busy = sum(e["dur"] for e in fr)
+        print("kernel busy %.1f us (sum over streams)" % busy)
+        prev_end = {}
+        last_end = t0
+        for e in fr:
+            st = e.get("args", {}).get("stream", "?")
+            print("%8.1f %7.2f gap %6.2f  s%-3s %s" % (e["ts"] - t0, e["dur"], e["ts"] - last_end, st, e["name"][:64]))
+            last_end = max(last_end, e["ts"] + e["dur"])
+        break
 os.remove(out)
