@@ -40,6 +40,8 @@ struct GemmParams {
 // BN = 128 for wide outputs, 64 when that would leave most SMs idle (M is only ~13 row tiles on this path).
 // Three stages keep two (BN 128) or three (BN 64) CTAs on an SM so main loops and epilogues overlap; the
 // long-K narrow GEMMs (fewer CTAs than SMs, 16-32 K blocks each) instead get a six-deep ring to cover TMA latency.
+// (Split-K over two CTAs per tile with atomic fp32 reductions was tried for the K = 2048 projections that accumulate
+// into the residual streams: 7.5 / 11.2 us became 10.0 / 12.5 us -- the K loop is not what these launches wait for.)
 template <int BN, int kGStages>
 __global__ void __launch_bounds__(kGThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
