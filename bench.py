@@ -446,9 +446,13 @@ def run_lockstep(model, local_rank, seq_ids, spec, steps, head, prefetch=True):
     frames = [torch.cat([pools[s][f] for s in range(S)]).to(dev) for f in range(n_pool)]     # [S, 3, h, w] each
     img = lambda f: frames[f % n_pool]
     eng = DeAOTEngine(model, local_rank, long_term_mem_gap=gap, n_sequences=S)
+    la = 1        # stacks of 2 lock-steps (2 S frames per encoder pass) measured slower: S = 2 1508 vs 1706, 720p 470 vs 675
 
     def step(f):
-        lg = eng.match_propogate_one_frame(img(f), output_size=(h, w), next_img=img(f + 1) if prefetch else None)
+        nxt = None
+        if prefetch and eng.frames_ahead() <= 1:
+            nxt = torch.cat([img(f + 1 + k) for k in range(la)])          # frame-major [la * S, 3, h, w]
+        lg = eng.match_propogate_one_frame(img(f), output_size=(h, w), next_img=nxt)
         eng.update_short_term_memory(eng.pred_label if eng.pred_label is not None else ops.argmax_label(lg))
 
     with torch.no_grad():
@@ -456,7 +460,7 @@ def run_lockstep(model, local_rank, seq_ids, spec, steps, head, prefetch=True):
         for f in range(1, 1 + head):
             step(f)
             if f == 1:
-                eng.precapture((h, w), prefetch=prefetch)
+                eng.precapture((h, w), prefetch=prefetch, lookahead=la)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

@@ -1115,9 +1115,7 @@ class DeAOTEngine:
         es.wait_event(ready)
         if img.is_cuda:
             img.record_stream(es)
-        B = img.shape[0] // self.S
-        if B > 1 and self.S > 1:
-            raise NotImplementedError("encoder look-ahead batches are implemented for one sequence per engine")
+        B = img.shape[0] // self.S            # lock-step engines: frame-major stack [B * S, ...], frame j = rows [j S, (j + 1) S)
         p = self._enc_set
         self._enc_set = 1 - p
         with torch.cuda.stream(es):

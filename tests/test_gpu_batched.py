@@ -120,7 +120,7 @@ def _clip(H, W, n, n_obj, seed):
     return imgs, lab.int()
 
 
-@pytest.mark.parametrize("prefetch", [False, True])
+@pytest.mark.parametrize("prefetch", [0, 1, 2])          # 0: no look-ahead; 1: next frame; 2: stacks of two lock-steps
 def test_lockstep_engine_vs_single_engines_and_oracle(lib_built, monkeypatch, prefetch):
     """DeAOTEngine(n_sequences = 3): three different clips (different object counts) through one set of launches,
     against (a) three single-sequence engines -- same banks, masks >= 99.9 %, logits to 2e-2 (the stream-K partition
@@ -145,7 +145,10 @@ def test_lockstep_engine_vs_single_engines_and_oracle(lib_built, monkeypatch, pr
         with torch.no_grad():
             engine.add_reference_frame(imgs(0), labs, obj_nums=[n_objs[s] for s in idxs], frame_step=0)
             for f in range(1, n):
-                kw = {"next_img": imgs(f + 1)} if (prefetch and f + 1 < n) else {}
+                kw = {}
+                if prefetch and f + 1 < n and engine.frames_ahead() <= 1:
+                    # frame-major stack [B * S, ...]: the frames of the next B lock-steps, sequences adjacent
+                    kw = {"next_img": torch.cat([imgs(k) for k in range(f + 1, min(f + 1 + prefetch, n))])}
                 lg = engine.match_propogate_one_frame(imgs(f), output_size=(H, W), **kw)
                 logits.append(lg.clone())
                 label = torch.argmax(lg, 1, keepdim=True).float()
