@@ -1010,7 +1010,16 @@ class DeAOTEngine:
             # ... and, in the same passes, conv_4x's GroupNorm + ReLU and the 1x1 conv_out (the normalised map is never
             # stored) and the evaluator's argmax (pred_label)
             if out is not None:
-                label = torch.empty(n, 1, output_size[0], output_size[1], device=conv.device, dtype=torch.float32)
+                shape = (n,) + tuple(output_size)
+                same_size = self.input_size_2d is not None and tuple(output_size) == tuple(self.input_size_2d)
+                have = self._label_buf is not None and tuple(self._label_buf.shape) == shape
+                if same_size and (have or not torch.cuda.is_current_stream_capturing()):
+                    # at the input resolution the label map is what update_short_term_memory is handed next: written
+                    # straight into the buffer the deferred write path reads, so that call copies nothing (the buffer
+                    # is never allocated inside a capture: the first propagated frame always runs eagerly)
+                    label = self._label_buffer_shape(shape).view(n, 1, *output_size)
+                else:
+                    label = torch.empty(n, 1, output_size[0], output_size[1], device=conv.device, dtype=torch.float32)
             _, b4, g4, be4 = dec.w["conv_4x"]
             ops.logits_head(conv, b4, g4, be4, dec.w_head, dec.w["conv_out"][1], n_valid, ws.pred_logits, out, label,
                             self._dec_gn_ws)
@@ -1177,8 +1186,11 @@ class DeAOTEngine:
         return len(self._graphs) - len(saved)
 
     def _label_buffer(self, like):
-        if self._label_buf is None or self._label_buf.shape != like.shape:
-            self._label_buf = torch.empty(like.shape, dtype=torch.float32, device=self.device)
+        return self._label_buffer_shape(tuple(like.shape))
+
+    def _label_buffer_shape(self, shape):
+        if self._label_buf is None or tuple(self._label_buf.shape) != tuple(shape):
+            self._label_buf = torch.empty(shape, dtype=torch.float32, device=self.device)
         return self._label_buf
 
     def _variants(self, T, output_size, sets, label):
@@ -1330,7 +1342,9 @@ class DeAOTEngine:
             # (a loop that does not prefetch keeps the write path on its own stream: there it overlaps the next
             # frame's encoder, which is worth more than the two graph boundaries -- 1055 vs 1017 frames/s)
             self._wait_write()                                    # an earlier deferred write path, if any
-            torch.mul(label, 1, out=self._label_buffer(label))    # SM copy (see _run)
+            buf = self._label_buffer(label)
+            if label.data_ptr() != buf.data_ptr():                # pred_label at the input size already lives there
+                torch.mul(label, 1, out=buf)                      # SM copy (see _run)
             self._pending_w = (T, update_long, do_evict, st)
         elif self.async_write:
             if self._wstream is None:
