@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RMEM_ABI_VERSION 10
+#define RMEM_ABI_VERSION 11
 
 #define RMEM_OK 0
 #define RMEM_ERR_ARG (-1)     /* invalid argument (shape / capacity)           */
@@ -200,6 +200,13 @@ int rmem_linear_ex(const void* a, int lda, const void* w, int ldw, const float* 
 int rmem_layernorm(const void* x0, const float* gamma0, const float* beta0, void* out0, int ld0,
                    int col0, const void* x1, const float* gamma1, const float* beta1, void* out1,
                    int ld1, int col1, int L, int C, int in_bf16, void* stream);
+
+/* The first LayerNorm of the first block (norm1 of layer 0, transformer.py:1104) reads the encoder's 16-bit embedding
+ * and starts the fp32 residual stream: LN(x) as bf16 at out[:, col0 : col0 + 256] and x itself as f32 in copy_f32
+ * [L][256] (the reference's `tgt = curr_embs`, transformer.py:785-790), one kernel instead of a copy + a LayerNorm.
+ *   in_kind 0: x f32, 1: bf16, 2: IEEE fp16 (the fp16 backbone); copy_f32 may be NULL. */
+int rmem_layernorm_copy(const void* x, int in_kind, const float* gamma, const float* beta, void* out, int ld, int col0,
+                        float* copy_f32, int L, int C, void* stream);
 
 /* 5x5 depth-wise convolution over the (h, w) token grid, channels-last bf16, zero padding 2.
  * Replaces DWConv2d.forward (layers/basic.py:38-57) behind the gate of GatedPropagation /

@@ -71,6 +71,7 @@ _SIGNATURES = {
     "rmem_bank_tick_batched": [_c_void_p, _c_int, _c_void_p],
     "rmem_logits_head_batched": [_c_void_p, _c_int] + [_c_void_p] * 3 + [_c_int] * 4 + [_c_void_p] * 2 +
                                 [_c_int, _c_void_p, _c_int] + [_c_void_p] * 2 + [_c_int] * 2 + [_c_void_p] * 3,
+    "rmem_layernorm_copy": [_c_void_p, _c_int] + [_c_void_p] * 3 + [_c_int] * 2 + [_c_void_p] + [_c_int] * 2 + [_c_void_p],
     "rmem_gn_upsample_add_nhwc": [_c_void_p] * 4 + [_c_int] * 4 + [_c_void_p] * 3 + [_c_int] * 4 + [_c_void_p] * 2,
     "rmem_groupnorm_nhwc_ex": [_c_void_p] * 5 + [_c_int] * 6 + [_c_void_p] * 2,
     "rmem_upsample_add_nhwc_ex": [_c_void_p, _c_int, _c_int] + [_c_void_p] * 3 + [_c_int] * 5 + [_c_void_p],
@@ -142,7 +143,7 @@ class GemmSegment(ctypes.Structure):
                 ("dst_col0", ctypes.c_int32)]
 
 
-ABI_VERSION = 10          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
+ABI_VERSION = 11          # must equal RMEM_ABI_VERSION of the library that gets loaded (include/rmem_b200.h)
 MAX_BANK = 16
 MAX_CHUNKS_PER_FRAME = 4
 BANK_STATE_WORDS = 5 * MAX_BANK + 8

@@ -125,6 +125,11 @@ int rmem_logits_head_batched(const void* x, int x_f16, const float* pre_bias, co
   return logits_head_batched_launch(x, x_f16, pre_bias, gamma, beta, Hs, Ws, C, groups, w_out, b_out, Co, n_valid_host, S,
                                     pred, out, Ho, Wo, label, workspace, ST(stream));
 }
+int rmem_layernorm_copy(const void* x, int in_kind, const float* gamma, const float* beta, void* out, int ld, int col0,
+                        float* copy_f32, int L, int C, void* stream) {
+  return layernorm_copy_launch(x, gamma, beta, out, ld, col0, nullptr, nullptr, nullptr, nullptr, 0, 0, L, C, in_kind,
+                               copy_f32, ST(stream));
+}
 int rmem_gn_upsample_add_nhwc(const void* x, const float* pre_bias, const float* gamma, const float* beta, int hi, int wi,
                               int C, int groups, const float* a, const float* a_bias, void* out, int ho, int wo, int S,
                               int f16, void* workspace, void* stream) {

@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <mutex>
 #include "sm100_ptx.cuh"
+#include <cuda_fp16.h>
 #include "rmem_internal.h"
 
 namespace rmem {
@@ -25,7 +26,8 @@ struct LnStream {
 };
 struct LnParams {
   LnStream s[2];
-  int L, in_bf16;
+  int L, in_bf16;      // 0: f32 input, 1: bf16, 2: IEEE fp16
+  float* copy_f32;     // optional: stream 0's input rows as f32 [L][256] (the residual stream the block adds into)
 };
 
 __global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
@@ -36,7 +38,17 @@ __global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
   pdl_trigger();
   if (row >= p.L) return;
   float v[8];
-  if (p.in_bf16) {
+  if (p.in_bf16 == 2) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(static_cast<const __half*>(st.x) +
+                                                      static_cast<size_t>(row) * 256 + lane * 8);
+    const __half2* h = reinterpret_cast<const __half2*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(h[i]);
+      v[2 * i] = f.x;
+      v[2 * i + 1] = f.y;
+    }
+  } else if (p.in_bf16) {
     const uint4 raw = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(st.x) +
                                                       static_cast<size_t>(row) * 256 + lane * 8);
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
@@ -50,6 +62,11 @@ __global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
                                                        static_cast<size_t>(row) * 256 + lane * 8);
     const float4 a = px[0], b = px[1];
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  if (p.copy_f32 && blockIdx.y == 0) {
+    float4* pc = reinterpret_cast<float4*>(p.copy_f32 + static_cast<size_t>(row) * 256 + lane * 8);
+    pc[0] = make_float4(v[0], v[1], v[2], v[3]);
+    pc[1] = make_float4(v[4], v[5], v[6], v[7]);
   }
   float s = 0.f;
 #pragma unroll
@@ -77,10 +94,18 @@ __global__ void __launch_bounds__(256) layernorm256_kernel(const LnParams p) {
 int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
                      const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
                      int L, int C, int in_bf16, cudaStream_t stream) {
+  return layernorm_copy_launch(x0, g0, b0, o0, ld0, c0, x1, g1, b1, o1, ld1, c1, L, C, in_bf16, nullptr, stream);
+}
+
+int layernorm_copy_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
+                          const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
+                          int L, int C, int in_kind, float* copy_f32, cudaStream_t stream) {
+  const int in_bf16 = in_kind;
+  if (in_kind < 0 || in_kind > 2) return set_error(RMEM_ERR_ARG, "layernorm: input kind must be 0 (f32), 1 (bf16), 2 (fp16)");
   if (C != 256 || L < 1 || (ld0 % 8) || (c0 % 8) || (x1 && ((ld1 % 8) || (c1 % 8))))
     return set_error(RMEM_ERR_ARG, "layernorm: C must be 256 and ld/col offsets multiples of 8");
   LnParams p;
-  p.L = L; p.in_bf16 = in_bf16;
+  p.L = L; p.in_bf16 = in_bf16; p.copy_f32 = copy_f32;
   p.s[0] = {x0, g0, b0, static_cast<__nv_bfloat16*>(o0), ld0, c0};
   p.s[1] = {x1, g1, b1, static_cast<__nv_bfloat16*>(o1), ld1, c1};
   dim3 grid((L + 7) / 8, x1 ? 2 : 1);

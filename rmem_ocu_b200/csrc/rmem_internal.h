@@ -97,6 +97,9 @@ int gemm_launch(const void* a, int lda, const void* w, int ldw, const float* bia
                 const rmem_gemm_segment* segs, int n_seg, cudaStream_t stream);
 int gemm_ex_launch(const void* a, int lda, const void* w, int ldw, const float* bias, int M, int N, int K,
                    const rmem_gemm_segment* segs, int n_seg, int ab_f16, cudaStream_t stream);
+int layernorm_copy_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
+                          const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
+                          int L, int C, int in_kind, float* copy_f32, cudaStream_t stream);
 int layernorm_launch(const void* x0, const float* g0, const float* b0, void* o0, int ld0, int c0,
                      const void* x1, const float* g1, const float* b1, void* o1, int ld1, int c1,
                      int L, int C, int in_bf16, cudaStream_t stream);

@@ -821,7 +821,10 @@ class DeAOTEngine:
     def _lstt_forward(self, curr_emb16, is_reference, save_atten_weights, T):
         """DualBranchGPM.forward (transformer.py:765-824): three GatedPropagationModule blocks + output norm."""
         ws, prep = self.ws, self.prep
-        ws.tgt.copy_(self._tokens(curr_emb16))
+        tok = self._tokens(curr_emb16)
+        self._tgt_src = tok if (self.deaot and tok.is_contiguous() and tok.dtype in (BF16, torch.float16)) else None
+        if self._tgt_src is None:
+            ws.tgt.copy_(tok)                 # (the DeAOT block's first LayerNorm makes this copy itself)
         we = self._w_events
         if we is not None and prep.num_layers == 1:
             we["l0"] = we["all"]
@@ -848,7 +851,10 @@ class DeAOTEngine:
             torch.cuda.current_stream().wait_event(we["all"])
             we["waited"] = True
         # norm1 (+ id_norm1 -> curr_ID_V, kept next to id_emb for the write path)
-        if i == 0:
+        if i == 0 and getattr(self, "_tgt_src", None) is not None:
+            # norm1 of layer 0 straight off the encoder's 16-bit embedding; the kernel also starts the fp32 residual stream
+            ops.layernorm_copy(self._tgt_src, *Lw["norm1"], ws.xn, 0, ws.tgt)
+        elif i == 0:
             ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0)
         else:
             ops.layernorm(ws.tgt, *Lw["norm1"], ws.xn, 0, ws.tgt_id, *Lw["id_norm1"], ws.idcat[i], 0)

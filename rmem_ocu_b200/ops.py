@@ -73,6 +73,17 @@ def layernorm(x0, g0, b0, out0, col0=0, x1=None, g1=None, b1=None, out1=None, co
     _count("rmem_layernorm")
 
 
+def layernorm_copy(x, gamma, beta, out, col0, copy_f32):
+    """LN(x) -> bf16 out[:, col0:col0+256] and x itself as f32 into copy_f32 [L, 256]; x [L, 256] f32 / bf16 / fp16."""
+    kind = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[x.dtype]
+    if not x.is_contiguous():
+        raise _lib.RmemError("layernorm_copy: x must be contiguous [L, 256]")
+    L, C = x.shape
+    _lib.check(_lib.lib().rmem_layernorm_copy(_p(x), kind, _p(gamma), _p(beta), _p(out), out.stride(0), col0,
+                                              _p(copy_f32), L, C, _stream()), "rmem_layernorm_copy")
+    _count("rmem_layernorm_copy")
+
+
 def dwconv5(x, xcol0, wt, y, ycol0, h, w, C, S=1):
     """x, y: [S * h * w, ld] token rows of S stacked (h, w) grids."""
     _lib.check(_lib.lib().rmem_dwconv5_batched(_p(x), x.stride(0), xcol0, _p(wt), _p(y), y.stride(0), ycol0, h, w, C,

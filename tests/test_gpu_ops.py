@@ -74,6 +74,23 @@ def test_layernorm_dual(lib_built, in_bf16):
     assert _rel(out[:, :256], r0) < 4e-3 and _rel(out[:, 256:], r1) < 4e-3
 
 
+@pytest.mark.parametrize("dt", [torch.float16, torch.bfloat16, torch.float32])
+def test_layernorm_copy(lib_built, dt):
+    """norm1 of layer 0 straight off the encoder's embedding (rmem_layernorm_copy): LN as bf16 at a column offset and
+    the input itself as the fp32 residual stream, exactly (a widening conversion)."""
+    from rmem_ocu_b200 import ops
+    torch.manual_seed(12)
+    L = 1705
+    x = (torch.randn(L, 256, device="cuda") * 3 + 1).to(dt)
+    g, b = torch.randn(256, device="cuda"), torch.randn(256, device="cuda")
+    out = torch.zeros(L, 512, device="cuda", dtype=torch.bfloat16)
+    tgt = torch.full((L, 256), float("nan"), device="cuda")
+    ops.layernorm_copy(x, g, b, out, 256, tgt)
+    torch.cuda.synchronize()
+    assert torch.equal(tgt, x.float())
+    assert _rel(out[:, 256:], F.layer_norm(x.float(), (256,), g, b, 1e-5)) < 4e-3 and (out[:, :256] == 0).all()
+
+
 @pytest.mark.parametrize("h,w", [(31, 55), (30, 54), (5, 3)])
 def test_dwconv5(lib_built, h, w):
     from rmem_ocu_b200 import ops
