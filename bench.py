@@ -451,7 +451,8 @@ def run_lockstep(model, local_rank, seq_ids, spec, steps, head, prefetch=True):
     def step(f):
         nxt = None
         if prefetch and eng.frames_ahead() <= 1:
-            nxt = torch.cat([img(f + 1 + k) for k in range(la)])          # frame-major [la * S, 3, h, w]
+            # frame-major [la * S, 3, h, w]; one lock-step ahead is the pool's tensor itself (no copy)
+            nxt = img(f + 1) if la == 1 else torch.cat([img(f + 1 + k) for k in range(la)])
         lg = eng.match_propogate_one_frame(img(f), output_size=(h, w), next_img=nxt)
         eng.update_short_term_memory(eng.pred_label if eng.pred_label is not None else ops.argmax_label(lg))
 

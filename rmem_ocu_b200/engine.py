@@ -609,6 +609,8 @@ class DeAOTEngine:
         self.lt_streamk = self.deaot and os_env_flag("RMEM_LT_STREAMK", True)
         self.fused_head = os_env_flag("RMEM_FUSED_HEAD", True)    # decoder tail: GN + ReLU + conv_out + mask in one pass
         self.pred_label = None       # argmax of the last frame's logits at the output size (f32 [S, 1, Ho, Wo]) or None
+        self.ln_copy = os_env_flag("RMEM_LN_COPY", True)          # layer 0's LayerNorm starts the fp32 residual stream
+        self.label_alias = os_env_flag("RMEM_LABEL_ALIAS", True)  # pred_label lives in the write path's label buffer
         self.check_prefetch = os_env_flag("RMEM_CHECK_PREFETCH", False)   # compare each frame with the one encoded ahead
         self.lt_single = os_env_flag("RMEM_LT_SINGLE", True)      # one-launch self-attention (no partials / combine)
         # 0 = one cluster per SM pair; k > 0 caps the clusters so that the short-term branch running beside the
@@ -822,7 +824,8 @@ class DeAOTEngine:
         """DualBranchGPM.forward (transformer.py:765-824): three GatedPropagationModule blocks + output norm."""
         ws, prep = self.ws, self.prep
         tok = self._tokens(curr_emb16)
-        self._tgt_src = tok if (self.deaot and tok.is_contiguous() and tok.dtype in (BF16, torch.float16)) else None
+        self._tgt_src = tok if (self.ln_copy and self.deaot and tok.is_contiguous() and
+                                tok.dtype in (BF16, torch.float16)) else None
         if self._tgt_src is None:
             ws.tgt.copy_(tok)                 # (the DeAOT block's first LayerNorm makes this copy itself)
         we = self._w_events
@@ -1019,7 +1022,7 @@ class DeAOTEngine:
                 shape = (n,) + tuple(output_size)
                 same_size = self.input_size_2d is not None and tuple(output_size) == tuple(self.input_size_2d)
                 have = self._label_buf is not None and tuple(self._label_buf.shape) == shape
-                if same_size and (have or not torch.cuda.is_current_stream_capturing()):
+                if self.label_alias and same_size and (have or not torch.cuda.is_current_stream_capturing()):
                     # at the input resolution the label map is what update_short_term_memory is handed next: written
                     # straight into the buffer the deferred write path reads, so that call copies nothing (the buffer
                     # is never allocated inside a capture: the first propagated frame always runs eagerly)
