@@ -70,7 +70,8 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemS0 = 0;
 constexpr uint32_t kTmemO = 256;
 constexpr float kRescaleThreshold = 8.0f;
-constexpr int kPolyEvery = LT_SK_POLY;     // every n-th pair of exponentials runs on the FMA pipes (MUFU: 16 / clk / SM)
+constexpr int kPolyEvery = LT_SK_POLY;     // every n-th pair of exponentials runs on the FMA pipes (MUFU: 16 / clk / SM);
+                                           // 3, 4, 5 and 8 all measure 35.5 us at L = 1620, T = 5: the exponentials are not the limiter
 
 // words per segment slot of the workspace
 // O partials are bf16: two adjacent columns per 32-bit word, column-pair-major [128][128] so that a warp's 32 rows
