@@ -8,8 +8,11 @@
  * Conventions
  *   - every pointer is a DEVICE pointer unless its name ends in _host; the caller owns all buffers,
  *     the library never allocates device memory; workspaces are passed in;
- *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*) and re-entrant across
- *     streams; no global mutable state besides a thread-local error string;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), launches on the CURRENT device
+ *     (cudaSetDevice is the caller's business) and is re-entrant across streams and host threads.  Process-wide
+ *     state: a thread-local error string; per (kernel, device) "dynamic shared memory opt-in granted" flags
+ *     (atomics); the SM count per device; a few switches read once from the environment (RMEM_PDL,
+ *     RMEM_LOCAL_AGG_VARIANT); and the 256-byte device scratch of rmem_groupnorm_tokens_static (see there);
  *   - return value: RMEM_OK (0) or a negative RMEM_ERR_* code; rmem_last_error() explains it;
  *   - bf16 = IEEE bfloat16 (uint16 storage), f32 = IEEE binary32; row-major, innermost dim last.
  */
