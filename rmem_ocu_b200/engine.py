@@ -457,6 +457,10 @@ def encoder_dtype():
         raise _lib.RmemError("RMEM_ENCODER_DTYPE must be bf16, fp16 or fp32, not %r" % name)
 
 
+class _EmbList(list):
+    """A list of embedding tensors that may carry the `_rmem_static` mark (see DeAOTEngine.encode_static)."""
+
+
 def os_env_flag(name, default):
     import os
     v = os.environ.get(name)
@@ -721,6 +725,16 @@ class DeAOTEngine:
     def encode_image(self, img):
         """ResNet-50 trunk + encoder_projector (cuDNN, bf16 channels-last) -> [x4, x8, x16, emb16]."""
         return self.prep.encoder(img.to(device=self.device, non_blocking=True))
+
+    @_on_device
+    def encode_static(self, img):
+        """encode_image + adapters through this engine's encoder graph: the outputs live at stable addresses, so other
+        engines (the object groups of one sequence) can replay their read graphs on them."""
+        if self._img_sig is not None and (img.dtype, tuple(img.shape)) != self._img_sig:
+            raise _lib.RmemError("frames of one sequence must share the reference frame's dtype and shape")
+        embs = _EmbList(self._run(("enc", 0, 1), self._encode_body, [img.to(self.device, non_blocking=True)]))
+        embs._rmem_static = self.use_cuda_graphs and ("enc", 0, 1) in self._graphs
+        return embs
 
     def _encode_body(self, img):
         """The encoder graph: encode_image + the decoder's adapter convolutions of its shortcuts (they depend on
@@ -1292,6 +1306,12 @@ class DeAOTEngine:
         st = self.st
         if img_embs is not None:
             self._wait_write()
+            if getattr(img_embs, "_rmem_static", False):
+                # embeddings that live at stable addresses (another engine's encoder graph: the object groups of one
+                # DeAOTInferEngine share the backbone pass): the read path replays as a graph on them
+                return self._logits_out(self._run(("read", T, osz, st, "ext"),
+                                                  lambda *e: self._read_body(None, _EmbList(e), T, osz, st),
+                                                  list(img_embs), alias=True))
             return self._logits_out(self._read_body(None, img_embs, T, osz, st))
         # two graphs per frame: the encoder (independent of the previous frame's write path, which may still be
         # running on its own stream) and, after waiting for that write path, LSTT + decoder
@@ -1483,12 +1503,12 @@ class DeAOTInferEngine:
             eng = self.aot_engines[0]
             eng.long_term_mem_gap = self.long_term_mem_gap
             return eng.match_propogate_one_frame(img, mask=mask, output_size=output_size, next_img=next_img)
-        img_embs = None
+        # more than 10 objects: the backbone runs once (first engine's encoder graph: outputs at stable addresses),
+        # every object group replays its own read graph on those embeddings, the logits are merged (aot_engine.py:695-712)
+        img_embs = self.aot_engines[0].encode_static(img)
         all_logits = []
         for engine in self.aot_engines:
             engine.long_term_mem_gap = self.long_term_mem_gap
-            if img_embs is None:
-                img_embs = engine.encode_image(img)
             all_logits.append(engine.match_propogate_one_frame(img, img_embs=img_embs, mask=mask,
                                                                output_size=output_size))
         return self.soft_logit_aggregation(all_logits)

@@ -244,6 +244,8 @@ def test_more_than_ten_objects_vs_oracle(lib_built, monkeypatch):
             eng.update_memory(o_masks[f - 1].float().view(1, 1, H, W).cuda())
     idx = [[list(e.long_memories_indexes) for e in eng.aot_engines]]
     assert len(eng.aot_engines) == 2 == len(oe.aot_engines)
+    # both object groups replay their read paths as CUDA graphs on the shared backbone pass (from the third frame on)
+    assert all(any(k[0] == "read" and k[-1] == "ext" for k in e._graphs) for e in eng.aot_engines)
     assert logits[0].shape[1] == 21                                    # background + 2 x 10 object channels
     assert idx[-1] == [list(e.long_memories_indexes) for e in oe.aot_engines]
     assert int(max(mk.max() for mk in o_masks)) > 10                   # the second group's objects are tracked
