@@ -223,7 +223,8 @@ int rmem_dwconv5(const void* x, int ldx, int xcol0, const float* wt, void* y, in
 /* GroupNorm over an [L][C] token matrix viewed as [1, C, L] (GroupNorm1D, layers/basic.py:6-12):
  * statistics per group over (C/groups channels x L tokens).  Replaces DualBranchGPM's
  * decoder_norms[-1] (transformer.py:806-808).  x = cat(x_a[L][Ca], x_b[L][C-Ca]) f32; out [L][C] bf16, or
- * f32 when out_f32 != 0 (the decoder's convolutions take f32).  Ca, C and C / groups are multiples of 4.
+ * f32 when out_f32 == 1, IEEE fp16 when out_f32 == 2 (whatever the decoder's convolutions take).  Ca, C and C / groups
+ * are multiples of 4.
  *   workspace: 16 * groups + 8 bytes, 8-byte aligned (fp64 sum / sum of squares + an arrival counter); the
  *   caller zero-fills it once, every call leaves it zero again
  */

@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(256)
 gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ xb,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ out_f32, int L, int C, int groups,
-                double* __restrict__ ws) {
+                double* __restrict__ ws, int out_is_f16) {
   pdl_wait();        // programmatic dependent launch: see rmem_internal.h
   pdl_trigger();
   xa += static_cast<size_t>(blockIdx.y) * L * Ca;
@@ -321,6 +321,12 @@ gn_apply_kernel(const float* __restrict__ xa, int Ca, const float* __restrict__ 
                                  (v.z - mean) * rstd * ga.z + be.z, (v.w - mean) * rstd * ga.w + be.w);
     if (out_f32) {
       *reinterpret_cast<float4*>(out_f32 + i * 4) = y;
+    } else if (out_is_f16) {                   // `out` holds IEEE fp16 (the fp16 decoder reads it as it is)
+      const __half2 h0 = __floats2half2_rn(y.x, y.y), h1 = __floats2half2_rn(y.z, y.w);
+      uint2 pk;
+      pk.x = *reinterpret_cast<const uint32_t*>(&h0);
+      pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+      *reinterpret_cast<uint2*>(out + i * 4) = pk;
     } else {
       uint2 pk;
       __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(&pk);
@@ -350,9 +356,9 @@ int groupnorm_tokens_batched_launch(const float* xa, int Ca, const float* xb, co
                                                                       static_cast<double*>(workspace));
   if (int r = check_launch("gn_stats_kernel")) return r;
   launch_k(gn_apply_kernel, dim3((296 + S - 1) / S, S), 256, 0, stream, xa, Ca, xb, gamma, beta,
-                                           out_f32 ? nullptr : static_cast<__nv_bfloat16*>(out),
-                                           out_f32 ? static_cast<float*>(out) : nullptr, L, C, groups,
-                                           static_cast<double*>(workspace));
+                                           out_f32 == 1 ? nullptr : static_cast<__nv_bfloat16*>(out),
+                                           out_f32 == 1 ? static_cast<float*>(out) : nullptr, L, C, groups,
+                                           static_cast<double*>(workspace), out_f32 == 2 ? 1 : 0);
   return check_launch("gn_apply_kernel");
 }
 

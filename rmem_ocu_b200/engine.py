@@ -523,7 +523,7 @@ class _Workspace:
             self.part_o = z(n_chunks, L, 1024, dt=f32)
             self.part_m, self.part_l = z(n_chunks, L, dt=f32), z(n_chunks, L, dt=f32)
         self.mass = z(R * _lib.MAX_BANK, dt=f32)              # layer-0 record_attn_weight, [S][L][T] packed
-        self.gn_out = z(R, 512, dt=f32)                       # f32: feeds the decoder's f32 convolutions as it is
+        self.gn_out = z(R, 512, dt=prep.decoder.dtype)        # in the decoder's activation type: its first convolution reads it as it is
         self.gn_ws = z(5 * S, dt=torch.float64)               # per sequence: 2 x 2 group sums + arrival counter
         self.fg = z(S, L, dt=f32)
         self.id_emb = z(R, 256)

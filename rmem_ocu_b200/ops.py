@@ -95,16 +95,17 @@ def groupnorm_tokens(xa, xb, gamma, beta, out, groups, workspace, S=1):
     """xa / xb / out: [S * L, C] rows of S stacked sequences (statistics per sequence; workspace: S blocks)."""
     L, Ca = xa.shape[0] // S, xa.shape[1]
     C = Ca + (xb.shape[1] if xb is not None else 0)
-    if out.dtype not in (torch.bfloat16, torch.float32):
-        raise _lib.RmemError("groupnorm_tokens: out must be bf16 or f32")
+    kinds = {torch.bfloat16: 0, torch.float32: 1, torch.float16: 2}
+    if out.dtype not in kinds:
+        raise _lib.RmemError("groupnorm_tokens: out must be bf16, f32 or fp16")
+    kind = kinds[out.dtype]
     if S == 1:
-        _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
-                                                    int(out.dtype == torch.float32), L, C, groups, _p(workspace),
-                                                    _stream()), "rmem_groupnorm_tokens")
+        _lib.check(_lib.lib().rmem_groupnorm_tokens(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), kind, L, C, groups,
+                                                    _p(workspace), _stream()), "rmem_groupnorm_tokens")
     else:
-        _lib.check(_lib.lib().rmem_groupnorm_tokens_batched(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out),
-                                                            int(out.dtype == torch.float32), L, C, groups, S,
-                                                            _p(workspace), _stream()), "rmem_groupnorm_tokens_batched")
+        _lib.check(_lib.lib().rmem_groupnorm_tokens_batched(_p(xa), Ca, _p(xb), _p(gamma), _p(beta), _p(out), kind, L, C,
+                                                            groups, S, _p(workspace), _stream()),
+                   "rmem_groupnorm_tokens_batched")
     _count("rmem_groupnorm_tokens")
 
 
