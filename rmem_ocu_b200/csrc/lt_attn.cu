@@ -19,6 +19,7 @@
 //   rmem_lt_attn_combine : merges the chunk partials, adds the per-frame TPE bias
 //       (q'.e_row -- a rank-1 term, so K is never rewritten), emits the per-frame attention mass
 //       W[q,t] (= record_attn_weight), applies the gate U and writes bf16.
+#include <cstdlib>
 #include "sm100_ptx.cuh"
 #include "rmem_internal.h"
 
@@ -63,7 +64,33 @@ struct LtParams {
   // normalises, applies the gate and writes bf16 -- no partials, no combine launch
   const __nv_bfloat16* direct_gate;   // [L][1024] or nullptr
   __nv_bfloat16* direct_out;          // [L][1024]; nullptr = partial mode
+  // direct mode on a 2-CTA cluster (gridDim.z = 2, cluster dims (1, 1, 2)): the CTAs take one half of the keys each;
+  // CTA 1 ships its un-normalised O, m and l into CTA 0's idle K / V rings through distributed shared memory and
+  // CTA 0 merges, normalises, gates and stores -- half the key tiles per CTA, twice the CTAs (104 instead of 52)
+  int direct_pair;
 };
+
+// cluster primitives used by the paired direct mode
+__device__ __forceinline__ uint32_t lt_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void lt_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t lt_map_to_cta(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void lt_st_cluster_f4(uint32_t addr, float4 v) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void lt_st_cluster_f1(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
 
 __global__ void __launch_bounds__(kThreads, 1)
 lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
@@ -151,6 +178,8 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
         tma_load_4d(sV + st * kVBytes, &tm_v, v_full + st, 0, key_begin + j * kBlockN, dv_split * 4, slot);
       }
     }
+    __syncwarp();                                                  // lanes 1..31 wait for the producing lane
+    if (p.direct_pair) { lt_cluster_sync(); lt_cluster_sync(); }   // the two barriers of the paired epilogue (below)
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     // (One issuing warp: giving Q K^T and P V a warp each, as the stream-K kernel does, changed the self-attention from
@@ -208,6 +237,7 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
       if (elect_one()) tc_commit(o_full);
       __syncwarp();
     }
+    if (p.direct_pair) { lt_cluster_sync(); lt_cluster_sync(); }   // the two barriers of the paired epilogue (below)
   } else {
     // ------------------------------------------------------------------ softmax + epilogue
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
@@ -325,7 +355,91 @@ lt_attn_partial_kernel(const __grid_constant__ CUtensorMap tm_q,
     // full-line writes, rows beyond L clipped by the tensor map.
     uint8_t* stage = sK;
     const uint32_t o_addr = tmem_base + lane_addr + kTmemO + hf * (kDVTile / 2);
-    if (p.direct_out != nullptr) {
+    if (p.direct_pair) {
+      // staging in CTA 0's K / V rings: O as [64 column quads][128 rows] float4 (a warp's 32 rows are 512 contiguous
+      // bytes), then m [128] and l [128]
+      const uint32_t rank = lt_cluster_rank();
+      const uint32_t stage_addr = smem_u32(stage);
+      constexpr uint32_t kStageML = kBlockM * kDVTile * 4;
+      lt_cluster_sync();                 // A: both CTAs have passed o_full -- CTA 0's rings are idle
+      if (rank == 1) {
+        const uint32_t remote = lt_map_to_cta(stage_addr, 0);
+#pragma unroll 1
+        for (int cb = 0; cb < kDVTile / 64; ++cb) {
+          uint32_t orow[32];
+          if (n_tiles > 0) {
+            tmem_ld32(o_addr + cb * 32, orow);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) orow[i] = 0u;
+          }
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            const int c4 = hf * 32 + cb * 8 + v;               // column quad of the 256-column tile
+            lt_st_cluster_f4(remote + (static_cast<uint32_t>(c4) * kBlockM + row) * 16,
+                             make_float4(__uint_as_float(orow[4 * v]), __uint_as_float(orow[4 * v + 1]),
+                                         __uint_as_float(orow[4 * v + 2]), __uint_as_float(orow[4 * v + 3])));
+          }
+        }
+        if (hf == 0) {
+          lt_st_cluster_f1(remote + kStageML + row * 4, n_tiles > 0 ? m_used : -INFINITY);
+          lt_st_cluster_f1(remote + kStageML + (kBlockM + row) * 4, n_tiles > 0 ? l_tot : 0.f);
+        }
+      }
+      lt_cluster_sync();                 // B: CTA 1's stores are visible in CTA 0's shared memory
+      if (rank == 0) {
+        const float* ml = reinterpret_cast<const float*>(stage + kStageML);
+        const float m1 = ml[row], l1 = ml[kBlockM + row];
+        const float m0 = n_tiles > 0 ? m_used : -INFINITY, l0 = n_tiles > 0 ? l_tot : 0.f;
+        const float M = fmaxf(m0, m1);
+        const float w0 = m0 == -INFINITY ? 0.f : exp2f(m0 - M), w1 = m1 == -INFINITY ? 0.f : exp2f(m1 - M);
+        const float denom = w0 * l0 + w1 * l1;
+        const float inv = denom > 0.f ? 1.f / denom : 0.f;
+        const float s0 = w0 * inv, s1 = w1 * inv;
+        const size_t base = static_cast<size_t>(q_global) * kDV + dv_split * kDVTile + hf * (kDVTile / 2);
+        const float4* st4p = reinterpret_cast<const float4*>(stage);
+#pragma unroll 1
+        for (int cb = 0; cb < kDVTile / 64; ++cb) {
+          uint32_t orow[32];
+          if (n_tiles > 0) {
+            tmem_ld32(o_addr + cb * 32, orow);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) orow[i] = 0u;
+          }
+          if (row_ok) {
+            uint4 g[4];
+            if (p.direct_gate) {
+#pragma unroll
+              for (int v = 0; v < 4; ++v)
+                g[v] = *reinterpret_cast<const uint4*>(p.direct_gate + base + cb * 32 + v * 8);
+            }
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              const float4 r0 = st4p[(hf * 32 + cb * 8 + 2 * v) * kBlockM + row];
+              const float4 r1 = st4p[(hf * 32 + cb * 8 + 2 * v + 1) * kBlockM + row];
+              const float other[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+              uint32_t w[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float a = __uint_as_float(orow[v * 8 + 2 * e]) * s0 + other[2 * e] * s1;
+                float b = __uint_as_float(orow[v * 8 + 2 * e + 1]) * s0 + other[2 * e + 1] * s1;
+                if (p.direct_gate) {
+                  const uint32_t gw = (&g[v].x)[e];
+                  const __nv_bfloat162 g2 = *reinterpret_cast<const __nv_bfloat162*>(&gw);
+                  a *= __bfloat162float(g2.x);
+                  b *= __bfloat162float(g2.y);
+                }
+                w[e] = pack_bf16x2(a, b);
+              }
+              *reinterpret_cast<uint4*>(p.direct_out + base + cb * 32 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+          }
+        }
+      }
+    } else if (p.direct_out != nullptr) {
       // this thread: row q_global, value channels [dv_split * 256 + hf * 128, +128): 64-byte runs per 32 channels
       const float inv = (n_tiles > 0 && l_tot > 0.f) ? 1.f / l_tot : 0.f;
       const size_t base = static_cast<size_t>(q_global) * kDV + dv_split * kDVTile + hf * (kDVTile / 2);
@@ -569,6 +683,7 @@ int lt_attn_partial_launch(const void* q, const void* kbank, const void* vbank,
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
   p.direct_gate = nullptr;
   p.direct_out = nullptr;
+  p.direct_pair = 0;
   dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, p.n_chunks);
   launch_k(lt_attn_partial_kernel, grid, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, tm_o, p);
   return check_launch("lt_attn_partial_kernel");
@@ -613,9 +728,30 @@ int lt_attn_direct_launch(const void* q, const void* k, const void* v, int L, co
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(kDK));
   p.direct_gate = static_cast<const __nv_bfloat16*>(gate);
   p.direct_out = static_cast<__nv_bfloat16*>(out);
-  dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, 1);
-  launch_k(lt_attn_partial_kernel, grid, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, tm_q /*unused*/, p);
-  return check_launch("lt_attn_partial_kernel (direct)");
+  // more than four key tiles: split the keys over a 2-CTA cluster (RMEM_LT_SINGLE_PAIR=0 keeps one CTA per tile)
+  static const bool pair_on = [] { const char* e = getenv("RMEM_LT_SINGLE_PAIR"); return !(e && e[0] == '0'); }();
+  p.direct_pair = (pair_on && L > 4 * kBlockN) ? 1 : 0;
+  if (!p.direct_pair) {
+    dim3 grid((L + kBlockM - 1) / kBlockM, kDVSplits, 1);
+    launch_k(lt_attn_partial_kernel, grid, kThreads, kSmemTotal, stream, tm_q, tm_k, tm_v, tm_q /*unused*/, p);
+    return check_launch("lt_attn_partial_kernel (direct)");
+  }
+  p.n_chunks = 2;
+  p.chunks_per_frame = 2;              // the existing chunk logic: keys [0, per) and [per, L), per a multiple of 128
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((L + kBlockM - 1) / kBlockM, kDVSplits, 2);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 2;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, lt_attn_partial_kernel, tm_q, tm_k, tm_v, tm_q /*unused*/, p);
+  return check_launch("lt_attn_partial_kernel (direct, paired)");
 }
 
 int lt_attn_combine_launch(const float* part_o, const float* part_m, const float* part_l,
